@@ -1,0 +1,221 @@
+/*
+ * ghost_b200.h — C ABI of the B200-native local-search engine behind GHOST's Solver.
+ *
+ * The reference (richoux/GHOST v3.2.0) has no FFI: its seam is the C++ call
+ *   Solver<T>::fast_search(double&, std::vector<int>&, double timeout_us, Options&)
+ *   (reference include/solver.hpp:431-434), which builds one SearchUnit per thread
+ *   (include/search_unit.hpp:648) and runs SearchUnit::local_search (search_unit.hpp:685).
+ * This header is what a binding for that path binds instead: plain pointers and sizes,
+ * int status codes, no exceptions, no torch / C++ types.
+ *
+ * Every function returns GHOST_B200_OK (0) or a negative GhostStatus; the message of the
+ * last failure on the calling thread is returned by ghost_b200_last_error().
+ * There is NO CPU fallback: a call that needs the GPU fails with GHOST_B200_ERR_CUDA when
+ * no device is present.
+ */
+#ifndef GHOST_B200_H
+#define GHOST_B200_H
+
+#include <stdint.h>
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- status codes --------------------------------------------------------------------- */
+typedef enum GhostStatus {
+	GHOST_B200_OK = 0,
+	GHOST_B200_ERR_INVALID = -1,      /* malformed descriptor / argument                       */
+	GHOST_B200_ERR_UNSUPPORTED = -2,  /* model outside the GPU path (user-defined constraint,   */
+	                                  /* non-integer coefficient, too large for shared memory) */
+	GHOST_B200_ERR_CUDA = -3,         /* CUDA runtime error, or no device                      */
+	GHOST_B200_ERR_NOMEM = -4
+} GhostStatus;
+
+/* ---- constraint / objective kinds ------------------------------------------------------
+ * One value per stock global constraint of the reference (src/global_constraints/):
+ *   all_different.cpp:59-110, linear_equation.cpp:50-74 with the compute_error of
+ *   linear_equation_{eq,neq,leq,geq,l,g}.cpp:54-61, fix_value.cpp:46-64.
+ * GHOST_KIND_USER marks a constraint that is not a stock kind: model_create rejects it
+ * (user-defined virtual constraints are outside the GPU path). */
+typedef enum GhostConstraintKind {
+	GHOST_KIND_ALL_DIFFERENT = 0,
+	GHOST_KIND_LINEAR_EQ = 1,
+	GHOST_KIND_LINEAR_NEQ = 2,
+	GHOST_KIND_LINEAR_LEQ = 3,
+	GHOST_KIND_LINEAR_GEQ = 4,
+	GHOST_KIND_LINEAR_L = 5,
+	GHOST_KIND_LINEAR_G = 6,
+	GHOST_KIND_FIX_VALUE = 7,
+	GHOST_KIND_PURE_OPTIMIZATION = 8, /* include/constraint.hpp:318-334: error 0, delta 0      */
+	GHOST_KIND_ALL_DIFFERENT_ABS_DIFF = 9, /* extension (no stock counterpart): all |x[i+1]-x[i]|
+	                                          over the scope, in scope order, pairwise different;
+	                                          error = sum_values C(count,2)                     */
+	GHOST_KIND_USER = 100
+} GhostConstraintKind;
+
+typedef enum GhostObjectiveKind {
+	GHOST_OBJ_NONE = 0,             /* NullObjective, include/objective.hpp:289-299            */
+	GHOST_OBJ_LINEAR_MINIMIZE = 1,  /* sum coef*x, Minimize (objective.hpp:313-383)             */
+	GHOST_OBJ_LINEAR_MAXIMIZE = 2,  /* sum coef*x, Maximize: cost negated inside the search     */
+	                                /* (src/objective.cpp:60-61), restored at the end           */
+	                                /* (include/solver.hpp:745-749)                             */
+	GHOST_OBJ_USER = 100
+} GhostObjectiveKind;
+
+/* ---- model descriptor: what crosses the seam instead of ghost::Model (include/model.hpp:43-58).
+ * All arrays are caller-owned and copied by ghost_b200_model_create. */
+typedef struct GhostModelDesc {
+	int32_t num_variables;        /* V */
+	int32_t num_constraints;      /* C */
+	int32_t permutation_problem;  /* Model::permutation_problem */
+	int32_t reserved0;
+
+	/* Variable domains (include/variable.hpp:56-63): values of variable v are
+	 * dom_values[dom_offset[v] .. dom_offset[v+1]).  Duplicates are rejected. */
+	const int32_t* dom_offset;    /* [V+1] */
+	const int32_t* dom_values;    /* [dom_offset[V]] */
+	const int32_t* start_value;   /* [V] value each variable holds when the model is built */
+
+	/* Constraints in Model::constraints order, scope in the constraint's own variable order
+	 * (Constraint::_variables_index, include/constraint.hpp:69). */
+	const int32_t* ctr_kind;      /* [C] GhostConstraintKind */
+	const int32_t* ctr_offset;    /* [C+1] */
+	const int32_t* ctr_vars;      /* [ctr_offset[C]] variable ids */
+	const double*  ctr_coefs;     /* [ctr_offset[C]] LinearEquation::_coefficients; ignored for other kinds */
+	const double*  ctr_param;     /* [C] LinearEquation::rhs, or FixValue::_value */
+
+	/* Objective */
+	int32_t objective_kind;       /* GhostObjectiveKind */
+	int32_t num_objective_terms;
+	const int32_t* obj_vars;      /* [num_objective_terms] */
+	const double*  obj_coefs;     /* [num_objective_terms] */
+} GhostModelDesc;
+
+/* ---- search options: POD copy of ghost::Options (include/options.hpp:44-58) after the
+ * "-1 means default" resolution of include/solver.hpp:451-473, plus the fields the GPU
+ * search adds.  Negative values in the first block are resolved by the library exactly as
+ * the reference does. */
+typedef struct GhostSearchOpts {
+	int32_t custom_starting_point;
+	int32_t resume_search;
+	int32_t enable_optimization_guidance;
+	int32_t tabu_time_local_min;
+	int32_t tabu_time_selected;
+	int32_t percent_chance_force_trying_on_plateau;
+	int32_t reset_threshold;
+	int32_t restart_threshold;
+	int32_t number_variables_to_reset;
+	int32_t number_start_samplings;
+
+	/* additions */
+	int32_t number_walkers;       /* parallel restarts on this GPU; <=0: fill the GPU          */
+	int32_t threads_per_walker;   /* 0 = choose from the model; else 32/64/128/256/512/1024     */
+	int32_t epoch_iterations;     /* iterations per walker per kernel launch; <=0: default     */
+	int32_t stop_on_first_solution; /* CSP: stop all walkers once one has sat error 0           */
+	uint64_t seed;                /* Philox key                                                */
+	uint64_t first_walker_id;     /* global id of this GPU's walker 0 (multi-GPU sharding)     */
+	double  timeout_us;           /* wall budget, checked between epochs                       */
+	int64_t max_iterations;       /* per-walker iteration cap; <=0: none (timeout only)        */
+} GhostSearchOpts;
+
+/* Counters: the seven of SearchUnitData (include/search_unit_data.hpp:67-73) plus the
+ * metric's numerator. */
+typedef struct GhostCounters {
+	int64_t search_iterations;
+	int64_t local_moves;
+	int64_t local_minimum;
+	int64_t plateau_moves;
+	int64_t plateau_force_trying_another_variable;
+	int64_t resets;
+	int64_t restarts;
+	int64_t candidates_evaluated;  /* entries of delta_errors (search_unit.hpp:834) summed      */
+} GhostCounters;
+
+typedef struct GhostResult {
+	int32_t found;                /* 1 iff some walker reached satisfaction error 0           */
+	int32_t winner_walker;        /* local index of the walker whose solution is returned     */
+	double  best_sat_error;       /* SearchUnitData::best_sat_error of the winner             */
+	double  best_opt_cost;        /* internal (sign-flipped for Maximize) best_opt_cost       */
+	double  final_cost;           /* what fast_search writes to final_cost (solver.hpp:743-754)*/
+	int32_t* solution;            /* [V] caller-allocated                                     */
+	GhostCounters winner;         /* counters of the winning walker                           */
+	GhostCounters total;          /* summed over all walkers                                  */
+	double  search_time_us;       /* wall time inside the search                              */
+	double  kernel_time_us;       /* device time of the search kernels (CUDA events)          */
+	int64_t kernel_launches;      /* number of kernels launched by this call                  */
+	int32_t threads_per_walker;   /* mapping actually used                                    */
+	int32_t walkers;              /* walkers actually run                                     */
+} GhostResult;
+
+typedef struct GhostModel GhostModel;   /* lowered model, owns device copies on the current device */
+typedef struct GhostSearch GhostSearch; /* walker population on one device */
+
+/* ---- model ------------------------------------------------------------------------------ */
+
+/* Validate + lower a descriptor (host only, no GPU needed).  Replaces ModelBuilder::build_model's
+ * hand-over to SearchUnit (src/model_builder.cpp:39-90, include/search_unit_data.hpp:95-102). */
+int ghost_b200_model_create(const GhostModelDesc* desc, GhostModel** out);
+void ghost_b200_model_destroy(GhostModel* model);
+/* Facts about the lowered model: max candidates of one iteration, bytes of walker state. */
+int ghost_b200_model_info(const GhostModel* model, int32_t* max_candidates, int64_t* walker_state_bytes,
+                          int32_t* default_threads_per_walker);
+
+/* Fill opts with ghost::Options() defaults (src/options.cpp:36-50) and resolve the -1 ones
+ * for a model of V variables as include/solver.hpp:451-473 does. */
+void ghost_b200_default_opts(GhostSearchOpts* opts);
+int ghost_b200_resolve_opts(const GhostModel* model, GhostSearchOpts* opts);
+
+/* ---- parity hook: the move-evaluation unit of work ----------------------------------------
+ * For each of num_walkers assignments x (row-major [W][V]) and its selected variable:
+ *   ctr_error[w][c]  = Constraint::error()               (src/constraint.cpp:57)
+ *   var_error[w][v]  = projected error of v               (adaptive_search_error_projection_algorithm.cpp:40-49)
+ *   cand_delta[w][k] = sum over constraints of simulate_delta for candidate k
+ *                      (include/search_unit.hpp:836-887 + adaptive_search_value_heuristic.cpp:57-58)
+ * Candidate index k: non-permutation -> k-th value of the selected variable's sorted domain;
+ * permutation -> swap partner variable k.  Entries that are not candidates (the current
+ * value; ineligible partners, search_unit.hpp:855-860) hold GHOST_B200_NOT_A_CANDIDATE.
+ * cand_stride = ghost_b200_model_info().max_candidates.  All pointers are HOST memory. */
+#define GHOST_B200_NOT_A_CANDIDATE INT32_MAX
+int ghost_b200_eval_moves(GhostModel* model, int32_t num_walkers,
+                          const int32_t* assignments, const int32_t* selected_var,
+                          int32_t* ctr_error, int32_t* var_error, int32_t* cand_delta);
+/* Same, all pointers DEVICE memory on the current device, asynchronous on `stream`
+ * (a cudaStream_t passed as void*). */
+int ghost_b200_eval_moves_device(GhostModel* model, int32_t num_walkers,
+                                 const int32_t* d_assignments, const int32_t* d_selected_var,
+                                 int32_t* d_ctr_error, int32_t* d_var_error, int32_t* d_cand_delta,
+                                 void* stream);
+
+/* ---- search ------------------------------------------------------------------------------ */
+
+/* Blocking search on the current device: what Solver::fast_search calls instead of spawning
+ * SearchUnits (include/solver.hpp:517-524, 552-587). */
+int ghost_b200_search(GhostModel* model, const GhostSearchOpts* opts, GhostResult* result);
+
+/* Stepwise form used by the multi-GPU driver and the benchmark: begin -> epoch* -> result -> end.
+ * begin allocates the walker population and runs the initial sampling
+ * (search_unit.hpp:711-717); each epoch advances every live walker by `iterations` iterations of
+ * the local_search loop (search_unit.hpp:728-1191) in one kernel launch on `stream`. */
+int ghost_b200_search_begin(GhostModel* model, const GhostSearchOpts* opts, GhostSearch** out);
+int ghost_b200_search_epoch(GhostSearch* search, int32_t iterations, void* stream);
+/* Packed 64-bit key of the best walker so far: smaller is better; see DESIGN.md.  Synchronises. */
+int ghost_b200_search_best_key(GhostSearch* search, uint64_t* key);
+int ghost_b200_search_result(GhostSearch* search, GhostResult* result);
+/* Ask every walker to stop at its next iteration (the analogue of SearchUnit::stop_search,
+ * search_unit.hpp:680). */
+int ghost_b200_search_request_stop(GhostSearch* search);
+void ghost_b200_search_end(GhostSearch* search);
+/* Per-walker outputs for tests: best assignment [W][V], best sat error [W], best opt cost [W],
+ * iterations [W].  Any pointer may be NULL.  Host memory. */
+int ghost_b200_search_walkers(GhostSearch* search, int32_t* best_x, int64_t* best_sat, int64_t* best_opt,
+                              GhostCounters* counters);
+
+const char* ghost_b200_last_error(void);
+const char* ghost_b200_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GHOST_B200_H */

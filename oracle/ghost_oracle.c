@@ -1,0 +1,983 @@
+/*
+ * ghost_oracle.c — TEST INFRASTRUCTURE ONLY (see ghost_oracle.h).  Never shipped, never on the
+ * product path.
+ *
+ * Restates, function by function, the reference's hot path (citations are file:line under the
+ * reference tree, richoux/GHOST v3.2.0).  Arithmetic is done in double exactly where the
+ * reference uses double, so that this file reproduces the reference's numbers, not the GPU's
+ * integer shortcut of them.
+ */
+#include "ghost_oracle.h"
+
+#include <float.h>
+#include <math.h>
+#include <stdlib.h>
+#include <string.h>
+
+/* ------------------------------------------------------------------------------------------
+ * Philox4x32-10 (Salmon et al., "Parallel random numbers: as easy as 1, 2, 3", SC'11).
+ * Not in the reference: replaces thirdparty/randutils.hpp's entropy-seeded mt19937.
+ * ------------------------------------------------------------------------------------------ */
+void oracle_philox4x32_10(const uint32_t ctr_in[4], const uint32_t key_in[2], uint32_t out[4])
+{
+	uint32_t c0 = ctr_in[0], c1 = ctr_in[1], c2 = ctr_in[2], c3 = ctr_in[3];
+	uint32_t k0 = key_in[0], k1 = key_in[1];
+	for (int round = 0; round < 10; ++round) {
+		uint64_t p0 = (uint64_t)0xD2511F53u * c0;
+		uint64_t p1 = (uint64_t)0xCD9E8D57u * c2;
+		uint32_t n0 = (uint32_t)(p1 >> 32) ^ c1 ^ k0;
+		uint32_t n1 = (uint32_t)p1;
+		uint32_t n2 = (uint32_t)(p0 >> 32) ^ c3 ^ k1;
+		uint32_t n3 = (uint32_t)p0;
+		c0 = n0; c1 = n1; c2 = n2; c3 = n3;
+		k0 += 0x9E3779B9u;
+		k1 += 0xBB67AE85u;
+	}
+	out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
+}
+
+typedef struct Rng {
+	uint64_t seed;
+	uint64_t walker;
+	uint64_t next_event;
+} Rng;
+
+/* word `w` (0..3) of the block (event, slot) of this walker's stream */
+static void rng_block(const Rng* r, uint64_t event, uint32_t slot, uint32_t out[4])
+{
+	uint32_t ctr[4] = { (uint32_t)event, (uint32_t)(event >> 32), slot, (uint32_t)r->walker };
+	uint32_t key[2] = { (uint32_t)r->seed, (uint32_t)(r->seed >> 32) ^ (uint32_t)(r->walker >> 32) };
+	oracle_philox4x32_10(ctr, key, out);
+}
+static uint32_t rng_word(const Rng* r, uint64_t event, uint32_t index)
+{
+	uint32_t blk[4];
+	rng_block(r, event, index >> 2, blk);
+	return blk[index & 3];
+}
+/* uniform integer in [0,n): multiply-high (bias <= n/2^32) */
+static uint32_t below(uint32_t word, uint32_t n) { return (uint32_t)(((uint64_t)word * n) >> 32); }
+
+/* ------------------------------------------------------------------------------------------ */
+struct OracleModel {
+	int32_t V, C, permutation;
+	int32_t* dom_off;   /* [V+1] */
+	int32_t* dom;       /* sorted ascending per variable */
+	int32_t* start;
+	int32_t* kind;
+	int32_t* coff;      /* [C+1] */
+	int32_t* cvars;
+	double*  ccoef;
+	double*  cparam;
+	/* matrix_var_ctr (include/search_unit_data.hpp:95-102): for every variable the ascending
+	 * list of constraints containing it */
+	int32_t* v2c_off;   /* [V+1] */
+	int32_t* v2c;       /* constraint ids */
+	int32_t* v2c_pos;   /* position of the variable inside that constraint's scope */
+	/* count tables of the AllDifferent-like constraints */
+	int32_t* cnt_off;   /* [C] offset into a per-walker count array, -1 if none */
+	int32_t* cnt_base;  /* [C] smallest value counted */
+	int32_t* cnt_size;  /* [C] */
+	int32_t  cnt_total;
+	int32_t  obj_kind;
+	double*  obj_coef;  /* dense [V] */
+	int32_t  max_candidates;
+};
+
+static int cmp_i32(const void* a, const void* b)
+{
+	int32_t x = *(const int32_t*)a, y = *(const int32_t*)b;
+	return (x > y) - (x < y);
+}
+
+static int is_alldiff_like(int32_t kind)
+{
+	return kind == GHOST_KIND_ALL_DIFFERENT || kind == GHOST_KIND_ALL_DIFFERENT_ABS_DIFF;
+}
+static int is_linear(int32_t kind) { return kind >= GHOST_KIND_LINEAR_EQ && kind <= GHOST_KIND_LINEAR_G; }
+
+OracleModel* oracle_model_create(const GhostModelDesc* d)
+{
+	OracleModel* m = (OracleModel*)calloc(1, sizeof *m);
+	int32_t V = d->num_variables, C = d->num_constraints;
+	m->V = V; m->C = C; m->permutation = d->permutation_problem;
+	int32_t ndom = d->dom_offset[V], nnz = d->ctr_offset[C];
+	m->dom_off = (int32_t*)malloc(sizeof(int32_t) * (V + 1));
+	m->dom = (int32_t*)malloc(sizeof(int32_t) * (ndom > 0 ? ndom : 1));
+	m->start = (int32_t*)malloc(sizeof(int32_t) * (V > 0 ? V : 1));
+	memcpy(m->dom_off, d->dom_offset, sizeof(int32_t) * (V + 1));
+	memcpy(m->dom, d->dom_values, sizeof(int32_t) * ndom);
+	memcpy(m->start, d->start_value, sizeof(int32_t) * V);
+	int32_t maxdom = 0;
+	for (int v = 0; v < V; ++v) {
+		int32_t n = m->dom_off[v + 1] - m->dom_off[v];
+		qsort(m->dom + m->dom_off[v], n, sizeof(int32_t), cmp_i32);
+		if (n > maxdom) maxdom = n;
+	}
+	m->max_candidates = m->permutation ? V : maxdom;
+	m->kind = (int32_t*)malloc(sizeof(int32_t) * C);
+	m->coff = (int32_t*)malloc(sizeof(int32_t) * (C + 1));
+	m->cvars = (int32_t*)malloc(sizeof(int32_t) * (nnz > 0 ? nnz : 1));
+	m->ccoef = (double*)malloc(sizeof(double) * (nnz > 0 ? nnz : 1));
+	m->cparam = (double*)malloc(sizeof(double) * C);
+	memcpy(m->kind, d->ctr_kind, sizeof(int32_t) * C);
+	memcpy(m->coff, d->ctr_offset, sizeof(int32_t) * (C + 1));
+	memcpy(m->cvars, d->ctr_vars, sizeof(int32_t) * nnz);
+	for (int i = 0; i < nnz; ++i) m->ccoef[i] = d->ctr_coefs ? d->ctr_coefs[i] : 1.0;
+	for (int c = 0; c < C; ++c) m->cparam[c] = d->ctr_param ? d->ctr_param[c] : 0.0;
+
+	/* SearchUnitData::initialize_matrix, include/search_unit_data.hpp:95-102 */
+	m->v2c_off = (int32_t*)calloc(V + 2, sizeof(int32_t));
+	for (int i = 0; i < nnz; ++i) m->v2c_off[m->cvars[i] + 1]++;
+	for (int v = 0; v < V; ++v) m->v2c_off[v + 1] += m->v2c_off[v];
+	m->v2c = (int32_t*)malloc(sizeof(int32_t) * (nnz > 0 ? nnz : 1));
+	m->v2c_pos = (int32_t*)malloc(sizeof(int32_t) * (nnz > 0 ? nnz : 1));
+	int32_t* fill = (int32_t*)calloc(V + 1, sizeof(int32_t));
+	for (int c = 0; c < C; ++c)
+		for (int i = m->coff[c]; i < m->coff[c + 1]; ++i) {
+			int v = m->cvars[i];
+			int at = m->v2c_off[v] + fill[v]++;
+			m->v2c[at] = c;
+			m->v2c_pos[at] = i - m->coff[c];
+		}
+	free(fill);
+
+	m->cnt_off = (int32_t*)malloc(sizeof(int32_t) * C);
+	m->cnt_base = (int32_t*)calloc(C, sizeof(int32_t));
+	m->cnt_size = (int32_t*)calloc(C, sizeof(int32_t));
+	m->cnt_total = 0;
+	for (int c = 0; c < C; ++c) {
+		m->cnt_off[c] = -1;
+		if (!is_alldiff_like(m->kind[c])) continue;
+		int32_t lo = INT32_MAX, hi = INT32_MIN;
+		for (int i = m->coff[c]; i < m->coff[c + 1]; ++i) {
+			int v = m->cvars[i];
+			if (m->dom_off[v + 1] > m->dom_off[v]) {
+				int32_t a = m->dom[m->dom_off[v]], b = m->dom[m->dom_off[v + 1] - 1];
+				if (a < lo) lo = a;
+				if (b > hi) hi = b;
+			}
+			/* start values may lie outside the domain only if the user built it so; include them */
+			if (m->start[v] < lo) lo = m->start[v];
+			if (m->start[v] > hi) hi = m->start[v];
+		}
+		if (lo > hi) { lo = 0; hi = 0; }
+		if (m->kind[c] == GHOST_KIND_ALL_DIFFERENT_ABS_DIFF) { hi = hi - lo; lo = 0; }
+		m->cnt_off[c] = m->cnt_total;
+		m->cnt_base[c] = lo;
+		m->cnt_size[c] = hi - lo + 1;
+		m->cnt_total += m->cnt_size[c];
+	}
+	m->obj_kind = d->objective_kind;
+	m->obj_coef = (double*)calloc(V > 0 ? V : 1, sizeof(double));
+	for (int i = 0; i < d->num_objective_terms; ++i) m->obj_coef[d->obj_vars[i]] += d->obj_coefs[i];
+	return m;
+}
+
+void oracle_model_destroy(OracleModel* m)
+{
+	if (!m) return;
+	free(m->dom_off); free(m->dom); free(m->start); free(m->kind); free(m->coff); free(m->cvars);
+	free(m->ccoef); free(m->cparam); free(m->v2c_off); free(m->v2c); free(m->v2c_pos);
+	free(m->cnt_off); free(m->cnt_base); free(m->cnt_size); free(m->obj_coef);
+	free(m);
+}
+
+int32_t oracle_max_candidates(const OracleModel* m) { return m->max_candidates; }
+
+/* ------------------------------------------------------------------------------------------
+ * Walker = SearchUnit + SearchUnitData + the mutable caches of its private Model copy.
+ * ------------------------------------------------------------------------------------------ */
+typedef struct Walker {
+	const OracleModel* m;
+	GhostSearchOpts opt;
+	Rng rng;
+	int32_t* x;            /* Variable::_current_value */
+	double*  cur_err;      /* Constraint::_current_error */
+	double*  cur_sum;      /* LinearEquation::_current_sum */
+	int32_t* count;        /* AllDifferent::_count, dense */
+	int32_t* tabu;         /* SearchUnitData::tabu_list */
+	double*  err_var;      /* SearchUnitData::error_variables */
+	double best_sat, best_opt, cur_sat, cur_opt;
+	int32_t* best_x;       /* SearchUnit::final_solution */
+	int32_t* cand; int32_t ncand; int must_compute;
+	GhostCounters k;
+	/* scratch */
+	int32_t* scratch_a; int32_t* scratch_b; uint8_t* flag; int32_t* sample;
+	double* deltas;        /* per-constraint deltas of one candidate */
+} Walker;
+
+static int in_domain(const OracleModel* m, int v, int32_t value)
+{
+	/* std::find over the domain (include/search_unit.hpp:857-860) */
+	int32_t lo = m->dom_off[v], hi = m->dom_off[v + 1];
+	while (lo < hi) {
+		int32_t mid = (lo + hi) / 2;
+		if (m->dom[mid] == value) return 1;
+		if (m->dom[mid] < value) lo = mid + 1; else hi = mid;
+	}
+	return 0;
+}
+
+/* AllDifferent::binomial_with_2, src/global_constraints/all_different.cpp:38-47 */
+static double binomial_with_2(int value)
+{
+	if (value <= 1) return 0;
+	if (value % 2 == 0) return (double)(value - 1) * (value / 2);
+	return (double)value * ((value - 1) / 2);
+}
+
+/* LinearEquation*::compute_error: linear_equation_eq.cpp:54-57, _neq.cpp:54-61, _leq.cpp:54-57,
+ * _geq.cpp:54-57, _l.cpp:54-61, _g.cpp:54-61 */
+static double linear_compute_error(int kind, double sum, double rhs)
+{
+	switch (kind) {
+	case GHOST_KIND_LINEAR_EQ:  return fabs(sum - rhs);
+	case GHOST_KIND_LINEAR_NEQ: return rhs == sum ? 1.0 : 0.0;
+	case GHOST_KIND_LINEAR_LEQ: return fmax(0.0, sum - rhs);
+	case GHOST_KIND_LINEAR_GEQ: return fmax(0.0, rhs - sum);
+	case GHOST_KIND_LINEAR_L:   return fmax(0.0, sum - rhs) + (rhs == sum ? 1.0 : 0.0);
+	case GHOST_KIND_LINEAR_G:   return fmax(0.0, rhs - sum) + (rhs == sum ? 1.0 : 0.0);
+	}
+	return 0.0;
+}
+
+/* Constraint::error -> required_error (src/constraint.cpp:57-65).  Rebuilds the constraint's
+ * cache as the reference's mutable members do. */
+static double ctr_error(Walker* w, int c)
+{
+	const OracleModel* m = w->m;
+	int b = m->coff[c], e = m->coff[c + 1];
+	switch (m->kind[c]) {
+	case GHOST_KIND_ALL_DIFFERENT: {
+		/* all_different.cpp:59-75 */
+		int32_t* cnt = w->count + m->cnt_off[c];
+		memset(cnt, 0, sizeof(int32_t) * m->cnt_size[c]);
+		for (int i = b; i < e; ++i) cnt[w->x[m->cvars[i]] - m->cnt_base[c]]++;
+		double counter = 0;
+		for (int t = 0; t < m->cnt_size[c]; ++t)
+			if (cnt[t] > 1) counter += binomial_with_2(cnt[t]);
+		return counter;
+	}
+	case GHOST_KIND_ALL_DIFFERENT_ABS_DIFF: {
+		/* extension: same SOFT_ALLDIFF measure on the |x[i+1]-x[i]| of the scope */
+		int32_t* cnt = w->count + m->cnt_off[c];
+		memset(cnt, 0, sizeof(int32_t) * m->cnt_size[c]);
+		for (int i = b; i + 1 < e; ++i) cnt[abs(w->x[m->cvars[i + 1]] - w->x[m->cvars[i]])]++;
+		double counter = 0;
+		for (int t = 0; t < m->cnt_size[c]; ++t)
+			if (cnt[t] > 1) counter += binomial_with_2(cnt[t]);
+		return counter;
+	}
+	case GHOST_KIND_FIX_VALUE: {
+		/* fix_value.cpp:46-52 */
+		double error = 0.;
+		int value = (int)m->cparam[c];
+		for (int i = b; i < e; ++i) error += abs(w->x[m->cvars[i]] - value);
+		return error;
+	}
+	case GHOST_KIND_PURE_OPTIMIZATION:
+		return 0.; /* include/constraint.hpp:320-323 */
+	default: {
+		/* linear_equation.cpp:50-57 */
+		w->cur_sum[c] = 0.0;
+		for (int i = b; i < e; ++i) w->cur_sum[c] += m->ccoef[i] * w->x[m->cvars[i]];
+		return linear_compute_error(m->kind[c], w->cur_sum[c], m->cparam[c]);
+	}
+	}
+}
+
+/* small multiset of touched count-table entries, to restate all_different.cpp:77-100 without
+ * copying the whole table (the reference copies its std::map; only touched keys matter) */
+typedef struct Touched { int32_t key[16]; int32_t copy[16]; int n; } Touched;
+static int32_t* touched_slot(Touched* t, const int32_t* cnt, int32_t key)
+{
+	for (int i = 0; i < t->n; ++i) if (t->key[i] == key) return &t->copy[i];
+	t->key[t->n] = key; t->copy[t->n] = cnt[key];
+	return &t->copy[t->n++];
+}
+
+/* Constraint::simulate_delta -> delta_error -> optional_delta_error (src/constraint.cpp:91-96,
+ * 67-89).  vars are GLOBAL ids (1 or 2 of them), vals their candidate values. */
+static double ctr_delta(const Walker* w, int c, int n, const int32_t* vars, const int32_t* vals)
+{
+	const OracleModel* m = w->m;
+	switch (m->kind[c]) {
+	case GHOST_KIND_ALL_DIFFERENT: {
+		/* all_different.cpp:77-100 */
+		const int32_t* cnt = w->count + m->cnt_off[c];
+		int32_t base = m->cnt_base[c];
+		Touched t; t.n = 0;
+		double diff = 0.0;
+		for (int i = 0; i < n; ++i) {
+			*touched_slot(&t, cnt, w->x[vars[i]] - base) -= 1;
+			*touched_slot(&t, cnt, vals[i] - base) += 1;
+		}
+		for (int i = 0; i < n; ++i) {
+			int32_t ko = w->x[vars[i]] - base, kn = vals[i] - base;
+			int32_t co = *touched_slot(&t, cnt, ko), cn = *touched_slot(&t, cnt, kn);
+			if (cnt[ko] != co) diff += binomial_with_2(co) - binomial_with_2(cnt[ko]);
+			if (cnt[kn] != cn) diff += binomial_with_2(cn) - binomial_with_2(cnt[kn]);
+		}
+		return diff;
+	}
+	case GHOST_KIND_ALL_DIFFERENT_ABS_DIFF: {
+		/* extension: remove the |differences| of every scope pair touching a changed variable,
+		 * add the new ones, compare C(count,2) over the touched keys (each key once). */
+		const int32_t* cnt = w->count + m->cnt_off[c];
+		int b = m->coff[c], e = m->coff[c + 1];
+		int32_t pairs[8]; int np = 0;
+		for (int i = 0; i < n; ++i)
+			for (int p = b; p < e; ++p)
+				if (m->cvars[p] == vars[i]) {
+					int cand[2] = { p - 1, p };
+					for (int q = 0; q < 2; ++q) {
+						int pp = cand[q];
+						if (pp < b || pp + 1 >= e) continue;
+						int seen = 0;
+						for (int z = 0; z < np; ++z) if (pairs[z] == pp) seen = 1;
+						if (!seen) pairs[np++] = pp;
+					}
+				}
+		Touched t; t.n = 0;
+		for (int z = 0; z < np; ++z) {
+			int va = m->cvars[pairs[z]], vb = m->cvars[pairs[z] + 1];
+			int32_t oa = w->x[va], ob = w->x[vb], na = oa, nb = ob;
+			for (int i = 0; i < n; ++i) { if (vars[i] == va) na = vals[i]; if (vars[i] == vb) nb = vals[i]; }
+			*touched_slot(&t, cnt, abs(ob - oa)) -= 1;
+			*touched_slot(&t, cnt, abs(nb - na)) += 1;
+		}
+		double diff = 0.0;
+		for (int i = 0; i < t.n; ++i)
+			diff += binomial_with_2(t.copy[i]) - binomial_with_2(cnt[t.key[i]]);
+		return diff;
+	}
+	case GHOST_KIND_FIX_VALUE: {
+		/* fix_value.cpp:54-64 */
+		double diff = 0.;
+		int value = (int)m->cparam[c];
+		for (int i = 0; i < n; ++i) diff += abs(vals[i] - value) - abs(w->x[vars[i]] - value);
+		return diff;
+	}
+	case GHOST_KIND_PURE_OPTIMIZATION:
+		return 0.; /* include/constraint.hpp:325-328 */
+	default: {
+		/* linear_equation.cpp:59-69; the coefficient of a variable is looked up by its position */
+		double sum = w->cur_sum[c];
+		for (int i = 0; i < n; ++i) {
+			double coef = 0.0;
+			for (int p = m->coff[c]; p < m->coff[c + 1]; ++p)
+				if (m->cvars[p] == vars[i]) { coef = m->ccoef[p]; break; }
+			sum += coef * (vals[i] - w->x[vars[i]]);
+		}
+		return linear_compute_error(m->kind[c], sum, m->cparam[c]) - w->cur_err[c];
+	}
+	}
+}
+
+/* Constraint::update -> conditional_update_data_structures; must run BEFORE x[var] is overwritten
+ * (all_different.cpp:102-110, linear_equation.cpp:71-74; FixValue has none). */
+static void ctr_update(Walker* w, int c, int var, int32_t new_value)
+{
+	const OracleModel* m = w->m;
+	if (m->kind[c] == GHOST_KIND_ALL_DIFFERENT) {
+		int32_t* cnt = w->count + m->cnt_off[c];
+		cnt[w->x[var] - m->cnt_base[c]] -= 1;
+		cnt[new_value - m->cnt_base[c]] += 1;
+	} else if (is_linear(m->kind[c])) {
+		for (int p = m->coff[c]; p < m->coff[c + 1]; ++p)
+			if (m->cvars[p] == var) { w->cur_sum[c] += m->ccoef[p] * (new_value - w->x[var]); break; }
+	}
+	/* ALL_DIFFERENT_ABS_DIFF: the count table is rebuilt after the value is written, see
+	 * abs_diff_rebuild() — its update needs both neighbours' final values. */
+}
+
+static int ctr_has_variable(const OracleModel* m, int c, int var)
+{
+	/* Constraint::has_variable, src/constraint.cpp:116-119 */
+	for (int p = m->coff[c]; p < m->coff[c + 1]; ++p) if (m->cvars[p] == var) return 1;
+	return 0;
+}
+
+/* Objective::cost (src/objective.cpp:53-64) for the linear objective; internal sign. */
+static double objective_cost(const Walker* w)
+{
+	const OracleModel* m = w->m;
+	double total = 0.0;
+	for (int v = 0; v < m->V; ++v) total += w->x[v] * m->obj_coef[v];
+	if (m->obj_kind == GHOST_OBJ_LINEAR_MAXIMIZE) total = -total;
+	return total;
+}
+static int is_optimization(const OracleModel* m) { return m->obj_kind != GHOST_OBJ_NONE; }
+
+/* SearchUnit::compute_constraints_errors, include/search_unit.hpp:434-447 */
+static double compute_constraints_errors(Walker* w)
+{
+	double satisfaction_error = 0.0;
+	for (int c = 0; c < w->m->C; ++c) {
+		double error = ctr_error(w, c);
+		w->cur_err[c] = error;
+		satisfaction_error += error;
+	}
+	return satisfaction_error;
+}
+
+/* AdaptiveSearchErrorProjection::compute_variable_errors,
+ * src/algorithms/adaptive_search_error_projection_algorithm.cpp:40-49 */
+static void compute_variable_errors(Walker* w)
+{
+	const OracleModel* m = w->m;
+	for (int v = 0; v < m->V; ++v) {
+		w->err_var[v] = 0.;
+		for (int i = m->v2c_off[v]; i < m->v2c_off[v + 1]; ++i) w->err_var[v] += w->cur_err[m->v2c[i]];
+	}
+}
+
+/* ---- sampling ---------------------------------------------------------------------------- */
+
+/* first `n` elements of a uniform shuffle of 0..V-1 == ordered sample without replacement;
+ * drawn by rejection from one RNG event (replaces rng.shuffle, search_unit.hpp:206-208, 239-244) */
+static void sample_distinct(Walker* w, int n, int32_t* out)
+{
+	const OracleModel* m = w->m;
+	uint64_t event = w->rng.next_event++;
+	memset(w->flag, 0, m->V);
+	uint32_t t = 0;
+	for (int got = 0; got < n; ++t) {
+		uint32_t idx = below(rng_word(&w->rng, event, t), (uint32_t)m->V);
+		if (w->flag[idx]) continue;
+		w->flag[idx] = 1;
+		out[got++] = (int32_t)idx;
+	}
+}
+
+/* SearchUnit::monte_carlo_sampling, include/search_unit.hpp:201-212 */
+static void monte_carlo_sampling(Walker* w, int nb_var)
+{
+	const OracleModel* m = w->m;
+	if (nb_var < 0 || nb_var >= m->V) {
+		uint64_t event = w->rng.next_event++;
+		for (int v = 0; v < m->V; ++v) {
+			uint32_t n = (uint32_t)(m->dom_off[v + 1] - m->dom_off[v]);
+			w->x[v] = m->dom[m->dom_off[v] + below(rng_word(&w->rng, event, (uint32_t)v), n)];
+		}
+		return;
+	}
+	sample_distinct(w, nb_var, w->sample);
+	uint64_t event = w->rng.next_event++;
+	for (int i = 0; i < nb_var; ++i) {
+		int v = w->sample[i];
+		uint32_t n = (uint32_t)(m->dom_off[v + 1] - m->dom_off[v]);
+		w->x[v] = m->dom[m->dom_off[v] + below(rng_word(&w->rng, event, (uint32_t)v), n)];
+	}
+}
+
+static void try_swap(Walker* w, int i, int j)
+{
+	/* the four conditions of include/search_unit.hpp:224-231 / 247-254 */
+	const OracleModel* m = w->m;
+	if (i != j && w->x[i] != w->x[j] && in_domain(m, j, w->x[i]) && in_domain(m, i, w->x[j])) {
+		int32_t t = w->x[i]; w->x[i] = w->x[j]; w->x[j] = t;
+	}
+}
+
+/* SearchUnit::random_permutations, include/search_unit.hpp:215-257 */
+static void random_permutations(Walker* w, int nb_var)
+{
+	const OracleModel* m = w->m;
+	if (nb_var < 0) {
+		uint64_t event = w->rng.next_event++;
+		uint32_t blocks = (uint32_t)((m->V + 127) / 128);
+		for (int i = 0; i < m->V - 1; ++i)
+			for (int j = i + 1; j < m->V; ++j) {
+				/* one coin per ordered pair: bit (j mod 128) of block (i, j/128) */
+				uint32_t word = rng_word(&w->rng, event, ((uint32_t)i * blocks + ((uint32_t)j >> 7)) * 4u + (((uint32_t)j >> 5) & 3u));
+				if ((word >> (j & 31)) & 1u) try_swap(w, i, j);
+			}
+		return;
+	}
+	if (nb_var > m->V) nb_var = m->V;
+	sample_distinct(w, nb_var, w->scratch_a);
+	sample_distinct(w, nb_var, w->scratch_b);
+	for (int i = 0; i < nb_var; ++i) try_swap(w, w->scratch_a[i], w->scratch_b[i]);
+}
+
+/* SearchUnit::set_initial_configuration, include/search_unit.hpp:153-198.
+ * Deviation D1 (documented in DESIGN.md): when a sample lowers data.best_sat_error (180-188) the
+ * reference does not copy it to final_solution, so final_solution can lag best_sat_error after a
+ * restart; here best_x is updated together with best_sat so that the returned assignment always
+ * has the returned error. */
+static void set_initial_configuration(Walker* w, int samplings)
+{
+	const OracleModel* m = w->m;
+	double best_so_far = DBL_MAX, current;
+	int32_t* best_values = w->scratch_b + m->V; /* second half of scratch_b */
+	if (samplings < 1) samplings = 1;
+	int loops = 0;
+	do {
+		if (m->permutation) random_permutations(w, -1); else monte_carlo_sampling(w, -1);
+		current = 0.0;
+		for (int c = 0; c < m->C; ++c) current += ctr_error(w, c);
+		if (best_so_far > current) {
+			best_so_far = current;
+			if (w->best_sat > best_so_far) {
+				w->best_sat = best_so_far;
+				memcpy(w->best_x, w->x, sizeof(int32_t) * m->V); /* D1 */
+			}
+			memcpy(best_values, w->x, sizeof(int32_t) * m->V);
+		}
+	} while (++loops < samplings && current > 0.0);
+	memcpy(w->x, best_values, sizeof(int32_t) * m->V);
+}
+
+/* SearchUnit::initialize_variable_values, include/search_unit.hpp:259-272 */
+static void initialize_variable_values(Walker* w)
+{
+	if (w->opt.custom_starting_point || w->opt.resume_search) {
+		if (w->opt.resume_search) w->opt.resume_search = 0;
+		memcpy(w->x, w->m->start, sizeof(int32_t) * w->m->V);
+	} else
+		set_initial_configuration(w, w->opt.number_start_samplings);
+}
+
+/* SearchUnit::initialize_data_structures, include/search_unit.hpp:274-317 */
+static void initialize_data_structures(Walker* w)
+{
+	const OracleModel* m = w->m;
+	w->must_compute = 1;
+	memset(w->tabu, 0, sizeof(int32_t) * m->V);
+	for (int c = 0; c < m->C; ++c) w->cur_err[c] = 0.0;
+	w->cur_sat = compute_constraints_errors(w);
+	if (w->best_sat > w->cur_sat) {
+		w->best_sat = w->cur_sat;
+		memcpy(w->best_x, w->x, sizeof(int32_t) * m->V);
+	}
+	if (is_optimization(m)) {
+		if (w->cur_sat == 0) {
+			w->cur_opt = objective_cost(w);
+			if (w->best_opt > w->cur_opt) {
+				w->best_opt = w->cur_opt;
+				memcpy(w->best_x, w->x, sizeof(int32_t) * m->V);
+			}
+		} else
+			w->cur_opt = DBL_MAX;
+	}
+	compute_variable_errors(w);
+}
+
+/* SearchUnit::reset, include/search_unit.hpp:333-367 */
+static void reset(Walker* w)
+{
+	++w->k.resets;
+	if (w->opt.restart_threshold > 0 && (w->k.resets % w->opt.restart_threshold == 0)) {
+		++w->k.restarts;
+		initialize_variable_values(w);
+	} else {
+		if (w->m->permutation) random_permutations(w, w->opt.number_variables_to_reset);
+		else monte_carlo_sampling(w, w->opt.number_variables_to_reset);
+	}
+	initialize_data_structures(w);
+}
+
+/* AdaptiveSearchVariableCandidatesHeuristic::compute_variable_candidates,
+ * src/algorithms/adaptive_search_variable_candidates_heuristic.cpp:38-60 */
+static void compute_variable_candidates(Walker* w)
+{
+	const OracleModel* m = w->m;
+	double worst = -1;
+	w->ncand = 0;
+	for (int v = 0; v < m->V; ++v)
+		if (worst <= w->err_var[v] && w->tabu[v] <= w->k.local_moves
+		    && (m->v2c_off[v + 1] > m->v2c_off[v] || (is_optimization(m) && w->cur_sat == 0))) {
+			if (worst < w->err_var[v]) {
+				w->ncand = 0;
+				w->cand[w->ncand++] = v;
+				worst = w->err_var[v];
+			} else if (worst == w->err_var[v])
+				w->cand[w->ncand++] = v;
+		}
+}
+
+/* The per-constraint deltas of ONE candidate, in the order the reference produces them
+ * (include/search_unit.hpp:841-848 and 862-885).  Returns their number; `affected` receives the
+ * constraint ids in the same order. */
+static int candidate_deltas(const Walker* w, int v, int candidate, double* deltas, int32_t* affected)
+{
+	const OracleModel* m = w->m;
+	int n = 0;
+	if (!m->permutation) {
+		if (m->v2c_off[v + 1] == m->v2c_off[v]) { deltas[0] = 0.0; if (affected) affected[0] = -1; return 1; }
+		for (int i = m->v2c_off[v]; i < m->v2c_off[v + 1]; ++i) {
+			int c = m->v2c[i];
+			int32_t vars[1] = { v }, vals[1] = { candidate };
+			if (affected) affected[n] = c;
+			deltas[n++] = ctr_delta(w, c, 1, vars, vals);
+		}
+		return n;
+	}
+	int j = candidate;
+	int32_t current_value = w->x[v], candidate_value = w->x[j];
+	for (int i = m->v2c_off[v]; i < m->v2c_off[v + 1]; ++i) {
+		int c = m->v2c[i];
+		if (affected) affected[n] = c;
+		if (ctr_has_variable(m, c, j)) {
+			int32_t vars[2] = { v, j }, vals[2] = { candidate_value, current_value };
+			deltas[n++] = ctr_delta(w, c, 2, vars, vals);
+		} else {
+			int32_t vars[1] = { v }, vals[1] = { candidate_value };
+			deltas[n++] = ctr_delta(w, c, 1, vars, vals);
+		}
+	}
+	for (int i = m->v2c_off[j]; i < m->v2c_off[j + 1]; ++i) {
+		int c = m->v2c[i];
+		if (ctr_has_variable(m, c, v)) continue; /* constraint_checked, search_unit.hpp:883 */
+		int32_t vars[1] = { j }, vals[1] = { current_value };
+		if (affected) affected[n] = c;
+		deltas[n++] = ctr_delta(w, c, 1, vars, vals);
+	}
+	return n;
+}
+
+/* is `k` (value index in the sorted domain / partner variable) a candidate of variable v?
+ * include/search_unit.hpp:831-833 and 855-860 */
+static int is_candidate(const Walker* w, int v, int k, int32_t* key)
+{
+	const OracleModel* m = w->m;
+	if (!m->permutation) {
+		int32_t d = m->dom[m->dom_off[v] + k];
+		*key = d;
+		return d != w->x[v];
+	}
+	*key = k;
+	return k != v && w->x[k] != w->x[v] && in_domain(m, v, w->x[k]) && in_domain(m, k, w->x[v]);
+}
+static int num_candidate_slots(const OracleModel* m, int v)
+{
+	return m->permutation ? m->V : m->dom_off[v + 1] - m->dom_off[v];
+}
+
+/* cumulated delta of every candidate + AdaptiveSearchValueHeuristic::select_value's running min
+ * and tie list (src/algorithms/adaptive_search_value_heuristic.cpp:43-69).  Candidates are
+ * visited in ascending key order like the reference's std::map. */
+static int evaluate_candidates(Walker* w, int v, double* cand_sum /* may be NULL */, int32_t* ties,
+                               double* min_conflict, int32_t* num_candidates)
+{
+	int slots = num_candidate_slots(w->m, v), nties = 0, ncandidates = 0;
+	*min_conflict = DBL_MAX;
+	for (int k = 0; k < slots; ++k) {
+		int32_t key;
+		if (!is_candidate(w, v, k, &key)) { if (cand_sum) cand_sum[k] = NAN; continue; }
+		int n = candidate_deltas(w, v, key, w->deltas, NULL);
+		double sum = 0.0; /* std::accumulate(..., 0.0) */
+		for (int i = 0; i < n; ++i) sum += w->deltas[i];
+		if (cand_sum) cand_sum[k] = sum;
+		++ncandidates;
+		if (*min_conflict > sum) { nties = 0; ties[nties++] = key; *min_conflict = sum; }
+		else if (*min_conflict == sum) ties[nties++] = key;
+	}
+	if (num_candidates) *num_candidates = ncandidates;
+	return nties;
+}
+
+/* SearchUnit::update_errors (include/search_unit.hpp:449-513) + the projection update
+ * (adaptive_search_error_projection_algorithm.cpp:51-58) */
+static void abs_diff_rebuild(Walker* w)
+{
+	/* extension kind: refresh the difference counts after values were written */
+	const OracleModel* m = w->m;
+	for (int c = 0; c < m->C; ++c)
+		if (m->kind[c] == GHOST_KIND_ALL_DIFFERENT_ABS_DIFF) {
+			int32_t* cnt = w->count + m->cnt_off[c];
+			memset(cnt, 0, sizeof(int32_t) * m->cnt_size[c]);
+			for (int i = m->coff[c]; i + 1 < m->coff[c + 1]; ++i)
+				cnt[abs(w->x[m->cvars[i + 1]] - w->x[m->cvars[i]])]++;
+		}
+}
+
+static void update_errors(Walker* w, int v, int new_value)
+{
+	const OracleModel* m = w->m;
+	int32_t* affected = w->scratch_a;
+	int n = candidate_deltas(w, v, new_value, w->deltas, affected);
+	if (!m->permutation) {
+		if (m->v2c_off[v + 1] == m->v2c_off[v]) return;
+		for (int i = 0; i < n; ++i) {
+			int c = affected[i];
+			w->cur_err[c] += w->deltas[i];
+			for (int p = m->coff[c]; p < m->coff[c + 1]; ++p) w->err_var[m->cvars[p]] += w->deltas[i];
+			ctr_update(w, c, v, new_value);
+		}
+		return;
+	}
+	int j = new_value;
+	int32_t current_value = w->x[v], next_value = w->x[j];
+	for (int i = 0; i < n; ++i) {
+		int c = affected[i];
+		w->cur_err[c] += w->deltas[i];
+		for (int p = m->coff[c]; p < m->coff[c + 1]; ++p) w->err_var[m->cvars[p]] += w->deltas[i];
+		if (ctr_has_variable(m, c, v)) {
+			ctr_update(w, c, v, next_value);
+			if (ctr_has_variable(m, c, j)) ctr_update(w, c, j, current_value);
+		} else
+			ctr_update(w, c, j, current_value);
+	}
+}
+
+/* SearchUnit::local_move, include/search_unit.hpp:516-541 */
+static void local_move(Walker* w, int v, int new_value, double min_conflict)
+{
+	++w->k.local_moves;
+	w->cur_sat += min_conflict;
+	w->tabu[v] = w->opt.tabu_time_selected + (int32_t)w->k.local_moves;
+	w->must_compute = 1;
+	update_errors(w, v, new_value);
+	if (w->m->permutation) {
+		int32_t current_value = w->x[v], next_value = w->x[new_value];
+		w->x[v] = next_value;
+		w->x[new_value] = current_value;
+	} else
+		w->x[v] = new_value;
+	abs_diff_rebuild(w);
+}
+
+/* candidate objective cost with the move applied, include/search_unit.hpp:1063-1094 */
+static double candidate_opt_cost(Walker* w, int v, int new_value)
+{
+	double cost;
+	if (w->m->permutation) {
+		int32_t a = w->x[v], b = w->x[new_value];
+		w->x[v] = b; w->x[new_value] = a;
+		cost = objective_cost(w);
+		w->x[v] = a; w->x[new_value] = b;
+	} else {
+		int32_t backup = w->x[v];
+		w->x[v] = new_value;
+		cost = objective_cost(w);
+		w->x[v] = backup;
+	}
+	return cost;
+}
+
+/* Objective::expert_heuristic_value, src/objective.cpp:69-109 (non-permutation COP tie-break) */
+static int heuristic_value(Walker* w, int v, const int32_t* possible, int n, uint32_t word)
+{
+	double min_cost = DBL_MAX;
+	int32_t backup = w->x[v];
+	int32_t* best = w->sample; int nbest = 0;
+	for (int i = 0; i < n; ++i) {
+		w->x[v] = possible[i];
+		double simulated = objective_cost(w);
+		if (min_cost > simulated) { min_cost = simulated; nbest = 0; best[nbest++] = possible[i]; }
+		else if (min_cost == simulated) best[nbest++] = possible[i];
+	}
+	w->x[v] = backup;
+	if (nbest > 0) return best[below(word, (uint32_t)nbest)];
+	if (n > 0) return possible[below(word, (uint32_t)n)];
+	return backup;
+}
+
+static Walker* walker_create(const OracleModel* m, const GhostSearchOpts* opts, uint64_t walker_id)
+{
+	Walker* w = (Walker*)calloc(1, sizeof *w);
+	int V = m->V > 0 ? m->V : 1, C = m->C > 0 ? m->C : 1;
+	w->m = m;
+	if (opts) w->opt = *opts;
+	w->rng.seed = opts ? opts->seed : 0; w->rng.walker = walker_id; w->rng.next_event = 0;
+	w->x = (int32_t*)calloc(V, sizeof(int32_t));
+	w->cur_err = (double*)calloc(C, sizeof(double));
+	w->cur_sum = (double*)calloc(C, sizeof(double));
+	w->count = (int32_t*)calloc(m->cnt_total > 0 ? m->cnt_total : 1, sizeof(int32_t));
+	w->tabu = (int32_t*)calloc(V, sizeof(int32_t));
+	w->err_var = (double*)calloc(V, sizeof(double));
+	w->best_x = (int32_t*)calloc(V, sizeof(int32_t));
+	w->cand = (int32_t*)calloc(V, sizeof(int32_t));
+	int big = V > C ? V : C; if (m->max_candidates > big) big = m->max_candidates;
+	w->scratch_a = (int32_t*)calloc(2 * big + 2, sizeof(int32_t));
+	w->scratch_b = (int32_t*)calloc(2 * big + 2, sizeof(int32_t));
+	w->sample = (int32_t*)calloc(big + 2, sizeof(int32_t));
+	w->flag = (uint8_t*)calloc(V, 1);
+	w->deltas = (double*)calloc(2 * C + 2, sizeof(double));
+	return w;
+}
+static void walker_destroy(Walker* w)
+{
+	free(w->x); free(w->cur_err); free(w->cur_sum); free(w->count); free(w->tabu); free(w->err_var);
+	free(w->best_x); free(w->cand); free(w->scratch_a); free(w->scratch_b); free(w->sample);
+	free(w->flag); free(w->deltas); free(w);
+}
+
+int oracle_eval_moves(const OracleModel* m, const int32_t* x, int32_t v, double* ctr_error_out,
+                      double* var_error_out, double* cand_delta, int32_t* ties, int32_t* num_ties,
+                      double* min_conflict)
+{
+	Walker* w = walker_create(m, NULL, 0);
+	memcpy(w->x, x, sizeof(int32_t) * m->V);
+	compute_constraints_errors(w);
+	compute_variable_errors(w);
+	if (ctr_error_out) memcpy(ctr_error_out, w->cur_err, sizeof(double) * m->C);
+	if (var_error_out) memcpy(var_error_out, w->err_var, sizeof(double) * m->V);
+	if (v >= 0) {
+		int32_t* t = ties ? ties : w->scratch_b;
+		double mc;
+		int n = evaluate_candidates(w, v, cand_delta, t, &mc, NULL);
+		if (num_ties) *num_ties = n;
+		if (min_conflict) *min_conflict = mc;
+	}
+	walker_destroy(w);
+	return 0;
+}
+
+int oracle_check(const OracleModel* m, const int32_t* x, double* sat_error, double* objective)
+{
+	Walker* w = walker_create(m, NULL, 0);
+	memcpy(w->x, x, sizeof(int32_t) * m->V);
+	double e = compute_constraints_errors(w);
+	if (sat_error) *sat_error = e;
+	if (objective) {
+		double c = objective_cost(w);
+		*objective = m->obj_kind == GHOST_OBJ_LINEAR_MAXIMIZE ? -c : c;
+	}
+	walker_destroy(w);
+	return 0;
+}
+
+/* include/solver.hpp:451-473 */
+void oracle_resolve_opts(int32_t V, GhostSearchOpts* o)
+{
+	if (o->tabu_time_local_min < 0) {
+		int a = 5 < V - 1 ? 5 : V - 1;
+		int b = (int)ceil(V / 5); /* integer division first, as in the reference */
+		o->tabu_time_local_min = (a > b ? a : b) + 1;
+	}
+	if (o->tabu_time_selected < 0) o->tabu_time_selected = 0;
+	if (o->percent_chance_force_trying_on_plateau < 0 || o->percent_chance_force_trying_on_plateau > 100)
+		o->percent_chance_force_trying_on_plateau = 10;
+	if (o->reset_threshold < 0) o->reset_threshold = o->tabu_time_local_min;
+	if (o->restart_threshold < 0) o->restart_threshold = V;
+	if (o->number_variables_to_reset < 0) {
+		int n = (int)ceil(V * 0.1);
+		o->number_variables_to_reset = n > 2 ? n : 2;
+	}
+	if (o->number_start_samplings < 0) o->number_start_samplings = 10;
+}
+
+/* SearchUnit::local_search, include/search_unit.hpp:685-1201 */
+int oracle_search(const OracleModel* m, const GhostSearchOpts* opts, uint64_t walker_id,
+                  int64_t max_iterations, int32_t* best_x, double* best_sat, double* best_opt,
+                  GhostCounters* counters, int32_t* final_x,
+                  OracleTraceRow* trace, int64_t trace_cap, int64_t* trace_len)
+{
+	Walker* w = walker_create(m, opts, walker_id);
+	int64_t ntrace = 0;
+	int optimization = is_optimization(m);
+	int32_t* ties = w->scratch_b; /* scratch_b's first half; set_initial_configuration uses the second */
+
+	w->best_sat = DBL_MAX; /* 708-709 */
+	w->best_opt = DBL_MAX;
+	memcpy(w->x, m->start, sizeof(int32_t) * m->V);
+	initialize_variable_values(w);  /* 711 */
+	initialize_data_structures(w);  /* 712 */
+	memcpy(w->best_x, w->x, sizeof(int32_t) * m->V); /* 714-717 */
+
+	while (w->k.search_iterations < max_iterations
+	       && (w->best_sat > 0.0 || (w->best_sat == 0.0 && optimization))) { /* 728-730 */
+		++w->k.search_iterations;
+		OracleTraceRow row; memset(&row, 0, sizeof row);
+		row.iteration = w->k.search_iterations;
+
+		if (w->must_compute) compute_variable_candidates(w); /* 749-750 */
+
+		int ntabu = 0; /* 761-763 */
+		for (int v = 0; v < m->V; ++v) if (w->tabu[v] > w->k.local_moves) ++ntabu;
+		if (ntabu >= w->opt.reset_threshold || w->ncand == 0) {
+			reset(w); /* 769-770 */
+			row.variable = -1; row.branch = 0; row.current_sat_error = w->cur_sat;
+			if (trace && ntrace < trace_cap) trace[ntrace] = row;
+			++ntrace;
+			continue;
+		}
+
+		/* one RNG event per evaluated iteration: word 0 picks the variable (806), word 1 the
+		 * value among ties (adaptive_search_value_heuristic.cpp:80 / objective.cpp:100-101,
+		 * 111-117), word 2 the plateau coin (547) */
+		uint32_t rnd[4];
+		rng_block(&w->rng, w->rng.next_event++, 0, rnd);
+
+		int pick = (int)below(rnd[0], (uint32_t)w->ncand);
+		int v = w->cand[pick];
+		/* erase (826-828); order is irrelevant to a uniform pick, so swap-with-last */
+		w->cand[pick] = w->cand[w->ncand - 1];
+		--w->ncand;
+
+		double min_conflict;
+		int32_t ncandidates = 0;
+		int nties = evaluate_candidates(w, v, NULL, ties, &min_conflict, &ncandidates); /* 831-891 */
+		w->k.candidates_evaluated += ncandidates;
+
+		int new_value;
+		if (nties == 0) new_value = v; /* adaptive_search_value_heuristic.cpp:68-69 */
+		else if (optimization && !m->permutation) new_value = heuristic_value(w, v, ties, nties, rnd[1]);
+		else new_value = ties[below(rnd[1], (uint32_t)nties)];
+
+		row.variable = v; row.new_value = new_value; row.min_conflict = min_conflict;
+		row.num_candidates = ncandidates;
+
+		int plateau = 0;
+		if (min_conflict < 0.0) { /* 1042-1050 */
+			local_move(w, v, new_value, min_conflict);
+			if (optimization) w->cur_opt = objective_cost(w);
+			row.branch = 1;
+		} else if (min_conflict == 0.0) {
+			if (optimization && w->opt.enable_optimization_guidance) { /* 1061-1135 */
+				double cand_opt = candidate_opt_cost(w, v, new_value);
+				if (w->cur_opt > cand_opt) {
+					local_move(w, v, new_value, min_conflict);
+					w->cur_opt = cand_opt;
+					row.branch = 2;
+				} else if (w->cur_opt == cand_opt) plateau = 1;
+				else {
+					/* local_minimum_management, 565-582 */
+					w->must_compute = 0;
+					if (w->ncand == 0) { w->tabu[v] = w->opt.tabu_time_local_min + (int32_t)w->k.local_moves; ++w->k.local_minimum; row.branch = 5; }
+					else row.branch = 6;
+				}
+			} else plateau = 1; /* 1136-1145 */
+		} else { /* 1147-1163 */
+			w->must_compute = 0;
+			if (w->ncand == 0) { w->tabu[v] = w->opt.tabu_time_local_min + (int32_t)w->k.local_moves; ++w->k.local_minimum; row.branch = 5; }
+			else row.branch = 6;
+		}
+		if (plateau) { /* plateau_management, 545-561 */
+			if ((int)below(rnd[2], 100u) + 1 <= w->opt.percent_chance_force_trying_on_plateau) {
+				w->tabu[v] = w->opt.tabu_time_local_min + (int32_t)w->k.local_moves;
+				w->must_compute = 1;
+				++w->k.plateau_force_trying_another_variable;
+				row.branch = 4;
+			} else {
+				local_move(w, v, new_value, 0);
+				++w->k.plateau_moves;
+				row.branch = 3;
+			}
+		}
+
+		if (w->best_sat > w->cur_sat) { /* 1166-1176 */
+			w->best_sat = w->cur_sat;
+			memcpy(w->best_x, w->x, sizeof(int32_t) * m->V);
+		} else if (optimization && w->cur_sat == 0.0 && w->best_opt > w->cur_opt) { /* 1177-1188 */
+			w->best_opt = w->cur_opt;
+			memcpy(w->best_x, w->x, sizeof(int32_t) * m->V);
+		}
+		row.current_sat_error = w->cur_sat;
+		if (trace && ntrace < trace_cap) trace[ntrace] = row;
+		++ntrace;
+	}
+
+	if (best_x) memcpy(best_x, w->best_x, sizeof(int32_t) * m->V);
+	if (final_x) memcpy(final_x, w->x, sizeof(int32_t) * m->V);
+	if (best_sat) *best_sat = w->best_sat;
+	if (best_opt) *best_opt = w->best_opt;
+	if (counters) *counters = w->k;
+	if (trace_len) *trace_len = ntrace;
+	walker_destroy(w);
+	return 0;
+}
