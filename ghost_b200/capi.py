@@ -1,0 +1,191 @@
+"""ctypes binding of libghost_b200.so (include/ghost_b200.h).
+
+This is the call a Python user makes; it goes straight through the C ABI into the sm_100a kernels.
+If the library is missing the import of this module raises: there is no CPU fallback.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+from .modeldesc import (GhostCountersStruct, GhostModelDescStruct, GhostResultStruct, GhostSearchOptsStruct,
+                        ModelDesc, default_opts)
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libghost_b200.so")
+
+
+class GhostError(RuntimeError):
+    def __init__(self, code, message):
+        super().__init__(f"ghost_b200 error {code}: {message}")
+        self.code = code
+        self.message = message
+
+
+OK, ERR_INVALID, ERR_UNSUPPORTED, ERR_CUDA, ERR_NOMEM = 0, -1, -2, -3, -4
+
+
+def _load():
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(
+            f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            "(nvcc, sm_100a). ghost_b200 has no CPU fallback.")
+    lib = C.CDLL(LIB_PATH)
+    vp, i32, i64 = C.c_void_p, C.c_int32, C.c_int64
+    lib.ghost_b200_last_error.restype = C.c_char_p
+    lib.ghost_b200_version.restype = C.c_char_p
+    lib.ghost_b200_model_create.argtypes = [C.POINTER(GhostModelDescStruct), C.POINTER(vp)]
+    lib.ghost_b200_model_destroy.argtypes = [vp]
+    lib.ghost_b200_model_destroy.restype = None
+    lib.ghost_b200_model_info.argtypes = [vp, C.POINTER(i32), C.POINTER(i64), C.POINTER(i32)]
+    lib.ghost_b200_default_opts.argtypes = [C.POINTER(GhostSearchOptsStruct)]
+    lib.ghost_b200_default_opts.restype = None
+    lib.ghost_b200_resolve_opts.argtypes = [vp, C.POINTER(GhostSearchOptsStruct)]
+    lib.ghost_b200_eval_moves.argtypes = [vp, i32, vp, vp, vp, vp, vp]
+    lib.ghost_b200_eval_moves_device.argtypes = [vp, i32, vp, vp, vp, vp, vp, vp]
+    lib.ghost_b200_search.argtypes = [vp, C.POINTER(GhostSearchOptsStruct), C.POINTER(GhostResultStruct)]
+    lib.ghost_b200_search_begin.argtypes = [vp, C.POINTER(GhostSearchOptsStruct), C.POINTER(vp)]
+    lib.ghost_b200_search_epoch.argtypes = [vp, i32, vp]
+    lib.ghost_b200_search_best_key.argtypes = [vp, C.POINTER(C.c_uint64)]
+    lib.ghost_b200_search_result.argtypes = [vp, C.POINTER(GhostResultStruct)]
+    lib.ghost_b200_search_request_stop.argtypes = [vp]
+    lib.ghost_b200_search_end.argtypes = [vp]
+    lib.ghost_b200_search_end.restype = None
+    lib.ghost_b200_search_walkers.argtypes = [vp, vp, vp, vp, vp]
+    lib.ghost_b200_search_trace.argtypes = [vp, vp, i32, C.POINTER(i32)]
+    return lib
+
+
+lib = _load()
+
+
+def _check(rc):
+    if rc != 0:
+        raise GhostError(rc, lib.ghost_b200_last_error().decode())
+
+
+def version():
+    return lib.ghost_b200_version().decode()
+
+
+def _ptr(a):
+    return None if a is None else a.ctypes.data
+
+
+class Model:
+    """Lowered model handle (GhostModel*).  Creating it needs no GPU; using it does."""
+
+    def __init__(self, desc: ModelDesc):
+        self.desc = desc
+        s, keep = desc.to_struct()
+        h = C.c_void_p()
+        _check(lib.ghost_b200_model_create(C.byref(s), C.byref(h)))
+        self.h = h
+        self.V, self.C = s.num_variables, s.num_constraints
+        mc, wb, tpw = C.c_int32(), C.c_int64(), C.c_int32()
+        _check(lib.ghost_b200_model_info(self.h, C.byref(mc), C.byref(wb), C.byref(tpw)))
+        self.max_candidates = mc.value
+        self.walker_state_bytes = wb.value
+        self.default_threads_per_walker = tpw.value
+
+    def close(self):
+        if getattr(self, "h", None):
+            lib.ghost_b200_model_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        self.close()
+
+    def resolve_opts(self, opts: GhostSearchOptsStruct):
+        _check(lib.ghost_b200_resolve_opts(self.h, C.byref(opts)))
+        return opts
+
+    # -- parity hook, host buffers --
+    def eval_moves(self, assignments, selected_var):
+        x = np.ascontiguousarray(assignments, dtype=np.int32).reshape(-1, self.V)
+        W = x.shape[0]
+        sel = np.ascontiguousarray(selected_var, dtype=np.int32).reshape(W)
+        ce = np.empty((W, self.C), dtype=np.int32)
+        ve = np.empty((W, self.V), dtype=np.int32)
+        cd = np.empty((W, self.max_candidates), dtype=np.int32)
+        _check(lib.ghost_b200_eval_moves(self.h, W, _ptr(x), _ptr(sel), _ptr(ce), _ptr(ve), _ptr(cd)))
+        return dict(ctr_error=ce, var_error=ve, cand_delta=cd)
+
+    # -- parity hook, device pointers (torch tensors or raw ints) --
+    def eval_moves_device(self, W, d_x, d_sel, d_ce, d_ve, d_cd, stream=0):
+        _check(lib.ghost_b200_eval_moves_device(self.h, W, d_x, d_sel, d_ce, d_ve, d_cd, stream))
+
+    def search(self, opts: GhostSearchOptsStruct):
+        """Blocking search; what Solver::fast_search calls."""
+        sol = np.zeros(self.V, dtype=np.int32)
+        res = GhostResultStruct()
+        res.solution = sol.ctypes.data_as(C.POINTER(C.c_int32))
+        _check(lib.ghost_b200_search(self.h, C.byref(opts), C.byref(res)))
+        return _result_dict(res, sol)
+
+    def begin(self, opts: GhostSearchOptsStruct):
+        return Search(self, opts)
+
+
+def _result_dict(res, sol):
+    return dict(found=bool(res.found), winner_walker=res.winner_walker, best_sat_error=res.best_sat_error,
+                best_opt_cost=res.best_opt_cost, final_cost=res.final_cost, solution=sol,
+                winner=res.winner.as_dict(), total=res.total.as_dict(), search_time_us=res.search_time_us,
+                kernel_time_us=res.kernel_time_us, kernel_launches=res.kernel_launches,
+                threads_per_walker=res.threads_per_walker, walkers=res.walkers)
+
+
+class Search:
+    """Stepwise search (GhostSearch*): begin -> epoch* -> result -> end."""
+
+    def __init__(self, model: Model, opts: GhostSearchOptsStruct):
+        self.model = model
+        h = C.c_void_p()
+        _check(lib.ghost_b200_search_begin(model.h, C.byref(opts), C.byref(h)))
+        self.h = h
+
+    def epoch(self, iterations, stream=0):
+        _check(lib.ghost_b200_search_epoch(self.h, int(iterations), stream))
+
+    def best_key(self):
+        k = C.c_uint64()
+        _check(lib.ghost_b200_search_best_key(self.h, C.byref(k)))
+        return k.value
+
+    def request_stop(self):
+        _check(lib.ghost_b200_search_request_stop(self.h))
+
+    def result(self):
+        sol = np.zeros(self.model.V, dtype=np.int32)
+        res = GhostResultStruct()
+        res.solution = sol.ctypes.data_as(C.POINTER(C.c_int32))
+        _check(lib.ghost_b200_search_result(self.h, C.byref(res)))
+        return _result_dict(res, sol)
+
+    def walkers(self, W):
+        best_x = np.zeros((W, self.model.V), dtype=np.int32)
+        best_sat = np.zeros(W, dtype=np.int64)
+        best_opt = np.zeros(W, dtype=np.int64)
+        counters = (GhostCountersStruct * W)()
+        _check(lib.ghost_b200_search_walkers(self.h, _ptr(best_x), _ptr(best_sat), _ptr(best_opt),
+                                             C.cast(counters, C.c_void_p)))
+        return dict(best_x=best_x, best_sat=best_sat, best_opt=best_opt, counters=[c.as_dict() for c in counters])
+
+    def trace(self, cap):
+        rows = np.zeros((cap, 8), dtype=np.int32)
+        n = C.c_int32()
+        _check(lib.ghost_b200_search_trace(self.h, _ptr(rows), cap, C.byref(n)))
+        return rows[:min(n.value, cap)]
+
+    def end(self):
+        if getattr(self, "h", None):
+            lib.ghost_b200_search_end(self.h)
+            self.h = None
+
+    def __del__(self):
+        self.end()
+
+
+__all__ = ["Model", "Search", "GhostError", "default_opts", "version", "lib", "LIB_PATH"]

@@ -1,0 +1,488 @@
+// capi.cu — the C ABI of include/ghost_b200.h over the sm_100a kernels.
+// Every entry point fails loudly (negative status + message) when CUDA is unavailable: there is
+// no CPU path in this library.
+#include <chrono>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <limits>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include <cuda_runtime.h>
+
+#include "kernels.cuh"
+
+using namespace ghost_b200;
+
+static thread_local std::string g_last_error;
+static int set_error(int code, const std::string& msg) { g_last_error = msg; return code; }
+#define CUDA_TRY(expr)                                                                                   \
+	do {                                                                                                 \
+		cudaError_t _e = (expr);                                                                         \
+		if (_e != cudaSuccess)                                                                           \
+			return set_error(GHOST_B200_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(_e));   \
+	} while (0)
+
+struct GhostModel {
+	LoweredModel low;
+	int device = -1;          // device holding d_blob, -1: not uploaded yet
+	int32_t* d_blob = nullptr;
+	int sm_count = 0;
+	int max_smem_optin = 0;
+};
+
+struct GhostSearch {
+	GhostModel* model = nullptr;
+	GhostSearchOpts opts{};
+	WalkerLayout layout{};
+	int T = 32, walkers = 0, walkers_per_cta = 1, grid = 0, block = 0;
+	size_t smem = 0;
+	unsigned char* d_state = nullptr;
+	WalkerScalars* d_scalars = nullptr;
+	int* d_best_x = nullptr;
+	int* d_stop = nullptr;
+	unsigned long long* d_best_key = nullptr;
+	int* d_trace = nullptr; int* d_trace_len = nullptr; int trace_cap = 0;
+	cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+	double kernel_ms = 0.0;
+	int64_t launches = 0;
+	std::chrono::steady_clock::time_point t_begin;
+};
+
+extern "C" const char* ghost_b200_last_error(void) { return g_last_error.c_str(); }
+extern "C" const char* ghost_b200_version(void) { return "ghost_b200 0.1 (sm_100a)"; }
+
+extern "C" int ghost_b200_model_create(const GhostModelDesc* desc, GhostModel** out)
+{
+	if (!out) return set_error(GHOST_B200_ERR_INVALID, "out is null");
+	*out = nullptr;
+	GhostModel* gm = new (std::nothrow) GhostModel();
+	if (!gm) return set_error(GHOST_B200_ERR_NOMEM, "out of host memory");
+	std::string why;
+	int rc = lower_model(desc, &gm->low, &why);
+	if (rc != GHOST_B200_OK) { delete gm; return set_error(rc, why); }
+	*out = gm;
+	return GHOST_B200_OK;
+}
+
+extern "C" void ghost_b200_model_destroy(GhostModel* gm)
+{
+	if (!gm) return;
+	if (gm->d_blob) cudaFree(gm->d_blob);
+	delete gm;
+}
+
+extern "C" int ghost_b200_model_info(const GhostModel* gm, int32_t* max_candidates, int64_t* walker_state_bytes,
+                                     int32_t* default_threads_per_walker)
+{
+	if (!gm) return set_error(GHOST_B200_ERR_INVALID, "model is null");
+	if (max_candidates) *max_candidates = gm->low.dev.max_candidates;
+	if (walker_state_bytes) *walker_state_bytes = gm->low.layout(32, std::max(2, (int)std::ceil(gm->low.V * 0.1))).total_bytes;
+	if (default_threads_per_walker) *default_threads_per_walker = gm->low.default_threads_per_walker();
+	return GHOST_B200_OK;
+}
+
+extern "C" void ghost_b200_default_opts(GhostSearchOpts* o)
+{
+	// ghost::Options::Options(), reference src/options.cpp:36-50
+	std::memset(o, 0, sizeof *o);
+	o->custom_starting_point = 0;
+	o->resume_search = 0;
+	o->enable_optimization_guidance = 1;
+	o->tabu_time_local_min = -1;
+	o->tabu_time_selected = -1;
+	o->percent_chance_force_trying_on_plateau = -1;
+	o->reset_threshold = -1;
+	o->restart_threshold = -1;
+	o->number_variables_to_reset = -1;
+	o->number_start_samplings = -1;
+	o->stop_on_first_solution = 1;
+}
+
+extern "C" int ghost_b200_resolve_opts(const GhostModel* gm, GhostSearchOpts* o)
+{
+	if (!gm || !o) return set_error(GHOST_B200_ERR_INVALID, "null argument");
+	// reference include/solver.hpp:451-473
+	const int V = gm->low.V;
+	if (o->tabu_time_local_min < 0)
+		o->tabu_time_local_min = std::max(std::min(5, V - 1), static_cast<int>(std::ceil(V / 5))) + 1;
+	if (o->tabu_time_selected < 0) o->tabu_time_selected = 0;
+	if (o->percent_chance_force_trying_on_plateau < 0 || o->percent_chance_force_trying_on_plateau > 100)
+		o->percent_chance_force_trying_on_plateau = 10;
+	if (o->reset_threshold < 0) o->reset_threshold = o->tabu_time_local_min;
+	if (o->restart_threshold < 0) o->restart_threshold = V;
+	if (o->number_variables_to_reset < 0)
+		o->number_variables_to_reset = std::max(2, static_cast<int>(std::ceil(V * 0.1)));
+	if (o->number_start_samplings < 0) o->number_start_samplings = 10;
+	return GHOST_B200_OK;
+}
+
+static int ensure_uploaded(GhostModel* gm)
+{
+	int dev = -1;
+	CUDA_TRY(cudaGetDevice(&dev));
+	if (gm->d_blob && gm->device == dev) return GHOST_B200_OK;
+	if (gm->d_blob) return set_error(GHOST_B200_ERR_INVALID, "model was uploaded on another device; create one model per device");
+	size_t bytes = gm->low.blob.size() * sizeof(int32_t);
+	CUDA_TRY(cudaMalloc(&gm->d_blob, bytes));
+	CUDA_TRY(cudaMemcpy(gm->d_blob, gm->low.blob.data(), bytes, cudaMemcpyHostToDevice));
+	gm->low.dev.blob = gm->d_blob;
+	gm->device = dev;
+	CUDA_TRY(cudaDeviceGetAttribute(&gm->sm_count, cudaDevAttrMultiProcessorCount, dev));
+	CUDA_TRY(cudaDeviceGetAttribute(&gm->max_smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
+	return GHOST_B200_OK;
+}
+
+// ---- launch configuration -----------------------------------------------------------------------
+struct LaunchCfg { int T, walkers_per_cta, block; size_t smem; };
+
+static int pick_launch(const GhostModel* gm, const WalkerLayout& L, int requested_T, LaunchCfg* cfg)
+{
+	int T = requested_T > 0 ? requested_T : gm->low.default_threads_per_walker();
+	if (!(T == 32 || T == 64 || T == 128 || T == 256 || T == 512))
+		return set_error(GHOST_B200_ERR_INVALID, "threads_per_walker must be 32, 64, 128, 256 or 512");
+	int wpc = 1;
+	if (T == 32) {
+		// several warp-walkers per CTA, bounded by shared memory
+		wpc = 4;
+		while (wpc > 1 && (size_t)wpc * L.total_bytes > (size_t)gm->max_smem_optin) wpc >>= 1;
+	}
+	size_t smem = (size_t)wpc * L.total_bytes;
+	if (smem > (size_t)gm->max_smem_optin)
+		return set_error(GHOST_B200_ERR_UNSUPPORTED, "walker state needs " + std::to_string(L.total_bytes) +
+		                 " bytes of shared memory; the device offers " + std::to_string(gm->max_smem_optin));
+	cfg->T = T; cfg->walkers_per_cta = wpc; cfg->block = T == 32 ? 32 * wpc : T; cfg->smem = smem;
+	return GHOST_B200_OK;
+}
+
+template <typename K>
+static cudaError_t allow_smem(K kernel, size_t smem)
+{
+	return cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+}
+
+static cudaError_t launch_search(int T, int grid, int block, size_t smem, cudaStream_t st, const DevModel& m,
+                                 const WalkerLayout& L, const SearchParams& p)
+{
+	cudaError_t e;
+	switch (T) {
+#define GB_CASE(TT)                                                                          \
+	case TT:                                                                                 \
+		e = allow_smem(search_kernel<TT>, smem);                                             \
+		if (e != cudaSuccess) return e;                                                      \
+		search_kernel<TT><<<grid, block, smem, st>>>(m, L, p);                               \
+		break;
+		GB_CASE(32) GB_CASE(64) GB_CASE(128) GB_CASE(256) GB_CASE(512)
+#undef GB_CASE
+	default: return cudaErrorInvalidValue;
+	}
+	return cudaGetLastError();
+}
+
+static cudaError_t launch_eval(int T, int grid, int block, size_t smem, cudaStream_t st, const DevModel& m,
+                               const WalkerLayout& L, int W, const int* x, const int* sel, int* ce, int* ve, int* cd)
+{
+	cudaError_t e;
+	switch (T) {
+#define GB_CASE(TT)                                                                          \
+	case TT:                                                                                 \
+		e = allow_smem(eval_kernel<TT>, smem);                                               \
+		if (e != cudaSuccess) return e;                                                      \
+		eval_kernel<TT><<<grid, block, smem, st>>>(m, L, W, x, sel, ce, ve, cd);             \
+		break;
+		GB_CASE(32) GB_CASE(64) GB_CASE(128) GB_CASE(256) GB_CASE(512)
+#undef GB_CASE
+	default: return cudaErrorInvalidValue;
+	}
+	return cudaGetLastError();
+}
+
+// ---- parity hook --------------------------------------------------------------------------------
+static int g_eval_threads = 0; // test knob: force a mapping (0 = default), set through the env
+
+extern "C" int ghost_b200_eval_moves_device(GhostModel* gm, int32_t W, const int32_t* d_x, const int32_t* d_sel,
+                                            int32_t* d_ce, int32_t* d_ve, int32_t* d_cd, void* stream)
+{
+	if (!gm || W <= 0 || !d_x) return set_error(GHOST_B200_ERR_INVALID, "bad argument to eval_moves");
+	int rc = ensure_uploaded(gm);
+	if (rc) return rc;
+	const char* env = std::getenv("GHOST_B200_EVAL_THREADS");
+	int T = env ? std::atoi(env) : g_eval_threads;
+	WalkerLayout L = gm->low.layout(T, 2);
+	LaunchCfg cfg;
+	rc = pick_launch(gm, L, T, &cfg);
+	if (rc) return rc;
+	int grid = (W + cfg.walkers_per_cta - 1) / cfg.walkers_per_cta;
+	CUDA_TRY(launch_eval(cfg.T, grid, cfg.block, cfg.smem, (cudaStream_t)stream, gm->low.dev, L, W, d_x, d_sel, d_ce, d_ve, d_cd));
+	return GHOST_B200_OK;
+}
+
+extern "C" int ghost_b200_eval_moves(GhostModel* gm, int32_t W, const int32_t* x, const int32_t* sel,
+                                     int32_t* ce, int32_t* ve, int32_t* cd)
+{
+	if (!gm || W <= 0 || !x) return set_error(GHOST_B200_ERR_INVALID, "bad argument to eval_moves");
+	int rc = ensure_uploaded(gm);
+	if (rc) return rc;
+	const DevModel& m = gm->low.dev;
+	int *d_x = nullptr, *d_sel = nullptr, *d_ce = nullptr, *d_ve = nullptr, *d_cd = nullptr;
+	auto cleanup = [&]() { cudaFree(d_x); cudaFree(d_sel); cudaFree(d_ce); cudaFree(d_ve); cudaFree(d_cd); };
+	size_t nx = (size_t)W * m.V, nc = (size_t)W * m.C, nd = (size_t)W * m.max_candidates;
+#define TRY_OR_CLEAN(expr) do { cudaError_t _e = (expr); if (_e != cudaSuccess) { cleanup(); return set_error(GHOST_B200_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(_e)); } } while (0)
+	TRY_OR_CLEAN(cudaMalloc(&d_x, nx * 4));
+	TRY_OR_CLEAN(cudaMemcpy(d_x, x, nx * 4, cudaMemcpyHostToDevice));
+	if (sel) { TRY_OR_CLEAN(cudaMalloc(&d_sel, (size_t)W * 4)); TRY_OR_CLEAN(cudaMemcpy(d_sel, sel, (size_t)W * 4, cudaMemcpyHostToDevice)); }
+	if (ce) TRY_OR_CLEAN(cudaMalloc(&d_ce, nc * 4));
+	if (ve) TRY_OR_CLEAN(cudaMalloc(&d_ve, nx * 4));
+	if (cd && sel) TRY_OR_CLEAN(cudaMalloc(&d_cd, nd * 4));
+	rc = ghost_b200_eval_moves_device(gm, W, d_x, d_sel, d_ce, d_ve, d_cd, nullptr);
+	if (rc) { cleanup(); return rc; }
+	TRY_OR_CLEAN(cudaDeviceSynchronize());
+	if (ce) TRY_OR_CLEAN(cudaMemcpy(ce, d_ce, nc * 4, cudaMemcpyDeviceToHost));
+	if (ve) TRY_OR_CLEAN(cudaMemcpy(ve, d_ve, nx * 4, cudaMemcpyDeviceToHost));
+	if (cd && sel) TRY_OR_CLEAN(cudaMemcpy(cd, d_cd, nd * 4, cudaMemcpyDeviceToHost));
+#undef TRY_OR_CLEAN
+	cleanup();
+	return GHOST_B200_OK;
+}
+
+// ---- search -------------------------------------------------------------------------------------
+extern "C" void ghost_b200_search_end(GhostSearch* s)
+{
+	if (!s) return;
+	cudaFree(s->d_state); cudaFree(s->d_scalars); cudaFree(s->d_best_x); cudaFree(s->d_stop);
+	cudaFree(s->d_best_key); cudaFree(s->d_trace); cudaFree(s->d_trace_len);
+	if (s->ev0) cudaEventDestroy(s->ev0);
+	if (s->ev1) cudaEventDestroy(s->ev1);
+	delete s;
+}
+
+extern "C" int ghost_b200_search_begin(GhostModel* gm, const GhostSearchOpts* opts_in, GhostSearch** out)
+{
+	if (!gm || !opts_in || !out) return set_error(GHOST_B200_ERR_INVALID, "null argument to search_begin");
+	*out = nullptr;
+	int rc = ensure_uploaded(gm);
+	if (rc) return rc;
+	GhostSearch* s = new (std::nothrow) GhostSearch();
+	if (!s) return set_error(GHOST_B200_ERR_NOMEM, "out of host memory");
+	s->model = gm;
+	s->opts = *opts_in;
+	ghost_b200_resolve_opts(gm, &s->opts);
+	const DevModel& m = gm->low.dev;
+	if (s->opts.number_variables_to_reset > m.V) s->opts.number_variables_to_reset = m.V;
+	s->layout = gm->low.layout(s->opts.threads_per_walker, s->opts.number_variables_to_reset);
+	LaunchCfg cfg;
+	rc = pick_launch(gm, s->layout, s->opts.threads_per_walker, &cfg);
+	if (rc) { delete s; return rc; }
+	s->T = cfg.T; s->walkers_per_cta = cfg.walkers_per_cta; s->block = cfg.block; s->smem = cfg.smem;
+	if (s->opts.number_walkers <= 0) {
+		// fill the GPU: as many CTAs as are resident at once, by shared memory and threads
+		int by_smem = (int)std::max<size_t>(1, (size_t)(227 * 1024) / std::max<size_t>(1, cfg.smem + 1024));
+		int by_threads = std::max(1, 2048 / cfg.block);
+		int ctas_per_sm = std::min(std::min(by_smem, by_threads), 32);
+		s->opts.number_walkers = gm->sm_count * ctas_per_sm * cfg.walkers_per_cta;
+	}
+	s->walkers = s->opts.number_walkers;
+	if (s->walkers >= (1 << 24)) { delete s; return set_error(GHOST_B200_ERR_INVALID, "at most 2^24-1 walkers per device"); }
+	s->grid = (s->walkers + cfg.walkers_per_cta - 1) / cfg.walkers_per_cta;
+	const size_t W = (size_t)s->walkers;
+#define TRY_OR_END(expr) do { cudaError_t _e = (expr); if (_e != cudaSuccess) { ghost_b200_search_end(s); return set_error(GHOST_B200_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(_e)); } } while (0)
+	TRY_OR_END(cudaMalloc(&s->d_state, W * s->layout.persist_bytes));
+	TRY_OR_END(cudaMalloc(&s->d_scalars, W * sizeof(WalkerScalars)));
+	TRY_OR_END(cudaMalloc(&s->d_best_x, W * m.V * sizeof(int)));
+	TRY_OR_END(cudaMalloc(&s->d_stop, sizeof(int)));
+	TRY_OR_END(cudaMalloc(&s->d_best_key, sizeof(unsigned long long)));
+	TRY_OR_END(cudaMemset(s->d_scalars, 0, W * sizeof(WalkerScalars)));
+	TRY_OR_END(cudaMemset(s->d_stop, 0, sizeof(int)));
+	TRY_OR_END(cudaMemset(s->d_best_key, 0xff, sizeof(unsigned long long)));
+	if (s->opts.resume_search) {
+		std::vector<WalkerScalars> init(W);
+		std::memset(init.data(), 0, W * sizeof(WalkerScalars));
+		for (auto& ws : init) ws.resume_pending = 1;
+		TRY_OR_END(cudaMemcpy(s->d_scalars, init.data(), W * sizeof(WalkerScalars), cudaMemcpyHostToDevice));
+	}
+	const char* tr = std::getenv("GHOST_B200_TRACE");
+	if (tr && std::atoi(tr) > 0) {
+		s->trace_cap = std::atoi(tr);
+		TRY_OR_END(cudaMalloc(&s->d_trace, (size_t)s->trace_cap * 8 * sizeof(int)));
+		TRY_OR_END(cudaMemset(s->d_trace, 0, (size_t)s->trace_cap * 8 * sizeof(int)));
+		TRY_OR_END(cudaMalloc(&s->d_trace_len, sizeof(int)));
+		TRY_OR_END(cudaMemset(s->d_trace_len, 0, sizeof(int)));
+	}
+	TRY_OR_END(cudaEventCreate(&s->ev0));
+	TRY_OR_END(cudaEventCreate(&s->ev1));
+#undef TRY_OR_END
+	s->t_begin = std::chrono::steady_clock::now();
+	*out = s;
+	return GHOST_B200_OK;
+}
+
+extern "C" int ghost_b200_search_epoch(GhostSearch* s, int32_t iterations, void* stream)
+{
+	if (!s || iterations <= 0) return set_error(GHOST_B200_ERR_INVALID, "bad argument to search_epoch");
+	const GhostSearchOpts& o = s->opts;
+	SearchParams p{};
+	p.num_walkers = s->walkers;
+	p.iterations = iterations;
+	p.max_iterations = o.max_iterations;
+	p.custom_start = o.custom_starting_point; p.guidance = o.enable_optimization_guidance;
+	p.tabu_local_min = o.tabu_time_local_min; p.tabu_selected = o.tabu_time_selected;
+	p.plateau_percent = o.percent_chance_force_trying_on_plateau;
+	p.reset_threshold = o.reset_threshold; p.restart_threshold = o.restart_threshold;
+	p.nreset = o.number_variables_to_reset; p.nsamplings = o.number_start_samplings;
+	p.stop_on_solution = o.stop_on_first_solution;
+	p.seed = o.seed; p.first_walker = o.first_walker_id;
+	p.state = s->d_state; p.scalars = s->d_scalars; p.best_x = s->d_best_x; p.stop_flag = s->d_stop;
+	p.best_key = s->d_best_key;
+	p.trace = s->d_trace; p.trace_cap = s->trace_cap; p.trace_walker = 0; p.trace_len = s->d_trace_len;
+	CUDA_TRY(launch_search(s->T, s->grid, s->block, s->smem, (cudaStream_t)stream, s->model->low.dev, s->layout, p));
+	s->launches += 1;
+	return GHOST_B200_OK;
+}
+
+extern "C" int ghost_b200_search_request_stop(GhostSearch* s)
+{
+	if (!s) return set_error(GHOST_B200_ERR_INVALID, "search is null");
+	int one = 1;
+	CUDA_TRY(cudaMemcpy(s->d_stop, &one, sizeof one, cudaMemcpyHostToDevice));
+	return GHOST_B200_OK;
+}
+
+extern "C" int ghost_b200_search_best_key(GhostSearch* s, uint64_t* key)
+{
+	if (!s || !key) return set_error(GHOST_B200_ERR_INVALID, "null argument");
+	unsigned long long k = 0;
+	CUDA_TRY(cudaMemcpy(&k, s->d_best_key, sizeof k, cudaMemcpyDeviceToHost));
+	*key = k;
+	return GHOST_B200_OK;
+}
+
+static double sat_to_double(int v) { return v == 0x7fffffff ? std::numeric_limits<double>::max() : (double)v; }
+static double opt_to_double(long long v) { return v == 0x7fffffffffffffffLL ? std::numeric_limits<double>::max() : (double)v; }
+
+static void add_counters(GhostCounters& a, const GhostCounters& b)
+{
+	a.search_iterations += b.search_iterations; a.local_moves += b.local_moves; a.local_minimum += b.local_minimum;
+	a.plateau_moves += b.plateau_moves; a.plateau_force_trying_another_variable += b.plateau_force_trying_another_variable;
+	a.resets += b.resets; a.restarts += b.restarts; a.candidates_evaluated += b.candidates_evaluated;
+}
+
+extern "C" int ghost_b200_search_walkers(GhostSearch* s, int32_t* best_x, int64_t* best_sat, int64_t* best_opt,
+                                         GhostCounters* counters)
+{
+	if (!s) return set_error(GHOST_B200_ERR_INVALID, "search is null");
+	const size_t W = (size_t)s->walkers;
+	CUDA_TRY(cudaDeviceSynchronize());
+	std::vector<WalkerScalars> sc(W);
+	CUDA_TRY(cudaMemcpy(sc.data(), s->d_scalars, W * sizeof(WalkerScalars), cudaMemcpyDeviceToHost));
+	if (best_x) CUDA_TRY(cudaMemcpy(best_x, s->d_best_x, W * s->model->low.V * sizeof(int), cudaMemcpyDeviceToHost));
+	for (size_t w = 0; w < W; ++w) {
+		if (best_sat) best_sat[w] = sc[w].best_sat;
+		if (best_opt) best_opt[w] = sc[w].best_opt;
+		if (counters) counters[w] = sc[w].k;
+	}
+	return GHOST_B200_OK;
+}
+
+extern "C" int ghost_b200_search_result(GhostSearch* s, GhostResult* res)
+{
+	if (!s || !res) return set_error(GHOST_B200_ERR_INVALID, "null argument");
+	const size_t W = (size_t)s->walkers;
+	const int V = s->model->low.V;
+	const bool optimization = s->model->low.dev.objective != GHOST_OBJ_NONE;
+	CUDA_TRY(cudaDeviceSynchronize());
+	std::vector<WalkerScalars> sc(W);
+	CUDA_TRY(cudaMemcpy(sc.data(), s->d_scalars, W * sizeof(WalkerScalars), cudaMemcpyDeviceToHost));
+	// winner selection as the parallel branch of Solver::fast_search (include/solver.hpp:665-723):
+	// a solution with the lowest optimisation cost, else the lowest satisfaction error.
+	size_t win = 0;
+	bool found = false;
+	GhostCounters total{};
+	for (size_t w = 0; w < W; ++w) {
+		add_counters(total, sc[w].k);
+		bool solved = sc[w].best_sat == 0;
+		if (solved && !found) { found = true; win = w; }
+		else if (solved && found) { if (optimization && sc[w].best_opt < sc[win].best_opt) win = w; }
+		else if (!found && sc[w].best_sat < sc[win].best_sat) win = w;
+	}
+	int32_t* solution = res->solution;
+	std::memset(res, 0, sizeof *res);
+	res->solution = solution;
+	res->found = found ? 1 : 0;
+	res->winner_walker = (int32_t)win;
+	res->best_sat_error = sat_to_double(sc[win].best_sat);
+	res->best_opt_cost = opt_to_double(sc[win].best_opt);
+	if (optimization) {
+		// include/solver.hpp:743-751
+		double c = res->best_opt_cost;
+		if (s->model->low.dev.objective == GHOST_OBJ_LINEAR_MAXIMIZE) c = -c;
+		res->final_cost = c;
+	} else res->final_cost = res->best_sat_error;
+	if (solution) CUDA_TRY(cudaMemcpy(solution, s->d_best_x + win * V, (size_t)V * sizeof(int), cudaMemcpyDeviceToHost));
+	res->winner = sc[win].k;
+	res->total = total;
+	res->search_time_us = std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now() - s->t_begin).count();
+	res->kernel_time_us = s->kernel_ms * 1000.0;
+	res->kernel_launches = s->launches;
+	res->threads_per_walker = s->T;
+	res->walkers = s->walkers;
+	return GHOST_B200_OK;
+}
+
+// test hook: copy the walker-0 trace rows ([n][8] ints) to host
+extern "C" int ghost_b200_search_trace(GhostSearch* s, int32_t* rows, int32_t cap, int32_t* len)
+{
+	if (!s || !s->d_trace) return set_error(GHOST_B200_ERR_INVALID, "tracing is off (set GHOST_B200_TRACE=<rows>)");
+	CUDA_TRY(cudaDeviceSynchronize());
+	int n = 0;
+	CUDA_TRY(cudaMemcpy(&n, s->d_trace_len, sizeof n, cudaMemcpyDeviceToHost));
+	if (len) *len = n;
+	int take = std::min(std::min(n, cap), s->trace_cap);
+	if (rows && take > 0) CUDA_TRY(cudaMemcpy(rows, s->d_trace, (size_t)take * 8 * sizeof(int), cudaMemcpyDeviceToHost));
+	return GHOST_B200_OK;
+}
+
+extern "C" int ghost_b200_search(GhostModel* gm, const GhostSearchOpts* opts, GhostResult* res)
+{
+	if (!gm || !opts || !res) return set_error(GHOST_B200_ERR_INVALID, "null argument to search");
+	GhostSearch* s = nullptr;
+	int rc = ghost_b200_search_begin(gm, opts, &s);
+	if (rc) return rc;
+	const bool optimization = gm->low.dev.objective != GHOST_OBJ_NONE;
+	int epoch = s->opts.epoch_iterations > 0 ? s->opts.epoch_iterations : 256;
+	const double budget_us = s->opts.timeout_us;
+	int64_t done_iterations = 0;
+	for (;;) {
+		cudaEventRecord(s->ev0, nullptr);
+		rc = ghost_b200_search_epoch(s, epoch, nullptr);
+		if (rc) { ghost_b200_search_end(s); return rc; }
+		cudaEventRecord(s->ev1, nullptr);
+		cudaError_t e = cudaEventSynchronize(s->ev1);
+		if (e != cudaSuccess) { ghost_b200_search_end(s); return set_error(GHOST_B200_ERR_CUDA, std::string("search kernel: ") + cudaGetErrorString(e)); }
+		float ms = 0.f;
+		cudaEventElapsedTime(&ms, s->ev0, s->ev1);
+		s->kernel_ms += ms;
+		done_iterations += epoch;
+		// the wall-clock test of search_unit.hpp:729, between epochs
+		double elapsed = std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now() - s->t_begin).count();
+		uint64_t key = 0;
+		rc = ghost_b200_search_best_key(s, &key);
+		if (rc) { ghost_b200_search_end(s); return rc; }
+		bool solved = !optimization && (key >> 24) == 0;
+		if (solved && s->opts.stop_on_first_solution) break;
+		if (budget_us > 0 && elapsed >= budget_us) break;
+		if (s->opts.max_iterations > 0 && done_iterations >= s->opts.max_iterations) break;
+		if (budget_us <= 0 && s->opts.max_iterations <= 0) break; // nothing bounds the search: one epoch
+		// adapt the epoch so that one launch stays well below the remaining budget
+		if (budget_us > 0 && ms > 0.f) {
+			double remaining_ms = (budget_us - elapsed) / 1000.0;
+			double per_it = ms / epoch;
+			int fit = (int)std::max(1.0, std::min(4096.0, 0.5 * remaining_ms / per_it));
+			epoch = std::min(std::max(fit, 1), std::max(epoch * 2, 16));
+		}
+	}
+	rc = ghost_b200_search_result(s, res);
+	ghost_b200_search_end(s);
+	return rc;
+}

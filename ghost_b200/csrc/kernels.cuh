@@ -1,0 +1,474 @@
+// kernels.cuh — the two kernels of the hot path:
+//   search_kernel<T> : SearchUnit::local_search (reference include/search_unit.hpp:685-1201) for a
+//                      population of independent walkers, `iterations` loop passes per launch;
+//   eval_kernel<T>   : the move-evaluation unit alone (projection + delta of every candidate), the
+//                      bit-exact parity hook.
+#pragma once
+
+#include "walker.cuh"
+
+namespace ghost_b200 {
+
+struct SearchParams {
+	int num_walkers;
+	int iterations;                 // loop passes per walker in this launch
+	long long max_iterations;       // total cap per walker (<= 0: none)
+	int custom_start, guidance, tabu_local_min, tabu_selected, plateau_percent;
+	int reset_threshold, restart_threshold, nreset, nsamplings;
+	int stop_on_solution;
+	unsigned long long seed, first_walker;
+	unsigned char* state;           // [W][persist_bytes]
+	WalkerScalars* scalars;         // [W]
+	int* best_x;                    // [W][V]
+	int* stop_flag;                 // one int
+	unsigned long long* best_key;   // one packed key, atomicMin
+	int* trace;                     // optional [trace_cap][8] rows of walker trace_walker
+	int trace_cap, trace_walker;
+	int* trace_len;
+};
+
+__device__ __forceinline__ unsigned long long quality_key(bool optimization, int best_sat, long long best_opt, int walker)
+{
+	unsigned long long q;
+	if (!optimization) q = (unsigned long long)(unsigned)best_sat;
+	else if (best_sat > 0 || best_opt == GB_I64_MAX) q = (1ULL << 39) + (unsigned long long)(unsigned)best_sat;
+	else q = (unsigned long long)(best_opt + (1LL << 38));
+	return (q << 24) | (unsigned long long)(walker & 0xFFFFFF);
+}
+
+// ---- sampling ---------------------------------------------------------------------------------
+
+// first n entries of a uniform shuffle of 0..V-1 (replaces rng.shuffle + prefix, search_unit.hpp:
+// 206-211, 239-246): rejection sampling over one RNG event, by thread 0.  out is uint16-safe int.
+template <int T>
+__device__ inline void sample_distinct(const DevModel& m, const WS& s, Rng& rng, int n, int* out)
+{
+	typedef Group<T> G;
+	const int tid = G::tid();
+	const uint64_t event = rng.next_event++;
+	for (int v = tid; v < m.V; v += T) s.flags[v] = 0;
+	G::sync();
+	if (tid == 0) {
+		uint32_t t = 0;
+		uint4 blk = make_uint4(0, 0, 0, 0);
+		for (int got = 0; got < n; ++t) {
+			if ((t & 3u) == 0) blk = rng.block(event, t >> 2);
+			uint32_t w = (t & 3u) == 0 ? blk.x : (t & 3u) == 1 ? blk.y : (t & 3u) == 2 ? blk.z : blk.w;
+			uint32_t idx = below(w, (uint32_t)m.V);
+			if (s.flags[idx]) continue;
+			s.flags[idx] = 1;
+			out[got++] = (int)idx;
+		}
+	}
+	G::sync();
+}
+
+// SearchUnit::monte_carlo_sampling (search_unit.hpp:201-212)
+template <int T>
+__device__ inline void monte_carlo_sampling(const DevModel& m, const WS& s, Rng& rng, int nb)
+{
+	typedef Group<T> G;
+	MV mv(m);
+	const int tid = G::tid();
+	if (nb < 0 || nb >= m.V) {
+		const uint64_t event = rng.next_event++;
+		for (int b = tid; b < (m.V + 3) / 4; b += T) {
+			uint4 r = rng.block(event, (uint32_t)b);
+			uint32_t w[4] = { r.x, r.y, r.z, r.w };
+#pragma unroll
+			for (int q = 0; q < 4; ++q) {
+				int v = 4 * b + q;
+				if (v < m.V) s.x[v] = mv.dom_value(v, (int)below(w[q], (uint32_t)mv.dom_size(v)));
+			}
+		}
+		G::sync();
+		return;
+	}
+	sample_distinct<T>(m, s, rng, nb, s.sample);
+	const uint64_t event = rng.next_event++;
+	for (int i = tid; i < nb; i += T) {
+		int v = s.sample[i];
+		s.x[v] = mv.dom_value(v, (int)below(rng.word(event, (uint32_t)v), (uint32_t)mv.dom_size(v)));
+	}
+	G::sync();
+}
+
+__device__ __forceinline__ void try_swap(const DevModel& m, const MV& mv, const WS& s, int i, int j)
+{
+	// search_unit.hpp:224-231 / 247-254
+	int xi = s.x[i], xj = s.x[j];
+	if (i != j && xi != xj && (m.identical_domains || (mv.in_domain(j, xi) && mv.in_domain(i, xj)))) {
+		s.x[i] = xj; s.x[j] = xi;
+	}
+}
+
+// SearchUnit::random_permutations (search_unit.hpp:215-257).
+// Full form: for every pair i<j a fair coin decides a swap.  For fixed i the swaps with the chosen
+// j1<j2<..<jm rotate the values along (i, j1, .., jm); with identical domains every swap is legal,
+// so one warp applies the rotation chunk-by-chunk with ballots (same result as the sequential
+// loop, coin for coin).  Otherwise thread 0 runs the sequential loop.
+template <int T>
+__device__ inline void random_permutations(const DevModel& m, const WS& s, Rng& rng, int nb)
+{
+	typedef Group<T> G;
+	MV mv(m);
+	const int tid = G::tid(), lane = threadIdx.x & 31;
+	if (nb < 0) {
+		const uint64_t event = rng.next_event++;
+		const uint32_t blocks = (uint32_t)((m.V + 127) / 128);
+		if (m.identical_domains) {
+			if (G::warp() == 0) {
+				for (int i = 0; i < m.V - 1; ++i) {
+					int carry = s.x[i];
+					bool any = false;
+					uint4 blk = make_uint4(0, 0, 0, 0);
+					int cur_block = -1;
+					for (int jb = (i + 1) & ~31; jb < m.V; jb += 32) {
+						if ((jb >> 7) != cur_block) { cur_block = jb >> 7; blk = rng.block(event, (uint32_t)i * blocks + (uint32_t)cur_block); }
+						uint32_t q = ((uint32_t)jb >> 5) & 3u;
+						uint32_t w = q == 0 ? blk.x : q == 1 ? blk.y : q == 2 ? blk.z : blk.w;
+						int j = jb + lane;
+						bool chosen = j > i && j < m.V && ((w >> lane) & 1u);
+						int old = (j < m.V) ? s.x[j] : 0;
+						unsigned b = __ballot_sync(0xffffffffu, chosen);
+						if (b == 0) continue;
+						unsigned lower = b & ((1u << lane) - 1u);
+						int src = lower ? 31 - __clz(lower) : 0;
+						int from = __shfl_sync(0xffffffffu, old, src);
+						if (chosen) s.x[j] = lower ? from : carry;
+						carry = __shfl_sync(0xffffffffu, old, 31 - __clz(b));
+						any = true;
+					}
+					if (any && lane == 0) s.x[i] = carry;
+					__syncwarp();
+				}
+			}
+		} else if (tid == 0) {
+			for (int i = 0; i < m.V - 1; ++i) {
+				uint4 blk = make_uint4(0, 0, 0, 0);
+				int cur_block = -1;
+				for (int j = i + 1; j < m.V; ++j) {
+					if ((j >> 7) != cur_block) { cur_block = j >> 7; blk = rng.block(event, (uint32_t)i * blocks + (uint32_t)cur_block); }
+					uint32_t q = ((uint32_t)j >> 5) & 3u;
+					uint32_t w = q == 0 ? blk.x : q == 1 ? blk.y : q == 2 ? blk.z : blk.w;
+					if ((w >> (j & 31)) & 1u) try_swap(m, mv, s, i, j);
+				}
+			}
+		}
+		G::sync();
+		return;
+	}
+	if (nb > m.V) nb = m.V;
+	sample_distinct<T>(m, s, rng, nb, s.sample);
+	sample_distinct<T>(m, s, rng, nb, s.sample + nb);
+	if (tid == 0)
+		for (int i = 0; i < nb; ++i) try_swap(m, mv, s, s.sample[i], s.sample[nb + i]);
+	G::sync();
+}
+
+// ---- walker registers ---------------------------------------------------------------------------
+struct WalkerRegs {
+	int must_compute, ncand, n_tabu, local_moves, cur_sat, best_sat, resume_pending, cand_max;
+	long long cur_opt, best_opt, obj_sum;
+	GhostCounters k;
+};
+
+__device__ __forceinline__ long long internal_cost(const DevModel& m, long long obj_sum)
+{
+	return m.objective == GHOST_OBJ_LINEAR_MAXIMIZE ? -obj_sum : obj_sum; // src/objective.cpp:60-61
+}
+
+template <int T>
+__device__ inline void copy_best(const DevModel& m, const WS& s, int* best_x)
+{
+	for (int v = Group<T>::tid(); v < m.V; v += T) best_x[v] = s.x[v];
+}
+
+// SearchUnit::initialize_data_structures (search_unit.hpp:274-317)
+template <int T>
+__device__ inline void initialize_data_structures(const DevModel& m, const WS& s, WalkerRegs& r, int* best_x)
+{
+	typedef Group<T> G;
+	MV mv(m);
+	r.must_compute = 1;
+	for (int v = G::tid(); v < m.V; v += T) s.tabu[v] = 0;
+	r.cur_sat = recompute_all<T>(m, s, s.red);
+	if (r.best_sat > r.cur_sat) { r.best_sat = r.cur_sat; copy_best<T>(m, s, best_x); }
+	if (m.objective != GHOST_OBJ_NONE) {
+		long long part = 0;
+		for (int v = G::tid(); v < m.V; v += T) part += (long long)mv.obj_coef(v) * s.x[v];
+		r.obj_sum = G::sum64(part, s.red + 16);
+		if (r.cur_sat == 0) {
+			r.cur_opt = internal_cost(m, r.obj_sum);
+			if (r.best_opt > r.cur_opt) { r.best_opt = r.cur_opt; copy_best<T>(m, s, best_x); }
+		} else r.cur_opt = GB_I64_MAX;
+	}
+	G::sync();
+}
+
+// SearchUnit::set_initial_configuration (search_unit.hpp:153-198); s.tabu doubles as the
+// best_values buffer (it is cleared by initialize_data_structures right after).
+// Deviation D1: best_x follows best_sat here too.
+template <int T>
+__device__ inline void set_initial_configuration(const DevModel& m, const WS& s, WalkerRegs& r, Rng& rng, int samplings, int* best_x)
+{
+	typedef Group<T> G;
+	int best_so_far = GB_INT_MAX, current;
+	if (samplings < 1) samplings = 1;
+	int loops = 0;
+	do {
+		if (m.permutation) random_permutations<T>(m, s, rng, -1); else monte_carlo_sampling<T>(m, s, rng, -1);
+		current = recompute_all<T>(m, s, s.red);
+		if (best_so_far > current) {
+			best_so_far = current;
+			if (r.best_sat > best_so_far) { r.best_sat = best_so_far; copy_best<T>(m, s, best_x); }
+			for (int v = G::tid(); v < m.V; v += T) s.tabu[v] = s.x[v];
+		}
+		G::sync();
+	} while (++loops < samplings && current > 0);
+	for (int v = G::tid(); v < m.V; v += T) s.x[v] = s.tabu[v];
+	G::sync();
+}
+
+// SearchUnit::initialize_variable_values (search_unit.hpp:259-272)
+template <int T>
+__device__ inline void initialize_variable_values(const DevModel& m, const WS& s, WalkerRegs& r, Rng& rng, const SearchParams& p, int* best_x)
+{
+	typedef Group<T> G;
+	MV mv(m);
+	if (p.custom_start || r.resume_pending) {
+		r.resume_pending = 0;
+		for (int v = G::tid(); v < m.V; v += T) s.x[v] = mv.ld(m.o.start, v);
+		G::sync();
+	} else
+		set_initial_configuration<T>(m, s, r, rng, p.nsamplings, best_x);
+}
+
+// SearchUnit::local_move (search_unit.hpp:516-541)
+template <int T>
+__device__ inline void local_move(const DevModel& m, const WS& s, WalkerRegs& r, const SearchParams& p, int v, int new_value, int delta)
+{
+	MV mv(m);
+	++r.local_moves;
+	++r.k.local_moves;
+	r.cur_sat += delta;
+	if (Group<T>::tid() == 0) s.tabu[v] = p.tabu_selected + r.local_moves;
+	r.must_compute = 1;
+	if (m.objective != GHOST_OBJ_NONE) {
+		if (m.permutation) {
+			int xv = s.x[v], xj = s.x[new_value];
+			r.obj_sum += (long long)mv.obj_coef(v) * (xj - xv) + (long long)mv.obj_coef(new_value) * (xv - xj);
+		} else
+			r.obj_sum += (long long)mv.obj_coef(v) * (new_value - s.x[v]);
+	}
+	apply_move<T>(m, s, v, new_value);
+}
+
+// =================================================================================================
+template <int T>
+__global__ void __launch_bounds__(T == 32 ? 256 : T)
+search_kernel(const DevModel m, const WalkerLayout L, const SearchParams p)
+{
+	typedef Group<T> G;
+	extern __shared__ __align__(16) unsigned char smem_raw[];
+	const int walkers_per_cta = (T == 32) ? (blockDim.x >> 5) : 1;
+	const int local = (T == 32) ? (threadIdx.x >> 5) : 0;
+	const int w = blockIdx.x * walkers_per_cta + local;
+	if (w >= p.num_walkers) return; // whole group leaves together
+	const WS s = make_ws(smem_raw + (size_t)local * L.total_bytes, L);
+	const int tid = G::tid();
+	MV mv(m);
+	const bool optimization = m.objective != GHOST_OBJ_NONE;
+	int* best_x = p.best_x + (size_t)w * m.V;
+	unsigned char* gstate = p.state + (size_t)w * L.persist_bytes;
+	WalkerScalars* gs = p.scalars + w;
+
+	Rng rng; rng.seed = p.seed; rng.walker = p.first_walker + (unsigned long long)w; rng.next_event = gs->next_event;
+	WalkerRegs r;
+	r.must_compute = gs->must_compute; r.ncand = gs->ncand; r.n_tabu = gs->n_tabu; r.local_moves = gs->local_moves;
+	r.cur_sat = gs->cur_sat; r.best_sat = gs->best_sat; r.resume_pending = gs->resume_pending; r.cand_max = gs->cand_max;
+	r.cur_opt = gs->cur_opt; r.best_opt = gs->best_opt; r.obj_sum = gs->obj_sum; r.k = gs->k;
+	int done = gs->done;
+
+	if (!gs->initialized) {
+		// search_unit.hpp:708-717
+		r.best_sat = GB_INT_MAX; r.best_opt = GB_I64_MAX; r.cur_opt = GB_I64_MAX;
+		for (int v = tid; v < m.V; v += T) s.x[v] = mv.ld(m.o.start, v);
+		for (int c = tid; c < m.C; c += T) s.mark[c] = 0;
+		G::sync();
+		initialize_variable_values<T>(m, s, r, rng, p, best_x);
+		initialize_data_structures<T>(m, s, r, best_x);
+		copy_best<T>(m, s, best_x);
+		done = !(r.best_sat > 0 || (r.best_sat == 0 && optimization));
+	} else {
+		const int4* src = reinterpret_cast<const int4*>(gstate);
+		int4* dst = reinterpret_cast<int4*>(smem_raw + (size_t)local * L.total_bytes);
+		for (int i = tid; i < L.persist_bytes / 16; i += T) dst[i] = src[i];
+		for (int c = tid; c < m.C; c += T) s.mark[c] = 0;
+		G::sync();
+	}
+
+	for (int it = 0; it < p.iterations && !done; ++it) {
+		if (p.max_iterations > 0 && r.k.search_iterations >= p.max_iterations) break;
+		if ((it & 7) == 0) {
+			// stop request (SearchUnit::stop_search_requested, search_unit.hpp:658-664, 728)
+			if (tid == 0) s.red[48] = *reinterpret_cast<volatile int*>(p.stop_flag);
+			G::sync();
+			int stop = s.red[48];
+			G::sync();
+			if (stop) break;
+		}
+		++r.k.search_iterations;
+
+		if (r.must_compute)
+			r.ncand = scan_candidates<T>(m, s, L.nchunks_v, r.local_moves, optimization && r.cur_sat == 0, s.red, &r.cand_max, &r.n_tabu);
+
+		int trace_var = -1, trace_val = 0, trace_branch = 0, trace_ncand = 0, trace_min = 0;
+		if (r.n_tabu >= p.reset_threshold || r.ncand == 0) {
+			// SearchUnit::reset (search_unit.hpp:333-367)
+			++r.k.resets;
+			if (p.restart_threshold > 0 && (r.k.resets % p.restart_threshold == 0)) {
+				++r.k.restarts;
+				initialize_variable_values<T>(m, s, r, rng, p, best_x);
+			} else if (m.permutation) random_permutations<T>(m, s, rng, p.nreset);
+			else monte_carlo_sampling<T>(m, s, rng, p.nreset);
+			initialize_data_structures<T>(m, s, r, best_x);
+		} else {
+			const uint4 rnd = rng.block(rng.next_event++, 0);
+			// UniformVariableHeuristic::select_variable (uniform_variable_heuristic.cpp:38-41)
+			const int v = pick_kth(s.cand_key, s.cand_bits, L.nchunks_v, r.cand_max, (int)below(rnd.x, (uint32_t)r.ncand));
+			--r.ncand;
+			const int deg = hoist_variable<T>(m, s, v);
+			G::sync();
+			if (tid == 0) s.cand_bits[v >> 5] &= ~(1u << (v & 31)); // search_unit.hpp:826-828
+			int mine = evaluate_candidates<T>(m, s, v, deg, L.nchunks_c, nullptr);
+			G::sync();
+			const int ncandidates = G::sum(mine, s.red + 16);
+			r.k.candidates_evaluated += ncandidates;
+			// AdaptiveSearchValueHeuristic::select_value (adaptive_search_value_heuristic.cpp:43-81)
+			const int gmin = chunks_min(s.val_key, L.nchunks_c);
+			const int nties = gmin == GB_INT_MAX ? 0 : chunks_count(s.val_key, s.val_bits, L.nchunks_c, gmin);
+			int new_value = v;
+			if (nties > 0) {
+				int k;
+				if (optimization && !m.permutation) {
+					// Objective::expert_heuristic_value (objective.cpp:69-109) for a linear objective:
+					// the cheapest tied value is the smallest / largest one, or any if the coefficient is 0
+					long long cf = internal_cost(m, (long long)mv.obj_coef(v));
+					k = cf > 0 ? 0 : cf < 0 ? nties - 1 : (int)below(rnd.y, (uint32_t)nties);
+				} else k = (int)below(rnd.y, (uint32_t)nties);
+				int slot = pick_kth(s.val_key, s.val_bits, L.nchunks_c, gmin, k);
+				new_value = m.permutation ? slot : mv.dom_value(v, slot);
+			}
+			trace_var = v; trace_val = new_value; trace_ncand = ncandidates; trace_min = gmin;
+
+			int plateau = 0, local_min = 0;
+			if (gmin < 0) { // search_unit.hpp:1042-1050
+				local_move<T>(m, s, r, p, v, new_value, gmin);
+				if (optimization) r.cur_opt = internal_cost(m, r.obj_sum);
+				trace_branch = 1;
+			} else if (gmin == 0) {
+				if (optimization && p.guidance) { // 1061-1135
+					long long obj2;
+					if (m.permutation) {
+						int xv = s.x[v], xj = s.x[new_value];
+						obj2 = r.obj_sum + (long long)mv.obj_coef(v) * (xj - xv) + (long long)mv.obj_coef(new_value) * (xv - xj);
+					} else obj2 = r.obj_sum + (long long)mv.obj_coef(v) * (new_value - s.x[v]);
+					long long cand_opt = internal_cost(m, obj2);
+					if (r.cur_opt > cand_opt) { local_move<T>(m, s, r, p, v, new_value, 0); r.cur_opt = cand_opt; trace_branch = 2; }
+					else if (r.cur_opt == cand_opt) plateau = 1;
+					else local_min = 1;
+				} else plateau = 1; // 1136-1145
+			} else local_min = 1; // 1147-1163 (also: no candidate at all, min_conflict stays DBL_MAX)
+
+			if (plateau) { // plateau_management, 545-561
+				if ((int)below(rnd.z, 100u) + 1 <= p.plateau_percent) {
+					if (tid == 0) s.tabu[v] = p.tabu_local_min + r.local_moves;
+					r.must_compute = 1;
+					++r.k.plateau_force_trying_another_variable;
+					trace_branch = 4;
+				} else {
+					local_move<T>(m, s, r, p, v, new_value, 0);
+					++r.k.plateau_moves;
+					trace_branch = 3;
+				}
+			}
+			if (local_min) { // local_minimum_management, 565-582
+				r.must_compute = 0;
+				if (r.ncand == 0) {
+					if (tid == 0) s.tabu[v] = p.tabu_local_min + r.local_moves;
+					if (p.tabu_local_min > 0) ++r.n_tabu;
+					++r.k.local_minimum;
+					trace_branch = 5;
+				} else trace_branch = 6;
+			}
+			G::sync();
+			if (m.permutation) unmark_variable<T>(m, s, v);
+
+			// search_unit.hpp:1166-1188
+			if (r.best_sat > r.cur_sat) { r.best_sat = r.cur_sat; copy_best<T>(m, s, best_x); }
+			else if (optimization && r.cur_sat == 0 && r.best_opt > r.cur_opt) { r.best_opt = r.cur_opt; copy_best<T>(m, s, best_x); }
+			G::sync();
+		}
+		if (p.trace && w == p.trace_walker && tid == 0) {
+			int row = (int)r.k.search_iterations - 1;
+			if (row < p.trace_cap) {
+				int* t = p.trace + 8 * row;
+				t[0] = (int)r.k.search_iterations; t[1] = trace_var; t[2] = trace_val; t[3] = trace_branch;
+				t[4] = trace_ncand; t[5] = trace_min; t[6] = r.cur_sat; t[7] = 0;
+			}
+			*p.trace_len = (int)r.k.search_iterations;
+		}
+		done = !(r.best_sat > 0 || (r.best_sat == 0 && optimization)); // search_unit.hpp:730
+		if (done && p.stop_on_solution && tid == 0) atomicExch(p.stop_flag, 1);
+	}
+
+	// persist
+	{
+		int4* dst = reinterpret_cast<int4*>(gstate);
+		const int4* src = reinterpret_cast<const int4*>(smem_raw + (size_t)local * L.total_bytes);
+		for (int i = tid; i < L.persist_bytes / 16; i += T) dst[i] = src[i];
+	}
+	if (tid == 0) {
+		gs->initialized = 1; gs->must_compute = r.must_compute; gs->ncand = r.ncand; gs->n_tabu = r.n_tabu;
+		gs->local_moves = r.local_moves; gs->cur_sat = r.cur_sat; gs->best_sat = r.best_sat;
+		gs->resume_pending = r.resume_pending; gs->cand_max = r.cand_max; gs->done = done;
+		gs->cur_opt = r.cur_opt; gs->best_opt = r.best_opt; gs->obj_sum = r.obj_sum;
+		gs->next_event = rng.next_event; gs->k = r.k;
+		atomicMin(p.best_key, quality_key(optimization, r.best_sat, r.best_opt, w));
+	}
+}
+
+// =================================================================================================
+// Parity hook: for each walker's assignment and selected variable write constraint errors,
+// projected errors and the cumulated delta of every candidate slot.
+template <int T>
+__global__ void __launch_bounds__(T == 32 ? 256 : T)
+eval_kernel(const DevModel m, const WalkerLayout L, int num_walkers, const int* __restrict__ assignments,
+            const int* __restrict__ selected, int* __restrict__ ctr_error, int* __restrict__ var_error,
+            int* __restrict__ cand_delta)
+{
+	typedef Group<T> G;
+	extern __shared__ __align__(16) unsigned char smem_raw[];
+	const int walkers_per_cta = (T == 32) ? (blockDim.x >> 5) : 1;
+	const int local = (T == 32) ? (threadIdx.x >> 5) : 0;
+	const int w = blockIdx.x * walkers_per_cta + local;
+	if (w >= num_walkers) return;
+	const WS s = make_ws(smem_raw + (size_t)local * L.total_bytes, L);
+	const int tid = G::tid();
+	for (int v = tid; v < m.V; v += T) s.x[v] = assignments[(size_t)w * m.V + v];
+	for (int c = tid; c < m.C; c += T) s.mark[c] = 0;
+	G::sync();
+	recompute_all<T>(m, s, s.red);
+	if (ctr_error) for (int c = tid; c < m.C; c += T) ctr_error[(size_t)w * m.C + c] = s.err_c[c];
+	if (var_error) for (int v = tid; v < m.V; v += T) var_error[(size_t)w * m.V + v] = s.err_var[v];
+	const int v = selected ? selected[w] : -1;
+	if (v < 0 || !cand_delta) return;
+	int* out = cand_delta + (size_t)w * m.max_candidates;
+	for (int k = L.nchunks_c * 32 + tid; k < m.max_candidates; k += T) out[k] = GB_INT_MAX;
+	const int deg = hoist_variable<T>(m, s, v);
+	G::sync();
+	evaluate_candidates<T>(m, s, v, deg, L.nchunks_c, out);
+}
+
+} // namespace ghost_b200

@@ -1,0 +1,260 @@
+// lower.cpp — host-only validation and lowering of a GhostModelDesc (no CUDA calls here, so the
+// descriptor checks run on a machine without a GPU).
+//
+// What it reproduces from the reference:
+//  * matrix_var_ctr: for every variable the ascending list of constraints that contain it
+//    (include/search_unit_data.hpp:95-102);
+//  * each variable's position / coefficient inside a constraint (Constraint::_variables_position,
+//    include/constraint.hpp:70; LinearEquation::_coefficients, linear_equation.hpp:46);
+//  * the dense count tables that stand for AllDifferent::_count (all_different.hpp:48).
+// What it rejects (GHOST_B200_ERR_UNSUPPORTED): user-defined constraints/objectives, non-integer
+// coefficients, error magnitudes that do not fit int32, models whose walker state does not fit in
+// shared memory.  There is no CPU fallback.
+#include "lowered.h"
+
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <limits>
+#include <set>
+
+namespace ghost_b200 {
+
+static bool is_linear(int k) { return k >= GHOST_KIND_LINEAR_EQ && k <= GHOST_KIND_LINEAR_G; }
+static bool is_alldiff_like(int k) { return k == GHOST_KIND_ALL_DIFFERENT || k == GHOST_KIND_ALL_DIFFERENT_ABS_DIFF; }
+
+static bool as_int(double d, int64_t* out)
+{
+	if (!(d == d) || std::fabs(d) > 4.0e15) return false;
+	double r = std::nearbyint(d);
+	if (r != d) return false;
+	*out = static_cast<int64_t>(r);
+	return true;
+}
+
+int lower_model(const GhostModelDesc* d, LoweredModel* out, std::string* why)
+{
+	auto fail = [&](int code, const std::string& msg) { if (why) *why = msg; return code; };
+	if (!d || !out) return fail(GHOST_B200_ERR_INVALID, "null descriptor");
+	const int V = d->num_variables, C = d->num_constraints;
+	if (V <= 0) return fail(GHOST_B200_ERR_INVALID, "model has no variable");
+	if (C <= 0) return fail(GHOST_B200_ERR_INVALID, "model has no constraint (pass one PURE_OPTIMIZATION constraint, as ModelBuilder::build_model does)");
+	if (V > 65535 * 32) return fail(GHOST_B200_ERR_UNSUPPORTED, "too many variables");
+	if (!d->dom_offset || !d->dom_values || !d->start_value || !d->ctr_kind || !d->ctr_offset || !d->ctr_vars)
+		return fail(GHOST_B200_ERR_INVALID, "null array in descriptor");
+	if (d->dom_offset[0] != 0 || d->ctr_offset[0] != 0) return fail(GHOST_B200_ERR_INVALID, "offset arrays must start at 0");
+
+	// ---- domains
+	std::vector<int32_t> dom_lo(V), dom_size(V), dom_off(V + 1, 0), dom_vals;
+	bool contiguous = true, identical = true;
+	int max_dom = 0;
+	int64_t max_abs_value = 0;
+	for (int v = 0; v < V; ++v) {
+		int b = d->dom_offset[v], e = d->dom_offset[v + 1];
+		if (e <= b) return fail(GHOST_B200_ERR_INVALID, "variable " + std::to_string(v) + " has an empty domain");
+		std::vector<int32_t> dv(d->dom_values + b, d->dom_values + e);
+		std::sort(dv.begin(), dv.end());
+		if (std::adjacent_find(dv.begin(), dv.end()) != dv.end())
+			return fail(GHOST_B200_ERR_INVALID, "variable " + std::to_string(v) + " has a duplicated domain value");
+		if (!std::binary_search(dv.begin(), dv.end(), d->start_value[v]))
+			return fail(GHOST_B200_ERR_INVALID, "start value of variable " + std::to_string(v) + " is not in its domain");
+		dom_lo[v] = dv.front();
+		dom_size[v] = static_cast<int32_t>(dv.size());
+		if (static_cast<int64_t>(dv.back()) - dv.front() + 1 != static_cast<int64_t>(dv.size())) contiguous = false;
+		dom_off[v + 1] = dom_off[v] + dom_size[v];
+		dom_vals.insert(dom_vals.end(), dv.begin(), dv.end());
+		max_dom = std::max(max_dom, dom_size[v]);
+		max_abs_value = std::max<int64_t>(max_abs_value, std::max(std::llabs((long long)dv.front()), std::llabs((long long)dv.back())));
+		if (v > 0) {
+			if (dom_size[v] != dom_size[0] || !std::equal(dv.begin(), dv.end(), dom_vals.begin())) identical = false;
+		}
+	}
+	if (max_abs_value > (1 << 28)) return fail(GHOST_B200_ERR_UNSUPPORTED, "domain values beyond 2^28 are outside the int32 GPU path");
+
+	// ---- constraints
+	const int nnz = d->ctr_offset[C];
+	std::vector<int32_t> kind(C), rhs(C, 0), cnt_tab(C, 0), c2v_off(C + 1, 0), c2v(nnz), ent_ctr(nnz), ent_coef(nnz, 0);
+	std::vector<int32_t> cnt_owner;
+	std::vector<std::vector<std::pair<int, int>>> rows(V); // (constraint, coefficient|position)
+	int cnt_total = 0;
+	int64_t error_bound = 0;
+	bool has_abs_diff = false;
+	for (int c = 0; c < C; ++c) {
+		int k = d->ctr_kind[c];
+		int b = d->ctr_offset[c], e = d->ctr_offset[c + 1];
+		if (e < b) return fail(GHOST_B200_ERR_INVALID, "constraint offsets not monotone");
+		if (!(is_linear(k) || is_alldiff_like(k) || k == GHOST_KIND_FIX_VALUE || k == GHOST_KIND_PURE_OPTIMIZATION))
+			return fail(GHOST_B200_ERR_UNSUPPORTED, "constraint " + std::to_string(c) + " is not a stock global constraint "
+			            "(user-defined Constraint subclasses are outside the GPU path; there is no CPU fallback)");
+		kind[c] = k;
+		c2v_off[c + 1] = e;
+		std::set<int> seen;
+		int64_t lo = std::numeric_limits<int64_t>::max(), hi = std::numeric_limits<int64_t>::min();
+		int64_t lin_bound = 0;
+		for (int i = b; i < e; ++i) {
+			int v = d->ctr_vars[i];
+			if (v < 0 || v >= V) return fail(GHOST_B200_ERR_INVALID, "constraint " + std::to_string(c) + " names variable " + std::to_string(v));
+			if (!seen.insert(v).second) return fail(GHOST_B200_ERR_INVALID, "constraint " + std::to_string(c) + " lists variable " + std::to_string(v) + " twice");
+			c2v[i] = v;
+			ent_ctr[i] = c;
+			int64_t vlo = dom_lo[v], vhi = dom_vals[dom_off[v + 1] - 1];
+			lo = std::min(lo, vlo); hi = std::max(hi, vhi);
+			int second = 0;
+			if (is_linear(k)) {
+				int64_t a;
+				double coef = d->ctr_coefs ? d->ctr_coefs[i] : 1.0;
+				if (!as_int(coef, &a) || std::llabs((long long)a) > (1 << 28))
+					return fail(GHOST_B200_ERR_UNSUPPORTED, "constraint " + std::to_string(c) + ": coefficient " + std::to_string(coef) +
+					            " is not a (small) integer; the GPU path computes in int32");
+				ent_coef[i] = static_cast<int32_t>(a);
+				second = static_cast<int32_t>(a);
+				lin_bound += std::llabs((long long)a) * std::max(std::llabs((long long)vlo), std::llabs((long long)vhi));
+			} else if (k == GHOST_KIND_ALL_DIFFERENT_ABS_DIFF) {
+				second = i - b; // position in scope
+			}
+			rows[v].emplace_back(c, second);
+		}
+		if (is_linear(k) || k == GHOST_KIND_FIX_VALUE) {
+			int64_t p;
+			double param = d->ctr_param ? d->ctr_param[c] : 0.0;
+			if (!as_int(param, &p) || std::llabs((long long)p) > (1LL << 30))
+				return fail(GHOST_B200_ERR_UNSUPPORTED, "constraint " + std::to_string(c) + ": rhs/value " + std::to_string(param) + " is not a (small) integer");
+			rhs[c] = static_cast<int32_t>(p);
+			if (is_linear(k)) {
+				if (lin_bound + std::llabs((long long)p) >= (1LL << 30))
+					return fail(GHOST_B200_ERR_UNSUPPORTED, "constraint " + std::to_string(c) + ": |sum| can exceed 2^30");
+				error_bound += lin_bound + std::llabs((long long)p) + 1;
+			} else {
+				for (int i = b; i < e; ++i) {
+					int v = c2v[i];
+					error_bound += std::max(std::llabs((long long)dom_lo[v] - p), std::llabs((long long)dom_vals[dom_off[v + 1] - 1] - p));
+				}
+			}
+		}
+		if (is_alldiff_like(k)) {
+			int64_t n = e - b;
+			if (n == 0) { lo = 0; hi = 0; }
+			int64_t base = lo, size = hi - lo + 1;
+			if (k == GHOST_KIND_ALL_DIFFERENT_ABS_DIFF) { base = 0; size = hi - lo + 1; has_abs_diff = true; }
+			if (size > (1 << 20)) return fail(GHOST_B200_ERR_UNSUPPORTED, "constraint " + std::to_string(c) + ": value range too wide for a dense count table");
+			if (n > 65535) return fail(GHOST_B200_ERR_UNSUPPORTED, "AllDifferent scope beyond 65535");
+			cnt_tab[c] = static_cast<int32_t>(cnt_total - base);
+			for (int64_t t = 0; t < size; ++t) cnt_owner.push_back(c);
+			cnt_total += static_cast<int>(size);
+			error_bound += n * (n - 1) / 2;
+		}
+	}
+	if (error_bound >= (1LL << 31) - 1)
+		return fail(GHOST_B200_ERR_UNSUPPORTED, "total satisfaction error can exceed int32 (bound " + std::to_string(error_bound) + ")");
+
+	// ---- var -> ctr rows (ascending constraint id by construction)
+	std::vector<int32_t> v2c_off(V + 1, 0), v2c;
+	int max_degree = 0;
+	for (int v = 0; v < V; ++v) {
+		v2c_off[v + 1] = v2c_off[v] + static_cast<int32_t>(rows[v].size());
+		max_degree = std::max<int>(max_degree, static_cast<int>(rows[v].size()));
+		for (auto& pr : rows[v]) { v2c.push_back(pr.first); v2c.push_back(pr.second); }
+	}
+	if (max_degree > 255) return fail(GHOST_B200_ERR_UNSUPPORTED, "a variable appears in more than 255 constraints");
+
+	// ---- objective
+	std::vector<int32_t> obj_coef(V, 0);
+	int ok = d->objective_kind;
+	if (!(ok == GHOST_OBJ_NONE || ok == GHOST_OBJ_LINEAR_MINIMIZE || ok == GHOST_OBJ_LINEAR_MAXIMIZE))
+		return fail(GHOST_B200_ERR_UNSUPPORTED, "objective is not a linear objective (user-defined Objective subclasses are outside the GPU path)");
+	if (ok != GHOST_OBJ_NONE) {
+		int64_t bound = 0;
+		for (int i = 0; i < d->num_objective_terms; ++i) {
+			int v = d->obj_vars[i];
+			int64_t a;
+			if (v < 0 || v >= V) return fail(GHOST_B200_ERR_INVALID, "objective names variable " + std::to_string(v));
+			if (!as_int(d->obj_coefs[i], &a) || std::llabs((long long)a) > (1 << 28))
+				return fail(GHOST_B200_ERR_UNSUPPORTED, "objective coefficient is not a (small) integer");
+			obj_coef[v] += static_cast<int32_t>(a);
+			bound += std::llabs((long long)a) * std::max(std::llabs((long long)dom_lo[v]), std::llabs((long long)dom_vals[dom_off[v + 1] - 1]));
+		}
+		if (bound >= (1LL << 62)) return fail(GHOST_B200_ERR_UNSUPPORTED, "objective magnitude too large");
+	}
+
+	// ---- blob
+	LoweredModel& L = *out;
+	L = LoweredModel();
+	L.V = V; L.C = C;
+	L.start.assign(d->start_value, d->start_value + V);
+	L.error_bound = error_bound;
+	std::vector<int32_t>& blob = L.blob;
+	BlobOffsets o{};
+	auto put = [&](const std::vector<int32_t>& a) {
+		int at = static_cast<int>(blob.size());
+		blob.insert(blob.end(), a.begin(), a.end());
+		while (blob.size() % 4) blob.push_back(0); // keep every section 16-byte aligned
+		return at;
+	};
+	o.dom_lo = put(dom_lo); o.dom_size = put(dom_size); o.dom_off = put(dom_off); o.dom_vals = put(dom_vals);
+	o.start = put(L.start);
+	o.v2c_off = put(v2c_off); o.v2c = put(v2c);
+	o.kind = put(kind); o.rhs = put(rhs); o.cnt_tab = put(cnt_tab);
+	o.c2v_off = put(c2v_off); o.c2v = put(c2v); o.ent_ctr = put(ent_ctr); o.ent_coef = put(ent_coef);
+	o.cnt_owner = put(cnt_owner);
+	o.obj_coef = put(obj_coef);
+	o.total = static_cast<int>(blob.size());
+
+	DevModel& m = L.dev;
+	m.blob = nullptr;
+	m.o = o;
+	m.V = V; m.C = C; m.nnz = nnz;
+	m.permutation = d->permutation_problem ? 1 : 0;
+	m.objective = ok;
+	m.contiguous_domains = contiguous ? 1 : 0;
+	m.identical_domains = identical ? 1 : 0;
+	m.cnt_total = cnt_total;
+	m.max_candidates = m.permutation ? V : max_dom;
+	m.max_degree = std::max(1, max_degree);
+	m.has_abs_diff = has_abs_diff ? 1 : 0;
+	return GHOST_B200_OK;
+}
+
+static int align_up(int x, int a) { return (x + a - 1) / a * a; }
+
+WalkerLayout LoweredModel::layout(int /*threads_per_walker*/, int nreset) const
+{
+	const DevModel& m = dev;
+	WalkerLayout w{};
+	int at = 0;
+	auto take = [&](int bytes) { int r = at; at = align_up(at + bytes, 16); return r; };
+	w.nchunks_v = (m.V + 31) / 32;
+	w.nchunks_c = (m.max_candidates + 31) / 32;
+	w.x = take(4 * m.V);
+	w.err_var = take(4 * m.V);
+	w.tabu = take(4 * m.V);
+	w.S = take(4 * m.C);
+	w.err_c = take(4 * m.C);
+	w.cand_key = take(4 * w.nchunks_v);
+	w.cand_bits = take(4 * w.nchunks_v);
+	w.cnt = take(2 * std::max(1, m.cnt_total));
+	w.persist_bytes = at;
+	w.mark = take(m.C);
+	w.flags = take(m.V);
+	w.val_key = take(4 * w.nchunks_c);
+	w.val_bits = take(4 * w.nchunks_c);
+	w.hoist = take(4 * 8 * m.max_degree);
+	w.upd = take(4 * 2 * 2 * m.max_degree);
+	w.sample = take(4 * 2 * std::max(1, nreset));
+	w.red = take(4 * 64);
+	w.total_bytes = at;
+	return w;
+}
+
+int LoweredModel::default_threads_per_walker() const
+{
+	// One warp per walker for small models; a CTA per walker once one iteration's candidate set
+	// (or the variable scan) no longer fits a handful of warp passes.
+	int work = std::max(dev.max_candidates, dev.V);
+	if (work <= 256) return 32;
+	if (work <= 512) return 64;
+	if (work <= 2048) return 128;
+	if (work <= 8192) return 256;
+	return 512;
+}
+
+} // namespace ghost_b200

@@ -1,0 +1,94 @@
+// lowered.h — the model as the kernels see it.
+//
+// ghost_b200_model_create() validates a GhostModelDesc and lowers it into one int32 blob that is
+// copied to the device once.  This replaces, for the GPU path, ModelBuilder::build_model()'s
+// pointer wiring (reference src/model_builder.cpp:39-90) and SearchUnitData::initialize_matrix
+// (reference include/search_unit_data.hpp:95-102).
+#pragma once
+
+#include <cstdint>
+#include <string>
+#include <vector>
+
+#include "../../include/ghost_b200.h"
+
+namespace ghost_b200 {
+
+// Offsets (in int32 words) of each section inside the blob.
+struct BlobOffsets {
+	int dom_lo, dom_size, dom_off, dom_vals, start;
+	int v2c_off, v2c;          // v2c: 2 words per entry {constraint id, coefficient | scope position}
+	int kind, rhs, cnt_tab;    // cnt_tab[c] = cnt_off[c] - cnt_base[c]  (index = cnt_tab[c] + value)
+	int c2v_off, c2v, ent_ctr; // ent_ctr[i] = constraint owning scope entry i
+	int ent_coef;              // coefficient of scope entry i (linear), 0 otherwise
+	int cnt_owner;             // [cnt_total] constraint owning count-table slot t
+	int obj_coef;              // dense [V]
+	int total;
+};
+
+// Plain-old-data view handed to kernels by value.
+struct DevModel {
+	const int32_t* blob;       // device pointer
+	BlobOffsets o;
+	int V, C, nnz;
+	int permutation;
+	int objective;             // GhostObjectiveKind
+	int contiguous_domains;    // every domain is [lo, lo+size)
+	int identical_domains;     // all variables share one domain (enables the parallel permutation sampler)
+	int cnt_total;             // total AllDifferent count-table slots
+	int max_candidates;        // max over variables of candidate slots (V for permutation problems)
+	int max_degree;            // max #constraints touching one variable
+	int has_abs_diff;
+};
+
+// Per-walker shared-memory layout, byte offsets from the walker's base.
+struct WalkerLayout {
+	int x, err_var, tabu, S, err_c;     // int32 arrays
+	int cnt;                            // uint16 [cnt_total]
+	int mark;                           // uint8 [C]
+	int flags;                          // uint8 [V]   sampling scratch
+	int cand_key, cand_bits;            // int32 [nchunks_v] each: candidate-variable chunks
+	int val_key, val_bits;              // int32 [nchunks_c] each: candidate-value chunks
+	int hoist;                          // int32 [max_degree * 8]
+	int upd;                            // int32 [2*max_degree * 2]
+	int sample;                         // int32 [2 * nreset]
+	int red;                            // int32 [64] cross-warp scratch
+	int persist_bytes;                  // x..cnt(+cand chunks) prefix that is saved between epochs
+	int total_bytes;
+	int nchunks_v, nchunks_c;
+};
+
+// Scalars of one walker that survive between kernel launches.
+struct WalkerScalars {
+	int32_t initialized;
+	int32_t must_compute;
+	int32_t ncand;
+	int32_t n_tabu;
+	int32_t local_moves;
+	int32_t cur_sat;
+	int32_t best_sat;
+	int32_t resume_pending;     // Options::resume_search not yet consumed
+	int32_t cand_max;           // projected error of the current candidate set
+	int32_t done;               // loop condition of search_unit.hpp:728-730 became false
+	int64_t cur_opt;
+	int64_t best_opt;
+	int64_t obj_sum;            // sum coef*x (unsigned by max/min)
+	uint64_t next_event;
+	GhostCounters k;
+};
+
+struct LoweredModel {
+	std::vector<int32_t> blob;
+	DevModel dev{};             // dev.blob filled when uploaded
+	// host copies used for validation / result conversion
+	int V = 0, C = 0;
+	std::vector<int32_t> start;
+	int64_t error_bound = 0;    // upper bound of the total satisfaction error (must fit int32)
+	WalkerLayout layout(int threads_per_walker, int nreset) const;
+	int default_threads_per_walker() const;
+};
+
+// Returns GHOST_B200_OK or an error code; on error `why` holds the message.
+int lower_model(const GhostModelDesc* d, LoweredModel* out, std::string* why);
+
+} // namespace ghost_b200

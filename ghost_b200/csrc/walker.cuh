@@ -1,0 +1,671 @@
+// walker.cuh — device code of the local-search walkers (sm_100a).
+//
+// One walker = one SearchUnit of the reference (include/search_unit.hpp:87) mapped on a group of
+// T threads: a warp (T = 32, several walkers per CTA) or a whole CTA (T = 64..512).  The walker's
+// assignment, projected errors, tabu list, constraint caches (running sums, AllDifferent count
+// tables) and candidate sets live in shared memory; the model (incidence both ways, coefficients,
+// domains) is one read-only int32 blob read through the L1/L2 read-only path.
+//
+// All arithmetic is int32: the stock constraints with integer coefficients produce integer-valued
+// doubles in the reference, so results are bit-identical after conversion (lower.cpp rejects
+// anything that would not fit).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "lowered.h"
+
+namespace ghost_b200 {
+
+#define GB_INT_MAX 0x7fffffff
+#define GB_I64_MAX 0x7fffffffffffffffLL
+
+// ---------------------------------------------------------------------------------------------
+// Philox4x32-10 counter-based RNG (Salmon et al., SC'11).  Replaces the reference's entropy-seeded
+// mt19937 (thirdparty/randutils.hpp:605-807).  Stream layout ("RNG protocol"):
+//   key = (seed_lo, seed_hi ^ walker_hi), counter = (event_lo, event_hi, slot, walker_lo).
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint4 philox4x32_10(uint4 c, uint2 k)
+{
+#pragma unroll
+	for (int r = 0; r < 10; ++r) {
+		uint32_t hi0 = __umulhi(0xD2511F53u, c.x), lo0 = 0xD2511F53u * c.x;
+		uint32_t hi1 = __umulhi(0xCD9E8D57u, c.z), lo1 = 0xCD9E8D57u * c.z;
+		c = make_uint4(hi1 ^ c.y ^ k.x, lo1, hi0 ^ c.w ^ k.y, lo0);
+		k.x += 0x9E3779B9u;
+		k.y += 0xBB67AE85u;
+	}
+	return c;
+}
+
+struct Rng {
+	uint64_t seed, walker, next_event;
+	__device__ __forceinline__ uint4 block(uint64_t event, uint32_t slot) const
+	{
+		return philox4x32_10(make_uint4((uint32_t)event, (uint32_t)(event >> 32), slot, (uint32_t)walker),
+		                     make_uint2((uint32_t)seed, (uint32_t)(seed >> 32) ^ (uint32_t)(walker >> 32)));
+	}
+	__device__ __forceinline__ uint32_t word(uint64_t event, uint32_t index) const
+	{
+		uint4 b = block(event, index >> 2);
+		uint32_t q = index & 3u;
+		return q == 0 ? b.x : q == 1 ? b.y : q == 2 ? b.z : b.w;
+	}
+};
+__device__ __forceinline__ uint32_t below(uint32_t word, uint32_t n) { return __umulhi(word, n); }
+
+// ---------------------------------------------------------------------------------------------
+// Thread group of one walker
+// ---------------------------------------------------------------------------------------------
+template <int T>
+struct Group {
+	static constexpr int NW = T / 32;
+	__device__ __forceinline__ static void sync()
+	{
+		if (T == 32) __syncwarp(); else __syncthreads();
+	}
+	__device__ __forceinline__ static int tid() { return T == 32 ? (threadIdx.x & 31) : threadIdx.x; }
+	__device__ __forceinline__ static int warp() { return T == 32 ? 0 : (threadIdx.x >> 5); }
+
+	// Sum over the group; `red` is a private 16-int scratch region that nobody else touches
+	// between this call and the next group barrier.
+	__device__ __forceinline__ static int sum(int v, int* red)
+	{
+		v = __reduce_add_sync(0xffffffffu, v);
+		if (T == 32) return v;
+		if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+		__syncthreads();
+		int s = 0;
+#pragma unroll
+		for (int w = 0; w < NW; ++w) s += red[w];
+		return s;
+	}
+	__device__ __forceinline__ static long long sum64(long long v, int* red)
+	{
+#pragma unroll
+		for (int off = 16; off > 0; off >>= 1) v += __shfl_xor_sync(0xffffffffu, v, off);
+		if (T == 32) return v;
+		long long* r64 = reinterpret_cast<long long*>(red);
+		if ((threadIdx.x & 31) == 0) r64[threadIdx.x >> 5] = v;
+		__syncthreads();
+		long long s = 0;
+#pragma unroll
+		for (int w = 0; w < NW; ++w) s += r64[w];
+		return s;
+	}
+};
+
+// Shared-memory view of one walker
+struct WS {
+	int* x; int* err_var; int* tabu; int* S; int* err_c;
+	int* cand_key; unsigned* cand_bits;
+	unsigned* cnt32;            // packed 16-bit counters, two per word
+	unsigned char* mark; unsigned char* flags;
+	int* val_key; unsigned* val_bits;
+	int* hoist; int* upd; int* sample; int* red;
+	__device__ __forceinline__ int cnt(int idx) const { return reinterpret_cast<const unsigned short*>(cnt32)[idx]; }
+	__device__ __forceinline__ void cnt_add(int idx, int d) const
+	{
+		atomicAdd(&cnt32[idx >> 1], (unsigned)d << ((idx & 1) * 16));
+	}
+};
+
+__device__ __forceinline__ WS make_ws(unsigned char* base, const WalkerLayout& L)
+{
+	WS s;
+	s.x = (int*)(base + L.x); s.err_var = (int*)(base + L.err_var); s.tabu = (int*)(base + L.tabu);
+	s.S = (int*)(base + L.S); s.err_c = (int*)(base + L.err_c);
+	s.cand_key = (int*)(base + L.cand_key); s.cand_bits = (unsigned*)(base + L.cand_bits);
+	s.cnt32 = (unsigned*)(base + L.cnt);
+	s.mark = base + L.mark; s.flags = base + L.flags;
+	s.val_key = (int*)(base + L.val_key); s.val_bits = (unsigned*)(base + L.val_bits);
+	s.hoist = (int*)(base + L.hoist); s.upd = (int*)(base + L.upd); s.sample = (int*)(base + L.sample);
+	s.red = (int*)(base + L.red);
+	return s;
+}
+
+// Model accessors (read-only path)
+struct MV {
+	const DevModel& m;
+	__device__ __forceinline__ MV(const DevModel& mm) : m(mm) {}
+	__device__ __forceinline__ int ld(int off, int i) const { return __ldg(m.blob + off + i); }
+	__device__ __forceinline__ int dom_lo(int v) const { return ld(m.o.dom_lo, v); }
+	__device__ __forceinline__ int dom_size(int v) const { return ld(m.o.dom_size, v); }
+	__device__ __forceinline__ int dom_value(int v, int k) const
+	{
+		return m.contiguous_domains ? dom_lo(v) + k : ld(m.o.dom_vals, ld(m.o.dom_off, v) + k);
+	}
+	__device__ __forceinline__ bool in_domain(int v, int value) const
+	{
+		int lo = dom_lo(v), n = dom_size(v);
+		if (m.contiguous_domains) return value >= lo && value < lo + n;
+		int b = ld(m.o.dom_off, v), e = b + n;
+		while (b < e) {
+			int mid = (b + e) >> 1, dv = ld(m.o.dom_vals, mid);
+			if (dv == value) return true;
+			if (dv < value) b = mid + 1; else e = mid;
+		}
+		return false;
+	}
+	__device__ __forceinline__ int row_begin(int v) const { return ld(m.o.v2c_off, v); }
+	__device__ __forceinline__ int2 row_entry(int e) const { return __ldg(reinterpret_cast<const int2*>(m.blob + m.o.v2c) + e); }
+	__device__ __forceinline__ int kind(int c) const { return ld(m.o.kind, c); }
+	__device__ __forceinline__ int rhs(int c) const { return ld(m.o.rhs, c); }
+	__device__ __forceinline__ int cnt_tab(int c) const { return ld(m.o.cnt_tab, c); }
+	__device__ __forceinline__ int scope_begin(int c) const { return ld(m.o.c2v_off, c); }
+	__device__ __forceinline__ int scope_var(int i) const { return ld(m.o.c2v, i); }
+	__device__ __forceinline__ int obj_coef(int v) const { return ld(m.o.obj_coef, v); }
+};
+
+// LinearEquation*::compute_error on t = sum - rhs
+// (reference linear_equation_eq.cpp:54-57, _neq.cpp:54-61, _leq.cpp:54-57, _geq.cpp:54-57,
+//  _l.cpp:54-61, _g.cpp:54-61)
+__device__ __forceinline__ int linear_error(int kind, int t)
+{
+	switch (kind) {
+	case GHOST_KIND_LINEAR_EQ:  return abs(t);
+	case GHOST_KIND_LINEAR_NEQ: return t == 0;
+	case GHOST_KIND_LINEAR_LEQ: return max(t, 0);
+	case GHOST_KIND_LINEAR_GEQ: return max(-t, 0);
+	case GHOST_KIND_LINEAR_L:   return max(t, 0) + (t == 0);
+	default:                    return max(-t, 0) + (t == 0); // GHOST_KIND_LINEAR_G
+	}
+}
+__device__ __forceinline__ bool kind_is_linear(int k) { return k >= GHOST_KIND_LINEAR_EQ && k <= GHOST_KIND_LINEAR_G; }
+__device__ __forceinline__ int binom2(int n) { return (n * (n - 1)) >> 1; } // all_different.cpp:38-47
+
+// ---------------------------------------------------------------------------------------------
+// AllDifferentAbsDiff (extension kind): delta of changing scope position pa to na (and pb to nb
+// when pb >= 0): recount the <= 4 neighbouring |differences|.
+// ---------------------------------------------------------------------------------------------
+__device__ inline int absdiff_delta(const MV& mv, const WS& s, int c, int pa, int na, int pb, int nb)
+{
+	int b = mv.scope_begin(c), n = mv.scope_begin(c + 1) - b, tab = mv.cnt_tab(c);
+	int pairs[4]; int np = 0;
+	auto add_pair = [&](int p) {
+		if (p < 0 || p + 1 >= n) return;
+		for (int z = 0; z < np; ++z) if (pairs[z] == p) return;
+		pairs[np++] = p;
+	};
+	add_pair(pa - 1); add_pair(pa);
+	if (pb >= 0) { add_pair(pb - 1); add_pair(pb); }
+	int keys[8], net[8]; int nk = 0;
+	auto touch = [&](int key, int d) {
+		for (int z = 0; z < nk; ++z) if (keys[z] == key) { net[z] += d; return; }
+		keys[nk] = key; net[nk] = d; ++nk;
+	};
+	for (int z = 0; z < np; ++z) {
+		int p = pairs[z];
+		int oa = s.x[mv.scope_var(b + p)], ob = s.x[mv.scope_var(b + p + 1)];
+		int va = (p == pa) ? na : (p == pb ? nb : oa);
+		int vb = (p + 1 == pa) ? na : (p + 1 == pb ? nb : ob);
+		touch(abs(ob - oa), -1);
+		touch(abs(vb - va), +1);
+	}
+	int diff = 0;
+	for (int z = 0; z < nk; ++z) {
+		int cur = s.cnt(tab + keys[z]);
+		diff += binom2(cur + net[z]) - binom2(cur);
+	}
+	return diff;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Delta of ONE constraint for a change of variable va (row entry second field = ea) to na, and,
+// when vb >= 0, of vb (second field eb) to nb.  Restates optional_delta_error of the stock
+// constraints (all_different.cpp:77-100, linear_equation.cpp:59-69, fix_value.cpp:54-64) in
+// integers.  Used on the update path; the hot evaluation path uses the hoisted forms below and is
+// checked against this one by the trajectory tests.
+// ---------------------------------------------------------------------------------------------
+__device__ inline int constraint_delta(const MV& mv, const WS& s, int c, int va, int ea, int na, int vb, int eb, int nb)
+{
+	int kind = mv.kind(c);
+	if (kind == GHOST_KIND_ALL_DIFFERENT) {
+		if (vb >= 0) {
+			// two changes; in the search these are always the swap {va,vb} -> {x[vb],x[va]}: no change
+			int oa = s.x[va], ob = s.x[vb];
+			if (na == ob && nb == oa) return 0;
+			// general two-change case, reference formula (counts both (old,new) pairs)
+			int tab = mv.cnt_tab(c);
+			int keys[4] = { oa, na, ob, nb }, net[4] = { -1, +1, -1, +1 };
+			int diff = 0;
+			for (int i = 0; i < 4; ++i) {
+				int total = 0;
+				for (int j = 0; j < 4; ++j) if (keys[j] == keys[i]) total += net[j];
+				int cur = s.cnt(tab + keys[i]);
+				if (total != 0) diff += binom2(cur + total) - binom2(cur);
+			}
+			return diff;
+		}
+		int o = s.x[va];
+		if (na == o) return 0;
+		int tab = mv.cnt_tab(c);
+		return s.cnt(tab + na) - (s.cnt(tab + o) - 1);
+	}
+	if (kind_is_linear(kind)) {
+		int t = s.S[c] - mv.rhs(c) + ea * (na - s.x[va]);
+		if (vb >= 0) t += eb * (nb - s.x[vb]);
+		return linear_error(kind, t) - s.err_c[c];
+	}
+	if (kind == GHOST_KIND_FIX_VALUE) {
+		int k = mv.rhs(c);
+		int d = abs(na - k) - abs(s.x[va] - k);
+		if (vb >= 0) d += abs(nb - k) - abs(s.x[vb] - k);
+		return d;
+	}
+	if (kind == GHOST_KIND_ALL_DIFFERENT_ABS_DIFF) return absdiff_delta(mv, s, c, ea, na, vb >= 0 ? eb : -1, nb);
+	return 0; // PURE_OPTIMIZATION
+}
+
+// ---------------------------------------------------------------------------------------------
+// (Re)compute every constraint error, cache and the projection from the assignment in s.x:
+// SearchUnit::compute_constraints_errors (search_unit.hpp:434-447) + Constraint::error's cache
+// rebuild (all_different.cpp:59-75, linear_equation.cpp:50-57, fix_value.cpp:46-52) +
+// AdaptiveSearchErrorProjection::compute_variable_errors (…projection_algorithm.cpp:40-49).
+// Flat over the scope entries with a warp-segmented reduction per constraint.
+// Returns the total satisfaction error.  Ends with a group barrier.
+// ---------------------------------------------------------------------------------------------
+template <int T>
+__device__ inline int recompute_all(const DevModel& m, const WS& s, int* red)
+{
+	typedef Group<T> G;
+	MV mv(m);
+	const int tid = G::tid(), lane = threadIdx.x & 31;
+	for (int c = tid; c < m.C; c += T) { s.S[c] = 0; s.err_c[c] = 0; }
+	for (int t = tid; t < (m.cnt_total + 1) / 2; t += T) s.cnt32[t] = 0;
+	G::sync();
+	const int nnz_pad = (m.nnz + 31) & ~31;
+	for (int i = tid; i < nnz_pad; i += T) {
+		int c = -1, val = 0, kind = -1;
+		if (i < m.nnz) {
+			c = mv.ld(m.o.ent_ctr, i);
+			kind = mv.kind(c);
+			int u = mv.scope_var(i);
+			int xu = s.x[u];
+			if (kind_is_linear(kind)) val = mv.ld(m.o.ent_coef, i) * xu;
+			else if (kind == GHOST_KIND_FIX_VALUE) val = abs(xu - mv.rhs(c));
+			else if (kind == GHOST_KIND_ALL_DIFFERENT) s.cnt_add(mv.cnt_tab(c) + xu, 1);
+			else if (kind == GHOST_KIND_ALL_DIFFERENT_ABS_DIFF) {
+				if (i + 1 < mv.scope_begin(c + 1)) s.cnt_add(mv.cnt_tab(c) + abs(s.x[mv.scope_var(i + 1)] - xu), 1);
+			}
+		}
+		// inclusive segmented scan by constraint id
+#pragma unroll
+		for (int off = 1; off < 32; off <<= 1) {
+			int c2 = __shfl_up_sync(0xffffffffu, c, off);
+			int v2 = __shfl_up_sync(0xffffffffu, val, off);
+			if (lane >= off && c2 == c) val += v2;
+		}
+		int cnext = __shfl_down_sync(0xffffffffu, c, 1);
+		bool tail = (lane == 31) || (cnext != c);
+		if (c >= 0 && tail && val != 0) {
+			if (kind_is_linear(kind)) atomicAdd(&s.S[c], val);
+			else if (kind == GHOST_KIND_FIX_VALUE) atomicAdd(&s.err_c[c], val);
+		}
+	}
+	G::sync();
+	for (int c = tid; c < m.C; c += T) {
+		int kind = mv.kind(c);
+		if (kind_is_linear(kind)) s.err_c[c] = linear_error(kind, s.S[c] - mv.rhs(c));
+	}
+	for (int t = tid; t < m.cnt_total; t += T) {
+		int n = s.cnt(t);
+		if (n > 1) atomicAdd(&s.err_c[mv.ld(m.o.cnt_owner, t)], binom2(n));
+	}
+	G::sync();
+	int part = 0;
+	for (int c = tid; c < m.C; c += T) part += s.err_c[c];
+	int total = G::sum(part, red);
+	for (int v = tid; v < m.V; v += T) {
+		int e = 0;
+		for (int r = mv.row_begin(v), re = mv.row_begin(v + 1); r < re; ++r) e += s.err_c[mv.row_entry(r).x];
+		s.err_var[v] = e;
+	}
+	G::sync();
+	return total;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Candidate sets are kept as (key, bitmask) per chunk of 32 slots: the set is every set bit of
+// the chunks whose key equals the global best key.  pick_kth returns the k-th member in ascending
+// slot order — the order of the reference's vectors (variable_candidates in ascending id,
+// adaptive_search_variable_candidates_heuristic.cpp:43-57; candidate_values in ascending key,
+// adaptive_search_value_heuristic.cpp:60-66).  Executed redundantly by every warp.
+// ---------------------------------------------------------------------------------------------
+__device__ inline int chunks_count(const int* key, const unsigned* bits, int nchunks, int best)
+{
+	const int lane = threadIdx.x & 31;
+	int n = 0;
+	for (int ch = lane; ch < ((nchunks + 31) & ~31); ch += 32) {
+		int c = (ch < nchunks && key[ch] == best) ? __popc(bits[ch]) : 0;
+		n += __reduce_add_sync(0xffffffffu, c);
+	}
+	return n;
+}
+__device__ inline int pick_kth(const int* key, const unsigned* bits, int nchunks, int best, int k)
+{
+	const int lane = threadIdx.x & 31;
+	int result = -1;
+	for (int base = 0; base < nchunks; base += 32) {
+		int ch = base + lane;
+		unsigned b = (ch < nchunks && key[ch] == best) ? bits[ch] : 0u;
+		int c = __popc(b);
+		int incl = c;
+#pragma unroll
+		for (int off = 1; off < 32; off <<= 1) {
+			int t = __shfl_up_sync(0xffffffffu, incl, off);
+			if (lane >= off) incl += t;
+		}
+		int total = __shfl_sync(0xffffffffu, incl, 31);
+		if (k < total) {
+			unsigned owner = __ballot_sync(0xffffffffu, incl > k);
+			int src = __ffs(owner) - 1;
+			int excl = __shfl_sync(0xffffffffu, incl - c, src);
+			unsigned wb = __shfl_sync(0xffffffffu, b, src);
+			int bit = __fns(wb, 0, k - excl + 1);
+			result = (base + src) * 32 + bit;
+			break;
+		}
+		k -= total;
+	}
+	return result;
+}
+// min (or max) of the chunk keys; redundantly per warp
+__device__ inline int chunks_min(const int* key, int nchunks)
+{
+	const int lane = threadIdx.x & 31;
+	int best = GB_INT_MAX;
+	for (int ch = lane; ch < ((nchunks + 31) & ~31); ch += 32) {
+		int k = ch < nchunks ? key[ch] : GB_INT_MAX;
+		best = min(best, __reduce_min_sync(0xffffffffu, k));
+	}
+	return best;
+}
+__device__ inline int chunks_max(const int* key, int nchunks)
+{
+	const int lane = threadIdx.x & 31;
+	int best = -GB_INT_MAX;
+	for (int ch = lane; ch < ((nchunks + 31) & ~31); ch += 32) {
+		int k = ch < nchunks ? key[ch] : -GB_INT_MAX;
+		best = max(best, __reduce_max_sync(0xffffffffu, k));
+	}
+	return best;
+}
+
+// ---------------------------------------------------------------------------------------------
+// AdaptiveSearchVariableCandidatesHeuristic::compute_variable_candidates (…candidates_heuristic.cpp:
+// 38-60) fused with the tabu count of the reset test (search_unit.hpp:761-763): one pass over the
+// variables.  Leaves (cand_key, cand_bits); returns ncand, writes worst error and tabu count.
+// Contains group barriers.
+// ---------------------------------------------------------------------------------------------
+template <int T>
+__device__ inline int scan_candidates(const DevModel& m, const WS& s, int nchunks_v, int local_moves,
+                                      bool free_vars_ok, int* red, int* worst_out, int* ntabu_out)
+{
+	typedef Group<T> G;
+	MV mv(m);
+	const int lane = threadIdx.x & 31;
+	int ntabu = 0;
+	for (int ch = G::warp(); ch < nchunks_v; ch += G::NW) {
+		int v = ch * 32 + lane;
+		int e = -1;
+		bool tabu = false;
+		if (v < m.V) {
+			tabu = s.tabu[v] > local_moves;
+			bool has_ctr = mv.row_begin(v + 1) > mv.row_begin(v);
+			if (!tabu && (has_ctr || free_vars_ok)) e = s.err_var[v];
+		}
+		int cmax = __reduce_max_sync(0xffffffffu, e);
+		unsigned bits = __ballot_sync(0xffffffffu, e == cmax && e >= 0);
+		ntabu += __popc(__ballot_sync(0xffffffffu, tabu));
+		if (lane == 0) { s.cand_key[ch] = cmax; s.cand_bits[ch] = bits; }
+	}
+	if (T > 32) {
+		if (lane == 0) red[G::warp()] = ntabu;
+	}
+	G::sync();
+	if (T > 32) {
+		ntabu = 0;
+#pragma unroll
+		for (int w = 0; w < G::NW; ++w) ntabu += red[w];
+	}
+	int worst = chunks_max(s.cand_key, nchunks_v);
+	int ncand = worst >= 0 ? chunks_count(s.cand_key, s.cand_bits, nchunks_v, worst) : 0;
+	*worst_out = worst;
+	*ntabu_out = ntabu;
+	return ncand;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Hoist the per-iteration invariants of the selected variable's constraints (these
+// are not charged per candidate).  Entry layout, 8 ints:
+//   [0] type 0 alldiff | 1 linear | 2 fix | 3 zero | 4 absdiff     [7] constraint id
+//   alldiff: [1] count-table base, [2] cnt[x_v]-1
+//   linear : [1] a_v, [2] S - rhs - a_v*x_v, [3] current error, [4] kind
+//   fix    : [1] k, [2] |x_v-k|
+//   absdiff: [1] scope position of v
+// In permutation mode mark[c] = entry index + 1.
+// ---------------------------------------------------------------------------------------------
+template <int T>
+__device__ inline int hoist_variable(const DevModel& m, const WS& s, int v)
+{
+	typedef Group<T> G;
+	MV mv(m);
+	const int rb = mv.row_begin(v), deg = mv.row_begin(v + 1) - rb;
+	const int xv = s.x[v];
+	for (int k = G::tid(); k < deg; k += T) {
+		int2 e = mv.row_entry(rb + k);
+		int c = e.x, kind = mv.kind(c);
+		int* h = s.hoist + 8 * k;
+		h[7] = c;
+		if (kind == GHOST_KIND_ALL_DIFFERENT) {
+			int tab = mv.cnt_tab(c);
+			h[0] = 0; h[1] = tab; h[2] = s.cnt(tab + xv) - 1;
+		} else if (kind_is_linear(kind)) {
+			h[0] = 1; h[1] = e.y; h[2] = s.S[c] - mv.rhs(c) - e.y * xv; h[3] = s.err_c[c]; h[4] = kind;
+		} else if (kind == GHOST_KIND_FIX_VALUE) {
+			int kk = mv.rhs(c);
+			h[0] = 2; h[1] = kk; h[2] = abs(xv - kk);
+		} else if (kind == GHOST_KIND_ALL_DIFFERENT_ABS_DIFF) {
+			h[0] = 4; h[1] = e.y;
+		} else h[0] = 3;
+		if (m.permutation) s.mark[c] = (unsigned char)(k + 1);
+	}
+	return deg;
+}
+template <int T>
+__device__ inline void unmark_variable(const DevModel& m, const WS& s, int v)
+{
+	MV mv(m);
+	const int rb = mv.row_begin(v), deg = mv.row_begin(v + 1) - rb;
+	for (int k = Group<T>::tid(); k < deg; k += T) s.mark[mv.row_entry(rb + k).x] = 0;
+}
+
+// delta of hoisted entry h when the selected variable alone takes value d (d != x_v)
+__device__ __forceinline__ int hoisted_single(const MV& mv, const WS& s, const int* h, int d)
+{
+	int4 a = *reinterpret_cast<const int4*>(h);
+	switch (a.x) {
+	case 0: return s.cnt(a.y + d) - a.z;
+	case 1: return linear_error(h[4], a.z + a.y * d) - a.w;
+	case 2: return abs(d - a.y) - a.z;
+	case 4: return absdiff_delta(mv, s, h[7], a.y, d, -1, 0);
+	default: return 0;
+	}
+}
+
+// Cumulated delta of one candidate (search_unit.hpp:836-887 + std::accumulate of
+// adaptive_search_value_heuristic.cpp:57-58).  slot = domain index (non-permutation) or partner
+// variable (permutation).  Returns false if the slot is not a candidate.
+__device__ __forceinline__ bool candidate_sum(const DevModel& m, const MV& mv, const WS& s, int v, int xv, int deg,
+                                              int slot, int nslots, int* out)
+{
+	if (slot >= nslots) return false;
+	if (!m.permutation) {
+		int d = mv.dom_value(v, slot);
+		if (d == xv) return false;                       // search_unit.hpp:833
+		int sum = 0;
+		for (int k = 0; k < deg; ++k) sum += hoisted_single(mv, s, s.hoist + 8 * k, d);
+		*out = sum;                                      // deg == 0: 0.0 (search_unit.hpp:847-848)
+		return true;
+	}
+	const int j = slot;
+	if (j == v) return false;
+	const int xj = s.x[j];
+	if (xj == xv) return false;                          // search_unit.hpp:855-860
+	if (!m.identical_domains && !(mv.in_domain(v, xj) && mv.in_domain(j, xv))) return false;
+	int sum = 0;
+	for (int k = 0; k < deg; ++k) sum += hoisted_single(mv, s, s.hoist + 8 * k, xj);
+	for (int r = mv.row_begin(j), re = mv.row_begin(j + 1); r < re; ++r) {
+		int2 e = mv.row_entry(r);
+		int c = e.x, mk = s.mark[c];
+		if (mk == 0) {
+			// constraint of the partner only: {j} -> {x_v}  (search_unit.hpp:881-885)
+			int kind = mv.kind(c);
+			if (kind == GHOST_KIND_ALL_DIFFERENT) {
+				int tab = mv.cnt_tab(c);
+				sum += s.cnt(tab + xv) - (s.cnt(tab + xj) - 1);
+			} else if (kind_is_linear(kind)) {
+				sum += linear_error(kind, s.S[c] - mv.rhs(c) + e.y * (xv - xj)) - s.err_c[c];
+			} else if (kind == GHOST_KIND_FIX_VALUE) {
+				int kk = mv.rhs(c);
+				sum += abs(xv - kk) - abs(xj - kk);
+			} else if (kind == GHOST_KIND_ALL_DIFFERENT_ABS_DIFF) {
+				sum += absdiff_delta(mv, s, c, e.y, xv, -1, 0);
+			}
+		} else {
+			// both variables in scope: {v,j} -> {x_j,x_v} (search_unit.hpp:872-874); replace the
+			// single-variable delta already added from the hoisted entry
+			const int* h = s.hoist + 8 * (mk - 1);
+			int type = h[0];
+			if (type == 0) sum -= s.cnt(h[1] + xj) - h[2];
+			else if (type == 1) {
+				int t1 = h[2] + h[1] * xj;
+				sum += linear_error(h[4], t1 + e.y * (xv - xj)) - linear_error(h[4], t1);
+			} else if (type == 2) sum += abs(xv - h[1]) - abs(xj - h[1]);
+			else if (type == 4) sum += absdiff_delta(mv, s, c, h[1], xj, e.y, xv) - absdiff_delta(mv, s, c, h[1], xj, -1, 0);
+		}
+	}
+	*out = sum;
+	return true;
+}
+
+// Evaluate every candidate of variable v: chunk minima + tie masks into (val_key, val_bits).
+// If out != nullptr also stores each candidate's sum (GHOST_B200_NOT_A_CANDIDATE otherwise).
+// Returns the number of candidates seen by this thread's warp chunks (to be group-summed).
+template <int T>
+__device__ inline int evaluate_candidates(const DevModel& m, const WS& s, int v, int deg, int nchunks_c, int* out)
+{
+	typedef Group<T> G;
+	MV mv(m);
+	const int lane = threadIdx.x & 31;
+	const int xv = s.x[v];
+	const int nslots = m.permutation ? m.V : mv.dom_size(v);
+	int ncandidates = 0;
+	for (int ch = G::warp(); ch < nchunks_c; ch += G::NW) {
+		int slot = ch * 32 + lane;
+		int sum = GB_INT_MAX;
+		bool ok = candidate_sum(m, mv, s, v, xv, deg, slot, nslots, &sum);
+		if (!ok) sum = GB_INT_MAX;
+		if (out && slot < m.max_candidates) out[slot] = sum;
+		int cmin = __reduce_min_sync(0xffffffffu, sum);
+		unsigned okmask = __ballot_sync(0xffffffffu, ok);
+		unsigned bits = __ballot_sync(0xffffffffu, ok && sum == cmin);
+		ncandidates += __popc(okmask);
+		if (lane == 0) { s.val_key[ch] = cmin; s.val_bits[ch] = bits; }
+	}
+	return lane == 0 ? ncandidates : 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// SearchUnit::local_move's update part (search_unit.hpp:449-541): constraint errors, caches,
+// projection, then the value(s).  One thread per affected constraint computes its delta with the
+// generic constraint_delta(); the projection update (…projection_algorithm.cpp:51-58) is a
+// shared-memory scatter.  Returns nothing; ends with a barrier.  `partner` is the swap partner in
+// permutation mode, `new_value` the value otherwise.
+// ---------------------------------------------------------------------------------------------
+template <int T>
+__device__ inline void apply_move(const DevModel& m, const WS& s, int v, int new_value)
+{
+	typedef Group<T> G;
+	MV mv(m);
+	const int tid = G::tid();
+	const int rbv = mv.row_begin(v), degv = mv.row_begin(v + 1) - rbv;
+	const int xv = s.x[v];
+	int j = -1, xj = 0, rbj = 0, degj = 0;
+	if (m.permutation) { j = new_value; xj = s.x[j]; rbj = mv.row_begin(j); degj = mv.row_begin(j + 1) - rbj; }
+	const int nv_new = m.permutation ? xj : new_value;
+	const int naff = degv + degj;
+	for (int k = tid; k < naff; k += T) {
+		int c, delta;
+		if (k < degv) {
+			int2 e = mv.row_entry(rbv + k);
+			c = e.x;
+			int eb = 0; bool both = false;
+			if (m.permutation) {
+				for (int r = rbj; r < rbj + degj; ++r) { int2 f = mv.row_entry(r); if (f.x == c) { both = true; eb = f.y; break; } }
+			}
+			delta = constraint_delta(mv, s, c, v, e.y, nv_new, both ? j : -1, eb, xv);
+			int kind = mv.kind(c);
+			if (kind == GHOST_KIND_ALL_DIFFERENT) {
+				if (!both && nv_new != xv) { int tab = mv.cnt_tab(c); s.cnt_add(tab + xv, -1); s.cnt_add(tab + nv_new, +1); }
+			} else if (kind_is_linear(kind)) {
+				s.S[c] += e.y * (nv_new - xv) + (both ? eb * (xv - xj) : 0);
+			}
+			s.err_c[c] += delta;
+		} else {
+			int2 e = mv.row_entry(rbj + (k - degv));
+			c = e.x;
+			if (s.mark[c] != 0) { s.upd[2 * k] = -1; continue; } // shared with v: handled above
+			delta = constraint_delta(mv, s, c, j, e.y, xv, -1, 0, 0);
+			int kind = mv.kind(c);
+			if (kind == GHOST_KIND_ALL_DIFFERENT) {
+				if (xv != xj) { int tab = mv.cnt_tab(c); s.cnt_add(tab + xj, -1); s.cnt_add(tab + xv, +1); }
+			} else if (kind_is_linear(kind)) s.S[c] += e.y * (xv - xj);
+			s.err_c[c] += delta;
+		}
+		s.upd[2 * k] = c; s.upd[2 * k + 1] = delta;
+	}
+	G::sync();
+	for (int k = 0; k < naff; ++k) {
+		int c = s.upd[2 * k], delta = s.upd[2 * k + 1];
+		if (c < 0 || delta == 0) continue;
+		int b = mv.scope_begin(c), e = mv.scope_begin(c + 1);
+		for (int i = b + tid; i < e; i += T) atomicAdd(&s.err_var[mv.scope_var(i)], delta);
+	}
+	if (tid == 0) {
+		s.x[v] = nv_new;
+		if (m.permutation) s.x[j] = xv;
+	}
+	G::sync();
+	if (m.has_abs_diff) {
+		// refresh the |difference| tables of the extension kind from the new assignment
+		for (int k = tid; k < naff; k += T) {
+			int c = s.upd[2 * k];
+			if (c < 0 || mv.kind(c) != GHOST_KIND_ALL_DIFFERENT_ABS_DIFF) continue;
+			int b = mv.scope_begin(c), n = mv.scope_begin(c + 1) - b, tab = mv.cnt_tab(c);
+			int2 e = (k < degv) ? mv.row_entry(rbv + k) : mv.row_entry(rbj + (k - degv));
+			int pa = e.y, pb = -1;
+			if (k < degv && m.permutation)
+				for (int r = rbj; r < rbj + degj; ++r) { int2 f = mv.row_entry(r); if (f.x == c) { pb = f.y; break; } }
+			int pairs[4]; int np = 0;
+			auto add_pair = [&](int p) { if (p < 0 || p + 1 >= n) return; for (int z = 0; z < np; ++z) if (pairs[z] == p) return; pairs[np++] = p; };
+			add_pair(pa - 1); add_pair(pa);
+			if (pb >= 0) { add_pair(pb - 1); add_pair(pb); }
+			int va = (k < degv) ? v : j, vb2 = (k < degv) ? j : -1;
+			for (int z = 0; z < np; ++z) {
+				int ua = mv.scope_var(b + pairs[z]), ub = mv.scope_var(b + pairs[z] + 1);
+				int na = s.x[ua], nb = s.x[ub];
+				// old values: undo the write
+				int oa = (ua == va) ? (k < degv ? xv : xj) : ((ua == vb2 && pb >= 0) ? xj : na);
+				int ob = (ub == va) ? (k < degv ? xv : xj) : ((ub == vb2 && pb >= 0) ? xj : nb);
+				s.cnt_add(tab + abs(ob - oa), -1);
+				s.cnt_add(tab + abs(nb - na), +1);
+			}
+		}
+		G::sync();
+	}
+}
+
+} // namespace ghost_b200

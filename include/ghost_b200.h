@@ -212,6 +212,12 @@ void ghost_b200_search_end(GhostSearch* search);
 int ghost_b200_search_walkers(GhostSearch* search, int32_t* best_x, int64_t* best_sat, int64_t* best_opt,
                               GhostCounters* counters);
 
+/* Debug/test hook (no reference counterpart; the reference prints its trace under GHOST_TRACE,
+ * include/search_unit.hpp:741-746, 808-819): when the environment variable GHOST_B200_TRACE=<rows>
+ * is set at search_begin, walker 0 records one row of 8 ints per iteration
+ * {iteration, variable, new value, branch, #candidates, min conflict, current sat error, 0}. */
+int ghost_b200_search_trace(GhostSearch* search, int32_t* rows, int32_t cap, int32_t* len);
+
 const char* ghost_b200_last_error(void);
 const char* ghost_b200_version(void);
 

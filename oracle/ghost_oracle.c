@@ -905,8 +905,8 @@ int oracle_search(const OracleModel* m, const GhostSearchOpts* opts, uint64_t wa
 
 		int pick = (int)below(rnd[0], (uint32_t)w->ncand);
 		int v = w->cand[pick];
-		/* erase (826-828); order is irrelevant to a uniform pick, so swap-with-last */
-		w->cand[pick] = w->cand[w->ncand - 1];
+		/* erase, keeping the ascending order of the vector (826-828) */
+		for (int i = pick; i + 1 < w->ncand; ++i) w->cand[i] = w->cand[i + 1];
 		--w->ncand;
 
 		double min_conflict;

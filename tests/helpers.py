@@ -1,0 +1,75 @@
+"""Shared helpers for the parity tests (test infrastructure)."""
+from __future__ import annotations
+
+import numpy as np
+
+from ghost_b200 import problems
+from ghost_b200.modeldesc import NOT_A_CANDIDATE, ModelDesc
+
+SMALL_MODELS = ["magic_square:4", "magic_square:7", "n_queens:8", "n_queens:20", "costas:6", "costas:9",
+                "knapsack:20x3", "knapsack:50x5", "all_interval:10"]
+
+
+def random_assignment(desc: ModelDesc, rng: np.random.Generator):
+    """Permutation problems: a shuffle of the start values; otherwise one value per domain."""
+    if desc.permutation_problem:
+        x = np.array(desc.start_values, dtype=np.int32)
+        rng.shuffle(x)
+        return x
+    return np.array([d[rng.integers(0, len(d))] for d in desc.domains], dtype=np.int32)
+
+
+def mixed_model() -> ModelDesc:
+    """Every stock kind at once, explicit (non-contiguous) domains, negative coefficients."""
+    m = ModelDesc(permutation_problem=False, name="mixed")
+    doms = [[1, 2, 5, 7, 8], [0, 3, 4, 9], [-3, -1, 2, 5, 6, 7], [2, 3, 4, 5], [1, 5, 9], [0, 1, 2, 3, 4, 5, 6, 7],
+            [-2, 0, 2, 4, 8], [5, 6, 7, 9]]
+    for d in doms:
+        m.add_variable(domain=d, index=1)
+    from ghost_b200 import modeldesc as md
+    m.all_different([0, 1, 2, 3, 4])
+    m.all_different([3, 4, 5, 6, 7])
+    m.linear(md.LINEAR_EQ, [0, 1, 2], 9, [2, -1, 3])
+    m.linear(md.LINEAR_NEQ, [1, 3], 7, [1, 1])
+    m.linear(md.LINEAR_LEQ, [2, 3, 4, 5], 10, [1, 2, -1, 1])
+    m.linear(md.LINEAR_GEQ, [4, 5, 6], 12, [1, 1, 1])
+    m.linear(md.LINEAR_L, [5, 6, 7], 14, [1, -2, 1])
+    m.linear(md.LINEAR_G, [0, 7], 6, [1, 1])
+    m.fix_value([2, 6], 2)
+    return m
+
+
+def mixed_permutation_model() -> ModelDesc:
+    """Permutation problem with different domains per variable (general eligibility path)."""
+    from ghost_b200 import modeldesc as md
+    m = ModelDesc(permutation_problem=True, name="mixed_perm")
+    n = 9
+    for i in range(n):
+        dom = list(range(1, n + 1)) if i % 3 else [v for v in range(1, n + 1) if v != ((i + 4) % n) + 1]
+        m.add_variable(domain=dom, index=dom.index(i + 1) if (i + 1) in dom else 0)
+    # make the start a permutation of 1..n where possible
+    m.all_different(range(n))
+    m.linear(md.LINEAR_EQ, [0, 1, 2], 15)
+    m.linear(md.LINEAR_LEQ, [3, 4, 5], 14, [1, 2, 1])
+    m.linear(md.LINEAR_GEQ, [6, 7, 8, 0], 12, [1, 1, 1, -1])
+    m.linear(md.LINEAR_NEQ, [2, 5], 9)
+    m.fix_value([4], 5)
+    m.all_different([0, 4, 8])
+    return m
+
+
+def to_int_or_sentinel(cand_delta_f64):
+    """Oracle doubles (NaN = not a candidate) -> the int32 convention of the C ABI."""
+    out = np.full(cand_delta_f64.shape, NOT_A_CANDIDATE, dtype=np.int64)
+    ok = ~np.isnan(cand_delta_f64)
+    assert np.all(cand_delta_f64[ok] == np.round(cand_delta_f64[ok]))
+    out[ok] = cand_delta_f64[ok].astype(np.int64)
+    return out
+
+
+def model_by_name(name):
+    if name == "mixed":
+        return mixed_model()
+    if name == "mixed_perm":
+        return mixed_permutation_model()
+    return problems.by_name(name)

@@ -1,0 +1,132 @@
+"""GPU parity of the whole walker state machine (SearchUnit::local_search, reference
+include/search_unit.hpp:685-1201) against the oracle restatement, walker by walker: with the same
+Philox stream the trajectories are identical, so best assignment, best errors and all eight counters
+must be equal.  Plus the reference-side properties: every returned solution has Σ error() == 0
+under the reference's own constraint code when oracle/_ref is available."""
+import os
+
+import numpy as np
+import pytest
+
+from ghost_b200.modeldesc import default_opts
+from tests.helpers import model_by_name
+
+pytestmark = pytest.mark.gpu
+
+INT_MAX = 2**31 - 1
+I64_MAX = 2**63 - 1
+
+
+def _run_gpu(desc, opts, iterations, epochs=1):
+    from ghost_b200 import capi
+    model = capi.Model(desc)
+    s = model.begin(opts)
+    per = iterations // epochs
+    for _ in range(epochs):
+        s.epoch(per)
+    W = opts.number_walkers
+    out = s.walkers(W)
+    res = s.result()
+    s.end()
+    model.close()
+    return out, res
+
+
+def _check_against_oracle(desc, oracle_built, iterations, walkers, seed, threads=0, epochs=1, first_walker=0, **kw):
+    port = oracle_built.OraclePort(desc)
+    opts = default_opts(seed=seed, number_walkers=walkers, threads_per_walker=threads, stop_on_first_solution=0,
+                        max_iterations=iterations, first_walker_id=first_walker, **kw)
+    port.resolve_opts(opts)
+    out, res = _run_gpu(desc, opts, iterations, epochs)
+    for w in range(walkers):
+        want = port.search(opts, first_walker + w, iterations)
+        got_c = out["counters"][w]
+        assert got_c == want["counters"], (desc.name, w, got_c, want["counters"])
+        bs = out["best_sat"][w]
+        assert (np.finfo(np.float64).max if bs == INT_MAX else float(bs)) == want["best_sat"], (desc.name, w)
+        bo = out["best_opt"][w]
+        assert (np.finfo(np.float64).max if bo == I64_MAX else float(bo)) == want["best_opt"], (desc.name, w)
+        assert np.array_equal(out["best_x"][w], want["best_x"]), (desc.name, w)
+        e, _ = port.check(out["best_x"][w])
+        assert e == want["best_sat"]
+    return out, res
+
+
+@pytest.mark.parametrize("name", ["magic_square:4", "magic_square:7", "n_queens:8", "n_queens:20", "costas:6",
+                                  "costas:9", "knapsack:20x3", "knapsack:50x5", "all_interval:10", "mixed",
+                                  "mixed_perm"])
+def test_trajectories_match_oracle(name, oracle_built):
+    _check_against_oracle(model_by_name(name), oracle_built, iterations=600, walkers=12, seed=2024)
+
+
+@pytest.mark.parametrize("threads", [32, 64, 128, 256])
+@pytest.mark.parametrize("name", ["magic_square:7", "n_queens:20", "mixed_perm", "knapsack:50x5"])
+def test_trajectories_every_mapping(name, threads, oracle_built):
+    _check_against_oracle(model_by_name(name), oracle_built, iterations=300, walkers=5, seed=5, threads=threads)
+
+
+def test_epochs_do_not_change_the_trajectory(oracle_built):
+    """State saved/restored between kernel launches: 8 epochs of 50 == 1 launch of 400."""
+    _check_against_oracle(model_by_name("magic_square:7"), oracle_built, iterations=400, walkers=6, seed=9, epochs=8)
+    _check_against_oracle(model_by_name("n_queens:20"), oracle_built, iterations=400, walkers=6, seed=9, epochs=8)
+
+
+def test_walker_ids_are_global(oracle_built):
+    """first_walker_id shards one logical population over GPUs: walker w of a shard starting at 1000
+    is walker 1000+w of the oracle."""
+    _check_against_oracle(model_by_name("costas:6"), oracle_built, iterations=300, walkers=4, seed=1, first_walker=1000)
+
+
+def test_custom_start_and_options(oracle_built):
+    _check_against_oracle(model_by_name("magic_square:7"), oracle_built, iterations=300, walkers=4, seed=3,
+                          custom_starting_point=1)
+    _check_against_oracle(model_by_name("n_queens:20"), oracle_built, iterations=300, walkers=4, seed=3,
+                          resume_search=1, tabu_time_selected=2, percent_chance_force_trying_on_plateau=35,
+                          restart_threshold=3, number_variables_to_reset=7, number_start_samplings=3)
+    _check_against_oracle(model_by_name("knapsack:50x5"), oracle_built, iterations=300, walkers=4, seed=3,
+                          enable_optimization_guidance=0)
+
+
+@pytest.mark.parametrize("name", ["magic_square:30", "n_queens:100", "costas:20", "knapsack:500x30"])
+def test_trajectories_baseline_sizes(name, oracle_built):
+    """BASELINE.json's configurations at full size, few walkers and iterations (oracle speed)."""
+    _check_against_oracle(model_by_name(name), oracle_built, iterations=60, walkers=3, seed=77)
+
+
+def test_blocking_search_solves_and_reference_accepts(oracle_built):
+    """ghost_b200_search (what Solver::fast_search calls): solutions of CSPs are re-checked with the
+    reference's own Constraint::error (oracle/_ref) when present, else with the oracle port."""
+    from ghost_b200 import capi
+    for name in ["magic_square:5", "n_queens:12", "costas:5", "all_interval:12"]:
+        desc = model_by_name(name)
+        model = capi.Model(desc)
+        opts = default_opts(seed=123, number_walkers=512, timeout_us=20e6, epoch_iterations=64)
+        res = model.search(opts)
+        assert res["found"], name
+        assert res["final_cost"] == 0.0
+        if oracle_built.have_ref():
+            e, _ = oracle_built.RefModel(desc).check(res["solution"])
+        else:
+            e, _ = oracle_built.OraclePort(desc).check(res["solution"])
+        assert e == 0.0, name
+        model.close()
+
+
+def test_blocking_search_cop_best_cost(oracle_built):
+    """COP: the returned assignment is feasible and its objective equals final_cost (sign restored for
+    Maximize, reference include/solver.hpp:743-751)."""
+    from ghost_b200 import capi
+    desc = model_by_name("knapsack:100x5")
+    model = capi.Model(desc)
+    opts = default_opts(seed=5, number_walkers=1024, timeout_us=1.5e6, epoch_iterations=128)
+    res = model.search(opts)
+    assert res["found"]
+    e, obj = oracle_built.OraclePort(desc).check(res["solution"])
+    assert e == 0.0
+    assert obj == res["final_cost"]
+    # at least as good as the best of 8 oracle walkers with the same per-walker iteration budget / 4
+    port = oracle_built.OraclePort(desc)
+    o = port.resolve_opts(default_opts(seed=5))
+    best = max(-port.search(o, w, 2000)["best_opt"] for w in range(8))
+    assert res["final_cost"] >= best
+    model.close()
