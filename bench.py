@@ -1,0 +1,333 @@
+#!/usr/bin/env python
+"""bench.py — candidate-move evaluations/s of the GHOST local-search hot path on B200.
+
+  python bench.py --gpus N --steps K --warmup W            our arm (CUDA walkers through the C ABI)
+  python bench.py --impl reference --gpus N --steps K ...  the unmodified reference on the host cores
+
+Workload (BASELINE.json configs[1]): magic square 30x30, permutation problem, V=900,
+1 AllDifferent + 62 LinearEquationEq, synthetic (the model is generated, no dataset).
+A step = one epoch: every walker of the resident population advances `--epoch` passes of the
+SearchUnit::local_search loop (reference include/search_unit.hpp:728-1191) in ONE kernel launch.
+`value` = candidate moves evaluated by all walkers of all ranks / device time (inputs = walker
+state resident in HBM).  `e2e` = the same metric through ghost_b200_search(), the call
+Solver::fast_search makes: host descriptor in, model upload, walker-pool set-up, initial sampling,
+search, result copied back — everything inside the timed region.
+One JSON line on stdout (rank 0).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+WORKLOAD = "magic_square:30"
+METRIC = "candidate_move_evals_per_sec"
+UNIT = "evals/s"
+# SURVEY.md §8d, algorithmic work of one magic-square swap candidate: the shared AllDifferent
+# (delta 0: 1 op), four LinearEquationEq sides (row+column of the selected variable and of the
+# partner: 5 ops each, the partner's two gather 20 B each), accumulate + argmin (#constraints + 2).
+OPS_PER_EVAL = 28.0
+SMEM_BYTES_PER_EVAL = 44.0
+
+
+def physical_cores():
+    try:
+        out = subprocess.run(["lscpu", "-p=core,socket"], capture_output=True, text=True).stdout
+        cores = {l for l in out.splitlines() if l and not l.startswith("#")}
+        if cores:
+            return len(cores)
+    except Exception:
+        pass
+    return max(1, (os.cpu_count() or 2) // 2)
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.gpu_index = gpu_index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-i", str(self.gpu_index), "-lms", "100"], stdout=subprocess.PIPE, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for l in self.lines:
+            f = [x.strip() for x in l.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for n, val in zip(names, f[5:9]):
+                if val.lower().startswith("active"):
+                    reasons.add(n)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def run_reference_sample(desc, seconds, threads, parallel=True):
+    """The unmodified reference (oracle/_ref/ref_bench, built with GHOST_BENCH) on the host cores."""
+    from oracle import binding
+    if not os.path.exists(binding.REF_BENCH):
+        if not binding.build_ref():
+            return None
+    with tempfile.TemporaryDirectory() as tmp:
+        rep = binding.run_ref_bench(desc, seconds * 1e6, parallel, threads, tmp)
+    its = rep.get("total_iterations" if parallel else "iterations", 0.0)
+    resets = rep.get("total_resets" if parallel else "resets", 0.0)
+    t = rep.get("search_time_us", seconds * 1e6) * 1e-6
+    cands = desc.num_variables - 1  # every other variable is an eligible swap partner (all values distinct)
+    return {"evals_per_s": (its - resets) * cands / t, "iters_per_s": its / t, "seconds": t,
+            "iterations": its, "resets": resets}
+
+
+def reference_arm(args):
+    """--impl reference: the reference's own multi-threaded CPU solver (parallel_runs=true) on this
+    box's host cores, same workload/metric; each step is a bounded sample."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    from ghost_b200 import problems
+    desc = problems.by_name(args.workload)
+    cores = physical_cores()
+    sample_s = args.ref_seconds
+    for _ in range(min(args.warmup, 1)):
+        run_reference_sample(desc, min(1.0, sample_s), cores)
+    evals, iters, secs = 0.0, 0.0, 0.0
+    for _ in range(args.steps):
+        r = run_reference_sample(desc, sample_s, cores)
+        if r is None:
+            print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref is not built and /root/reference is not mounted"}))
+            return 0
+        evals += r["evals_per_s"] * r["seconds"]; iters += r["iterations"]; secs += r["seconds"]
+    value = evals / secs
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * secs / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": args.workload, "walkers": cores, "parallelism": f"{cores} host threads (parallel_runs)"},
+        "walker_iters_per_sec": iters / secs,
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "reference",
+                         "sample": f"{args.steps} x {sample_s:g}s of Solver::fast_search, parallel_runs=true, {cores} threads"},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line))
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default=WORKLOAD)
+    ap.add_argument("--epoch", type=int, default=64, help="loop passes per walker per step (one kernel launch)")
+    ap.add_argument("--walkers", type=int, default=0, help="walkers per GPU (0: fill the GPU)")
+    ap.add_argument("--threads-per-walker", type=int, default=0)
+    ap.add_argument("--ref-seconds", type=float, default=5.0)
+    ap.add_argument("--cpu-seconds", type=float, default=10.0)
+    ap.add_argument("--e2e-seconds", type=float, default=1.0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.warmup < 3 and args.impl == "ours":
+        args.warmup = max(args.warmup, 3)  # timing rule: at least 3 warm-up steps
+    if args.impl == "reference":
+        return reference_arm(args)
+
+    import torch
+    import torch.distributed as dist
+    from ghost_b200 import capi, problems
+    from ghost_b200.modeldesc import default_opts
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: ghost_b200 has no CPU fallback")
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    stream = torch.cuda.current_stream()
+    sptr = stream.cuda_stream
+
+    desc = problems.by_name(args.workload)
+    model = capi.Model(desc)
+    opts = default_opts(seed=20261106, number_walkers=args.walkers, threads_per_walker=args.threads_per_walker,
+                        stop_on_first_solution=0, first_walker_id=0)
+    search = model.begin(opts)
+    res0 = search.result()
+    W = res0["walkers"]
+    search.end()
+    # shard the logical population: rank r owns walkers [r*W, (r+1)*W)
+    opts.number_walkers = W
+    opts.first_walker_id = rank * W
+    search = model.begin(opts)
+
+    key = torch.zeros(1, dtype=torch.int64, device="cuda")
+    flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device="cuda")  # > 126 MB L2
+
+    def step():
+        search.epoch(args.epoch, sptr)
+        if world > 1:
+            # the path's one exchange step: best cost of the epoch, min over GPUs (NCCL over NVLink)
+            search.export_key(key.data_ptr(), sptr)
+            dist.all_reduce(key, op=dist.ReduceOp.MIN)
+
+    def counters():
+        torch.cuda.synchronize()
+        return search.result()["total"]
+
+    # the first step also runs the initial sampling; it is part of the warm-up
+    for _ in range(args.warmup):
+        step()
+        flush.fill_(1)
+    c0 = counters()
+
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    starts = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
+    ends = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
+    t_wall0 = time.perf_counter()
+    for i in range(args.steps):
+        flush.fill_(i & 0xff)  # L2 flush between timed steps, outside the event pair
+        starts[i].record(stream)
+        step()
+        ends[i].record(stream)
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    t_wall = time.perf_counter() - t_wall0
+    clocks = sampler.stop()
+    ms = sum(s.elapsed_time(e) for s, e in zip(starts, ends))
+    c1 = counters()
+    evals = c1["candidates_evaluated"] - c0["candidates_evaluated"]
+    iters = c1["search_iterations"] - c0["search_iterations"]
+
+    if world > 1:
+        t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+        cnt = torch.tensor([evals, iters], dtype=torch.float64, device="cuda")
+        dist.all_reduce(cnt, op=dist.ReduceOp.SUM)
+        evals, iters = float(cnt[0].item()), float(cnt[1].item())
+    value = evals / (ms * 1e-3)
+
+    # ---- roofline of the search kernel (the only kernel of a step): measured denominators
+    issue_peak, smem_peak = capi.microbench()
+    evals_rank = (c1["candidates_evaluated"] - c0["candidates_evaluated"]) / (ms * 1e-3)
+    persist = None
+    roofline = {
+        "bound": "issue", "kernel": f"search_kernel<{res0['threads_per_walker']}>",
+        "achieved": evals_rank * OPS_PER_EVAL / 1e12, "peak": issue_peak / 1e12, "unit": "Tlane-op/s",
+        "frac": evals_rank * OPS_PER_EVAL / issue_peak,
+        "peak_source": "ghost_b200_microbench (IMAD/IADD3/LOP3 chains, measured in this run)",
+        "algorithmic_ops_per_eval": OPS_PER_EVAL,
+        "smem": {"achieved": evals_rank * SMEM_BYTES_PER_EVAL / 1e9, "peak": smem_peak / 1e9, "unit": "GB/s",
+                 "frac": evals_rank * SMEM_BYTES_PER_EVAL / smem_peak, "algorithmic_bytes_per_eval": SMEM_BYTES_PER_EVAL},
+        "traffic": None,
+    }
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        hbm_peak, src = float(peaks["hbm_gbs"]), "MEASURED_PEAKS.json"
+    except Exception:
+        hbm_peak, src = 6650.0, "fallback (B200_PROFILING.md)"
+    state_bytes = 2.0 * model.walker_state_bytes * W  # load + store of the walker state per launch (upper bound)
+    roofline["hbm"] = {"achieved": state_bytes * args.steps / (ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
+                       "frac": state_bytes * args.steps / (ms * 1e-3) / 1e9 / hbm_peak, "peak_source": src,
+                       "note": "walker state load+store per launch; the model graph stays in L1/L2"}
+
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "int32", "data": "synthetic",
+        "config": {"workload": args.workload, "walkers_per_gpu": W, "threads_per_walker": res0["threads_per_walker"],
+                   "epoch_iterations": args.epoch, "parallelism": f"walkers sharded over {world} GPU(s)",
+                   "l2": "flushed between timed steps (256 MiB fill)"},
+        "walker_iters_per_sec": iters / (ms * 1e-3),
+        "gpu_launches": args.steps, "clocks": clocks, "roofline": roofline, "wall_s": t_wall,
+    }
+
+    if rank == 0:
+        # ---- e2e: ghost_b200_search from host buffers, everything inside the timed region
+        e2e_model_bytes = 0
+        t0 = time.perf_counter()
+        m2 = capi.Model(desc)
+        o2 = default_opts(seed=7, number_walkers=W, threads_per_walker=args.threads_per_walker, stop_on_first_solution=0,
+                          timeout_us=args.e2e_seconds * 1e6, epoch_iterations=args.epoch)
+        r2 = m2.search(o2)
+        dt = time.perf_counter() - t0
+        m2.close()
+        a = desc.arrays()
+        e2e_model_bytes = int(sum(v.nbytes for v in a.values() if hasattr(v, "nbytes")))
+        d2h = int(W * 136 + desc.num_variables * 4 + 8 * max(1, r2["kernel_launches"]))
+        line["e2e"] = {"value": r2["total"]["candidates_evaluated"] / dt, "unit": UNIT,
+                       "h2d_bytes_per_step": e2e_model_bytes, "d2h_bytes_per_step": d2h,
+                       "call": "ghost_b200_search (model_create + upload + walker set-up + search + result)",
+                       "seconds": dt, "kernel_launches": r2["kernel_launches"]}
+        # ---- CPU baseline on this box's host cores (N=1 only)
+        if world == 1 and not args.no_cpu_baseline:
+            cores = physical_cores()
+            r = run_reference_sample(desc, args.cpu_seconds, cores)
+            if r is not None:
+                line["cpu_baseline"] = {"value": r["evals_per_s"], "unit": UNIT, "cores": cores, "kind": "reference",
+                                        "sample": f"{args.cpu_seconds:g}s of the unmodified reference Solver::fast_search, "
+                                                  f"parallel_runs=true, {cores} threads",
+                                        "walker_iters_per_sec": r["iters_per_s"]}
+            else:
+                from oracle import binding
+                port = binding.OraclePort(desc)
+                o = port.resolve_opts(default_opts(seed=1))
+                t0 = time.perf_counter()
+                rr = port.search(o, 0, 300)
+                dt = time.perf_counter() - t0
+                line["cpu_baseline"] = {"value": rr["counters"]["candidates_evaluated"] / dt, "unit": UNIT, "cores": 1,
+                                        "kind": "port", "sample": "300 iterations of the oracle port, 1 thread"}
+        print(json.dumps(line))
+    search.end()
+    model.close()
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -55,6 +55,8 @@ def _load():
     lib.ghost_b200_search_end.restype = None
     lib.ghost_b200_search_walkers.argtypes = [vp, vp, vp, vp, vp]
     lib.ghost_b200_search_trace.argtypes = [vp, vp, i32, C.POINTER(i32)]
+    lib.ghost_b200_search_export_key.argtypes = [vp, vp, vp]
+    lib.ghost_b200_microbench.argtypes = [C.POINTER(C.c_double), C.POINTER(C.c_double)]
     return lib
 
 
@@ -68,6 +70,13 @@ def _check(rc):
 
 def version():
     return lib.ghost_b200_version().decode()
+
+
+def microbench():
+    """(issue lane-ops/s, shared-memory bytes/s) measured on the current device."""
+    a, b = C.c_double(), C.c_double()
+    _check(lib.ghost_b200_microbench(C.byref(a), C.byref(b)))
+    return a.value, b.value
 
 
 def _ptr(a):
@@ -153,6 +162,9 @@ class Search:
         k = C.c_uint64()
         _check(lib.ghost_b200_search_best_key(self.h, C.byref(k)))
         return k.value
+
+    def export_key(self, d_key, stream=0):
+        _check(lib.ghost_b200_search_export_key(self.h, d_key, stream))
 
     def request_stop(self):
         _check(lib.ghost_b200_search_request_stop(self.h))

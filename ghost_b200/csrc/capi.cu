@@ -358,6 +358,13 @@ extern "C" int ghost_b200_search_best_key(GhostSearch* s, uint64_t* key)
 	return GHOST_B200_OK;
 }
 
+extern "C" int ghost_b200_search_export_key(GhostSearch* s, void* d_key, void* stream)
+{
+	if (!s || !d_key) return set_error(GHOST_B200_ERR_INVALID, "null argument");
+	CUDA_TRY(cudaMemcpyAsync(d_key, s->d_best_key, sizeof(unsigned long long), cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+	return GHOST_B200_OK;
+}
+
 static double sat_to_double(int v) { return v == 0x7fffffff ? std::numeric_limits<double>::max() : (double)v; }
 static double opt_to_double(long long v) { return v == 0x7fffffffffffffffLL ? std::numeric_limits<double>::max() : (double)v; }
 

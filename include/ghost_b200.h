@@ -202,6 +202,10 @@ int ghost_b200_search_begin(GhostModel* model, const GhostSearchOpts* opts, Ghos
 int ghost_b200_search_epoch(GhostSearch* search, int32_t iterations, void* stream);
 /* Packed 64-bit key of the best walker so far: smaller is better; see DESIGN.md.  Synchronises. */
 int ghost_b200_search_best_key(GhostSearch* search, uint64_t* key);
+/* Same key, copied device-to-device into d_key (one uint64 on the current device) on `stream`
+ * without synchronising: the operand of the per-epoch NCCL allreduce-min across GPUs (the analogue
+ * of the future polling + best-of-threads reduction of include/solver.hpp:594-644, 665-723). */
+int ghost_b200_search_export_key(GhostSearch* search, void* d_key, void* stream);
 int ghost_b200_search_result(GhostSearch* search, GhostResult* result);
 /* Ask every walker to stop at its next iteration (the analogue of SearchUnit::stop_search,
  * search_unit.hpp:680). */
@@ -217,6 +221,11 @@ int ghost_b200_search_walkers(GhostSearch* search, int32_t* best_x, int64_t* bes
  * is set at search_begin, walker 0 records one row of 8 ints per iteration
  * {iteration, variable, new value, branch, #candidates, min conflict, current sat error, 0}. */
 int ghost_b200_search_trace(GhostSearch* search, int32_t* rows, int32_t cap, int32_t* len);
+
+/* Measured roofline denominators of the move-evaluation kernel on the current device (no reference
+ * counterpart): SM integer issue rate in lane-ops/s and conflict-free shared-memory bandwidth in
+ * bytes/s, each from a short CUDA-event-timed microbenchmark. */
+int ghost_b200_microbench(double* issue_lane_ops_per_s, double* smem_bytes_per_s);
 
 const char* ghost_b200_last_error(void);
 const char* ghost_b200_version(void);
