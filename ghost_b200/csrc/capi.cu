@@ -170,9 +170,15 @@ static cudaError_t launch_search(int T, int grid, int block, size_t smem, cudaSt
 	switch (T) {
 #define GB_CASE(TT)                                                                          \
 	case TT:                                                                                 \
-		e = allow_smem(search_kernel<TT>, smem);                                             \
-		if (e != cudaSuccess) return e;                                                      \
-		search_kernel<TT><<<grid, block, smem, st>>>(m, L, p);                               \
+		if (m.permutation) {                                                                 \
+			e = allow_smem(search_kernel<TT, true>, smem);                                   \
+			if (e != cudaSuccess) return e;                                                  \
+			search_kernel<TT, true><<<grid, block, smem, st>>>(m, L, p);                     \
+		} else {                                                                             \
+			e = allow_smem(search_kernel<TT, false>, smem);                                  \
+			if (e != cudaSuccess) return e;                                                  \
+			search_kernel<TT, false><<<grid, block, smem, st>>>(m, L, p);                    \
+		}                                                                                    \
 		break;
 		GB_CASE(32) GB_CASE(64) GB_CASE(128) GB_CASE(256) GB_CASE(512)
 #undef GB_CASE
@@ -188,9 +194,15 @@ static cudaError_t launch_eval(int T, int grid, int block, size_t smem, cudaStre
 	switch (T) {
 #define GB_CASE(TT)                                                                          \
 	case TT:                                                                                 \
-		e = allow_smem(eval_kernel<TT>, smem);                                               \
-		if (e != cudaSuccess) return e;                                                      \
-		eval_kernel<TT><<<grid, block, smem, st>>>(m, L, W, x, sel, ce, ve, cd);             \
+		if (m.permutation) {                                                                 \
+			e = allow_smem(eval_kernel<TT, true>, smem);                                     \
+			if (e != cudaSuccess) return e;                                                  \
+			eval_kernel<TT, true><<<grid, block, smem, st>>>(m, L, W, x, sel, ce, ve, cd);   \
+		} else {                                                                             \
+			e = allow_smem(eval_kernel<TT, false>, smem);                                    \
+			if (e != cudaSuccess) return e;                                                  \
+			eval_kernel<TT, false><<<grid, block, smem, st>>>(m, L, W, x, sel, ce, ve, cd);  \
+		}                                                                                    \
 		break;
 		GB_CASE(32) GB_CASE(64) GB_CASE(128) GB_CASE(256) GB_CASE(512)
 #undef GB_CASE

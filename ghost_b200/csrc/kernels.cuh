@@ -1,8 +1,8 @@
 // kernels.cuh — the two kernels of the hot path:
-//   search_kernel<T> : SearchUnit::local_search (reference include/search_unit.hpp:685-1201) for a
-//                      population of independent walkers, `iterations` loop passes per launch;
-//   eval_kernel<T>   : the move-evaluation unit alone (projection + delta of every candidate), the
-//                      bit-exact parity hook.
+//   search_kernel<T,PERM> : SearchUnit::local_search (reference include/search_unit.hpp:685-1201)
+//                           for a population of independent walkers, `iterations` loop passes per launch;
+//   eval_kernel<T,PERM>   : the move-evaluation unit alone (projection + delta of every candidate),
+//                           the bit-exact parity hook.
 #pragma once
 
 #include "walker.cuh"
@@ -27,6 +27,9 @@ struct SearchParams {
 	int* trace_len;
 };
 
+// indices into the shared-memory counter block (GhostCounters order)
+enum { K_ITER = 0, K_MOVES = 1, K_LOCALMIN = 2, K_PLATEAU = 3, K_FORCE = 4, K_RESETS = 5, K_RESTARTS = 6, K_EVALS = 7 };
+
 __device__ __forceinline__ unsigned long long quality_key(bool optimization, int best_sat, long long best_opt, int walker)
 {
 	unsigned long long q;
@@ -39,7 +42,7 @@ __device__ __forceinline__ unsigned long long quality_key(bool optimization, int
 // ---- sampling ---------------------------------------------------------------------------------
 
 // first n entries of a uniform shuffle of 0..V-1 (replaces rng.shuffle + prefix, search_unit.hpp:
-// 206-211, 239-246): rejection sampling over one RNG event, by thread 0.  out is uint16-safe int.
+// 206-211, 239-246): rejection sampling over one RNG event, by thread 0.
 template <int T>
 __device__ inline void sample_distinct(const DevModel& m, const WS& s, Rng& rng, int n, int* out)
 {
@@ -74,12 +77,11 @@ __device__ inline void monte_carlo_sampling(const DevModel& m, const WS& s, Rng&
 		const uint64_t event = rng.next_event++;
 		for (int b = tid; b < (m.V + 3) / 4; b += T) {
 			uint4 r = rng.block(event, (uint32_t)b);
-			uint32_t w[4] = { r.x, r.y, r.z, r.w };
-#pragma unroll
-			for (int q = 0; q < 4; ++q) {
-				int v = 4 * b + q;
-				if (v < m.V) s.x[v] = mv.dom_value(v, (int)below(w[q], (uint32_t)mv.dom_size(v)));
-			}
+			int v = 4 * b;
+			if (v < m.V) s.x[v] = mv.dom_value(v, (int)below(r.x, (uint32_t)mv.dom_size(v)));
+			if (v + 1 < m.V) s.x[v + 1] = mv.dom_value(v + 1, (int)below(r.y, (uint32_t)mv.dom_size(v + 1)));
+			if (v + 2 < m.V) s.x[v + 2] = mv.dom_value(v + 2, (int)below(r.z, (uint32_t)mv.dom_size(v + 2)));
+			if (v + 3 < m.V) s.x[v + 3] = mv.dom_value(v + 3, (int)below(r.w, (uint32_t)mv.dom_size(v + 3)));
 		}
 		G::sync();
 		return;
@@ -166,11 +168,12 @@ __device__ inline void random_permutations(const DevModel& m, const WS& s, Rng& 
 	G::sync();
 }
 
-// ---- walker registers ---------------------------------------------------------------------------
+// ---- walker registers (uniform across the group) -------------------------------------------------
 struct WalkerRegs {
 	int must_compute, ncand, n_tabu, local_moves, cur_sat, best_sat, resume_pending, cand_max;
+	int resets;                 // low bits of the reset counter, for the restart test
 	long long cur_opt, best_opt, obj_sum;
-	GhostCounters k;
+	long long iterations;
 };
 
 __device__ __forceinline__ long long internal_cost(const DevModel& m, long long obj_sum)
@@ -250,9 +253,8 @@ __device__ inline void local_move(const DevModel& m, const WS& s, WalkerRegs& r,
 {
 	MV mv(m);
 	++r.local_moves;
-	++r.k.local_moves;
 	r.cur_sat += delta;
-	if (Group<T>::tid() == 0) s.tabu[v] = p.tabu_selected + r.local_moves;
+	if (Group<T>::tid() == 0) { s.tabu[v] = p.tabu_selected + r.local_moves; s.counters[K_MOVES] += 1; }
 	r.must_compute = 1;
 	if (m.objective != GHOST_OBJ_NONE) {
 		if (m.permutation) {
@@ -265,8 +267,8 @@ __device__ inline void local_move(const DevModel& m, const WS& s, WalkerRegs& r,
 }
 
 // =================================================================================================
-template <int T>
-__global__ void __launch_bounds__(T == 32 ? 256 : T)
+template <int T, bool PERM>
+__global__ void __launch_bounds__(T == 32 ? 128 : T)
 search_kernel(const DevModel m, const WalkerLayout L, const SearchParams p)
 {
 	typedef Group<T> G;
@@ -287,14 +289,19 @@ search_kernel(const DevModel m, const WalkerLayout L, const SearchParams p)
 	WalkerRegs r;
 	r.must_compute = gs->must_compute; r.ncand = gs->ncand; r.n_tabu = gs->n_tabu; r.local_moves = gs->local_moves;
 	r.cur_sat = gs->cur_sat; r.best_sat = gs->best_sat; r.resume_pending = gs->resume_pending; r.cand_max = gs->cand_max;
-	r.cur_opt = gs->cur_opt; r.best_opt = gs->best_opt; r.obj_sum = gs->obj_sum; r.k = gs->k;
+	r.cur_opt = gs->cur_opt; r.best_opt = gs->best_opt; r.obj_sum = gs->obj_sum;
+	r.iterations = gs->k.search_iterations; r.resets = (int)gs->k.resets;
 	int done = gs->done;
+	if (tid == 0) {
+		const long long* k = reinterpret_cast<const long long*>(&gs->k);
+#pragma unroll
+		for (int i = 0; i < 8; ++i) s.counters[i] = k[i];
+	}
 
 	if (!gs->initialized) {
 		// search_unit.hpp:708-717
 		r.best_sat = GB_INT_MAX; r.best_opt = GB_I64_MAX; r.cur_opt = GB_I64_MAX;
 		for (int v = tid; v < m.V; v += T) s.x[v] = mv.ld(m.o.start, v);
-		for (int c = tid; c < m.C; c += T) s.mark[c] = 0;
 		G::sync();
 		initialize_variable_values<T>(m, s, r, rng, p, best_x);
 		initialize_data_structures<T>(m, s, r, best_x);
@@ -304,12 +311,11 @@ search_kernel(const DevModel m, const WalkerLayout L, const SearchParams p)
 		const int4* src = reinterpret_cast<const int4*>(gstate);
 		int4* dst = reinterpret_cast<int4*>(smem_raw + (size_t)local * L.total_bytes);
 		for (int i = tid; i < L.persist_bytes / 16; i += T) dst[i] = src[i];
-		for (int c = tid; c < m.C; c += T) s.mark[c] = 0;
 		G::sync();
 	}
 
 	for (int it = 0; it < p.iterations && !done; ++it) {
-		if (p.max_iterations > 0 && r.k.search_iterations >= p.max_iterations) break;
+		if (p.max_iterations > 0 && r.iterations >= p.max_iterations) break;
 		if ((it & 7) == 0) {
 			// stop request (SearchUnit::stop_search_requested, search_unit.hpp:658-664, 728)
 			if (tid == 0) s.red[48] = *reinterpret_cast<volatile int*>(p.stop_flag);
@@ -318,7 +324,7 @@ search_kernel(const DevModel m, const WalkerLayout L, const SearchParams p)
 			G::sync();
 			if (stop) break;
 		}
-		++r.k.search_iterations;
+		++r.iterations;
 
 		if (r.must_compute)
 			r.ncand = scan_candidates<T>(m, s, L.nchunks_v, r.local_moves, optimization && r.cur_sat == 0, s.red, &r.cand_max, &r.n_tabu);
@@ -326,11 +332,12 @@ search_kernel(const DevModel m, const WalkerLayout L, const SearchParams p)
 		int trace_var = -1, trace_val = 0, trace_branch = 0, trace_ncand = 0, trace_min = 0;
 		if (r.n_tabu >= p.reset_threshold || r.ncand == 0) {
 			// SearchUnit::reset (search_unit.hpp:333-367)
-			++r.k.resets;
-			if (p.restart_threshold > 0 && (r.k.resets % p.restart_threshold == 0)) {
-				++r.k.restarts;
+			++r.resets;
+			if (tid == 0) s.counters[K_RESETS] += 1;
+			if (p.restart_threshold > 0 && (r.resets % p.restart_threshold == 0)) {
+				if (tid == 0) s.counters[K_RESTARTS] += 1;
 				initialize_variable_values<T>(m, s, r, rng, p, best_x);
-			} else if (m.permutation) random_permutations<T>(m, s, rng, p.nreset);
+			} else if (PERM) random_permutations<T>(m, s, rng, p.nreset);
 			else monte_carlo_sampling<T>(m, s, rng, p.nreset);
 			initialize_data_structures<T>(m, s, r, best_x);
 		} else {
@@ -338,27 +345,28 @@ search_kernel(const DevModel m, const WalkerLayout L, const SearchParams p)
 			// UniformVariableHeuristic::select_variable (uniform_variable_heuristic.cpp:38-41)
 			const int v = pick_kth(s.cand_key, s.cand_bits, L.nchunks_v, r.cand_max, (int)below(rnd.x, (uint32_t)r.ncand));
 			--r.ncand;
-			const int deg = hoist_variable<T>(m, s, v);
+			int bias;
+			const int nh = hoist_variable<T>(m, s, v, &bias);
 			G::sync();
 			if (tid == 0) s.cand_bits[v >> 5] &= ~(1u << (v & 31)); // search_unit.hpp:826-828
-			int mine = evaluate_candidates<T>(m, s, v, deg, L.nchunks_c, nullptr);
+			int mine = evaluate_candidates<T, PERM>(m, s, v, nh, bias, L.nchunks_c, nullptr);
 			G::sync();
 			const int ncandidates = G::sum(mine, s.red + 16);
-			r.k.candidates_evaluated += ncandidates;
+			if (tid == 0) s.counters[K_EVALS] += ncandidates;
 			// AdaptiveSearchValueHeuristic::select_value (adaptive_search_value_heuristic.cpp:43-81)
 			const int gmin = chunks_min(s.val_key, L.nchunks_c);
 			const int nties = gmin == GB_INT_MAX ? 0 : chunks_count(s.val_key, s.val_bits, L.nchunks_c, gmin);
 			int new_value = v;
 			if (nties > 0) {
 				int k;
-				if (optimization && !m.permutation) {
+				if (optimization && !PERM) {
 					// Objective::expert_heuristic_value (objective.cpp:69-109) for a linear objective:
 					// the cheapest tied value is the smallest / largest one, or any if the coefficient is 0
 					long long cf = internal_cost(m, (long long)mv.obj_coef(v));
 					k = cf > 0 ? 0 : cf < 0 ? nties - 1 : (int)below(rnd.y, (uint32_t)nties);
 				} else k = (int)below(rnd.y, (uint32_t)nties);
 				int slot = pick_kth(s.val_key, s.val_bits, L.nchunks_c, gmin, k);
-				new_value = m.permutation ? slot : mv.dom_value(v, slot);
+				new_value = PERM ? slot : mv.dom_value(v, slot);
 			}
 			trace_var = v; trace_val = new_value; trace_ncand = ncandidates; trace_min = gmin;
 
@@ -370,7 +378,7 @@ search_kernel(const DevModel m, const WalkerLayout L, const SearchParams p)
 			} else if (gmin == 0) {
 				if (optimization && p.guidance) { // 1061-1135
 					long long obj2;
-					if (m.permutation) {
+					if (PERM) {
 						int xv = s.x[v], xj = s.x[new_value];
 						obj2 = r.obj_sum + (long long)mv.obj_coef(v) * (xj - xv) + (long long)mv.obj_coef(new_value) * (xv - xj);
 					} else obj2 = r.obj_sum + (long long)mv.obj_coef(v) * (new_value - s.x[v]);
@@ -383,27 +391,25 @@ search_kernel(const DevModel m, const WalkerLayout L, const SearchParams p)
 
 			if (plateau) { // plateau_management, 545-561
 				if ((int)below(rnd.z, 100u) + 1 <= p.plateau_percent) {
-					if (tid == 0) s.tabu[v] = p.tabu_local_min + r.local_moves;
+					if (tid == 0) { s.tabu[v] = p.tabu_local_min + r.local_moves; s.counters[K_FORCE] += 1; }
 					r.must_compute = 1;
-					++r.k.plateau_force_trying_another_variable;
 					trace_branch = 4;
 				} else {
 					local_move<T>(m, s, r, p, v, new_value, 0);
-					++r.k.plateau_moves;
+					if (tid == 0) s.counters[K_PLATEAU] += 1;
 					trace_branch = 3;
 				}
 			}
 			if (local_min) { // local_minimum_management, 565-582
 				r.must_compute = 0;
 				if (r.ncand == 0) {
-					if (tid == 0) s.tabu[v] = p.tabu_local_min + r.local_moves;
+					if (tid == 0) { s.tabu[v] = p.tabu_local_min + r.local_moves; s.counters[K_LOCALMIN] += 1; }
 					if (p.tabu_local_min > 0) ++r.n_tabu;
-					++r.k.local_minimum;
 					trace_branch = 5;
 				} else trace_branch = 6;
 			}
 			G::sync();
-			if (m.permutation) unmark_variable<T>(m, s, v);
+			if (PERM) unmark_variable<T>(m, s, v);
 
 			// search_unit.hpp:1166-1188
 			if (r.best_sat > r.cur_sat) { r.best_sat = r.cur_sat; copy_best<T>(m, s, best_x); }
@@ -411,19 +417,20 @@ search_kernel(const DevModel m, const WalkerLayout L, const SearchParams p)
 			G::sync();
 		}
 		if (p.trace && w == p.trace_walker && tid == 0) {
-			int row = (int)r.k.search_iterations - 1;
+			int row = (int)r.iterations - 1;
 			if (row < p.trace_cap) {
 				int* t = p.trace + 8 * row;
-				t[0] = (int)r.k.search_iterations; t[1] = trace_var; t[2] = trace_val; t[3] = trace_branch;
+				t[0] = (int)r.iterations; t[1] = trace_var; t[2] = trace_val; t[3] = trace_branch;
 				t[4] = trace_ncand; t[5] = trace_min; t[6] = r.cur_sat; t[7] = 0;
 			}
-			*p.trace_len = (int)r.k.search_iterations;
+			*p.trace_len = (int)r.iterations;
 		}
 		done = !(r.best_sat > 0 || (r.best_sat == 0 && optimization)); // search_unit.hpp:730
 		if (done && p.stop_on_solution && tid == 0) atomicExch(p.stop_flag, 1);
 	}
 
 	// persist
+	G::sync();
 	{
 		int4* dst = reinterpret_cast<int4*>(gstate);
 		const int4* src = reinterpret_cast<const int4*>(smem_raw + (size_t)local * L.total_bytes);
@@ -434,7 +441,11 @@ search_kernel(const DevModel m, const WalkerLayout L, const SearchParams p)
 		gs->local_moves = r.local_moves; gs->cur_sat = r.cur_sat; gs->best_sat = r.best_sat;
 		gs->resume_pending = r.resume_pending; gs->cand_max = r.cand_max; gs->done = done;
 		gs->cur_opt = r.cur_opt; gs->best_opt = r.best_opt; gs->obj_sum = r.obj_sum;
-		gs->next_event = rng.next_event; gs->k = r.k;
+		gs->next_event = rng.next_event;
+		long long* k = reinterpret_cast<long long*>(&gs->k);
+#pragma unroll
+		for (int i = 0; i < 8; ++i) k[i] = s.counters[i];
+		k[K_ITER] = r.iterations;
 		atomicMin(p.best_key, quality_key(optimization, r.best_sat, r.best_opt, w));
 	}
 }
@@ -442,8 +453,8 @@ search_kernel(const DevModel m, const WalkerLayout L, const SearchParams p)
 // =================================================================================================
 // Parity hook: for each walker's assignment and selected variable write constraint errors,
 // projected errors and the cumulated delta of every candidate slot.
-template <int T>
-__global__ void __launch_bounds__(T == 32 ? 256 : T)
+template <int T, bool PERM>
+__global__ void __launch_bounds__(T == 32 ? 128 : T)
 eval_kernel(const DevModel m, const WalkerLayout L, int num_walkers, const int* __restrict__ assignments,
             const int* __restrict__ selected, int* __restrict__ ctr_error, int* __restrict__ var_error,
             int* __restrict__ cand_delta)
@@ -457,18 +468,17 @@ eval_kernel(const DevModel m, const WalkerLayout L, int num_walkers, const int* 
 	const WS s = make_ws(smem_raw + (size_t)local * L.total_bytes, L);
 	const int tid = G::tid();
 	for (int v = tid; v < m.V; v += T) s.x[v] = assignments[(size_t)w * m.V + v];
-	for (int c = tid; c < m.C; c += T) s.mark[c] = 0;
 	G::sync();
 	recompute_all<T>(m, s, s.red);
-	if (ctr_error) for (int c = tid; c < m.C; c += T) ctr_error[(size_t)w * m.C + c] = s.err_c[c];
+	if (ctr_error) for (int c = tid; c < m.C; c += T) ctr_error[(size_t)w * m.C + c] = s.err_of(c);
 	if (var_error) for (int v = tid; v < m.V; v += T) var_error[(size_t)w * m.V + v] = s.err_var[v];
 	const int v = selected ? selected[w] : -1;
 	if (v < 0 || !cand_delta) return;
 	int* out = cand_delta + (size_t)w * m.max_candidates;
-	for (int k = L.nchunks_c * 32 + tid; k < m.max_candidates; k += T) out[k] = GB_INT_MAX;
-	const int deg = hoist_variable<T>(m, s, v);
+	int bias;
+	const int nh = hoist_variable<T>(m, s, v, &bias);
 	G::sync();
-	evaluate_candidates<T>(m, s, v, deg, L.nchunks_c, out);
+	evaluate_candidates<T, PERM>(m, s, v, nh, bias, L.nchunks_c, out);
 }
 
 } // namespace ghost_b200

@@ -197,6 +197,40 @@ int lower_model(const GhostModelDesc* d, LoweredModel* out, std::string* why)
 	o.c2v_off = put(c2v_off); o.c2v = put(c2v); o.ent_ctr = put(ent_ctr); o.ent_coef = put(ent_coef);
 	o.cnt_owner = put(cnt_owner);
 	o.obj_coef = put(obj_coef);
+	// ELL rows for the hot loop: one fixed-stride row per variable, class / error weights packed in
+	// the entry so that the candidate loop needs no per-constraint global lookups for linear kinds.
+	const int stride = std::max(1, max_degree);
+	std::vector<int32_t> ell(static_cast<size_t>(V) * stride * 2, 0), has_ctr((V + 31) / 32, 0);
+	for (int v = 0; v < V; ++v) {
+		if (!rows[v].empty()) has_ctr[v >> 5] |= (1u << (v & 31));
+		for (int k = 0; k < stride; ++k) {
+			int w0 = GB_ELL_END, w1 = 0;
+			if (k < static_cast<int>(rows[v].size())) {
+				int c = rows[v][k].first, kd = kind[c];
+				int cls = GB_CLS_ZERO, wbits = 0;
+				switch (kd) {
+				case GHOST_KIND_LINEAR_EQ:  cls = GB_CLS_LINEAR; wbits = 3; break; // |t| = max(t,0) + max(-t,0)
+				case GHOST_KIND_LINEAR_NEQ: cls = GB_CLS_LINEAR; wbits = 4; break;
+				case GHOST_KIND_LINEAR_LEQ: cls = GB_CLS_LINEAR; wbits = 1; break;
+				case GHOST_KIND_LINEAR_GEQ: cls = GB_CLS_LINEAR; wbits = 2; break;
+				case GHOST_KIND_LINEAR_L:   cls = GB_CLS_LINEAR; wbits = 5; break;
+				case GHOST_KIND_LINEAR_G:   cls = GB_CLS_LINEAR; wbits = 6; break;
+				case GHOST_KIND_ALL_DIFFERENT: cls = GB_CLS_ALLDIFF; break;
+				case GHOST_KIND_FIX_VALUE: cls = GB_CLS_FIX; break;
+				case GHOST_KIND_ALL_DIFFERENT_ABS_DIFF: cls = GB_CLS_ABSDIFF; break;
+				default: cls = GB_CLS_ZERO; break;
+				}
+				int universal = (c2v_off[c + 1] - c2v_off[c] == V) ? 1 : 0;
+				w0 = c | (cls << 20) | (wbits << 24) | (universal << 27);
+				w1 = rows[v][k].second;
+			}
+			ell[(static_cast<size_t>(v) * stride + k) * 2] = w0;
+			ell[(static_cast<size_t>(v) * stride + k) * 2 + 1] = w1;
+		}
+	}
+	if (C >= GB_ELL_END) return fail(GHOST_B200_ERR_UNSUPPORTED, "too many constraints");
+	o.ell = put(ell);
+	o.has_ctr = put(has_ctr);
 	o.total = static_cast<int>(blob.size());
 
 	DevModel& m = L.dev;
@@ -211,6 +245,7 @@ int lower_model(const GhostModelDesc* d, LoweredModel* out, std::string* why)
 	m.max_candidates = m.permutation ? V : max_dom;
 	m.max_degree = std::max(1, max_degree);
 	m.has_abs_diff = has_abs_diff ? 1 : 0;
+	m.ell_stride = stride;
 	return GHOST_B200_OK;
 }
 
@@ -227,13 +262,12 @@ WalkerLayout LoweredModel::layout(int /*threads_per_walker*/, int nreset) const
 	w.x = take(4 * m.V);
 	w.err_var = take(4 * m.V);
 	w.tabu = take(4 * m.V);
-	w.S = take(4 * m.C);
-	w.err_c = take(4 * m.C);
+	w.cs = take(16 * m.C);
 	w.cand_key = take(4 * w.nchunks_v);
 	w.cand_bits = take(4 * w.nchunks_v);
 	w.cnt = take(2 * std::max(1, m.cnt_total));
 	w.persist_bytes = at;
-	w.mark = take(m.C);
+	w.counters = take(8 * 8);
 	w.flags = take(m.V);
 	w.val_key = take(4 * w.nchunks_c);
 	w.val_bits = take(4 * w.nchunks_c);

@@ -23,6 +23,8 @@ struct BlobOffsets {
 	int ent_coef;              // coefficient of scope entry i (linear), 0 otherwise
 	int cnt_owner;             // [cnt_total] constraint owning count-table slot t
 	int obj_coef;              // dense [V]
+	int ell;                   // [V][ell_stride] int2 rows: {c | cls<<20 | w<<24 | universal<<27, coef|pos}; c=0xFFFFF ends a row
+	int has_ctr;               // [ceil(V/32)] bit v%32 set iff variable v appears in some constraint
 	int total;
 };
 
@@ -39,13 +41,19 @@ struct DevModel {
 	int max_candidates;        // max over variables of candidate slots (V for permutation problems)
 	int max_degree;            // max #constraints touching one variable
 	int has_abs_diff;
+	int ell_stride;            // entries per ELL row (= max_degree)
 };
+
+// ELL entry encoding (word 0)
+enum : int { GB_ELL_END = 0xFFFFF, GB_CLS_LINEAR = 0, GB_CLS_ALLDIFF = 1, GB_CLS_FIX = 2, GB_CLS_ABSDIFF = 3, GB_CLS_ZERO = 4 };
+enum : int { GB_MARK_SKIP = 1 << 20 };
 
 // Per-walker shared-memory layout, byte offsets from the walker's base.
 struct WalkerLayout {
-	int x, err_var, tabu, S, err_c;     // int32 arrays
+	int x, err_var, tabu;               // int32 [V] arrays
+	int cs;                             // int4 [C]: {T = sum - rhs (linear), current error, mark, 0}
 	int cnt;                            // uint16 [cnt_total]
-	int mark;                           // uint8 [C]
+	int counters;                       // int64 [8] GhostCounters, updated by thread 0
 	int flags;                          // uint8 [V]   sampling scratch
 	int cand_key, cand_bits;            // int32 [nchunks_v] each: candidate-variable chunks
 	int val_key, val_bits;              // int32 [nchunks_c] each: candidate-value chunks

@@ -98,29 +98,34 @@ struct Group {
 
 // Shared-memory view of one walker
 struct WS {
-	int* x; int* err_var; int* tabu; int* S; int* err_c;
+	int* x; int* err_var; int* tabu;
+	int4* cs;                   // per constraint {T = sum - rhs (linear kinds), current error, mark, 0}
 	int* cand_key; unsigned* cand_bits;
 	unsigned* cnt32;            // packed 16-bit counters, two per word
-	unsigned char* mark; unsigned char* flags;
+	long long* counters;        // GhostCounters, thread 0 only
+	unsigned char* flags;
 	int* val_key; unsigned* val_bits;
-	int* hoist; int* upd; int* sample; int* red;
+	int4* hoist; int* upd; int* sample; int* red;
 	__device__ __forceinline__ int cnt(int idx) const { return reinterpret_cast<const unsigned short*>(cnt32)[idx]; }
 	__device__ __forceinline__ void cnt_add(int idx, int d) const
 	{
 		atomicAdd(&cnt32[idx >> 1], (unsigned)d << ((idx & 1) * 16));
 	}
+	__device__ __forceinline__ int& T_of(int c) const { return reinterpret_cast<int*>(cs + c)[0]; }
+	__device__ __forceinline__ int& err_of(int c) const { return reinterpret_cast<int*>(cs + c)[1]; }
+	__device__ __forceinline__ int& mark_of(int c) const { return reinterpret_cast<int*>(cs + c)[2]; }
 };
 
 __device__ __forceinline__ WS make_ws(unsigned char* base, const WalkerLayout& L)
 {
 	WS s;
 	s.x = (int*)(base + L.x); s.err_var = (int*)(base + L.err_var); s.tabu = (int*)(base + L.tabu);
-	s.S = (int*)(base + L.S); s.err_c = (int*)(base + L.err_c);
+	s.cs = (int4*)(base + L.cs);
 	s.cand_key = (int*)(base + L.cand_key); s.cand_bits = (unsigned*)(base + L.cand_bits);
 	s.cnt32 = (unsigned*)(base + L.cnt);
-	s.mark = base + L.mark; s.flags = base + L.flags;
+	s.counters = (long long*)(base + L.counters); s.flags = base + L.flags;
 	s.val_key = (int*)(base + L.val_key); s.val_bits = (unsigned*)(base + L.val_bits);
-	s.hoist = (int*)(base + L.hoist); s.upd = (int*)(base + L.upd); s.sample = (int*)(base + L.sample);
+	s.hoist = (int4*)(base + L.hoist); s.upd = (int*)(base + L.upd); s.sample = (int*)(base + L.sample);
 	s.red = (int*)(base + L.red);
 	return s;
 }
@@ -150,6 +155,7 @@ struct MV {
 	}
 	__device__ __forceinline__ int row_begin(int v) const { return ld(m.o.v2c_off, v); }
 	__device__ __forceinline__ int2 row_entry(int e) const { return __ldg(reinterpret_cast<const int2*>(m.blob + m.o.v2c) + e); }
+	__device__ __forceinline__ const int2* ell_row(int v) const { return reinterpret_cast<const int2*>(m.blob + m.o.ell) + (size_t)v * m.ell_stride; }
 	__device__ __forceinline__ int kind(int c) const { return ld(m.o.kind, c); }
 	__device__ __forceinline__ int rhs(int c) const { return ld(m.o.rhs, c); }
 	__device__ __forceinline__ int cnt_tab(int c) const { return ld(m.o.cnt_tab, c); }
@@ -158,30 +164,41 @@ struct MV {
 	__device__ __forceinline__ int obj_coef(int v) const { return ld(m.o.obj_coef, v); }
 };
 
+// ELL entry decoding (lower.cpp)
+__device__ __forceinline__ int ell_ctr(int w0) { return w0 & 0xFFFFF; }
+__device__ __forceinline__ int ell_cls(int w0) { return (w0 >> 20) & 0xF; }
+__device__ __forceinline__ int ell_w(int w0) { return (w0 >> 24) & 0x7; }
+__device__ __forceinline__ bool ell_universal(int w0) { return (w0 >> 27) & 1; }
+
 // LinearEquation*::compute_error on t = sum - rhs
 // (reference linear_equation_eq.cpp:54-57, _neq.cpp:54-61, _leq.cpp:54-57, _geq.cpp:54-57,
-//  _l.cpp:54-61, _g.cpp:54-61)
-__device__ __forceinline__ int linear_error(int kind, int t)
+//  _l.cpp:54-61, _g.cpp:54-61), branch-free: w bit0 counts max(t,0), bit1 max(-t,0), bit2 [t==0].
+//  Eq = 3, Leq = 1, Geq = 2, Neq = 4, L = 5, G = 6.
+__device__ __forceinline__ int linear_error_w(int w, int t)
 {
-	switch (kind) {
-	case GHOST_KIND_LINEAR_EQ:  return abs(t);
-	case GHOST_KIND_LINEAR_NEQ: return t == 0;
-	case GHOST_KIND_LINEAR_LEQ: return max(t, 0);
-	case GHOST_KIND_LINEAR_GEQ: return max(-t, 0);
-	case GHOST_KIND_LINEAR_L:   return max(t, 0) + (t == 0);
-	default:                    return max(-t, 0) + (t == 0); // GHOST_KIND_LINEAR_G
-	}
+	int pos = max(t, 0), neg = pos - t;
+	int e = (w & 1) ? pos : 0;
+	e += (w & 2) ? neg : 0;
+	e += ((w & 4) && t == 0) ? 1 : 0;
+	return e;
+}
+__device__ __forceinline__ int linear_w_of_kind(int kind)
+{
+	return kind == GHOST_KIND_LINEAR_EQ ? 3 : kind == GHOST_KIND_LINEAR_LEQ ? 1 : kind == GHOST_KIND_LINEAR_GEQ ? 2
+	     : kind == GHOST_KIND_LINEAR_NEQ ? 4 : kind == GHOST_KIND_LINEAR_L ? 5 : 6;
 }
 __device__ __forceinline__ bool kind_is_linear(int k) { return k >= GHOST_KIND_LINEAR_EQ && k <= GHOST_KIND_LINEAR_G; }
 __device__ __forceinline__ int binom2(int n) { return (n * (n - 1)) >> 1; } // all_different.cpp:38-47
 
 // ---------------------------------------------------------------------------------------------
 // AllDifferentAbsDiff (extension kind): delta of changing scope position pa to na (and pb to nb
-// when pb >= 0): recount the <= 4 neighbouring |differences|.
+// when pb >= 0): recount the <= 4 neighbouring |differences|.  Kept out of line: only models that
+// use the extension pay for it.
 // ---------------------------------------------------------------------------------------------
-__device__ inline int absdiff_delta(const MV& mv, const WS& s, int c, int pa, int na, int pb, int nb)
+__device__ __noinline__ int absdiff_delta(const int32_t* blob, int c2v_off_sec, int c2v_sec, int cnt_tab_sec,
+                                          const int* x, const unsigned* cnt32, int c, int pa, int na, int pb, int nb)
 {
-	int b = mv.scope_begin(c), n = mv.scope_begin(c + 1) - b, tab = mv.cnt_tab(c);
+	int b = __ldg(blob + c2v_off_sec + c), n = __ldg(blob + c2v_off_sec + c + 1) - b, tab = __ldg(blob + cnt_tab_sec + c);
 	int pairs[4]; int np = 0;
 	auto add_pair = [&](int p) {
 		if (p < 0 || p + 1 >= n) return;
@@ -197,7 +214,7 @@ __device__ inline int absdiff_delta(const MV& mv, const WS& s, int c, int pa, in
 	};
 	for (int z = 0; z < np; ++z) {
 		int p = pairs[z];
-		int oa = s.x[mv.scope_var(b + p)], ob = s.x[mv.scope_var(b + p + 1)];
+		int oa = x[__ldg(blob + c2v_sec + b + p)], ob = x[__ldg(blob + c2v_sec + b + p + 1)];
 		int va = (p == pa) ? na : (p == pb ? nb : oa);
 		int vb = (p + 1 == pa) ? na : (p + 1 == pb ? nb : ob);
 		touch(abs(ob - oa), -1);
@@ -205,10 +222,14 @@ __device__ inline int absdiff_delta(const MV& mv, const WS& s, int c, int pa, in
 	}
 	int diff = 0;
 	for (int z = 0; z < nk; ++z) {
-		int cur = s.cnt(tab + keys[z]);
+		int cur = reinterpret_cast<const unsigned short*>(cnt32)[tab + keys[z]];
 		diff += binom2(cur + net[z]) - binom2(cur);
 	}
 	return diff;
+}
+__device__ __forceinline__ int absdiff_delta(const MV& mv, const WS& s, int c, int pa, int na, int pb, int nb)
+{
+	return absdiff_delta(mv.m.blob, mv.m.o.c2v_off, mv.m.o.c2v, mv.m.o.cnt_tab, s.x, s.cnt32, c, pa, na, pb, nb);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -244,9 +265,9 @@ __device__ inline int constraint_delta(const MV& mv, const WS& s, int c, int va,
 		return s.cnt(tab + na) - (s.cnt(tab + o) - 1);
 	}
 	if (kind_is_linear(kind)) {
-		int t = s.S[c] - mv.rhs(c) + ea * (na - s.x[va]);
+		int t = s.T_of(c) + ea * (na - s.x[va]);
 		if (vb >= 0) t += eb * (nb - s.x[vb]);
-		return linear_error(kind, t) - s.err_c[c];
+		return linear_error_w(linear_w_of_kind(kind), t) - s.err_of(c);
 	}
 	if (kind == GHOST_KIND_FIX_VALUE) {
 		int k = mv.rhs(c);
@@ -272,7 +293,7 @@ __device__ inline int recompute_all(const DevModel& m, const WS& s, int* red)
 	typedef Group<T> G;
 	MV mv(m);
 	const int tid = G::tid(), lane = threadIdx.x & 31;
-	for (int c = tid; c < m.C; c += T) { s.S[c] = 0; s.err_c[c] = 0; }
+	for (int c = tid; c < m.C; c += T) s.cs[c] = make_int4(0, 0, 0, 0);
 	for (int t = tid; t < (m.cnt_total + 1) / 2; t += T) s.cnt32[t] = 0;
 	G::sync();
 	const int nnz_pad = (m.nnz + 31) & ~31;
@@ -300,26 +321,30 @@ __device__ inline int recompute_all(const DevModel& m, const WS& s, int* red)
 		int cnext = __shfl_down_sync(0xffffffffu, c, 1);
 		bool tail = (lane == 31) || (cnext != c);
 		if (c >= 0 && tail && val != 0) {
-			if (kind_is_linear(kind)) atomicAdd(&s.S[c], val);
-			else if (kind == GHOST_KIND_FIX_VALUE) atomicAdd(&s.err_c[c], val);
+			if (kind_is_linear(kind)) atomicAdd(&s.T_of(c), val);
+			else if (kind == GHOST_KIND_FIX_VALUE) atomicAdd(&s.err_of(c), val);
 		}
 	}
 	G::sync();
 	for (int c = tid; c < m.C; c += T) {
 		int kind = mv.kind(c);
-		if (kind_is_linear(kind)) s.err_c[c] = linear_error(kind, s.S[c] - mv.rhs(c));
+		if (kind_is_linear(kind)) {
+			int t = s.T_of(c) - mv.rhs(c);
+			s.T_of(c) = t;
+			s.err_of(c) = linear_error_w(linear_w_of_kind(kind), t);
+		}
 	}
 	for (int t = tid; t < m.cnt_total; t += T) {
 		int n = s.cnt(t);
-		if (n > 1) atomicAdd(&s.err_c[mv.ld(m.o.cnt_owner, t)], binom2(n));
+		if (n > 1) atomicAdd(&s.err_of(mv.ld(m.o.cnt_owner, t)), binom2(n));
 	}
 	G::sync();
 	int part = 0;
-	for (int c = tid; c < m.C; c += T) part += s.err_c[c];
+	for (int c = tid; c < m.C; c += T) part += s.err_of(c);
 	int total = G::sum(part, red);
 	for (int v = tid; v < m.V; v += T) {
 		int e = 0;
-		for (int r = mv.row_begin(v), re = mv.row_begin(v + 1); r < re; ++r) e += s.err_c[mv.row_entry(r).x];
+		for (int r = mv.row_begin(v), re = mv.row_begin(v + 1); r < re; ++r) e += s.err_of(mv.row_entry(r).x);
 		s.err_var[v] = e;
 	}
 	G::sync();
@@ -409,12 +434,12 @@ __device__ inline int scan_candidates(const DevModel& m, const WS& s, int nchunk
 	int ntabu = 0;
 	for (int ch = G::warp(); ch < nchunks_v; ch += G::NW) {
 		int v = ch * 32 + lane;
+		unsigned has_ctr = free_vars_ok ? 0xffffffffu : (unsigned)mv.ld(m.o.has_ctr, ch);
 		int e = -1;
 		bool tabu = false;
 		if (v < m.V) {
 			tabu = s.tabu[v] > local_moves;
-			bool has_ctr = mv.row_begin(v + 1) > mv.row_begin(v);
-			if (!tabu && (has_ctr || free_vars_ok)) e = s.err_var[v];
+			if (!tabu && ((has_ctr >> lane) & 1u)) e = s.err_var[v];
 		}
 		int cmax = __reduce_max_sync(0xffffffffu, e);
 		unsigned bits = __ballot_sync(0xffffffffu, e == cmax && e >= 0);
@@ -439,75 +464,98 @@ __device__ inline int scan_candidates(const DevModel& m, const WS& s, int nchunk
 
 // ---------------------------------------------------------------------------------------------
 // Hoist the per-iteration invariants of the selected variable's constraints (these
-// are not charged per candidate).  Entry layout, 8 ints:
-//   [0] type 0 alldiff | 1 linear | 2 fix | 3 zero | 4 absdiff     [7] constraint id
-//   alldiff: [1] count-table base, [2] cnt[x_v]-1
-//   linear : [1] a_v, [2] S - rhs - a_v*x_v, [3] current error, [4] kind
-//   fix    : [1] k, [2] |x_v-k|
-//   absdiff: [1] scope position of v
-// In permutation mode mark[c] = entry index + 1.
+// are not charged per candidate).  One int4 per hoisted constraint:
+//   .x = type (GB_CLS_*) | w << 4 | constraint id << 8
+//   linear : .y = a_v, .z = T - a_v*x_v            (error term: linear_error_w(w, .z + .y*d))
+//   alldiff: .y = count-table base, .z = cnt[x_v]-1
+//   fix    : .y = k
+//   absdiff: .y = scope position of v
+// The constant part of every candidate's sum (- current errors, - (cnt[x_v]-1), - |x_v-k|) is
+// returned in *bias.  In permutation mode mark[c] = entry index + 1; constraints over ALL variables
+// (a swap inside them never changes an AllDifferent) are marked GB_MARK_SKIP and not hoisted.
+// Returns the number of hoisted entries.  The caller must barrier before reading.
 // ---------------------------------------------------------------------------------------------
 template <int T>
-__device__ inline int hoist_variable(const DevModel& m, const WS& s, int v)
+__device__ inline int hoist_variable(const DevModel& m, const WS& s, int v, int* bias_out)
 {
-	typedef Group<T> G;
 	MV mv(m);
-	const int rb = mv.row_begin(v), deg = mv.row_begin(v + 1) - rb;
+	const int2* row = mv.ell_row(v);
 	const int xv = s.x[v];
-	for (int k = G::tid(); k < deg; k += T) {
-		int2 e = mv.row_entry(rb + k);
-		int c = e.x, kind = mv.kind(c);
-		int* h = s.hoist + 8 * k;
-		h[7] = c;
-		if (kind == GHOST_KIND_ALL_DIFFERENT) {
+	int nh = 0, bias = 0;
+	const bool writer = Group<T>::tid() == 0;
+	// every thread walks the (short) row: the count and the bias are needed by all, thread 0 writes
+	for (int k = 0; k < m.ell_stride; ++k) {
+		int2 e = __ldg(row + k);
+		int c = ell_ctr(e.x);
+		if (c == GB_ELL_END) break;
+		int cls = ell_cls(e.x);
+		if (m.permutation && cls == GB_CLS_ALLDIFF && ell_universal(e.x)) {
+			if (writer) s.mark_of(c) = GB_MARK_SKIP;
+			continue;
+		}
+		int4 h = make_int4(cls | (ell_w(e.x) << 4) | (c << 8), 0, 0, 0);
+		if (cls == GB_CLS_LINEAR) {
+			int4 st = s.cs[c];
+			h.y = e.y; h.z = st.x - e.y * xv;
+			bias -= st.y;
+		} else if (cls == GB_CLS_ALLDIFF) {
 			int tab = mv.cnt_tab(c);
-			h[0] = 0; h[1] = tab; h[2] = s.cnt(tab + xv) - 1;
-		} else if (kind_is_linear(kind)) {
-			h[0] = 1; h[1] = e.y; h[2] = s.S[c] - mv.rhs(c) - e.y * xv; h[3] = s.err_c[c]; h[4] = kind;
-		} else if (kind == GHOST_KIND_FIX_VALUE) {
+			int sub = s.cnt(tab + xv) - 1;
+			h.y = tab; h.z = sub;
+			bias -= sub;
+		} else if (cls == GB_CLS_FIX) {
 			int kk = mv.rhs(c);
-			h[0] = 2; h[1] = kk; h[2] = abs(xv - kk);
-		} else if (kind == GHOST_KIND_ALL_DIFFERENT_ABS_DIFF) {
-			h[0] = 4; h[1] = e.y;
-		} else h[0] = 3;
-		if (m.permutation) s.mark[c] = (unsigned char)(k + 1);
+			h.y = kk;
+			bias -= abs(xv - kk);
+		} else if (cls == GB_CLS_ABSDIFF) {
+			h.y = e.y;
+		}
+		if (writer) {
+			s.hoist[nh] = h;
+			if (m.permutation) s.mark_of(c) = nh + 1;
+		}
+		++nh;
 	}
-	return deg;
+	*bias_out = bias;
+	return nh;
 }
 template <int T>
 __device__ inline void unmark_variable(const DevModel& m, const WS& s, int v)
 {
 	MV mv(m);
-	const int rb = mv.row_begin(v), deg = mv.row_begin(v + 1) - rb;
-	for (int k = Group<T>::tid(); k < deg; k += T) s.mark[mv.row_entry(rb + k).x] = 0;
+	const int2* row = mv.ell_row(v);
+	for (int k = Group<T>::tid(); k < m.ell_stride; k += T) {
+		int c = ell_ctr(__ldg(row + k).x);
+		if (c != GB_ELL_END) s.mark_of(c) = 0;
+	}
 }
 
-// delta of hoisted entry h when the selected variable alone takes value d (d != x_v)
-__device__ __forceinline__ int hoisted_single(const MV& mv, const WS& s, const int* h, int d)
+// variable part of hoisted entry h when the selected variable alone takes value d (d != x_v);
+// the constant part is in the bias
+__device__ __forceinline__ int hoisted_term(const MV& mv, const WS& s, const int4 h, int d)
 {
-	int4 a = *reinterpret_cast<const int4*>(h);
-	switch (a.x) {
-	case 0: return s.cnt(a.y + d) - a.z;
-	case 1: return linear_error(h[4], a.z + a.y * d) - a.w;
-	case 2: return abs(d - a.y) - a.z;
-	case 4: return absdiff_delta(mv, s, h[7], a.y, d, -1, 0);
-	default: return 0;
-	}
+	int type = h.x & 0xF;
+	if (type == GB_CLS_LINEAR) return linear_error_w((h.x >> 4) & 7, h.z + h.y * d);
+	if (type == GB_CLS_ALLDIFF) return s.cnt(h.y + d);
+	if (type == GB_CLS_FIX) return abs(d - h.y);
+	if (type == GB_CLS_ABSDIFF) return absdiff_delta(mv, s, h.x >> 8, h.y, d, -1, 0);
+	return 0;
 }
 
 // Cumulated delta of one candidate (search_unit.hpp:836-887 + std::accumulate of
 // adaptive_search_value_heuristic.cpp:57-58).  slot = domain index (non-permutation) or partner
 // variable (permutation).  Returns false if the slot is not a candidate.
-__device__ __forceinline__ bool candidate_sum(const DevModel& m, const MV& mv, const WS& s, int v, int xv, int deg,
+template <bool PERM>
+__device__ __forceinline__ bool candidate_sum(const DevModel& m, const MV& mv, const WS& s, int v, int xv, int nh, int bias,
                                               int slot, int nslots, int* out)
 {
 	if (slot >= nslots) return false;
-	if (!m.permutation) {
+	if (!PERM) {
 		int d = mv.dom_value(v, slot);
 		if (d == xv) return false;                       // search_unit.hpp:833
-		int sum = 0;
-		for (int k = 0; k < deg; ++k) sum += hoisted_single(mv, s, s.hoist + 8 * k, d);
-		*out = sum;                                      // deg == 0: 0.0 (search_unit.hpp:847-848)
+		int sum = bias;
+		for (int k = 0; k < nh; ++k) sum += hoisted_term(mv, s, s.hoist[k], d);
+		*out = sum;                                      // no constraint: 0.0 (search_unit.hpp:847-848)
 		return true;
 	}
 	const int j = slot;
@@ -515,36 +563,36 @@ __device__ __forceinline__ bool candidate_sum(const DevModel& m, const MV& mv, c
 	const int xj = s.x[j];
 	if (xj == xv) return false;                          // search_unit.hpp:855-860
 	if (!m.identical_domains && !(mv.in_domain(v, xj) && mv.in_domain(j, xv))) return false;
-	int sum = 0;
-	for (int k = 0; k < deg; ++k) sum += hoisted_single(mv, s, s.hoist + 8 * k, xj);
-	for (int r = mv.row_begin(j), re = mv.row_begin(j + 1); r < re; ++r) {
-		int2 e = mv.row_entry(r);
-		int c = e.x, mk = s.mark[c];
-		if (mk == 0) {
+	int sum = bias;
+	for (int k = 0; k < nh; ++k) sum += hoisted_term(mv, s, s.hoist[k], xj);
+	const int dx = xv - xj;
+	const int2* row = mv.ell_row(j);
+	for (int k = 0; k < m.ell_stride; ++k) {
+		int2 e = __ldg(row + k);
+		int c = ell_ctr(e.x);
+		if (c == GB_ELL_END) break;
+		int4 st = s.cs[c];
+		int cls = ell_cls(e.x);
+		if (st.z == 0) {
 			// constraint of the partner only: {j} -> {x_v}  (search_unit.hpp:881-885)
-			int kind = mv.kind(c);
-			if (kind == GHOST_KIND_ALL_DIFFERENT) {
+			if (cls == GB_CLS_LINEAR) sum += linear_error_w(ell_w(e.x), st.x + e.y * dx) - st.y;
+			else if (cls == GB_CLS_ALLDIFF) {
 				int tab = mv.cnt_tab(c);
 				sum += s.cnt(tab + xv) - (s.cnt(tab + xj) - 1);
-			} else if (kind_is_linear(kind)) {
-				sum += linear_error(kind, s.S[c] - mv.rhs(c) + e.y * (xv - xj)) - s.err_c[c];
-			} else if (kind == GHOST_KIND_FIX_VALUE) {
+			} else if (cls == GB_CLS_FIX) {
 				int kk = mv.rhs(c);
 				sum += abs(xv - kk) - abs(xj - kk);
-			} else if (kind == GHOST_KIND_ALL_DIFFERENT_ABS_DIFF) {
-				sum += absdiff_delta(mv, s, c, e.y, xv, -1, 0);
-			}
-		} else {
+			} else if (cls == GB_CLS_ABSDIFF) sum += absdiff_delta(mv, s, c, e.y, xv, -1, 0);
+		} else if (st.z != GB_MARK_SKIP) {
 			// both variables in scope: {v,j} -> {x_j,x_v} (search_unit.hpp:872-874); replace the
 			// single-variable delta already added from the hoisted entry
-			const int* h = s.hoist + 8 * (mk - 1);
-			int type = h[0];
-			if (type == 0) sum -= s.cnt(h[1] + xj) - h[2];
-			else if (type == 1) {
-				int t1 = h[2] + h[1] * xj;
-				sum += linear_error(h[4], t1 + e.y * (xv - xj)) - linear_error(h[4], t1);
-			} else if (type == 2) sum += abs(xv - h[1]) - abs(xj - h[1]);
-			else if (type == 4) sum += absdiff_delta(mv, s, c, h[1], xj, e.y, xv) - absdiff_delta(mv, s, c, h[1], xj, -1, 0);
+			const int4 h = s.hoist[st.z - 1];
+			if (cls == GB_CLS_LINEAR) {
+				int w = ell_w(e.x), t1 = h.z + h.y * xj;
+				sum += linear_error_w(w, t1 + e.y * dx) - linear_error_w(w, t1);
+			} else if (cls == GB_CLS_ALLDIFF) sum -= s.cnt(h.y + xj) - h.z;
+			else if (cls == GB_CLS_FIX) sum += abs(xv - h.y) - abs(xj - h.y);
+			else if (cls == GB_CLS_ABSDIFF) sum += absdiff_delta(mv, s, c, h.y, xj, e.y, xv) - absdiff_delta(mv, s, c, h.y, xj, -1, 0);
 		}
 	}
 	*out = sum;
@@ -553,20 +601,20 @@ __device__ __forceinline__ bool candidate_sum(const DevModel& m, const MV& mv, c
 
 // Evaluate every candidate of variable v: chunk minima + tie masks into (val_key, val_bits).
 // If out != nullptr also stores each candidate's sum (GHOST_B200_NOT_A_CANDIDATE otherwise).
-// Returns the number of candidates seen by this thread's warp chunks (to be group-summed).
-template <int T>
-__device__ inline int evaluate_candidates(const DevModel& m, const WS& s, int v, int deg, int nchunks_c, int* out)
+// Returns (in lane 0 of each warp) the number of candidates seen by the warp's chunks.
+template <int T, bool PERM>
+__device__ inline int evaluate_candidates(const DevModel& m, const WS& s, int v, int nh, int bias, int nchunks_c, int* out)
 {
 	typedef Group<T> G;
 	MV mv(m);
 	const int lane = threadIdx.x & 31;
 	const int xv = s.x[v];
-	const int nslots = m.permutation ? m.V : mv.dom_size(v);
+	const int nslots = PERM ? m.V : mv.dom_size(v);
 	int ncandidates = 0;
 	for (int ch = G::warp(); ch < nchunks_c; ch += G::NW) {
 		int slot = ch * 32 + lane;
 		int sum = GB_INT_MAX;
-		bool ok = candidate_sum(m, mv, s, v, xv, deg, slot, nslots, &sum);
+		bool ok = candidate_sum<PERM>(m, mv, s, v, xv, nh, bias, slot, nslots, &sum);
 		if (!ok) sum = GB_INT_MAX;
 		if (out && slot < m.max_candidates) out[slot] = sum;
 		int cmin = __reduce_min_sync(0xffffffffu, sum);
@@ -582,8 +630,8 @@ __device__ inline int evaluate_candidates(const DevModel& m, const WS& s, int v,
 // SearchUnit::local_move's update part (search_unit.hpp:449-541): constraint errors, caches,
 // projection, then the value(s).  One thread per affected constraint computes its delta with the
 // generic constraint_delta(); the projection update (…projection_algorithm.cpp:51-58) is a
-// shared-memory scatter.  Returns nothing; ends with a barrier.  `partner` is the swap partner in
-// permutation mode, `new_value` the value otherwise.
+// shared-memory scatter.  Ends with a barrier.  `new_value` is the swap partner in permutation
+// mode, the value otherwise.
 // ---------------------------------------------------------------------------------------------
 template <int T>
 __device__ inline void apply_move(const DevModel& m, const WS& s, int v, int new_value)
@@ -611,19 +659,19 @@ __device__ inline void apply_move(const DevModel& m, const WS& s, int v, int new
 			if (kind == GHOST_KIND_ALL_DIFFERENT) {
 				if (!both && nv_new != xv) { int tab = mv.cnt_tab(c); s.cnt_add(tab + xv, -1); s.cnt_add(tab + nv_new, +1); }
 			} else if (kind_is_linear(kind)) {
-				s.S[c] += e.y * (nv_new - xv) + (both ? eb * (xv - xj) : 0);
+				s.T_of(c) += e.y * (nv_new - xv) + (both ? eb * (xv - xj) : 0);
 			}
-			s.err_c[c] += delta;
+			s.err_of(c) += delta;
 		} else {
 			int2 e = mv.row_entry(rbj + (k - degv));
 			c = e.x;
-			if (s.mark[c] != 0) { s.upd[2 * k] = -1; continue; } // shared with v: handled above
+			if (s.mark_of(c) != 0) { s.upd[2 * k] = -1; continue; } // shared with v: handled above
 			delta = constraint_delta(mv, s, c, j, e.y, xv, -1, 0, 0);
 			int kind = mv.kind(c);
 			if (kind == GHOST_KIND_ALL_DIFFERENT) {
 				if (xv != xj) { int tab = mv.cnt_tab(c); s.cnt_add(tab + xj, -1); s.cnt_add(tab + xv, +1); }
-			} else if (kind_is_linear(kind)) s.S[c] += e.y * (xv - xj);
-			s.err_c[c] += delta;
+			} else if (kind_is_linear(kind)) s.T_of(c) += e.y * (xv - xj);
+			s.err_of(c) += delta;
 		}
 		s.upd[2 * k] = c; s.upd[2 * k + 1] = delta;
 	}
