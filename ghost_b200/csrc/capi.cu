@@ -13,6 +13,7 @@
 #include <cuda_runtime.h>
 
 #include "kernels.cuh"
+#include "launch.h"
 
 using namespace ghost_b200;
 
@@ -141,8 +142,8 @@ struct LaunchCfg { int T, walkers_per_cta, block; size_t smem; };
 static int pick_launch(const GhostModel* gm, const WalkerLayout& L, int requested_T, LaunchCfg* cfg)
 {
 	int T = requested_T > 0 ? requested_T : gm->low.default_threads_per_walker();
-	if (!(T == 32 || T == 64 || T == 128 || T == 256 || T == 512))
-		return set_error(GHOST_B200_ERR_INVALID, "threads_per_walker must be 32, 64, 128, 256 or 512");
+	if (!(T == 32 || T == 64 || T == 128 || T == 256))
+		return set_error(GHOST_B200_ERR_INVALID, "threads_per_walker must be 32, 64, 128 or 256");
 	int wpc = 1;
 	if (T == 32) {
 		// several warp-walkers per CTA, bounded by shared memory
@@ -157,58 +158,28 @@ static int pick_launch(const GhostModel* gm, const WalkerLayout& L, int requeste
 	return GHOST_B200_OK;
 }
 
-template <typename K>
-static cudaError_t allow_smem(K kernel, size_t smem)
-{
-	return cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-}
-
 static cudaError_t launch_search(int T, int grid, int block, size_t smem, cudaStream_t st, const DevModel& m,
                                  const WalkerLayout& L, const SearchParams& p)
 {
-	cudaError_t e;
 	switch (T) {
-#define GB_CASE(TT)                                                                          \
-	case TT:                                                                                 \
-		if (m.permutation) {                                                                 \
-			e = allow_smem(search_kernel<TT, true>, smem);                                   \
-			if (e != cudaSuccess) return e;                                                  \
-			search_kernel<TT, true><<<grid, block, smem, st>>>(m, L, p);                     \
-		} else {                                                                             \
-			e = allow_smem(search_kernel<TT, false>, smem);                                  \
-			if (e != cudaSuccess) return e;                                                  \
-			search_kernel<TT, false><<<grid, block, smem, st>>>(m, L, p);                    \
-		}                                                                                    \
-		break;
-		GB_CASE(32) GB_CASE(64) GB_CASE(128) GB_CASE(256) GB_CASE(512)
-#undef GB_CASE
+	case 32: return launch_search_t32(grid, block, smem, st, m, L, p);
+	case 64: return launch_search_t64(grid, block, smem, st, m, L, p);
+	case 128: return launch_search_t128(grid, block, smem, st, m, L, p);
+	case 256: return launch_search_t256(grid, block, smem, st, m, L, p);
 	default: return cudaErrorInvalidValue;
 	}
-	return cudaGetLastError();
 }
 
 static cudaError_t launch_eval(int T, int grid, int block, size_t smem, cudaStream_t st, const DevModel& m,
                                const WalkerLayout& L, int W, const int* x, const int* sel, int* ce, int* ve, int* cd)
 {
-	cudaError_t e;
 	switch (T) {
-#define GB_CASE(TT)                                                                          \
-	case TT:                                                                                 \
-		if (m.permutation) {                                                                 \
-			e = allow_smem(eval_kernel<TT, true>, smem);                                     \
-			if (e != cudaSuccess) return e;                                                  \
-			eval_kernel<TT, true><<<grid, block, smem, st>>>(m, L, W, x, sel, ce, ve, cd);   \
-		} else {                                                                             \
-			e = allow_smem(eval_kernel<TT, false>, smem);                                    \
-			if (e != cudaSuccess) return e;                                                  \
-			eval_kernel<TT, false><<<grid, block, smem, st>>>(m, L, W, x, sel, ce, ve, cd);  \
-		}                                                                                    \
-		break;
-		GB_CASE(32) GB_CASE(64) GB_CASE(128) GB_CASE(256) GB_CASE(512)
-#undef GB_CASE
+	case 32: return launch_eval_t32(grid, block, smem, st, m, L, W, x, sel, ce, ve, cd);
+	case 64: return launch_eval_t64(grid, block, smem, st, m, L, W, x, sel, ce, ve, cd);
+	case 128: return launch_eval_t128(grid, block, smem, st, m, L, W, x, sel, ce, ve, cd);
+	case 256: return launch_eval_t256(grid, block, smem, st, m, L, W, x, sel, ce, ve, cd);
 	default: return cudaErrorInvalidValue;
 	}
-	return cudaGetLastError();
 }
 
 // ---- parity hook --------------------------------------------------------------------------------

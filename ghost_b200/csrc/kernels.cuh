@@ -43,7 +43,7 @@ __device__ __forceinline__ unsigned long long quality_key(bool optimization, int
 
 // first n entries of a uniform shuffle of 0..V-1 (replaces rng.shuffle + prefix, search_unit.hpp:
 // 206-211, 239-246): rejection sampling over one RNG event, by thread 0.
-template <int T>
+template <int T, class WS>
 __device__ inline void sample_distinct(const DevModel& m, const WS& s, Rng& rng, int n, int* out)
 {
 	typedef Group<T> G;
@@ -67,7 +67,7 @@ __device__ inline void sample_distinct(const DevModel& m, const WS& s, Rng& rng,
 }
 
 // SearchUnit::monte_carlo_sampling (search_unit.hpp:201-212)
-template <int T>
+template <int T, class WS>
 __device__ inline void monte_carlo_sampling(const DevModel& m, const WS& s, Rng& rng, int nb)
 {
 	typedef Group<T> G;
@@ -95,6 +95,7 @@ __device__ inline void monte_carlo_sampling(const DevModel& m, const WS& s, Rng&
 	G::sync();
 }
 
+template <class WS>
 __device__ __forceinline__ void try_swap(const DevModel& m, const MV& mv, const WS& s, int i, int j)
 {
 	// search_unit.hpp:224-231 / 247-254
@@ -109,7 +110,7 @@ __device__ __forceinline__ void try_swap(const DevModel& m, const MV& mv, const 
 // j1<j2<..<jm rotate the values along (i, j1, .., jm); with identical domains every swap is legal,
 // so one warp applies the rotation chunk-by-chunk with ballots (same result as the sequential
 // loop, coin for coin).  Otherwise thread 0 runs the sequential loop.
-template <int T>
+template <int T, class WS>
 __device__ inline void random_permutations(const DevModel& m, const WS& s, Rng& rng, int nb)
 {
 	typedef Group<T> G;
@@ -181,14 +182,14 @@ __device__ __forceinline__ long long internal_cost(const DevModel& m, long long 
 	return m.objective == GHOST_OBJ_LINEAR_MAXIMIZE ? -obj_sum : obj_sum; // src/objective.cpp:60-61
 }
 
-template <int T>
+template <int T, class WS>
 __device__ inline void copy_best(const DevModel& m, const WS& s, int* best_x)
 {
 	for (int v = Group<T>::tid(); v < m.V; v += T) best_x[v] = s.x[v];
 }
 
 // SearchUnit::initialize_data_structures (search_unit.hpp:274-317)
-template <int T>
+template <int T, class WS>
 __device__ inline void initialize_data_structures(const DevModel& m, const WS& s, WalkerRegs& r, int* best_x)
 {
 	typedef Group<T> G;
@@ -212,7 +213,7 @@ __device__ inline void initialize_data_structures(const DevModel& m, const WS& s
 // SearchUnit::set_initial_configuration (search_unit.hpp:153-198); s.tabu doubles as the
 // best_values buffer (it is cleared by initialize_data_structures right after).
 // Deviation D1: best_x follows best_sat here too.
-template <int T>
+template <int T, class WS>
 __device__ inline void set_initial_configuration(const DevModel& m, const WS& s, WalkerRegs& r, Rng& rng, int samplings, int* best_x)
 {
 	typedef Group<T> G;
@@ -234,7 +235,7 @@ __device__ inline void set_initial_configuration(const DevModel& m, const WS& s,
 }
 
 // SearchUnit::initialize_variable_values (search_unit.hpp:259-272)
-template <int T>
+template <int T, class WS>
 __device__ inline void initialize_variable_values(const DevModel& m, const WS& s, WalkerRegs& r, Rng& rng, const SearchParams& p, int* best_x)
 {
 	typedef Group<T> G;
@@ -248,7 +249,7 @@ __device__ inline void initialize_variable_values(const DevModel& m, const WS& s
 }
 
 // SearchUnit::local_move (search_unit.hpp:516-541)
-template <int T>
+template <int T, class WS>
 __device__ inline void local_move(const DevModel& m, const WS& s, WalkerRegs& r, const SearchParams& p, int v, int new_value, int delta)
 {
 	MV mv(m);
@@ -267,7 +268,7 @@ __device__ inline void local_move(const DevModel& m, const WS& s, WalkerRegs& r,
 }
 
 // =================================================================================================
-template <int T, bool PERM>
+template <int T, bool PERM, bool EQ, class XT>
 __global__ void __launch_bounds__(T == 32 ? 128 : T)
 search_kernel(const DevModel m, const WalkerLayout L, const SearchParams p)
 {
@@ -277,7 +278,8 @@ search_kernel(const DevModel m, const WalkerLayout L, const SearchParams p)
 	const int local = (T == 32) ? (threadIdx.x >> 5) : 0;
 	const int w = blockIdx.x * walkers_per_cta + local;
 	if (w >= p.num_walkers) return; // whole group leaves together
-	const WS s = make_ws(smem_raw + (size_t)local * L.total_bytes, L);
+	typedef WST<XT> WS;
+	const WS s = make_ws<WS>(smem_raw + (size_t)local * L.total_bytes, L);
 	const int tid = G::tid();
 	MV mv(m);
 	const bool optimization = m.objective != GHOST_OBJ_NONE;
@@ -349,7 +351,7 @@ search_kernel(const DevModel m, const WalkerLayout L, const SearchParams p)
 			const int nh = hoist_variable<T>(m, s, v, &bias);
 			G::sync();
 			if (tid == 0) s.cand_bits[v >> 5] &= ~(1u << (v & 31)); // search_unit.hpp:826-828
-			int mine = evaluate_candidates<T, PERM>(m, s, v, nh, bias, L.nchunks_c, nullptr);
+			int mine = evaluate_candidates<T, PERM, EQ>(m, s, v, nh, bias, L.nchunks_c, nullptr);
 			G::sync();
 			const int ncandidates = G::sum(mine, s.red + 16);
 			if (tid == 0) s.counters[K_EVALS] += ncandidates;
@@ -453,7 +455,7 @@ search_kernel(const DevModel m, const WalkerLayout L, const SearchParams p)
 // =================================================================================================
 // Parity hook: for each walker's assignment and selected variable write constraint errors,
 // projected errors and the cumulated delta of every candidate slot.
-template <int T, bool PERM>
+template <int T, bool PERM, bool EQ, class XT>
 __global__ void __launch_bounds__(T == 32 ? 128 : T)
 eval_kernel(const DevModel m, const WalkerLayout L, int num_walkers, const int* __restrict__ assignments,
             const int* __restrict__ selected, int* __restrict__ ctr_error, int* __restrict__ var_error,
@@ -465,7 +467,8 @@ eval_kernel(const DevModel m, const WalkerLayout L, int num_walkers, const int* 
 	const int local = (T == 32) ? (threadIdx.x >> 5) : 0;
 	const int w = blockIdx.x * walkers_per_cta + local;
 	if (w >= num_walkers) return;
-	const WS s = make_ws(smem_raw + (size_t)local * L.total_bytes, L);
+	typedef WST<XT> WS;
+	const WS s = make_ws<WS>(smem_raw + (size_t)local * L.total_bytes, L);
 	const int tid = G::tid();
 	for (int v = tid; v < m.V; v += T) s.x[v] = assignments[(size_t)w * m.V + v];
 	G::sync();
@@ -478,7 +481,7 @@ eval_kernel(const DevModel m, const WalkerLayout L, int num_walkers, const int* 
 	int bias;
 	const int nh = hoist_variable<T>(m, s, v, &bias);
 	G::sync();
-	evaluate_candidates<T, PERM>(m, s, v, nh, bias, L.nchunks_c, out);
+	evaluate_candidates<T, PERM, EQ>(m, s, v, nh, bias, L.nchunks_c, out);
 }
 
 } // namespace ghost_b200

@@ -1,0 +1,62 @@
+// launch_impl.cuh — instantiates the kernels for ONE threads-per-walker value (GB_T) so that the
+// variants compile in parallel (launch_t32.cu, launch_t64.cu, ...).  Variant axes: permutation
+// problem, "every live constraint is a LinearEquationEq" fast path, int16 assignment storage.
+#include "kernels.cuh"
+#include "launch.h"
+
+namespace ghost_b200 {
+
+template <typename K>
+static cudaError_t allow_smem(K kernel, size_t smem)
+{
+	return cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+}
+
+template <bool PERM, bool EQ, class XT>
+static cudaError_t do_search(int grid, int block, size_t smem, cudaStream_t st, const DevModel& m, const WalkerLayout& L, const SearchParams& p)
+{
+	cudaError_t e = allow_smem(search_kernel<GB_T, PERM, EQ, XT>, smem);
+	if (e != cudaSuccess) return e;
+	search_kernel<GB_T, PERM, EQ, XT><<<grid, block, smem, st>>>(m, L, p);
+	return cudaGetLastError();
+}
+template <bool PERM, bool EQ, class XT>
+static cudaError_t do_eval(int grid, int block, size_t smem, cudaStream_t st, const DevModel& m, const WalkerLayout& L, int W,
+                           const int* x, const int* sel, int* ce, int* ve, int* cd)
+{
+	cudaError_t e = allow_smem(eval_kernel<GB_T, PERM, EQ, XT>, smem);
+	if (e != cudaSuccess) return e;
+	eval_kernel<GB_T, PERM, EQ, XT><<<grid, block, smem, st>>>(m, L, W, x, sel, ce, ve, cd);
+	return cudaGetLastError();
+}
+
+#define GB_DISPATCH(FN, ...)                                                                      \
+	do {                                                                                          \
+		const int key = (m.permutation ? 4 : 0) | (m.eq_only ? 2 : 0) | (m.x16 ? 1 : 0);           \
+		switch (key) {                                                                            \
+		case 0: return FN<false, false, int>(__VA_ARGS__);                                        \
+		case 1: return FN<false, false, short>(__VA_ARGS__);                                      \
+		case 2: return FN<false, true, int>(__VA_ARGS__);                                         \
+		case 3: return FN<false, true, short>(__VA_ARGS__);                                       \
+		case 4: return FN<true, false, int>(__VA_ARGS__);                                         \
+		case 5: return FN<true, false, short>(__VA_ARGS__);                                       \
+		case 6: return FN<true, true, int>(__VA_ARGS__);                                          \
+		default: return FN<true, true, short>(__VA_ARGS__);                                       \
+		}                                                                                         \
+	} while (0)
+
+#define GB_CAT2(a, b) a##b
+#define GB_CAT(a, b) GB_CAT2(a, b)
+
+cudaError_t GB_CAT(launch_search_t, GB_T)(int grid, int block, size_t smem, cudaStream_t st, const DevModel& m,
+                                          const WalkerLayout& L, const SearchParams& p)
+{
+	GB_DISPATCH(do_search, grid, block, smem, st, m, L, p);
+}
+cudaError_t GB_CAT(launch_eval_t, GB_T)(int grid, int block, size_t smem, cudaStream_t st, const DevModel& m,
+                                        const WalkerLayout& L, int W, const int* x, const int* sel, int* ce, int* ve, int* cd)
+{
+	GB_DISPATCH(do_eval, grid, block, smem, st, m, L, W, x, sel, ce, ve, cd);
+}
+
+} // namespace ghost_b200

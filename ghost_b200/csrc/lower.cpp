@@ -48,7 +48,7 @@ int lower_model(const GhostModelDesc* d, LoweredModel* out, std::string* why)
 	std::vector<int32_t> dom_lo(V), dom_size(V), dom_off(V + 1, 0), dom_vals;
 	bool contiguous = true, identical = true;
 	int max_dom = 0;
-	int64_t max_abs_value = 0;
+	int64_t max_abs_value = 0, min_value = 0, max_value = 0;
 	for (int v = 0; v < V; ++v) {
 		int b = d->dom_offset[v], e = d->dom_offset[v + 1];
 		if (e <= b) return fail(GHOST_B200_ERR_INVALID, "variable " + std::to_string(v) + " has an empty domain");
@@ -64,6 +64,8 @@ int lower_model(const GhostModelDesc* d, LoweredModel* out, std::string* why)
 		dom_off[v + 1] = dom_off[v] + dom_size[v];
 		dom_vals.insert(dom_vals.end(), dv.begin(), dv.end());
 		max_dom = std::max(max_dom, dom_size[v]);
+		min_value = std::min<int64_t>(min_value, dv.front());
+		max_value = std::max<int64_t>(max_value, dv.back());
 		max_abs_value = std::max<int64_t>(max_abs_value, std::max(std::llabs((long long)dv.front()), std::llabs((long long)dv.back())));
 		if (v > 0) {
 			if (dom_size[v] != dom_size[0] || !std::equal(dv.begin(), dv.end(), dom_vals.begin())) identical = false;
@@ -131,7 +133,24 @@ int lower_model(const GhostModelDesc* d, LoweredModel* out, std::string* why)
 				}
 			}
 		}
-		if (is_alldiff_like(k)) {
+		if (k == GHOST_KIND_ALL_DIFFERENT && d->permutation_problem && (e - b) == V) {
+			// A permutation problem only ever swaps values, so an AllDifferent over ALL variables keeps
+			// the error its start values give it, and every move's delta on it is 0
+			// (all_different.cpp:77-100 with both swapped variables in scope): no cache, no table.
+			std::vector<int32_t> vals(d->start_value, d->start_value + V);
+			std::sort(vals.begin(), vals.end());
+			int64_t err = 0;
+			for (size_t i = 0; i < vals.size();) {
+				size_t j2 = i;
+				while (j2 < vals.size() && vals[j2] == vals[i]) ++j2;
+				int64_t n2 = static_cast<int64_t>(j2 - i);
+				err += n2 * (n2 - 1) / 2;
+				i = j2;
+			}
+			kind[c] = GB_KIND_STATIC;
+			rhs[c] = static_cast<int32_t>(err);
+			error_bound += err;
+		} else if (is_alldiff_like(k)) {
 			int64_t n = e - b;
 			if (n == 0) { lo = 0; hi = 0; }
 			int64_t base = lo, size = hi - lo + 1;
@@ -199,14 +218,22 @@ int lower_model(const GhostModelDesc* d, LoweredModel* out, std::string* why)
 	o.obj_coef = put(obj_coef);
 	// ELL rows for the hot loop: one fixed-stride row per variable, class / error weights packed in
 	// the entry so that the candidate loop needs no per-constraint global lookups for linear kinds.
-	const int stride = std::max(1, max_degree);
+	std::vector<std::vector<std::pair<int, int>>> live(V); // rows without the static constraints
+	int live_degree = 0;
+	bool eq_only = true;
+	for (int c = 0; c < C; ++c) if (!(kind[c] == GHOST_KIND_LINEAR_EQ || kind[c] == GB_KIND_STATIC)) eq_only = false;
+	for (int v = 0; v < V; ++v) {
+		for (auto& pr : rows[v]) if (kind[pr.first] != GB_KIND_STATIC) live[v].push_back(pr);
+		live_degree = std::max<int>(live_degree, static_cast<int>(live[v].size()));
+	}
+	const int stride = std::max(1, live_degree);
 	std::vector<int32_t> ell(static_cast<size_t>(V) * stride * 2, 0), has_ctr((V + 31) / 32, 0);
 	for (int v = 0; v < V; ++v) {
 		if (!rows[v].empty()) has_ctr[v >> 5] |= (1u << (v & 31));
 		for (int k = 0; k < stride; ++k) {
 			int w0 = GB_ELL_END, w1 = 0;
-			if (k < static_cast<int>(rows[v].size())) {
-				int c = rows[v][k].first, kd = kind[c];
+			if (k < static_cast<int>(live[v].size())) {
+				int c = live[v][k].first, kd = kind[c];
 				int cls = GB_CLS_ZERO, wbits = 0;
 				switch (kd) {
 				case GHOST_KIND_LINEAR_EQ:  cls = GB_CLS_LINEAR; wbits = 3; break; // |t| = max(t,0) + max(-t,0)
@@ -222,7 +249,7 @@ int lower_model(const GhostModelDesc* d, LoweredModel* out, std::string* why)
 				}
 				int universal = (c2v_off[c + 1] - c2v_off[c] == V) ? 1 : 0;
 				w0 = c | (cls << 20) | (wbits << 24) | (universal << 27);
-				w1 = rows[v][k].second;
+				w1 = live[v][k].second;
 			}
 			ell[(static_cast<size_t>(v) * stride + k) * 2] = w0;
 			ell[(static_cast<size_t>(v) * stride + k) * 2 + 1] = w1;
@@ -246,6 +273,8 @@ int lower_model(const GhostModelDesc* d, LoweredModel* out, std::string* why)
 	m.max_degree = std::max(1, max_degree);
 	m.has_abs_diff = has_abs_diff ? 1 : 0;
 	m.ell_stride = stride;
+	m.eq_only = eq_only ? 1 : 0;
+	m.x16 = (min_value >= -32768 && max_value <= 32767) ? 1 : 0;
 	return GHOST_B200_OK;
 }
 
@@ -259,7 +288,7 @@ WalkerLayout LoweredModel::layout(int /*threads_per_walker*/, int nreset) const
 	auto take = [&](int bytes) { int r = at; at = align_up(at + bytes, 16); return r; };
 	w.nchunks_v = (m.V + 31) / 32;
 	w.nchunks_c = (m.max_candidates + 31) / 32;
-	w.x = take(4 * m.V);
+	w.x = take((m.x16 ? 2 : 4) * m.V);
 	w.err_var = take(4 * m.V);
 	w.tabu = take(4 * m.V);
 	w.cs = take(16 * m.C);
@@ -268,12 +297,14 @@ WalkerLayout LoweredModel::layout(int /*threads_per_walker*/, int nreset) const
 	w.cnt = take(2 * std::max(1, m.cnt_total));
 	w.persist_bytes = at;
 	w.counters = take(8 * 8);
-	w.flags = take(m.V);
+	// sampling scratch lives in arrays that are dead while a reset samples: the tabu list (cleared by
+	// initialize_data_structures afterwards) and the projected errors (recomputed afterwards)
+	w.flags = w.tabu;
 	w.val_key = take(4 * w.nchunks_c);
 	w.val_bits = take(4 * w.nchunks_c);
 	w.hoist = take(4 * 8 * m.max_degree);
 	w.upd = take(4 * 2 * 2 * m.max_degree);
-	w.sample = take(4 * 2 * std::max(1, nreset));
+	w.sample = (8 * std::max(1, nreset) <= 4 * m.V) ? w.err_var : take(4 * 2 * std::max(1, nreset));
 	w.red = take(4 * 64);
 	w.total_bytes = at;
 	return w;
@@ -287,8 +318,7 @@ int LoweredModel::default_threads_per_walker() const
 	if (work <= 256) return 32;
 	if (work <= 512) return 64;
 	if (work <= 2048) return 128;
-	if (work <= 8192) return 256;
-	return 512;
+	return 256;
 }
 
 } // namespace ghost_b200

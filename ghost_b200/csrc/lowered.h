@@ -41,8 +41,14 @@ struct DevModel {
 	int max_candidates;        // max over variables of candidate slots (V for permutation problems)
 	int max_degree;            // max #constraints touching one variable
 	int has_abs_diff;
-	int ell_stride;            // entries per ELL row (= max_degree)
+	int ell_stride;            // entries per ELL row (max number of non-static constraints of a variable)
+	int eq_only;               // every constraint is LINEAR_EQ or static: the specialised evaluation applies
+	int x16;                   // every domain value fits int16: assignments are stored as shorts
 };
+
+// device-only constraint kind: an AllDifferent over all variables of a permutation problem
+// (constant error, delta 0 for every swap); its error is stored in the rhs section
+enum : int { GB_KIND_STATIC = 16 };
 
 // ELL entry encoding (word 0)
 enum : int { GB_ELL_END = 0xFFFFF, GB_CLS_LINEAR = 0, GB_CLS_ALLDIFF = 1, GB_CLS_FIX = 2, GB_CLS_ABSDIFF = 3, GB_CLS_ZERO = 4 };

@@ -96,9 +96,11 @@ struct Group {
 	}
 };
 
-// Shared-memory view of one walker
-struct WS {
-	int* x; int* err_var; int* tabu;
+// Shared-memory view of one walker; XT = short when every domain value fits int16, else int
+template <class XT>
+struct WST {
+	typedef XT x_type;
+	XT* x; int* err_var; int* tabu;
 	int4* cs;                   // per constraint {T = sum - rhs (linear kinds), current error, mark, 0}
 	int* cand_key; unsigned* cand_bits;
 	unsigned* cnt32;            // packed 16-bit counters, two per word
@@ -116,10 +118,11 @@ struct WS {
 	__device__ __forceinline__ int& mark_of(int c) const { return reinterpret_cast<int*>(cs + c)[2]; }
 };
 
+template <class WS>
 __device__ __forceinline__ WS make_ws(unsigned char* base, const WalkerLayout& L)
 {
 	WS s;
-	s.x = (int*)(base + L.x); s.err_var = (int*)(base + L.err_var); s.tabu = (int*)(base + L.tabu);
+	s.x = (typename WS::x_type*)(base + L.x); s.err_var = (int*)(base + L.err_var); s.tabu = (int*)(base + L.tabu);
 	s.cs = (int4*)(base + L.cs);
 	s.cand_key = (int*)(base + L.cand_key); s.cand_bits = (unsigned*)(base + L.cand_bits);
 	s.cnt32 = (unsigned*)(base + L.cnt);
@@ -195,8 +198,9 @@ __device__ __forceinline__ int binom2(int n) { return (n * (n - 1)) >> 1; } // a
 // when pb >= 0): recount the <= 4 neighbouring |differences|.  Kept out of line: only models that
 // use the extension pay for it.
 // ---------------------------------------------------------------------------------------------
+template <class XT>
 __device__ __noinline__ int absdiff_delta(const int32_t* blob, int c2v_off_sec, int c2v_sec, int cnt_tab_sec,
-                                          const int* x, const unsigned* cnt32, int c, int pa, int na, int pb, int nb)
+                                          const XT* x, const unsigned* cnt32, int c, int pa, int na, int pb, int nb)
 {
 	int b = __ldg(blob + c2v_off_sec + c), n = __ldg(blob + c2v_off_sec + c + 1) - b, tab = __ldg(blob + cnt_tab_sec + c);
 	int pairs[4]; int np = 0;
@@ -227,6 +231,7 @@ __device__ __noinline__ int absdiff_delta(const int32_t* blob, int c2v_off_sec, 
 	}
 	return diff;
 }
+template <class WS>
 __device__ __forceinline__ int absdiff_delta(const MV& mv, const WS& s, int c, int pa, int na, int pb, int nb)
 {
 	return absdiff_delta(mv.m.blob, mv.m.o.c2v_off, mv.m.o.c2v, mv.m.o.cnt_tab, s.x, s.cnt32, c, pa, na, pb, nb);
@@ -239,6 +244,7 @@ __device__ __forceinline__ int absdiff_delta(const MV& mv, const WS& s, int c, i
 // integers.  Used on the update path; the hot evaluation path uses the hoisted forms below and is
 // checked against this one by the trajectory tests.
 // ---------------------------------------------------------------------------------------------
+template <class WS>
 __device__ inline int constraint_delta(const MV& mv, const WS& s, int c, int va, int ea, int na, int vb, int eb, int nb)
 {
 	int kind = mv.kind(c);
@@ -287,7 +293,7 @@ __device__ inline int constraint_delta(const MV& mv, const WS& s, int c, int va,
 // Flat over the scope entries with a warp-segmented reduction per constraint.
 // Returns the total satisfaction error.  Ends with a group barrier.
 // ---------------------------------------------------------------------------------------------
-template <int T>
+template <int T, class WS>
 __device__ inline int recompute_all(const DevModel& m, const WS& s, int* red)
 {
 	typedef Group<T> G;
@@ -332,7 +338,7 @@ __device__ inline int recompute_all(const DevModel& m, const WS& s, int* red)
 			int t = s.T_of(c) - mv.rhs(c);
 			s.T_of(c) = t;
 			s.err_of(c) = linear_error_w(linear_w_of_kind(kind), t);
-		}
+		} else if (kind == GB_KIND_STATIC) s.err_of(c) = mv.rhs(c);
 	}
 	for (int t = tid; t < m.cnt_total; t += T) {
 		int n = s.cnt(t);
@@ -424,7 +430,7 @@ __device__ inline int chunks_max(const int* key, int nchunks)
 // variables.  Leaves (cand_key, cand_bits); returns ncand, writes worst error and tabu count.
 // Contains group barriers.
 // ---------------------------------------------------------------------------------------------
-template <int T>
+template <int T, class WS>
 __device__ inline int scan_candidates(const DevModel& m, const WS& s, int nchunks_v, int local_moves,
                                       bool free_vars_ok, int* red, int* worst_out, int* ntabu_out)
 {
@@ -475,7 +481,7 @@ __device__ inline int scan_candidates(const DevModel& m, const WS& s, int nchunk
 // (a swap inside them never changes an AllDifferent) are marked GB_MARK_SKIP and not hoisted.
 // Returns the number of hoisted entries.  The caller must barrier before reading.
 // ---------------------------------------------------------------------------------------------
-template <int T>
+template <int T, class WS>
 __device__ inline int hoist_variable(const DevModel& m, const WS& s, int v, int* bias_out)
 {
 	MV mv(m);
@@ -489,10 +495,6 @@ __device__ inline int hoist_variable(const DevModel& m, const WS& s, int v, int*
 		int c = ell_ctr(e.x);
 		if (c == GB_ELL_END) break;
 		int cls = ell_cls(e.x);
-		if (m.permutation && cls == GB_CLS_ALLDIFF && ell_universal(e.x)) {
-			if (writer) s.mark_of(c) = GB_MARK_SKIP;
-			continue;
-		}
 		int4 h = make_int4(cls | (ell_w(e.x) << 4) | (c << 8), 0, 0, 0);
 		if (cls == GB_CLS_LINEAR) {
 			int4 st = s.cs[c];
@@ -519,7 +521,7 @@ __device__ inline int hoist_variable(const DevModel& m, const WS& s, int v, int*
 	*bias_out = bias;
 	return nh;
 }
-template <int T>
+template <int T, class WS>
 __device__ inline void unmark_variable(const DevModel& m, const WS& s, int v)
 {
 	MV mv(m);
@@ -532,6 +534,7 @@ __device__ inline void unmark_variable(const DevModel& m, const WS& s, int v)
 
 // variable part of hoisted entry h when the selected variable alone takes value d (d != x_v);
 // the constant part is in the bias
+template <class WS>
 __device__ __forceinline__ int hoisted_term(const MV& mv, const WS& s, const int4 h, int d)
 {
 	int type = h.x & 0xF;
@@ -545,7 +548,7 @@ __device__ __forceinline__ int hoisted_term(const MV& mv, const WS& s, const int
 // Cumulated delta of one candidate (search_unit.hpp:836-887 + std::accumulate of
 // adaptive_search_value_heuristic.cpp:57-58).  slot = domain index (non-permutation) or partner
 // variable (permutation).  Returns false if the slot is not a candidate.
-template <bool PERM>
+template <bool PERM, bool EQ, class WS>
 __device__ __forceinline__ bool candidate_sum(const DevModel& m, const MV& mv, const WS& s, int v, int xv, int nh, int bias,
                                               int slot, int nslots, int* out)
 {
@@ -554,7 +557,11 @@ __device__ __forceinline__ bool candidate_sum(const DevModel& m, const MV& mv, c
 		int d = mv.dom_value(v, slot);
 		if (d == xv) return false;                       // search_unit.hpp:833
 		int sum = bias;
-		for (int k = 0; k < nh; ++k) sum += hoisted_term(mv, s, s.hoist[k], d);
+		if (EQ) {
+			// every constraint is a LinearEquationEq: |T - a*x_v + a*d| per constraint
+			for (int k = 0; k < nh; ++k) { int4 h = s.hoist[k]; sum += abs(h.z + h.y * d); }
+		} else
+			for (int k = 0; k < nh; ++k) sum += hoisted_term(mv, s, s.hoist[k], d);
 		*out = sum;                                      // no constraint: 0.0 (search_unit.hpp:847-848)
 		return true;
 	}
@@ -564,9 +571,29 @@ __device__ __forceinline__ bool candidate_sum(const DevModel& m, const MV& mv, c
 	if (xj == xv) return false;                          // search_unit.hpp:855-860
 	if (!m.identical_domains && !(mv.in_domain(v, xj) && mv.in_domain(j, xv))) return false;
 	int sum = bias;
-	for (int k = 0; k < nh; ++k) sum += hoisted_term(mv, s, s.hoist[k], xj);
 	const int dx = xv - xj;
 	const int2* row = mv.ell_row(j);
+	if (EQ) {
+		// specialised evaluation when every live constraint is a LinearEquationEq (linear_equation.cpp:
+		// 59-69 with linear_equation_eq.cpp:54-57): no kind dispatch at all
+		for (int k = 0; k < nh; ++k) { int4 h = s.hoist[k]; sum += abs(h.z + h.y * xj); }
+#pragma unroll 4
+		for (int k = 0; k < m.ell_stride; ++k) {
+			int2 e = __ldg(row + k);
+			int c = ell_ctr(e.x);
+			if (c == GB_ELL_END) break;
+			int4 st = s.cs[c];
+			if (st.z == 0) sum += abs(st.x + e.y * dx) - st.y;
+			else {
+				const int4 h = s.hoist[st.z - 1];
+				int t1 = h.z + h.y * xj;
+				sum += abs(t1 + e.y * dx) - abs(t1);
+			}
+		}
+		*out = sum;
+		return true;
+	}
+	for (int k = 0; k < nh; ++k) sum += hoisted_term(mv, s, s.hoist[k], xj);
 	for (int k = 0; k < m.ell_stride; ++k) {
 		int2 e = __ldg(row + k);
 		int c = ell_ctr(e.x);
@@ -583,7 +610,7 @@ __device__ __forceinline__ bool candidate_sum(const DevModel& m, const MV& mv, c
 				int kk = mv.rhs(c);
 				sum += abs(xv - kk) - abs(xj - kk);
 			} else if (cls == GB_CLS_ABSDIFF) sum += absdiff_delta(mv, s, c, e.y, xv, -1, 0);
-		} else if (st.z != GB_MARK_SKIP) {
+		} else {
 			// both variables in scope: {v,j} -> {x_j,x_v} (search_unit.hpp:872-874); replace the
 			// single-variable delta already added from the hoisted entry
 			const int4 h = s.hoist[st.z - 1];
@@ -602,7 +629,7 @@ __device__ __forceinline__ bool candidate_sum(const DevModel& m, const MV& mv, c
 // Evaluate every candidate of variable v: chunk minima + tie masks into (val_key, val_bits).
 // If out != nullptr also stores each candidate's sum (GHOST_B200_NOT_A_CANDIDATE otherwise).
 // Returns (in lane 0 of each warp) the number of candidates seen by the warp's chunks.
-template <int T, bool PERM>
+template <int T, bool PERM, bool EQ, class WS>
 __device__ inline int evaluate_candidates(const DevModel& m, const WS& s, int v, int nh, int bias, int nchunks_c, int* out)
 {
 	typedef Group<T> G;
@@ -614,7 +641,7 @@ __device__ inline int evaluate_candidates(const DevModel& m, const WS& s, int v,
 	for (int ch = G::warp(); ch < nchunks_c; ch += G::NW) {
 		int slot = ch * 32 + lane;
 		int sum = GB_INT_MAX;
-		bool ok = candidate_sum<PERM>(m, mv, s, v, xv, nh, bias, slot, nslots, &sum);
+		bool ok = candidate_sum<PERM, EQ>(m, mv, s, v, xv, nh, bias, slot, nslots, &sum);
 		if (!ok) sum = GB_INT_MAX;
 		if (out && slot < m.max_candidates) out[slot] = sum;
 		int cmin = __reduce_min_sync(0xffffffffu, sum);
@@ -633,7 +660,7 @@ __device__ inline int evaluate_candidates(const DevModel& m, const WS& s, int v,
 // shared-memory scatter.  Ends with a barrier.  `new_value` is the swap partner in permutation
 // mode, the value otherwise.
 // ---------------------------------------------------------------------------------------------
-template <int T>
+template <int T, class WS>
 __device__ inline void apply_move(const DevModel& m, const WS& s, int v, int new_value)
 {
 	typedef Group<T> G;
