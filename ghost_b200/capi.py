@@ -14,7 +14,7 @@ from .modeldesc import (GhostCountersStruct, GhostModelDescStruct, GhostResultSt
                         ModelDesc, default_opts)
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libghost_b200.so")
+LIB_PATH = os.environ.get("GHOST_B200_LIB") or os.path.join(_HERE, "libghost_b200.so")
 
 
 class GhostError(RuntimeError):

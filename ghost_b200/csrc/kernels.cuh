@@ -268,8 +268,14 @@ __device__ inline void local_move(const DevModel& m, const WS& s, WalkerRegs& r,
 }
 
 // =================================================================================================
+// Resident warps per SM the register allocator is asked to leave room for (the walkers' shared
+// memory allows about 20 per SM on the magic-square benchmark model).
+#ifndef GB_WARPS_PER_SM
+#define GB_WARPS_PER_SM 20
+#endif
+
 template <int T, bool PERM, bool EQ, class XT>
-__global__ void __launch_bounds__(T == 32 ? 128 : T)
+__global__ void __launch_bounds__(T == 32 ? 128 : T, (GB_WARPS_PER_SM * 32) / (T == 32 ? 128 : T))
 search_kernel(const DevModel m, const WalkerLayout L, const SearchParams p)
 {
 	typedef Group<T> G;
@@ -298,6 +304,7 @@ search_kernel(const DevModel m, const WalkerLayout L, const SearchParams p)
 		const long long* k = reinterpret_cast<const long long*>(&gs->k);
 #pragma unroll
 		for (int i = 0; i < 8; ++i) s.counters[i] = k[i];
+		s.cs[m.C] = make_int4(0, 0, 0, 0); // the dummy constraint that pads the ELL rows
 	}
 
 	if (!gs->initialized) {
@@ -471,6 +478,7 @@ eval_kernel(const DevModel m, const WalkerLayout L, int num_walkers, const int* 
 	const WS s = make_ws<WS>(smem_raw + (size_t)local * L.total_bytes, L);
 	const int tid = G::tid();
 	for (int v = tid; v < m.V; v += T) s.x[v] = assignments[(size_t)w * m.V + v];
+	if (tid == 0) s.cs[m.C] = make_int4(0, 0, 0, 0);
 	G::sync();
 	recompute_all<T>(m, s, s.red);
 	if (ctr_error) for (int c = tid; c < m.C; c += T) ctr_error[(size_t)w * m.C + c] = s.err_of(c);

@@ -231,7 +231,9 @@ int lower_model(const GhostModelDesc* d, LoweredModel* out, std::string* why)
 	for (int v = 0; v < V; ++v) {
 		if (!rows[v].empty()) has_ctr[v >> 5] |= (1u << (v & 31));
 		for (int k = 0; k < stride; ++k) {
-			int w0 = GB_ELL_END, w1 = 0;
+			// rows are padded with the dummy constraint C: coefficient 0, error 0, never marked, so the
+			// specialised loops need no end-of-row test
+			int w0 = C | (GB_CLS_ZERO << 20), w1 = 0;
 			if (k < static_cast<int>(live[v].size())) {
 				int c = live[v][k].first, kd = kind[c];
 				int cls = GB_CLS_ZERO, wbits = 0;
@@ -291,7 +293,7 @@ WalkerLayout LoweredModel::layout(int /*threads_per_walker*/, int nreset) const
 	w.x = take((m.x16 ? 2 : 4) * m.V);
 	w.err_var = take(4 * m.V);
 	w.tabu = take(4 * m.V);
-	w.cs = take(16 * m.C);
+	w.cs = take(16 * (m.C + 1)); // + the all-zero dummy constraint that pads the ELL rows
 	w.cand_key = take(4 * w.nchunks_v);
 	w.cand_bits = take(4 * w.nchunks_v);
 	w.cnt = take(2 * std::max(1, m.cnt_total));

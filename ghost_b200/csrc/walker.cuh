@@ -493,7 +493,7 @@ __device__ inline int hoist_variable(const DevModel& m, const WS& s, int v, int*
 	for (int k = 0; k < m.ell_stride; ++k) {
 		int2 e = __ldg(row + k);
 		int c = ell_ctr(e.x);
-		if (c == GB_ELL_END) break;
+		if (c == m.C) break; // padding
 		int cls = ell_cls(e.x);
 		int4 h = make_int4(cls | (ell_w(e.x) << 4) | (c << 8), 0, 0, 0);
 		if (cls == GB_CLS_LINEAR) {
@@ -528,7 +528,7 @@ __device__ inline void unmark_variable(const DevModel& m, const WS& s, int v)
 	const int2* row = mv.ell_row(v);
 	for (int k = Group<T>::tid(); k < m.ell_stride; k += T) {
 		int c = ell_ctr(__ldg(row + k).x);
-		if (c != GB_ELL_END) s.mark_of(c) = 0;
+		if (c != m.C) s.mark_of(c) = 0;
 	}
 }
 
@@ -557,11 +557,7 @@ __device__ __forceinline__ bool candidate_sum(const DevModel& m, const MV& mv, c
 		int d = mv.dom_value(v, slot);
 		if (d == xv) return false;                       // search_unit.hpp:833
 		int sum = bias;
-		if (EQ) {
-			// every constraint is a LinearEquationEq: |T - a*x_v + a*d| per constraint
-			for (int k = 0; k < nh; ++k) { int4 h = s.hoist[k]; sum += abs(h.z + h.y * d); }
-		} else
-			for (int k = 0; k < nh; ++k) sum += hoisted_term(mv, s, s.hoist[k], d);
+		for (int k = 0; k < nh; ++k) sum += hoisted_term(mv, s, s.hoist[k], d);
 		*out = sum;                                      // no constraint: 0.0 (search_unit.hpp:847-848)
 		return true;
 	}
@@ -573,31 +569,11 @@ __device__ __forceinline__ bool candidate_sum(const DevModel& m, const MV& mv, c
 	int sum = bias;
 	const int dx = xv - xj;
 	const int2* row = mv.ell_row(j);
-	if (EQ) {
-		// specialised evaluation when every live constraint is a LinearEquationEq (linear_equation.cpp:
-		// 59-69 with linear_equation_eq.cpp:54-57): no kind dispatch at all
-		for (int k = 0; k < nh; ++k) { int4 h = s.hoist[k]; sum += abs(h.z + h.y * xj); }
-#pragma unroll 4
-		for (int k = 0; k < m.ell_stride; ++k) {
-			int2 e = __ldg(row + k);
-			int c = ell_ctr(e.x);
-			if (c == GB_ELL_END) break;
-			int4 st = s.cs[c];
-			if (st.z == 0) sum += abs(st.x + e.y * dx) - st.y;
-			else {
-				const int4 h = s.hoist[st.z - 1];
-				int t1 = h.z + h.y * xj;
-				sum += abs(t1 + e.y * dx) - abs(t1);
-			}
-		}
-		*out = sum;
-		return true;
-	}
 	for (int k = 0; k < nh; ++k) sum += hoisted_term(mv, s, s.hoist[k], xj);
 	for (int k = 0; k < m.ell_stride; ++k) {
 		int2 e = __ldg(row + k);
 		int c = ell_ctr(e.x);
-		if (c == GB_ELL_END) break;
+		if (c == m.C) break; // padding
 		int4 st = s.cs[c];
 		int cls = ell_cls(e.x);
 		if (st.z == 0) {
@@ -629,9 +605,71 @@ __device__ __forceinline__ bool candidate_sum(const DevModel& m, const MV& mv, c
 // Evaluate every candidate of variable v: chunk minima + tie masks into (val_key, val_bits).
 // If out != nullptr also stores each candidate's sum (GHOST_B200_NOT_A_CANDIDATE otherwise).
 // Returns (in lane 0 of each warp) the number of candidates seen by the warp's chunks.
+// Specialised evaluation when every live constraint is a LinearEquationEq (linear_equation.cpp:59-69
+// with linear_equation_eq.cpp:54-57): |T + a*delta| - error per constraint, no kind dispatch, the
+// selected variable's (a, T - a*x_v) pairs held in registers, no end-of-row tests (padded ELL rows),
+// no divergent control flow except the rare "partner shares a constraint with v" case.
+template <int T, bool PERM, class WS>
+__device__ inline int evaluate_candidates_eq(const DevModel& m, const WS& s, int v, int nh, int bias, int nchunks_c, int* out)
+{
+	typedef Group<T> G;
+	MV mv(m);
+	const int lane = threadIdx.x & 31;
+	const int xv = s.x[v];
+	const int nslots = PERM ? m.V : mv.dom_size(v);
+	int a0 = 0, b0 = 0, a1 = 0, b1 = 0, a2 = 0, b2 = 0, a3 = 0, b3 = 0;
+	if (nh > 0) { int4 h = s.hoist[0]; a0 = h.y; b0 = h.z; }
+	if (nh > 1) { int4 h = s.hoist[1]; a1 = h.y; b1 = h.z; }
+	if (nh > 2) { int4 h = s.hoist[2]; a2 = h.y; b2 = h.z; }
+	if (nh > 3) { int4 h = s.hoist[3]; a3 = h.y; b3 = h.z; }
+	const int stride = m.ell_stride;
+	const int2* ell = reinterpret_cast<const int2*>(m.blob + m.o.ell);
+	int ncandidates = 0;
+	for (int ch = G::warp(); ch < nchunks_c; ch += G::NW) {
+		const int slot = ch * 32 + lane;
+		bool ok = slot < nslots;
+		int d, j = 0;
+		if (PERM) {
+			j = min(slot, m.V - 1);
+			ok = ok && j != v;
+			d = s.x[j];
+			ok = ok && d != xv;                              // search_unit.hpp:855-860
+			if (!m.identical_domains) ok = ok && mv.in_domain(v, d) && mv.in_domain(j, xv);
+		} else {
+			d = mv.dom_value(v, min(slot, nslots - 1));
+			ok = ok && d != xv;                              // search_unit.hpp:833
+		}
+		int sum = bias + abs(b0 + a0 * d) + abs(b1 + a1 * d) + abs(b2 + a2 * d) + abs(b3 + a3 * d);
+		for (int k = 4; k < nh; ++k) { int4 h = s.hoist[k]; sum += abs(h.z + h.y * d); }
+		if (PERM) {
+			const int dx = xv - d;
+			const int2* row = ell + (size_t)j * stride;
+			for (int k = 0; k < stride; ++k) {
+				const int2 e = __ldg(row + k);
+				const int4 st = s.cs[ell_ctr(e.x)];
+				if (st.z == 0) sum += abs(st.x + e.y * dx) - st.y;       // partner's own constraint (881-885)
+				else {                                                    // shared with v (872-874)
+					const int4 h = s.hoist[st.z - 1];
+					const int t1 = h.z + h.y * d;
+					sum += abs(t1 + e.y * dx) - abs(t1);
+				}
+			}
+		}
+		if (!ok) sum = GB_INT_MAX;
+		if (out && slot < m.max_candidates) out[slot] = sum;
+		const int cmin = __reduce_min_sync(0xffffffffu, sum);
+		const unsigned okmask = __ballot_sync(0xffffffffu, ok);
+		const unsigned bits = __ballot_sync(0xffffffffu, ok && sum == cmin);
+		ncandidates += __popc(okmask);
+		if (lane == 0) { s.val_key[ch] = cmin; s.val_bits[ch] = bits; }
+	}
+	return lane == 0 ? ncandidates : 0;
+}
+
 template <int T, bool PERM, bool EQ, class WS>
 __device__ inline int evaluate_candidates(const DevModel& m, const WS& s, int v, int nh, int bias, int nchunks_c, int* out)
 {
+	if (EQ) return evaluate_candidates_eq<T, PERM>(m, s, v, nh, bias, nchunks_c, out);
 	typedef Group<T> G;
 	MV mv(m);
 	const int lane = threadIdx.x & 31;
