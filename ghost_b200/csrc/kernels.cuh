@@ -173,6 +173,9 @@ __device__ inline void random_permutations(const DevModel& m, const WS& s, Rng& 
 struct WalkerRegs {
 	int must_compute, ncand, n_tabu, local_moves, cur_sat, best_sat, resume_pending, cand_max;
 	int resets;                 // low bits of the reset counter, for the restart test
+	int best_pending;           // best_x is the CURRENT assignment but has not been written out yet:
+	                            // the copy (final_solution, search_unit.hpp:1172-1187) is deferred
+	                            // until the assignment is about to change in a non-improving way
 	long long cur_opt, best_opt, obj_sum;
 	long long iterations;
 };
@@ -197,14 +200,14 @@ __device__ inline void initialize_data_structures(const DevModel& m, const WS& s
 	r.must_compute = 1;
 	for (int v = G::tid(); v < m.V; v += T) s.tabu[v] = 0;
 	r.cur_sat = recompute_all<T>(m, s, s.red);
-	if (r.best_sat > r.cur_sat) { r.best_sat = r.cur_sat; copy_best<T>(m, s, best_x); }
+	if (r.best_sat > r.cur_sat) { r.best_sat = r.cur_sat; r.best_pending = 1; }
 	if (m.objective != GHOST_OBJ_NONE) {
 		long long part = 0;
 		for (int v = G::tid(); v < m.V; v += T) part += (long long)mv.obj_coef(v) * s.x[v];
 		r.obj_sum = G::sum64(part, s.red + 16);
 		if (r.cur_sat == 0) {
 			r.cur_opt = internal_cost(m, r.obj_sum);
-			if (r.best_opt > r.cur_opt) { r.best_opt = r.cur_opt; copy_best<T>(m, s, best_x); }
+			if (r.best_opt > r.cur_opt) { r.best_opt = r.cur_opt; r.best_pending = 1; }
 		} else r.cur_opt = GB_I64_MAX;
 	}
 	G::sync();
@@ -225,7 +228,7 @@ __device__ inline void set_initial_configuration(const DevModel& m, const WS& s,
 		current = recompute_all<T>(m, s, s.red);
 		if (best_so_far > current) {
 			best_so_far = current;
-			if (r.best_sat > best_so_far) { r.best_sat = best_so_far; copy_best<T>(m, s, best_x); }
+			if (r.best_sat > best_so_far) { r.best_sat = best_so_far; copy_best<T>(m, s, best_x); r.best_pending = 0; }
 			for (int v = G::tid(); v < m.V; v += T) s.tabu[v] = s.x[v];
 		}
 		G::sync();
@@ -250,9 +253,10 @@ __device__ inline void initialize_variable_values(const DevModel& m, const WS& s
 
 // SearchUnit::local_move (search_unit.hpp:516-541)
 template <int T, class WS>
-__device__ inline void local_move(const DevModel& m, const WS& s, WalkerRegs& r, const SearchParams& p, int v, int new_value, int delta)
+__device__ inline void local_move(const DevModel& m, const WS& s, WalkerRegs& r, const SearchParams& p, int* best_x, int v, int new_value, int delta)
 {
 	MV mv(m);
+	if (r.best_pending && delta >= 0) { copy_best<T>(m, s, best_x); r.best_pending = 0; }
 	++r.local_moves;
 	r.cur_sat += delta;
 	if (Group<T>::tid() == 0) { s.tabu[v] = p.tabu_selected + r.local_moves; s.counters[K_MOVES] += 1; }
@@ -298,7 +302,7 @@ search_kernel(const DevModel m, const WalkerLayout L, const SearchParams p)
 	r.must_compute = gs->must_compute; r.ncand = gs->ncand; r.n_tabu = gs->n_tabu; r.local_moves = gs->local_moves;
 	r.cur_sat = gs->cur_sat; r.best_sat = gs->best_sat; r.resume_pending = gs->resume_pending; r.cand_max = gs->cand_max;
 	r.cur_opt = gs->cur_opt; r.best_opt = gs->best_opt; r.obj_sum = gs->obj_sum;
-	r.iterations = gs->k.search_iterations; r.resets = (int)gs->k.resets;
+	r.iterations = gs->k.search_iterations; r.resets = (int)gs->k.resets; r.best_pending = 0;
 	int done = gs->done;
 	if (tid == 0) {
 		const long long* k = reinterpret_cast<const long long*>(&gs->k);
@@ -314,7 +318,7 @@ search_kernel(const DevModel m, const WalkerLayout L, const SearchParams p)
 		G::sync();
 		initialize_variable_values<T>(m, s, r, rng, p, best_x);
 		initialize_data_structures<T>(m, s, r, best_x);
-		copy_best<T>(m, s, best_x);
+		r.best_pending = 1; // search_unit.hpp:714-717: final_solution = the initial assignment
 		done = !(r.best_sat > 0 || (r.best_sat == 0 && optimization));
 	} else {
 		const int4* src = reinterpret_cast<const int4*>(gstate);
@@ -343,6 +347,7 @@ search_kernel(const DevModel m, const WalkerLayout L, const SearchParams p)
 			// SearchUnit::reset (search_unit.hpp:333-367)
 			++r.resets;
 			if (tid == 0) s.counters[K_RESETS] += 1;
+			if (r.best_pending) { copy_best<T>(m, s, best_x); r.best_pending = 0; G::sync(); }
 			if (p.restart_threshold > 0 && (r.resets % p.restart_threshold == 0)) {
 				if (tid == 0) s.counters[K_RESTARTS] += 1;
 				initialize_variable_values<T>(m, s, r, rng, p, best_x);
@@ -381,7 +386,7 @@ search_kernel(const DevModel m, const WalkerLayout L, const SearchParams p)
 
 			int plateau = 0, local_min = 0;
 			if (gmin < 0) { // search_unit.hpp:1042-1050
-				local_move<T>(m, s, r, p, v, new_value, gmin);
+				local_move<T>(m, s, r, p, best_x, v, new_value, gmin);
 				if (optimization) r.cur_opt = internal_cost(m, r.obj_sum);
 				trace_branch = 1;
 			} else if (gmin == 0) {
@@ -392,7 +397,7 @@ search_kernel(const DevModel m, const WalkerLayout L, const SearchParams p)
 						obj2 = r.obj_sum + (long long)mv.obj_coef(v) * (xj - xv) + (long long)mv.obj_coef(new_value) * (xv - xj);
 					} else obj2 = r.obj_sum + (long long)mv.obj_coef(v) * (new_value - s.x[v]);
 					long long cand_opt = internal_cost(m, obj2);
-					if (r.cur_opt > cand_opt) { local_move<T>(m, s, r, p, v, new_value, 0); r.cur_opt = cand_opt; trace_branch = 2; }
+					if (r.cur_opt > cand_opt) { local_move<T>(m, s, r, p, best_x, v, new_value, 0); r.cur_opt = cand_opt; trace_branch = 2; }
 					else if (r.cur_opt == cand_opt) plateau = 1;
 					else local_min = 1;
 				} else plateau = 1; // 1136-1145
@@ -404,7 +409,7 @@ search_kernel(const DevModel m, const WalkerLayout L, const SearchParams p)
 					r.must_compute = 1;
 					trace_branch = 4;
 				} else {
-					local_move<T>(m, s, r, p, v, new_value, 0);
+					local_move<T>(m, s, r, p, best_x, v, new_value, 0);
 					if (tid == 0) s.counters[K_PLATEAU] += 1;
 					trace_branch = 3;
 				}
@@ -421,8 +426,8 @@ search_kernel(const DevModel m, const WalkerLayout L, const SearchParams p)
 			if (PERM) unmark_variable<T>(m, s, v);
 
 			// search_unit.hpp:1166-1188
-			if (r.best_sat > r.cur_sat) { r.best_sat = r.cur_sat; copy_best<T>(m, s, best_x); }
-			else if (optimization && r.cur_sat == 0 && r.best_opt > r.cur_opt) { r.best_opt = r.cur_opt; copy_best<T>(m, s, best_x); }
+			if (r.best_sat > r.cur_sat) { r.best_sat = r.cur_sat; r.best_pending = 1; }
+			else if (optimization && r.cur_sat == 0 && r.best_opt > r.cur_opt) { r.best_opt = r.cur_opt; r.best_pending = 1; }
 			G::sync();
 		}
 		if (p.trace && w == p.trace_walker && tid == 0) {
@@ -439,6 +444,7 @@ search_kernel(const DevModel m, const WalkerLayout L, const SearchParams p)
 	}
 
 	// persist
+	if (r.best_pending) { copy_best<T>(m, s, best_x); r.best_pending = 0; }
 	G::sync();
 	{
 		int4* dst = reinterpret_cast<int4*>(gstate);

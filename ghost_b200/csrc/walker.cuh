@@ -514,7 +514,12 @@ __device__ inline int hoist_variable(const DevModel& m, const WS& s, int v, int*
 		}
 		if (writer) {
 			s.hoist[nh] = h;
-			if (m.permutation) s.mark_of(c) = nh + 1;
+			if (m.permutation) {
+				// mark + the selected variable's coefficient next to the constraint state: the swap
+				// partner's loop reads one int4 and needs no second lookup for a shared constraint
+				int* st = reinterpret_cast<int*>(s.cs + c);
+				st[2] = nh + 1; st[3] = e.y;
+			}
 		}
 		++nh;
 	}
@@ -528,7 +533,7 @@ __device__ inline void unmark_variable(const DevModel& m, const WS& s, int v)
 	const int2* row = mv.ell_row(v);
 	for (int k = Group<T>::tid(); k < m.ell_stride; k += T) {
 		int c = ell_ctr(__ldg(row + k).x);
-		if (c != m.C) s.mark_of(c) = 0;
+		if (c != m.C) { int* st = reinterpret_cast<int*>(s.cs + c); st[2] = 0; st[3] = 0; }
 	}
 }
 
@@ -639,20 +644,23 @@ __device__ inline int evaluate_candidates_eq(const DevModel& m, const WS& s, int
 			d = mv.dom_value(v, min(slot, nslots - 1));
 			ok = ok && d != xv;                              // search_unit.hpp:833
 		}
-		int sum = bias + abs(b0 + a0 * d) + abs(b1 + a1 * d) + abs(b2 + a2 * d) + abs(b3 + a3 * d);
-		for (int k = 4; k < nh; ++k) { int4 h = s.hoist[k]; sum += abs(h.z + h.y * d); }
+		int sum = bias + abs(b0 + a0 * d) + abs(b1 + a1 * d);
+		if (nh > 2) {
+			sum += abs(b2 + a2 * d) + abs(b3 + a3 * d);
+			for (int k = 4; k < nh; ++k) { int4 h = s.hoist[k]; sum += abs(h.z + h.y * d); }
+		}
 		if (PERM) {
 			const int dx = xv - d;
 			const int2* row = ell + (size_t)j * stride;
 			for (int k = 0; k < stride; ++k) {
 				const int2 e = __ldg(row + k);
 				const int4 st = s.cs[ell_ctr(e.x)];
-				if (st.z == 0) sum += abs(st.x + e.y * dx) - st.y;       // partner's own constraint (881-885)
-				else {                                                    // shared with v (872-874)
-					const int4 h = s.hoist[st.z - 1];
-					const int t1 = h.z + h.y * d;
-					sum += abs(t1 + e.y * dx) - abs(t1);
-				}
+				// st = {T, error, mark, a_v}.  Partner's own constraint (mark 0, a_v 0; 881-885):
+				//   |T + a_j*dx| - error.  Shared with v (872-874): the hoisted single-variable term
+				//   |T - a_v*dx| is replaced by the two-variable one |T - a_v*dx + a_j*dx|.
+				const int t1 = st.x - st.w * dx;
+				const int sub = st.z ? abs(t1) : st.y;
+				sum += abs(t1 + e.y * dx) - sub;
 			}
 		}
 		if (!ok) sum = GB_INT_MAX;
