@@ -314,12 +314,14 @@ WalkerLayout LoweredModel::layout(int /*threads_per_walker*/, int nreset) const
 
 int LoweredModel::default_threads_per_walker() const
 {
-	// One warp per walker for small models; a CTA per walker once one iteration's candidate set
-	// (or the variable scan) no longer fits a handful of warp passes.
+	// One warp per walker is the throughput optimum as long as an iteration is a few dozen warp
+	// passes (measured on the magic-square 30x30 benchmark: 32 > 64 > 128 threads per walker, the
+	// serial part of an iteration is not replicated across warps); wider groups only when one
+	// iteration's candidate set (or the variable scan) is thousands of slots.
 	int work = std::max(dev.max_candidates, dev.V);
-	if (work <= 256) return 32;
-	if (work <= 512) return 64;
-	if (work <= 2048) return 128;
+	if (work <= 1024) return 32;
+	if (work <= 4096) return 64;
+	if (work <= 16384) return 128;
 	return 256;
 }
 

@@ -36,14 +36,17 @@ __global__ void __launch_bounds__(1024) smem_kernel(int iters, int* sink)
 	__syncthreads();
 	int acc0 = 0, acc1 = 0, acc2 = 0, acc3 = 0;
 	int idx = threadIdx.x;
+	// volatile: the addresses repeat with period 2, so without it the compiler merges half the loads
+	// (the first version of this benchmark reported twice the real bandwidth that way)
+	const volatile int* vb = buf;
 #pragma unroll 1
 	for (int i = 0; i < iters; ++i) {
 #pragma unroll
 		for (int u = 0; u < 4; ++u) {
-			acc0 += buf[(idx) & 8191];
-			acc1 += buf[(idx + 1024) & 8191];
-			acc2 += buf[(idx + 2048) & 8191];
-			acc3 += buf[(idx + 3072) & 8191];
+			acc0 += vb[(idx) & 8191];
+			acc1 += vb[(idx + 1024) & 8191];
+			acc2 += vb[(idx + 2048) & 8191];
+			acc3 += vb[(idx + 3072) & 8191];
 			idx += 4096;
 		}
 	}

@@ -14,7 +14,16 @@ def random_assignment(desc: ModelDesc, rng: np.random.Generator):
     """Permutation problems: a shuffle of the start values; otherwise one value per domain."""
     if desc.permutation_problem:
         x = np.array(desc.start_values, dtype=np.int32)
-        rng.shuffle(x)
+        doms = [set(d) for d in desc.domains]
+        if all(d == doms[0] for d in doms):
+            rng.shuffle(x)
+            return x
+        # different domains: random swaps that keep every value inside its variable's domain
+        n = len(x)
+        for _ in range(4 * n):
+            i, j = int(rng.integers(0, n)), int(rng.integers(0, n))
+            if i != j and int(x[i]) in doms[j] and int(x[j]) in doms[i]:
+                x[i], x[j] = x[j], x[i]
         return x
     return np.array([d[rng.integers(0, len(d))] for d in desc.domains], dtype=np.int32)
 
