@@ -25,6 +25,8 @@ class GhostError(RuntimeError):
 
 
 OK, ERR_INVALID, ERR_UNSUPPORTED, ERR_CUDA, ERR_NOMEM = 0, -1, -2, -3, -4
+NOALLOC_SCRATCH_BYTES = 32 * 1024 * 1024   # GHOST_B200_NOALLOC_SCRATCH_BYTES
+SUMMARY_WORDS = 10                         # GhostWalkerSummary as int64: best_sat, best_opt, 8 counters
 
 
 def _load():
@@ -57,6 +59,7 @@ def _load():
     lib.ghost_b200_search_trace.argtypes = [vp, vp, i32, C.POINTER(i32)]
     lib.ghost_b200_search_export_key.argtypes = [vp, vp, vp]
     lib.ghost_b200_microbench.argtypes = [C.POINTER(C.c_double), C.POINTER(C.c_double)]
+    lib.ghost_b200_search_noalloc.argtypes = [vp, C.POINTER(GhostSearchOptsStruct), i32, i32, vp, vp, vp]
     return lib
 
 
@@ -136,6 +139,15 @@ class Model:
 
     def begin(self, opts: GhostSearchOptsStruct):
         return Search(self, opts)
+
+    def search_noalloc(self, opts: GhostSearchOptsStruct, epochs, iterations_per_epoch, d_best_x, d_summary=None,
+                       stream=0):
+        """ghost_b200_search_noalloc: the search with its walker pool in the library's built-in
+        fixed array, for callers that must not allocate device memory.  d_best_x / d_summary are
+        DEVICE pointers the caller owns ([W][V] int32, [W] SUMMARY_WORDS int64); asynchronous on
+        `stream`.  Calls that overlap on the GPU race on the shared array."""
+        _check(lib.ghost_b200_search_noalloc(self.h, C.byref(opts), int(epochs), int(iterations_per_epoch),
+                                             d_best_x, d_summary, stream))
 
 
 def _result_dict(res, sol):

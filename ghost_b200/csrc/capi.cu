@@ -476,3 +476,7 @@ extern "C" int ghost_b200_search(GhostModel* gm, const GhostSearchOpts* opts, Gh
 	ghost_b200_search_end(s);
 	return rc;
 }
+
+// ---- private hooks for noalloc.cu (declared in noalloc_internal.h) ------------------------------
+const ghost_b200::LoweredModel* ghost_b200_internal_lowered(const GhostModel* model) { return &model->low; }
+void ghost_b200_internal_set_error(int code, const char* message) { set_error(code, message); }

@@ -222,6 +222,44 @@ int ghost_b200_search_walkers(GhostSearch* search, int32_t* best_x, int64_t* bes
  * {iteration, variable, new value, branch, #candidates, min conflict, current sat error, 0}. */
 int ghost_b200_search_trace(GhostSearch* search, int32_t* rows, int32_t cap, int32_t* len);
 
+/* ---- search without any allocation -------------------------------------------------------------
+ * No counterpart in the reference (its SearchUnits live on the host heap; nothing there maps to
+ * device memory management).
+ *
+ * For hosts that may not allocate on their hot path: a game or robotics loop that calls the solver
+ * every frame with a millisecond budget (cudaMalloc/cudaFree can stall the whole device and take
+ * unbounded time), or a process whose device memory was handed out once at start-up by an
+ * engine-wide memory manager, so that a later cudaMalloc would simply fail.
+ * ghost_b200_search_begin() allocates the walker pool; this call runs the same search with the pool
+ * inside a fixed array compiled into the library, and performs no cudaMalloc / cudaFree / other
+ * allocating call.
+ *
+ * What the caller passes: the model handle and options (number_walkers must be > 0), how many
+ * epochs of how many iterations to run, and two DEVICE output buffers it owns:
+ *   d_best_x  [number_walkers][V] int32 — each walker's best assignment;
+ *   d_summary [number_walkers]          — best errors and counters of each walker (may be NULL).
+ * The work is queued on `stream` (a cudaStream_t passed as void*) and the call returns without
+ * synchronising; read the outputs after synchronising that stream.
+ *
+ * Limits and sharing:
+ *  - the built-in array is GHOST_B200_NOALLOC_SCRATCH_BYTES on every GPU that loads the library,
+ *    for the life of the process; the lowered model + number_walkers walker states must fit in it,
+ *    otherwise the call returns GHOST_B200_ERR_UNSUPPORTED with the sizes in the message;
+ *  - the first call on a device looks up the array's device address (no allocation, but a runtime
+ *    query): make that first call before starting any stream capture;
+ *  - all calls on a device share the one array, which keeps the previous call's walkers; each call
+ *    re-initialises the population, and two calls whose GPU work overlaps race on it — issue them
+ *    one after the other (same stream, or synchronise in between). */
+#define GHOST_B200_NOALLOC_SCRATCH_BYTES (32u * 1024u * 1024u)
+typedef struct GhostWalkerSummary {
+	int64_t best_sat;             /* INT32_MAX = none yet                                      */
+	int64_t best_opt;             /* INT64_MAX = none yet; internal sign (negated for Maximize) */
+	GhostCounters counters;
+} GhostWalkerSummary;
+int ghost_b200_search_noalloc(GhostModel* model, const GhostSearchOpts* opts, int32_t epochs,
+                              int32_t iterations_per_epoch, int32_t* d_best_x, GhostWalkerSummary* d_summary,
+                              void* stream);
+
 /* Measured roofline denominators of the move-evaluation kernel on the current device (no reference
  * counterpart): SM integer issue rate in lane-ops/s and conflict-free shared-memory bandwidth in
  * bytes/s, each from a short CUDA-event-timed microbenchmark. */
