@@ -125,11 +125,15 @@ def reference_arm(args):
     from ghost_b200 import problems
     desc = problems.by_name(args.workload)
     cores = physical_cores()
-    sample_s = args.ref_seconds
-    for _ in range(min(args.warmup, 1)):
-        run_reference_sample(desc, min(1.0, sample_s), cores)
+    # Each fast_search call of the reference first samples 10 start configurations, which alone costs
+    # seconds on this model (random_permutations copies a 900-value domain twice per pair,
+    # search_unit.hpp:219-235), so a sample shorter than ~10 s measures only that.  The K steps are
+    # therefore mapped on at most `ref-budget` seconds of fast_search calls of >= 12 s each.
+    budget = min(args.steps * args.ref_seconds, args.ref_budget)
+    n_runs = max(1, min(args.steps, int(budget // 12.0)))
+    sample_s = max(12.0, budget / n_runs)
     evals, iters, secs = 0.0, 0.0, 0.0
-    for _ in range(args.steps):
+    for _ in range(n_runs):
         r = run_reference_sample(desc, sample_s, cores)
         if r is None:
             print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref is not built and /root/reference is not mounted"}))
@@ -143,7 +147,8 @@ def reference_arm(args):
         "config": {"workload": args.workload, "walkers": cores, "parallelism": f"{cores} host threads (parallel_runs)"},
         "walker_iters_per_sec": iters / secs,
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "reference",
-                         "sample": f"{args.steps} x {sample_s:g}s of Solver::fast_search, parallel_runs=true, {cores} threads"},
+                         "sample": f"{n_runs} x {sample_s:g}s of Solver::fast_search (initial sampling included), "
+                                   f"parallel_runs=true, {cores} threads"},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     print(json.dumps(line))
@@ -153,14 +158,15 @@ def reference_arm(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=100)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default=WORKLOAD)
     ap.add_argument("--epoch", type=int, default=64, help="loop passes per walker per step (one kernel launch)")
     ap.add_argument("--walkers", type=int, default=0, help="walkers per GPU (0: fill the GPU)")
     ap.add_argument("--threads-per-walker", type=int, default=0)
-    ap.add_argument("--ref-seconds", type=float, default=5.0)
+    ap.add_argument("--ref-seconds", type=float, default=12.0)
+    ap.add_argument("--ref-budget", type=float, default=60.0, help="cap on the reference arm's total CPU time")
     ap.add_argument("--cpu-seconds", type=float, default=10.0)
     ap.add_argument("--e2e-seconds", type=float, default=1.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -265,6 +271,15 @@ def main():
                  "frac": evals_rank * SMEM_BYTES_PER_EVAL / smem_peak, "algorithmic_bytes_per_eval": SMEM_BYTES_PER_EVAL},
         "traffic": None,
     }
+    try:
+        # dram__bytes_read.sum + dram__bytes_write.sum of one `ncu --set full` capture of this kernel on this
+        # workload (profiles/r1_search_kernel_ncu.txt); per launch
+        tr = json.load(open(os.path.join(ROOT, "profiles", "r1_traffic.json")))
+        if args.workload == WORKLOAD and W == 2960 and args.epoch == 64:
+            roofline["traffic"] = tr["dram_bytes_per_launch"]
+            roofline["traffic_source"] = tr["source"]
+    except Exception:
+        pass
     try:
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
         hbm_peak, src = float(peaks["hbm_gbs"]), "MEASURED_PEAKS.json"

@@ -34,8 +34,9 @@ __device__ __forceinline__ unsigned long long quality_key(bool optimization, int
 {
 	unsigned long long q;
 	if (!optimization) q = (unsigned long long)(unsigned)best_sat;
-	else if (best_sat > 0 || best_opt == GB_I64_MAX) q = (1ULL << 39) + (unsigned long long)(unsigned)best_sat;
-	else q = (unsigned long long)(best_opt + (1LL << 38));
+	// the key stays below 2^63 so that it can also travel as a signed 64-bit integer (NCCL / torch)
+	else if (best_sat > 0 || best_opt == GB_I64_MAX) q = (1ULL << 38) + (unsigned long long)(unsigned)best_sat;
+	else q = (unsigned long long)(best_opt + (1LL << 37));
 	return (q << 24) | (unsigned long long)(walker & 0xFFFFFF);
 }
 

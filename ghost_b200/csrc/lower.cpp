@@ -192,7 +192,8 @@ int lower_model(const GhostModelDesc* d, LoweredModel* out, std::string* why)
 			obj_coef[v] += static_cast<int32_t>(a);
 			bound += std::llabs((long long)a) * std::max(std::llabs((long long)dom_lo[v]), std::llabs((long long)dom_vals[dom_off[v + 1] - 1]));
 		}
-		if (bound >= (1LL << 62)) return fail(GHOST_B200_ERR_UNSUPPORTED, "objective magnitude too large");
+		// the packed best-key (quality << 24 | walker) keeps 38 bits for a solved COP's cost
+		if (bound >= (1LL << 37)) return fail(GHOST_B200_ERR_UNSUPPORTED, "objective magnitude beyond 2^37");
 	}
 
 	// ---- blob
