@@ -268,6 +268,10 @@ extern "C" int ghost_b200_search_begin(GhostModel* gm, const GhostSearchOpts* op
 	}
 	s->walkers = s->opts.number_walkers;
 	if (s->walkers >= (1 << 24)) { delete s; return set_error(GHOST_B200_ERR_INVALID, "at most 2^24-1 walkers per device"); }
+	if (s->opts.tabu_time_local_min > 30000 || s->opts.tabu_time_selected > 30000) {
+		delete s;
+		return set_error(GHOST_B200_ERR_UNSUPPORTED, "tabu times beyond 30000 moves do not fit the 16-bit tabu list of the GPU walkers");
+	}
 	s->grid = (s->walkers + cfg.walkers_per_cta - 1) / cfg.walkers_per_cta;
 	const size_t W = (size_t)s->walkers;
 #define TRY_OR_END(expr) do { cudaError_t _e = (expr); if (_e != cudaSuccess) { ghost_b200_search_end(s); return set_error(GHOST_B200_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(_e)); } } while (0)

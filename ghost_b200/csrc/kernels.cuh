@@ -174,6 +174,8 @@ __device__ inline void random_permutations(const DevModel& m, const WS& s, Rng& 
 struct WalkerRegs {
 	int must_compute, ncand, n_tabu, local_moves, cur_sat, best_sat, resume_pending, cand_max;
 	int resets;                 // low bits of the reset counter, for the restart test
+	int tabu_base;              // the tabu list stores (tabu_until - tabu_base) in 16 bits; the base moves to
+	                            // local_moves whenever the list is cleared (every reset) or re-based
 	int best_pending;           // best_x is the CURRENT assignment but has not been written out yet:
 	                            // the copy (final_solution, search_unit.hpp:1172-1187) is deferred
 	                            // until the assignment is about to change in a non-improving way
@@ -200,7 +202,8 @@ __device__ inline void initialize_data_structures(const DevModel& m, const WS& s
 	MV mv(m);
 	r.must_compute = 1;
 	for (int v = G::tid(); v < m.V; v += T) s.tabu[v] = 0;
-	r.cur_sat = recompute_all<T>(m, s, s.red);
+	r.tabu_base = r.local_moves;
+	r.cur_sat = recompute_all<T, true>(m, s, s.red);
 	if (r.best_sat > r.cur_sat) { r.best_sat = r.cur_sat; r.best_pending = 1; }
 	if (m.objective != GHOST_OBJ_NONE) {
 		long long part = 0;
@@ -226,15 +229,15 @@ __device__ inline void set_initial_configuration(const DevModel& m, const WS& s,
 	int loops = 0;
 	do {
 		if (m.permutation) random_permutations<T>(m, s, rng, -1); else monte_carlo_sampling<T>(m, s, rng, -1);
-		current = recompute_all<T>(m, s, s.red);
+		current = recompute_all<T, false>(m, s, s.red); // total only: err_var holds the best sample
 		if (best_so_far > current) {
 			best_so_far = current;
 			if (r.best_sat > best_so_far) { r.best_sat = best_so_far; copy_best<T>(m, s, best_x); r.best_pending = 0; }
-			for (int v = G::tid(); v < m.V; v += T) s.tabu[v] = s.x[v];
+			for (int v = G::tid(); v < m.V; v += T) s.err_var[v] = s.x[v];
 		}
 		G::sync();
 	} while (++loops < samplings && current > 0);
-	for (int v = G::tid(); v < m.V; v += T) s.x[v] = s.tabu[v];
+	for (int v = G::tid(); v < m.V; v += T) s.x[v] = s.err_var[v];
 	G::sync();
 }
 
@@ -253,14 +256,14 @@ __device__ inline void initialize_variable_values(const DevModel& m, const WS& s
 }
 
 // SearchUnit::local_move (search_unit.hpp:516-541)
-template <int T, class WS>
-__device__ inline void local_move(const DevModel& m, const WS& s, WalkerRegs& r, const SearchParams& p, int* best_x, int v, int new_value, int delta)
+template <int T, bool PERM, bool EQ, class WS>
+__device__ inline void local_move(const DevModel& m, const WS& s, WalkerRegs& r, const SearchParams& p, int* best_x, int v, int new_value, int delta, int nh)
 {
 	MV mv(m);
 	if (r.best_pending && delta >= 0) { copy_best<T>(m, s, best_x); r.best_pending = 0; }
 	++r.local_moves;
 	r.cur_sat += delta;
-	if (Group<T>::tid() == 0) { s.tabu[v] = p.tabu_selected + r.local_moves; s.counters[K_MOVES] += 1; }
+	if (Group<T>::tid() == 0) { s.tabu[v] = (unsigned short)(p.tabu_selected + r.local_moves - r.tabu_base); s.counters[K_MOVES] += 1; }
 	r.must_compute = 1;
 	if (m.objective != GHOST_OBJ_NONE) {
 		if (m.permutation) {
@@ -269,14 +272,15 @@ __device__ inline void local_move(const DevModel& m, const WS& s, WalkerRegs& r,
 		} else
 			r.obj_sum += (long long)mv.obj_coef(v) * (new_value - s.x[v]);
 	}
-	apply_move<T>(m, s, v, new_value);
+	if (EQ) apply_move_eq<T, PERM>(m, s, v, new_value, nh);
+	else apply_move<T>(m, s, v, new_value);
 }
 
 // =================================================================================================
 // Resident warps per SM the register allocator is asked to leave room for (the walkers' shared
 // memory allows about 20 per SM on the magic-square benchmark model).
 #ifndef GB_WARPS_PER_SM
-#define GB_WARPS_PER_SM 20
+#define GB_WARPS_PER_SM 24
 #endif
 
 template <int T, bool PERM, bool EQ, class XT>
@@ -300,7 +304,7 @@ search_kernel(const DevModel m, const WalkerLayout L, const SearchParams p)
 
 	Rng rng; rng.seed = p.seed; rng.walker = p.first_walker + (unsigned long long)w; rng.next_event = gs->next_event;
 	WalkerRegs r;
-	r.must_compute = gs->must_compute; r.ncand = gs->ncand; r.n_tabu = gs->n_tabu; r.local_moves = gs->local_moves;
+	r.must_compute = gs->must_compute; r.ncand = gs->ncand; r.n_tabu = gs->n_tabu; r.local_moves = gs->local_moves; r.tabu_base = gs->tabu_base;
 	r.cur_sat = gs->cur_sat; r.best_sat = gs->best_sat; r.resume_pending = gs->resume_pending; r.cand_max = gs->cand_max;
 	r.cur_opt = gs->cur_opt; r.best_opt = gs->best_opt; r.obj_sum = gs->obj_sum;
 	r.iterations = gs->k.search_iterations; r.resets = (int)gs->k.resets; r.best_pending = 0;
@@ -339,9 +343,16 @@ search_kernel(const DevModel m, const WalkerLayout L, const SearchParams p)
 			if (stop) break;
 		}
 		++r.iterations;
+		if (r.local_moves - r.tabu_base > 30000) {
+			// keep the 16-bit relative tabu entries in range: re-base them on the current move count
+			const int shift = r.local_moves - r.tabu_base;
+			for (int v = tid; v < m.V; v += T) { int t = (int)s.tabu[v] - shift; s.tabu[v] = (unsigned short)(t > 0 ? t : 0); }
+			r.tabu_base = r.local_moves;
+			G::sync();
+		}
 
 		if (r.must_compute)
-			r.ncand = scan_candidates<T>(m, s, L.nchunks_v, r.local_moves, optimization && r.cur_sat == 0, s.red, &r.cand_max, &r.n_tabu);
+			r.ncand = scan_candidates<T>(m, s, L.nchunks_v, r.local_moves - r.tabu_base, optimization && r.cur_sat == 0, s.red, &r.cand_max, &r.n_tabu);
 
 		int trace_var = -1, trace_val = 0, trace_branch = 0, trace_ncand = 0, trace_min = 0;
 		if (r.n_tabu >= p.reset_threshold || r.ncand == 0) {
@@ -387,7 +398,7 @@ search_kernel(const DevModel m, const WalkerLayout L, const SearchParams p)
 
 			int plateau = 0, local_min = 0;
 			if (gmin < 0) { // search_unit.hpp:1042-1050
-				local_move<T>(m, s, r, p, best_x, v, new_value, gmin);
+				local_move<T, PERM, EQ>(m, s, r, p, best_x, v, new_value, gmin, nh);
 				if (optimization) r.cur_opt = internal_cost(m, r.obj_sum);
 				trace_branch = 1;
 			} else if (gmin == 0) {
@@ -398,7 +409,7 @@ search_kernel(const DevModel m, const WalkerLayout L, const SearchParams p)
 						obj2 = r.obj_sum + (long long)mv.obj_coef(v) * (xj - xv) + (long long)mv.obj_coef(new_value) * (xv - xj);
 					} else obj2 = r.obj_sum + (long long)mv.obj_coef(v) * (new_value - s.x[v]);
 					long long cand_opt = internal_cost(m, obj2);
-					if (r.cur_opt > cand_opt) { local_move<T>(m, s, r, p, best_x, v, new_value, 0); r.cur_opt = cand_opt; trace_branch = 2; }
+					if (r.cur_opt > cand_opt) { local_move<T, PERM, EQ>(m, s, r, p, best_x, v, new_value, 0, nh); r.cur_opt = cand_opt; trace_branch = 2; }
 					else if (r.cur_opt == cand_opt) plateau = 1;
 					else local_min = 1;
 				} else plateau = 1; // 1136-1145
@@ -406,11 +417,11 @@ search_kernel(const DevModel m, const WalkerLayout L, const SearchParams p)
 
 			if (plateau) { // plateau_management, 545-561
 				if ((int)below(rnd.z, 100u) + 1 <= p.plateau_percent) {
-					if (tid == 0) { s.tabu[v] = p.tabu_local_min + r.local_moves; s.counters[K_FORCE] += 1; }
+					if (tid == 0) { s.tabu[v] = (unsigned short)(p.tabu_local_min + r.local_moves - r.tabu_base); s.counters[K_FORCE] += 1; }
 					r.must_compute = 1;
 					trace_branch = 4;
 				} else {
-					local_move<T>(m, s, r, p, best_x, v, new_value, 0);
+					local_move<T, PERM, EQ>(m, s, r, p, best_x, v, new_value, 0, nh);
 					if (tid == 0) s.counters[K_PLATEAU] += 1;
 					trace_branch = 3;
 				}
@@ -418,7 +429,7 @@ search_kernel(const DevModel m, const WalkerLayout L, const SearchParams p)
 			if (local_min) { // local_minimum_management, 565-582
 				r.must_compute = 0;
 				if (r.ncand == 0) {
-					if (tid == 0) { s.tabu[v] = p.tabu_local_min + r.local_moves; s.counters[K_LOCALMIN] += 1; }
+					if (tid == 0) { s.tabu[v] = (unsigned short)(p.tabu_local_min + r.local_moves - r.tabu_base); s.counters[K_LOCALMIN] += 1; }
 					if (p.tabu_local_min > 0) ++r.n_tabu;
 					trace_branch = 5;
 				} else trace_branch = 6;
@@ -453,7 +464,7 @@ search_kernel(const DevModel m, const WalkerLayout L, const SearchParams p)
 		for (int i = tid; i < L.persist_bytes / 16; i += T) dst[i] = src[i];
 	}
 	if (tid == 0) {
-		gs->initialized = 1; gs->must_compute = r.must_compute; gs->ncand = r.ncand; gs->n_tabu = r.n_tabu;
+		gs->initialized = 1; gs->must_compute = r.must_compute; gs->ncand = r.ncand; gs->n_tabu = r.n_tabu; gs->tabu_base = r.tabu_base;
 		gs->local_moves = r.local_moves; gs->cur_sat = r.cur_sat; gs->best_sat = r.best_sat;
 		gs->resume_pending = r.resume_pending; gs->cand_max = r.cand_max; gs->done = done;
 		gs->cur_opt = r.cur_opt; gs->best_opt = r.best_opt; gs->obj_sum = r.obj_sum;
@@ -487,7 +498,7 @@ eval_kernel(const DevModel m, const WalkerLayout L, int num_walkers, const int* 
 	for (int v = tid; v < m.V; v += T) s.x[v] = assignments[(size_t)w * m.V + v];
 	if (tid == 0) s.cs[m.C] = make_int4(0, 0, 0, 0);
 	G::sync();
-	recompute_all<T>(m, s, s.red);
+	recompute_all<T, true>(m, s, s.red);
 	if (ctr_error) for (int c = tid; c < m.C; c += T) ctr_error[(size_t)w * m.C + c] = s.err_of(c);
 	if (var_error) for (int v = tid; v < m.V; v += T) var_error[(size_t)w * m.V + v] = s.err_var[v];
 	const int v = selected ? selected[w] : -1;

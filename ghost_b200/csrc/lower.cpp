@@ -293,7 +293,7 @@ WalkerLayout LoweredModel::layout(int /*threads_per_walker*/, int nreset) const
 	w.nchunks_c = (m.max_candidates + 31) / 32;
 	w.x = take((m.x16 ? 2 : 4) * m.V);
 	w.err_var = take(4 * m.V);
-	w.tabu = take(4 * m.V);
+	w.tabu = take(2 * m.V);
 	w.cs = take(16 * (m.C + 1)); // + the all-zero dummy constraint that pads the ELL rows
 	w.cand_key = take(4 * w.nchunks_v);
 	w.cand_bits = take(4 * w.nchunks_v);

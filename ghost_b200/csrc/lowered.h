@@ -78,6 +78,7 @@ struct WalkerScalars {
 	int32_t must_compute;
 	int32_t ncand;
 	int32_t n_tabu;
+	int32_t tabu_base;          // local_moves value the 16-bit tabu entries are relative to
 	int32_t local_moves;
 	int32_t cur_sat;
 	int32_t best_sat;

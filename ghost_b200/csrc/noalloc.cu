@@ -146,6 +146,8 @@ extern "C" int ghost_b200_search_noalloc(GhostModel* model, const GhostSearchOpt
 		return fail(GHOST_B200_ERR_UNSUPPORTED, "walker state does not fit in shared memory");
 	const int W = o.number_walkers;
 	if (W >= (1 << 24)) return fail(GHOST_B200_ERR_INVALID, "at most 2^24-1 walkers per device");
+	if (o.tabu_time_local_min > 30000 || o.tabu_time_selected > 30000)
+		return fail(GHOST_B200_ERR_UNSUPPORTED, "tabu times beyond 30000 moves do not fit the 16-bit tabu list of the GPU walkers");
 
 	// carve the static array: [model blob][walker states][walker scalars][stop flag, best key]
 	const size_t blob_bytes = low->blob.size() * sizeof(int32_t);

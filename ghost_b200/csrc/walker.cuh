@@ -100,7 +100,8 @@ struct Group {
 template <class XT>
 struct WST {
 	typedef XT x_type;
-	XT* x; int* err_var; int* tabu;
+	XT* x; int* err_var;
+	unsigned short* tabu;       // tabu_until - tabu_base, 16 bits (see WalkerRegs::tabu_base)
 	int4* cs;                   // per constraint {T = sum - rhs (linear kinds), current error, mark, 0}
 	int* cand_key; unsigned* cand_bits;
 	unsigned* cnt32;            // packed 16-bit counters, two per word
@@ -122,7 +123,7 @@ template <class WS>
 __device__ __forceinline__ WS make_ws(unsigned char* base, const WalkerLayout& L)
 {
 	WS s;
-	s.x = (typename WS::x_type*)(base + L.x); s.err_var = (int*)(base + L.err_var); s.tabu = (int*)(base + L.tabu);
+	s.x = (typename WS::x_type*)(base + L.x); s.err_var = (int*)(base + L.err_var); s.tabu = (unsigned short*)(base + L.tabu);
 	s.cs = (int4*)(base + L.cs);
 	s.cand_key = (int*)(base + L.cand_key); s.cand_bits = (unsigned*)(base + L.cand_bits);
 	s.cnt32 = (unsigned*)(base + L.cnt);
@@ -293,7 +294,7 @@ __device__ inline int constraint_delta(const MV& mv, const WS& s, int c, int va,
 // Flat over the scope entries with a warp-segmented reduction per constraint.
 // Returns the total satisfaction error.  Ends with a group barrier.
 // ---------------------------------------------------------------------------------------------
-template <int T, class WS>
+template <int T, bool PROJECT, class WS>
 __device__ inline int recompute_all(const DevModel& m, const WS& s, int* red)
 {
 	typedef Group<T> G;
@@ -348,7 +349,7 @@ __device__ inline int recompute_all(const DevModel& m, const WS& s, int* red)
 	int part = 0;
 	for (int c = tid; c < m.C; c += T) part += s.err_of(c);
 	int total = G::sum(part, red);
-	for (int v = tid; v < m.V; v += T) {
+	if (PROJECT) for (int v = tid; v < m.V; v += T) {
 		int e = 0;
 		for (int r = mv.row_begin(v), re = mv.row_begin(v + 1); r < re; ++r) e += s.err_of(mv.row_entry(r).x);
 		s.err_var[v] = e;
@@ -444,7 +445,7 @@ __device__ inline int scan_candidates(const DevModel& m, const WS& s, int nchunk
 		int e = -1;
 		bool tabu = false;
 		if (v < m.V) {
-			tabu = s.tabu[v] > local_moves;
+			tabu = (int)s.tabu[v] > local_moves;
 			if (!tabu && ((has_ctr >> lane) & 1u)) e = s.err_var[v];
 		}
 		int cmax = __reduce_max_sync(0xffffffffu, e);
@@ -697,6 +698,79 @@ __device__ inline int evaluate_candidates(const DevModel& m, const WS& s, int v,
 		if (lane == 0) { s.val_key[ch] = cmin; s.val_bits[ch] = bits; }
 	}
 	return lane == 0 ? ncandidates : 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// The update part of a move when every live constraint is a LinearEquationEq (same contract as
+// apply_move below): the affected constraints are the hoisted ones of v plus, for a swap, the
+// partner's own row entries; their new state is T' = T + a*delta and error |T'| — no kind lookups,
+// no CSR walks.  The projection scatter first gathers each affected constraint's scope bounds in one
+// lane each, then broadcasts them, so that the dependent loads of different constraints overlap.
+// ---------------------------------------------------------------------------------------------
+template <int T, bool PERM, class WS>
+__device__ inline void apply_move_eq(const DevModel& m, const WS& s, int v, int new_value, int nh)
+{
+	typedef Group<T> G;
+	MV mv(m);
+	const int tid = G::tid(), lane = threadIdx.x & 31;
+	const int xv = s.x[v];
+	int j = 0, xj = 0;
+	if (PERM) { j = new_value; xj = s.x[j]; }
+	const int nv_new = PERM ? xj : new_value;
+	const int stride = m.ell_stride;
+	const int2* ell = reinterpret_cast<const int2*>(m.blob + m.o.ell);
+	const int naff = nh + (PERM ? stride : 0);
+	for (int k = tid; k < naff; k += T) {
+		int c = -1, delta = 0;
+		if (k < nh) {
+			const int4 h = s.hoist[k];
+			c = h.x >> 8;
+			const int told = s.T_of(c);
+			int tnew = told + h.y * (nv_new - xv);
+			if (PERM)
+				for (int e = 0; e < stride; ++e) {
+					const int2 f = __ldg(ell + (j * stride + e));
+					if (ell_ctr(f.x) == c) { tnew += f.y * (xv - xj); break; } // the partner is in this scope too
+				}
+			delta = abs(tnew) - abs(told);
+			s.T_of(c) = tnew; s.err_of(c) = abs(tnew);
+		} else {
+			const int2 f = __ldg(ell + (j * stride + (k - nh)));
+			const int cc = ell_ctr(f.x);
+			if (cc != m.C && s.mark_of(cc) == 0) { // not padding, not shared with v (handled above)
+				c = cc;
+				const int told = s.T_of(c), tnew = told + f.y * (xv - xj);
+				delta = abs(tnew) - abs(told);
+				s.T_of(c) = tnew; s.err_of(c) = abs(tnew);
+			}
+		}
+		s.upd[2 * k] = c; s.upd[2 * k + 1] = delta;
+	}
+	G::sync();
+	if (naff <= 32) {
+		int myd = 0, myb = 0, mye = 0;
+		if (lane < naff) {
+			const int c = s.upd[2 * lane];
+			myd = s.upd[2 * lane + 1];
+			if (c >= 0 && myd != 0) { myb = mv.scope_begin(c); mye = mv.scope_begin(c + 1); }
+		}
+		for (int k = 0; k < naff; ++k) {
+			const int d = __shfl_sync(0xffffffffu, myd, k), b = __shfl_sync(0xffffffffu, myb, k), e = __shfl_sync(0xffffffffu, mye, k);
+			if (d == 0) continue;
+			for (int i = b + tid; i < e; i += T) atomicAdd(&s.err_var[mv.scope_var(i)], d);
+		}
+	} else {
+		for (int k = 0; k < naff; ++k) {
+			const int c = s.upd[2 * k], d = s.upd[2 * k + 1];
+			if (c < 0 || d == 0) continue;
+			for (int i = mv.scope_begin(c) + tid, e = mv.scope_begin(c + 1); i < e; i += T) atomicAdd(&s.err_var[mv.scope_var(i)], d);
+		}
+	}
+	if (tid == 0) {
+		s.x[v] = nv_new;
+		if (PERM) s.x[j] = xv;
+	}
+	G::sync();
 }
 
 // ---------------------------------------------------------------------------------------------
