@@ -120,8 +120,15 @@ struct WST {
 };
 
 template <class WS>
-__device__ __forceinline__ WS make_ws(unsigned char* base, const WalkerLayout& L)
+__device__ __forceinline__ WS make_ws(unsigned char* base_in, const WalkerLayout& L)
 {
+	// The walker's base is turned into a 32-bit shared-window address and hidden from the optimiser
+	// once: otherwise, with the register cap of the hot loop, the compiler re-derives every array
+	// pointer from threadIdx (S2R + shifts + multiplies, ~7% of all instructions) instead of keeping
+	// one register and adding a constant.
+	unsigned sbase = static_cast<unsigned>(__cvta_generic_to_shared(base_in));
+	asm volatile("" : "+r"(sbase));
+	unsigned char* base = static_cast<unsigned char*>(__cvta_shared_to_generic(sbase));
 	WS s;
 	s.x = (typename WS::x_type*)(base + L.x); s.err_var = (int*)(base + L.err_var); s.tabu = (unsigned short*)(base + L.tabu);
 	s.cs = (int4*)(base + L.cs);
