@@ -115,8 +115,9 @@ struct WST {
 		atomicAdd(&cnt32[idx >> 1], (unsigned)d << ((idx & 1) * 16));
 	}
 	__device__ __forceinline__ int& T_of(int c) const { return reinterpret_cast<int*>(cs + c)[0]; }
-	__device__ __forceinline__ int& err_of(int c) const { return reinterpret_cast<int*>(cs + c)[1]; }
-	__device__ __forceinline__ int& mark_of(int c) const { return reinterpret_cast<int*>(cs + c)[2]; }
+	// field order {T, a_v, error, mark}: the LinearEq evaluation loop needs only the first two
+	__device__ __forceinline__ int& err_of(int c) const { return reinterpret_cast<int*>(cs + c)[2]; }
+	__device__ __forceinline__ int& mark_of(int c) const { return reinterpret_cast<int*>(cs + c)[3]; }
 };
 
 template <class WS>
@@ -446,19 +447,28 @@ __device__ inline int scan_candidates(const DevModel& m, const WS& s, int nchunk
 	MV mv(m);
 	const int lane = threadIdx.x & 31;
 	int ntabu = 0;
-	for (int ch = G::warp(); ch < nchunks_v; ch += G::NW) {
-		int v = ch * 32 + lane;
-		unsigned has_ctr = free_vars_ok ? 0xffffffffu : (unsigned)mv.ld(m.o.has_ctr, ch);
-		int e = -1;
-		bool tabu = false;
-		if (v < m.V) {
-			tabu = (int)s.tabu[v] > local_moves;
-			if (!tabu && ((has_ctr >> lane) & 1u)) e = s.err_var[v];
+	// two chunks per pass, loads first and unconditional (clamped index), so that their latencies overlap
+	for (int ch0 = G::warp(); ch0 < nchunks_v; ch0 += 2 * G::NW) {
+		const int ch1 = ch0 + G::NW;
+		const bool two = ch1 < nchunks_v; // warp-uniform
+		const int v0 = ch0 * 32 + lane, v1 = ch1 * 32 + lane;
+		const int i0 = min(v0, m.V - 1), i1 = min(v1, m.V - 1);
+		const int t0 = s.tabu[i0], t1 = s.tabu[i1];
+		const int p0 = s.err_var[i0], p1 = s.err_var[i1];
+		unsigned h0 = 0xffffffffu, h1 = 0xffffffffu;
+		if (!free_vars_ok) { h0 = (unsigned)mv.ld(m.o.has_ctr, ch0); h1 = two ? (unsigned)mv.ld(m.o.has_ctr, ch1) : 0u; }
+		const bool tabu0 = v0 < m.V && t0 > local_moves, tabu1 = two && v1 < m.V && t1 > local_moves;
+		const int e0 = (v0 < m.V && !tabu0 && ((h0 >> lane) & 1u)) ? p0 : -1;
+		const int e1 = (two && v1 < m.V && !tabu1 && ((h1 >> lane) & 1u)) ? p1 : -1;
+		const int c0 = __reduce_max_sync(0xffffffffu, e0);
+		const int c1 = __reduce_max_sync(0xffffffffu, e1);
+		const unsigned b0 = __ballot_sync(0xffffffffu, e0 == c0 && e0 >= 0);
+		const unsigned b1 = __ballot_sync(0xffffffffu, e1 == c1 && e1 >= 0);
+		ntabu += __popc(__ballot_sync(0xffffffffu, tabu0)) + __popc(__ballot_sync(0xffffffffu, tabu1));
+		if (lane == 0) {
+			s.cand_key[ch0] = c0; s.cand_bits[ch0] = b0;
+			if (two) { s.cand_key[ch1] = c1; s.cand_bits[ch1] = b1; }
 		}
-		int cmax = __reduce_max_sync(0xffffffffu, e);
-		unsigned bits = __ballot_sync(0xffffffffu, e == cmax && e >= 0);
-		ntabu += __popc(__ballot_sync(0xffffffffu, tabu));
-		if (lane == 0) { s.cand_key[ch] = cmax; s.cand_bits[ch] = bits; }
 	}
 	if (T > 32) {
 		if (lane == 0) red[G::warp()] = ntabu;
@@ -507,7 +517,7 @@ __device__ inline int hoist_variable(const DevModel& m, const WS& s, int v, int*
 		if (cls == GB_CLS_LINEAR) {
 			int4 st = s.cs[c];
 			h.y = e.y; h.z = st.x - e.y * xv;
-			bias -= st.y;
+			bias -= st.z;
 		} else if (cls == GB_CLS_ALLDIFF) {
 			int tab = mv.cnt_tab(c);
 			int sub = s.cnt(tab + xv) - 1;
@@ -526,7 +536,7 @@ __device__ inline int hoist_variable(const DevModel& m, const WS& s, int v, int*
 				// mark + the selected variable's coefficient next to the constraint state: the swap
 				// partner's loop reads one int4 and needs no second lookup for a shared constraint
 				int* st = reinterpret_cast<int*>(s.cs + c);
-				st[2] = nh + 1; st[3] = e.y;
+				st[3] = nh + 1; st[1] = e.y;
 			}
 		}
 		++nh;
@@ -541,7 +551,7 @@ __device__ inline void unmark_variable(const DevModel& m, const WS& s, int v)
 	const int2* row = mv.ell_row(v);
 	for (int k = Group<T>::tid(); k < m.ell_stride; k += T) {
 		int c = ell_ctr(__ldg(row + k).x);
-		if (c != m.C) { int* st = reinterpret_cast<int*>(s.cs + c); st[2] = 0; st[3] = 0; }
+		if (c != m.C) { int* st = reinterpret_cast<int*>(s.cs + c); st[1] = 0; st[3] = 0; }
 	}
 }
 
@@ -589,9 +599,9 @@ __device__ __forceinline__ bool candidate_sum(const DevModel& m, const MV& mv, c
 		if (c == m.C) break; // padding
 		int4 st = s.cs[c];
 		int cls = ell_cls(e.x);
-		if (st.z == 0) {
+		if (st.w == 0) {
 			// constraint of the partner only: {j} -> {x_v}  (search_unit.hpp:881-885)
-			if (cls == GB_CLS_LINEAR) sum += linear_error_w(ell_w(e.x), st.x + e.y * dx) - st.y;
+			if (cls == GB_CLS_LINEAR) sum += linear_error_w(ell_w(e.x), st.x + e.y * dx) - st.z;
 			else if (cls == GB_CLS_ALLDIFF) {
 				int tab = mv.cnt_tab(c);
 				sum += s.cnt(tab + xv) - (s.cnt(tab + xj) - 1);
@@ -602,7 +612,7 @@ __device__ __forceinline__ bool candidate_sum(const DevModel& m, const MV& mv, c
 		} else {
 			// both variables in scope: {v,j} -> {x_j,x_v} (search_unit.hpp:872-874); replace the
 			// single-variable delta already added from the hoisted entry
-			const int4 h = s.hoist[st.z - 1];
+			const int4 h = s.hoist[st.w - 1];
 			if (cls == GB_CLS_LINEAR) {
 				int w = ell_w(e.x), t1 = h.z + h.y * xj;
 				sum += linear_error_w(w, t1 + e.y * dx) - linear_error_w(w, t1);
@@ -662,13 +672,12 @@ __device__ inline int evaluate_candidates_eq(const DevModel& m, const WS& s, int
 			const int2* row = ell + (size_t)j * stride;
 			for (int k = 0; k < stride; ++k) {
 				const int2 e = __ldg(row + k);
-				const int4 st = s.cs[ell_ctr(e.x)];
-				// st = {T, error, mark, a_v}.  Partner's own constraint (mark 0, a_v 0; 881-885):
-				//   |T + a_j*dx| - error.  Shared with v (872-874): the hoisted single-variable term
-				//   |T - a_v*dx| is replaced by the two-variable one |T - a_v*dx + a_j*dx|.
-				const int t1 = st.x - st.w * dx;
-				const int sub = st.z ? abs(t1) : st.y;
-				sum += abs(t1 + e.y * dx) - sub;
+				const int2 st = *reinterpret_cast<const int2*>(s.cs + ell_ctr(e.x)); // {T, a_v}
+				// Partner's own constraint (a_v = 0; 881-885): |T + a_j*dx| - |T|, |T| being the current
+				// error of an Eq constraint.  Shared with v (872-874): the hoisted single-variable term
+				// |T - a_v*dx| is replaced by the two-variable one |T - a_v*dx + a_j*dx|.
+				const int t1 = st.x - st.y * dx;
+				sum += abs(t1 + e.y * dx) - abs(t1);
 			}
 		}
 		if (!ok) sum = GB_INT_MAX;
