@@ -100,8 +100,12 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
-def run_reference_sample(desc, seconds, threads, parallel=True):
-    """The unmodified reference (oracle/_ref/ref_bench, built with GHOST_BENCH) on the host cores."""
+def run_reference_sample(desc, seconds, threads, parallel=True, evals_per_evaluated_iteration=None):
+    """The unmodified reference (oracle/_ref/ref_bench, built with GHOST_BENCH) on the host cores.
+    The reference counts iterations and resets (include/solver.hpp:805-822), not candidates: its
+    evaluations are (iterations - resets) x candidates per evaluated iteration, which is exactly V-1 on
+    the permutation benchmarks (every other variable is an eligible partner) and, otherwise, the
+    ratio measured on the same model by the GPU run (or the mean domain size - 1)."""
     from oracle import binding
     if not os.path.exists(binding.REF_BENCH):
         if not binding.build_ref():
@@ -111,7 +115,12 @@ def run_reference_sample(desc, seconds, threads, parallel=True):
     its = rep.get("total_iterations" if parallel else "iterations", 0.0)
     resets = rep.get("total_resets" if parallel else "resets", 0.0)
     t = rep.get("search_time_us", seconds * 1e6) * 1e-6
-    cands = desc.num_variables - 1  # every other variable is an eligible swap partner (all values distinct)
+    if evals_per_evaluated_iteration is not None:
+        cands = evals_per_evaluated_iteration
+    elif desc.permutation_problem:
+        cands = desc.num_variables - 1
+    else:
+        cands = sum(len(d) - 1 for d in desc.domains) / max(1, desc.num_variables)
     return {"evals_per_s": (its - resets) * cands / t, "iters_per_s": its / t, "seconds": t,
             "iterations": its, "resets": resets}
 
@@ -321,7 +330,9 @@ def main():
         # ---- CPU baseline on this box's host cores (N=1 only)
         if world == 1 and not args.no_cpu_baseline:
             cores = physical_cores()
-            r = run_reference_sample(desc, args.cpu_seconds, cores)
+            evaluated = (c1["search_iterations"] - c0["search_iterations"]) - (c1["resets"] - c0["resets"])
+            ratio = None if desc.permutation_problem else (c1["candidates_evaluated"] - c0["candidates_evaluated"]) / max(1, evaluated)
+            r = run_reference_sample(desc, args.cpu_seconds, cores, evals_per_evaluated_iteration=ratio)
             if r is not None:
                 line["cpu_baseline"] = {"value": r["evals_per_s"], "unit": UNIT, "cores": cores, "kind": "reference",
                                         "sample": f"{args.cpu_seconds:g}s of the unmodified reference Solver::fast_search, "

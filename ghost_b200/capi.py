@@ -59,6 +59,8 @@ def _load():
     lib.ghost_b200_search_trace.argtypes = [vp, vp, i32, C.POINTER(i32)]
     lib.ghost_b200_search_export_key.argtypes = [vp, vp, vp]
     lib.ghost_b200_microbench.argtypes = [C.POINTER(C.c_double), C.POINTER(C.c_double)]
+    lib.ghost_b200_search_stop_flag_export.argtypes = [vp, vp]
+    lib.ghost_b200_search_stop_flag_import.argtypes = [vp, vp]
     lib.ghost_b200_search_noalloc.argtypes = [vp, C.POINTER(GhostSearchOptsStruct), i32, i32, vp, vp, vp]
     return lib
 
@@ -177,6 +179,15 @@ class Search:
 
     def export_key(self, d_key, stream=0):
         _check(lib.ghost_b200_search_export_key(self.h, d_key, stream))
+
+    def export_stop_flag(self) -> bytes:
+        buf = C.create_string_buffer(64)
+        _check(lib.ghost_b200_search_stop_flag_export(self.h, buf))
+        return buf.raw
+
+    def import_stop_flag(self, handle: bytes):
+        buf = C.create_string_buffer(bytes(handle), 64)
+        _check(lib.ghost_b200_search_stop_flag_import(self.h, buf))
 
     def request_stop(self):
         _check(lib.ghost_b200_search_request_stop(self.h))

@@ -44,6 +44,7 @@ struct GhostSearch {
 	WalkerScalars* d_scalars = nullptr;
 	int* d_best_x = nullptr;
 	int* d_stop = nullptr;
+	int* d_stop_peer = nullptr;     // another process's stop flag, mapped over NVLink (CUDA IPC); used instead of d_stop when set
 	unsigned long long* d_best_key = nullptr;
 	int* d_trace = nullptr; int* d_trace_len = nullptr; int trace_cap = 0;
 	cudaEvent_t ev0 = nullptr, ev1 = nullptr;
@@ -234,6 +235,7 @@ extern "C" int ghost_b200_eval_moves(GhostModel* gm, int32_t W, const int32_t* x
 extern "C" void ghost_b200_search_end(GhostSearch* s)
 {
 	if (!s) return;
+	if (s->d_stop_peer) cudaIpcCloseMemHandle(s->d_stop_peer);
 	cudaFree(s->d_state); cudaFree(s->d_scalars); cudaFree(s->d_best_x); cudaFree(s->d_stop);
 	cudaFree(s->d_best_key); cudaFree(s->d_trace); cudaFree(s->d_trace_len);
 	if (s->ev0) cudaEventDestroy(s->ev0);
@@ -320,7 +322,7 @@ extern "C" int ghost_b200_search_epoch(GhostSearch* s, int32_t iterations, void*
 	p.nreset = o.number_variables_to_reset; p.nsamplings = o.number_start_samplings;
 	p.stop_on_solution = o.stop_on_first_solution;
 	p.seed = o.seed; p.first_walker = o.first_walker_id;
-	p.state = s->d_state; p.scalars = s->d_scalars; p.best_x = s->d_best_x; p.stop_flag = s->d_stop;
+	p.state = s->d_state; p.scalars = s->d_scalars; p.best_x = s->d_best_x; p.stop_flag = s->d_stop_peer ? s->d_stop_peer : s->d_stop;
 	p.best_key = s->d_best_key;
 	p.trace = s->d_trace; p.trace_cap = s->trace_cap; p.trace_walker = 0; p.trace_len = s->d_trace_len;
 	CUDA_TRY(launch_search(s->T, s->grid, s->block, s->smem, (cudaStream_t)stream, s->model->low.dev, s->layout, p));
@@ -332,7 +334,31 @@ extern "C" int ghost_b200_search_request_stop(GhostSearch* s)
 {
 	if (!s) return set_error(GHOST_B200_ERR_INVALID, "search is null");
 	int one = 1;
-	CUDA_TRY(cudaMemcpy(s->d_stop, &one, sizeof one, cudaMemcpyHostToDevice));
+	CUDA_TRY(cudaMemcpy(s->d_stop_peer ? s->d_stop_peer : s->d_stop, &one, sizeof one, cudaMemcpyDefault));
+	return GHOST_B200_OK;
+}
+
+// One stop flag for the whole job: rank 0 exports its flag, the other ranks map it (peer memory over
+// NVLink) and their walkers poll / set that one word instead of a private one.
+extern "C" int ghost_b200_search_stop_flag_export(GhostSearch* s, unsigned char* handle)
+{
+	if (!s || !handle) return set_error(GHOST_B200_ERR_INVALID, "null argument");
+	static_assert(sizeof(cudaIpcMemHandle_t) == GHOST_B200_IPC_HANDLE_BYTES, "IPC handle size");
+	cudaIpcMemHandle_t h;
+	CUDA_TRY(cudaIpcGetMemHandle(&h, s->d_stop));
+	std::memcpy(handle, &h, sizeof h);
+	return GHOST_B200_OK;
+}
+
+extern "C" int ghost_b200_search_stop_flag_import(GhostSearch* s, const unsigned char* handle)
+{
+	if (!s || !handle) return set_error(GHOST_B200_ERR_INVALID, "null argument");
+	if (s->d_stop_peer) return set_error(GHOST_B200_ERR_INVALID, "a peer stop flag is already mapped");
+	cudaIpcMemHandle_t h;
+	std::memcpy(&h, handle, sizeof h);
+	void* ptr = nullptr;
+	CUDA_TRY(cudaIpcOpenMemHandle(&ptr, h, cudaIpcMemLazyEnablePeerAccess));
+	s->d_stop_peer = static_cast<int*>(ptr);
 	return GHOST_B200_OK;
 }
 

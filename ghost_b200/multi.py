@@ -69,6 +69,18 @@ class Coordinator:
             dist.all_reduce(t, op=dist.ReduceOp.SUM)
         return {n: int(v) for n, v in zip(names, t.tolist())}
 
+    def share_stop_flag(self, search):
+        """Rank 0 exports its stop flag (CUDA IPC), every other rank maps it: one flag for the job,
+        polled by all walkers through NVLink peer memory.  No-op on one rank or without the hooks."""
+        if self.world == 1 or not hasattr(search, "export_stop_flag"):
+            return
+        t = torch.zeros(64, dtype=torch.uint8, device=self.device)
+        if self.rank == 0:
+            t = torch.tensor(list(search.export_stop_flag()), dtype=torch.uint8, device=self.device)
+        dist.broadcast(t, src=0)
+        if self.rank != 0:
+            search.import_stop_flag(bytes(t.cpu().tolist()))
+
     def any_true(self, flag: bool) -> bool:
         t = torch.tensor([1 if flag else 0], dtype=torch.int32, device=self.device)
         if self.world > 1:
@@ -80,6 +92,7 @@ def search_multi(search, coord: Coordinator, optimization: bool, epoch_iteration
                  max_epochs: int = 0, stop_on_first_solution: bool = True):
     """Epoch loop over any object with .epoch(n), .best_key() and .result() (ghost_b200.capi.Search on
     a GPU; a stub in the CPU tests).  Returns (found, winner_rank, best_quality, solution, epochs)."""
+    coord.share_stop_flag(search)
     t0 = time.perf_counter()
     epochs = 0
     quality, winner = INT64_MAX >> KEY_WALKER_BITS, 0

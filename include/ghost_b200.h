@@ -210,6 +210,14 @@ int ghost_b200_search_result(GhostSearch* search, GhostResult* result);
 /* Ask every walker to stop at its next iteration (the analogue of SearchUnit::stop_search,
  * search_unit.hpp:680). */
 int ghost_b200_search_request_stop(GhostSearch* search);
+/* One stop flag for a multi-process job (one process per GPU): the exporting search hands out a CUDA
+ * IPC handle of its flag; a search in another process imports it and from then on polls / sets that
+ * word through peer memory over NVLink, so that the first solution stops every GPU inside the epoch
+ * (the reference's stop_search() to all threads, include/solver.hpp:651-653).  Exchange the 64 handle
+ * bytes with any transport (the drivers here broadcast them with torch.distributed). */
+#define GHOST_B200_IPC_HANDLE_BYTES 64
+int ghost_b200_search_stop_flag_export(GhostSearch* search, unsigned char* handle);
+int ghost_b200_search_stop_flag_import(GhostSearch* search, const unsigned char* handle);
 void ghost_b200_search_end(GhostSearch* search);
 /* Per-walker outputs for tests: best assignment [W][V], best sat error [W], best opt cost [W],
  * iterations [W].  Any pointer may be NULL.  Host memory. */
