@@ -260,6 +260,11 @@ int lower_model(const GhostModelDesc* d, LoweredModel* out, std::string* why)
 	}
 	if (C >= GB_ELL_END) return fail(GHOST_B200_ERR_UNSUPPORTED, "too many constraints");
 	o.ell = put(ell);
+	{
+		std::vector<int32_t> ell_eq(eq_only ? ell.size() : 0);
+		for (size_t i = 0; i + 1 < ell_eq.size(); i += 2) { ell_eq[i] = (ell[i] & 0xFFFFF) * 16; ell_eq[i + 1] = ell[i + 1]; }
+		o.ell_eq = put(ell_eq);
+	}
 	o.has_ctr = put(has_ctr);
 	o.total = static_cast<int>(blob.size());
 

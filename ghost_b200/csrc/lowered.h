@@ -24,6 +24,8 @@ struct BlobOffsets {
 	int cnt_owner;             // [cnt_total] constraint owning count-table slot t
 	int obj_coef;              // dense [V]
 	int ell;                   // [V][ell_stride] int2 rows: {c | cls<<20 | w<<24 | universal<<27, coef|pos}; c=0xFFFFF ends a row
+	int ell_eq;                // same rows for the LinearEq-only evaluation loop: word 0 = byte offset of the
+	                           // constraint's state in shared memory (16 * id), word 1 = coefficient
 	int has_ctr;               // [ceil(V/32)] bit v%32 set iff variable v appears in some constraint
 	int total;
 };

@@ -632,8 +632,9 @@ __device__ __forceinline__ bool candidate_sum(const DevModel& m, const MV& mv, c
 // with linear_equation_eq.cpp:54-57): |T + a*delta| - error per constraint, no kind dispatch, the
 // selected variable's (a, T - a*x_v) pairs held in registers, no end-of-row tests (padded ELL rows),
 // no divergent control flow except the rare "partner shares a constraint with v" case.
-template <int T, bool PERM, class WS>
-__device__ inline int evaluate_candidates_eq(const DevModel& m, const WS& s, int v, int nh, int bias, int nchunks_c, int* out)
+// S = compile-time row length of the padded ELL rows (0: read it at run time)
+template <int T, bool PERM, int S, class WS>
+__device__ inline int evaluate_candidates_eq_s(const DevModel& m, const WS& s, int v, int nh, int bias, int nchunks_c, int* out)
 {
 	typedef Group<T> G;
 	MV mv(m);
@@ -645,38 +646,42 @@ __device__ inline int evaluate_candidates_eq(const DevModel& m, const WS& s, int
 	if (nh > 1) { int4 h = s.hoist[1]; a1 = h.y; b1 = h.z; }
 	if (nh > 2) { int4 h = s.hoist[2]; a2 = h.y; b2 = h.z; }
 	if (nh > 3) { int4 h = s.hoist[3]; a3 = h.y; b3 = h.z; }
-	const int stride = m.ell_stride;
-	const int2* ell = reinterpret_cast<const int2*>(m.blob + m.o.ell);
+	const int stride = S > 0 ? S : m.ell_stride;
+	const int2* ell = reinterpret_cast<const int2*>(m.blob + m.o.ell_eq);
+	const unsigned char* cs_bytes = reinterpret_cast<const unsigned char*>(s.cs);
+	int* const val_key = s.val_key;
+	unsigned* const val_bits = s.val_bits;
+	const int vmax = m.V - 1;
 	int ncandidates = 0;
 	for (int ch = G::warp(); ch < nchunks_c; ch += G::NW) {
 		const int slot = ch * 32 + lane;
 		bool ok = slot < nslots;
 		int d, j = 0;
 		if (PERM) {
-			j = min(slot, m.V - 1);
+			j = min(slot, vmax);
 			ok = ok && j != v;
 			d = s.x[j];
-			ok = ok && d != xv;                              // search_unit.hpp:855-860
 			if (!m.identical_domains) ok = ok && mv.in_domain(v, d) && mv.in_domain(j, xv);
 		} else {
 			d = mv.dom_value(v, min(slot, nslots - 1));
-			ok = ok && d != xv;                              // search_unit.hpp:833
 		}
+		ok = ok && d != xv;                                  // search_unit.hpp:833 / 855-860
 		int sum = bias + abs(b0 + a0 * d) + abs(b1 + a1 * d);
 		if (nh > 2) {
 			sum += abs(b2 + a2 * d) + abs(b3 + a3 * d);
 			for (int k = 4; k < nh; ++k) { int4 h = s.hoist[k]; sum += abs(h.z + h.y * d); }
 		}
 		if (PERM) {
-			const int dx = xv - d;
-			const int2* row = ell + (size_t)j * stride;
+			const int dx = xv - d, ndx = d - xv;
+			const int2* row = ell + j * stride;
+#pragma unroll
 			for (int k = 0; k < stride; ++k) {
-				const int2 e = __ldg(row + k);
-				const int2 st = *reinterpret_cast<const int2*>(s.cs + ell_ctr(e.x)); // {T, a_v}
+				const int2 e = __ldg(row + k);               // {byte offset of the constraint state, a_j}
+				const int2 st = *reinterpret_cast<const int2*>(cs_bytes + e.x); // {T, a_v}
 				// Partner's own constraint (a_v = 0; 881-885): |T + a_j*dx| - |T|, |T| being the current
 				// error of an Eq constraint.  Shared with v (872-874): the hoisted single-variable term
 				// |T - a_v*dx| is replaced by the two-variable one |T - a_v*dx + a_j*dx|.
-				const int t1 = st.x - st.y * dx;
+				const int t1 = st.x + st.y * ndx;
 				sum += abs(t1 + e.y * dx) - abs(t1);
 			}
 		}
@@ -686,9 +691,22 @@ __device__ inline int evaluate_candidates_eq(const DevModel& m, const WS& s, int
 		const unsigned okmask = __ballot_sync(0xffffffffu, ok);
 		const unsigned bits = __ballot_sync(0xffffffffu, ok && sum == cmin);
 		ncandidates += __popc(okmask);
-		if (lane == 0) { s.val_key[ch] = cmin; s.val_bits[ch] = bits; }
+		if (lane == 0) { val_key[ch] = cmin; val_bits[ch] = bits; }
 	}
 	return lane == 0 ? ncandidates : 0;
+}
+
+template <int T, bool PERM, class WS>
+__device__ inline int evaluate_candidates_eq(const DevModel& m, const WS& s, int v, int nh, int bias, int nchunks_c, int* out)
+{
+	if (!PERM) return evaluate_candidates_eq_s<T, PERM, 0>(m, s, v, nh, bias, nchunks_c, out);
+	switch (m.ell_stride) { // warp-uniform: fully unrolled row loops for the usual row lengths
+	case 1: return evaluate_candidates_eq_s<T, PERM, 1>(m, s, v, nh, bias, nchunks_c, out);
+	case 2: return evaluate_candidates_eq_s<T, PERM, 2>(m, s, v, nh, bias, nchunks_c, out);
+	case 3: return evaluate_candidates_eq_s<T, PERM, 3>(m, s, v, nh, bias, nchunks_c, out);
+	case 4: return evaluate_candidates_eq_s<T, PERM, 4>(m, s, v, nh, bias, nchunks_c, out);
+	default: return evaluate_candidates_eq_s<T, PERM, 0>(m, s, v, nh, bias, nchunks_c, out);
+	}
 }
 
 template <int T, bool PERM, bool EQ, class WS>
