@@ -320,6 +320,8 @@ search_kernel(const DevModel m, const WalkerLayout L, const SearchParams p)
 		// search_unit.hpp:708-717
 		r.best_sat = GB_INT_MAX; r.best_opt = GB_I64_MAX; r.cur_opt = GB_I64_MAX;
 		for (int v = tid; v < m.V; v += T) s.x[v] = mv.ld(m.o.start, v);
+		// padding of the scan arrays up to a multiple of 32 variables: tabu for ever, error 0
+		for (int v = m.V + tid; v < L.nchunks_v * 32; v += T) { s.tabu[v] = 0xFFFFu; s.err_var[v] = 0; }
 		G::sync();
 		initialize_variable_values<T>(m, s, r, rng, p, best_x);
 		initialize_data_structures<T>(m, s, r, best_x);
@@ -336,9 +338,9 @@ search_kernel(const DevModel m, const WalkerLayout L, const SearchParams p)
 		if (p.max_iterations > 0 && r.iterations >= p.max_iterations) break;
 		if ((it & 7) == 0) {
 			// stop request (SearchUnit::stop_search_requested, search_unit.hpp:658-664, 728)
-			if (tid == 0) s.red[48] = *reinterpret_cast<volatile int*>(p.stop_flag);
+			if (tid == 0) s.red[8] = *reinterpret_cast<volatile int*>(p.stop_flag);
 			G::sync();
-			int stop = s.red[48];
+			int stop = s.red[8];
 			G::sync();
 			if (stop) break;
 		}
@@ -375,13 +377,17 @@ search_kernel(const DevModel m, const WalkerLayout L, const SearchParams p)
 			const int nh = hoist_variable<T>(m, s, v, &bias);
 			G::sync();
 			if (tid == 0) s.cand_bits[v >> 5] &= ~(1u << (v & 31)); // search_unit.hpp:826-828
-			int mine = evaluate_candidates<T, PERM, EQ>(m, s, v, nh, bias, L.nchunks_c, nullptr);
+			int gmin, nties;
+			int mine = evaluate_candidates<T, PERM, EQ>(m, s, v, nh, bias, L.nchunks_c, nullptr, &gmin, &nties);
 			G::sync();
-			const int ncandidates = G::sum(mine, s.red + 16);
+			const int ncandidates = T == 32 ? mine : G::sum((threadIdx.x & 31) == 0 ? mine : 0, s.red + 16);
 			if (tid == 0) s.counters[K_EVALS] += ncandidates;
 			// AdaptiveSearchValueHeuristic::select_value (adaptive_search_value_heuristic.cpp:43-81)
-			const int gmin = chunks_min(s.val_key, L.nchunks_c);
-			const int nties = gmin == GB_INT_MAX ? 0 : chunks_count(s.val_key, s.val_bits, L.nchunks_c, gmin);
+			if (T > 32) {
+				gmin = chunks_min(s.val_key, L.nchunks_c);
+				nties = chunks_count(s.val_key, s.val_bits, L.nchunks_c, gmin);
+			}
+			if (gmin == GB_INT_MAX) nties = 0;
 			int new_value = v;
 			if (nties > 0) {
 				int k;
@@ -507,7 +513,8 @@ eval_kernel(const DevModel m, const WalkerLayout L, int num_walkers, const int* 
 	int bias;
 	const int nh = hoist_variable<T>(m, s, v, &bias);
 	G::sync();
-	evaluate_candidates<T, PERM, EQ>(m, s, v, nh, bias, L.nchunks_c, out);
+	int gmin, nties;
+	evaluate_candidates<T, PERM, EQ>(m, s, v, nh, bias, L.nchunks_c, out, &gmin, &nties);
 }
 
 } // namespace ghost_b200

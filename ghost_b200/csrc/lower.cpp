@@ -282,6 +282,8 @@ int lower_model(const GhostModelDesc* d, LoweredModel* out, std::string* why)
 	m.has_abs_diff = has_abs_diff ? 1 : 0;
 	m.ell_stride = stride;
 	m.eq_only = eq_only ? 1 : 0;
+	m.all_have_ctr = 1;
+	for (int v = 0; v < V; ++v) if (rows[v].empty()) m.all_have_ctr = 0;
 	m.x16 = (min_value >= -32768 && max_value <= 32767) ? 1 : 0;
 	return GHOST_B200_OK;
 }
@@ -297,8 +299,9 @@ WalkerLayout LoweredModel::layout(int /*threads_per_walker*/, int nreset) const
 	w.nchunks_v = (m.V + 31) / 32;
 	w.nchunks_c = (m.max_candidates + 31) / 32;
 	w.x = take((m.x16 ? 2 : 4) * m.V);
-	w.err_var = take(4 * m.V);
-	w.tabu = take(2 * m.V);
+	const int vpad = w.nchunks_v * 32;   // scan without bounds tests: padded, the padding is always tabu
+	w.err_var = take(4 * vpad);
+	w.tabu = take(2 * vpad);
 	w.cs = take(16 * (m.C + 1)); // + the all-zero dummy constraint that pads the ELL rows
 	w.cand_key = take(4 * w.nchunks_v);
 	w.cand_bits = take(4 * w.nchunks_v);
@@ -310,10 +313,10 @@ WalkerLayout LoweredModel::layout(int /*threads_per_walker*/, int nreset) const
 	w.flags = w.tabu;
 	w.val_key = take(4 * w.nchunks_c);
 	w.val_bits = take(4 * w.nchunks_c);
-	w.hoist = take(4 * 8 * m.max_degree);
+	w.hoist = take(16 * m.max_degree);
 	w.upd = take(4 * 2 * 2 * m.max_degree);
 	w.sample = (8 * std::max(1, nreset) <= 4 * m.V) ? w.err_var : take(4 * 2 * std::max(1, nreset));
-	w.red = take(4 * 64);
+	w.red = take(4 * 32);   // [0,8) per-warp partials, [8] stop-flag broadcast, [16,32) 64-bit partials
 	w.total_bytes = at;
 	return w;
 }

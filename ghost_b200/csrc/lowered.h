@@ -45,6 +45,7 @@ struct DevModel {
 	int has_abs_diff;
 	int ell_stride;            // entries per ELL row (max number of non-static constraints of a variable)
 	int eq_only;               // every constraint is LINEAR_EQ or static: the specialised evaluation applies
+	int all_have_ctr;          // every variable appears in at least one constraint
 	int x16;                   // every domain value fits int16: assignments are stored as shorts
 };
 

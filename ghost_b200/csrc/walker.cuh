@@ -447,19 +447,22 @@ __device__ inline int scan_candidates(const DevModel& m, const WS& s, int nchunk
 	MV mv(m);
 	const int lane = threadIdx.x & 31;
 	int ntabu = 0;
-	// two chunks per pass, loads first and unconditional (clamped index), so that their latencies overlap
+	// The tabu list and the projected errors are padded to a multiple of 32 entries (padding: always
+	// tabu), so a chunk needs no bounds test; two chunks per pass so that their loads overlap.  With one
+	// warp per walker the arg-max and its multiplicity are folded into the same loop.
+	const bool use_mask = !free_vars_ok && !m.all_have_ctr;
+	int worst = -1, ncand = 0;
 	for (int ch0 = G::warp(); ch0 < nchunks_v; ch0 += 2 * G::NW) {
 		const int ch1 = ch0 + G::NW;
 		const bool two = ch1 < nchunks_v; // warp-uniform
-		const int v0 = ch0 * 32 + lane, v1 = ch1 * 32 + lane;
-		const int i0 = min(v0, m.V - 1), i1 = min(v1, m.V - 1);
+		const int i0 = ch0 * 32 + lane, i1 = (two ? ch1 : ch0) * 32 + lane;
 		const int t0 = s.tabu[i0], t1 = s.tabu[i1];
 		const int p0 = s.err_var[i0], p1 = s.err_var[i1];
 		unsigned h0 = 0xffffffffu, h1 = 0xffffffffu;
-		if (!free_vars_ok) { h0 = (unsigned)mv.ld(m.o.has_ctr, ch0); h1 = two ? (unsigned)mv.ld(m.o.has_ctr, ch1) : 0u; }
-		const bool tabu0 = v0 < m.V && t0 > local_moves, tabu1 = two && v1 < m.V && t1 > local_moves;
-		const int e0 = (v0 < m.V && !tabu0 && ((h0 >> lane) & 1u)) ? p0 : -1;
-		const int e1 = (two && v1 < m.V && !tabu1 && ((h1 >> lane) & 1u)) ? p1 : -1;
+		if (use_mask) { h0 = (unsigned)mv.ld(m.o.has_ctr, ch0); h1 = (unsigned)mv.ld(m.o.has_ctr, two ? ch1 : ch0); }
+		const bool tabu0 = t0 > local_moves, tabu1 = two && t1 > local_moves;
+		const int e0 = (!tabu0 && ((h0 >> lane) & 1u)) ? p0 : -1;
+		const int e1 = (two && !tabu1 && ((h1 >> lane) & 1u)) ? p1 : -1;
 		const int c0 = __reduce_max_sync(0xffffffffu, e0);
 		const int c1 = __reduce_max_sync(0xffffffffu, e1);
 		const unsigned b0 = __ballot_sync(0xffffffffu, e0 == c0 && e0 >= 0);
@@ -469,18 +472,24 @@ __device__ inline int scan_candidates(const DevModel& m, const WS& s, int nchunk
 			s.cand_key[ch0] = c0; s.cand_bits[ch0] = b0;
 			if (two) { s.cand_key[ch1] = c1; s.cand_bits[ch1] = b1; }
 		}
+		if (T == 32) {
+			if (c0 > worst) { worst = c0; ncand = __popc(b0); } else if (c0 == worst) ncand += __popc(b0);
+			if (c1 > worst) { worst = c1; ncand = __popc(b1); } else if (c1 == worst) ncand += __popc(b1);
+		}
 	}
+	ntabu -= nchunks_v * 32 - m.V; // the padding entries are tabu by construction
 	if (T > 32) {
 		if (lane == 0) red[G::warp()] = ntabu;
 	}
 	G::sync();
 	if (T > 32) {
-		ntabu = 0;
+		ntabu = (G::NW - 1) * (nchunks_v * 32 - m.V); // the padding was subtracted once per warp
 #pragma unroll
 		for (int w = 0; w < G::NW; ++w) ntabu += red[w];
+		worst = chunks_max(s.cand_key, nchunks_v);
+		ncand = worst >= 0 ? chunks_count(s.cand_key, s.cand_bits, nchunks_v, worst) : 0;
 	}
-	int worst = chunks_max(s.cand_key, nchunks_v);
-	int ncand = worst >= 0 ? chunks_count(s.cand_key, s.cand_bits, nchunks_v, worst) : 0;
+	if (worst < 0) ncand = 0;
 	*worst_out = worst;
 	*ntabu_out = ntabu;
 	return ncand;
@@ -634,7 +643,7 @@ __device__ __forceinline__ bool candidate_sum(const DevModel& m, const MV& mv, c
 // no divergent control flow except the rare "partner shares a constraint with v" case.
 // S = compile-time row length of the padded ELL rows (0: read it at run time)
 template <int T, bool PERM, int S, class WS>
-__device__ inline int evaluate_candidates_eq_s(const DevModel& m, const WS& s, int v, int nh, int bias, int nchunks_c, int* out)
+__device__ inline int evaluate_candidates_eq_s(const DevModel& m, const WS& s, int v, int nh, int bias, int nchunks_c, int* out, int* gmin_out, int* nties_out)
 {
 	typedef Group<T> G;
 	MV mv(m);
@@ -652,7 +661,7 @@ __device__ inline int evaluate_candidates_eq_s(const DevModel& m, const WS& s, i
 	int* const val_key = s.val_key;
 	unsigned* const val_bits = s.val_bits;
 	const int vmax = m.V - 1;
-	int ncandidates = 0;
+	int ncandidates = 0, gmin = GB_INT_MAX, nties = 0;
 	for (int ch = G::warp(); ch < nchunks_c; ch += G::NW) {
 		const int slot = ch * 32 + lane;
 		bool ok = slot < nslots;
@@ -692,33 +701,35 @@ __device__ inline int evaluate_candidates_eq_s(const DevModel& m, const WS& s, i
 		const unsigned bits = __ballot_sync(0xffffffffu, ok && sum == cmin);
 		ncandidates += __popc(okmask);
 		if (lane == 0) { val_key[ch] = cmin; val_bits[ch] = bits; }
+		if (cmin < gmin) { gmin = cmin; nties = __popc(bits); } else if (cmin == gmin) nties += __popc(bits);
 	}
-	return lane == 0 ? ncandidates : 0;
+	*gmin_out = gmin; *nties_out = nties; // complete only when one warp owns the walker (T == 32)
+	return ncandidates;
 }
 
 template <int T, bool PERM, class WS>
-__device__ inline int evaluate_candidates_eq(const DevModel& m, const WS& s, int v, int nh, int bias, int nchunks_c, int* out)
+__device__ inline int evaluate_candidates_eq(const DevModel& m, const WS& s, int v, int nh, int bias, int nchunks_c, int* out, int* gmin_out, int* nties_out)
 {
-	if (!PERM) return evaluate_candidates_eq_s<T, PERM, 0>(m, s, v, nh, bias, nchunks_c, out);
+	if (!PERM) return evaluate_candidates_eq_s<T, PERM, 0>(m, s, v, nh, bias, nchunks_c, out, gmin_out, nties_out);
 	switch (m.ell_stride) { // warp-uniform: fully unrolled row loops for the usual row lengths
-	case 1: return evaluate_candidates_eq_s<T, PERM, 1>(m, s, v, nh, bias, nchunks_c, out);
-	case 2: return evaluate_candidates_eq_s<T, PERM, 2>(m, s, v, nh, bias, nchunks_c, out);
-	case 3: return evaluate_candidates_eq_s<T, PERM, 3>(m, s, v, nh, bias, nchunks_c, out);
-	case 4: return evaluate_candidates_eq_s<T, PERM, 4>(m, s, v, nh, bias, nchunks_c, out);
-	default: return evaluate_candidates_eq_s<T, PERM, 0>(m, s, v, nh, bias, nchunks_c, out);
+	case 1: return evaluate_candidates_eq_s<T, PERM, 1>(m, s, v, nh, bias, nchunks_c, out, gmin_out, nties_out);
+	case 2: return evaluate_candidates_eq_s<T, PERM, 2>(m, s, v, nh, bias, nchunks_c, out, gmin_out, nties_out);
+	case 3: return evaluate_candidates_eq_s<T, PERM, 3>(m, s, v, nh, bias, nchunks_c, out, gmin_out, nties_out);
+	case 4: return evaluate_candidates_eq_s<T, PERM, 4>(m, s, v, nh, bias, nchunks_c, out, gmin_out, nties_out);
+	default: return evaluate_candidates_eq_s<T, PERM, 0>(m, s, v, nh, bias, nchunks_c, out, gmin_out, nties_out);
 	}
 }
 
 template <int T, bool PERM, bool EQ, class WS>
-__device__ inline int evaluate_candidates(const DevModel& m, const WS& s, int v, int nh, int bias, int nchunks_c, int* out)
+__device__ inline int evaluate_candidates(const DevModel& m, const WS& s, int v, int nh, int bias, int nchunks_c, int* out, int* gmin_out, int* nties_out)
 {
-	if (EQ) return evaluate_candidates_eq<T, PERM>(m, s, v, nh, bias, nchunks_c, out);
+	if (EQ) return evaluate_candidates_eq<T, PERM>(m, s, v, nh, bias, nchunks_c, out, gmin_out, nties_out);
 	typedef Group<T> G;
 	MV mv(m);
 	const int lane = threadIdx.x & 31;
 	const int xv = s.x[v];
 	const int nslots = PERM ? m.V : mv.dom_size(v);
-	int ncandidates = 0;
+	int ncandidates = 0, gmin = GB_INT_MAX, nties = 0;
 	for (int ch = G::warp(); ch < nchunks_c; ch += G::NW) {
 		int slot = ch * 32 + lane;
 		int sum = GB_INT_MAX;
@@ -730,8 +741,10 @@ __device__ inline int evaluate_candidates(const DevModel& m, const WS& s, int v,
 		unsigned bits = __ballot_sync(0xffffffffu, ok && sum == cmin);
 		ncandidates += __popc(okmask);
 		if (lane == 0) { s.val_key[ch] = cmin; s.val_bits[ch] = bits; }
+		if (cmin < gmin) { gmin = cmin; nties = __popc(bits); } else if (cmin == gmin) nties += __popc(bits);
 	}
-	return lane == 0 ? ncandidates : 0;
+	*gmin_out = gmin; *nties_out = nties; // complete only when one warp owns the walker (T == 32)
+	return ncandidates;
 }
 
 // ---------------------------------------------------------------------------------------------
