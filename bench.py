@@ -179,6 +179,8 @@ def main():
     ap.add_argument("--cpu-seconds", type=float, default=10.0)
     ap.add_argument("--e2e-seconds", type=float, default=1.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--tts-seeds", type=int, default=9, help="time-to-solution runs (0: skip)")
+    ap.add_argument("--tts-timeout", type=float, default=10.0)
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "ours":
         args.warmup = max(args.warmup, 3)  # timing rule: at least 3 warm-up steps
@@ -284,7 +286,7 @@ def main():
         # dram__bytes_read.sum + dram__bytes_write.sum of one `ncu --set full` capture of this kernel on this
         # workload (profiles/r1_search_kernel_ncu.txt); per launch
         tr = json.load(open(os.path.join(ROOT, "profiles", "r1_traffic.json")))
-        if args.workload == WORKLOAD and W == 2960 and args.epoch == 64:
+        if args.workload == tr.get("workload") and W == tr.get("walkers") and args.epoch == tr.get("epoch_iterations"):
             roofline["traffic"] = tr["dram_bytes_per_launch"]
             roofline["traffic_source"] = tr["source"]
     except Exception:
@@ -327,6 +329,21 @@ def main():
                        "h2d_bytes_per_step": e2e_model_bytes, "d2h_bytes_per_step": d2h,
                        "call": "ghost_b200_search (model_create + upload + walker set-up + search + result)",
                        "seconds": dt, "kernel_launches": r2["kernel_launches"]}
+        # ---- time-to-solution (the third part of BASELINE.json's metric): wall time of the blocking call
+        # from host descriptor to the first walker with satisfaction error 0, median over seeds
+        if world == 1 and args.tts_seeds > 0:
+            times = []
+            for seed in range(args.tts_seeds):
+                m3 = capi.Model(desc)
+                t0 = time.perf_counter()
+                r3 = m3.search(default_opts(seed=5000 + seed, number_walkers=W, threads_per_walker=args.threads_per_walker,
+                                            timeout_us=args.tts_timeout * 1e6, epoch_iterations=16))
+                times.append(time.perf_counter() - t0 if r3["found"] else float("inf"))
+                m3.close()
+            times.sort()
+            line["time_to_solution"] = {"median_s": times[len(times) // 2], "min_s": times[0], "max_s": times[-1],
+                                        "seeds": args.tts_seeds, "solved": sum(t != float("inf") for t in times),
+                                        "call": "ghost_b200_search, stop at the first solution", "timeout_s": args.tts_timeout}
         # ---- CPU baseline on this box's host cores (N=1 only)
         if world == 1 and not args.no_cpu_baseline:
             cores = physical_cores()
