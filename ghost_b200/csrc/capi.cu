@@ -142,7 +142,7 @@ struct LaunchCfg { int T, walkers_per_cta, block; size_t smem; };
 
 static int pick_launch(const GhostModel* gm, const WalkerLayout& L, int requested_T, LaunchCfg* cfg)
 {
-	int T = requested_T > 0 ? requested_T : gm->low.default_threads_per_walker();
+	int T = gm->low.effective_threads_per_walker(requested_T);
 	if (!(T == 32 || T == 64 || T == 128 || T == 256))
 		return set_error(GHOST_B200_ERR_INVALID, "threads_per_walker must be 32, 64, 128 or 256");
 	int wpc = 1;

@@ -263,7 +263,7 @@ __device__ inline void local_move(const DevModel& m, const WS& s, WalkerRegs& r,
 	if (r.best_pending && delta >= 0) { copy_best<T>(m, s, best_x); r.best_pending = 0; }
 	++r.local_moves;
 	r.cur_sat += delta;
-	if (Group<T>::tid() == 0) { s.tabu[v] = (unsigned short)(p.tabu_selected + r.local_moves - r.tabu_base); s.counters[K_MOVES] += 1; }
+	if (Group<T>::tid() == 0) { s.tabu[scan_pos(m, v)] = (unsigned short)(p.tabu_selected + r.local_moves - r.tabu_base); s.counters[K_MOVES] += 1; }
 	r.must_compute = 1;
 	if (m.objective != GHOST_OBJ_NONE) {
 		if (m.permutation) {
@@ -309,6 +309,9 @@ search_kernel(const DevModel m, const WalkerLayout L, const SearchParams p)
 	r.cur_opt = gs->cur_opt; r.best_opt = gs->best_opt; r.obj_sum = gs->obj_sum;
 	r.iterations = gs->k.search_iterations; r.resets = (int)gs->k.resets; r.best_pending = 0;
 	int done = gs->done;
+	ChunkRegs cq, vq;           // T == 32: candidate-variable / candidate-value chunk summaries, lane = chunk
+	cq.key = -1; cq.bits = 0u;
+	int evals_lane = 0;         // candidates evaluated by this lane since the last flush into the counters
 	if (tid == 0) {
 		const long long* k = reinterpret_cast<const long long*>(&gs->k);
 #pragma unroll
@@ -321,7 +324,7 @@ search_kernel(const DevModel m, const WalkerLayout L, const SearchParams p)
 		r.best_sat = GB_INT_MAX; r.best_opt = GB_I64_MAX; r.cur_opt = GB_I64_MAX;
 		for (int v = tid; v < m.V; v += T) s.x[v] = mv.ld(m.o.start, v);
 		// padding of the scan arrays up to a multiple of 32 variables: tabu for ever, error 0
-		for (int v = m.V + tid; v < L.nchunks_v * 32; v += T) { s.tabu[v] = 0xFFFFu; s.err_var[v] = 0; }
+		for (int v = m.V + tid; v < L.nchunks_v * 32; v += T) { s.tabu[v] = 0xFFFFu; s.err_var[v] = 0; s.x[v] = 0; }
 		G::sync();
 		initialize_variable_values<T>(m, s, r, rng, p, best_x);
 		initialize_data_structures<T>(m, s, r, best_x);
@@ -332,6 +335,7 @@ search_kernel(const DevModel m, const WalkerLayout L, const SearchParams p)
 		int4* dst = reinterpret_cast<int4*>(smem_raw + (size_t)local * L.total_bytes);
 		for (int i = tid; i < L.persist_bytes / 16; i += T) dst[i] = src[i];
 		G::sync();
+		if (T == 32 && tid < L.nchunks_v) { cq.key = s.cand_key[tid]; cq.bits = s.cand_bits[tid]; }
 	}
 
 	for (int it = 0; it < p.iterations && !done; ++it) {
@@ -342,6 +346,9 @@ search_kernel(const DevModel m, const WalkerLayout L, const SearchParams p)
 			G::sync();
 			int stop = s.red[8];
 			G::sync();
+			const int tot = T == 32 ? __reduce_add_sync(0xffffffffu, evals_lane) : G::sum(evals_lane, s.red + 16);
+			if (tid == 0) s.counters[K_EVALS] += tot;
+			evals_lane = 0;
 			if (stop) break;
 		}
 		++r.iterations;
@@ -354,7 +361,7 @@ search_kernel(const DevModel m, const WalkerLayout L, const SearchParams p)
 		}
 
 		if (r.must_compute)
-			r.ncand = scan_candidates<T>(m, s, L.nchunks_v, r.local_moves - r.tabu_base, optimization && r.cur_sat == 0, s.red, &r.cand_max, &r.n_tabu);
+			r.ncand = scan_candidates<T>(m, s, L.nchunks_v, r.local_moves - r.tabu_base, optimization && r.cur_sat == 0, s.red, &r.cand_max, &r.n_tabu, cq);
 
 		int trace_var = -1, trace_val = 0, trace_branch = 0, trace_ncand = 0, trace_min = 0;
 		if (r.n_tabu >= p.reset_threshold || r.ncand == 0) {
@@ -371,19 +378,24 @@ search_kernel(const DevModel m, const WalkerLayout L, const SearchParams p)
 		} else {
 			const uint4 rnd = rng.block(rng.next_event++, 0);
 			// UniformVariableHeuristic::select_variable (uniform_variable_heuristic.cpp:38-41)
-			const int v = pick_kth(s.cand_key, s.cand_bits, L.nchunks_v, r.cand_max, (int)below(rnd.x, (uint32_t)r.ncand));
+			const int kv = (int)below(rnd.x, (uint32_t)r.ncand);
+			const int v = T == 32 ? regs_pick_kth(cq, r.cand_max, kv) : pick_kth(s.cand_key, s.cand_bits, L.nchunks_v, r.cand_max, kv);
 			--r.ncand;
 			int bias;
 			const int nh = hoist_variable<T>(m, s, v, &bias);
 			G::sync();
-			if (tid == 0) s.cand_bits[v >> 5] &= ~(1u << (v & 31)); // search_unit.hpp:826-828
+			// search_unit.hpp:826-828
+			if (T == 32) { if (tid == (v >> 5)) cq.bits &= ~(1u << (v & 31)); }
+			else if (tid == 0) s.cand_bits[v >> 5] &= ~(1u << (v & 31));
 			int gmin, nties;
-			int mine = evaluate_candidates<T, PERM, EQ>(m, s, v, nh, bias, L.nchunks_c, nullptr, &gmin, &nties);
+			const int mine = evaluate_candidates<T, PERM, EQ>(m, s, v, nh, bias, L.nchunks_c, nullptr, vq);
+			evals_lane += mine;
 			G::sync();
-			const int ncandidates = T == 32 ? mine : G::sum((threadIdx.x & 31) == 0 ? mine : 0, s.red + 16);
-			if (tid == 0) s.counters[K_EVALS] += ncandidates;
 			// AdaptiveSearchValueHeuristic::select_value (adaptive_search_value_heuristic.cpp:43-81)
-			if (T > 32) {
+			if (T == 32) {
+				gmin = __reduce_min_sync(0xffffffffu, vq.key);
+				nties = regs_count(vq, gmin);
+			} else {
 				gmin = chunks_min(s.val_key, L.nchunks_c);
 				nties = chunks_count(s.val_key, s.val_bits, L.nchunks_c, gmin);
 			}
@@ -397,10 +409,11 @@ search_kernel(const DevModel m, const WalkerLayout L, const SearchParams p)
 					long long cf = internal_cost(m, (long long)mv.obj_coef(v));
 					k = cf > 0 ? 0 : cf < 0 ? nties - 1 : (int)below(rnd.y, (uint32_t)nties);
 				} else k = (int)below(rnd.y, (uint32_t)nties);
-				int slot = pick_kth(s.val_key, s.val_bits, L.nchunks_c, gmin, k);
+				int slot = T == 32 ? regs_pick_kth(vq, gmin, k) : pick_kth(s.val_key, s.val_bits, L.nchunks_c, gmin, k);
 				new_value = PERM ? slot : mv.dom_value(v, slot);
 			}
-			trace_var = v; trace_val = new_value; trace_ncand = ncandidates; trace_min = gmin;
+			trace_var = v; trace_val = new_value; trace_min = gmin;
+			if (p.trace) trace_ncand = T == 32 ? __reduce_add_sync(0xffffffffu, mine) : G::sum(mine, s.red + 16);
 
 			int plateau = 0, local_min = 0;
 			if (gmin < 0) { // search_unit.hpp:1042-1050
@@ -423,7 +436,7 @@ search_kernel(const DevModel m, const WalkerLayout L, const SearchParams p)
 
 			if (plateau) { // plateau_management, 545-561
 				if ((int)below(rnd.z, 100u) + 1 <= p.plateau_percent) {
-					if (tid == 0) { s.tabu[v] = (unsigned short)(p.tabu_local_min + r.local_moves - r.tabu_base); s.counters[K_FORCE] += 1; }
+					if (tid == 0) { s.tabu[scan_pos(m, v)] = (unsigned short)(p.tabu_local_min + r.local_moves - r.tabu_base); s.counters[K_FORCE] += 1; }
 					r.must_compute = 1;
 					trace_branch = 4;
 				} else {
@@ -435,7 +448,7 @@ search_kernel(const DevModel m, const WalkerLayout L, const SearchParams p)
 			if (local_min) { // local_minimum_management, 565-582
 				r.must_compute = 0;
 				if (r.ncand == 0) {
-					if (tid == 0) { s.tabu[v] = (unsigned short)(p.tabu_local_min + r.local_moves - r.tabu_base); s.counters[K_LOCALMIN] += 1; }
+					if (tid == 0) { s.tabu[scan_pos(m, v)] = (unsigned short)(p.tabu_local_min + r.local_moves - r.tabu_base); s.counters[K_LOCALMIN] += 1; }
 					if (p.tabu_local_min > 0) ++r.n_tabu;
 					trace_branch = 5;
 				} else trace_branch = 6;
@@ -463,6 +476,11 @@ search_kernel(const DevModel m, const WalkerLayout L, const SearchParams p)
 
 	// persist
 	if (r.best_pending) { copy_best<T>(m, s, best_x); r.best_pending = 0; }
+	{
+		const int tot = T == 32 ? __reduce_add_sync(0xffffffffu, evals_lane) : G::sum(evals_lane, s.red + 16);
+		if (tid == 0) s.counters[K_EVALS] += tot;
+	}
+	if (T == 32 && tid < L.nchunks_v) { s.cand_key[tid] = cq.key; s.cand_bits[tid] = cq.bits; }
 	G::sync();
 	{
 		int4* dst = reinterpret_cast<int4*>(gstate);
@@ -501,20 +519,20 @@ eval_kernel(const DevModel m, const WalkerLayout L, int num_walkers, const int* 
 	typedef WST<XT> WS;
 	const WS s = make_ws<WS>(smem_raw + (size_t)local * L.total_bytes, L);
 	const int tid = G::tid();
-	for (int v = tid; v < m.V; v += T) s.x[v] = assignments[(size_t)w * m.V + v];
+	for (int v = tid; v < L.nchunks_v * 32; v += T) s.x[v] = v < m.V ? assignments[(size_t)w * m.V + v] : 0;
 	if (tid == 0) s.cs[m.C] = make_int4(0, 0, 0, 0);
 	G::sync();
 	recompute_all<T, true>(m, s, s.red);
 	if (ctr_error) for (int c = tid; c < m.C; c += T) ctr_error[(size_t)w * m.C + c] = s.err_of(c);
-	if (var_error) for (int v = tid; v < m.V; v += T) var_error[(size_t)w * m.V + v] = s.err_var[v];
+	if (var_error) for (int v = tid; v < m.V; v += T) var_error[(size_t)w * m.V + v] = s.err_var[scan_pos(m, v)];
 	const int v = selected ? selected[w] : -1;
 	if (v < 0 || !cand_delta) return;
 	int* out = cand_delta + (size_t)w * m.max_candidates;
 	int bias;
 	const int nh = hoist_variable<T>(m, s, v, &bias);
 	G::sync();
-	int gmin, nties;
-	evaluate_candidates<T, PERM, EQ>(m, s, v, nh, bias, L.nchunks_c, out, &gmin, &nties);
+	ChunkRegs vq;
+	evaluate_candidates<T, PERM, EQ>(m, s, v, nh, bias, L.nchunks_c, out, vq);
 }
 
 } // namespace ghost_b200

@@ -1,6 +1,6 @@
 // launch_impl.cuh — instantiates the kernels for ONE threads-per-walker value (GB_T) so that the
 // variants compile in parallel (launch_t32.cu, launch_t64.cu, ...).  Variant axes: permutation
-// problem, "every live constraint is a LinearEquationEq" fast path, int16 assignment storage.
+// problem, "every live constraint is a LinearEquationEq" fast path, 16-bit assignment storage.
 #include "kernels.cuh"
 #include "launch.h"
 
@@ -35,13 +35,13 @@ static cudaError_t do_eval(int grid, int block, size_t smem, cudaStream_t st, co
 		const int key = (m.permutation ? 4 : 0) | (m.eq_only ? 2 : 0) | (m.x16 ? 1 : 0);           \
 		switch (key) {                                                                            \
 		case 0: return FN<false, false, int>(__VA_ARGS__);                                        \
-		case 1: return FN<false, false, short>(__VA_ARGS__);                                      \
+		case 1: return FN<false, false, unsigned short>(__VA_ARGS__);                                      \
 		case 2: return FN<false, true, int>(__VA_ARGS__);                                         \
-		case 3: return FN<false, true, short>(__VA_ARGS__);                                       \
+		case 3: return FN<false, true, unsigned short>(__VA_ARGS__);                                       \
 		case 4: return FN<true, false, int>(__VA_ARGS__);                                         \
-		case 5: return FN<true, false, short>(__VA_ARGS__);                                       \
+		case 5: return FN<true, false, unsigned short>(__VA_ARGS__);                                       \
 		case 6: return FN<true, true, int>(__VA_ARGS__);                                          \
-		default: return FN<true, true, short>(__VA_ARGS__);                                       \
+		default: return FN<true, true, unsigned short>(__VA_ARGS__);                                       \
 		}                                                                                         \
 	} while (0)
 

@@ -228,14 +228,17 @@ int lower_model(const GhostModelDesc* d, LoweredModel* out, std::string* why)
 		live_degree = std::max<int>(live_degree, static_cast<int>(live[v].size()));
 	}
 	const int stride = std::max(1, live_degree);
-	std::vector<int32_t> ell(static_cast<size_t>(V) * stride * 2, 0), has_ctr((V + 31) / 32, 0);
-	for (int v = 0; v < V; ++v) {
-		if (!rows[v].empty()) has_ctr[v >> 5] |= (1u << (v & 31));
+	// one row per variable, padded with all-dummy rows to a whole number of 32-variable chunks: the
+	// candidate loop of a permutation problem then reads the row of every slot of a chunk unconditionally
+	const int vpad_rows = (V + 31) / 32 * 32;
+	std::vector<int32_t> ell(static_cast<size_t>(vpad_rows) * stride * 2, 0), has_ctr((V + 31) / 32, 0);
+	for (int v = 0; v < vpad_rows; ++v) {
+		if (v < V && !rows[v].empty()) has_ctr[v >> 5] |= (1u << (v & 31));
 		for (int k = 0; k < stride; ++k) {
 			// rows are padded with the dummy constraint C: coefficient 0, error 0, never marked, so the
 			// specialised loops need no end-of-row test
 			int w0 = C | (GB_CLS_ZERO << 20), w1 = 0;
-			if (k < static_cast<int>(live[v].size())) {
+			if (v < V && k < static_cast<int>(live[v].size())) {
 				int c = live[v][k].first, kd = kind[c];
 				int cls = GB_CLS_ZERO, wbits = 0;
 				switch (kd) {
@@ -284,7 +287,8 @@ int lower_model(const GhostModelDesc* d, LoweredModel* out, std::string* why)
 	m.eq_only = eq_only ? 1 : 0;
 	m.all_have_ctr = 1;
 	for (int v = 0; v < V; ++v) if (rows[v].empty()) m.all_have_ctr = 0;
-	m.x16 = (min_value >= -32768 && max_value <= 32767) ? 1 : 0;
+	m.x16 = (min_value >= 0 && max_value <= 65535) ? 1 : 0;
+	m.v128 = V & ~127;
 	return GHOST_B200_OK;
 }
 
@@ -298,8 +302,8 @@ WalkerLayout LoweredModel::layout(int /*threads_per_walker*/, int nreset) const
 	auto take = [&](int bytes) { int r = at; at = align_up(at + bytes, 16); return r; };
 	w.nchunks_v = (m.V + 31) / 32;
 	w.nchunks_c = (m.max_candidates + 31) / 32;
-	w.x = take((m.x16 ? 2 : 4) * m.V);
-	const int vpad = w.nchunks_v * 32;   // scan without bounds tests: padded, the padding is always tabu
+	const int vpad = w.nchunks_v * 32;
+	w.x = take((m.x16 ? 2 : 4) * vpad);  // padded: a chunk of swap partners is read without a clamp   // scan without bounds tests: padded, the padding is always tabu
 	w.err_var = take(4 * vpad);
 	w.tabu = take(2 * vpad);
 	w.cs = take(16 * (m.C + 1)); // + the all-zero dummy constraint that pads the ELL rows
@@ -332,6 +336,15 @@ int LoweredModel::default_threads_per_walker() const
 	if (work <= 4096) return 64;
 	if (work <= 16384) return 128;
 	return 256;
+}
+
+int LoweredModel::effective_threads_per_walker(int requested) const
+{
+	// A one-warp walker keeps its chunk summaries in registers, one chunk per lane: at most 1024
+	// variables and 1024 candidate slots.  Larger models asked to run on one warp get two.
+	int T = requested > 0 ? requested : default_threads_per_walker();
+	if (T == 32 && std::max(dev.max_candidates, dev.V) > 1024) T = 64;
+	return T;
 }
 
 } // namespace ghost_b200

@@ -46,7 +46,8 @@ struct DevModel {
 	int ell_stride;            // entries per ELL row (max number of non-static constraints of a variable)
 	int eq_only;               // every constraint is LINEAR_EQ or static: the specialised evaluation applies
 	int all_have_ctr;          // every variable appears in at least one constraint
-	int x16;                   // every domain value fits int16: assignments are stored as shorts
+	int x16;                   // every domain value is in [0, 65535]: assignments are stored as unsigned shorts
+	int v128;                  // V rounded down to a multiple of 128: the part of the scan arrays stored block-transposed
 };
 
 // device-only constraint kind: an AllDifferent over all variables of a permutation problem
@@ -59,7 +60,7 @@ enum : int { GB_MARK_SKIP = 1 << 20 };
 
 // Per-walker shared-memory layout, byte offsets from the walker's base.
 struct WalkerLayout {
-	int x, err_var, tabu;               // int32 [V] arrays
+	int x, err_var, tabu;               // [V padded to 32]: x uint16/int32, err_var int32, tabu uint16
 	int cs;                             // int4 [C]: {T = sum - rhs (linear), current error, mark, 0}
 	int cnt;                            // uint16 [cnt_total]
 	int counters;                       // int64 [8] GhostCounters, updated by thread 0
@@ -104,6 +105,7 @@ struct LoweredModel {
 	int64_t error_bound = 0;    // upper bound of the total satisfaction error (must fit int32)
 	WalkerLayout layout(int threads_per_walker, int nreset) const;
 	int default_threads_per_walker() const;
+	int effective_threads_per_walker(int requested) const;
 };
 
 // Returns GHOST_B200_OK or an error code; on error `why` holds the message.

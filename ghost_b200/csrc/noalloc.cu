@@ -136,7 +136,7 @@ extern "C" int ghost_b200_search_noalloc(GhostModel* model, const GhostSearchOpt
 	ghost_b200_resolve_opts(model, &o);
 	if (o.number_variables_to_reset > low->V) o.number_variables_to_reset = low->V;
 	const WalkerLayout L = low->layout(o.threads_per_walker, o.number_variables_to_reset);
-	int T = o.threads_per_walker > 0 ? o.threads_per_walker : low->default_threads_per_walker();
+	int T = low->effective_threads_per_walker(o.threads_per_walker);
 	if (!(T == 32 || T == 64 || T == 128 || T == 256))
 		return fail(GHOST_B200_ERR_INVALID, "threads_per_walker must be 32, 64, 128 or 256");
 	int wpc = 1;

@@ -96,7 +96,18 @@ struct Group {
 	}
 };
 
-// Shared-memory view of one walker; XT = short when every domain value fits int16, else int
+// Storage order of the two arrays the variable scan reads (projected errors, tabu list): inside every
+// full block of 128 variables the entry of variable 128b + 32s + l sits at position 128b + 4l + s, so
+// that lane l fetches its entry of four consecutive 32-variable chunks with ONE 128-bit (errors) and
+// ONE 64-bit (tabu) load.  The tail (< 128 variables) keeps the natural order.  Positions [0, V) are
+// exactly the real entries in both parts, so loops over "all entries" need no mapping.
+__device__ __forceinline__ int scan_pos(const DevModel& m, int v)
+{
+	return v < m.v128 ? ((v & ~127) | ((v & 31) << 2) | ((v >> 5) & 3)) : v;
+}
+
+// Shared-memory view of one walker; XT = unsigned short when every domain value is in [0, 65535]
+// (zero-extending 16-bit loads cost nothing, sign-extending ones an extra instruction), else int
 template <class XT>
 struct WST {
 	typedef XT x_type;
@@ -360,7 +371,7 @@ __device__ inline int recompute_all(const DevModel& m, const WS& s, int* red)
 	if (PROJECT) for (int v = tid; v < m.V; v += T) {
 		int e = 0;
 		for (int r = mv.row_begin(v), re = mv.row_begin(v + 1); r < re; ++r) e += s.err_of(mv.row_entry(r).x);
-		s.err_var[v] = e;
+		s.err_var[scan_pos(m, v)] = e;
 	}
 	G::sync();
 	return total;
@@ -434,61 +445,103 @@ __device__ inline int chunks_max(const int* key, int nchunks)
 }
 
 // ---------------------------------------------------------------------------------------------
+// Chunk summaries of a walker owned by ONE warp (T == 32; at most 32 chunks, i.e. 1024 slots):
+// lane ch keeps (key, bits) of chunk ch in two registers instead of shared memory.
+// ---------------------------------------------------------------------------------------------
+struct ChunkRegs { int key; unsigned bits; };
+
+__device__ __forceinline__ int regs_count(const ChunkRegs& q, int best)
+{
+	return __reduce_add_sync(0xffffffffu, q.key == best ? __popc(q.bits) : 0);
+}
+__device__ __forceinline__ int regs_pick_kth(const ChunkRegs& q, int best, int k)
+{
+	const int lane = threadIdx.x & 31;
+	const unsigned b = q.key == best ? q.bits : 0u;
+	const int c = __popc(b);
+	int incl = c;
+#pragma unroll
+	for (int off = 1; off < 32; off <<= 1) {
+		int t = __shfl_up_sync(0xffffffffu, incl, off);
+		if (lane >= off) incl += t;
+	}
+	const unsigned owner = __ballot_sync(0xffffffffu, incl > k);
+	const int src = __ffs(owner) - 1;
+	const int excl = __shfl_sync(0xffffffffu, incl - c, src);
+	const unsigned wb = __shfl_sync(0xffffffffu, b, src);
+	return src * 32 + __fns(wb, 0, k - excl + 1);
+}
+
+// One chunk of the variable scan: the chunk's largest eligible error and the lanes that hold it.
+template <int T, class WS>
+__device__ __forceinline__ void commit_scan_chunk(const WS& s, ChunkRegs& q, int ch, int e)
+{
+	const int c = __reduce_max_sync(0xffffffffu, e);
+	const unsigned b = __ballot_sync(0xffffffffu, e == c);   // meaningless when c < 0: such a key never wins
+	if (T == 32) { if ((threadIdx.x & 31) == ch) { q.key = c; q.bits = b; } }
+	else if ((threadIdx.x & 31) == 0) { s.cand_key[ch] = c; s.cand_bits[ch] = b; }
+}
+
+// ---------------------------------------------------------------------------------------------
 // AdaptiveSearchVariableCandidatesHeuristic::compute_variable_candidates (…candidates_heuristic.cpp:
 // 38-60) fused with the tabu count of the reset test (search_unit.hpp:761-763): one pass over the
-// variables.  Leaves (cand_key, cand_bits); returns ncand, writes worst error and tabu count.
-// Contains group barriers.
+// variables.  Leaves the chunk summaries in `q` (T == 32) or in (cand_key, cand_bits); returns ncand,
+// writes worst error and tabu count.  Contains group barriers when T > 32.
+// Full blocks of 128 variables are read with one 128-bit and one 64-bit load per lane (see scan_pos);
+// both arrays are padded to a multiple of 32 entries (padding: always tabu), so no chunk needs a
+// bounds test.
 // ---------------------------------------------------------------------------------------------
 template <int T, class WS>
 __device__ inline int scan_candidates(const DevModel& m, const WS& s, int nchunks_v, int local_moves,
-                                      bool free_vars_ok, int* red, int* worst_out, int* ntabu_out)
+                                      bool free_vars_ok, int* red, int* worst_out, int* ntabu_out, ChunkRegs& q)
 {
 	typedef Group<T> G;
 	MV mv(m);
 	const int lane = threadIdx.x & 31;
-	int ntabu = 0;
-	// The tabu list and the projected errors are padded to a multiple of 32 entries (padding: always
-	// tabu), so a chunk needs no bounds test; two chunks per pass so that their loads overlap.  With one
-	// warp per walker the arg-max and its multiplicity are folded into the same loop.
 	const bool use_mask = !free_vars_ok && !m.all_have_ctr;
-	int worst = -1, ncand = 0;
-	for (int ch0 = G::warp(); ch0 < nchunks_v; ch0 += 2 * G::NW) {
-		const int ch1 = ch0 + G::NW;
-		const bool two = ch1 < nchunks_v; // warp-uniform
-		const int i0 = ch0 * 32 + lane, i1 = (two ? ch1 : ch0) * 32 + lane;
-		const int t0 = s.tabu[i0], t1 = s.tabu[i1];
-		const int p0 = s.err_var[i0], p1 = s.err_var[i1];
-		unsigned h0 = 0xffffffffu, h1 = 0xffffffffu;
-		if (use_mask) { h0 = (unsigned)mv.ld(m.o.has_ctr, ch0); h1 = (unsigned)mv.ld(m.o.has_ctr, two ? ch1 : ch0); }
-		const bool tabu0 = t0 > local_moves, tabu1 = two && t1 > local_moves;
-		const int e0 = (!tabu0 && ((h0 >> lane) & 1u)) ? p0 : -1;
-		const int e1 = (two && !tabu1 && ((h1 >> lane) & 1u)) ? p1 : -1;
-		const int c0 = __reduce_max_sync(0xffffffffu, e0);
-		const int c1 = __reduce_max_sync(0xffffffffu, e1);
-		const unsigned b0 = __ballot_sync(0xffffffffu, e0 == c0 && e0 >= 0);
-		const unsigned b1 = __ballot_sync(0xffffffffu, e1 == c1 && e1 >= 0);
-		ntabu += __popc(__ballot_sync(0xffffffffu, tabu0)) + __popc(__ballot_sync(0xffffffffu, tabu1));
-		if (lane == 0) {
-			s.cand_key[ch0] = c0; s.cand_bits[ch0] = b0;
-			if (two) { s.cand_key[ch1] = c1; s.cand_bits[ch1] = b1; }
+	const int nblocks = m.v128 >> 7;
+	int ntabu = 0; // per lane
+	q.key = -1; q.bits = 0u;
+	const int4* e4 = reinterpret_cast<const int4*>(s.err_var);
+	const uint2* t4 = reinterpret_cast<const uint2*>(s.tabu);
+	for (int b = G::warp(); b < nblocks; b += G::NW) {
+		const int4 e = e4[b * 32 + lane];
+		const uint2 t = t4[b * 32 + lane];
+		const bool k0 = (int)(t.x & 0xFFFFu) > local_moves, k1 = (int)(t.x >> 16) > local_moves;
+		const bool k2 = (int)(t.y & 0xFFFFu) > local_moves, k3 = (int)(t.y >> 16) > local_moves;
+		ntabu += (k0 ? 1 : 0) + (k1 ? 1 : 0) + (k2 ? 1 : 0) + (k3 ? 1 : 0);
+		int e0 = k0 ? -1 : e.x, e1 = k1 ? -1 : e.y, e2 = k2 ? -1 : e.z, e3 = k3 ? -1 : e.w;
+		if (use_mask) {
+			const int4 h = __ldg(reinterpret_cast<const int4*>(m.blob + m.o.has_ctr) + b);
+			if (!(((unsigned)h.x >> lane) & 1u)) e0 = -1;
+			if (!(((unsigned)h.y >> lane) & 1u)) e1 = -1;
+			if (!(((unsigned)h.z >> lane) & 1u)) e2 = -1;
+			if (!(((unsigned)h.w >> lane) & 1u)) e3 = -1;
 		}
-		if (T == 32) {
-			if (c0 > worst) { worst = c0; ncand = __popc(b0); } else if (c0 == worst) ncand += __popc(b0);
-			if (c1 > worst) { worst = c1; ncand = __popc(b1); } else if (c1 == worst) ncand += __popc(b1);
-		}
+		commit_scan_chunk<T>(s, q, 4 * b + 0, e0);
+		commit_scan_chunk<T>(s, q, 4 * b + 1, e1);
+		commit_scan_chunk<T>(s, q, 4 * b + 2, e2);
+		commit_scan_chunk<T>(s, q, 4 * b + 3, e3);
 	}
-	ntabu -= nchunks_v * 32 - m.V; // the padding entries are tabu by construction
-	if (T > 32) {
-		if (lane == 0) red[G::warp()] = ntabu;
+	for (int ch = 4 * nblocks + G::warp(); ch < nchunks_v; ch += G::NW) { // the tail, natural order
+		const int i = ch * 32 + lane;
+		const bool k = (int)s.tabu[i] > local_moves;
+		ntabu += k ? 1 : 0;
+		int e = k ? -1 : s.err_var[i];
+		if (use_mask && !(((unsigned)mv.ld(m.o.has_ctr, ch) >> lane) & 1u)) e = -1;
+		commit_scan_chunk<T>(s, q, ch, e);
 	}
-	G::sync();
-	if (T > 32) {
-		ntabu = (G::NW - 1) * (nchunks_v * 32 - m.V); // the padding was subtracted once per warp
-#pragma unroll
-		for (int w = 0; w < G::NW; ++w) ntabu += red[w];
+	int worst, ncand;
+	if (T == 32) {
+		ntabu = __reduce_add_sync(0xffffffffu, ntabu);
+		worst = __reduce_max_sync(0xffffffffu, q.key);
+		ncand = regs_count(q, worst);
+	} else {
+		ntabu = G::sum(ntabu, red); // barrier inside: the summaries are visible afterwards
 		worst = chunks_max(s.cand_key, nchunks_v);
 		ncand = worst >= 0 ? chunks_count(s.cand_key, s.cand_bits, nchunks_v, worst) : 0;
 	}
+	ntabu -= nchunks_v * 32 - m.V; // the padding entries are tabu by construction
 	if (worst < 0) ncand = 0;
 	*worst_out = worst;
 	*ntabu_out = ntabu;
@@ -634,117 +687,141 @@ __device__ __forceinline__ bool candidate_sum(const DevModel& m, const MV& mv, c
 	return true;
 }
 
-// Evaluate every candidate of variable v: chunk minima + tie masks into (val_key, val_bits).
-// If out != nullptr also stores each candidate's sum (GHOST_B200_NOT_A_CANDIDATE otherwise).
-// Returns (in lane 0 of each warp) the number of candidates seen by the warp's chunks.
+// One chunk of the value evaluation: the chunk's smallest cumulated delta and the lanes that hold it
+// (non-candidates carry INT_MAX; a chunk without candidates gets the key INT_MAX, which never wins).
+template <int T, class WS>
+__device__ __forceinline__ void commit_value_chunk(const WS& s, ChunkRegs& q, int ch, int sum)
+{
+	const int cmin = __reduce_min_sync(0xffffffffu, sum);
+	const unsigned bits = __ballot_sync(0xffffffffu, sum == cmin);
+	if (T == 32) { if ((threadIdx.x & 31) == ch) { q.key = cmin; q.bits = bits; } }
+	else if ((threadIdx.x & 31) == 0) { s.val_key[ch] = cmin; s.val_bits[ch] = bits; }
+}
+
+// Evaluate every candidate of variable v: chunk minima + tie masks into `q` (T == 32: lane ch keeps
+// chunk ch) or into (val_key, val_bits).  If out != nullptr also stores each candidate's sum
+// (GHOST_B200_NOT_A_CANDIDATE otherwise).  Returns this lane's number of candidates.
 // Specialised evaluation when every live constraint is a LinearEquationEq (linear_equation.cpp:59-69
 // with linear_equation_eq.cpp:54-57): |T + a*delta| - error per constraint, no kind dispatch, the
-// selected variable's (a, T - a*x_v) pairs held in registers, no end-of-row tests (padded ELL rows),
-// no divergent control flow except the rare "partner shares a constraint with v" case.
+// selected variable's (a, T - a*x_v) pairs held in registers, no end-of-row tests (the ELL rows and
+// the assignment are padded to whole chunks), no divergent control flow.
 // S = compile-time row length of the padded ELL rows (0: read it at run time)
-template <int T, bool PERM, int S, class WS>
-__device__ inline int evaluate_candidates_eq_s(const DevModel& m, const WS& s, int v, int nh, int bias, int nchunks_c, int* out, int* gmin_out, int* nties_out)
+// FAST = at most two hoisted constraints and, for a permutation problem, one common domain
+template <int T, bool PERM, int S, bool FAST, class WS>
+__device__ inline int evaluate_candidates_eq_s(const DevModel& m, const WS& s, int v, int nh, int bias, int nchunks_c, int* out, ChunkRegs& q)
 {
 	typedef Group<T> G;
 	MV mv(m);
 	const int lane = threadIdx.x & 31;
-	const int xv = s.x[v];
+	int xv = s.x[v];
+	asm("" : "+r"(xv));
 	const int nslots = PERM ? m.V : mv.dom_size(v);
 	int a0 = 0, b0 = 0, a1 = 0, b1 = 0, a2 = 0, b2 = 0, a3 = 0, b3 = 0;
 	if (nh > 0) { int4 h = s.hoist[0]; a0 = h.y; b0 = h.z; }
 	if (nh > 1) { int4 h = s.hoist[1]; a1 = h.y; b1 = h.z; }
-	if (nh > 2) { int4 h = s.hoist[2]; a2 = h.y; b2 = h.z; }
-	if (nh > 3) { int4 h = s.hoist[3]; a3 = h.y; b3 = h.z; }
+	if (!FAST) {
+		if (nh > 2) { int4 h = s.hoist[2]; a2 = h.y; b2 = h.z; }
+		if (nh > 3) { int4 h = s.hoist[3]; a3 = h.y; b3 = h.z; }
+	}
 	const int stride = S > 0 ? S : m.ell_stride;
 	const int2* ell = reinterpret_cast<const int2*>(m.blob + m.o.ell_eq);
 	const unsigned char* cs_bytes = reinterpret_cast<const unsigned char*>(s.cs);
-	int* const val_key = s.val_key;
-	unsigned* const val_bits = s.val_bits;
-	const int vmax = m.V - 1;
-	int ncandidates = 0, gmin = GB_INT_MAX, nties = 0;
+	int mine = 0;
+	q.key = GB_INT_MAX; q.bits = 0u;
 	for (int ch = G::warp(); ch < nchunks_c; ch += G::NW) {
 		const int slot = ch * 32 + lane;
+		int2 e[S > 0 ? S : 1];
+		if (PERM && S > 0) {
+			// the partner's row first: these loads do not depend on the walker's state
+			const int2* row = ell + slot * S;
+#pragma unroll
+			for (int k = 0; k < S; ++k) e[k] = __ldg(row + k);
+		}
 		bool ok = slot < nslots;
-		int d, j = 0;
+		int d;
 		if (PERM) {
-			j = min(slot, vmax);
-			ok = ok && j != v;
-			d = s.x[j];
-			if (!m.identical_domains) ok = ok && mv.in_domain(v, d) && mv.in_domain(j, xv);
+			ok = ok && slot != v;
+			d = s.x[slot];                                   // padded: no clamp
+			if (!FAST && !m.identical_domains) ok = ok && mv.in_domain(v, d) && mv.in_domain(min(slot, m.V - 1), xv);
 		} else {
 			d = mv.dom_value(v, min(slot, nslots - 1));
 		}
+		// keeps the comparison below in 32 bits: narrowed to the 16-bit storage type it would cost a
+		// sign extension of both operands per chunk
+		asm("" : "+r"(d));
 		ok = ok && d != xv;                                  // search_unit.hpp:833 / 855-860
 		int sum = bias + abs(b0 + a0 * d) + abs(b1 + a1 * d);
-		if (nh > 2) {
+		if (!FAST && nh > 2) {
 			sum += abs(b2 + a2 * d) + abs(b3 + a3 * d);
 			for (int k = 4; k < nh; ++k) { int4 h = s.hoist[k]; sum += abs(h.z + h.y * d); }
 		}
 		if (PERM) {
 			const int dx = xv - d, ndx = d - xv;
-			const int2* row = ell + j * stride;
+			const int2* row = ell + slot * stride;
 #pragma unroll
 			for (int k = 0; k < stride; ++k) {
-				const int2 e = __ldg(row + k);               // {byte offset of the constraint state, a_j}
-				const int2 st = *reinterpret_cast<const int2*>(cs_bytes + e.x); // {T, a_v}
+				const int2 f = S > 0 ? e[k] : __ldg(row + k);    // {byte offset of the constraint state, a_j}
+				const int2 st = *reinterpret_cast<const int2*>(cs_bytes + f.x); // {T, a_v}
 				// Partner's own constraint (a_v = 0; 881-885): |T + a_j*dx| - |T|, |T| being the current
 				// error of an Eq constraint.  Shared with v (872-874): the hoisted single-variable term
 				// |T - a_v*dx| is replaced by the two-variable one |T - a_v*dx + a_j*dx|.
 				const int t1 = st.x + st.y * ndx;
-				sum += abs(t1 + e.y * dx) - abs(t1);
+				sum += abs(t1 + f.y * dx) - abs(t1);
 			}
 		}
+		mine += ok ? 1 : 0;
 		if (!ok) sum = GB_INT_MAX;
 		if (out && slot < m.max_candidates) out[slot] = sum;
-		const int cmin = __reduce_min_sync(0xffffffffu, sum);
-		const unsigned okmask = __ballot_sync(0xffffffffu, ok);
-		const unsigned bits = __ballot_sync(0xffffffffu, ok && sum == cmin);
-		ncandidates += __popc(okmask);
-		if (lane == 0) { val_key[ch] = cmin; val_bits[ch] = bits; }
-		if (cmin < gmin) { gmin = cmin; nties = __popc(bits); } else if (cmin == gmin) nties += __popc(bits);
+		commit_value_chunk<T>(s, q, ch, sum);
 	}
-	*gmin_out = gmin; *nties_out = nties; // complete only when one warp owns the walker (T == 32)
-	return ncandidates;
+	return mine;
 }
 
 template <int T, bool PERM, class WS>
-__device__ inline int evaluate_candidates_eq(const DevModel& m, const WS& s, int v, int nh, int bias, int nchunks_c, int* out, int* gmin_out, int* nties_out)
+__device__ inline int evaluate_candidates_eq(const DevModel& m, const WS& s, int v, int nh, int bias, int nchunks_c, int* out, ChunkRegs& q)
 {
-	if (!PERM) return evaluate_candidates_eq_s<T, PERM, 0>(m, s, v, nh, bias, nchunks_c, out, gmin_out, nties_out);
-	switch (m.ell_stride) { // warp-uniform: fully unrolled row loops for the usual row lengths
-	case 1: return evaluate_candidates_eq_s<T, PERM, 1>(m, s, v, nh, bias, nchunks_c, out, gmin_out, nties_out);
-	case 2: return evaluate_candidates_eq_s<T, PERM, 2>(m, s, v, nh, bias, nchunks_c, out, gmin_out, nties_out);
-	case 3: return evaluate_candidates_eq_s<T, PERM, 3>(m, s, v, nh, bias, nchunks_c, out, gmin_out, nties_out);
-	case 4: return evaluate_candidates_eq_s<T, PERM, 4>(m, s, v, nh, bias, nchunks_c, out, gmin_out, nties_out);
-	default: return evaluate_candidates_eq_s<T, PERM, 0>(m, s, v, nh, bias, nchunks_c, out, gmin_out, nties_out);
+	if (!PERM) {
+		if (nh <= 2) return evaluate_candidates_eq_s<T, PERM, 0, true>(m, s, v, nh, bias, nchunks_c, out, q);
+		return evaluate_candidates_eq_s<T, PERM, 0, false>(m, s, v, nh, bias, nchunks_c, out, q);
+	}
+	if (nh <= 2 && m.identical_domains) {
+		switch (m.ell_stride) { // warp-uniform: fully unrolled row loops for the usual row lengths
+		case 1: return evaluate_candidates_eq_s<T, PERM, 1, true>(m, s, v, nh, bias, nchunks_c, out, q);
+		case 2: return evaluate_candidates_eq_s<T, PERM, 2, true>(m, s, v, nh, bias, nchunks_c, out, q);
+		case 3: return evaluate_candidates_eq_s<T, PERM, 3, true>(m, s, v, nh, bias, nchunks_c, out, q);
+		case 4: return evaluate_candidates_eq_s<T, PERM, 4, true>(m, s, v, nh, bias, nchunks_c, out, q);
+		default: break;
+		}
+	}
+	switch (m.ell_stride) {
+	case 2: return evaluate_candidates_eq_s<T, PERM, 2, false>(m, s, v, nh, bias, nchunks_c, out, q);
+	case 3: return evaluate_candidates_eq_s<T, PERM, 3, false>(m, s, v, nh, bias, nchunks_c, out, q);
+	case 4: return evaluate_candidates_eq_s<T, PERM, 4, false>(m, s, v, nh, bias, nchunks_c, out, q);
+	default: return evaluate_candidates_eq_s<T, PERM, 0, false>(m, s, v, nh, bias, nchunks_c, out, q);
 	}
 }
 
 template <int T, bool PERM, bool EQ, class WS>
-__device__ inline int evaluate_candidates(const DevModel& m, const WS& s, int v, int nh, int bias, int nchunks_c, int* out, int* gmin_out, int* nties_out)
+__device__ inline int evaluate_candidates(const DevModel& m, const WS& s, int v, int nh, int bias, int nchunks_c, int* out, ChunkRegs& q)
 {
-	if (EQ) return evaluate_candidates_eq<T, PERM>(m, s, v, nh, bias, nchunks_c, out, gmin_out, nties_out);
+	if (EQ) return evaluate_candidates_eq<T, PERM>(m, s, v, nh, bias, nchunks_c, out, q);
 	typedef Group<T> G;
 	MV mv(m);
 	const int lane = threadIdx.x & 31;
 	const int xv = s.x[v];
 	const int nslots = PERM ? m.V : mv.dom_size(v);
-	int ncandidates = 0, gmin = GB_INT_MAX, nties = 0;
+	int mine = 0;
+	q.key = GB_INT_MAX; q.bits = 0u;
 	for (int ch = G::warp(); ch < nchunks_c; ch += G::NW) {
 		int slot = ch * 32 + lane;
 		int sum = GB_INT_MAX;
 		bool ok = candidate_sum<PERM, EQ>(m, mv, s, v, xv, nh, bias, slot, nslots, &sum);
+		mine += ok ? 1 : 0;
 		if (!ok) sum = GB_INT_MAX;
 		if (out && slot < m.max_candidates) out[slot] = sum;
-		int cmin = __reduce_min_sync(0xffffffffu, sum);
-		unsigned okmask = __ballot_sync(0xffffffffu, ok);
-		unsigned bits = __ballot_sync(0xffffffffu, ok && sum == cmin);
-		ncandidates += __popc(okmask);
-		if (lane == 0) { s.val_key[ch] = cmin; s.val_bits[ch] = bits; }
-		if (cmin < gmin) { gmin = cmin; nties = __popc(bits); } else if (cmin == gmin) nties += __popc(bits);
+		commit_value_chunk<T>(s, q, ch, sum);
 	}
-	*gmin_out = gmin; *nties_out = nties; // complete only when one warp owns the walker (T == 32)
-	return ncandidates;
+	return mine;
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -804,13 +881,13 @@ __device__ inline void apply_move_eq(const DevModel& m, const WS& s, int v, int 
 		for (int k = 0; k < naff; ++k) {
 			const int d = __shfl_sync(0xffffffffu, myd, k), b = __shfl_sync(0xffffffffu, myb, k), e = __shfl_sync(0xffffffffu, mye, k);
 			if (d == 0) continue;
-			for (int i = b + tid; i < e; i += T) atomicAdd(&s.err_var[mv.scope_var(i)], d);
+			for (int i = b + tid; i < e; i += T) atomicAdd(&s.err_var[scan_pos(m, mv.scope_var(i))], d);
 		}
 	} else {
 		for (int k = 0; k < naff; ++k) {
 			const int c = s.upd[2 * k], d = s.upd[2 * k + 1];
 			if (c < 0 || d == 0) continue;
-			for (int i = mv.scope_begin(c) + tid, e = mv.scope_begin(c + 1); i < e; i += T) atomicAdd(&s.err_var[mv.scope_var(i)], d);
+			for (int i = mv.scope_begin(c) + tid, e = mv.scope_begin(c + 1); i < e; i += T) atomicAdd(&s.err_var[scan_pos(m, mv.scope_var(i))], d);
 		}
 	}
 	if (tid == 0) {
@@ -874,7 +951,7 @@ __device__ inline void apply_move(const DevModel& m, const WS& s, int v, int new
 		int c = s.upd[2 * k], delta = s.upd[2 * k + 1];
 		if (c < 0 || delta == 0) continue;
 		int b = mv.scope_begin(c), e = mv.scope_begin(c + 1);
-		for (int i = b + tid; i < e; i += T) atomicAdd(&s.err_var[mv.scope_var(i)], delta);
+		for (int i = b + tid; i < e; i += T) atomicAdd(&s.err_var[scan_pos(m, mv.scope_var(i))], delta);
 	}
 	if (tid == 0) {
 		s.x[v] = nv_new;

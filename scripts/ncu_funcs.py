@@ -10,7 +10,7 @@ def func_ranges(fn):
             if m2: out.append((i, m2.group(1)))
     return out
 ranges = {'walker.cuh': func_ranges('ghost_b200/csrc/walker.cuh'), 'kernels.cuh': func_ranges('ghost_b200/csrc/kernels.cuh')}
-rows = list(csv.reader(open(path)))
+rows = list(csv.reader(open(path, errors="replace")))
 fname = None; hdr = None; agg = {}
 for r in rows:
     if len(r) == 2 and r[0] == "File Path": fname = r[1].split("/")[-1]; continue

@@ -1,7 +1,7 @@
 """Aggregate an `ncu --page source --csv --print-source cuda,sass` dump by CUDA source line."""
 import csv, sys
 path = sys.argv[1]; top = int(sys.argv[2]) if len(sys.argv) > 2 else 40
-rows = list(csv.reader(open(path)))
+rows = list(csv.reader(open(path, errors="replace")))
 fname = None; hdr = None; agg = {}; order = []
 seen_kernel = 0
 for r in rows:
