@@ -382,7 +382,7 @@ search_kernel(const DevModel m, const WalkerLayout L, const SearchParams p)
 			const int v = T == 32 ? regs_pick_kth(cq, r.cand_max, kv) : pick_kth(s.cand_key, s.cand_bits, L.nchunks_v, r.cand_max, kv);
 			--r.ncand;
 			int bias;
-			const int nh = hoist_variable<T>(m, s, v, &bias);
+			const int nh = EQ ? hoist_variable_eq<T, PERM>(m, s, v, &bias) : hoist_variable<T>(m, s, v, &bias);
 			G::sync();
 			// search_unit.hpp:826-828
 			if (T == 32) { if (tid == (v >> 5)) cq.bits &= ~(1u << (v & 31)); }
@@ -454,7 +454,7 @@ search_kernel(const DevModel m, const WalkerLayout L, const SearchParams p)
 				} else trace_branch = 6;
 			}
 			G::sync();
-			if (PERM) unmark_variable<T>(m, s, v);
+			if (PERM) { if (EQ) unmark_variable_eq<T>(m, s, v); else unmark_variable<T>(m, s, v); }
 
 			// search_unit.hpp:1166-1188
 			if (r.best_sat > r.cur_sat) { r.best_sat = r.cur_sat; r.best_pending = 1; }
@@ -529,7 +529,7 @@ eval_kernel(const DevModel m, const WalkerLayout L, int num_walkers, const int* 
 	if (v < 0 || !cand_delta) return;
 	int* out = cand_delta + (size_t)w * m.max_candidates;
 	int bias;
-	const int nh = hoist_variable<T>(m, s, v, &bias);
+	const int nh = EQ ? hoist_variable_eq<T, PERM>(m, s, v, &bias) : hoist_variable<T>(m, s, v, &bias);
 	G::sync();
 	ChunkRegs vq;
 	evaluate_candidates<T, PERM, EQ>(m, s, v, nh, bias, L.nchunks_c, out, vq);

@@ -263,10 +263,37 @@ int lower_model(const GhostModelDesc* d, LoweredModel* out, std::string* why)
 	}
 	if (C >= GB_ELL_END) return fail(GHOST_B200_ERR_UNSUPPORTED, "too many constraints");
 	o.ell = put(ell);
+	// Packed rows of the LinearEq-only paths: 16-bit state offset + 16-bit coefficient per entry, a whole
+	// row in one aligned load.  The table (4 B x stride x V) is what the candidate loop streams through
+	// L1 every iteration, next to shared-memory carve-outs that leave L1 only a few tens of KB.
+	const int stride_eq = stride <= 2 ? stride : (stride + 3) / 4 * 4;
+	if ((C + 1) * 16 > 65535) eq_only = false;
+	for (size_t i = 0; eq_only && i + 1 < ell.size(); i += 2) if (ell[i + 1] < -32768 || ell[i + 1] > 32767) eq_only = false;
 	{
-		std::vector<int32_t> ell_eq(eq_only ? ell.size() : 0);
-		for (size_t i = 0; i + 1 < ell_eq.size(); i += 2) { ell_eq[i] = (ell[i] & 0xFFFFF) * 16; ell_eq[i + 1] = ell[i + 1]; }
+		std::vector<int32_t> ell_eq(eq_only ? static_cast<size_t>(vpad_rows) * stride_eq : 0);
+		for (int v = 0; eq_only && v < vpad_rows; ++v)
+			for (int k = 0; k < stride_eq; ++k) {
+				uint32_t off = static_cast<uint32_t>(C) * 16u, coef = 0;
+				if (k < stride) {
+					size_t i = (static_cast<size_t>(v) * stride + k) * 2;
+					off = static_cast<uint32_t>(ell[i] & 0xFFFFF) * 16u;
+					coef = static_cast<uint32_t>(ell[i + 1]) & 0xFFFFu;
+				}
+				ell_eq[static_cast<size_t>(v) * stride_eq + k] = static_cast<int32_t>(off | (coef << 16));
+			}
 		o.ell_eq = put(ell_eq);
+	}
+	{
+		// scope lists as 16-bit scan positions (see scan_pos in walker.cuh)
+		const int v128 = V & ~127;
+		std::vector<int32_t> packed((c2v.size() + 1) / 2, 0);
+		for (size_t i = 0; i < c2v.size(); ++i) {
+			int v = c2v[i];
+			uint32_t pos = v < v128 ? static_cast<uint32_t>((v & ~127) | ((v & 31) << 2) | ((v >> 5) & 3)) : static_cast<uint32_t>(v);
+			packed[i / 2] |= static_cast<int32_t>(pos << ((i & 1) * 16));
+		}
+		if (V > 65535) return fail(GHOST_B200_ERR_UNSUPPORTED, "more than 65535 variables");
+		o.c2v_pos = put(packed);
 	}
 	o.has_ctr = put(has_ctr);
 	o.total = static_cast<int>(blob.size());
@@ -284,6 +311,7 @@ int lower_model(const GhostModelDesc* d, LoweredModel* out, std::string* why)
 	m.max_degree = std::max(1, max_degree);
 	m.has_abs_diff = has_abs_diff ? 1 : 0;
 	m.ell_stride = stride;
+	m.ell_eq_stride = stride_eq;
 	m.eq_only = eq_only ? 1 : 0;
 	m.all_have_ctr = 1;
 	for (int v = 0; v < V; ++v) if (rows[v].empty()) m.all_have_ctr = 0;

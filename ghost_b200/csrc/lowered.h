@@ -24,8 +24,10 @@ struct BlobOffsets {
 	int cnt_owner;             // [cnt_total] constraint owning count-table slot t
 	int obj_coef;              // dense [V]
 	int ell;                   // [V][ell_stride] int2 rows: {c | cls<<20 | w<<24 | universal<<27, coef|pos}; c=0xFFFFF ends a row
-	int ell_eq;                // same rows for the LinearEq-only evaluation loop: word 0 = byte offset of the
-	                           // constraint's state in shared memory (16 * id), word 1 = coefficient
+	int ell_eq;                // same rows for the LinearEq-only paths, 4 bytes per entry: low half = byte offset of
+	                           // the constraint's state in shared memory (16 * id), high half = coefficient (int16);
+	                           // ell_eq_stride entries per row
+	int c2v_pos;               // uint16 per scope entry: scan_pos() of the variable (projection scatter)
 	int has_ctr;               // [ceil(V/32)] bit v%32 set iff variable v appears in some constraint
 	int total;
 };
@@ -44,7 +46,9 @@ struct DevModel {
 	int max_degree;            // max #constraints touching one variable
 	int has_abs_diff;
 	int ell_stride;            // entries per ELL row (max number of non-static constraints of a variable)
-	int eq_only;               // every constraint is LINEAR_EQ or static: the specialised evaluation applies
+	int ell_eq_stride;         // ell_stride rounded up to 1, 2 or a multiple of 4: a row is one 32/64/128-bit load
+	int eq_only;               // every constraint is LINEAR_EQ or static (and ids / coefficients fit the packed
+	                           // rows): the specialised paths apply
 	int all_have_ctr;          // every variable appears in at least one constraint
 	int x16;                   // every domain value is in [0, 65535]: assignments are stored as unsigned shorts
 	int v128;                  // V rounded down to a multiple of 128: the part of the scan arrays stored block-transposed

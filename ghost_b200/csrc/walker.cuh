@@ -184,6 +184,10 @@ struct MV {
 	__device__ __forceinline__ int cnt_tab(int c) const { return ld(m.o.cnt_tab, c); }
 	__device__ __forceinline__ int scope_begin(int c) const { return ld(m.o.c2v_off, c); }
 	__device__ __forceinline__ int scope_var(int i) const { return ld(m.o.c2v, i); }
+	// scan_pos() of scope entry i, precomputed (16 bits)
+	__device__ __forceinline__ int scope_pos(int i) const { return __ldg(reinterpret_cast<const unsigned short*>(m.blob + m.o.c2v_pos) + i); }
+	// packed row entries of the LinearEq-only paths
+	__device__ __forceinline__ const unsigned* eq_row(int v) const { return reinterpret_cast<const unsigned*>(m.blob + m.o.ell_eq) + v * m.ell_eq_stride; }
 	__device__ __forceinline__ int obj_coef(int v) const { return ld(m.o.obj_coef, v); }
 };
 
@@ -617,6 +621,52 @@ __device__ inline void unmark_variable(const DevModel& m, const WS& s, int v)
 	}
 }
 
+// The same two steps when every live constraint is a LinearEquationEq: the packed row (lower.cpp) is
+// read by one lane per entry; live entries come first in a row, so entry k is hoisted entry k.
+template <int T, bool PERM, class WS>
+__device__ inline int hoist_variable_eq(const DevModel& m, const WS& s, int v, int* bias_out)
+{
+	MV mv(m);
+	const int lane = threadIdx.x & 31;
+	const int xv = s.x[v];
+	const int nrow = m.ell_eq_stride, dummy = m.C * 16;
+	const unsigned* row = mv.eq_row(v);
+	unsigned char* cs_bytes = reinterpret_cast<unsigned char*>(s.cs);
+	const bool writer = Group<T>::warp() == 0;
+	int nh = 0, bias = 0;
+	for (int base = 0; base < nrow; base += 32) {
+		const int k = base + lane;
+		const unsigned f = k < nrow ? __ldg(row + k) : (unsigned)dummy;
+		const int off = (int)(f & 0xFFFFu), a = (int)f >> 16;
+		const bool valid = off != dummy;
+		int err = 0;
+		if (valid) {
+			int* st = reinterpret_cast<int*>(cs_bytes + off);
+			const int t = st[0];
+			err = st[2];
+			if (writer) {
+				s.hoist[k] = make_int4(GB_CLS_LINEAR | (3 << 4) | ((off >> 4) << 8), a, t - a * xv, 0);
+				if (PERM) { st[3] = k + 1; st[1] = a; }
+			}
+		}
+		nh += __popc(__ballot_sync(0xffffffffu, valid));
+		bias -= __reduce_add_sync(0xffffffffu, err);
+	}
+	*bias_out = bias;
+	return nh;
+}
+template <int T, class WS>
+__device__ inline void unmark_variable_eq(const DevModel& m, const WS& s, int v)
+{
+	MV mv(m);
+	const unsigned* row = mv.eq_row(v);
+	unsigned char* cs_bytes = reinterpret_cast<unsigned char*>(s.cs);
+	for (int k = Group<T>::tid(); k < m.ell_eq_stride; k += T) {
+		int* st = reinterpret_cast<int*>(cs_bytes + (__ldg(row + k) & 0xFFFFu));
+		st[1] = 0; st[3] = 0; // the dummy entry is all zeros anyway
+	}
+}
+
 // variable part of hoisted entry h when the selected variable alone takes value d (d != x_v);
 // the constant part is in the bias
 template <class WS>
@@ -723,19 +773,19 @@ __device__ inline int evaluate_candidates_eq_s(const DevModel& m, const WS& s, i
 		if (nh > 2) { int4 h = s.hoist[2]; a2 = h.y; b2 = h.z; }
 		if (nh > 3) { int4 h = s.hoist[3]; a3 = h.y; b3 = h.z; }
 	}
-	const int stride = S > 0 ? S : m.ell_stride;
-	const int2* ell = reinterpret_cast<const int2*>(m.blob + m.o.ell_eq);
+	constexpr int SP = S <= 2 ? S : 4;  // entries per packed row when S is known (one 32/64/128-bit load)
+	const unsigned* ell = reinterpret_cast<const unsigned*>(m.blob + m.o.ell_eq);
 	const unsigned char* cs_bytes = reinterpret_cast<const unsigned char*>(s.cs);
 	int mine = 0;
 	q.key = GB_INT_MAX; q.bits = 0u;
 	for (int ch = G::warp(); ch < nchunks_c; ch += G::NW) {
 		const int slot = ch * 32 + lane;
-		int2 e[S > 0 ? S : 1];
+		unsigned e[SP > 0 ? SP : 1];
 		if (PERM && S > 0) {
-			// the partner's row first: these loads do not depend on the walker's state
-			const int2* row = ell + slot * S;
-#pragma unroll
-			for (int k = 0; k < S; ++k) e[k] = __ldg(row + k);
+			// the partner's row first: this load does not depend on the walker's state
+			if (SP == 1) e[0] = __ldg(ell + slot);
+			else if (SP == 2) { const uint2 r = __ldg(reinterpret_cast<const uint2*>(ell) + slot); e[0] = r.x; e[1] = r.y; }
+			else { const uint4 r = __ldg(reinterpret_cast<const uint4*>(ell) + slot); e[0] = r.x; e[1] = r.y; e[SP > 2 ? 2 : 0] = r.z; e[SP > 2 ? 3 : 0] = r.w; }
 		}
 		bool ok = slot < nslots;
 		int d;
@@ -757,16 +807,18 @@ __device__ inline int evaluate_candidates_eq_s(const DevModel& m, const WS& s, i
 		}
 		if (PERM) {
 			const int dx = xv - d, ndx = d - xv;
-			const int2* row = ell + slot * stride;
+			const int nrow = S > 0 ? S : m.ell_eq_stride;
+			const unsigned* row = ell + slot * nrow;
 #pragma unroll
-			for (int k = 0; k < stride; ++k) {
-				const int2 f = S > 0 ? e[k] : __ldg(row + k);    // {byte offset of the constraint state, a_j}
-				const int2 st = *reinterpret_cast<const int2*>(cs_bytes + f.x); // {T, a_v}
+			for (int k = 0; k < nrow; ++k) {
+				const unsigned f = S > 0 ? e[k] : __ldg(row + k); // byte offset of the constraint state | a_j << 16
+				const int fy = (int)f >> 16;
+				const int2 st = *reinterpret_cast<const int2*>(cs_bytes + (f & 0xFFFFu)); // {T, a_v}
 				// Partner's own constraint (a_v = 0; 881-885): |T + a_j*dx| - |T|, |T| being the current
 				// error of an Eq constraint.  Shared with v (872-874): the hoisted single-variable term
 				// |T - a_v*dx| is replaced by the two-variable one |T - a_v*dx + a_j*dx|.
 				const int t1 = st.x + st.y * ndx;
-				sum += abs(t1 + f.y * dx) - abs(t1);
+				sum += abs(t1 + fy * dx) - abs(t1);
 			}
 		}
 		mine += ok ? 1 : 0;
@@ -841,10 +893,13 @@ __device__ inline void apply_move_eq(const DevModel& m, const WS& s, int v, int 
 	int j = 0, xj = 0;
 	if (PERM) { j = new_value; xj = s.x[j]; }
 	const int nv_new = PERM ? xj : new_value;
-	const int stride = m.ell_stride;
-	const int2* ell = reinterpret_cast<const int2*>(m.blob + m.o.ell);
-	const int naff = nh + (PERM ? stride : 0);
-	for (int k = tid; k < naff; k += T) {
+	const int nrow = m.ell_eq_stride;
+	const unsigned* rowj = mv.eq_row(j);
+	unsigned char* cs_bytes = reinterpret_cast<unsigned char*>(s.cs);
+	const int naff = nh + (PERM ? nrow : 0);
+	// new state of affected constraint k (hoisted ones first, then the partner's row); returns its id
+	// (-1: nothing to do) and the change of its error
+	auto update = [&](int k, int* delta_out) -> int {
 		int c = -1, delta = 0;
 		if (k < nh) {
 			const int4 h = s.hoist[k];
@@ -852,22 +907,49 @@ __device__ inline void apply_move_eq(const DevModel& m, const WS& s, int v, int 
 			const int told = s.T_of(c);
 			int tnew = told + h.y * (nv_new - xv);
 			if (PERM)
-				for (int e = 0; e < stride; ++e) {
-					const int2 f = __ldg(ell + (j * stride + e));
-					if (ell_ctr(f.x) == c) { tnew += f.y * (xv - xj); break; } // the partner is in this scope too
+				for (int e = 0; e < nrow; ++e) {
+					const unsigned f = __ldg(rowj + e);
+					if ((int)(f & 0xFFFFu) == c * 16) { tnew += ((int)f >> 16) * (xv - xj); break; } // the partner is in this scope too
 				}
 			delta = abs(tnew) - abs(told);
 			s.T_of(c) = tnew; s.err_of(c) = abs(tnew);
 		} else {
-			const int2 f = __ldg(ell + (j * stride + (k - nh)));
-			const int cc = ell_ctr(f.x);
-			if (cc != m.C && s.mark_of(cc) == 0) { // not padding, not shared with v (handled above)
-				c = cc;
-				const int told = s.T_of(c), tnew = told + f.y * (xv - xj);
+			const unsigned f = __ldg(rowj + (k - nh));
+			int* st = reinterpret_cast<int*>(cs_bytes + (f & 0xFFFFu));
+			if ((int)(f & 0xFFFFu) != m.C * 16 && st[3] == 0) { // not padding, not shared with v (handled above)
+				c = (int)(f & 0xFFFFu) >> 4;
+				const int told = st[0], tnew = told + ((int)f >> 16) * (xv - xj);
 				delta = abs(tnew) - abs(told);
-				s.T_of(c) = tnew; s.err_of(c) = abs(tnew);
+				st[0] = tnew; st[2] = abs(tnew);
 			}
 		}
+		*delta_out = delta;
+		return c;
+	};
+	if (T == 32 && naff <= 32) {
+		// one warp: everything stays in registers
+		int myd = 0, myb = 0, mye = 0;
+		if (lane < naff) {
+			const int c = update(lane, &myd);
+			if (c >= 0 && myd != 0) { myb = mv.scope_begin(c); mye = mv.scope_begin(c + 1); }
+		}
+		__syncwarp();
+		for (int k = 0; k < naff; ++k) {
+			const int d = __shfl_sync(0xffffffffu, myd, k), b = __shfl_sync(0xffffffffu, myb, k), e = __shfl_sync(0xffffffffu, mye, k);
+			if (d == 0) continue;
+			for (int i = b + lane; i < e; i += 32) atomicAdd(&s.err_var[mv.scope_pos(i)], d);
+		}
+		__syncwarp();
+		if (lane == 0) {
+			s.x[v] = nv_new;
+			if (PERM) s.x[j] = xv;
+		}
+		__syncwarp();
+		return;
+	}
+	for (int k = tid; k < naff; k += T) {
+		int delta;
+		const int c = update(k, &delta);
 		s.upd[2 * k] = c; s.upd[2 * k + 1] = delta;
 	}
 	G::sync();
@@ -881,13 +963,13 @@ __device__ inline void apply_move_eq(const DevModel& m, const WS& s, int v, int 
 		for (int k = 0; k < naff; ++k) {
 			const int d = __shfl_sync(0xffffffffu, myd, k), b = __shfl_sync(0xffffffffu, myb, k), e = __shfl_sync(0xffffffffu, mye, k);
 			if (d == 0) continue;
-			for (int i = b + tid; i < e; i += T) atomicAdd(&s.err_var[scan_pos(m, mv.scope_var(i))], d);
+			for (int i = b + tid; i < e; i += T) atomicAdd(&s.err_var[mv.scope_pos(i)], d);
 		}
 	} else {
 		for (int k = 0; k < naff; ++k) {
 			const int c = s.upd[2 * k], d = s.upd[2 * k + 1];
 			if (c < 0 || d == 0) continue;
-			for (int i = mv.scope_begin(c) + tid, e = mv.scope_begin(c + 1); i < e; i += T) atomicAdd(&s.err_var[scan_pos(m, mv.scope_var(i))], d);
+			for (int i = mv.scope_begin(c) + tid, e = mv.scope_begin(c + 1); i < e; i += T) atomicAdd(&s.err_var[mv.scope_pos(i)], d);
 		}
 	}
 	if (tid == 0) {
@@ -951,7 +1033,7 @@ __device__ inline void apply_move(const DevModel& m, const WS& s, int v, int new
 		int c = s.upd[2 * k], delta = s.upd[2 * k + 1];
 		if (c < 0 || delta == 0) continue;
 		int b = mv.scope_begin(c), e = mv.scope_begin(c + 1);
-		for (int i = b + tid; i < e; i += T) atomicAdd(&s.err_var[scan_pos(m, mv.scope_var(i))], delta);
+		for (int i = b + tid; i < e; i += T) atomicAdd(&s.err_var[mv.scope_pos(i)], delta);
 	}
 	if (tid == 0) {
 		s.x[v] = nv_new;
