@@ -171,7 +171,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default=WORKLOAD)
-    ap.add_argument("--epoch", type=int, default=64, help="loop passes per walker per step (one kernel launch)")
+    ap.add_argument("--epoch", type=int, default=256, help="loop passes per walker per step (one kernel launch)")
     ap.add_argument("--walkers", type=int, default=0, help="walkers per GPU (0: fill the GPU)")
     ap.add_argument("--threads-per-walker", type=int, default=0)
     ap.add_argument("--ref-seconds", type=float, default=12.0)

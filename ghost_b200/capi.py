@@ -62,6 +62,15 @@ def _load():
     lib.ghost_b200_search_stop_flag_export.argtypes = [vp, vp]
     lib.ghost_b200_search_stop_flag_import.argtypes = [vp, vp]
     lib.ghost_b200_search_noalloc.argtypes = [vp, C.POINTER(GhostSearchOptsStruct), i32, i32, vp, vp, vp]
+    lib.ghost_b200_complete_search.argtypes = [vp, i64, C.POINTER(vp)]
+    lib.ghost_b200_solutions_count.argtypes = [vp]
+    lib.ghost_b200_solutions_count.restype = i64
+    lib.ghost_b200_solutions_truncated.argtypes = [vp]
+    lib.ghost_b200_solutions_truncated.restype = i32
+    lib.ghost_b200_solutions_read.argtypes = [vp, i64, i64, vp, vp]
+    lib.ghost_b200_solutions_stats.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(i64), C.POINTER(i64), C.POINTER(i32)]
+    lib.ghost_b200_solutions_destroy.argtypes = [vp]
+    lib.ghost_b200_solutions_destroy.restype = None
     return lib
 
 
@@ -115,6 +124,25 @@ class Model:
     def resolve_opts(self, opts: GhostSearchOptsStruct):
         _check(lib.ghost_b200_resolve_opts(self.h, C.byref(opts)))
         return opts
+
+    def complete_search(self, max_solutions: int = 0):
+        """ghost_b200_complete_search: every solution in the reference's enumeration order.
+        Returns dict(solutions [n][V] int32, costs [n] float64, truncated, kernel_time_us, kernel_launches,
+        frontier_nodes, frontier_depth)."""
+        h = C.c_void_p()
+        _check(lib.ghost_b200_complete_search(self.h, int(max_solutions), C.byref(h)))
+        try:
+            n = lib.ghost_b200_solutions_count(h)
+            sol = np.zeros((n, self.V), dtype=np.int32)
+            cost = np.zeros(n, dtype=np.float64)
+            if n:
+                _check(lib.ghost_b200_solutions_read(h, 0, n, _ptr(sol), _ptr(cost)))
+            us, nl, fn, fd = C.c_double(0), C.c_int64(0), C.c_int64(0), C.c_int32(0)
+            _check(lib.ghost_b200_solutions_stats(h, C.byref(us), C.byref(nl), C.byref(fn), C.byref(fd)))
+            return dict(solutions=sol, costs=cost, truncated=bool(lib.ghost_b200_solutions_truncated(h)),
+                        kernel_time_us=us.value, kernel_launches=nl.value, frontier_nodes=fn.value, frontier_depth=fd.value)
+        finally:
+            lib.ghost_b200_solutions_destroy(h)
 
     # -- parity hook, host buffers --
     def eval_moves(self, assignments, selected_var):

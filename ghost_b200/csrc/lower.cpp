@@ -200,6 +200,13 @@ int lower_model(const GhostModelDesc* d, LoweredModel* out, std::string* why)
 	LoweredModel& L = *out;
 	L = LoweredModel();
 	L.V = V; L.C = C;
+	L.desc.dom_off.assign(d->dom_offset, d->dom_offset + V + 1);
+	L.desc.dom_val.assign(d->dom_values, d->dom_values + d->dom_offset[V]);
+	L.desc.kind.assign(d->ctr_kind, d->ctr_kind + C);
+	L.desc.ctr_off = c2v_off; L.desc.ctr_var = c2v; L.desc.ctr_coef = ent_coef;
+	L.desc.ctr_param.assign(C, 0);
+	for (int c = 0; c < C; ++c) if (is_linear(d->ctr_kind[c]) || d->ctr_kind[c] == GHOST_KIND_FIX_VALUE) L.desc.ctr_param[c] = static_cast<int32_t>(std::llround(d->ctr_param ? d->ctr_param[c] : 0.0));
+	L.desc.obj_coef = obj_coef; L.desc.objective = ok;
 	L.start.assign(d->start_value, d->start_value + V);
 	L.error_bound = error_bound;
 	std::vector<int32_t>& blob = L.blob;

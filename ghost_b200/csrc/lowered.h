@@ -100,7 +100,18 @@ struct WalkerScalars {
 	GhostCounters k;
 };
 
+// The descriptor as the user gave it (validated, integers), for the paths that do not run on the
+// lowered walker tables: the complete search keeps each domain in descriptor order and the real
+// constraint kinds (no "static" rewrite).
+struct HostDesc {
+	std::vector<int32_t> dom_off, dom_val;               // [V+1], values in descriptor order
+	std::vector<int32_t> kind, ctr_off, ctr_var, ctr_coef, ctr_param;
+	std::vector<int32_t> obj_coef;                       // dense [V]
+	int objective = 0;
+};
+
 struct LoweredModel {
+	HostDesc desc;
 	std::vector<int32_t> blob;
 	DevModel dev{};             // dev.blob filled when uploaded
 	// host copies used for validation / result conversion

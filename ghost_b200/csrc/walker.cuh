@@ -508,6 +508,9 @@ __device__ inline int scan_candidates(const DevModel& m, const WS& s, int nchunk
 	q.key = -1; q.bits = 0u;
 	const int4* e4 = reinterpret_cast<const int4*>(s.err_var);
 	const uint2* t4 = reinterpret_cast<const uint2*>(s.tabu);
+#ifdef GB_UNROLL1
+#pragma unroll 1
+#endif
 	for (int b = G::warp(); b < nblocks; b += G::NW) {
 		const int4 e = e4[b * 32 + lane];
 		const uint2 t = t4[b * 32 + lane];
@@ -778,14 +781,30 @@ __device__ inline int evaluate_candidates_eq_s(const DevModel& m, const WS& s, i
 	const unsigned char* cs_bytes = reinterpret_cast<const unsigned char*>(s.cs);
 	int mine = 0;
 	q.key = GB_INT_MAX; q.bits = 0u;
+	auto load_row = [&](int slot, unsigned* e) {
+		if (SP == 1) e[0] = __ldg(ell + slot);
+		else if (SP == 2) { const uint2 r = __ldg(reinterpret_cast<const uint2*>(ell) + slot); e[0] = r.x; e[1] = r.y; }
+		else { const uint4 r = __ldg(reinterpret_cast<const uint4*>(ell) + slot); e[0] = r.x; e[1] = r.y; e[SP > 2 ? 2 : 0] = r.z; e[SP > 2 ? 3 : 0] = r.w; }
+	};
+#ifdef GB_PREFETCH
+	unsigned en[SP > 0 ? SP : 1];
+	if (PERM && S > 0) load_row(G::warp() * 32 + lane, en);
+#endif
+#ifdef GB_UNROLL1
+#pragma unroll 1
+#endif
 	for (int ch = G::warp(); ch < nchunks_c; ch += G::NW) {
 		const int slot = ch * 32 + lane;
 		unsigned e[SP > 0 ? SP : 1];
 		if (PERM && S > 0) {
 			// the partner's row first: this load does not depend on the walker's state
-			if (SP == 1) e[0] = __ldg(ell + slot);
-			else if (SP == 2) { const uint2 r = __ldg(reinterpret_cast<const uint2*>(ell) + slot); e[0] = r.x; e[1] = r.y; }
-			else { const uint4 r = __ldg(reinterpret_cast<const uint4*>(ell) + slot); e[0] = r.x; e[1] = r.y; e[SP > 2 ? 2 : 0] = r.z; e[SP > 2 ? 3 : 0] = r.w; }
+#ifdef GB_PREFETCH
+#pragma unroll
+			for (int k = 0; k < SP; ++k) e[k] = en[k];
+			load_row(min(slot + 32 * G::NW, nchunks_c * 32 - 1), en); // next chunk's row, one pass ahead
+#else
+			load_row(slot, e);
+#endif
 		}
 		bool ok = slot < nslots;
 		int d;

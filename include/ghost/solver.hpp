@@ -107,14 +107,6 @@ namespace ghost
 			return e;
 		}
 
-		// complete_search helper: all constraints whose scope is fully assigned (ids <= last) hold
-		bool consistent_up_to(int last, const std::vector<std::vector<int>>& scopes_max) const
-		{
-			for (std::size_t c = 0; c < _model.constraints.size(); ++c)
-				if (scopes_max[c][0] == last && _model.constraints[c]->error() != 0.0) return false;
-			return true;
-		}
-
 	public:
 		Solver(const ModelBuilderType& model_builder) : _model_builder(model_builder) {}
 
@@ -193,38 +185,43 @@ namespace ghost
 			return fast_search(final_cost, final_solution, timeout, options);
 		}
 
-		/*! Enumerate every solution (reference include/solver.hpp:932-987: AC-3 filtering + depth-first
-		 * search in variable order).  Host implementation: depth-first in the same variable and value
-		 * order, pruning as soon as a constraint's scope is fully assigned — filtering only removes
-		 * dead branches, so the solutions and their order are the reference's.  The device version is a
-		 * later row of the scope table. */
+		/*! Enumerate every solution (same contract as the reference, include/solver.hpp:932-987): appends to
+		 * final_solutions all assignments with error 0 in the reference's depth-first order (variable 0
+		 * first, values in domain order) and to final_costs the objective value of each (user's sign; 0
+		 * for a satisfaction problem); returns true iff there is at least one.  The enumeration runs on
+		 * the GPU through ghost_b200_complete_search; every returned row is re-checked with the host-side
+		 * constraints.  Models outside the stock constraint set are refused (no CPU fallback). */
 		bool complete_search(std::vector<double>& final_costs, std::vector<std::vector<int>>& final_solutions, Options&)
 		{
 			_model = _model_builder.build_model();
-			const int n = static_cast<int>(_model.variables.size());
-			std::vector<std::vector<int>> scopes_max(_model.constraints.size(), std::vector<int>(1, -1));
-			for (std::size_t c = 0; c < _model.constraints.size(); ++c)
-				for (int id : _model.constraints[c]->get_variable_ids()) scopes_max[c][0] = std::max(scopes_max[c][0], id);
-			std::vector<std::vector<int>> domains;
-			for (const auto& v : _model.variables) domains.push_back(v.get_full_domain());
-			std::function<void(int)> dfs = [&](int depth) {
-				if (depth == n) {
-					std::vector<int> solution;
-					for (const auto& v : _model.variables) solution.push_back(v.get_value());
-					double cost = _model.objective->cost();
-					if (_model.objective->is_maximization()) cost = -cost;
-					final_costs.push_back(cost);
-					final_solutions.push_back(solution);
-					return;
-				}
-				for (int value : domains[static_cast<std::size_t>(depth)]) {
-					_model.variables[static_cast<std::size_t>(depth)].set_value(value);
-					if (consistent_up_to(depth, scopes_max)) dfs(depth + 1);
-				}
-			};
-			const std::size_t before = final_solutions.size();
-			if (n > 0) dfs(0);
-			return final_solutions.size() > before;
+			Lowered L;
+			lower(_model, L);
+			GhostModel* gm = nullptr;
+			if (ghost_b200_model_create(&L.desc, &gm) != GHOST_B200_OK) throw std::runtime_error(ghost_b200_last_error());
+			GhostSolutionSet* set = nullptr;
+			const int rc = ghost_b200_complete_search(gm, 0, &set);
+			ghost_b200_model_destroy(gm);
+			if (rc != GHOST_B200_OK) throw std::runtime_error(ghost_b200_last_error());
+			const int64_t n = ghost_b200_solutions_count(set);
+			const std::size_t V = _model.variables.size();
+			std::vector<int32_t> flat(static_cast<std::size_t>(n) * V);
+			std::vector<double> costs(static_cast<std::size_t>(n));
+			const int rr = n > 0 ? ghost_b200_solutions_read(set, 0, n, flat.data(), costs.data()) : GHOST_B200_OK;
+			double kernel_us = 0; int64_t launches = 0;
+			ghost_b200_solutions_stats(set, &kernel_us, &launches, nullptr, nullptr);
+			ghost_b200_solutions_destroy(set);
+			if (rr != GHOST_B200_OK) throw std::runtime_error(ghost_b200_last_error());
+			_stats = SearchStatistics();
+			_stats.kernel_time_us = kernel_us; _stats.kernel_launches = launches;
+			for (int64_t i = 0; i < n; ++i) {
+				std::vector<int> solution(flat.begin() + static_cast<std::ptrdiff_t>(i * V), flat.begin() + static_cast<std::ptrdiff_t>((i + 1) * V));
+				for (std::size_t v = 0; v < V; ++v) _model.variables[v].set_value(solution[v]);
+				if (total_error() != 0.0)
+					throw std::logic_error("ghost_b200: the GPU enumerated an assignment that the host-side constraints reject");
+				final_costs.push_back(costs[static_cast<std::size_t>(i)]);
+				final_solutions.emplace_back(std::move(solution));
+			}
+			return n > 0;
 		}
 		bool complete_search(std::vector<double>& final_costs, std::vector<std::vector<int>>& final_solutions)
 		{

@@ -230,6 +230,32 @@ int ghost_b200_search_walkers(GhostSearch* search, int32_t* best_x, int64_t* bes
  * {iteration, variable, new value, branch, #candidates, min conflict, current sat error, 0}. */
 int ghost_b200_search_trace(GhostSearch* search, int32_t* rows, int32_t cap, int32_t* len);
 
+/* ---- complete search ------------------------------------------------------------------------------
+ * What Solver::complete_search calls (include/solver.hpp:932-987; helpers prefiltering 161-181,
+ * ac3_filtering 186-243, has_support 249-295, the recursive enumeration 300-347): EVERY solution of
+ * the model, in the order the reference's depth-first enumeration produces them — variable 0 first,
+ * each variable's values in the order of its domain as given in the descriptor — with the cost the
+ * reference reports next to each one (the objective value with the user's sign, 0 for a satisfaction
+ * problem; solver.hpp:969-975).  The reference's arc-consistency filtering only prunes the
+ * enumeration, it never changes the set or the order; the device enumeration prunes with its own
+ * bounds and returns the same list.  The model's permutation flag and start values play
+ * no role here, exactly as in the reference.
+ * max_solutions > 0 caps the list (the first max_solutions in order); 0 = all, failing with
+ * GHOST_B200_ERR_UNSUPPORTED if they do not fit the device.  Limits: at most 64 variables. */
+typedef struct GhostSolutionSet GhostSolutionSet;
+int ghost_b200_complete_search(GhostModel* model, int64_t max_solutions, GhostSolutionSet** out);
+int64_t ghost_b200_solutions_count(const GhostSolutionSet* set);
+/* 1 if the enumeration stopped at max_solutions with more solutions left. */
+int32_t ghost_b200_solutions_truncated(const GhostSolutionSet* set);
+/* Copy solutions [first, first+count) to HOST memory: solutions [count][V] (may be NULL), costs [count]
+ * (may be NULL). */
+int ghost_b200_solutions_read(const GhostSolutionSet* set, int64_t first, int64_t count, int32_t* solutions,
+                              double* costs);
+/* Device time of the enumeration kernels (CUDA events) and the number of kernels launched. */
+int ghost_b200_solutions_stats(const GhostSolutionSet* set, double* kernel_time_us, int64_t* kernel_launches,
+                               int64_t* frontier_nodes, int32_t* frontier_depth);
+void ghost_b200_solutions_destroy(GhostSolutionSet* set);
+
 /* ---- search without any allocation -------------------------------------------------------------
  * No counterpart in the reference (its SearchUnits live on the host heap; nothing there maps to
  * device memory management).

@@ -70,6 +70,7 @@ def _load_port():
         lib.oracle_check.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         lib.oracle_resolve_opts.argtypes = [C.c_int32, C.POINTER(GhostSearchOptsStruct)]
         lib.oracle_philox4x32_10.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        lib.oracle_complete_search.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         _port = lib
     return _port
 
@@ -117,6 +118,14 @@ class OraclePort:
         self.lib.oracle_check(self.h, x.ctypes.data, C.byref(e), C.byref(o))
         return e.value, o.value
 
+    def complete_search(self, max_solutions: int):
+        """All solutions (at most max_solutions > 0) in the reference's enumeration order: (solutions, costs, truncated)."""
+        sol = np.zeros((max_solutions, self.V), dtype=np.int32)
+        cost = np.zeros(max_solutions, dtype=np.float64)
+        n, tr = C.c_int64(0), C.c_int32(0)
+        self.lib.oracle_complete_search(self.h, int(max_solutions), sol.ctypes.data, cost.ctypes.data, C.byref(n), C.byref(tr))
+        return sol[:n.value].copy(), cost[:n.value].copy(), bool(tr.value)
+
     def resolve_opts(self, opts: GhostSearchOptsStruct):
         self.lib.oracle_resolve_opts(self.V, C.byref(opts))
         return opts
@@ -154,6 +163,7 @@ def _load_ref():
         lib.ref_check.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         lib.ref_fast_search.argtypes = [C.POINTER(GhostModelDescStruct), C.c_double, C.c_int, C.c_int, C.c_int,
                                         C.c_void_p, C.c_void_p, C.c_void_p]
+        lib.ref_complete_search.argtypes = [C.POINTER(GhostModelDescStruct), C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]
         _ref = lib
     return _ref
 
@@ -203,6 +213,17 @@ class RefModel:
         if rc != 0:
             raise RuntimeError("ref_check failed")
         return e.value, o.value
+
+    def complete_search(self, max_solutions: int):
+        """The reference's own Solver::complete_search: (solutions[:max], costs[:max], total count)."""
+        sol = np.zeros((max_solutions, self.V), dtype=np.int32)
+        cost = np.zeros(max_solutions, dtype=np.float64)
+        n = C.c_int64(0)
+        rc = self.lib.ref_complete_search(C.byref(self._s), int(max_solutions), sol.ctypes.data, cost.ctypes.data, C.byref(n))
+        if rc < 0:
+            raise RuntimeError("ref_complete_search failed")
+        k = min(n.value, max_solutions)
+        return sol[:k].copy(), cost[:k].copy(), n.value
 
     def fast_search(self, timeout_us, parallel_runs=False, threads=0, custom_start=False):
         cost, el = C.c_double(0), C.c_double(0)

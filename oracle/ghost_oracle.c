@@ -63,6 +63,7 @@ struct OracleModel {
 	int32_t V, C, permutation;
 	int32_t* dom_off;   /* [V+1] */
 	int32_t* dom;       /* sorted ascending per variable */
+	int32_t* dom_given; /* the same values in the order of the descriptor (complete search) */
 	int32_t* start;
 	int32_t* kind;
 	int32_t* coff;      /* [C+1] */
@@ -107,6 +108,8 @@ OracleModel* oracle_model_create(const GhostModelDesc* d)
 	m->start = (int32_t*)malloc(sizeof(int32_t) * (V > 0 ? V : 1));
 	memcpy(m->dom_off, d->dom_offset, sizeof(int32_t) * (V + 1));
 	memcpy(m->dom, d->dom_values, sizeof(int32_t) * ndom);
+	m->dom_given = (int32_t*)malloc(sizeof(int32_t) * (ndom > 0 ? ndom : 1));
+	memcpy(m->dom_given, d->dom_values, sizeof(int32_t) * ndom);
 	memcpy(m->start, d->start_value, sizeof(int32_t) * V);
 	int32_t maxdom = 0;
 	for (int v = 0; v < V; ++v) {
@@ -177,7 +180,7 @@ OracleModel* oracle_model_create(const GhostModelDesc* d)
 void oracle_model_destroy(OracleModel* m)
 {
 	if (!m) return;
-	free(m->dom_off); free(m->dom); free(m->start); free(m->kind); free(m->coff); free(m->cvars);
+	free(m->dom_off); free(m->dom); free(m->dom_given); free(m->start); free(m->kind); free(m->coff); free(m->cvars);
 	free(m->ccoef); free(m->cparam); free(m->v2c_off); free(m->v2c); free(m->v2c_pos);
 	free(m->cnt_off); free(m->cnt_base); free(m->cnt_size); free(m->obj_coef);
 	free(m);
@@ -979,5 +982,195 @@ int oracle_search(const OracleModel* m, const GhostSearchOpts* opts, uint64_t wa
 	if (counters) *counters = w->k;
 	if (trace_len) *trace_len = ntrace;
 	walker_destroy(w);
+	return 0;
+}
+
+/* ==========================================================================================
+ * Solver::complete_search (include/solver.hpp:932-987) restated with its helpers: prefiltering
+ * (161-181), ac3_filtering (186-243), has_support (249-295) and the recursive enumeration
+ * (300-347).  Domains are per-variable value lists in descriptor order; a "copy" of the domains
+ * (the reference passes them by value) is a copy of the size array + the value array.
+ * ========================================================================================== */
+typedef struct CsDoms { int32_t* val; int32_t* size; } CsDoms; /* val: flat, capacity = original sizes */
+
+typedef struct CsCtx {
+	Walker* w;
+	const OracleModel* m;
+	int32_t ndom;
+	int64_t cap, count;
+	int32_t* out_x; double* out_cost;
+	int truncated;
+} CsCtx;
+
+static CsDoms cs_copy(const CsCtx* c, const CsDoms* d)
+{
+	CsDoms r;
+	r.val = (int32_t*)malloc(sizeof(int32_t) * (c->ndom > 0 ? c->ndom : 1));
+	r.size = (int32_t*)malloc(sizeof(int32_t) * c->m->V);
+	memcpy(r.val, d->val, sizeof(int32_t) * c->ndom);
+	memcpy(r.size, d->size, sizeof(int32_t) * c->m->V);
+	return r;
+}
+static void cs_free(CsDoms* d) { free(d->val); free(d->size); }
+static void cs_erase(const CsCtx* c, CsDoms* d, int var, int32_t value)
+{
+	int32_t* v = d->val + c->m->dom_off[var];
+	int n = d->size[var], i = 0;
+	while (i < n && v[i] != value) ++i;
+	if (i == n) return;
+	for (; i + 1 < n; ++i) v[i] = v[i + 1]; /* std::vector::erase keeps the order */
+	d->size[var] = n - 1;
+}
+
+/* solver.hpp:161-181 */
+static void cs_prefiltering(CsCtx* c, CsDoms* d)
+{
+	const OracleModel* m = c->m;
+	for (int ctr = 0; ctr < m->C; ++ctr) {
+		if (m->coff[ctr + 1] - m->coff[ctr] != 1) continue;
+		int index = m->cvars[m->coff[ctr]];
+		int n = d->size[index], nrem = 0;
+		int32_t* rem = (int32_t*)malloc(sizeof(int32_t) * (n > 0 ? n : 1));
+		for (int i = 0; i < n; ++i) {
+			int32_t value = d->val[m->dom_off[index] + i];
+			c->w->x[index] = value;
+			if (ctr_error(c->w, ctr) > 0.0) rem[nrem++] = value;
+		}
+		for (int i = 0; i < nrem; ++i) cs_erase(c, d, index, rem[i]);
+		free(rem);
+	}
+}
+
+/* solver.hpp:249-295 */
+static int cs_has_support(CsCtx* c, int ctr, int variable_id, int index_v, const CsDoms* d)
+{
+	const OracleModel* m = c->m;
+	int b = m->coff[ctr], e = m->coff[ctr + 1];
+	int* scope = (int*)malloc(sizeof(int) * (e - b + 1));
+	int ns = 0;
+	for (int i = b; i < e; ++i) if (m->cvars[i] > index_v && m->cvars[i] != variable_id) scope[ns++] = m->cvars[i];
+	if (ns == 0) { free(scope); return ctr_error(c->w, ctr) == 0.0; }
+	int* indexes = (int*)calloc(ns + 1, sizeof(int));
+	int fake_index = ns, found = 0;
+	while (indexes[fake_index] == 0) {
+		for (int i = 0; i < fake_index; ++i) c->w->x[scope[i]] = d->val[m->dom_off[scope[i]] + indexes[i]];
+		if (ctr_error(c->w, ctr) == 0.0) { found = 1; break; }
+		int changed, index = 0;
+		do {
+			changed = 0;
+			++indexes[index];
+			if (index < fake_index && indexes[index] >= d->size[scope[index]]) { indexes[index] = 0; changed = 1; ++index; }
+		} while (changed);
+	}
+	free(indexes); free(scope);
+	return found;
+}
+
+/* solver.hpp:186-243; returns a filtered copy of the domains */
+static CsDoms cs_ac3(CsCtx* c, int index_v, const CsDoms* in)
+{
+	const OracleModel* m = c->m;
+	CsDoms d = cs_copy(c, in);
+	int cap = 64, head = 0, tail = 0;
+	int* qc = (int*)malloc(sizeof(int) * cap); int* qv = (int*)malloc(sizeof(int) * cap);
+#define CS_PUSH(cc, vv) do { if (tail == cap) { cap *= 2; qc = (int*)realloc(qc, sizeof(int) * cap); qv = (int*)realloc(qv, sizeof(int) * cap); } qc[tail] = (cc); qv[tail] = (vv); ++tail; } while (0)
+	for (int r = m->v2c_off[index_v]; r < m->v2c_off[index_v + 1]; ++r) {
+		int ctr = m->v2c[r];
+		for (int i = m->coff[ctr]; i < m->coff[ctr + 1]; ++i) if (m->cvars[i] > index_v) CS_PUSH(ctr, m->cvars[i]);
+	}
+	int32_t* rem = (int32_t*)malloc(sizeof(int32_t) * (c->ndom > 0 ? c->ndom : 1));
+	while (head < tail) {
+		int ctr = qc[head], variable_id = qv[head];
+		++head;
+		int nrem = 0, n = d.size[variable_id];
+		for (int k = 0; k < n; ++k) {
+			int32_t value = d.val[m->dom_off[variable_id] + k];
+			c->w->x[variable_id] = value;
+			if (!cs_has_support(c, ctr, variable_id, index_v, &d)) {
+				rem[nrem++] = value;
+				for (int r = m->v2c_off[variable_id]; r < m->v2c_off[variable_id + 1]; ++r) {
+					int c_id = m->v2c[r];
+					if (c_id == ctr) continue;
+					for (int i = m->coff[c_id]; i < m->coff[c_id + 1]; ++i) {
+						int v_id = m->cvars[i];
+						if (v_id <= index_v || v_id == variable_id) continue;
+						int present = 0;
+						for (int q = head; q < tail && !present; ++q) present = qc[q] == c_id && qv[q] == v_id;
+						if (!present) CS_PUSH(c_id, v_id);
+					}
+				}
+			}
+		}
+		for (int i = 0; i < nrem; ++i) cs_erase(c, &d, variable_id, rem[i]);
+		if (d.size[variable_id] == 0) break; /* once a domain is empty, no need to go further */
+	}
+#undef CS_PUSH
+	free(rem); free(qc); free(qv);
+	return d;
+}
+
+static void cs_emit(CsCtx* c)
+{
+	const OracleModel* m = c->m;
+	if (c->cap > 0 && c->count >= c->cap) { c->truncated = 1; return; }
+	if (c->out_x) memcpy(c->out_x + (size_t)c->count * m->V, c->w->x, sizeof(int32_t) * m->V);
+	if (c->out_cost) {
+		/* solver.hpp:969-975: objective->cost(), negated back for a maximisation */
+		double cost = objective_cost(c->w);
+		c->out_cost[c->count] = m->obj_kind == GHOST_OBJ_LINEAR_MAXIMIZE ? -cost : cost;
+	}
+	++c->count;
+}
+
+/* solver.hpp:300-347 */
+static void cs_recurse(CsCtx* c, int index_v, const CsDoms* domains)
+{
+	const OracleModel* m = c->m;
+	if (index_v >= m->V) return;
+	CsDoms nd;
+	if (index_v > 0) {
+		nd = cs_ac3(c, index_v, domains);
+		for (int v = 0; v < m->V; ++v) if (nd.size[v] == 0) { cs_free(&nd); return; }
+	} else nd = cs_copy(c, domains); /* already filtered */
+	int next_var = index_v + 1;
+	for (int k = 0; k < nd.size[next_var] && !c->truncated; ++k) {
+		c->w->x[next_var] = nd.val[m->dom_off[next_var] + k];
+		if (next_var == m->V - 1) cs_emit(c);
+		else cs_recurse(c, next_var, &nd);
+	}
+	cs_free(&nd);
+}
+
+int oracle_complete_search(const OracleModel* m, int64_t max_solutions, int32_t* solutions, double* costs,
+                           int64_t* count, int32_t* truncated)
+{
+	CsCtx c;
+	memset(&c, 0, sizeof c);
+	c.m = m; c.w = walker_create(m, NULL, 0);
+	c.ndom = m->dom_off[m->V];
+	c.cap = max_solutions; c.out_x = solutions; c.out_cost = costs;
+	CsDoms d;
+	d.val = (int32_t*)malloc(sizeof(int32_t) * (c.ndom > 0 ? c.ndom : 1));
+	d.size = (int32_t*)malloc(sizeof(int32_t) * m->V);
+	memcpy(d.val, m->dom_given, sizeof(int32_t) * c.ndom);
+	for (int v = 0; v < m->V; ++v) d.size[v] = m->dom_off[v + 1] - m->dom_off[v];
+	memcpy(c.w->x, m->start, sizeof(int32_t) * m->V);
+	cs_prefiltering(&c, &d);
+	/* solver.hpp:957-982 */
+	for (int k = 0; k < d.size[0] && !c.truncated; ++k) {
+		c.w->x[0] = d.val[m->dom_off[0] + k];
+		CsDoms nd = cs_ac3(&c, 0, &d);
+		int empty = 0;
+		for (int v = 0; v < m->V; ++v) if (nd.size[v] == 0) empty = 1;
+		if (!empty) {
+			if (m->V == 1) cs_emit(&c); /* the reference indexes variable 1 here (undefined for V = 1) */
+			else cs_recurse(&c, 0, &nd);
+		}
+		cs_free(&nd);
+	}
+	cs_free(&d);
+	if (count) *count = c.count;
+	if (truncated) *truncated = c.truncated;
+	walker_destroy(c.w);
 	return 0;
 }

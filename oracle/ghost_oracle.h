@@ -68,6 +68,12 @@ int oracle_search(const OracleModel* m, const GhostSearchOpts* opts, uint64_t wa
  * objective cost (sign as the user sees it). */
 int oracle_check(const OracleModel* m, const int32_t* x, double* sat_error, double* objective);
 
+/* Solver::complete_search (include/solver.hpp:932-987 with 161-347): all solutions in the reference's
+ * enumeration order, with the cost it reports for each.  solutions [max][V] and costs [max] may be
+ * NULL (count only); max_solutions <= 0 means no cap — then the buffers must be large enough. */
+int oracle_complete_search(const OracleModel* m, int64_t max_solutions, int32_t* solutions, double* costs,
+                           int64_t* count, int32_t* truncated);
+
 /* resolve the -1 defaults like include/solver.hpp:451-473 */
 void oracle_resolve_opts(int32_t num_variables, GhostSearchOpts* opts);
 

@@ -464,6 +464,30 @@ extern "C" int ref_fast_search( const GhostModelDesc* d, double timeout_us, int 
 	catch( const std::exception& e ) { std::fprintf( stderr, "ref_fast_search: %s\n", e.what() ); return -1; }
 }
 
+/* ---- 2b. the reference's own complete search (include/solver.hpp:932-987) ------------------------ */
+extern "C" int ref_complete_search( const GhostModelDesc* d, int64_t max_solutions, int32_t* solutions, double* costs, int64_t* count )
+{
+	try
+	{
+		DescBuilder builder( std::make_shared<const DescCopy>( d ) );
+		Solver<DescBuilder> solver( builder );
+		Options options;
+		std::vector<double> final_costs;
+		std::vector<std::vector<int>> final_solutions;
+		bool found = solver.complete_search( final_costs, final_solutions, options );
+		int64_t n = static_cast<int64_t>( final_solutions.size() );
+		if( count ) *count = n;
+		int64_t keep = max_solutions > 0 && n > max_solutions ? max_solutions : n;
+		for( int64_t i = 0 ; i < keep ; ++i )
+		{
+			if( solutions ) for( int v = 0 ; v < d->num_variables ; ++v ) solutions[ i * d->num_variables + v ] = final_solutions[i][v];
+			if( costs ) costs[i] = final_costs[i];
+		}
+		return found ? 1 : 0;
+	}
+	catch( const std::exception& e ) { std::fprintf( stderr, "ref_complete_search: %s\n", e.what() ); return -1; }
+}
+
 #else /* REF_MAIN */
 /* ---- 3. executable: fast_search on a descriptor file; GHOST_BENCH / GHOST_TRACE decide what the
  *         reference itself prints.  usage: ref_bench desc.txt timeout_us parallel threads [custom_start] */

@@ -164,9 +164,8 @@ int main(int argc, char** argv)
 {
 	const bool gpu = argc > 1 && std::strcmp(argv[1], "gpu") == 0;
 	test_variable();
-	test_complete_search();
 	test_user_constraint_rejected();
-	if (gpu) test_gpu_searches();
+	if (gpu) { test_gpu_searches(); test_complete_search(); } // complete_search enumerates on the device
 	std::cout << (failures ? "FAILED" : "OK") << " (" << failures << " failures)\n";
 	return failures ? 1 : 0;
 }

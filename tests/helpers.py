@@ -3,6 +3,8 @@ from __future__ import annotations
 
 import numpy as np
 
+from ghost_b200 import modeldesc as md
+
 from ghost_b200 import problems
 from ghost_b200.modeldesc import NOT_A_CANDIDATE, ModelDesc
 
@@ -76,7 +78,86 @@ def to_int_or_sentinel(cand_delta_f64):
     return out
 
 
+# ---- small models for Solver::complete_search (every solution is enumerated; the reference's support
+# check is exponential in the scope, so scopes and domains stay tiny) -------------------------------
+def _cs_linear():
+    m = ModelDesc(permutation_problem=False, name="cs_linear")
+    for d in ([3, 0, 2, 1], [0, 1, 2, 3], [0, 1, 2], [1, 2, 3, 4], [0, 1]):   # first domain NOT ascending
+        m.add_variable(domain=d, index=0)
+    m.linear(md.LINEAR_EQ, [0, 1, 2], 5, [1, 1, 1])
+    m.linear(md.LINEAR_LEQ, [1, 3], 5, [1, 1])
+    m.linear(md.LINEAR_GEQ, [2, 3, 4], 3, [1, 1, 1])
+    m.linear(md.LINEAR_NEQ, [0, 4], 2, [1, 2])
+    m.linear(md.LINEAR_L, [0, 3], 6, [1, 1])
+    m.linear(md.LINEAR_G, [1, 2], 1, [1, 1])
+    return m
+
+
+def _cs_alldiff():
+    m = ModelDesc(permutation_problem=True, name="cs_alldiff")
+    for i in range(5):
+        m.add_variable(domain=[1, 2, 3, 4, 5], index=i)
+    m.all_different(range(5))
+    m.linear(md.LINEAR_EQ, [0, 1], 5, [1, 1])
+    m.linear(md.LINEAR_LEQ, [2, 3], 0, [1, -1])
+    return m
+
+
+def _cs_fix():
+    m = ModelDesc(permutation_problem=False, name="cs_fix")
+    for d in ([0, 1, 2, 3], [5, 3, 1], [0, 1, 2, 3], [2, 3, 4]):
+        m.add_variable(domain=d, index=0)
+    m.fix_value([1], 3)                 # unary: the reference prefilters it
+    m.fix_value([0, 2], 2)
+    m.linear(md.LINEAR_GEQ, [1, 3], 6, [1, 1])
+    m.all_different([0, 3])
+    return m
+
+
+def _cs_cop(maximize=True):
+    m = ModelDesc(permutation_problem=False, name="cs_cop_max" if maximize else "cs_cop_min")
+    for _ in range(6):
+        m.add_variable(domain=[0, 1], index=0)
+    m.linear(md.LINEAR_LEQ, range(6), 10, [3, 4, 5, 2, 6, 1])
+    m.linear(md.LINEAR_LEQ, range(6), 9, [2, 2, 4, 5, 1, 3])
+    m.linear(md.LINEAR_GEQ, [0, 1, 2], 1, [1, 1, 1])
+    m.linear_objective(range(6), [7, 3, 9, 4, 8, 2], maximize=maximize)
+    return m
+
+
+def _cs_free():
+    m = ModelDesc(permutation_problem=False, name="cs_free")
+    for d in ([0, 1, 2], [4, 2], [0, 1, 2], [7]):
+        m.add_variable(domain=d, index=0)
+    m.linear(md.LINEAR_NEQ, [0, 2], 2, [1, 1])   # variables 1 and 3 are in no constraint
+    return m
+
+
+def _cs_unsat():
+    m = ModelDesc(permutation_problem=False, name="cs_unsat")
+    for _ in range(4):
+        m.add_variable(domain=[0, 1, 2], index=0)
+    m.all_different([0, 1, 2, 3])                # four variables, three values
+    m.linear(md.LINEAR_EQ, [0, 1], 2, [1, 1])
+    return m
+
+
+COMPLETE_MODELS = {
+    "cs_linear": _cs_linear, "cs_alldiff": _cs_alldiff, "cs_fix": _cs_fix,
+    "cs_cop_max": lambda: _cs_cop(True), "cs_cop_min": lambda: _cs_cop(False),
+    "cs_free": _cs_free, "cs_unsat": _cs_unsat,
+    "cs_all_interval": lambda: problems.by_name("all_interval:5"),
+    "cs_queens4": lambda: problems.by_name("n_queens:4"),
+}
+
+
+# models whose full solution list from the reference is committed in tests/golden/complete_search.json
+COMPLETE_GOLDEN = list(COMPLETE_MODELS) + ["n_queens:6", "all_interval:7", "costas:5", "knapsack:12x3", "magic_square:3"]
+
+
 def model_by_name(name):
+    if name in COMPLETE_MODELS:
+        return COMPLETE_MODELS[name]()
     if name == "mixed":
         return mixed_model()
     if name == "mixed_perm":

@@ -1,7 +1,7 @@
 """The host C++ API (include/ghost/*.hpp — the reference's ModelBuilder / Model / Variable / Constraint /
 Objective / Options / Solver names) compiled with g++ and linked to libghost_b200.so.
-CPU: Variable semantics (the reference's own test expectations, tests/src/test_variable.cpp),
-complete_search enumeration, refusal of user-defined constraints.  GPU: Solver::fast_search end to end."""
+CPU: Variable semantics (the reference's own test expectations, tests/src/test_variable.cpp), refusal of
+user-defined constraints.  GPU: Solver::fast_search and Solver::complete_search end to end."""
 import os
 import subprocess
 
