@@ -1,5 +1,5 @@
 #!/usr/bin/env python
-"""Generate tests/golden/complete_search.json from the UNMODIFIED reference's Solver::complete_search
+"""Generate tests/golden/complete/solutions.json from the UNMODIFIED reference's Solver::complete_search
 (include/solver.hpp:932-987) through oracle/_ref/libghost_ref.so.  Run in the build container, where the
 reference tree is mounted:   python tests/golden/generate_complete.py
 For every model: the full list of solutions in the reference's order and the cost it reports for each.
@@ -26,7 +26,7 @@ def main():
         assert total == len(sol)
         out[name] = {"num_variables": desc.num_variables, "solutions": sol.tolist(), "costs": [float(c) for c in cost]}
         print(name, total, "solutions")
-    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "complete_search.json")
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "complete", "solutions.json")
     with open(path, "w") as f:
         json.dump(out, f, separators=(",", ":"))
     print("wrote", path, os.path.getsize(path), "bytes")

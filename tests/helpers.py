@@ -151,7 +151,7 @@ COMPLETE_MODELS = {
 }
 
 
-# models whose full solution list from the reference is committed in tests/golden/complete_search.json
+# models whose full solution list from the reference is committed in tests/golden/complete/solutions.json
 COMPLETE_GOLDEN = list(COMPLETE_MODELS) + ["n_queens:6", "all_interval:7", "costas:5", "knapsack:12x3", "magic_square:3"]
 
 

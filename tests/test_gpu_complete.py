@@ -11,7 +11,7 @@ from oracle import binding
 from tests.helpers import COMPLETE_GOLDEN, model_by_name
 
 pytestmark = pytest.mark.gpu
-GOLDEN = os.path.join(os.path.dirname(__file__), "golden", "complete_search.json")
+GOLDEN = os.path.join(os.path.dirname(__file__), "golden", "complete", "solutions.json")
 
 
 @pytest.fixture(scope="module")

@@ -1,5 +1,5 @@
 """Solver::complete_search: the C restatement (oracle/ghost_oracle.c) against the reference's committed
-solution lists (tests/golden/complete_search.json, generated from the unmodified reference by
+solution lists (tests/golden/complete/solutions.json, generated from the unmodified reference by
 tests/golden/generate_complete.py) and, where the reference is built, against the reference itself."""
 import json
 import os
@@ -10,7 +10,7 @@ import pytest
 from oracle import binding
 from tests.helpers import COMPLETE_GOLDEN, COMPLETE_MODELS, model_by_name
 
-GOLDEN = os.path.join(os.path.dirname(__file__), "golden", "complete_search.json")
+GOLDEN = os.path.join(os.path.dirname(__file__), "golden", "complete", "solutions.json")
 
 
 @pytest.fixture(scope="module")
