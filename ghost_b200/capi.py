@@ -63,6 +63,8 @@ def _load():
     lib.ghost_b200_search_stop_flag_import.argtypes = [vp, vp]
     lib.ghost_b200_search_noalloc.argtypes = [vp, C.POINTER(GhostSearchOptsStruct), i32, i32, vp, vp, vp]
     lib.ghost_b200_complete_search.argtypes = [vp, i64, C.POINTER(vp)]
+    lib.ghost_b200_search_devices.argtypes = [C.POINTER(GhostModelDescStruct), C.POINTER(GhostSearchOptsStruct), i32,
+                                              C.POINTER(GhostResultStruct)]
     lib.ghost_b200_solutions_count.argtypes = [vp]
     lib.ghost_b200_solutions_count.restype = i64
     lib.ghost_b200_solutions_truncated.argtypes = [vp]
@@ -178,6 +180,16 @@ class Model:
         `stream`.  Calls that overlap on the GPU race on the shared array."""
         _check(lib.ghost_b200_search_noalloc(self.h, C.byref(opts), int(epochs), int(iterations_per_epoch),
                                              d_best_x, d_summary, stream))
+
+
+def search_devices(desc: ModelDesc, opts: GhostSearchOptsStruct, device_count: int = 0):
+    """ghost_b200_search_devices: one blocking search over `device_count` GPUs of this process (0 = all)."""
+    s, keep = desc.to_struct()
+    sol = np.zeros(s.num_variables, dtype=np.int32)
+    res = GhostResultStruct()
+    res.solution = sol.ctypes.data_as(C.POINTER(C.c_int32))
+    _check(lib.ghost_b200_search_devices(C.byref(s), C.byref(opts), int(device_count), C.byref(res)))
+    return _result_dict(res, sol)
 
 
 def _result_dict(res, sol):

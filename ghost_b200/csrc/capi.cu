@@ -44,7 +44,8 @@ struct GhostSearch {
 	WalkerScalars* d_scalars = nullptr;
 	int* d_best_x = nullptr;
 	int* d_stop = nullptr;
-	int* d_stop_peer = nullptr;     // another process's stop flag, mapped over NVLink (CUDA IPC); used instead of d_stop when set
+	int* d_stop_peer = nullptr;     // another search's stop flag, mapped over NVLink; used instead of d_stop when set
+	bool stop_peer_is_ipc = false;  // mapped from another process (CUDA IPC) rather than a peer device of this one
 	unsigned long long* d_best_key = nullptr;
 	int* d_trace = nullptr; int* d_trace_len = nullptr; int trace_cap = 0;
 	cudaEvent_t ev0 = nullptr, ev1 = nullptr;
@@ -235,7 +236,7 @@ extern "C" int ghost_b200_eval_moves(GhostModel* gm, int32_t W, const int32_t* x
 extern "C" void ghost_b200_search_end(GhostSearch* s)
 {
 	if (!s) return;
-	if (s->d_stop_peer) cudaIpcCloseMemHandle(s->d_stop_peer);
+	if (s->d_stop_peer && s->stop_peer_is_ipc) cudaIpcCloseMemHandle(s->d_stop_peer);
 	cudaFree(s->d_state); cudaFree(s->d_scalars); cudaFree(s->d_best_x); cudaFree(s->d_stop);
 	cudaFree(s->d_best_key); cudaFree(s->d_trace); cudaFree(s->d_trace_len);
 	if (s->ev0) cudaEventDestroy(s->ev0);
@@ -359,6 +360,7 @@ extern "C" int ghost_b200_search_stop_flag_import(GhostSearch* s, const unsigned
 	void* ptr = nullptr;
 	CUDA_TRY(cudaIpcOpenMemHandle(&ptr, h, cudaIpcMemLazyEnablePeerAccess));
 	s->d_stop_peer = static_cast<int*>(ptr);
+	s->stop_peer_is_ipc = true;
 	return GHOST_B200_OK;
 }
 
@@ -505,6 +507,130 @@ extern "C" int ghost_b200_search(GhostModel* gm, const GhostSearchOpts* opts, Gh
 	rc = ghost_b200_search_result(s, res);
 	ghost_b200_search_end(s);
 	return rc;
+}
+
+// ---- one search over several GPUs of this process -------------------------------------------------
+// The reference's parallel_runs (include/solver.hpp:548-587: one SearchUnit per thread, the main thread
+// polling the futures, 594-644, and stopping everybody at the first solution, 651-653) across devices:
+// device d owns walkers [d*W, (d+1)*W) of one population; the calling thread launches every device's
+// epoch (the launches are asynchronous, so the GPUs run concurrently), then reads the 8-byte best keys
+// and takes their minimum; the walkers of devices 1.. poll and set device 0's stop flag through
+// peer-mapped memory (NVLink), so a solution found anywhere ends the epoch everywhere.
+extern "C" int ghost_b200_search_devices(const GhostModelDesc* desc, const GhostSearchOpts* opts, int32_t device_count,
+                                         GhostResult* res)
+{
+	if (!desc || !opts || !res) return set_error(GHOST_B200_ERR_INVALID, "null argument to search_devices");
+	int visible = 0, home = 0;
+	CUDA_TRY(cudaGetDeviceCount(&visible));
+	CUDA_TRY(cudaGetDevice(&home));
+	const int n = device_count <= 0 ? visible : device_count;
+	if (n > visible) return set_error(GHOST_B200_ERR_INVALID, "search_devices: " + std::to_string(n) + " devices asked, " + std::to_string(visible) + " visible");
+	std::vector<GhostModel*> gm(n, nullptr);
+	std::vector<GhostSearch*> ss(n, nullptr);
+	std::vector<cudaEvent_t> ev0(n, nullptr), ev1(n, nullptr);
+	auto cleanup = [&]() {
+		for (int d = 0; d < n; ++d) {
+			cudaSetDevice(d);
+			if (ss[d]) ghost_b200_search_end(ss[d]);
+			if (gm[d]) ghost_b200_model_destroy(gm[d]);
+			if (ev0[d]) cudaEventDestroy(ev0[d]);
+			if (ev1[d]) cudaEventDestroy(ev1[d]);
+		}
+		cudaSetDevice(home);
+	};
+#define DEV_TRY(call) do { int _rc = (call); if (_rc != GHOST_B200_OK) { std::string keep = g_last_error; cleanup(); g_last_error = keep; return _rc; } } while (0)
+#define DEV_CUDA(expr) do { cudaError_t _e = (expr); if (_e != cudaSuccess) { cleanup(); return set_error(GHOST_B200_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(_e)); } } while (0)
+	const auto t_begin = std::chrono::steady_clock::now();
+	int W = 0;
+	for (int d = 0; d < n; ++d) {
+		DEV_CUDA(cudaSetDevice(d));
+		DEV_TRY(ghost_b200_model_create(desc, &gm[d]));
+		GhostSearchOpts o = *opts;
+		if (d > 0) o.number_walkers = W;
+		o.first_walker_id = opts->first_walker_id + (uint64_t)d * (uint64_t)W;
+		DEV_TRY(ghost_b200_search_begin(gm[d], &o, &ss[d]));
+		if (d == 0) W = ss[0]->walkers;
+		DEV_CUDA(cudaEventCreate(&ev0[d]));
+		DEV_CUDA(cudaEventCreate(&ev1[d]));
+		if (d > 0) {
+			int can = 0;
+			DEV_CUDA(cudaDeviceCanAccessPeer(&can, d, 0));
+			if (can) {
+				cudaError_t e = cudaDeviceEnablePeerAccess(0, 0);
+				if (e == cudaErrorPeerAccessAlreadyEnabled) { cudaGetLastError(); e = cudaSuccess; }
+				if (e == cudaSuccess) ss[d]->d_stop_peer = ss[0]->d_stop; // else: this device stops at epoch boundaries only
+				else cudaGetLastError();
+			}
+		}
+	}
+	const bool optimization = gm[0]->low.dev.objective != GHOST_OBJ_NONE;
+	int epoch = ss[0]->opts.epoch_iterations > 0 ? ss[0]->opts.epoch_iterations : 256;
+	const double budget_us = ss[0]->opts.timeout_us;
+	int64_t done_iterations = 0, launches = 0;
+	double kernel_ms = 0.0;
+	std::vector<uint64_t> key(n, ~0ull);
+	for (;;) {
+		for (int d = 0; d < n; ++d) {
+			DEV_CUDA(cudaSetDevice(d));
+			cudaEventRecord(ev0[d], nullptr);
+			DEV_TRY(ghost_b200_search_epoch(ss[d], epoch, nullptr));
+			cudaEventRecord(ev1[d], nullptr);
+		}
+		float slowest = 0.f;
+		uint64_t best = ~0ull;
+		for (int d = 0; d < n; ++d) {
+			DEV_CUDA(cudaSetDevice(d));
+			DEV_TRY(ghost_b200_search_best_key(ss[d], &key[d])); // synchronises the device
+			float ms = 0.f;
+			cudaEventElapsedTime(&ms, ev0[d], ev1[d]);
+			slowest = std::max(slowest, ms);
+			best = std::min(best, key[d] >> 24);
+		}
+		kernel_ms += slowest;
+		launches += n;
+		done_iterations += epoch;
+		const double elapsed = std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now() - t_begin).count();
+		const bool solved = !optimization && best == 0;
+		if (solved && opts->stop_on_first_solution) break;
+		if (budget_us > 0 && elapsed >= budget_us) break;
+		if (opts->max_iterations > 0 && done_iterations >= opts->max_iterations) break;
+		if (budget_us <= 0 && opts->max_iterations <= 0) break;
+		if (budget_us > 0 && slowest > 0.f) {
+			const double remaining_ms = (budget_us - elapsed) / 1000.0, per_it = slowest / epoch;
+			const int fit = (int)std::max(1.0, std::min(4096.0, 0.5 * remaining_ms / per_it));
+			epoch = std::min(std::max(fit, 1), std::max(epoch * 2, 16));
+		}
+	}
+	// the winner: lowest quality, lowest device among equals (solver.hpp:665-723 picks the first best thread)
+	int win = 0;
+	for (int d = 1; d < n; ++d) if ((key[d] >> 24) < (key[win] >> 24)) win = d;
+	const int V = gm[0]->low.V;
+	int32_t* solution = res->solution;
+	std::vector<int32_t> scratch((size_t)V);
+	GhostCounters total{};
+	GhostResult winner{};
+	int walkers = 0;
+	for (int d = 0; d < n; ++d) {
+		DEV_CUDA(cudaSetDevice(d));
+		GhostResult r{};
+		r.solution = d == win ? solution : scratch.data();
+		DEV_TRY(ghost_b200_search_result(ss[d], &r));
+		add_counters(total, r.total);
+		walkers += r.walkers;
+		if (d == win) winner = r;
+	}
+	*res = winner;
+	res->solution = solution;
+	res->winner_walker = win * W + winner.winner_walker;
+	res->total = total;
+	res->walkers = walkers;
+	res->kernel_time_us = kernel_ms * 1000.0;
+	res->kernel_launches = launches;
+	res->search_time_us = std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now() - t_begin).count();
+	cleanup();
+#undef DEV_TRY
+#undef DEV_CUDA
+	return GHOST_B200_OK;
 }
 
 // ---- private hooks for noalloc.cu (declared in noalloc_internal.h) ------------------------------

@@ -32,5 +32,6 @@ namespace ghost
 		int threads_per_walker = 0;             //!< 0 = chosen from the model (32, 64, 128 or 256)
 		int epoch_iterations = 0;               //!< iterations per kernel launch; 0 = adaptive
 		std::uint64_t seed = 0;                 //!< Philox key; 0 = drawn from std::random_device
+		int number_gpus = 1;                    //!< GPUs of this process to search on; 0 = every visible one
 	};
 }

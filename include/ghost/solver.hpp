@@ -144,7 +144,9 @@ namespace ghost
 			final_solution.assign(_model.variables.size(), 0);
 			GhostResult r{};
 			r.solution = final_solution.data();
-			const int rc = ghost_b200_search(gm, &o, &r);
+			// one GPU: the model handle created above; several: walkers sharded over the devices, one stop flag
+			const int rc = options.number_gpus == 1 ? ghost_b200_search(gm, &o, &r)
+			                                        : ghost_b200_search_devices(&L.desc, &o, options.number_gpus, &r);
 			ghost_b200_model_destroy(gm);
 			if (rc != GHOST_B200_OK) throw std::runtime_error(ghost_b200_last_error());
 

@@ -194,6 +194,18 @@ int ghost_b200_eval_moves_device(GhostModel* model, int32_t num_walkers,
  * SearchUnits (include/solver.hpp:517-524, 552-587). */
 int ghost_b200_search(GhostModel* model, const GhostSearchOpts* opts, GhostResult* result);
 
+/* The same blocking search over `device_count` GPUs of this process (devices 0..device_count-1;
+ * 0 = every visible device): what Options::parallel_runs is to threads (include/solver.hpp:548-587,
+ * 594-644, 651-653).  Device d runs walkers [d*W, (d+1)*W) of one population (W = opts->number_walkers, or
+ * what fills one GPU); after every epoch the best keys of the devices are reduced to their minimum by the
+ * calling thread; the walkers of all devices poll one stop flag (device 0's, peer-mapped over NVLink),
+ * so the first solution stops every GPU inside the epoch.  Takes the descriptor because a lowered model
+ * lives on one device.  result->winner_walker is the global walker index, totals are summed over devices,
+ * kernel_time_us adds each epoch's slowest device.  (One process per GPU instead: the stepwise calls
+ * below + ghost_b200_search_export_key with an NCCL allreduce-min, see ghost_b200/multi.py.) */
+int ghost_b200_search_devices(const GhostModelDesc* desc, const GhostSearchOpts* opts, int32_t device_count,
+                              GhostResult* result);
+
 /* Stepwise form used by the multi-GPU driver and the benchmark: begin -> epoch* -> result -> end.
  * begin allocates the walker population and runs the initial sampling
  * (search_unit.hpp:711-717); each epoch advances every live walker by `iterations` iterations of

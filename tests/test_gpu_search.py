@@ -130,3 +130,46 @@ def test_blocking_search_cop_best_cost(oracle_built):
     best = max(-port.search(o, w, 2000)["best_opt"] for w in range(8))
     assert res["final_cost"] >= best
     model.close()
+
+
+def _device_count():
+    import torch
+    return torch.cuda.device_count()
+
+
+@pytest.mark.gpu
+def test_search_devices_all_visible_gpus(oracle_built):
+    """ghost_b200_search_devices over every visible GPU (one on the round-end box, N under gpurun --gpus N):
+    the walkers are one population sharded by device, so the run with D devices of W walkers visits exactly
+    the trajectories of walkers 0..D*W-1 — its summed counters equal those of D single-device searches with
+    first_walker_id = d*W, and the returned solution passes the reference's checker (oracle)."""
+    from ghost_b200 import capi
+    desc = model_by_name("magic_square:5")
+    D = _device_count()
+    W, iters = 64, 300
+    opts = default_opts(seed=11, number_walkers=W, stop_on_first_solution=0, max_iterations=iters, epoch_iterations=100)
+    r = capi.search_devices(desc, opts, 0)
+    assert r["walkers"] == D * W
+    want = None
+    for d in range(D):
+        o = default_opts(seed=11, number_walkers=W, stop_on_first_solution=0, max_iterations=iters, epoch_iterations=100,
+                         first_walker_id=d * W)
+        m = capi.Model(desc)
+        one = m.search(o)
+        m.close()
+        want = one["total"] if want is None else {k: want[k] + v for k, v in one["total"].items()}
+    assert r["total"] == want
+    if r["found"]:
+        assert oracle_built.OraclePort(desc).check(r["solution"])[0] == 0.0
+    with pytest.raises(capi.GhostError):
+        capi.search_devices(desc, opts, D + 1)
+
+
+@pytest.mark.gpu
+def test_search_devices_stops_on_first_solution():
+    from ghost_b200 import capi
+    desc = model_by_name("magic_square:6")
+    r = capi.search_devices(desc, default_opts(seed=5, timeout_us=20e6), 0)
+    assert r["found"] and r["final_cost"] == 0.0
+    x = r["solution"].reshape(6, 6)
+    assert sorted(r["solution"].tolist()) == list(range(1, 37)) and set(x.sum(0)) == {111} and set(x.sum(1)) == {111}
