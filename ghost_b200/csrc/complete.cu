@@ -17,6 +17,7 @@
 //   LinearEquation{Eq,...}  the interval [sum of assigned terms + min of the free terms,
 //                           ... + max of the free terms] misses the satisfying set of its compute_error
 //                           (linear_equation_eq.cpp:54-57, _neq/_leq/_geq/_l/_g.cpp alike);
+//   AllEqual                two assigned variables of its scope differ (all_equal.cpp:47-60);
 //   FixValue                an assigned variable differs from the value (fix_value.cpp:46-52);
 //   AllDifferentAbsDiff     two complete adjacent differences are equal (extension kind).
 // When a constraint's last variable is assigned the test is exact, hence every leaf is a solution and
@@ -72,6 +73,9 @@ __device__ bool cs_feasible(const CsModel& M, const int* x, int k)
 		} else if (kind == GHOST_KIND_ALL_DIFFERENT) {
 			const int xk = x[k];
 			for (int i = b; i < e; ++i) { const int v = M.cvar[i]; if (v < k && x[v] == xk) return false; }
+		} else if (kind == GHOST_KIND_ALL_EQUAL) {
+			const int xk = x[k];
+			for (int i = b; i < e; ++i) { const int v = M.cvar[i]; if (v < k && x[v] != xk) return false; }
 		} else if (kind == GHOST_KIND_FIX_VALUE) {
 			if (x[k] != M.param[c]) return false;
 		} else if (kind == GHOST_KIND_ALL_DIFFERENT_ABS_DIFF) {

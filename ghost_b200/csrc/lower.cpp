@@ -21,7 +21,8 @@
 namespace ghost_b200 {
 
 static bool is_linear(int k) { return k >= GHOST_KIND_LINEAR_EQ && k <= GHOST_KIND_LINEAR_G; }
-static bool is_alldiff_like(int k) { return k == GHOST_KIND_ALL_DIFFERENT || k == GHOST_KIND_ALL_DIFFERENT_ABS_DIFF; }
+// kinds that keep a value-count table
+static bool is_alldiff_like(int k) { return k == GHOST_KIND_ALL_DIFFERENT || k == GHOST_KIND_ALL_DIFFERENT_ABS_DIFF || k == GHOST_KIND_ALL_EQUAL; }
 
 static bool as_int(double d, int64_t* out)
 {
@@ -76,7 +77,8 @@ int lower_model(const GhostModelDesc* d, LoweredModel* out, std::string* why)
 	// ---- constraints
 	const int nnz = d->ctr_offset[C];
 	std::vector<int32_t> kind(C), rhs(C, 0), cnt_tab(C, 0), c2v_off(C + 1, 0), c2v(nnz), ent_ctr(nnz), ent_coef(nnz, 0);
-	std::vector<int32_t> cnt_owner;
+	std::vector<int32_t> cnt_owner, cnt_lo(C, 0), cnt_n(C, 0);
+	bool has_all_equal = false;
 	std::vector<std::vector<std::pair<int, int>>> rows(V); // (constraint, coefficient|position)
 	int cnt_total = 0;
 	int64_t error_bound = 0;
@@ -158,9 +160,11 @@ int lower_model(const GhostModelDesc* d, LoweredModel* out, std::string* why)
 			if (size > (1 << 20)) return fail(GHOST_B200_ERR_UNSUPPORTED, "constraint " + std::to_string(c) + ": value range too wide for a dense count table");
 			if (n > 65535) return fail(GHOST_B200_ERR_UNSUPPORTED, "AllDifferent scope beyond 65535");
 			cnt_tab[c] = static_cast<int32_t>(cnt_total - base);
+			cnt_lo[c] = cnt_total; cnt_n[c] = static_cast<int32_t>(size);
+			if (k == GHOST_KIND_ALL_EQUAL) { has_all_equal = true; if (n > 32767) return fail(GHOST_B200_ERR_UNSUPPORTED, "AllEqual scope beyond 32767"); }
 			for (int64_t t = 0; t < size; ++t) cnt_owner.push_back(c);
 			cnt_total += static_cast<int>(size);
-			error_bound += n * (n - 1) / 2;
+			error_bound += k == GHOST_KIND_ALL_EQUAL ? n : n * (n - 1) / 2;
 		}
 	}
 	if (error_bound >= (1LL << 31) - 1)
@@ -222,7 +226,7 @@ int lower_model(const GhostModelDesc* d, LoweredModel* out, std::string* why)
 	o.v2c_off = put(v2c_off); o.v2c = put(v2c);
 	o.kind = put(kind); o.rhs = put(rhs); o.cnt_tab = put(cnt_tab);
 	o.c2v_off = put(c2v_off); o.c2v = put(c2v); o.ent_ctr = put(ent_ctr); o.ent_coef = put(ent_coef);
-	o.cnt_owner = put(cnt_owner);
+	o.cnt_owner = put(cnt_owner); o.cnt_lo = put(cnt_lo); o.cnt_n = put(cnt_n);
 	o.obj_coef = put(obj_coef);
 	// ELL rows for the hot loop: one fixed-stride row per variable, class / error weights packed in
 	// the entry so that the candidate loop needs no per-constraint global lookups for linear kinds.
@@ -258,6 +262,7 @@ int lower_model(const GhostModelDesc* d, LoweredModel* out, std::string* why)
 				case GHOST_KIND_ALL_DIFFERENT: cls = GB_CLS_ALLDIFF; break;
 				case GHOST_KIND_FIX_VALUE: cls = GB_CLS_FIX; break;
 				case GHOST_KIND_ALL_DIFFERENT_ABS_DIFF: cls = GB_CLS_ABSDIFF; break;
+				case GHOST_KIND_ALL_EQUAL: cls = GB_CLS_ALLEQ; break;
 				default: cls = GB_CLS_ZERO; break;
 				}
 				int universal = (c2v_off[c + 1] - c2v_off[c] == V) ? 1 : 0;
@@ -317,6 +322,7 @@ int lower_model(const GhostModelDesc* d, LoweredModel* out, std::string* why)
 	m.max_candidates = m.permutation ? V : max_dom;
 	m.max_degree = std::max(1, max_degree);
 	m.has_abs_diff = has_abs_diff ? 1 : 0;
+	m.has_all_equal = has_all_equal ? 1 : 0;
 	m.ell_stride = stride;
 	m.ell_eq_stride = stride_eq;
 	m.eq_only = eq_only ? 1 : 0;

@@ -22,6 +22,7 @@ struct BlobOffsets {
 	int c2v_off, c2v, ent_ctr; // ent_ctr[i] = constraint owning scope entry i
 	int ent_coef;              // coefficient of scope entry i (linear), 0 otherwise
 	int cnt_owner;             // [cnt_total] constraint owning count-table slot t
+	int cnt_lo, cnt_n;         // [C] first slot and number of slots of the constraint's count table (0, 0: none)
 	int obj_coef;              // dense [V]
 	int ell;                   // [V][ell_stride] int2 rows: {c | cls<<20 | w<<24 | universal<<27, coef|pos}; c=0xFFFFF ends a row
 	int ell_eq;                // same rows for the LinearEq-only paths, 4 bytes per entry: low half = byte offset of
@@ -45,6 +46,7 @@ struct DevModel {
 	int max_candidates;        // max over variables of candidate slots (V for permutation problems)
 	int max_degree;            // max #constraints touching one variable
 	int has_abs_diff;
+	int has_all_equal;
 	int ell_stride;            // entries per ELL row (max number of non-static constraints of a variable)
 	int ell_eq_stride;         // ell_stride rounded up to 1, 2 or a multiple of 4: a row is one 32/64/128-bit load
 	int eq_only;               // every constraint is LINEAR_EQ or static (and ids / coefficients fit the packed
@@ -59,7 +61,7 @@ struct DevModel {
 enum : int { GB_KIND_STATIC = 16 };
 
 // ELL entry encoding (word 0)
-enum : int { GB_ELL_END = 0xFFFFF, GB_CLS_LINEAR = 0, GB_CLS_ALLDIFF = 1, GB_CLS_FIX = 2, GB_CLS_ABSDIFF = 3, GB_CLS_ZERO = 4 };
+enum : int { GB_ELL_END = 0xFFFFF, GB_CLS_LINEAR = 0, GB_CLS_ALLDIFF = 1, GB_CLS_FIX = 2, GB_CLS_ABSDIFF = 3, GB_CLS_ZERO = 4, GB_CLS_ALLEQ = 5 };
 enum : int { GB_MARK_SKIP = 1 << 20 };
 
 // Per-walker shared-memory layout, byte offsets from the walker's base.

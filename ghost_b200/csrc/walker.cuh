@@ -261,6 +261,48 @@ __device__ __forceinline__ int absdiff_delta(const MV& mv, const WS& s, int c, i
 	return absdiff_delta(mv.m.blob, mv.m.o.c2v_off, mv.m.o.c2v, mv.m.o.cnt_tab, s.x, s.cnt32, c, pa, na, pb, nb);
 }
 
+// AllEqual (src/global_constraints/all_equal.cpp:47-95): error = scope size - largest count; the delta of
+// a change is (largest count before) - (largest count after).  The constraint's state word keeps the
+// largest count (low half) and the largest count once ONE holder of it is set aside (high half:
+// equal to it when two values share the lead), so the largest count after moving one variable from
+// value a to value d != a is max(cnt[d] + 1, base) with base = the lead unless a held it alone.
+__device__ __forceinline__ int alleq_max1(int state) { return state & 0xFFFF; }
+__device__ __forceinline__ int alleq_base(int state, int cnt_a)
+{
+	const int max1 = state & 0xFFFF, max2 = state >> 16;
+	return cnt_a == max1 ? max(max2, max1 - 1) : max1;
+}
+template <class WS>
+__device__ __forceinline__ int alleq_single_delta(const WS& s, int state, int tab, int a, int d)
+{
+	return alleq_max1(state) - max(s.cnt(tab + d) + 1, alleq_base(state, s.cnt(tab + a)));
+}
+// Recompute the state word and the error of AllEqual constraint c from its count table (one warp).
+template <int T, class WS>
+__device__ inline void alleq_refresh(const DevModel& m, const WS& s, int c)
+{
+	if (Group<T>::warp() != 0) return;
+	const int lane = threadIdx.x & 31;
+	const int lo = __ldg(m.blob + m.o.cnt_lo + c), n = __ldg(m.blob + m.o.cnt_n + c);
+	int m1 = 0, k1 = 0, m2 = 0; // largest count, number of values holding it, largest count below it
+	for (int t = lane; t < n; t += 32) {
+		const int v = s.cnt(lo + t);
+		if (v > m1) { m2 = m1; m1 = v; k1 = 1; } else if (v == m1) ++k1; else if (v > m2) m2 = v;
+	}
+#pragma unroll
+	for (int off = 16; off > 0; off >>= 1) {
+		const int om1 = __shfl_xor_sync(0xffffffffu, m1, off), ok1 = __shfl_xor_sync(0xffffffffu, k1, off), om2 = __shfl_xor_sync(0xffffffffu, m2, off);
+		if (om1 == m1) { k1 += ok1; m2 = max(m2, om2); }
+		else if (om1 > m1) { m2 = max(m1, om2); m1 = om1; k1 = ok1; }
+		else m2 = max(m2, om1);
+	}
+	if (lane == 0) {
+		const int scope = __ldg(m.blob + m.o.c2v_off + c + 1) - __ldg(m.blob + m.o.c2v_off + c);
+		s.T_of(c) = m1 | ((k1 > 1 ? m1 : m2) << 16);
+		s.err_of(c) = scope - m1;
+	}
+}
+
 // ---------------------------------------------------------------------------------------------
 // Delta of ONE constraint for a change of variable va (row entry second field = ea) to na, and,
 // when vb >= 0, of vb (second field eb) to nb.  Restates optional_delta_error of the stock
@@ -306,6 +348,23 @@ __device__ inline int constraint_delta(const MV& mv, const WS& s, int c, int va,
 		return d;
 	}
 	if (kind == GHOST_KIND_ALL_DIFFERENT_ABS_DIFF) return absdiff_delta(mv, s, c, ea, na, vb >= 0 ? eb : -1, nb);
+	if (kind == GHOST_KIND_ALL_EQUAL) {
+		const int tab = mv.cnt_tab(c), oa = s.x[va];
+		if (vb >= 0) {
+			const int ob = s.x[vb];
+			if (na == ob && nb == oa) return 0; // a swap inside the scope leaves the counts alone
+			// general two-change case (never produced by the search): rescan the table with the changes applied
+			const int lo = mv.ld(mv.m.o.cnt_lo, c), n = mv.ld(mv.m.o.cnt_n, c);
+			int best = 0;
+			for (int t = 0; t < n; ++t) {
+				const int key = lo + t - tab;
+				best = max(best, s.cnt(lo + t) - (key == oa) - (key == ob) + (key == na) + (key == nb));
+			}
+			return alleq_max1(s.T_of(c)) - best;
+		}
+		if (na == oa) return 0;
+		return alleq_single_delta(s, s.T_of(c), tab, oa, na);
+	}
 	return 0; // PURE_OPTIMIZATION
 }
 
@@ -336,7 +395,7 @@ __device__ inline int recompute_all(const DevModel& m, const WS& s, int* red)
 			int xu = s.x[u];
 			if (kind_is_linear(kind)) val = mv.ld(m.o.ent_coef, i) * xu;
 			else if (kind == GHOST_KIND_FIX_VALUE) val = abs(xu - mv.rhs(c));
-			else if (kind == GHOST_KIND_ALL_DIFFERENT) s.cnt_add(mv.cnt_tab(c) + xu, 1);
+			else if (kind == GHOST_KIND_ALL_DIFFERENT || kind == GHOST_KIND_ALL_EQUAL) s.cnt_add(mv.cnt_tab(c) + xu, 1);
 			else if (kind == GHOST_KIND_ALL_DIFFERENT_ABS_DIFF) {
 				if (i + 1 < mv.scope_begin(c + 1)) s.cnt_add(mv.cnt_tab(c) + abs(s.x[mv.scope_var(i + 1)] - xu), 1);
 			}
@@ -366,7 +425,14 @@ __device__ inline int recompute_all(const DevModel& m, const WS& s, int* red)
 	}
 	for (int t = tid; t < m.cnt_total; t += T) {
 		int n = s.cnt(t);
-		if (n > 1) atomicAdd(&s.err_of(mv.ld(m.o.cnt_owner, t)), binom2(n));
+		if (n > 1) {
+			const int owner = mv.ld(m.o.cnt_owner, t);
+			if (!m.has_all_equal || mv.kind(owner) != GHOST_KIND_ALL_EQUAL) atomicAdd(&s.err_of(owner), binom2(n));
+		}
+	}
+	if (m.has_all_equal) {
+		G::sync();
+		for (int c = 0; c < m.C; ++c) if (mv.kind(c) == GHOST_KIND_ALL_EQUAL) alleq_refresh<T>(m, s, c);
 	}
 	G::sync();
 	int part = 0;
@@ -598,6 +664,10 @@ __device__ inline int hoist_variable(const DevModel& m, const WS& s, int v, int*
 			bias -= abs(xv - kk);
 		} else if (cls == GB_CLS_ABSDIFF) {
 			h.y = e.y;
+		} else if (cls == GB_CLS_ALLEQ) {
+			const int tab = mv.cnt_tab(c), state = s.T_of(c);
+			h.y = tab; h.z = alleq_base(state, s.cnt(tab + xv));
+			bias += alleq_max1(state);
 		}
 		if (writer) {
 			s.hoist[nh] = h;
@@ -680,6 +750,7 @@ __device__ __forceinline__ int hoisted_term(const MV& mv, const WS& s, const int
 	if (type == GB_CLS_ALLDIFF) return s.cnt(h.y + d);
 	if (type == GB_CLS_FIX) return abs(d - h.y);
 	if (type == GB_CLS_ABSDIFF) return absdiff_delta(mv, s, h.x >> 8, h.y, d, -1, 0);
+	if (type == GB_CLS_ALLEQ) return -max(s.cnt(h.y + d) + 1, h.z);
 	return 0;
 }
 
@@ -724,6 +795,7 @@ __device__ __forceinline__ bool candidate_sum(const DevModel& m, const MV& mv, c
 				int kk = mv.rhs(c);
 				sum += abs(xv - kk) - abs(xj - kk);
 			} else if (cls == GB_CLS_ABSDIFF) sum += absdiff_delta(mv, s, c, e.y, xv, -1, 0);
+			else if (cls == GB_CLS_ALLEQ) sum += alleq_single_delta(s, st.x, mv.cnt_tab(c), xj, xv);
 		} else {
 			// both variables in scope: {v,j} -> {x_j,x_v} (search_unit.hpp:872-874); replace the
 			// single-variable delta already added from the hoisted entry
@@ -734,6 +806,7 @@ __device__ __forceinline__ bool candidate_sum(const DevModel& m, const MV& mv, c
 			} else if (cls == GB_CLS_ALLDIFF) sum -= s.cnt(h.y + xj) - h.z;
 			else if (cls == GB_CLS_FIX) sum += abs(xv - h.y) - abs(xj - h.y);
 			else if (cls == GB_CLS_ABSDIFF) sum += absdiff_delta(mv, s, c, h.y, xj, e.y, xv) - absdiff_delta(mv, s, c, h.y, xj, -1, 0);
+			else if (cls == GB_CLS_ALLEQ) sum += max(s.cnt(h.y + xj) + 1, h.z) - alleq_max1(st.x); // the swap changes nothing
 		}
 	}
 	*out = sum;
@@ -1028,7 +1101,7 @@ __device__ inline void apply_move(const DevModel& m, const WS& s, int v, int new
 			}
 			delta = constraint_delta(mv, s, c, v, e.y, nv_new, both ? j : -1, eb, xv);
 			int kind = mv.kind(c);
-			if (kind == GHOST_KIND_ALL_DIFFERENT) {
+			if (kind == GHOST_KIND_ALL_DIFFERENT || kind == GHOST_KIND_ALL_EQUAL) {
 				if (!both && nv_new != xv) { int tab = mv.cnt_tab(c); s.cnt_add(tab + xv, -1); s.cnt_add(tab + nv_new, +1); }
 			} else if (kind_is_linear(kind)) {
 				s.T_of(c) += e.y * (nv_new - xv) + (both ? eb * (xv - xj) : 0);
@@ -1040,7 +1113,7 @@ __device__ inline void apply_move(const DevModel& m, const WS& s, int v, int new
 			if (s.mark_of(c) != 0) { s.upd[2 * k] = -1; continue; } // shared with v: handled above
 			delta = constraint_delta(mv, s, c, j, e.y, xv, -1, 0, 0);
 			int kind = mv.kind(c);
-			if (kind == GHOST_KIND_ALL_DIFFERENT) {
+			if (kind == GHOST_KIND_ALL_DIFFERENT || kind == GHOST_KIND_ALL_EQUAL) {
 				if (xv != xj) { int tab = mv.cnt_tab(c); s.cnt_add(tab + xj, -1); s.cnt_add(tab + xv, +1); }
 			} else if (kind_is_linear(kind)) s.T_of(c) += e.y * (xv - xj);
 			s.err_of(c) += delta;
@@ -1053,6 +1126,13 @@ __device__ inline void apply_move(const DevModel& m, const WS& s, int v, int new
 		if (c < 0 || delta == 0) continue;
 		int b = mv.scope_begin(c), e = mv.scope_begin(c + 1);
 		for (int i = b + tid; i < e; i += T) atomicAdd(&s.err_var[mv.scope_pos(i)], delta);
+	}
+	if (m.has_all_equal) {
+		// the count tables changed: new lead counts of the AllEqual constraints among the affected ones
+		for (int k = 0; k < naff; ++k) {
+			const int c = s.upd[2 * k];
+			if (c >= 0 && mv.kind(c) == GHOST_KIND_ALL_EQUAL) alleq_refresh<T>(m, s, c);
+		}
 	}
 	if (tid == 0) {
 		s.x[v] = nv_new;

@@ -23,6 +23,7 @@ LINEAR_G = 6
 FIX_VALUE = 7
 PURE_OPTIMIZATION = 8
 ALL_DIFFERENT_ABS_DIFF = 9
+ALL_EQUAL = 10
 KIND_USER = 100
 
 OBJ_NONE = 0
@@ -179,6 +180,9 @@ class ModelDesc:
     # -- stock global constraints --
     def all_different(self, variables):
         self.constraints.append((ALL_DIFFERENT, list(variables), None, 0.0))
+
+    def all_equal(self, variables):
+        self.constraints.append((ALL_EQUAL, list(variables), None, 0.0))
 
     def all_different_abs_diff(self, variables):
         self.constraints.append((ALL_DIFFERENT_ABS_DIFF, list(variables), None, 0.0))

@@ -52,6 +52,8 @@ typedef enum GhostConstraintKind {
 	GHOST_KIND_ALL_DIFFERENT_ABS_DIFF = 9, /* extension (no stock counterpart): all |x[i+1]-x[i]|
 	                                          over the scope, in scope order, pairwise different;
 	                                          error = sum_values C(count,2)                     */
+	GHOST_KIND_ALL_EQUAL = 10,        /* src/global_constraints/all_equal.cpp:47-95: error = scope size
+	                                     minus the count of the most frequent value                */
 	GHOST_KIND_USER = 100
 } GhostConstraintKind;
 

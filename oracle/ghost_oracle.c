@@ -91,9 +91,9 @@ static int cmp_i32(const void* a, const void* b)
 	return (x > y) - (x < y);
 }
 
-static int is_alldiff_like(int32_t kind)
+static int is_alldiff_like(int32_t kind) /* kinds that keep a value-count table */
 {
-	return kind == GHOST_KIND_ALL_DIFFERENT || kind == GHOST_KIND_ALL_DIFFERENT_ABS_DIFF;
+	return kind == GHOST_KIND_ALL_DIFFERENT || kind == GHOST_KIND_ALL_DIFFERENT_ABS_DIFF || kind == GHOST_KIND_ALL_EQUAL;
 }
 static int is_linear(int32_t kind) { return kind >= GHOST_KIND_LINEAR_EQ && kind <= GHOST_KIND_LINEAR_G; }
 
@@ -272,6 +272,15 @@ static double ctr_error(Walker* w, int c)
 			if (cnt[t] > 1) counter += binomial_with_2(cnt[t]);
 		return counter;
 	}
+	case GHOST_KIND_ALL_EQUAL: {
+		/* all_equal.cpp:47-60: scope size minus the count of the most frequent value */
+		int32_t* cnt = w->count + m->cnt_off[c];
+		memset(cnt, 0, sizeof(int32_t) * m->cnt_size[c]);
+		for (int i = b; i < e; ++i) cnt[w->x[m->cvars[i]] - m->cnt_base[c]]++;
+		int32_t mx = 0;
+		for (int t = 0; t < m->cnt_size[c]; ++t) if (cnt[t] > mx) mx = cnt[t];
+		return (double)(e - b) - mx;
+	}
 	case GHOST_KIND_FIX_VALUE: {
 		/* fix_value.cpp:46-52 */
 		double error = 0.;
@@ -355,6 +364,24 @@ static double ctr_delta(const Walker* w, int c, int n, const int32_t* vars, cons
 			diff += binomial_with_2(t.copy[i]) - binomial_with_2(cnt[t.key[i]]);
 		return diff;
 	}
+	case GHOST_KIND_ALL_EQUAL: {
+		/* all_equal.cpp:62-85: largest count before minus largest count after the changes */
+		const int32_t* cnt = w->count + m->cnt_off[c];
+		int32_t base = m->cnt_base[c];
+		int32_t mx = 0, mx_bis = 0;
+		for (int t = 0; t < m->cnt_size[c]; ++t) if (cnt[t] > mx) mx = cnt[t];
+		Touched t; t.n = 0;
+		for (int i = 0; i < n; ++i) {
+			*touched_slot(&t, cnt, w->x[vars[i]] - base) -= 1;
+			*touched_slot(&t, cnt, vals[i] - base) += 1;
+		}
+		for (int k = 0; k < m->cnt_size[c]; ++k) {
+			int32_t v = cnt[k];
+			for (int i = 0; i < t.n; ++i) if (t.key[i] == k) v = t.copy[i];
+			if (v > mx_bis) mx_bis = v;
+		}
+		return (double)(mx - mx_bis);
+	}
 	case GHOST_KIND_FIX_VALUE: {
 		/* fix_value.cpp:54-64 */
 		double diff = 0.;
@@ -383,7 +410,7 @@ static double ctr_delta(const Walker* w, int c, int n, const int32_t* vars, cons
 static void ctr_update(Walker* w, int c, int var, int32_t new_value)
 {
 	const OracleModel* m = w->m;
-	if (m->kind[c] == GHOST_KIND_ALL_DIFFERENT) {
+	if (m->kind[c] == GHOST_KIND_ALL_DIFFERENT || m->kind[c] == GHOST_KIND_ALL_EQUAL) { /* all_equal.cpp:87-95 alike */
 		int32_t* cnt = w->count + m->cnt_off[c];
 		cnt[w->x[var] - m->cnt_base[c]] -= 1;
 		cnt[new_value - m->cnt_base[c]] += 1;

@@ -38,6 +38,7 @@
 #include "solver.hpp"
 #include "global_constraints/all_different.hpp"
 #include "global_constraints/fix_value.hpp"
+#include "global_constraints/all_equal.hpp"
 #include "global_constraints/linear_equation_eq.hpp"
 #include "global_constraints/linear_equation_neq.hpp"
 #include "global_constraints/linear_equation_leq.hpp"
@@ -202,6 +203,7 @@ public:
 			case GHOST_KIND_LINEAR_G:   constraints.emplace_back( std::make_shared<LinearEquationG>( ids, p, coef ) ); break;
 			case GHOST_KIND_FIX_VALUE:  constraints.emplace_back( std::make_shared<FixValue>( ids, static_cast<int>( p ) ) ); break;
 			case GHOST_KIND_ALL_DIFFERENT_ABS_DIFF: constraints.emplace_back( std::make_shared<HarnessAllDifferentAbsDiff>( ids ) ); break;
+			case GHOST_KIND_ALL_EQUAL: constraints.emplace_back( std::make_shared<AllEqual>( ids ) ); break;
 			case GHOST_KIND_PURE_OPTIMIZATION: break; /* build_model() inserts PureOptimization when there is no constraint */
 			default: break;
 			}

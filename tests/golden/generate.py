@@ -24,7 +24,7 @@ from oracle import binding  # noqa: E402
 from tests.helpers import model_by_name, random_assignment  # noqa: E402
 
 MODELS = ["magic_square:3", "magic_square:6", "n_queens:8", "costas:5", "knapsack:12x3", "all_interval:8", "mixed",
-          "mixed_perm", "magic_square:30", "n_queens:100", "costas:20"]
+          "mixed_perm", "magic_square:30", "n_queens:100", "costas:20", "mixed_eq", "mixed_perm_eq"]
 CASES = {"magic_square:30": 3, "n_queens:100": 4, "costas:20": 4}
 
 
@@ -32,7 +32,12 @@ def main():
     assert binding.build_ref(), "the reference tree is not mounted"
     out_dir = os.path.dirname(os.path.abspath(__file__))
     rng = np.random.default_rng(20261106)
-    for name in MODELS:
+    only = sys.argv[1:]   # optional: regenerate just these models (each has its own seeded stream)
+    for index, name in enumerate(MODELS):
+        if only and name not in only:
+            continue
+        if only:
+            rng = np.random.default_rng(20261106 + 1000 * index)
         desc = model_by_name(name)
         ref = binding.RefModel(desc)
         cases = []

@@ -19,14 +19,19 @@ from tests.helpers import COMPLETE_GOLDEN, model_by_name  # noqa: E402
 
 def main():
     assert binding.build_ref(), "the reference tree is not mounted"
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "complete", "solutions.json")
     out = {}
+    if "--missing" in sys.argv and os.path.exists(path):   # keep what is there, add the new models only
+        with open(path) as f:
+            out = json.load(f)
     for name in COMPLETE_GOLDEN:
+        if name in out:
+            continue
         desc = model_by_name(name)
         sol, cost, total = binding.RefModel(desc).complete_search(1 << 20)
         assert total == len(sol)
         out[name] = {"num_variables": desc.num_variables, "solutions": sol.tolist(), "costs": [float(c) for c in cost]}
         print(name, total, "solutions")
-    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "complete", "solutions.json")
     with open(path, "w") as f:
         json.dump(out, f, separators=(",", ":"))
     print("wrote", path, os.path.getsize(path), "bytes")

@@ -69,6 +69,34 @@ def mixed_permutation_model() -> ModelDesc:
     return m
 
 
+def all_equal_model() -> ModelDesc:
+    """AllEqual (src/global_constraints/all_equal.cpp) next to the other kinds, non-permutation."""
+    m = ModelDesc(permutation_problem=False, name="mixed_eq")
+    doms = [[0, 1, 2, 3], [1, 2, 3, 5], [0, 2, 3, 4], [1, 2, 3], [0, 1, 2, 3, 4, 5], [2, 3, 7], [0, 1, 2, 3], [3, 4, 5]]
+    for d in doms:
+        m.add_variable(domain=d, index=1)
+    m.all_equal([0, 1, 2, 3, 4])
+    m.all_equal([4, 5, 6])
+    m.all_different([5, 6, 7])
+    m.linear(md.LINEAR_LEQ, [0, 4, 7], 9, [1, 1, 1])
+    m.linear(md.LINEAR_EQ, [2, 6], 5, [1, 1])
+    return m
+
+
+def all_equal_permutation_model() -> ModelDesc:
+    """AllEqual inside a permutation problem: swaps with one or both variables in its scope."""
+    m = ModelDesc(permutation_problem=True, name="mixed_perm_eq")
+    start = [1, 1, 2, 2, 3, 3, 1, 2, 3, 4]
+    for i, sv in enumerate(start):
+        dom = [1, 2, 3, 4]
+        m.add_variable(domain=dom, index=dom.index(sv))
+    m.all_equal([0, 1, 2, 3])
+    m.all_equal([3, 4, 5, 6, 7])
+    m.linear(md.LINEAR_GEQ, [7, 8, 9], 6, [1, 1, 1])
+    m.linear(md.LINEAR_NEQ, [0, 9], 5, [1, 1])
+    return m
+
+
 def to_int_or_sentinel(cand_delta_f64):
     """Oracle doubles (NaN = not a candidate) -> the int32 convention of the C ABI."""
     out = np.full(cand_delta_f64.shape, NOT_A_CANDIDATE, dtype=np.int64)
@@ -152,7 +180,8 @@ COMPLETE_MODELS = {
 
 
 # models whose full solution list from the reference is committed in tests/golden/complete/solutions.json
-COMPLETE_GOLDEN = list(COMPLETE_MODELS) + ["n_queens:6", "all_interval:7", "costas:5", "knapsack:12x3", "magic_square:3"]
+COMPLETE_GOLDEN = list(COMPLETE_MODELS) + ["n_queens:6", "all_interval:7", "costas:5", "knapsack:12x3", "magic_square:3",
+                                            "mixed_perm_eq"]
 
 
 def model_by_name(name):
@@ -162,4 +191,8 @@ def model_by_name(name):
         return mixed_model()
     if name == "mixed_perm":
         return mixed_permutation_model()
+    if name == "mixed_eq":
+        return all_equal_model()
+    if name == "mixed_perm_eq":
+        return all_equal_permutation_model()
     return problems.by_name(name)

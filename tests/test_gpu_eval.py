@@ -35,13 +35,13 @@ def _compare(desc, oracle_built, n_cases, seed, threads=None):
         os.environ.pop("GHOST_B200_EVAL_THREADS", None)
 
 
-@pytest.mark.parametrize("name", SMALL_MODELS + ["mixed", "mixed_perm"])
+@pytest.mark.parametrize("name", SMALL_MODELS + ["mixed", "mixed_perm", "mixed_eq", "mixed_perm_eq"])
 def test_eval_matches_oracle_small(name, oracle_built):
     _compare(model_by_name(name), oracle_built, n_cases=24, seed=7)
 
 
 @pytest.mark.parametrize("threads", [32, 64, 128, 256])
-@pytest.mark.parametrize("name", ["magic_square:7", "n_queens:20", "mixed", "mixed_perm", "all_interval:10"])
+@pytest.mark.parametrize("name", ["magic_square:7", "n_queens:20", "mixed", "mixed_perm", "all_interval:10", "mixed_eq", "mixed_perm_eq"])
 def test_eval_every_mapping(name, threads, oracle_built):
     """warp-per-walker and CTA-per-walker mappings must give identical numbers."""
     _compare(model_by_name(name), oracle_built, n_cases=9, seed=11, threads=threads)

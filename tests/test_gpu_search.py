@@ -54,13 +54,13 @@ def _check_against_oracle(desc, oracle_built, iterations, walkers, seed, threads
 
 @pytest.mark.parametrize("name", ["magic_square:4", "magic_square:7", "n_queens:8", "n_queens:20", "costas:6",
                                   "costas:9", "knapsack:20x3", "knapsack:50x5", "all_interval:10", "mixed",
-                                  "mixed_perm"])
+                                  "mixed_perm", "mixed_eq", "mixed_perm_eq"])
 def test_trajectories_match_oracle(name, oracle_built):
     _check_against_oracle(model_by_name(name), oracle_built, iterations=600, walkers=12, seed=2024)
 
 
 @pytest.mark.parametrize("threads", [32, 64, 128, 256])
-@pytest.mark.parametrize("name", ["magic_square:7", "n_queens:20", "mixed_perm", "knapsack:50x5"])
+@pytest.mark.parametrize("name", ["magic_square:7", "n_queens:20", "mixed_perm", "knapsack:50x5", "mixed_perm_eq"])
 def test_trajectories_every_mapping(name, threads, oracle_built):
     _check_against_oracle(model_by_name(name), oracle_built, iterations=300, walkers=5, seed=5, threads=threads)
 
@@ -130,6 +130,27 @@ def test_blocking_search_cop_best_cost(oracle_built):
     best = max(-port.search(o, w, 2000)["best_opt"] for w in range(8))
     assert res["final_cost"] >= best
     model.close()
+
+
+def test_cop_no_worse_than_the_reference_at_equal_wall_budget(oracle_built):
+    """north_star correctness part 2 on config 4 (multi-dimensional knapsack, Maximize): with the same wall
+    budget the GPU search returns an objective at least as good as the unmodified reference's
+    Solver::fast_search with parallel_runs on the host cores (oracle/_ref, skipped where it is not built)."""
+    if not oracle_built.have_ref():
+        pytest.skip("oracle/_ref not built")
+    from ghost_b200 import capi
+    budget_us = 1.0e6
+    for name in ["knapsack:100x5", "knapsack:250x10"]:
+        desc = model_by_name(name)
+        ref = oracle_built.RefModel(desc).fast_search(budget_us, parallel_runs=True, threads=max(2, (os.cpu_count() or 2) // 2))
+        model = capi.Model(desc)
+        res = model.search(default_opts(seed=2026, timeout_us=budget_us))
+        model.close()
+        assert res["found"]
+        e, obj = oracle_built.OraclePort(desc).check(res["solution"])
+        assert e == 0.0 and obj == res["final_cost"]
+        if ref["found"] == 1:
+            assert res["final_cost"] >= ref["cost"], (name, res["final_cost"], ref["cost"])
 
 
 def _device_count():

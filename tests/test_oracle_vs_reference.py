@@ -11,7 +11,7 @@ import pytest
 from tests.helpers import SMALL_MODELS, model_by_name, random_assignment
 
 
-@pytest.mark.parametrize("name", SMALL_MODELS + ["mixed", "mixed_perm", "n_queens:100"])
+@pytest.mark.parametrize("name", SMALL_MODELS + ["mixed", "mixed_perm", "n_queens:100", "mixed_eq", "mixed_perm_eq"])
 def test_eval_matches_live_reference(name, ref_built):
     desc = model_by_name(name)
     port, ref = ref_built.OraclePort(desc), ref_built.RefModel(desc)
