@@ -469,8 +469,11 @@ extern "C" int ghost_b200_search(GhostModel* gm, const GhostSearchOpts* opts, Gh
 {
 	if (!gm || !opts || !res) return set_error(GHOST_B200_ERR_INVALID, "null argument to search");
 	GhostSearch* s = nullptr;
+	const bool timing = std::getenv("GHOST_B200_TIMING") != nullptr; // diagnostic: phase times on stderr
+	const auto tp0 = std::chrono::steady_clock::now();
 	int rc = ghost_b200_search_begin(gm, opts, &s);
 	if (rc) return rc;
+	const auto tp1 = std::chrono::steady_clock::now();
 	const bool optimization = gm->low.dev.objective != GHOST_OBJ_NONE;
 	int epoch = s->opts.epoch_iterations > 0 ? s->opts.epoch_iterations : 256;
 	const double budget_us = s->opts.timeout_us;
@@ -504,8 +507,15 @@ extern "C" int ghost_b200_search(GhostModel* gm, const GhostSearchOpts* opts, Gh
 			epoch = std::min(std::max(fit, 1), std::max(epoch * 2, 16));
 		}
 	}
+	const auto tp2 = std::chrono::steady_clock::now();
 	rc = ghost_b200_search_result(s, res);
+	const auto tp3 = std::chrono::steady_clock::now();
 	ghost_b200_search_end(s);
+	if (timing) {
+		auto ms = [](std::chrono::steady_clock::time_point a, std::chrono::steady_clock::time_point b) { return std::chrono::duration<double, std::milli>(b - a).count(); };
+		std::fprintf(stderr, "ghost_b200_search: begin %.2f ms, epochs %.2f ms, result %.2f ms, end %.2f ms\n", ms(tp0, tp1), ms(tp1, tp2), ms(tp2, tp3),
+		             ms(tp3, std::chrono::steady_clock::now()));
+	}
 	return rc;
 }
 
