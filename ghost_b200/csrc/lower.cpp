@@ -54,7 +54,7 @@ int lower_model(const GhostModelDesc* d, LoweredModel* out, std::string* why)
 		int b = d->dom_offset[v], e = d->dom_offset[v + 1];
 		if (e <= b) return fail(GHOST_B200_ERR_INVALID, "variable " + std::to_string(v) + " has an empty domain");
 		std::vector<int32_t> dv(d->dom_values + b, d->dom_values + e);
-		std::sort(dv.begin(), dv.end());
+		if (!std::is_sorted(dv.begin(), dv.end())) std::sort(dv.begin(), dv.end());
 		if (std::adjacent_find(dv.begin(), dv.end()) != dv.end())
 			return fail(GHOST_B200_ERR_INVALID, "variable " + std::to_string(v) + " has a duplicated domain value");
 		if (!std::binary_search(dv.begin(), dv.end(), d->start_value[v]))

@@ -213,10 +213,17 @@ class ModelDesc:
     # -- flat arrays --
     def arrays(self):
         V = self.num_variables
-        dom_offset = np.zeros(V + 1, dtype=np.int32)
-        for v, d in enumerate(self.domains):
-            dom_offset[v + 1] = dom_offset[v] + len(d)
-        dom_values = _i32([x for d in self.domains for x in d]) if V else _i32([])
+        # the flattened domains are memoised (V*D Python ints to convert): same list objects, same lengths
+        finger = tuple((id(d), len(d)) for d in self.domains)
+        cached = getattr(self, "_dom_cache", None)
+        if cached is not None and cached[0] == finger:
+            dom_offset, dom_values = cached[1], cached[2]
+        else:
+            dom_offset = np.zeros(V + 1, dtype=np.int32)
+            for v, d in enumerate(self.domains):
+                dom_offset[v + 1] = dom_offset[v] + len(d)
+            dom_values = _i32(np.fromiter((x for d in self.domains for x in d), dtype=np.int32, count=int(dom_offset[V]))) if V else _i32([])
+            self._dom_cache = (finger, dom_offset, dom_values)
         ctrs = list(self.constraints)
         if not ctrs:
             # ModelBuilder::build_model inserts PureOptimization over all variables
