@@ -7,6 +7,7 @@
 #include <cstring>
 #include <limits>
 #include <mutex>
+#include <new>
 #include <string>
 #include <vector>
 
@@ -554,7 +555,13 @@ extern "C" int ghost_b200_search_devices(const GhostModelDesc* desc, const Ghost
 	int W = 0;
 	for (int d = 0; d < n; ++d) {
 		DEV_CUDA(cudaSetDevice(d));
-		DEV_TRY(ghost_b200_model_create(desc, &gm[d]));
+		if (d == 0) DEV_TRY(ghost_b200_model_create(desc, &gm[0]));
+		else {
+			// the lowering is device independent: copy it, upload it to this device at first use
+			gm[d] = new (std::nothrow) GhostModel(*gm[0]);
+			if (!gm[d]) { cleanup(); return set_error(GHOST_B200_ERR_NOMEM, "out of host memory"); }
+			gm[d]->device = -1; gm[d]->d_blob = nullptr; gm[d]->low.dev.blob = nullptr;
+		}
 		GhostSearchOpts o = *opts;
 		if (d > 0) o.number_walkers = W;
 		o.first_walker_id = opts->first_walker_id + (uint64_t)d * (uint64_t)W;

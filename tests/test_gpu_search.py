@@ -93,6 +93,34 @@ def test_trajectories_baseline_sizes(name, oracle_built):
     _check_against_oracle(model_by_name(name), oracle_built, iterations=60, walkers=3, seed=77)
 
 
+def test_config5_population_131072_walkers_per_gpu(oracle_built):
+    """BASELINE.json config 5 per GPU: Costas n=20 with 131072 walkers on one device (1 M over 8 GPUs) — many
+    waves of CTAs per launch, the walker states living in HBM between launches.  Walkers sampled across the
+    population (first, middle, last) follow the oracle's trajectories for their global ids; the counters of
+    the whole population add up."""
+    from ghost_b200 import capi
+    desc = model_by_name("costas:20")
+    W, iters = 131072, 24
+    port = oracle_built.OraclePort(desc)
+    opts = default_opts(seed=4242, number_walkers=W, stop_on_first_solution=0, max_iterations=iters)
+    port.resolve_opts(opts)
+    model = capi.Model(desc)
+    s = model.begin(opts)
+    s.epoch(16)
+    s.epoch(8)
+    out = s.walkers(W)
+    res = s.result()
+    s.end()
+    model.close()
+    assert res["walkers"] == W
+    assert res["total"]["search_iterations"] == sum(c["search_iterations"] for c in out["counters"])
+    assert all(c["search_iterations"] <= iters for c in out["counters"])
+    for w in (0, 1, 65535, 65536, 100003, W - 1):
+        want = port.search(opts, w, iters)
+        assert out["counters"][w] == want["counters"], w
+        assert np.array_equal(out["best_x"][w], want["best_x"]), w
+
+
 def test_blocking_search_solves_and_reference_accepts(oracle_built):
     """ghost_b200_search (what Solver::fast_search calls): solutions of CSPs are re-checked with the
     reference's own Constraint::error (oracle/_ref) when present, else with the oracle port."""
