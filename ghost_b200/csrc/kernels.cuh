@@ -43,7 +43,22 @@ __device__ __forceinline__ unsigned long long quality_key(bool optimization, int
 // ---- sampling ---------------------------------------------------------------------------------
 
 // first n entries of a uniform shuffle of 0..V-1 (replaces rng.shuffle + prefix, search_unit.hpp:
-// 206-211, 239-246): rejection sampling over one RNG event, by thread 0.
+// 206-211, 239-246): rejection sampling over one RNG event, by thread 0.  The serial part is one
+// shared out-of-line copy (plain pointers and scalars only), see GB_OUTLINE in walker.cuh.
+static __device__ GB_OUTLINE void sample_distinct_serial(unsigned char* flags, int* out, int n, int V, uint64_t seed, uint64_t walker, uint64_t event)
+{
+	Rng rng; rng.seed = seed; rng.walker = walker; rng.next_event = 0;
+	uint32_t t = 0;
+	uint4 blk = make_uint4(0, 0, 0, 0);
+	for (int got = 0; got < n; ++t) {
+		if ((t & 3u) == 0) blk = rng.block(event, t >> 2);
+		uint32_t w = (t & 3u) == 0 ? blk.x : (t & 3u) == 1 ? blk.y : (t & 3u) == 2 ? blk.z : blk.w;
+		uint32_t idx = below(w, (uint32_t)V);
+		if (flags[idx]) continue;
+		flags[idx] = 1;
+		out[got++] = (int)idx;
+	}
+}
 template <int T, class WS>
 __device__ inline void sample_distinct(const DevModel& m, const WS& s, Rng& rng, int n, int* out)
 {
@@ -52,18 +67,7 @@ __device__ inline void sample_distinct(const DevModel& m, const WS& s, Rng& rng,
 	const uint64_t event = rng.next_event++;
 	for (int v = tid; v < m.V; v += T) s.flags[v] = 0;
 	G::sync();
-	if (tid == 0) {
-		uint32_t t = 0;
-		uint4 blk = make_uint4(0, 0, 0, 0);
-		for (int got = 0; got < n; ++t) {
-			if ((t & 3u) == 0) blk = rng.block(event, t >> 2);
-			uint32_t w = (t & 3u) == 0 ? blk.x : (t & 3u) == 1 ? blk.y : (t & 3u) == 2 ? blk.z : blk.w;
-			uint32_t idx = below(w, (uint32_t)m.V);
-			if (s.flags[idx]) continue;
-			s.flags[idx] = 1;
-			out[got++] = (int)idx;
-		}
-	}
+	if (tid == 0) sample_distinct_serial(s.flags, out, n, m.V, rng.seed, rng.walker, event);
 	G::sync();
 }
 
@@ -195,7 +199,7 @@ __device__ inline void copy_best(const DevModel& m, const WS& s, int* best_x)
 }
 
 // SearchUnit::initialize_data_structures (search_unit.hpp:274-317)
-template <int T, class WS>
+template <int T, bool EQ, class WS>
 __device__ inline void initialize_data_structures(const DevModel& m, const WS& s, WalkerRegs& r, int* best_x)
 {
 	typedef Group<T> G;
@@ -203,7 +207,7 @@ __device__ inline void initialize_data_structures(const DevModel& m, const WS& s
 	r.must_compute = 1;
 	for (int v = G::tid(); v < m.V; v += T) s.tabu[v] = 0;
 	r.tabu_base = r.local_moves;
-	r.cur_sat = recompute_all<T, true>(m, s, s.red);
+	r.cur_sat = recompute_all<T, true, EQ>(m, s, s.red);
 	if (r.best_sat > r.cur_sat) { r.best_sat = r.cur_sat; r.best_pending = 1; }
 	if (m.objective != GHOST_OBJ_NONE) {
 		long long part = 0;
@@ -220,7 +224,7 @@ __device__ inline void initialize_data_structures(const DevModel& m, const WS& s
 // SearchUnit::set_initial_configuration (search_unit.hpp:153-198); s.tabu doubles as the
 // best_values buffer (it is cleared by initialize_data_structures right after).
 // Deviation D1: best_x follows best_sat here too.
-template <int T, class WS>
+template <int T, bool EQ, class WS>
 __device__ inline void set_initial_configuration(const DevModel& m, const WS& s, WalkerRegs& r, Rng& rng, int samplings, int* best_x)
 {
 	typedef Group<T> G;
@@ -229,7 +233,7 @@ __device__ inline void set_initial_configuration(const DevModel& m, const WS& s,
 	int loops = 0;
 	do {
 		if (m.permutation) random_permutations<T>(m, s, rng, -1); else monte_carlo_sampling<T>(m, s, rng, -1);
-		current = recompute_all<T, false>(m, s, s.red); // total only: err_var holds the best sample
+		current = recompute_all<T, false, EQ>(m, s, s.red); // total only: err_var holds the best sample
 		if (best_so_far > current) {
 			best_so_far = current;
 			if (r.best_sat > best_so_far) { r.best_sat = best_so_far; copy_best<T>(m, s, best_x); r.best_pending = 0; }
@@ -242,7 +246,7 @@ __device__ inline void set_initial_configuration(const DevModel& m, const WS& s,
 }
 
 // SearchUnit::initialize_variable_values (search_unit.hpp:259-272)
-template <int T, class WS>
+template <int T, bool EQ, class WS>
 __device__ inline void initialize_variable_values(const DevModel& m, const WS& s, WalkerRegs& r, Rng& rng, const SearchParams& p, int* best_x)
 {
 	typedef Group<T> G;
@@ -252,7 +256,7 @@ __device__ inline void initialize_variable_values(const DevModel& m, const WS& s
 		for (int v = G::tid(); v < m.V; v += T) s.x[v] = mv.ld(m.o.start, v);
 		G::sync();
 	} else
-		set_initial_configuration<T>(m, s, r, rng, p.nsamplings, best_x);
+		set_initial_configuration<T, EQ>(m, s, r, rng, p.nsamplings, best_x);
 }
 
 // SearchUnit::local_move (search_unit.hpp:516-541)
@@ -279,13 +283,70 @@ __device__ inline void local_move(const DevModel& m, const WS& s, WalkerRegs& r,
 // =================================================================================================
 // Resident warps per SM the register allocator is asked to leave room for (the walkers' shared
 // memory allows about 20 per SM on the magic-square benchmark model).
+// Branch hints: the cold branches (first launch, resets, tracing) should be laid out away from the
+// per-iteration path, whose size decides the instruction-cache hit rate of an SM running 24 walkers.
+#ifdef GB_NO_HINTS
+#define GB_UNLIKELY(x) (x)
+#else
+#define GB_UNLIKELY(x) __builtin_expect(!!(x), 0)
+#endif
 #ifndef GB_WARPS_PER_SM
 #define GB_WARPS_PER_SM 24
 #endif
 
+// ---- the cold part of a walker's life, kept out of line -------------------------------------------
+// First-launch initialisation (search_unit.hpp:708-717), restart and reset (333-367) run once per
+// launch or once every few dozen iterations, but their code (sampling, full recomputation) is several
+// times the size of the per-iteration path.  Inlined, it sits between the hot blocks and spreads them
+// over 130 KB of addresses; the SM's instruction cache then thrashes on set conflicts (hit rate 77%,
+// every fourth issue slot lost to instruction fetch).  As one __noinline__ function the kernel body is
+// the hot path alone.  The walker scalars it reads and writes travel by value: handing it WalkerRegs by
+// reference would pin that struct in local memory for the whole kernel.
+struct ColdState {
+	int must_compute, tabu_base, local_moves, cur_sat, best_sat, best_pending, resume_pending;
+	long long cur_opt, best_opt, obj_sum;
+	unsigned long long next_event;
+};
+enum { GB_COLD_FIRST = 0, GB_COLD_RESTART = 1, GB_COLD_PERTURB = 2 };
+
+template <int T, bool PERM, bool EQ, class XT>
+static __device__ __noinline__ ColdState walker_reinit(const DevModel& m, const WalkerLayout& L, const SearchParams& p,
+                                                       unsigned char* base, int* best_x, unsigned long long walker, int mode, ColdState c)
+{
+	typedef Group<T> G;
+	typedef WST<XT> WS;
+	const WS s = make_ws<WS>(base, L);
+	MV mv(m);
+	const int tid = G::tid();
+	Rng rng; rng.seed = p.seed; rng.walker = walker; rng.next_event = c.next_event;
+	WalkerRegs r{};
+	r.must_compute = c.must_compute; r.tabu_base = c.tabu_base; r.local_moves = c.local_moves; r.cur_sat = c.cur_sat;
+	r.best_sat = c.best_sat; r.best_pending = c.best_pending; r.resume_pending = c.resume_pending;
+	r.cur_opt = c.cur_opt; r.best_opt = c.best_opt; r.obj_sum = c.obj_sum;
+	if (mode == GB_COLD_FIRST) {
+		// search_unit.hpp:708-717
+		r.best_sat = GB_INT_MAX; r.best_opt = GB_I64_MAX; r.cur_opt = GB_I64_MAX;
+		for (int v = tid; v < m.V; v += T) s.x[v] = mv.ld(m.o.start, v);
+		// padding of the scan arrays up to a multiple of 32 variables: tabu for ever, error 0
+		for (int v = m.V + tid; v < L.nchunks_v * 32; v += T) { s.tabu[v] = 0xFFFFu; s.err_var[v] = 0; s.x[v] = 0; }
+		G::sync();
+		initialize_variable_values<T, EQ>(m, s, r, rng, p, best_x);
+	} else if (mode == GB_COLD_RESTART) {
+		if (tid == 0) s.counters[K_RESTARTS] += 1;
+		initialize_variable_values<T, EQ>(m, s, r, rng, p, best_x);
+	} else if (PERM) random_permutations<T>(m, s, rng, p.nreset);
+	else monte_carlo_sampling<T>(m, s, rng, p.nreset);
+	initialize_data_structures<T, EQ>(m, s, r, best_x);
+	if (mode == GB_COLD_FIRST) r.best_pending = 1; // search_unit.hpp:714-717: final_solution = the initial assignment
+	c.must_compute = r.must_compute; c.tabu_base = r.tabu_base; c.cur_sat = r.cur_sat; c.best_sat = r.best_sat;
+	c.best_pending = r.best_pending; c.resume_pending = r.resume_pending;
+	c.cur_opt = r.cur_opt; c.best_opt = r.best_opt; c.obj_sum = r.obj_sum; c.next_event = rng.next_event;
+	return c;
+}
+
 template <int T, bool PERM, bool EQ, class XT>
 __global__ void __launch_bounds__(T == 32 ? 128 : T, (GB_WARPS_PER_SM * 32) / (T == 32 ? 128 : T))
-search_kernel(const DevModel m, const WalkerLayout L, const SearchParams p)
+search_kernel(const __grid_constant__ DevModel m, const __grid_constant__ WalkerLayout L, const __grid_constant__ SearchParams p)
 {
 	typedef Group<T> G;
 	extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -319,16 +380,20 @@ search_kernel(const DevModel m, const WalkerLayout L, const SearchParams p)
 		s.cs[m.C] = make_int4(0, 0, 0, 0); // the dummy constraint that pads the ELL rows
 	}
 
-	if (!gs->initialized) {
-		// search_unit.hpp:708-717
-		r.best_sat = GB_INT_MAX; r.best_opt = GB_I64_MAX; r.cur_opt = GB_I64_MAX;
-		for (int v = tid; v < m.V; v += T) s.x[v] = mv.ld(m.o.start, v);
-		// padding of the scan arrays up to a multiple of 32 variables: tabu for ever, error 0
-		for (int v = m.V + tid; v < L.nchunks_v * 32; v += T) { s.tabu[v] = 0xFFFFu; s.err_var[v] = 0; s.x[v] = 0; }
+	unsigned char* const walker_base = smem_raw + (size_t)local * L.total_bytes;
+	auto reinit = [&](int mode) {
+		ColdState c;
+		c.must_compute = r.must_compute; c.tabu_base = r.tabu_base; c.local_moves = r.local_moves; c.cur_sat = r.cur_sat;
+		c.best_sat = r.best_sat; c.best_pending = r.best_pending; c.resume_pending = r.resume_pending;
+		c.cur_opt = r.cur_opt; c.best_opt = r.best_opt; c.obj_sum = r.obj_sum; c.next_event = rng.next_event;
 		G::sync();
-		initialize_variable_values<T>(m, s, r, rng, p, best_x);
-		initialize_data_structures<T>(m, s, r, best_x);
-		r.best_pending = 1; // search_unit.hpp:714-717: final_solution = the initial assignment
+		c = walker_reinit<T, PERM, EQ, XT>(m, L, p, walker_base, best_x, rng.walker, mode, c);
+		r.must_compute = c.must_compute; r.tabu_base = c.tabu_base; r.cur_sat = c.cur_sat; r.best_sat = c.best_sat;
+		r.best_pending = c.best_pending; r.resume_pending = c.resume_pending;
+		r.cur_opt = c.cur_opt; r.best_opt = c.best_opt; r.obj_sum = c.obj_sum; rng.next_event = c.next_event;
+	};
+	if (GB_UNLIKELY(!gs->initialized)) {
+		reinit(GB_COLD_FIRST);
 		done = !(r.best_sat > 0 || (r.best_sat == 0 && optimization));
 	} else {
 		const int4* src = reinterpret_cast<const int4*>(gstate);
@@ -352,7 +417,7 @@ search_kernel(const DevModel m, const WalkerLayout L, const SearchParams p)
 			if (stop) break;
 		}
 		++r.iterations;
-		if (r.local_moves - r.tabu_base > 30000) {
+		if (GB_UNLIKELY(r.local_moves - r.tabu_base > 30000)) {
 			// keep the 16-bit relative tabu entries in range: re-base them on the current move count
 			const int shift = r.local_moves - r.tabu_base;
 			for (int v = tid; v < m.V; v += T) { int t = (int)s.tabu[v] - shift; s.tabu[v] = (unsigned short)(t > 0 ? t : 0); }
@@ -364,17 +429,12 @@ search_kernel(const DevModel m, const WalkerLayout L, const SearchParams p)
 			r.ncand = scan_candidates<T>(m, s, L.nchunks_v, r.local_moves - r.tabu_base, optimization && r.cur_sat == 0, s.red, &r.cand_max, &r.n_tabu, cq);
 
 		int trace_var = -1, trace_val = 0, trace_branch = 0, trace_ncand = 0, trace_min = 0;
-		if (r.n_tabu >= p.reset_threshold || r.ncand == 0) {
+		if (GB_UNLIKELY(r.n_tabu >= p.reset_threshold || r.ncand == 0)) {
 			// SearchUnit::reset (search_unit.hpp:333-367)
 			++r.resets;
 			if (tid == 0) s.counters[K_RESETS] += 1;
 			if (r.best_pending) { copy_best<T>(m, s, best_x); r.best_pending = 0; G::sync(); }
-			if (p.restart_threshold > 0 && (r.resets % p.restart_threshold == 0)) {
-				if (tid == 0) s.counters[K_RESTARTS] += 1;
-				initialize_variable_values<T>(m, s, r, rng, p, best_x);
-			} else if (PERM) random_permutations<T>(m, s, rng, p.nreset);
-			else monte_carlo_sampling<T>(m, s, rng, p.nreset);
-			initialize_data_structures<T>(m, s, r, best_x);
+			reinit(p.restart_threshold > 0 && (r.resets % p.restart_threshold == 0) ? GB_COLD_RESTART : GB_COLD_PERTURB);
 		} else {
 			const uint4 rnd = rng.block(rng.next_event++, 0);
 			// UniformVariableHeuristic::select_variable (uniform_variable_heuristic.cpp:38-41)
@@ -461,7 +521,7 @@ search_kernel(const DevModel m, const WalkerLayout L, const SearchParams p)
 			else if (optimization && r.cur_sat == 0 && r.best_opt > r.cur_opt) { r.best_opt = r.cur_opt; r.best_pending = 1; }
 			G::sync();
 		}
-		if (p.trace && w == p.trace_walker && tid == 0) {
+		if (GB_UNLIKELY(p.trace && w == p.trace_walker && tid == 0)) {
 			int row = (int)r.iterations - 1;
 			if (row < p.trace_cap) {
 				int* t = p.trace + 8 * row;

@@ -26,7 +26,14 @@ namespace ghost_b200 {
 // mt19937 (thirdparty/randutils.hpp:605-807).  Stream layout ("RNG protocol"):
 //   key = (seed_lo, seed_hi ^ walker_hi), counter = (event_lo, event_hi, slot, walker_lo).
 // ---------------------------------------------------------------------------------------------
-__device__ __forceinline__ uint4 philox4x32_10(uint4 c, uint2 k)
+// Not inlined on purpose (GB_OUTLINE): the generator is used on the hot iteration path and all over the
+// reset / sampling paths; one shared copy keeps the instruction working set of an SM — 24 warps in
+// different phases of the walk — inside its instruction cache (measured: the inlined copies pushed the
+// hot code past it and the icache hit rate from 98% to 77%).
+#ifndef GB_OUTLINE
+#define GB_OUTLINE __noinline__
+#endif
+static __device__ GB_OUTLINE uint4 philox4x32_10(uint4 c, uint2 k)
 {
 #pragma unroll
 	for (int r = 0; r < 10; ++r) {
@@ -376,19 +383,23 @@ __device__ inline int constraint_delta(const MV& mv, const WS& s, int c, int va,
 // Flat over the scope entries with a warp-segmented reduction per constraint.
 // Returns the total satisfaction error.  Ends with a group barrier.
 // ---------------------------------------------------------------------------------------------
-template <int T, bool PROJECT, class WS>
+// EQ: every live constraint is a LinearEquationEq (plus, possibly, the static AllDifferent of a
+// permutation problem, whose entries carry coefficient 0): no kind lookups, no count tables.
+template <int T, bool PROJECT, bool EQ = false, class WS>
 __device__ inline int recompute_all(const DevModel& m, const WS& s, int* red)
 {
 	typedef Group<T> G;
 	MV mv(m);
 	const int tid = G::tid(), lane = threadIdx.x & 31;
 	for (int c = tid; c < m.C; c += T) s.cs[c] = make_int4(0, 0, 0, 0);
-	for (int t = tid; t < (m.cnt_total + 1) / 2; t += T) s.cnt32[t] = 0;
+	if (!EQ) for (int t = tid; t < (m.cnt_total + 1) / 2; t += T) s.cnt32[t] = 0;
 	G::sync();
 	const int nnz_pad = (m.nnz + 31) & ~31;
 	for (int i = tid; i < nnz_pad; i += T) {
 		int c = -1, val = 0, kind = -1;
-		if (i < m.nnz) {
+		if (EQ) {
+			if (i < m.nnz) { c = mv.ld(m.o.ent_ctr, i); kind = GHOST_KIND_LINEAR_EQ; val = mv.ld(m.o.ent_coef, i) * s.x[mv.scope_var(i)]; }
+		} else if (i < m.nnz) {
 			c = mv.ld(m.o.ent_ctr, i);
 			kind = mv.kind(c);
 			int u = mv.scope_var(i);
@@ -423,14 +434,14 @@ __device__ inline int recompute_all(const DevModel& m, const WS& s, int* red)
 			s.err_of(c) = linear_error_w(linear_w_of_kind(kind), t);
 		} else if (kind == GB_KIND_STATIC) s.err_of(c) = mv.rhs(c);
 	}
-	for (int t = tid; t < m.cnt_total; t += T) {
+	if (!EQ) for (int t = tid; t < m.cnt_total; t += T) {
 		int n = s.cnt(t);
 		if (n > 1) {
 			const int owner = mv.ld(m.o.cnt_owner, t);
 			if (!m.has_all_equal || mv.kind(owner) != GHOST_KIND_ALL_EQUAL) atomicAdd(&s.err_of(owner), binom2(n));
 		}
 	}
-	if (m.has_all_equal) {
+	if (!EQ && m.has_all_equal) {
 		G::sync();
 		for (int c = 0; c < m.C; ++c) if (mv.kind(c) == GHOST_KIND_ALL_EQUAL) alleq_refresh<T>(m, s, c);
 	}
@@ -524,10 +535,10 @@ __device__ __forceinline__ int regs_count(const ChunkRegs& q, int best)
 {
 	return __reduce_add_sync(0xffffffffu, q.key == best ? __popc(q.bits) : 0);
 }
-__device__ __forceinline__ int regs_pick_kth(const ChunkRegs& q, int best, int k)
+static __device__ GB_OUTLINE int regs_pick_kth_impl(int key, unsigned bits, int best, int k)
 {
 	const int lane = threadIdx.x & 31;
-	const unsigned b = q.key == best ? q.bits : 0u;
+	const unsigned b = key == best ? bits : 0u;
 	const int c = __popc(b);
 	int incl = c;
 #pragma unroll
@@ -541,6 +552,7 @@ __device__ __forceinline__ int regs_pick_kth(const ChunkRegs& q, int best, int k
 	const unsigned wb = __shfl_sync(0xffffffffu, b, src);
 	return src * 32 + __fns(wb, 0, k - excl + 1);
 }
+__device__ __forceinline__ int regs_pick_kth(const ChunkRegs& q, int best, int k) { return regs_pick_kth_impl(q.key, q.bits, best, k); }
 
 // One chunk of the variable scan: the chunk's largest eligible error and the lanes that hold it.
 template <int T, class WS>
@@ -574,7 +586,7 @@ __device__ inline int scan_candidates(const DevModel& m, const WS& s, int nchunk
 	q.key = -1; q.bits = 0u;
 	const int4* e4 = reinterpret_cast<const int4*>(s.err_var);
 	const uint2* t4 = reinterpret_cast<const uint2*>(s.tabu);
-#ifdef GB_UNROLL1
+#ifndef GB_UNROLL2   // not unrolled: the loop body has to stay small enough for the per-scheduler instruction cache (measured)
 #pragma unroll 1
 #endif
 	for (int b = G::warp(); b < nblocks; b += G::NW) {
@@ -832,7 +844,8 @@ __device__ __forceinline__ void commit_value_chunk(const WS& s, ChunkRegs& q, in
 // selected variable's (a, T - a*x_v) pairs held in registers, no end-of-row tests (the ELL rows and
 // the assignment are padded to whole chunks), no divergent control flow.
 // S = compile-time row length of the padded ELL rows (0: read it at run time)
-// FAST = at most two hoisted constraints and, for a permutation problem, one common domain
+// FAST = at most four hoisted constraints (all held in registers, absent ones as zeros: ONE loop body for
+// every selected variable keeps the hot code small) and, for a permutation problem, one common domain
 template <int T, bool PERM, int S, bool FAST, class WS>
 __device__ inline int evaluate_candidates_eq_s(const DevModel& m, const WS& s, int v, int nh, int bias, int nchunks_c, int* out, ChunkRegs& q)
 {
@@ -845,10 +858,8 @@ __device__ inline int evaluate_candidates_eq_s(const DevModel& m, const WS& s, i
 	int a0 = 0, b0 = 0, a1 = 0, b1 = 0, a2 = 0, b2 = 0, a3 = 0, b3 = 0;
 	if (nh > 0) { int4 h = s.hoist[0]; a0 = h.y; b0 = h.z; }
 	if (nh > 1) { int4 h = s.hoist[1]; a1 = h.y; b1 = h.z; }
-	if (!FAST) {
-		if (nh > 2) { int4 h = s.hoist[2]; a2 = h.y; b2 = h.z; }
-		if (nh > 3) { int4 h = s.hoist[3]; a3 = h.y; b3 = h.z; }
-	}
+	if (nh > 2) { int4 h = s.hoist[2]; a2 = h.y; b2 = h.z; }
+	if (nh > 3) { int4 h = s.hoist[3]; a3 = h.y; b3 = h.z; }
 	constexpr int SP = S <= 2 ? S : 4;  // entries per packed row when S is known (one 32/64/128-bit load)
 	const unsigned* ell = reinterpret_cast<const unsigned*>(m.blob + m.o.ell_eq);
 	const unsigned char* cs_bytes = reinterpret_cast<const unsigned char*>(s.cs);
@@ -863,7 +874,7 @@ __device__ inline int evaluate_candidates_eq_s(const DevModel& m, const WS& s, i
 	unsigned en[SP > 0 ? SP : 1];
 	if (PERM && S > 0) load_row(G::warp() * 32 + lane, en);
 #endif
-#ifdef GB_UNROLL1
+#ifndef GB_UNROLL2   // not unrolled: the loop body has to stay small enough for the per-scheduler instruction cache (measured)
 #pragma unroll 1
 #endif
 	for (int ch = G::warp(); ch < nchunks_c; ch += G::NW) {
@@ -893,7 +904,8 @@ __device__ inline int evaluate_candidates_eq_s(const DevModel& m, const WS& s, i
 		asm("" : "+r"(d));
 		ok = ok && d != xv;                                  // search_unit.hpp:833 / 855-860
 		int sum = bias + abs(b0 + a0 * d) + abs(b1 + a1 * d);
-		if (!FAST && nh > 2) {
+		if (FAST) sum += abs(b2 + a2 * d) + abs(b3 + a3 * d);   // absent entries are 0*d + 0: one loop for every variable
+		else if (nh > 2) {
 			sum += abs(b2 + a2 * d) + abs(b3 + a3 * d);
 			for (int k = 4; k < nh; ++k) { int4 h = s.hoist[k]; sum += abs(h.z + h.y * d); }
 		}
@@ -925,10 +937,15 @@ template <int T, bool PERM, class WS>
 __device__ inline int evaluate_candidates_eq(const DevModel& m, const WS& s, int v, int nh, int bias, int nchunks_c, int* out, ChunkRegs& q)
 {
 	if (!PERM) {
-		if (nh <= 2) return evaluate_candidates_eq_s<T, PERM, 0, true>(m, s, v, nh, bias, nchunks_c, out, q);
+		if (nh <= 4) return evaluate_candidates_eq_s<T, PERM, 0, true>(m, s, v, nh, bias, nchunks_c, out, q);
 		return evaluate_candidates_eq_s<T, PERM, 0, false>(m, s, v, nh, bias, nchunks_c, out, q);
 	}
-	if (nh <= 2 && m.identical_domains) {
+#ifndef GB_NOFAST
+	if (nh <= 4 && m.identical_domains)
+#else
+	if (false)
+#endif
+	{
 		switch (m.ell_stride) { // warp-uniform: fully unrolled row loops for the usual row lengths
 		case 1: return evaluate_candidates_eq_s<T, PERM, 1, true>(m, s, v, nh, bias, nchunks_c, out, q);
 		case 2: return evaluate_candidates_eq_s<T, PERM, 2, true>(m, s, v, nh, bias, nchunks_c, out, q);
