@@ -377,7 +377,7 @@ search_kernel(const __grid_constant__ DevModel m, const __grid_constant__ Walker
 		const long long* k = reinterpret_cast<const long long*>(&gs->k);
 #pragma unroll
 		for (int i = 0; i < 8; ++i) s.counters[i] = k[i];
-		s.cs[m.C] = make_int4(0, 0, 0, 0); // the dummy constraint that pads the ELL rows
+		s.cs[m.C] = make_int2(0, 0); s.cem[m.C] = make_int2(0, 0); // the dummy constraint that pads the ELL rows
 	}
 
 	unsigned char* const walker_base = smem_raw + (size_t)local * L.total_bytes;
@@ -580,7 +580,7 @@ eval_kernel(const DevModel m, const WalkerLayout L, int num_walkers, const int* 
 	const WS s = make_ws<WS>(smem_raw + (size_t)local * L.total_bytes, L);
 	const int tid = G::tid();
 	for (int v = tid; v < L.nchunks_v * 32; v += T) s.x[v] = v < m.V ? assignments[(size_t)w * m.V + v] : 0;
-	if (tid == 0) s.cs[m.C] = make_int4(0, 0, 0, 0);
+	if (tid == 0) { s.cs[m.C] = make_int2(0, 0); s.cem[m.C] = make_int2(0, 0); }
 	G::sync();
 	recompute_all<T, true>(m, s, s.red);
 	if (ctr_error) for (int c = tid; c < m.C; c += T) ctr_error[(size_t)w * m.C + c] = s.err_of(c);

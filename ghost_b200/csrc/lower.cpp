@@ -279,16 +279,16 @@ int lower_model(const GhostModelDesc* d, LoweredModel* out, std::string* why)
 	// row in one aligned load.  The table (4 B x stride x V) is what the candidate loop streams through
 	// L1 every iteration, next to shared-memory carve-outs that leave L1 only a few tens of KB.
 	const int stride_eq = stride <= 2 ? stride : (stride + 3) / 4 * 4;
-	if ((C + 1) * 16 > 65535) eq_only = false;
+	if ((C + 1) * 8 > 65535) eq_only = false;
 	for (size_t i = 0; eq_only && i + 1 < ell.size(); i += 2) if (ell[i + 1] < -32768 || ell[i + 1] > 32767) eq_only = false;
 	{
 		std::vector<int32_t> ell_eq(eq_only ? static_cast<size_t>(vpad_rows) * stride_eq : 0);
 		for (int v = 0; eq_only && v < vpad_rows; ++v)
 			for (int k = 0; k < stride_eq; ++k) {
-				uint32_t off = static_cast<uint32_t>(C) * 16u, coef = 0;
+				uint32_t off = static_cast<uint32_t>(C) * 8u, coef = 0;
 				if (k < stride) {
 					size_t i = (static_cast<size_t>(v) * stride + k) * 2;
-					off = static_cast<uint32_t>(ell[i] & 0xFFFFF) * 16u;
+					off = static_cast<uint32_t>(ell[i] & 0xFFFFF) * 8u;
 					coef = static_cast<uint32_t>(ell[i + 1]) & 0xFFFFu;
 				}
 				ell_eq[static_cast<size_t>(v) * stride_eq + k] = static_cast<int32_t>(off | (coef << 16));
@@ -347,7 +347,8 @@ WalkerLayout LoweredModel::layout(int /*threads_per_walker*/, int nreset) const
 	w.x = take((m.x16 ? 2 : 4) * vpad);  // padded: a chunk of swap partners is read without a clamp   // scan without bounds tests: padded, the padding is always tabu
 	w.err_var = take(4 * vpad);
 	w.tabu = take(2 * vpad);
-	w.cs = take(16 * (m.C + 1)); // + the all-zero dummy constraint that pads the ELL rows
+	w.cs = take(8 * (m.C + 1));  // + the all-zero dummy constraint that pads the ELL rows
+	w.cs_em = take(8 * (m.C + 1));
 	w.cand_key = take(4 * w.nchunks_v);
 	w.cand_bits = take(4 * w.nchunks_v);
 	w.cnt = take(2 * std::max(1, m.cnt_total));

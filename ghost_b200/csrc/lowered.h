@@ -67,7 +67,9 @@ enum : int { GB_MARK_SKIP = 1 << 20 };
 // Per-walker shared-memory layout, byte offsets from the walker's base.
 struct WalkerLayout {
 	int x, err_var, tabu;               // [V padded to 32]: x uint16/int32, err_var int32, tabu uint16
-	int cs;                             // int4 [C]: {T = sum - rhs (linear), current error, mark, 0}
+	int cs;                             // int2 [C+1]: {T = sum - rhs (linear kinds), a_v of the hoisted variable}: 8-byte stride, so
+	                                    // that the gather of the evaluation loop over consecutive constraints is bank-conflict free
+	int cs_em;                          // int2 [C+1]: {current error, mark}
 	int cnt;                            // uint16 [cnt_total]
 	int counters;                       // int64 [8] GhostCounters, updated by thread 0
 	int flags;                          // uint8 [V]   sampling scratch

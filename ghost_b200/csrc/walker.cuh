@@ -120,7 +120,8 @@ struct WST {
 	typedef XT x_type;
 	XT* x; int* err_var;
 	unsigned short* tabu;       // tabu_until - tabu_base, 16 bits (see WalkerRegs::tabu_base)
-	int4* cs;                   // per constraint {T = sum - rhs (linear kinds), current error, mark, 0}
+	int2* cs;                   // per constraint {T = sum - rhs (linear kinds), a_v of the hoisted variable}
+	int2* cem;                  // per constraint {current error, mark}
 	int* cand_key; unsigned* cand_bits;
 	unsigned* cnt32;            // packed 16-bit counters, two per word
 	long long* counters;        // GhostCounters, thread 0 only
@@ -133,9 +134,10 @@ struct WST {
 		atomicAdd(&cnt32[idx >> 1], (unsigned)d << ((idx & 1) * 16));
 	}
 	__device__ __forceinline__ int& T_of(int c) const { return reinterpret_cast<int*>(cs + c)[0]; }
+	__device__ __forceinline__ int& av_of(int c) const { return reinterpret_cast<int*>(cs + c)[1]; }
 	// field order {T, a_v, error, mark}: the LinearEq evaluation loop needs only the first two
-	__device__ __forceinline__ int& err_of(int c) const { return reinterpret_cast<int*>(cs + c)[2]; }
-	__device__ __forceinline__ int& mark_of(int c) const { return reinterpret_cast<int*>(cs + c)[3]; }
+	__device__ __forceinline__ int& err_of(int c) const { return reinterpret_cast<int*>(cem + c)[0]; }
+	__device__ __forceinline__ int& mark_of(int c) const { return reinterpret_cast<int*>(cem + c)[1]; }
 };
 
 template <class WS>
@@ -150,7 +152,7 @@ __device__ __forceinline__ WS make_ws(unsigned char* base_in, const WalkerLayout
 	unsigned char* base = static_cast<unsigned char*>(__cvta_shared_to_generic(sbase));
 	WS s;
 	s.x = (typename WS::x_type*)(base + L.x); s.err_var = (int*)(base + L.err_var); s.tabu = (unsigned short*)(base + L.tabu);
-	s.cs = (int4*)(base + L.cs);
+	s.cs = (int2*)(base + L.cs); s.cem = (int2*)(base + L.cs_em);
 	s.cand_key = (int*)(base + L.cand_key); s.cand_bits = (unsigned*)(base + L.cand_bits);
 	s.cnt32 = (unsigned*)(base + L.cnt);
 	s.counters = (long long*)(base + L.counters); s.flags = base + L.flags;
@@ -391,7 +393,7 @@ __device__ inline int recompute_all(const DevModel& m, const WS& s, int* red)
 	typedef Group<T> G;
 	MV mv(m);
 	const int tid = G::tid(), lane = threadIdx.x & 31;
-	for (int c = tid; c < m.C; c += T) s.cs[c] = make_int4(0, 0, 0, 0);
+	for (int c = tid; c < m.C; c += T) { s.cs[c] = make_int2(0, 0); s.cem[c] = make_int2(0, 0); }
 	if (!EQ) for (int t = tid; t < (m.cnt_total + 1) / 2; t += T) s.cnt32[t] = 0;
 	G::sync();
 	const int nnz_pad = (m.nnz + 31) & ~31;
@@ -662,9 +664,8 @@ __device__ inline int hoist_variable(const DevModel& m, const WS& s, int v, int*
 		int cls = ell_cls(e.x);
 		int4 h = make_int4(cls | (ell_w(e.x) << 4) | (c << 8), 0, 0, 0);
 		if (cls == GB_CLS_LINEAR) {
-			int4 st = s.cs[c];
-			h.y = e.y; h.z = st.x - e.y * xv;
-			bias -= st.z;
+			h.y = e.y; h.z = s.T_of(c) - e.y * xv;
+			bias -= s.err_of(c);
 		} else if (cls == GB_CLS_ALLDIFF) {
 			int tab = mv.cnt_tab(c);
 			int sub = s.cnt(tab + xv) - 1;
@@ -686,8 +687,7 @@ __device__ inline int hoist_variable(const DevModel& m, const WS& s, int v, int*
 			if (m.permutation) {
 				// mark + the selected variable's coefficient next to the constraint state: the swap
 				// partner's loop reads one int4 and needs no second lookup for a shared constraint
-				int* st = reinterpret_cast<int*>(s.cs + c);
-				st[3] = nh + 1; st[1] = e.y;
+				s.mark_of(c) = nh + 1; s.av_of(c) = e.y;
 			}
 		}
 		++nh;
@@ -702,7 +702,7 @@ __device__ inline void unmark_variable(const DevModel& m, const WS& s, int v)
 	const int2* row = mv.ell_row(v);
 	for (int k = Group<T>::tid(); k < m.ell_stride; k += T) {
 		int c = ell_ctr(__ldg(row + k).x);
-		if (c != m.C) { int* st = reinterpret_cast<int*>(s.cs + c); st[1] = 0; st[3] = 0; }
+		if (c != m.C) { s.av_of(c) = 0; s.mark_of(c) = 0; }
 	}
 }
 
@@ -714,7 +714,7 @@ __device__ inline int hoist_variable_eq(const DevModel& m, const WS& s, int v, i
 	MV mv(m);
 	const int lane = threadIdx.x & 31;
 	const int xv = s.x[v];
-	const int nrow = m.ell_eq_stride, dummy = m.C * 16;
+	const int nrow = m.ell_eq_stride, dummy = m.C * 8;
 	const unsigned* row = mv.eq_row(v);
 	unsigned char* cs_bytes = reinterpret_cast<unsigned char*>(s.cs);
 	const bool writer = Group<T>::warp() == 0;
@@ -726,12 +726,12 @@ __device__ inline int hoist_variable_eq(const DevModel& m, const WS& s, int v, i
 		const bool valid = off != dummy;
 		int err = 0;
 		if (valid) {
-			int* st = reinterpret_cast<int*>(cs_bytes + off);
-			const int t = st[0];
-			err = st[2];
+			const int c = off >> 3;
+			const int t = s.T_of(c);
+			err = s.err_of(c);
 			if (writer) {
-				s.hoist[k] = make_int4(GB_CLS_LINEAR | (3 << 4) | ((off >> 4) << 8), a, t - a * xv, 0);
-				if (PERM) { st[3] = k + 1; st[1] = a; }
+				s.hoist[k] = make_int4(GB_CLS_LINEAR | (3 << 4) | (c << 8), a, t - a * xv, 0);
+				if (PERM) { s.mark_of(c) = k + 1; s.av_of(c) = a; }
 			}
 		}
 		nh += __popc(__ballot_sync(0xffffffffu, valid));
@@ -747,8 +747,8 @@ __device__ inline void unmark_variable_eq(const DevModel& m, const WS& s, int v)
 	const unsigned* row = mv.eq_row(v);
 	unsigned char* cs_bytes = reinterpret_cast<unsigned char*>(s.cs);
 	for (int k = Group<T>::tid(); k < m.ell_eq_stride; k += T) {
-		int* st = reinterpret_cast<int*>(cs_bytes + (__ldg(row + k) & 0xFFFFu));
-		st[1] = 0; st[3] = 0; // the dummy entry is all zeros anyway
+		const int c = (int)(__ldg(row + k) & 0xFFFFu) >> 3;
+		s.av_of(c) = 0; s.mark_of(c) = 0; // the dummy entry is all zeros anyway
 	}
 }
 
@@ -795,7 +795,7 @@ __device__ __forceinline__ bool candidate_sum(const DevModel& m, const MV& mv, c
 		int2 e = __ldg(row + k);
 		int c = ell_ctr(e.x);
 		if (c == m.C) break; // padding
-		int4 st = s.cs[c];
+		const int4 st = make_int4(s.T_of(c), 0, s.err_of(c), s.mark_of(c));
 		int cls = ell_cls(e.x);
 		if (st.w == 0) {
 			// constraint of the partner only: {j} -> {x_v}  (search_unit.hpp:881-885)
@@ -1018,18 +1018,18 @@ __device__ inline void apply_move_eq(const DevModel& m, const WS& s, int v, int 
 			if (PERM)
 				for (int e = 0; e < nrow; ++e) {
 					const unsigned f = __ldg(rowj + e);
-					if ((int)(f & 0xFFFFu) == c * 16) { tnew += ((int)f >> 16) * (xv - xj); break; } // the partner is in this scope too
+					if ((int)(f & 0xFFFFu) == c * 8) { tnew += ((int)f >> 16) * (xv - xj); break; } // the partner is in this scope too
 				}
 			delta = abs(tnew) - abs(told);
 			s.T_of(c) = tnew; s.err_of(c) = abs(tnew);
 		} else {
 			const unsigned f = __ldg(rowj + (k - nh));
-			int* st = reinterpret_cast<int*>(cs_bytes + (f & 0xFFFFu));
-			if ((int)(f & 0xFFFFu) != m.C * 16 && st[3] == 0) { // not padding, not shared with v (handled above)
-				c = (int)(f & 0xFFFFu) >> 4;
-				const int told = st[0], tnew = told + ((int)f >> 16) * (xv - xj);
+			const int cc = (int)(f & 0xFFFFu) >> 3;
+			if (cc != m.C && s.mark_of(cc) == 0) { // not padding, not shared with v (handled above)
+				c = cc;
+				const int told = s.T_of(c), tnew = told + ((int)f >> 16) * (xv - xj);
 				delta = abs(tnew) - abs(told);
-				st[0] = tnew; st[2] = abs(tnew);
+				s.T_of(c) = tnew; s.err_of(c) = abs(tnew);
 			}
 		}
 		*delta_out = delta;
