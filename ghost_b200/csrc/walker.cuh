@@ -652,45 +652,53 @@ template <int T, class WS>
 __device__ inline int hoist_variable(const DevModel& m, const WS& s, int v, int* bias_out)
 {
 	MV mv(m);
+	const int lane = threadIdx.x & 31;
 	const int2* row = mv.ell_row(v);
 	const int xv = s.x[v];
 	int nh = 0, bias = 0;
-	const bool writer = Group<T>::tid() == 0;
-	// every thread walks the (short) row: the count and the bias are needed by all, thread 0 writes
-	for (int k = 0; k < m.ell_stride; ++k) {
-		int2 e = __ldg(row + k);
-		int c = ell_ctr(e.x);
-		if (c == m.C) break; // padding
-		int cls = ell_cls(e.x);
-		int4 h = make_int4(cls | (ell_w(e.x) << 4) | (c << 8), 0, 0, 0);
-		if (cls == GB_CLS_LINEAR) {
-			h.y = e.y; h.z = s.T_of(c) - e.y * xv;
-			bias -= s.err_of(c);
-		} else if (cls == GB_CLS_ALLDIFF) {
-			int tab = mv.cnt_tab(c);
-			int sub = s.cnt(tab + xv) - 1;
-			h.y = tab; h.z = sub;
-			bias -= sub;
-		} else if (cls == GB_CLS_FIX) {
-			int kk = mv.rhs(c);
-			h.y = kk;
-			bias -= abs(xv - kk);
-		} else if (cls == GB_CLS_ABSDIFF) {
-			h.y = e.y;
-		} else if (cls == GB_CLS_ALLEQ) {
-			const int tab = mv.cnt_tab(c), state = s.T_of(c);
-			h.y = tab; h.z = alleq_base(state, s.cnt(tab + xv));
-			bias += alleq_max1(state);
-		}
-		if (writer) {
-			s.hoist[nh] = h;
-			if (m.permutation) {
-				// mark + the selected variable's coefficient next to the constraint state: the swap
-				// partner's loop reads one int4 and needs no second lookup for a shared constraint
-				s.mark_of(c) = nh + 1; s.av_of(c) = e.y;
+	const bool writer = Group<T>::warp() == 0;
+	// one lane per row entry (live entries come first in a row, so entry k is hoisted entry k); the count
+	// and the bias are warp reductions, every warp of a wider group computes them, warp 0 writes
+	for (int base = 0; base < m.ell_stride; base += 32) {
+		const int k = base + lane;
+		int2 e = make_int2(m.C | (GB_CLS_ZERO << 20), 0);
+		if (k < m.ell_stride) e = __ldg(row + k);
+		const int c = ell_ctr(e.x);
+		const bool valid = c != m.C;
+		int contrib = 0;
+		if (valid) {
+			const int cls = ell_cls(e.x);
+			int4 h = make_int4(cls | (ell_w(e.x) << 4) | (c << 8), 0, 0, 0);
+			if (cls == GB_CLS_LINEAR) {
+				h.y = e.y; h.z = s.T_of(c) - e.y * xv;
+				contrib = -s.err_of(c);
+			} else if (cls == GB_CLS_ALLDIFF) {
+				const int tab = mv.cnt_tab(c);
+				const int sub = s.cnt(tab + xv) - 1;
+				h.y = tab; h.z = sub;
+				contrib = -sub;
+			} else if (cls == GB_CLS_FIX) {
+				const int kk = mv.rhs(c);
+				h.y = kk;
+				contrib = -abs(xv - kk);
+			} else if (cls == GB_CLS_ABSDIFF) {
+				h.y = e.y;
+			} else if (cls == GB_CLS_ALLEQ) {
+				const int tab = mv.cnt_tab(c), state = s.T_of(c);
+				h.y = tab; h.z = alleq_base(state, s.cnt(tab + xv));
+				contrib = alleq_max1(state);
+			}
+			if (writer) {
+				s.hoist[k] = h;
+				if (m.permutation) {
+					// mark + the selected variable's coefficient next to the constraint state: the swap
+					// partner's loop needs no second lookup for a shared constraint
+					s.mark_of(c) = k + 1; s.av_of(c) = e.y;
+				}
 			}
 		}
-		++nh;
+		nh += __popc(__ballot_sync(0xffffffffu, valid));
+		bias += __reduce_add_sync(0xffffffffu, contrib);
 	}
 	*bias_out = bias;
 	return nh;
