@@ -1146,6 +1146,20 @@ __device__ inline void apply_move(const DevModel& m, const WS& s, int v, int new
 		s.upd[2 * k] = c; s.upd[2 * k + 1] = delta;
 	}
 	G::sync();
+	// projection update (…projection_algorithm.cpp:51-58).  A constraint with a short scope (the binary
+	// and ternary links of the n-queens / Costas models) is scattered by ONE thread, all of them at once;
+	// a long scope (AllDifferent, knapsack rows) by the whole group.
+	for (int base = 0; base < naff; base += T) {
+		const int k = base + tid;
+		int c = -1, delta = 0, b = 0, e = 0;
+		if (k < naff) { c = s.upd[2 * k]; delta = s.upd[2 * k + 1]; }
+		const bool live = c >= 0 && delta != 0;
+		if (live) { b = mv.scope_begin(c); e = mv.scope_begin(c + 1); }
+		const bool small = live && e - b <= 8;
+		if (small) for (int i = b; i < e; ++i) atomicAdd(&s.err_var[mv.scope_pos(i)], delta);
+		if (live && !small) s.upd[2 * k + 1] = delta; else if (k < naff) s.upd[2 * k + 1] = 0; // what is left for the group pass
+	}
+	G::sync();
 	for (int k = 0; k < naff; ++k) {
 		int c = s.upd[2 * k], delta = s.upd[2 * k + 1];
 		if (c < 0 || delta == 0) continue;
