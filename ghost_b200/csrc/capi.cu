@@ -264,10 +264,17 @@ extern "C" int ghost_b200_search_begin(GhostModel* gm, const GhostSearchOpts* op
 	if (rc) { delete s; return rc; }
 	s->T = cfg.T; s->walkers_per_cta = cfg.walkers_per_cta; s->block = cfg.block; s->smem = cfg.smem;
 	if (s->opts.number_walkers <= 0) {
-		// fill the GPU: as many CTAs as are resident at once, by shared memory and threads
-		int by_smem = (int)std::max<size_t>(1, (size_t)(227 * 1024) / std::max<size_t>(1, cfg.smem + 1024));
-		int by_threads = std::max(1, 2048 / cfg.block);
-		int ctas_per_sm = std::min(std::min(by_smem, by_threads), 32);
+		// fill the GPU with exactly one wave: as many CTAs as the kernel this model runs keeps resident at
+		// once (registers, shared memory, threads) — one CTA more per SM would start a second, nearly empty wave
+		int ctas_per_sm = 0;
+		cudaError_t oe = cudaErrorInvalidValue;
+		switch (cfg.T) {
+		case 32: oe = occupancy_search_t32(cfg.block, cfg.smem, m, &ctas_per_sm); break;
+		case 64: oe = occupancy_search_t64(cfg.block, cfg.smem, m, &ctas_per_sm); break;
+		case 128: oe = occupancy_search_t128(cfg.block, cfg.smem, m, &ctas_per_sm); break;
+		case 256: oe = occupancy_search_t256(cfg.block, cfg.smem, m, &ctas_per_sm); break;
+		}
+		if (oe != cudaSuccess || ctas_per_sm < 1) { delete s; return set_error(GHOST_B200_ERR_CUDA, std::string("occupancy query: ") + cudaGetErrorString(oe)); }
 		s->opts.number_walkers = gm->sm_count * ctas_per_sm * cfg.walkers_per_cta;
 	}
 	s->walkers = s->opts.number_walkers;

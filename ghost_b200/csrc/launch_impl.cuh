@@ -20,6 +20,14 @@ static cudaError_t do_search(int grid, int block, size_t smem, cudaStream_t st, 
 	search_kernel<GB_T, PERM, EQ, XT><<<grid, block, smem, st>>>(m, L, p);
 	return cudaGetLastError();
 }
+// resident CTAs per SM of the search kernel this model dispatches to (registers, shared memory, threads)
+template <bool PERM, bool EQ, class XT>
+static cudaError_t do_occupancy(int block, size_t smem, int* ctas_per_sm)
+{
+	cudaError_t e = allow_smem(search_kernel<GB_T, PERM, EQ, XT>, smem);
+	if (e != cudaSuccess) return e;
+	return cudaOccupancyMaxActiveBlocksPerMultiprocessor(ctas_per_sm, search_kernel<GB_T, PERM, EQ, XT>, block, smem);
+}
 template <bool PERM, bool EQ, class XT>
 static cudaError_t do_eval(int grid, int block, size_t smem, cudaStream_t st, const DevModel& m, const WalkerLayout& L, int W,
                            const int* x, const int* sel, int* ce, int* ve, int* cd)
@@ -52,6 +60,10 @@ cudaError_t GB_CAT(launch_search_t, GB_T)(int grid, int block, size_t smem, cuda
                                           const WalkerLayout& L, const SearchParams& p)
 {
 	GB_DISPATCH(do_search, grid, block, smem, st, m, L, p);
+}
+cudaError_t GB_CAT(occupancy_search_t, GB_T)(int block, size_t smem, const DevModel& m, int* ctas_per_sm)
+{
+	GB_DISPATCH(do_occupancy, block, smem, ctas_per_sm);
 }
 cudaError_t GB_CAT(launch_eval_t, GB_T)(int grid, int block, size_t smem, cudaStream_t st, const DevModel& m,
                                         const WalkerLayout& L, int W, const int* x, const int* sel, int* ce, int* ve, int* cd)
