@@ -179,7 +179,7 @@ def main():
     ap.add_argument("--cpu-seconds", type=float, default=10.0)
     ap.add_argument("--e2e-seconds", type=float, default=1.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--tts-seeds", type=int, default=9, help="time-to-solution runs (0: skip)")
+    ap.add_argument("--tts-seeds", type=int, default=21, help="time-to-solution runs (0: skip)")
     ap.add_argument("--tts-timeout", type=float, default=10.0)
     ap.add_argument("--reseed-every", type=int, default=16, help="timed steps per walker population (0: never replace it)")
     ap.add_argument("--opt", action="append", default=[], help="search option override name=int (diagnostics)")
