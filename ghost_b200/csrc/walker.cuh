@@ -135,7 +135,7 @@ struct WST {
 	}
 	__device__ __forceinline__ int& T_of(int c) const { return reinterpret_cast<int*>(cs + c)[0]; }
 	__device__ __forceinline__ int& av_of(int c) const { return reinterpret_cast<int*>(cs + c)[1]; }
-	// field order {T, a_v, error, mark}: the LinearEq evaluation loop needs only the first two
+	// two arrays of 8-byte stride: {T, a_v} is all the LinearEq evaluation loop gathers; {error, mark} serves the rest
 	__device__ __forceinline__ int& err_of(int c) const { return reinterpret_cast<int*>(cem + c)[0]; }
 	__device__ __forceinline__ int& mark_of(int c) const { return reinterpret_cast<int*>(cem + c)[1]; }
 };
@@ -724,7 +724,6 @@ __device__ inline int hoist_variable_eq(const DevModel& m, const WS& s, int v, i
 	const int xv = s.x[v];
 	const int nrow = m.ell_eq_stride, dummy = m.C * 8;
 	const unsigned* row = mv.eq_row(v);
-	unsigned char* cs_bytes = reinterpret_cast<unsigned char*>(s.cs);
 	const bool writer = Group<T>::warp() == 0;
 	int nh = 0, bias = 0;
 	for (int base = 0; base < nrow; base += 32) {
@@ -753,7 +752,6 @@ __device__ inline void unmark_variable_eq(const DevModel& m, const WS& s, int v)
 {
 	MV mv(m);
 	const unsigned* row = mv.eq_row(v);
-	unsigned char* cs_bytes = reinterpret_cast<unsigned char*>(s.cs);
 	for (int k = Group<T>::tid(); k < m.ell_eq_stride; k += T) {
 		const int c = (int)(__ldg(row + k) & 0xFFFFu) >> 3;
 		s.av_of(c) = 0; s.mark_of(c) = 0; // the dummy entry is all zeros anyway
@@ -1012,7 +1010,6 @@ __device__ inline void apply_move_eq(const DevModel& m, const WS& s, int v, int 
 	const int nv_new = PERM ? xj : new_value;
 	const int nrow = m.ell_eq_stride;
 	const unsigned* rowj = mv.eq_row(j);
-	unsigned char* cs_bytes = reinterpret_cast<unsigned char*>(s.cs);
 	const int naff = nh + (PERM ? nrow : 0);
 	// new state of affected constraint k (hoisted ones first, then the partner's row); returns its id
 	// (-1: nothing to do) and the change of its error
