@@ -439,7 +439,7 @@ search_kernel(const __grid_constant__ DevModel m, const __grid_constant__ Walker
 			const uint4 rnd = rng.block(rng.next_event++, 0);
 			// UniformVariableHeuristic::select_variable (uniform_variable_heuristic.cpp:38-41)
 			const int kv = (int)below(rnd.x, (uint32_t)r.ncand);
-			const int v = T == 32 ? regs_pick_kth(cq, r.cand_max, kv) : pick_kth(s.cand_key, s.cand_bits, L.nchunks_v, r.cand_max, kv);
+			const int v = T == 32 ? regs_pick_kth(cq, r.cand_max, kv, r.ncand) : pick_kth(s.cand_key, s.cand_bits, L.nchunks_v, r.cand_max, kv);
 			--r.ncand;
 			int bias;
 			const int nh = EQ ? hoist_variable_eq<T, PERM>(m, s, v, &bias) : hoist_variable<T>(m, s, v, &bias);
@@ -469,7 +469,7 @@ search_kernel(const __grid_constant__ DevModel m, const __grid_constant__ Walker
 					long long cf = internal_cost(m, (long long)mv.obj_coef(v));
 					k = cf > 0 ? 0 : cf < 0 ? nties - 1 : (int)below(rnd.y, (uint32_t)nties);
 				} else k = (int)below(rnd.y, (uint32_t)nties);
-				int slot = T == 32 ? regs_pick_kth(vq, gmin, k) : pick_kth(s.val_key, s.val_bits, L.nchunks_c, gmin, k);
+				int slot = T == 32 ? regs_pick_kth(vq, gmin, k, nties) : pick_kth(s.val_key, s.val_bits, L.nchunks_c, gmin, k);
 				new_value = PERM ? slot : mv.dom_value(v, slot);
 			}
 			trace_var = v; trace_val = new_value; trace_min = gmin;

@@ -537,10 +537,14 @@ __device__ __forceinline__ int regs_count(const ChunkRegs& q, int best)
 {
 	return __reduce_add_sync(0xffffffffu, q.key == best ? __popc(q.bits) : 0);
 }
-static __device__ GB_OUTLINE int regs_pick_kth_impl(int key, unsigned bits, int best, int k)
+static __device__ GB_OUTLINE int regs_pick_kth_impl(int key, unsigned bits, int best, int k, int n)
 {
 	const int lane = threadIdx.x & 31;
 	const unsigned b = key == best ? bits : 0u;
+	if (n == 1) { // a single member (the usual case for the min-conflict value): no prefix sum needed
+		const int only = __ffs(__ballot_sync(0xffffffffu, b != 0u)) - 1;
+		return only * 32 + __ffs(__shfl_sync(0xffffffffu, b, only)) - 1;
+	}
 	const int c = __popc(b);
 	int incl = c;
 #pragma unroll
@@ -554,7 +558,8 @@ static __device__ GB_OUTLINE int regs_pick_kth_impl(int key, unsigned bits, int 
 	const unsigned wb = __shfl_sync(0xffffffffu, b, src);
 	return src * 32 + __fns(wb, 0, k - excl + 1);
 }
-__device__ __forceinline__ int regs_pick_kth(const ChunkRegs& q, int best, int k) { return regs_pick_kth_impl(q.key, q.bits, best, k); }
+// n = size of the set (known to the caller)
+__device__ __forceinline__ int regs_pick_kth(const ChunkRegs& q, int best, int k, int n) { return regs_pick_kth_impl(q.key, q.bits, best, k, n); }
 
 // One chunk of the variable scan: the chunk's largest eligible error and the lanes that hold it.
 template <int T, class WS>
