@@ -1052,10 +1052,12 @@ __device__ inline void apply_move_eq(const DevModel& m, const WS& s, int v, int 
 			const int c = update(lane, &myd);
 			if (c >= 0 && myd != 0) { myb = mv.scope_begin(c); mye = mv.scope_begin(c + 1); }
 		}
-		__syncwarp();
-		for (int k = 0; k < naff; ++k) {
+		// only the constraints whose error changed (padding entries, shared ones and zero deltas drop out here)
+		unsigned todo = __ballot_sync(0xffffffffu, myd != 0);
+		while (todo) {
+			const int k = __ffs(todo) - 1;
+			todo &= todo - 1;
 			const int d = __shfl_sync(0xffffffffu, myd, k), b = __shfl_sync(0xffffffffu, myb, k), e = __shfl_sync(0xffffffffu, mye, k);
-			if (d == 0) continue;
 			for (int i = b + lane; i < e; i += 32) atomicAdd(&s.err_var[mv.scope_pos(i)], d);
 		}
 		__syncwarp();

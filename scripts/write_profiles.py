@@ -1,0 +1,46 @@
+"""Turn the captures a gpurun call left in gpurun_out/ (r1_launches.csv, r1_search_full.ncu-rep) into the tracked
+summaries under profiles/: launch list + share per kernel, key ncu metrics of the search kernel, DRAM traffic json."""
+import csv, json, os, shutil, subprocess, sys
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+G, P = os.path.join(ROOT, "gpurun_out"), os.path.join(ROOT, "profiles")
+CMD = "python bench.py --steps 10 --warmup 3 --no-cpu-baseline --tts-seeds 0"
+shutil.copy(os.path.join(G, "r1_launches.csv"), os.path.join(P, "r1_launches.csv"))
+summ = subprocess.run([sys.executable, os.path.join(ROOT, "scripts", "ncu_launches.py"), os.path.join(G, "r1_launches.csv")], capture_output=True, text=True).stdout
+with open(os.path.join(P, "r1_launches_summary.txt"), "w") as f:
+    f.write(f"# ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv {CMD}\n"
+            "# (B200, magic_square:30, 3552 walkers, 256 iterations per launch; per-launch times under ncu are serialised and\n"
+            "#  cold-cache: the kernel's SHARE of the step is what carries over, not the absolute time)\n")
+    f.write("\n".join(l[:170] for l in summ.splitlines()) + "\n\n")
+    f.write("# search_kernel launches = 3 warm-up + 10 timed steps of bench.py's value leg and the 3 x (initial sampling + adaptive\n"
+            "# epochs) of its e2e leg (ghost_b200_search); issue_kernel / smem_kernel are the roofline microbenchmarks; the torch fill\n"
+            "# kernels are the 256 MiB L2 flush between timed steps (outside the event pairs).\n")
+raw = subprocess.run(["ncu", "-i", os.path.join(G, "r1_search_full.ncu-rep"), "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+r = list(csv.reader(raw.splitlines())); h, u, v = r[0], r[1], r[-1]
+want = ['gpu__time_duration.sum', 'launch__grid_size', 'launch__block_size', 'launch__registers_per_thread', 'launch__shared_mem_per_block_dynamic',
+        'launch__occupancy_limit_registers', 'launch__occupancy_limit_shared_mem', 'launch__waves_per_multiprocessor',
+        'sm__warps_active.avg.pct_of_peak_sustained_active', 'smsp__inst_executed.sum', 'sm__inst_executed.avg.per_cycle_elapsed',
+        'smsp__issue_active.avg.pct_of_peak_sustained_active', 'smsp__thread_inst_executed_per_inst_executed.ratio',
+        'smsp__warps_eligible.avg.per_cycle_active', 'sm__icc_request_hit_rate.pct', 'l1tex__t_sector_hit_rate.pct', 'lts__t_sector_hit_rate.pct',
+        'dram__bytes_read.sum', 'dram__bytes_write.sum', 'l1tex__data_pipe_lsu_wavefronts_mem_shared.sum',
+        'l1tex__data_pipe_lsu_wavefronts_mem_shared.sum.pct_of_peak_sustained_elapsed', 'l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum',
+        'sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active', 'sm__inst_executed_pipe_fma.avg.pct_of_peak_sustained_active',
+        'sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active', 'sm__throughput.avg.pct_of_peak_sustained_elapsed']
+want += [k for k in h if k.startswith('smsp__average_warps_issue_stalled_') and k.endswith('_per_issue_active.ratio') and 'not_issued' not in k]
+lines = [f"ncu --set full --clock-control none --import-source on, search_kernel<32,true,true,unsigned short>, magic_square:30, 3552 walkers x 256 "
+         f"iterations, 1 launch (7th launch of: {CMD})"]
+val = {}
+for k in want:
+    if k not in h: continue
+    i = h.index(k); val[k] = (v[i], u[i])
+    try:
+        if k.startswith('smsp__average') and float(v[i]) < 0.1: continue
+    except ValueError: pass
+    lines.append(f"{k:100s} {v[i]:>16s} {u[i]}")
+scale = {'byte': 1, 'Kbyte': 1e3, 'Mbyte': 1e6, 'Gbyte': 1e9}
+tb = int(sum(float(val[k][0].replace(',', '')) * scale[val[k][1]] for k in ('dram__bytes_read.sum', 'dram__bytes_write.sum')))
+lines.append(f"traffic (dram read+write) bytes per launch: {tb}")
+lines.append("algorithmic HBM bytes per launch: walker state load + store = 2 x 3552 x 8.9 KB (persist region) = 63 MB; the stores stay in L2 within the launch")
+open(os.path.join(P, "r1_search_kernel_ncu.txt"), "w").write("\n".join(lines) + "\n")
+json.dump({"workload": "magic_square:30", "walkers": 3552, "epoch_iterations": 256, "dram_bytes_per_launch": tb,
+           "source": "profiles/r1_search_kernel_ncu.txt (ncu --set full, one launch)"}, open(os.path.join(P, "r1_traffic.json"), "w"))
+print("profiles written; traffic", tb)
