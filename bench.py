@@ -182,6 +182,8 @@ def main():
     ap.add_argument("--tts-seeds", type=int, default=21, help="time-to-solution runs (0: skip)")
     ap.add_argument("--tts-timeout", type=float, default=10.0)
     ap.add_argument("--reseed-every", type=int, default=16, help="timed steps per walker population (0: never replace it)")
+    ap.add_argument("--rigid-epochs", action="store_true", help="exactly --epoch iterations per walker per step (default: elastic "
+                    "epochs, GhostSearchOpts::elastic_epochs: early finishers keep iterating until the slowest walker is done)")
     ap.add_argument("--opt", action="append", default=[], help="search option override name=int (diagnostics)")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "ours":
@@ -208,7 +210,7 @@ def main():
     desc = problems.by_name(args.workload)
     model = capi.Model(desc)
     opts = default_opts(seed=20261106, number_walkers=args.walkers, threads_per_walker=args.threads_per_walker,
-                        stop_on_first_solution=0, first_walker_id=0)
+                        stop_on_first_solution=0, first_walker_id=0, elastic_epochs=0 if args.rigid_epochs else 1)
     for kv in args.opt:   # diagnostic overrides of the search options (not used by the default run)
         name, value = kv.split("=")
         setattr(opts, name, int(value))
@@ -330,7 +332,7 @@ def main():
         "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "int32", "data": "synthetic",
         "config": {"workload": args.workload, "walkers_per_gpu": W, "threads_per_walker": res0["threads_per_walker"],
-                   "epoch_iterations": args.epoch, "parallelism": f"walkers sharded over {world} GPU(s)",
+                   "epoch_iterations": args.epoch, "elastic_epochs": not args.rigid_epochs, "parallelism": f"walkers sharded over {world} GPU(s)",
                    "l2": "flushed between timed steps (256 MiB fill)"},
         "walker_iters_per_sec": iters / (ms * 1e-3),
         "gpu_launches": args.steps, "clocks": clocks, "roofline": roofline, "wall_s": t_wall,

@@ -45,6 +45,9 @@ struct GhostSearch {
 	WalkerScalars* d_scalars = nullptr;
 	int* d_best_x = nullptr;
 	int* d_stop = nullptr;
+	int* d_finished = nullptr;      // elastic epochs: per-launch count of walkers that have done their nominal share
+	int resident_walkers = 0;       // walkers one wave of the kernel keeps resident (elastic epochs need the whole grid resident)
+	int elastic = 0;                // this search runs elastic epochs
 	int* d_stop_peer = nullptr;     // another search's stop flag, mapped over NVLink; used instead of d_stop when set
 	bool stop_peer_is_ipc = false;  // mapped from another process (CUDA IPC) rather than a peer device of this one
 	unsigned long long* d_best_key = nullptr;
@@ -238,7 +241,7 @@ extern "C" void ghost_b200_search_end(GhostSearch* s)
 {
 	if (!s) return;
 	if (s->d_stop_peer && s->stop_peer_is_ipc) cudaIpcCloseMemHandle(s->d_stop_peer);
-	cudaFree(s->d_state); cudaFree(s->d_scalars); cudaFree(s->d_best_x); cudaFree(s->d_stop);
+	cudaFree(s->d_state); cudaFree(s->d_scalars); cudaFree(s->d_best_x); cudaFree(s->d_stop); cudaFree(s->d_finished);
 	cudaFree(s->d_best_key); cudaFree(s->d_trace); cudaFree(s->d_trace_len);
 	if (s->ev0) cudaEventDestroy(s->ev0);
 	if (s->ev1) cudaEventDestroy(s->ev1);
@@ -263,9 +266,10 @@ extern "C" int ghost_b200_search_begin(GhostModel* gm, const GhostSearchOpts* op
 	rc = pick_launch(gm, s->layout, s->opts.threads_per_walker, &cfg);
 	if (rc) { delete s; return rc; }
 	s->T = cfg.T; s->walkers_per_cta = cfg.walkers_per_cta; s->block = cfg.block; s->smem = cfg.smem;
-	if (s->opts.number_walkers <= 0) {
-		// fill the GPU with exactly one wave: as many CTAs as the kernel this model runs keeps resident at
-		// once (registers, shared memory, threads) — one CTA more per SM would start a second, nearly empty wave
+	{
+		// one wave = as many CTAs as the kernel this model runs keeps resident at once (registers, shared
+		// memory, threads).  The default population is exactly that: one CTA more per SM would start a
+		// second, nearly empty wave.
 		int ctas_per_sm = 0;
 		cudaError_t oe = cudaErrorInvalidValue;
 		switch (cfg.T) {
@@ -275,8 +279,10 @@ extern "C" int ghost_b200_search_begin(GhostModel* gm, const GhostSearchOpts* op
 		case 256: oe = occupancy_search_t256(cfg.block, cfg.smem, m, &ctas_per_sm); break;
 		}
 		if (oe != cudaSuccess || ctas_per_sm < 1) { delete s; return set_error(GHOST_B200_ERR_CUDA, std::string("occupancy query: ") + cudaGetErrorString(oe)); }
-		s->opts.number_walkers = gm->sm_count * ctas_per_sm * cfg.walkers_per_cta;
+		s->resident_walkers = gm->sm_count * ctas_per_sm * cfg.walkers_per_cta;
+		if (s->opts.number_walkers <= 0) s->opts.number_walkers = s->resident_walkers;
 	}
+	s->elastic = s->opts.elastic_epochs == 1 ? 1 : 0;
 	s->walkers = s->opts.number_walkers;
 	if (s->walkers >= (1 << 24)) { delete s; return set_error(GHOST_B200_ERR_INVALID, "at most 2^24-1 walkers per device"); }
 	if (s->opts.tabu_time_local_min > 30000 || s->opts.tabu_time_selected > 30000) {
@@ -293,6 +299,8 @@ extern "C" int ghost_b200_search_begin(GhostModel* gm, const GhostSearchOpts* op
 	TRY_OR_END(cudaMalloc(&s->d_best_key, sizeof(unsigned long long)));
 	TRY_OR_END(cudaMemset(s->d_scalars, 0, W * sizeof(WalkerScalars)));
 	TRY_OR_END(cudaMemset(s->d_stop, 0, sizeof(int)));
+	TRY_OR_END(cudaMalloc(&s->d_finished, sizeof(int)));
+	TRY_OR_END(cudaMemset(s->d_finished, 0, sizeof(int)));
 	TRY_OR_END(cudaMemset(s->d_best_key, 0xff, sizeof(unsigned long long)));
 	if (s->opts.resume_search) {
 		std::vector<WalkerScalars> init(W);
@@ -333,6 +341,9 @@ extern "C" int ghost_b200_search_epoch(GhostSearch* s, int32_t iterations, void*
 	p.seed = o.seed; p.first_walker = o.first_walker_id;
 	p.state = s->d_state; p.scalars = s->d_scalars; p.best_x = s->d_best_x; p.stop_flag = s->d_stop_peer ? s->d_stop_peer : s->d_stop;
 	p.best_key = s->d_best_key;
+	p.finished = s->d_finished;
+	p.elastic = (s->elastic && s->walkers <= s->resident_walkers) ? 1 : 0;
+	if (p.elastic) CUDA_TRY(cudaMemsetAsync(s->d_finished, 0, sizeof(int), (cudaStream_t)stream));
 	p.trace = s->d_trace; p.trace_cap = s->trace_cap; p.trace_walker = 0; p.trace_len = s->d_trace_len;
 	CUDA_TRY(launch_search(s->T, s->grid, s->block, s->smem, (cudaStream_t)stream, s->model->low.dev, s->layout, p));
 	s->launches += 1;
@@ -481,6 +492,7 @@ extern "C" int ghost_b200_search(GhostModel* gm, const GhostSearchOpts* opts, Gh
 	const auto tp0 = std::chrono::steady_clock::now();
 	int rc = ghost_b200_search_begin(gm, opts, &s);
 	if (rc) return rc;
+	if (opts->elastic_epochs == 0 && opts->timeout_us > 0 && opts->max_iterations <= 0) s->elastic = 1; // auto, see the header
 	const auto tp1 = std::chrono::steady_clock::now();
 	const bool optimization = gm->low.dev.objective != GHOST_OBJ_NONE;
 	int epoch = s->opts.epoch_iterations > 0 ? s->opts.epoch_iterations : 256;
@@ -573,6 +585,7 @@ extern "C" int ghost_b200_search_devices(const GhostModelDesc* desc, const Ghost
 		if (d > 0) o.number_walkers = W;
 		o.first_walker_id = opts->first_walker_id + (uint64_t)d * (uint64_t)W;
 		DEV_TRY(ghost_b200_search_begin(gm[d], &o, &ss[d]));
+		if (opts->elastic_epochs == 0 && opts->timeout_us > 0 && opts->max_iterations <= 0) ss[d]->elastic = 1;
 		if (d == 0) W = ss[0]->walkers;
 		DEV_CUDA(cudaEventCreate(&ev0[d]));
 		DEV_CUDA(cudaEventCreate(&ev1[d]));

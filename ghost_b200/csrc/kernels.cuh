@@ -21,6 +21,8 @@ struct SearchParams {
 	WalkerScalars* scalars;         // [W]
 	int* best_x;                    // [W][V]
 	int* stop_flag;                 // one int
+	int* finished;                  // elastic epochs: walkers of this launch that have done their nominal share
+	int elastic;                    // see GhostSearchOpts::elastic_epochs (only set when the whole grid is co-resident)
 	unsigned long long* best_key;   // one packed key, atomicMin
 	int* trace;                     // optional [trace_cap][8] rows of walker trace_walker
 	int trace_cap, trace_walker;
@@ -403,11 +405,21 @@ search_kernel(const __grid_constant__ DevModel m, const __grid_constant__ Walker
 		if (T == 32 && tid < L.nchunks_v) { cq.key = s.cand_key[tid]; cq.bits = s.cand_bits[tid]; }
 	}
 
-	for (int it = 0; it < p.iterations && !done; ++it) {
+	// Elastic epoch: after its nominal `iterations` a walker announces itself and keeps going until all
+	// walkers of the launch have announced (polled with the stop flag), bounded by 50% extra so that a
+	// grid that is unexpectedly not co-resident cannot wait for ever.
+	int announced = 0;
+	const int hard_limit = p.elastic ? p.iterations + (p.iterations >> 1) : p.iterations;
+	for (int it = 0; it < hard_limit && !done; ++it) {
 		if (p.max_iterations > 0 && r.iterations >= p.max_iterations) break;
+		if (it >= p.iterations && !announced) { announced = 1; if (tid == 0) atomicAdd(p.finished, 1); }
 		if ((it & 7) == 0) {
 			// stop request (SearchUnit::stop_search_requested, search_unit.hpp:658-664, 728)
-			if (tid == 0) s.red[8] = *reinterpret_cast<volatile int*>(p.stop_flag);
+			if (tid == 0) {
+				int stop_now = *reinterpret_cast<volatile int*>(p.stop_flag);
+				if (announced && *reinterpret_cast<volatile int*>(p.finished) >= p.num_walkers) stop_now = 1;
+				s.red[8] = stop_now;
+			}
 			G::sync();
 			int stop = s.red[8];
 			G::sync();
@@ -534,6 +546,7 @@ search_kernel(const __grid_constant__ DevModel m, const __grid_constant__ Walker
 		if (done && p.stop_on_solution && tid == 0) atomicExch(p.stop_flag, 1);
 	}
 
+	if (p.elastic && !announced && tid == 0) atomicAdd(p.finished, 1); // left early (solved, stopped, capped): still counts
 	// persist
 	if (r.best_pending) { copy_best<T>(m, s, best_x); r.best_pending = 0; }
 	{

@@ -74,6 +74,8 @@ class GhostSearchOptsStruct(C.Structure):
         ("first_walker_id", C.c_uint64),
         ("timeout_us", C.c_double),
         ("max_iterations", C.c_int64),
+        ("elastic_epochs", C.c_int32),
+        ("reserved1", C.c_int32),
     ]
 
 
@@ -128,6 +130,8 @@ def default_opts(**overrides) -> GhostSearchOptsStruct:
     o.first_walker_id = 0
     o.timeout_us = 0.0
     o.max_iterations = 0
+    o.elastic_epochs = 0
+    o.reserved1 = 0
     for k, v in overrides.items():
         if not hasattr(o, k):
             raise AttributeError(k)

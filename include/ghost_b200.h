@@ -120,6 +120,13 @@ typedef struct GhostSearchOpts {
 	uint64_t first_walker_id;     /* global id of this GPU's walker 0 (multi-GPU sharding)     */
 	double  timeout_us;           /* wall budget, checked between epochs                       */
 	int64_t max_iterations;       /* per-walker iteration cap; <=0: none (timeout only)        */
+	int32_t elastic_epochs;       /* 1: a walker that has done its epoch_iterations keeps iterating until every   */
+	                              /* walker of the launch has done its own (at most 50% more), so no warp idles   */
+	                              /* while the slowest one finishes; per-walker trajectories are unchanged, only  */
+	                              /* how far each one gets per launch varies.  0: auto = on in the blocking,      */
+	                              /* timeout-driven ghost_b200_search / _search_devices, off in the stepwise      */
+	                              /* calls (exactly `iterations` per walker).  -1: off everywhere.                */
+	int32_t reserved1;
 } GhostSearchOpts;
 
 /* Counters: the seven of SearchUnitData (include/search_unit_data.hpp:67-73) plus the

@@ -121,6 +121,33 @@ def test_config5_population_131072_walkers_per_gpu(oracle_built):
         assert np.array_equal(out["best_x"][w], want["best_x"]), w
 
 
+def test_elastic_epochs_keep_every_trajectory(oracle_built):
+    """GhostSearchOpts::elastic_epochs: each walker does AT LEAST the epoch's iterations (at most 50% more) and
+    whatever count it reached, its state is the oracle's after exactly that many iterations of the same walker
+    — the elastic tail changes how far a walker gets per launch, never where it goes."""
+    from ghost_b200 import capi
+    desc = model_by_name("magic_square:7")
+    port = oracle_built.OraclePort(desc)
+    W, nominal = 64, 40
+    opts = default_opts(seed=99, number_walkers=W, stop_on_first_solution=0, elastic_epochs=1)
+    port.resolve_opts(opts)
+    model = capi.Model(desc)
+    s = model.begin(opts)
+    s.epoch(nominal)
+    s.epoch(nominal)
+    out = s.walkers(W)
+    s.end()
+    model.close()
+    counts = [c["search_iterations"] for c in out["counters"]]
+    assert min(counts) >= 2 * nominal and max(counts) <= 2 * (nominal + nominal // 2)
+    for w in range(0, W, 7):
+        want = port.search(opts, w, counts[w])
+        if want["counters"]["search_iterations"] < counts[w]:
+            continue  # the oracle walker stopped at a solution earlier than the cap: nothing to compare beyond it
+        assert out["counters"][w] == want["counters"], w
+        assert np.array_equal(out["best_x"][w], want["best_x"]), w
+
+
 def test_blocking_search_solves_and_reference_accepts(oracle_built):
     """ghost_b200_search (what Solver::fast_search calls): solutions of CSPs are re-checked with the
     reference's own Constraint::error (oracle/_ref) when present, else with the oracle port."""
