@@ -27,7 +27,7 @@ want = ['gpu__time_duration.sum', 'launch__grid_size', 'launch__block_size', 'la
         'sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active', 'sm__throughput.avg.pct_of_peak_sustained_elapsed']
 want += [k for k in h if k.startswith('smsp__average_warps_issue_stalled_') and k.endswith('_per_issue_active.ratio') and 'not_issued' not in k]
 lines = [f"ncu --set full --clock-control none --import-source on, search_kernel<32,true,true,unsigned short>, magic_square:30, 3552 walkers x 256 "
-         f"iterations, 1 launch (7th launch of: {CMD})"]
+         f"iterations (elastic epoch: up to 50% more for the early finishers), 1 launch (7th launch of: {CMD})"]
 val = {}
 for k in want:
     if k not in h: continue
