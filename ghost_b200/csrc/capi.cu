@@ -58,6 +58,12 @@ struct GhostSearch {
 	std::chrono::steady_clock::time_point t_begin;
 };
 
+extern "C" void ghost_b200_abi_sizes(int32_t out[6])
+{
+	out[0] = (int32_t)sizeof(GhostModelDesc); out[1] = (int32_t)sizeof(GhostSearchOpts); out[2] = (int32_t)sizeof(GhostCounters);
+	out[3] = (int32_t)sizeof(GhostResult); out[4] = (int32_t)sizeof(GhostWalkerSummary); out[5] = (int32_t)sizeof(void*);
+}
+
 extern "C" const char* ghost_b200_last_error(void) { return g_last_error.c_str(); }
 extern "C" const char* ghost_b200_version(void) { return "ghost_b200 0.1 (sm_100a)"; }
 

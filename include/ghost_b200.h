@@ -113,7 +113,7 @@ typedef struct GhostSearchOpts {
 
 	/* additions */
 	int32_t number_walkers;       /* parallel restarts on this GPU; <=0: fill the GPU          */
-	int32_t threads_per_walker;   /* 0 = choose from the model; else 32/64/128/256/512/1024     */
+	int32_t threads_per_walker;   /* 0 = choose from the model; else 32, 64, 128 or 256       */
 	int32_t epoch_iterations;     /* iterations per walker per kernel launch; <=0: default     */
 	int32_t stop_on_first_solution; /* CSP: stop all walkers once one has sat error 0           */
 	uint64_t seed;                /* Philox key                                                */
@@ -319,6 +319,10 @@ int ghost_b200_search_noalloc(GhostModel* model, const GhostSearchOpts* opts, in
  * counterpart): SM integer issue rate in lane-ops/s and conflict-free shared-memory bandwidth in
  * bytes/s, each from a short CUDA-event-timed microbenchmark. */
 int ghost_b200_microbench(double* issue_lane_ops_per_s, double* smem_bytes_per_s);
+
+/* sizeof of the structs that cross this ABI, for bindings that mirror them by hand (ctypes, cgo, JNI):
+ * out[0..5] = GhostModelDesc, GhostSearchOpts, GhostCounters, GhostResult, GhostWalkerSummary, pointer. */
+void ghost_b200_abi_sizes(int32_t out[6]);
 
 const char* ghost_b200_last_error(void);
 const char* ghost_b200_version(void);

@@ -142,3 +142,15 @@ def test_product_never_imports_the_oracle():
                 for line in text.splitlines():
                     if re.search(r"^\s*(from|import)\s+oracle|#include\s+\".*oracle|liboracle|libghost_oracle|libghost_ref", line):
                         raise AssertionError(os.path.join(base, f) + ": " + line)
+
+
+def test_ctypes_mirrors_have_the_c_sizes():
+    """The hand-written ctypes structs (ghost_b200/modeldesc.py) against sizeof in the library."""
+    import ctypes as C
+    from ghost_b200 import capi
+    from ghost_b200.modeldesc import GhostCountersStruct, GhostModelDescStruct, GhostResultStruct, GhostSearchOptsStruct
+    out = (C.c_int32 * 6)()
+    capi.lib.ghost_b200_abi_sizes(out)
+    assert list(out)[:4] == [C.sizeof(GhostModelDescStruct), C.sizeof(GhostSearchOptsStruct), C.sizeof(GhostCountersStruct),
+                             C.sizeof(GhostResultStruct)]
+    assert out[4] == 8 * capi.SUMMARY_WORDS and out[5] == C.sizeof(C.c_void_p)

@@ -148,6 +148,23 @@ def test_elastic_epochs_keep_every_trajectory(oracle_built):
         assert np.array_equal(out["best_x"][w], want["best_x"]), w
 
 
+def test_elastic_epochs_are_off_when_the_grid_is_not_resident():
+    """More walkers than one resident wave: a walker could wait for CTAs that have not started, so the epochs
+    stay rigid (exactly the asked iterations) even when elastic_epochs = 1."""
+    from ghost_b200 import capi
+    desc = model_by_name("magic_square:7")
+    W, nominal = 40000, 24
+    model = capi.Model(desc)
+    s = model.begin(default_opts(seed=3, number_walkers=W, stop_on_first_solution=0, elastic_epochs=1))
+    s.epoch(nominal)
+    out = s.walkers(W)
+    s.end()
+    model.close()
+    counts = np.array([c["search_iterations"] for c in out["counters"]])
+    solved = np.array(out["best_sat"]) == 0
+    assert np.all(counts[~solved] == nominal) and np.all(counts <= nominal)
+
+
 def test_blocking_search_solves_and_reference_accepts(oracle_built):
     """ghost_b200_search (what Solver::fast_search calls): solutions of CSPs are re-checked with the
     reference's own Constraint::error (oracle/_ref) when present, else with the oracle port."""
