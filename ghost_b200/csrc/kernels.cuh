@@ -45,20 +45,28 @@ __device__ __forceinline__ unsigned long long quality_key(bool optimization, int
 // ---- sampling ---------------------------------------------------------------------------------
 
 // first n entries of a uniform shuffle of 0..V-1 (replaces rng.shuffle + prefix, search_unit.hpp:
-// 206-211, 239-246): rejection sampling over one RNG event, by thread 0.  The serial part is one
-// shared out-of-line copy (plain pointers and scalars only), see GB_OUTLINE in walker.cuh.
-static __device__ GB_OUTLINE void sample_distinct_serial(unsigned char* flags, int* out, int n, int V, uint64_t seed, uint64_t walker, uint64_t event)
+// 206-211, 239-246): rejection sampling over one RNG event.  Word t of the event (block t/4,
+// component t%4) proposes index below(word, V); proposals already taken are skipped.  One warp runs
+// it: every lane computes ONE Philox block of a batch of 32 (128 proposals), then the proposals are
+// consumed in order, each broadcast with a shuffle — the same sequence a single thread would see, at
+// 1/32 of the generator work.  One shared out-of-line copy (see GB_OUTLINE in walker.cuh).
+static __device__ GB_OUTLINE void sample_distinct_warp(unsigned char* flags, int* out, int n, int V, uint64_t seed, uint64_t walker, uint64_t event)
 {
 	Rng rng; rng.seed = seed; rng.walker = walker; rng.next_event = 0;
-	uint32_t t = 0;
-	uint4 blk = make_uint4(0, 0, 0, 0);
-	for (int got = 0; got < n; ++t) {
-		if ((t & 3u) == 0) blk = rng.block(event, t >> 2);
-		uint32_t w = (t & 3u) == 0 ? blk.x : (t & 3u) == 1 ? blk.y : (t & 3u) == 2 ? blk.z : blk.w;
-		uint32_t idx = below(w, (uint32_t)V);
-		if (flags[idx]) continue;
-		flags[idx] = 1;
-		out[got++] = (int)idx;
+	const int lane = threadIdx.x & 31;
+	int got = 0;
+	for (uint32_t batch = 0; got < n; ++batch) {
+		const uint4 blk = rng.block(event, batch * 32u + (uint32_t)lane);
+		for (int t = 0; t < 128 && got < n; ++t) {
+			const int q = t & 3;
+			const uint32_t mine = q == 0 ? blk.x : q == 1 ? blk.y : q == 2 ? blk.z : blk.w;
+			const uint32_t idx = below(__shfl_sync(0xffffffffu, mine, t >> 2), (uint32_t)V);
+			if (flags[idx]) continue;          // same address in every lane: a broadcast read, a uniform branch
+			__syncwarp();
+			if (lane == 0) { flags[idx] = 1; out[got] = (int)idx; }
+			__syncwarp();
+			++got;
+		}
 	}
 }
 template <int T, class WS>
@@ -69,7 +77,7 @@ __device__ inline void sample_distinct(const DevModel& m, const WS& s, Rng& rng,
 	const uint64_t event = rng.next_event++;
 	for (int v = tid; v < m.V; v += T) s.flags[v] = 0;
 	G::sync();
-	if (tid == 0) sample_distinct_serial(s.flags, out, n, m.V, rng.seed, rng.walker, event);
+	if (G::warp() == 0) sample_distinct_warp(s.flags, out, n, m.V, rng.seed, rng.walker, event);
 	G::sync();
 }
 
@@ -128,15 +136,32 @@ __device__ inline void random_permutations(const DevModel& m, const WS& s, Rng& 
 		const uint32_t blocks = (uint32_t)((m.V + 127) / 128);
 		if (m.identical_domains) {
 			if (G::warp() == 0) {
+				// The coins of row i are the bits of blocks (i, 0..blocks-1).  With at most 32 blocks per row the
+				// warp generates the blocks of `rows_per_batch` rows at once, one per lane, instead of every lane
+				// computing the same block: same bits, 1/32 of the generator work.
+				const bool batched = blocks <= 32u;
+				const int rows_per_batch = batched ? 32 / (int)blocks : 1;
+				uint4 mine = make_uint4(0, 0, 0, 0);
 				for (int i = 0; i < m.V - 1; ++i) {
+					const int r = i % rows_per_batch;
+					if (batched && r == 0) {
+						const uint32_t row = (uint32_t)i + (uint32_t)lane / blocks, blk_in_row = (uint32_t)lane % blocks;
+						mine = rng.block(event, row * blocks + blk_in_row); // lanes beyond the batch compute a block nobody reads
+					}
 					int carry = s.x[i];
 					bool any = false;
 					uint4 blk = make_uint4(0, 0, 0, 0);
 					int cur_block = -1;
 					for (int jb = (i + 1) & ~31; jb < m.V; jb += 32) {
-						if ((jb >> 7) != cur_block) { cur_block = jb >> 7; blk = rng.block(event, (uint32_t)i * blocks + (uint32_t)cur_block); }
 						uint32_t q = ((uint32_t)jb >> 5) & 3u;
-						uint32_t w = q == 0 ? blk.x : q == 1 ? blk.y : q == 2 ? blk.z : blk.w;
+						uint32_t w;
+						if (batched) {
+							const uint32_t sel = q == 0 ? mine.x : q == 1 ? mine.y : q == 2 ? mine.z : mine.w;
+							w = __shfl_sync(0xffffffffu, sel, r * (int)blocks + (jb >> 7));
+						} else {
+							if ((jb >> 7) != cur_block) { cur_block = jb >> 7; blk = rng.block(event, (uint32_t)i * blocks + (uint32_t)cur_block); }
+							w = q == 0 ? blk.x : q == 1 ? blk.y : q == 2 ? blk.z : blk.w;
+						}
 						int j = jb + lane;
 						bool chosen = j > i && j < m.V && ((w >> lane) & 1u);
 						int old = (j < m.V) ? s.x[j] : 0;
