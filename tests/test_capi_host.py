@@ -128,6 +128,12 @@ def test_no_gpu_means_loud_failure_not_fallback():
     with pytest.raises(capi.GhostError) as e:
         m.search(md.default_opts(number_walkers=4, max_iterations=10))
     assert e.value.code == capi.ERR_CUDA
+    with pytest.raises(capi.GhostError) as e:
+        m.complete_search()
+    assert e.value.code == capi.ERR_CUDA
+    with pytest.raises(capi.GhostError) as e:
+        capi.search_devices(model_by_name("magic_square:3"), md.default_opts(number_walkers=4, max_iterations=10), 0)
+    assert e.value.code == capi.ERR_CUDA
 
 
 def test_product_never_imports_the_oracle():
