@@ -42,6 +42,7 @@ def _load():
     lib.ghost_b200_model_destroy.argtypes = [vp]
     lib.ghost_b200_model_destroy.restype = None
     lib.ghost_b200_model_info.argtypes = [vp, C.POINTER(i32), C.POINTER(i64), C.POINTER(i32)]
+    lib.ghost_b200_model_variant.argtypes = [vp, i32, C.POINTER(i32)]
     lib.ghost_b200_default_opts.argtypes = [C.POINTER(GhostSearchOptsStruct)]
     lib.ghost_b200_default_opts.restype = None
     lib.ghost_b200_resolve_opts.argtypes = [vp, C.POINTER(GhostSearchOptsStruct)]
@@ -122,6 +123,13 @@ class Model:
 
     def __del__(self):
         self.close()
+
+    def variant(self, threads_per_walker: int = 0) -> int:
+        """GHOST_B200_VARIANT_* bits of the search kernel this model dispatches to (1 permutation, 2 LinearEq only,
+        4 16-bit assignment, 8 fp32 swap evaluation)."""
+        v = C.c_int32()
+        _check(lib.ghost_b200_model_variant(self.h, threads_per_walker, C.byref(v)))
+        return v.value
 
     def resolve_opts(self, opts: GhostSearchOptsStruct):
         _check(lib.ghost_b200_resolve_opts(self.h, C.byref(opts)))

@@ -97,6 +97,17 @@ extern "C" int ghost_b200_model_info(const GhostModel* gm, int32_t* max_candidat
 	return GHOST_B200_OK;
 }
 
+extern "C" int ghost_b200_model_variant(const GhostModel* gm, int32_t threads_per_walker, int32_t* variant)
+{
+	if (!gm || !variant) return set_error(GHOST_B200_ERR_INVALID, "null argument");
+	const DevModel& m = gm->low.dev;
+	const int T = gm->low.effective_threads_per_walker(threads_per_walker);
+	int v = (m.permutation ? GHOST_B200_VARIANT_PERMUTATION : 0) | (m.eq_only ? GHOST_B200_VARIANT_LINEAR_EQ_ONLY : 0) | (m.x16 ? GHOST_B200_VARIANT_X16 : 0);
+	if (T == 32 && v == 7 && m.f32_ok) v |= GHOST_B200_VARIANT_F32; // the rule of GB_DISPATCH (launch_impl.cuh)
+	*variant = v;
+	return GHOST_B200_OK;
+}
+
 extern "C" void ghost_b200_default_opts(GhostSearchOpts* o)
 {
 	// ghost::Options::Options(), reference src/options.cpp:36-50

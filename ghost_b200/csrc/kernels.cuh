@@ -226,7 +226,7 @@ __device__ inline void copy_best(const DevModel& m, const WS& s, int* best_x)
 }
 
 // SearchUnit::initialize_data_structures (search_unit.hpp:274-317)
-template <int T, bool EQ, class WS>
+template <int T, bool EQ, bool F32, class WS>
 __device__ inline void initialize_data_structures(const DevModel& m, const WS& s, WalkerRegs& r, int* best_x)
 {
 	typedef Group<T> G;
@@ -234,7 +234,7 @@ __device__ inline void initialize_data_structures(const DevModel& m, const WS& s
 	r.must_compute = 1;
 	for (int v = G::tid(); v < m.V; v += T) s.tabu[v] = 0;
 	r.tabu_base = r.local_moves;
-	r.cur_sat = recompute_all<T, true, EQ>(m, s, s.red);
+	r.cur_sat = recompute_all<T, true, EQ, F32>(m, s, s.red);
 	if (r.best_sat > r.cur_sat) { r.best_sat = r.cur_sat; r.best_pending = 1; }
 	if (m.objective != GHOST_OBJ_NONE) {
 		long long part = 0;
@@ -251,7 +251,7 @@ __device__ inline void initialize_data_structures(const DevModel& m, const WS& s
 // SearchUnit::set_initial_configuration (search_unit.hpp:153-198); s.tabu doubles as the
 // best_values buffer (it is cleared by initialize_data_structures right after).
 // Deviation D1: best_x follows best_sat here too.
-template <int T, bool EQ, class WS>
+template <int T, bool EQ, bool F32, class WS>
 __device__ inline void set_initial_configuration(const DevModel& m, const WS& s, WalkerRegs& r, Rng& rng, int samplings, int* best_x)
 {
 	typedef Group<T> G;
@@ -260,7 +260,7 @@ __device__ inline void set_initial_configuration(const DevModel& m, const WS& s,
 	int loops = 0;
 	do {
 		if (m.permutation) random_permutations<T>(m, s, rng, -1); else monte_carlo_sampling<T>(m, s, rng, -1);
-		current = recompute_all<T, false, EQ>(m, s, s.red); // total only: err_var holds the best sample
+		current = recompute_all<T, false, EQ, F32>(m, s, s.red); // total only: err_var holds the best sample
 		if (best_so_far > current) {
 			best_so_far = current;
 			if (r.best_sat > best_so_far) { r.best_sat = best_so_far; copy_best<T>(m, s, best_x); r.best_pending = 0; }
@@ -273,7 +273,7 @@ __device__ inline void set_initial_configuration(const DevModel& m, const WS& s,
 }
 
 // SearchUnit::initialize_variable_values (search_unit.hpp:259-272)
-template <int T, bool EQ, class WS>
+template <int T, bool EQ, bool F32, class WS>
 __device__ inline void initialize_variable_values(const DevModel& m, const WS& s, WalkerRegs& r, Rng& rng, const SearchParams& p, int* best_x)
 {
 	typedef Group<T> G;
@@ -283,11 +283,11 @@ __device__ inline void initialize_variable_values(const DevModel& m, const WS& s
 		for (int v = G::tid(); v < m.V; v += T) s.x[v] = mv.ld(m.o.start, v);
 		G::sync();
 	} else
-		set_initial_configuration<T, EQ>(m, s, r, rng, p.nsamplings, best_x);
+		set_initial_configuration<T, EQ, F32>(m, s, r, rng, p.nsamplings, best_x);
 }
 
 // SearchUnit::local_move (search_unit.hpp:516-541)
-template <int T, bool PERM, bool EQ, class WS>
+template <int T, bool PERM, bool EQ, bool F32, class WS>
 __device__ inline void local_move(const DevModel& m, const WS& s, WalkerRegs& r, const SearchParams& p, int* best_x, int v, int new_value, int delta, int nh)
 {
 	MV mv(m);
@@ -303,7 +303,8 @@ __device__ inline void local_move(const DevModel& m, const WS& s, WalkerRegs& r,
 		} else
 			r.obj_sum += (long long)mv.obj_coef(v) * (new_value - s.x[v]);
 	}
-	if (EQ) apply_move_eq<T, PERM>(m, s, v, new_value, nh);
+	if (F32) apply_move_f32(m, s, v, new_value, nh);
+	else if (EQ) apply_move_eq<T, PERM>(m, s, v, new_value, nh);
 	else apply_move<T>(m, s, v, new_value);
 }
 
@@ -336,7 +337,7 @@ struct ColdState {
 };
 enum { GB_COLD_FIRST = 0, GB_COLD_RESTART = 1, GB_COLD_PERTURB = 2 };
 
-template <int T, bool PERM, bool EQ, class XT>
+template <int T, bool PERM, bool EQ, class XT, bool F32>
 static __device__ __noinline__ ColdState walker_reinit(const DevModel& m, const WalkerLayout& L, const SearchParams& p,
                                                        unsigned char* base, int* best_x, unsigned long long walker, int mode, ColdState c)
 {
@@ -357,13 +358,13 @@ static __device__ __noinline__ ColdState walker_reinit(const DevModel& m, const 
 		// padding of the scan arrays up to a multiple of 32 variables: tabu for ever, error 0
 		for (int v = m.V + tid; v < L.nchunks_v * 32; v += T) { s.tabu[v] = 0xFFFFu; s.err_var[v] = 0; s.x[v] = 0; }
 		G::sync();
-		initialize_variable_values<T, EQ>(m, s, r, rng, p, best_x);
+		initialize_variable_values<T, EQ, F32>(m, s, r, rng, p, best_x);
 	} else if (mode == GB_COLD_RESTART) {
 		if (tid == 0) s.counters[K_RESTARTS] += 1;
-		initialize_variable_values<T, EQ>(m, s, r, rng, p, best_x);
+		initialize_variable_values<T, EQ, F32>(m, s, r, rng, p, best_x);
 	} else if (PERM) random_permutations<T>(m, s, rng, p.nreset);
 	else monte_carlo_sampling<T>(m, s, rng, p.nreset);
-	initialize_data_structures<T, EQ>(m, s, r, best_x);
+	initialize_data_structures<T, EQ, F32>(m, s, r, best_x);
 	if (mode == GB_COLD_FIRST) r.best_pending = 1; // search_unit.hpp:714-717: final_solution = the initial assignment
 	c.must_compute = r.must_compute; c.tabu_base = r.tabu_base; c.cur_sat = r.cur_sat; c.best_sat = r.best_sat;
 	c.best_pending = r.best_pending; c.resume_pending = r.resume_pending;
@@ -371,7 +372,8 @@ static __device__ __noinline__ ColdState walker_reinit(const DevModel& m, const 
 	return c;
 }
 
-template <int T, bool PERM, bool EQ, class XT>
+// F32: the fp32 form of the LinearEq-only swap evaluation (walker.cuh, evaluate_f32); T == 32, PERM, EQ, 16-bit x only
+template <int T, bool PERM, bool EQ, class XT, bool F32 = false>
 __global__ void __launch_bounds__(T == 32 ? 128 : T, (GB_WARPS_PER_SM * 32) / (T == 32 ? 128 : T))
 search_kernel(const __grid_constant__ DevModel m, const __grid_constant__ WalkerLayout L, const __grid_constant__ SearchParams p)
 {
@@ -414,7 +416,7 @@ search_kernel(const __grid_constant__ DevModel m, const __grid_constant__ Walker
 		c.best_sat = r.best_sat; c.best_pending = r.best_pending; c.resume_pending = r.resume_pending;
 		c.cur_opt = r.cur_opt; c.best_opt = r.best_opt; c.obj_sum = r.obj_sum; c.next_event = rng.next_event;
 		G::sync();
-		c = walker_reinit<T, PERM, EQ, XT>(m, L, p, walker_base, best_x, rng.walker, mode, c);
+		c = walker_reinit<T, PERM, EQ, XT, F32>(m, L, p, walker_base, best_x, rng.walker, mode, c);
 		r.must_compute = c.must_compute; r.tabu_base = c.tabu_base; r.cur_sat = c.cur_sat; r.best_sat = c.best_sat;
 		r.best_pending = c.best_pending; r.resume_pending = c.resume_pending;
 		r.cur_opt = c.cur_opt; r.best_opt = c.best_opt; r.obj_sum = c.obj_sum; rng.next_event = c.next_event;
@@ -479,24 +481,26 @@ search_kernel(const __grid_constant__ DevModel m, const __grid_constant__ Walker
 			const int v = T == 32 ? regs_pick_kth(cq, r.cand_max, kv, r.ncand) : pick_kth(s.cand_key, s.cand_bits, L.nchunks_v, r.cand_max, kv);
 			--r.ncand;
 			int bias;
-			const int nh = EQ ? hoist_variable_eq<T, PERM>(m, s, v, &bias) : hoist_variable<T>(m, s, v, &bias);
+			const int nh = F32 ? hoist_variable_f32(m, s, v, &bias) : EQ ? hoist_variable_eq<T, PERM>(m, s, v, &bias) : hoist_variable<T>(m, s, v, &bias);
 			G::sync();
 			// search_unit.hpp:826-828
 			if (T == 32) { if (tid == (v >> 5)) cq.bits &= ~(1u << (v & 31)); }
 			else if (tid == 0) s.cand_bits[v >> 5] &= ~(1u << (v & 31));
-			int gmin, nties;
-			const int mine = evaluate_candidates<T, PERM, EQ>(m, s, v, nh, bias, L.nchunks_c, nullptr, vq);
+			int gkey, nties;
+			const int mine = evaluate_candidates<T, PERM, EQ, F32>(m, s, v, nh, bias, L.nchunks_c, nullptr, vq);
 			evals_lane += mine;
 			G::sync();
 			// AdaptiveSearchValueHeuristic::select_value (adaptive_search_value_heuristic.cpp:43-81)
 			if (T == 32) {
-				gmin = __reduce_min_sync(0xffffffffu, vq.key);
-				nties = regs_count(vq, gmin);
+				gkey = __reduce_min_sync(0xffffffffu, vq.key);
+				nties = regs_count(vq, gkey);
 			} else {
-				gmin = chunks_min(s.val_key, L.nchunks_c);
-				nties = chunks_count(s.val_key, s.val_bits, L.nchunks_c, gmin);
+				gkey = chunks_min(s.val_key, L.nchunks_c);
+				nties = chunks_count(s.val_key, s.val_bits, L.nchunks_c, gkey);
 			}
-			if (gmin == GB_INT_MAX) nties = 0;
+			if (gkey == GB_INT_MAX) nties = 0;
+			// the fp32 evaluation hands back the bits of (1.5 * 2^23 + sum): an integer offset away from the sum
+			const int gmin = (F32 && gkey != GB_INT_MAX) ? gkey - GB_F32_BASE_BITS : gkey;
 			int new_value = v;
 			if (nties > 0) {
 				int k;
@@ -506,7 +510,7 @@ search_kernel(const __grid_constant__ DevModel m, const __grid_constant__ Walker
 					long long cf = internal_cost(m, (long long)mv.obj_coef(v));
 					k = cf > 0 ? 0 : cf < 0 ? nties - 1 : (int)below(rnd.y, (uint32_t)nties);
 				} else k = (int)below(rnd.y, (uint32_t)nties);
-				int slot = T == 32 ? regs_pick_kth(vq, gmin, k, nties) : pick_kth(s.val_key, s.val_bits, L.nchunks_c, gmin, k);
+				int slot = T == 32 ? regs_pick_kth(vq, gkey, k, nties) : pick_kth(s.val_key, s.val_bits, L.nchunks_c, gkey, k);
 				new_value = PERM ? slot : mv.dom_value(v, slot);
 			}
 			trace_var = v; trace_val = new_value; trace_min = gmin;
@@ -514,7 +518,7 @@ search_kernel(const __grid_constant__ DevModel m, const __grid_constant__ Walker
 
 			int plateau = 0, local_min = 0;
 			if (gmin < 0) { // search_unit.hpp:1042-1050
-				local_move<T, PERM, EQ>(m, s, r, p, best_x, v, new_value, gmin, nh);
+				local_move<T, PERM, EQ, F32>(m, s, r, p, best_x, v, new_value, gmin, nh);
 				if (optimization) r.cur_opt = internal_cost(m, r.obj_sum);
 				trace_branch = 1;
 			} else if (gmin == 0) {
@@ -525,7 +529,7 @@ search_kernel(const __grid_constant__ DevModel m, const __grid_constant__ Walker
 						obj2 = r.obj_sum + (long long)mv.obj_coef(v) * (xj - xv) + (long long)mv.obj_coef(new_value) * (xv - xj);
 					} else obj2 = r.obj_sum + (long long)mv.obj_coef(v) * (new_value - s.x[v]);
 					long long cand_opt = internal_cost(m, obj2);
-					if (r.cur_opt > cand_opt) { local_move<T, PERM, EQ>(m, s, r, p, best_x, v, new_value, 0, nh); r.cur_opt = cand_opt; trace_branch = 2; }
+					if (r.cur_opt > cand_opt) { local_move<T, PERM, EQ, F32>(m, s, r, p, best_x, v, new_value, 0, nh); r.cur_opt = cand_opt; trace_branch = 2; }
 					else if (r.cur_opt == cand_opt) plateau = 1;
 					else local_min = 1;
 				} else plateau = 1; // 1136-1145
@@ -537,7 +541,7 @@ search_kernel(const __grid_constant__ DevModel m, const __grid_constant__ Walker
 					r.must_compute = 1;
 					trace_branch = 4;
 				} else {
-					local_move<T, PERM, EQ>(m, s, r, p, best_x, v, new_value, 0, nh);
+					local_move<T, PERM, EQ, F32>(m, s, r, p, best_x, v, new_value, 0, nh);
 					if (tid == 0) s.counters[K_PLATEAU] += 1;
 					trace_branch = 3;
 				}
@@ -551,7 +555,7 @@ search_kernel(const __grid_constant__ DevModel m, const __grid_constant__ Walker
 				} else trace_branch = 6;
 			}
 			G::sync();
-			if (PERM) { if (EQ) unmark_variable_eq<T>(m, s, v); else unmark_variable<T>(m, s, v); }
+			if (PERM) { if (F32) unmark_variable_f32(m, s, v); else if (EQ) unmark_variable_eq<T>(m, s, v); else unmark_variable<T>(m, s, v); }
 
 			// search_unit.hpp:1166-1188
 			if (r.best_sat > r.cur_sat) { r.best_sat = r.cur_sat; r.best_pending = 1; }
@@ -602,7 +606,7 @@ search_kernel(const __grid_constant__ DevModel m, const __grid_constant__ Walker
 // =================================================================================================
 // Parity hook: for each walker's assignment and selected variable write constraint errors,
 // projected errors and the cumulated delta of every candidate slot.
-template <int T, bool PERM, bool EQ, class XT>
+template <int T, bool PERM, bool EQ, class XT, bool F32 = false>
 __global__ void __launch_bounds__(T == 32 ? 128 : T)
 eval_kernel(const DevModel m, const WalkerLayout L, int num_walkers, const int* __restrict__ assignments,
             const int* __restrict__ selected, int* __restrict__ ctr_error, int* __restrict__ var_error,
@@ -620,17 +624,17 @@ eval_kernel(const DevModel m, const WalkerLayout L, int num_walkers, const int* 
 	for (int v = tid; v < L.nchunks_v * 32; v += T) s.x[v] = v < m.V ? assignments[(size_t)w * m.V + v] : 0;
 	if (tid == 0) { s.cs[m.C] = make_int2(0, 0); s.cem[m.C] = make_int2(0, 0); }
 	G::sync();
-	recompute_all<T, true>(m, s, s.red);
+	recompute_all<T, true, EQ, F32>(m, s, s.red);
 	if (ctr_error) for (int c = tid; c < m.C; c += T) ctr_error[(size_t)w * m.C + c] = s.err_of(c);
 	if (var_error) for (int v = tid; v < m.V; v += T) var_error[(size_t)w * m.V + v] = s.err_var[scan_pos(m, v)];
 	const int v = selected ? selected[w] : -1;
 	if (v < 0 || !cand_delta) return;
 	int* out = cand_delta + (size_t)w * m.max_candidates;
 	int bias;
-	const int nh = EQ ? hoist_variable_eq<T, PERM>(m, s, v, &bias) : hoist_variable<T>(m, s, v, &bias);
+	const int nh = F32 ? hoist_variable_f32(m, s, v, &bias) : EQ ? hoist_variable_eq<T, PERM>(m, s, v, &bias) : hoist_variable<T>(m, s, v, &bias);
 	G::sync();
 	ChunkRegs vq;
-	evaluate_candidates<T, PERM, EQ>(m, s, v, nh, bias, L.nchunks_c, out, vq);
+	evaluate_candidates<T, PERM, EQ, F32>(m, s, v, nh, bias, L.nchunks_c, out, vq);
 }
 
 } // namespace ghost_b200

@@ -12,35 +12,37 @@ static cudaError_t allow_smem(K kernel, size_t smem)
 	return cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
 }
 
-template <bool PERM, bool EQ, class XT>
+template <bool PERM, bool EQ, class XT, bool F32 = false>
 static cudaError_t do_search(int grid, int block, size_t smem, cudaStream_t st, const DevModel& m, const WalkerLayout& L, const SearchParams& p)
 {
-	cudaError_t e = allow_smem(search_kernel<GB_T, PERM, EQ, XT>, smem);
+	cudaError_t e = allow_smem(search_kernel<GB_T, PERM, EQ, XT, F32>, smem);
 	if (e != cudaSuccess) return e;
-	search_kernel<GB_T, PERM, EQ, XT><<<grid, block, smem, st>>>(m, L, p);
+	search_kernel<GB_T, PERM, EQ, XT, F32><<<grid, block, smem, st>>>(m, L, p);
 	return cudaGetLastError();
 }
 // resident CTAs per SM of the search kernel this model dispatches to (registers, shared memory, threads)
-template <bool PERM, bool EQ, class XT>
+template <bool PERM, bool EQ, class XT, bool F32 = false>
 static cudaError_t do_occupancy(int block, size_t smem, int* ctas_per_sm)
 {
-	cudaError_t e = allow_smem(search_kernel<GB_T, PERM, EQ, XT>, smem);
+	cudaError_t e = allow_smem(search_kernel<GB_T, PERM, EQ, XT, F32>, smem);
 	if (e != cudaSuccess) return e;
-	return cudaOccupancyMaxActiveBlocksPerMultiprocessor(ctas_per_sm, search_kernel<GB_T, PERM, EQ, XT>, block, smem);
+	return cudaOccupancyMaxActiveBlocksPerMultiprocessor(ctas_per_sm, search_kernel<GB_T, PERM, EQ, XT, F32>, block, smem);
 }
-template <bool PERM, bool EQ, class XT>
+template <bool PERM, bool EQ, class XT, bool F32 = false>
 static cudaError_t do_eval(int grid, int block, size_t smem, cudaStream_t st, const DevModel& m, const WalkerLayout& L, int W,
                            const int* x, const int* sel, int* ce, int* ve, int* cd)
 {
-	cudaError_t e = allow_smem(eval_kernel<GB_T, PERM, EQ, XT>, smem);
+	cudaError_t e = allow_smem(eval_kernel<GB_T, PERM, EQ, XT, F32>, smem);
 	if (e != cudaSuccess) return e;
-	eval_kernel<GB_T, PERM, EQ, XT><<<grid, block, smem, st>>>(m, L, W, x, sel, ce, ve, cd);
+	eval_kernel<GB_T, PERM, EQ, XT, F32><<<grid, block, smem, st>>>(m, L, W, x, sel, ce, ve, cd);
 	return cudaGetLastError();
 }
 
 #define GB_DISPATCH(FN, ...)                                                                      \
 	do {                                                                                          \
 		const int key = (m.permutation ? 4 : 0) | (m.eq_only ? 2 : 0) | (m.x16 ? 1 : 0);           \
+		/* one-warp walkers of a model that qualifies (lower.cpp) evaluate in fp32 */              \
+		if (GB_T == 32 && key == 7 && m.f32_ok) return FN<true, true, unsigned short, GB_T == 32>(__VA_ARGS__); \
 		switch (key) {                                                                            \
 		case 0: return FN<false, false, int>(__VA_ARGS__);                                        \
 		case 1: return FN<false, false, unsigned short>(__VA_ARGS__);                                      \

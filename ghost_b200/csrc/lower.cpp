@@ -14,6 +14,7 @@
 
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <limits>
 #include <set>
@@ -82,6 +83,7 @@ int lower_model(const GhostModelDesc* d, LoweredModel* out, std::string* why)
 	std::vector<std::vector<std::pair<int, int>>> rows(V); // (constraint, coefficient|position)
 	int cnt_total = 0;
 	int64_t error_bound = 0;
+	int64_t max_T_bound = 0, max_abs_coef = 0;   // over the linear constraints: |sum - rhs| and |coefficient|
 	bool has_abs_diff = false;
 	for (int c = 0; c < C; ++c) {
 		int k = d->ctr_kind[c];
@@ -113,6 +115,7 @@ int lower_model(const GhostModelDesc* d, LoweredModel* out, std::string* why)
 				ent_coef[i] = static_cast<int32_t>(a);
 				second = static_cast<int32_t>(a);
 				lin_bound += std::llabs((long long)a) * std::max(std::llabs((long long)vlo), std::llabs((long long)vhi));
+				max_abs_coef = std::max<int64_t>(max_abs_coef, std::llabs((long long)a));
 			} else if (k == GHOST_KIND_ALL_DIFFERENT_ABS_DIFF) {
 				second = i - b; // position in scope
 			}
@@ -128,6 +131,7 @@ int lower_model(const GhostModelDesc* d, LoweredModel* out, std::string* why)
 				if (lin_bound + std::llabs((long long)p) >= (1LL << 30))
 					return fail(GHOST_B200_ERR_UNSUPPORTED, "constraint " + std::to_string(c) + ": |sum| can exceed 2^30");
 				error_bound += lin_bound + std::llabs((long long)p) + 1;
+				max_T_bound = std::max<int64_t>(max_T_bound, lin_bound + std::llabs((long long)p));
 			} else {
 				for (int i = b; i < e; ++i) {
 					int v = c2v[i];
@@ -295,6 +299,43 @@ int lower_model(const GhostModelDesc* d, LoweredModel* out, std::string* why)
 			}
 		o.ell_eq = put(ell_eq);
 	}
+	// fp32 evaluation of the swap candidates (walker.cuh, evaluate_f32): every term is |T + a*dx| on integers, so
+	// fp32 is exact while magnitudes stay below 2^24.  B bounds one term (|T| plus both variables' a*dx); a
+	// candidate's sum has at most 4 + 2*4 + 4 terms and is accumulated on top of the constant 1.5*2^23 (its bit
+	// pattern is then the integer sum plus a constant: the arg-min needs no conversion), which needs every partial
+	// sum inside (-2^22, 2^22).
+	bool f32_ok = eq_only && d->permutation_problem && identical && stride <= 4 && min_value >= 0 && max_value <= 65535 && V <= 1024;
+	if (f32_ok) {
+		const int64_t B = max_T_bound + 2 * max_abs_coef * (max_value - min_value);
+		if (max_abs_coef > 2048 || 16 * B >= (1LL << 22)) f32_ok = false;
+		std::vector<int32_t> sv(d->start_value, d->start_value + V);
+		std::sort(sv.begin(), sv.end());
+		if (std::adjacent_find(sv.begin(), sv.end()) != sv.end()) f32_ok = false; // the candidates of a variable are then exactly the V - 1 others
+		if (std::getenv("GHOST_B200_NO_F32")) f32_ok = false; // test knob: the int32 evaluation of the same model
+	}
+	{
+		auto half_bits = [](int a) -> uint32_t { // IEEE binary16 of an integer |a| <= 2048 (exact)
+			if (a == 0) return 0u;
+			const uint32_t sign = a < 0 ? 0x8000u : 0u;
+			uint32_t mag = static_cast<uint32_t>(a < 0 ? -a : a);
+			int e = 0;
+			while ((mag >> (e + 1)) != 0) ++e;
+			const uint32_t mant = e <= 10 ? (mag << (10 - e)) & 0x3FFu : (mag >> (e - 10)) & 0x3FFu;
+			return sign | (static_cast<uint32_t>(e + 15) << 10) | mant;
+		};
+		std::vector<int32_t> ell_f32(f32_ok ? static_cast<size_t>(vpad_rows) * stride_eq : 0);
+		for (int v = 0; f32_ok && v < vpad_rows; ++v)
+			for (int k = 0; k < stride_eq; ++k) {
+				uint32_t off = static_cast<uint32_t>(C) * 8u, coef = 0;
+				if (k < stride) {
+					size_t i = (static_cast<size_t>(v) * stride + k) * 2;
+					off = static_cast<uint32_t>(ell[i] & 0xFFFFF) * 8u;
+					coef = half_bits(ell[i + 1]);
+				}
+				ell_f32[static_cast<size_t>(v) * stride_eq + k] = static_cast<int32_t>((off << 16) | coef);
+			}
+		o.ell_f32 = put(ell_f32);
+	}
 	{
 		// scope lists as 16-bit scan positions (see scan_pos in walker.cuh)
 		const int v128 = V & ~127;
@@ -330,6 +371,7 @@ int lower_model(const GhostModelDesc* d, LoweredModel* out, std::string* why)
 	for (int v = 0; v < V; ++v) if (rows[v].empty()) m.all_have_ctr = 0;
 	m.x16 = (min_value >= 0 && max_value <= 65535) ? 1 : 0;
 	m.v128 = V & ~127;
+	m.f32_ok = f32_ok ? 1 : 0;
 	return GHOST_B200_OK;
 }
 

@@ -28,6 +28,9 @@ struct BlobOffsets {
 	int ell_eq;                // same rows for the LinearEq-only paths, 4 bytes per entry: low half = byte offset of
 	                           // the constraint's state in shared memory (16 * id), high half = coefficient (int16);
 	                           // ell_eq_stride entries per row
+	int ell_f32;               // the same rows for the fp32 evaluation (DevModel::f32_ok), 4 bytes per entry: high half = byte
+	                           // offset of the constraint's state in shared memory (8 * id), low half = coefficient as an
+	                           // IEEE half (exact: |a| <= 2048); ell_eq_stride entries per row
 	int c2v_pos;               // uint16 per scope entry: scan_pos() of the variable (projection scatter)
 	int has_ctr;               // [ceil(V/32)] bit v%32 set iff variable v appears in some constraint
 	int total;
@@ -54,6 +57,10 @@ struct DevModel {
 	int all_have_ctr;          // every variable appears in at least one constraint
 	int x16;                   // every domain value is in [0, 65535]: assignments are stored as unsigned shorts
 	int v128;                  // V rounded down to a multiple of 128: the part of the scan arrays stored block-transposed
+	int f32_ok;                // the candidate evaluation may run in fp32 (one-warp walkers only): permutation problem, every live
+	                           // constraint a LinearEquationEq, one common domain, pairwise distinct start values, at most four
+	                           // live constraints per variable, and every intermediate magnitude so far below 2^24 that each
+	                           // fp32 operation is exact on these integers (lower.cpp states the bound)
 };
 
 // device-only constraint kind: an AllDifferent over all variables of a permutation problem

@@ -11,6 +11,7 @@
 // anything that would not fit).
 #pragma once
 
+#include <cuda_fp16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -387,7 +388,8 @@ __device__ inline int constraint_delta(const MV& mv, const WS& s, int c, int va,
 // ---------------------------------------------------------------------------------------------
 // EQ: every live constraint is a LinearEquationEq (plus, possibly, the static AllDifferent of a
 // permutation problem, whose entries carry coefficient 0): no kind lookups, no count tables.
-template <int T, bool PROJECT, bool EQ = false, class WS>
+// F32: the linear constraints' T is left as an fp32 number (the fp32 evaluation below reads it as such).
+template <int T, bool PROJECT, bool EQ = false, bool F32 = false, class WS>
 __device__ inline int recompute_all(const DevModel& m, const WS& s, int* red)
 {
 	typedef Group<T> G;
@@ -432,7 +434,7 @@ __device__ inline int recompute_all(const DevModel& m, const WS& s, int* red)
 		int kind = mv.kind(c);
 		if (kind_is_linear(kind)) {
 			int t = s.T_of(c) - mv.rhs(c);
-			s.T_of(c) = t;
+			s.T_of(c) = F32 ? __float_as_int((float)t) : t;
 			s.err_of(c) = linear_error_w(linear_w_of_kind(kind), t);
 		} else if (kind == GB_KIND_STATIC) s.err_of(c) = mv.rhs(c);
 	}
@@ -973,9 +975,191 @@ __device__ inline int evaluate_candidates_eq(const DevModel& m, const WS& s, int
 	}
 }
 
-template <int T, bool PERM, bool EQ, class WS>
+// ---------------------------------------------------------------------------------------------
+// fp32 form of the swap evaluation (DevModel::f32_ok: permutation problem, LinearEquationEq only, one
+// common domain, distinct start values, <= 4 live constraints per variable, one warp per walker).
+//
+// Every term of a candidate's sum is |T + a*dx| on integers that lower.cpp bounds far below 2^24, so
+// fp32 computes them exactly, and it computes them on the FMA pipe: t = fma(a, dx, T) and sum += |t|
+// (the absolute value is a source modifier of the add) are two instructions where the integer form
+// needs IMAD + IABS + IADD, two of them on the ALU pipe that limits this kernel.  The constraint state
+// {T, a_v} is kept as two floats; the 16-bit assignment becomes a float by OR-ing it into the mantissa
+// of 2^23 (dx is then one exact subtraction of two such numbers); the coefficient of a row entry is
+// stored as an IEEE half (one conversion instruction, FMA pipe); and the sum starts at 1.5 * 2^23, so
+// that the bit pattern of the finished sum is 0x4B400000 + (integer sum): the arg-min and the tie
+// ballot work on those bits directly, no float-to-int conversion per candidate.
+// Same results as the integer path bit for bit (the golden and trajectory tests run both).
+// ---------------------------------------------------------------------------------------------
+#define GB_F32_BASE 12582912.0f
+#define GB_F32_BASE_BITS 0x4B400000
+template <class WS> __device__ __forceinline__ float& Tf_of(const WS& s, int c) { return reinterpret_cast<float*>(s.cs + c)[0]; }
+template <class WS> __device__ __forceinline__ float& avf_of(const WS& s, int c) { return reinterpret_cast<float*>(s.cs + c)[1]; }
+__device__ __forceinline__ float half_bits_to_float(unsigned f) { return __half2float(__ushort_as_half((unsigned short)f)); }
+
+// Hoist of the selected variable (see hoist_variable_eq): hoist[k] = {constraint id, a_v, T} with a_v, T as float bits.
+template <class WS>
+__device__ inline int hoist_variable_f32(const DevModel& m, const WS& s, int v, int* bias_out)
+{
+	const int lane = threadIdx.x & 31;
+	const int nrow = m.ell_eq_stride;
+	const unsigned dummy = (unsigned)m.C * 8u;
+	const unsigned* row = reinterpret_cast<const unsigned*>(m.blob + m.o.ell_f32) + v * nrow;
+	const unsigned f = lane < nrow ? __ldg(row + lane) : (dummy << 16);
+	const unsigned off = f >> 16;
+	const bool valid = off != dummy;
+	int err = 0;
+	if (valid) {
+		const int c = (int)(off >> 3);
+		const float a = half_bits_to_float(f), t = Tf_of(s, c);
+		err = s.err_of(c);
+		s.hoist[lane] = make_int4(c, __float_as_int(a), __float_as_int(t), 0);
+		s.mark_of(c) = lane + 1; avf_of(s, c) = a;
+	}
+	*bias_out = -__reduce_add_sync(0xffffffffu, err);
+	return __popc(__ballot_sync(0xffffffffu, valid));
+}
+template <class WS>
+__device__ inline void unmark_variable_f32(const DevModel& m, const WS& s, int v)
+{
+	const int lane = threadIdx.x & 31;
+	if (lane < m.ell_eq_stride) {
+		const int c = (int)(__ldg(reinterpret_cast<const unsigned*>(m.blob + m.o.ell_f32) + v * m.ell_eq_stride + lane) >> 19);
+		s.av_of(c) = 0; s.mark_of(c) = 0; // the dummy entry is all zeros anyway
+	}
+}
+
+// NH = hoisted register pairs evaluated per candidate (2 or 4, absent ones are 0*dx + 0), S = entries per row
+// (a row of three is stored in four words: one 128-bit load)
+template <int NH, int S, class WS>
+__device__ inline int evaluate_f32(const DevModel& m, const WS& s, int v, int nh, int bias, int nchunks_c, int* out, ChunkRegs& q)
+{
+	const int lane = threadIdx.x & 31;
+	int xv = s.x[v];
+	asm("" : "+r"(xv));
+	const float xvo = __int_as_float(0x4B000000 | xv);
+	float a0 = 0.f, t0 = 0.f, a1 = 0.f, t1 = 0.f, a2 = 0.f, t2 = 0.f, a3 = 0.f, t3 = 0.f;
+	if (nh > 0) { const int4 h = s.hoist[0]; a0 = __int_as_float(h.y); t0 = __int_as_float(h.z); }
+	if (nh > 1) { const int4 h = s.hoist[1]; a1 = __int_as_float(h.y); t1 = __int_as_float(h.z); }
+	if (NH > 2 && nh > 2) { const int4 h = s.hoist[2]; a2 = __int_as_float(h.y); t2 = __int_as_float(h.z); }
+	if (NH > 2 && nh > 3) { const int4 h = s.hoist[3]; a3 = __int_as_float(h.y); t3 = __int_as_float(h.z); }
+	const float base = (float)bias + GB_F32_BASE;
+	const int nslots = m.V;
+	const unsigned* ell = reinterpret_cast<const unsigned*>(m.blob + m.o.ell_f32);
+	const unsigned char* cs_bytes = reinterpret_cast<const unsigned char*>(s.cs);
+	q.key = GB_INT_MAX; q.bits = 0u;
+#pragma unroll 1
+	for (int ch = 0; ch < nchunks_c; ++ch) {
+		const int slot = ch * 32 + lane;
+		constexpr int SW = S == 3 ? 4 : S;
+		unsigned e[SW];
+		// the partner's row first: this load does not depend on the walker's state
+		if (SW == 1) e[0] = __ldg(ell + slot);
+		else if (SW == 2) { const uint2 r = __ldg(reinterpret_cast<const uint2*>(ell) + slot); e[0] = r.x; e[SW > 1 ? 1 : 0] = r.y; }
+		else { const uint4 r = __ldg(reinterpret_cast<const uint4*>(ell) + slot); e[0] = r.x; e[SW > 1 ? 1 : 0] = r.y; e[SW > 2 ? 2 : 0] = r.z; e[SW > 2 ? 3 : 0] = r.w; }
+		int d = s.x[slot];                                   // padded: no clamp
+		asm("" : "+r"(d));
+		const float dx = xvo - __int_as_float(0x4B000000 | d);   // x_v - x_j, exact
+		// the selected variable's constraints with x_v replaced by x_j: |T - a_v*dx|
+		float sum = base + fabsf(fmaf(-a0, dx, t0));
+		sum += fabsf(fmaf(-a1, dx, t1));
+		if (NH > 2) { sum += fabsf(fmaf(-a2, dx, t2)); sum += fabsf(fmaf(-a3, dx, t3)); }
+		float part = 0.f;   // a second accumulator: the two chains overlap (any association is exact here)
+#pragma unroll
+		for (int k = 0; k < S; ++k) {
+			const unsigned f = e[k];                         // state offset << 16 | a_j as a half
+			const float2 st = *reinterpret_cast<const float2*>(cs_bytes + (f >> 16)); // {T, a_v}
+			const float aj = half_bits_to_float(f);
+			// Partner's own constraint (a_v = 0; search_unit.hpp:881-885): |T + a_j*dx| - |T|.  Shared with v
+			// (872-874): the hoisted single-variable term |T - a_v*dx| is replaced by |T - a_v*dx + a_j*dx|.
+			const float u1 = fmaf(-st.y, dx, st.x);
+			const float u2 = fmaf(aj, dx, u1);
+			part += fabsf(u2);
+			part -= fabsf(u1);
+		}
+		sum += part;
+		const bool ok = d != xv && slot < nslots;           // search_unit.hpp:855-860 (the values are pairwise distinct)
+		const int key = ok ? __float_as_int(sum) : GB_INT_MAX;
+		if (out && slot < m.max_candidates) out[slot] = ok ? key - GB_F32_BASE_BITS : GB_INT_MAX;
+		commit_value_chunk<32>(s, q, ch, key);
+	}
+	// this lane's candidates: its slots below V, minus the selected variable itself
+	return ((m.V - lane + 31) >> 5) - (lane == (v & 31) ? 1 : 0);
+}
+
+template <class WS>
+__device__ inline int evaluate_candidates_f32(const DevModel& m, const WS& s, int v, int nh, int bias, int nchunks_c, int* out, ChunkRegs& q)
+{
+	if (nh <= 2) {
+		switch (m.ell_stride) { // warp-uniform
+		case 1: return evaluate_f32<2, 1>(m, s, v, nh, bias, nchunks_c, out, q);
+		case 2: return evaluate_f32<2, 2>(m, s, v, nh, bias, nchunks_c, out, q);
+		case 3: return evaluate_f32<2, 3>(m, s, v, nh, bias, nchunks_c, out, q);
+		default: return evaluate_f32<2, 4>(m, s, v, nh, bias, nchunks_c, out, q);
+		}
+	}
+	switch (m.ell_stride) {
+	case 1: return evaluate_f32<4, 1>(m, s, v, nh, bias, nchunks_c, out, q);
+	case 2: return evaluate_f32<4, 2>(m, s, v, nh, bias, nchunks_c, out, q);
+	case 3: return evaluate_f32<4, 3>(m, s, v, nh, bias, nchunks_c, out, q);
+	default: return evaluate_f32<4, 4>(m, s, v, nh, bias, nchunks_c, out, q);
+	}
+}
+
+// The update part of a swap (same contract as apply_move_eq), constraint state in fp32.
+template <class WS>
+__device__ inline void apply_move_f32(const DevModel& m, const WS& s, int v, int j, int nh)
+{
+	MV mv(m);
+	const int lane = threadIdx.x & 31;
+	const int xv = s.x[v], xj = s.x[j];
+	const float dxf = (float)(xv - xj);
+	const int nrow = m.ell_eq_stride;
+	const unsigned* rowj = reinterpret_cast<const unsigned*>(m.blob + m.o.ell_f32) + j * nrow;
+	int myd = 0, myb = 0, mye = 0;
+	if (lane < nh + nrow) {
+		int c = -1;
+		float told = 0.f, tnew = 0.f;
+		if (lane < nh) {
+			const int4 h = s.hoist[lane];
+			c = h.x;
+			told = Tf_of(s, c);
+			tnew = fmaf(-__int_as_float(h.y), dxf, told);
+			for (int e = 0; e < nrow; ++e) {
+				const unsigned f = __ldg(rowj + e);
+				if ((int)(f >> 19) == c) { tnew = fmaf(half_bits_to_float(f), dxf, tnew); break; } // the partner is in this scope too
+			}
+		} else {
+			const unsigned f = __ldg(rowj + (lane - nh));
+			const int cc = (int)(f >> 19);
+			if (cc != m.C && s.mark_of(cc) == 0) { // not padding, not shared with v (handled above)
+				c = cc;
+				told = Tf_of(s, c);
+				tnew = fmaf(half_bits_to_float(f), dxf, told);
+			}
+		}
+		if (c >= 0) {
+			myd = __float2int_rn(fabsf(tnew) - fabsf(told));
+			Tf_of(s, c) = tnew; s.err_of(c) = __float2int_rn(fabsf(tnew));
+			if (myd != 0) { myb = mv.scope_begin(c); mye = mv.scope_begin(c + 1); }
+		}
+	}
+	// only the constraints whose error changed (padding entries, shared ones and zero deltas drop out here)
+	unsigned todo = __ballot_sync(0xffffffffu, myd != 0);
+	while (todo) {
+		const int k = __ffs(todo) - 1;
+		todo &= todo - 1;
+		const int d = __shfl_sync(0xffffffffu, myd, k), b = __shfl_sync(0xffffffffu, myb, k), e = __shfl_sync(0xffffffffu, mye, k);
+		for (int i = b + lane; i < e; i += 32) atomicAdd(&s.err_var[mv.scope_pos(i)], d);
+	}
+	__syncwarp();
+	if (lane == 0) { s.x[v] = xj; s.x[j] = xv; }
+	__syncwarp();
+}
+
+template <int T, bool PERM, bool EQ, bool F32 = false, class WS>
 __device__ inline int evaluate_candidates(const DevModel& m, const WS& s, int v, int nh, int bias, int nchunks_c, int* out, ChunkRegs& q)
 {
+	if (F32) return evaluate_candidates_f32(m, s, v, nh, bias, nchunks_c, out, q);
 	if (EQ) return evaluate_candidates_eq<T, PERM>(m, s, v, nh, bias, nchunks_c, out, q);
 	typedef Group<T> G;
 	MV mv(m);

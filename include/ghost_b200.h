@@ -170,6 +170,15 @@ void ghost_b200_model_destroy(GhostModel* model);
 /* Facts about the lowered model: max candidates of one iteration, bytes of walker state. */
 int ghost_b200_model_info(const GhostModel* model, int32_t* max_candidates, int64_t* walker_state_bytes,
                           int32_t* default_threads_per_walker);
+/* Which specialisation of the search kernel a search of this model with `threads_per_walker` (0: default)
+ * threads per walker dispatches to, as GHOST_B200_VARIANT_* bits.  A diagnostic with no counterpart in the
+ * reference (the reference has ONE code path, include/search_unit.hpp:685-1201; the variants compute the
+ * same results and the parity tests run each of them).  Host only. */
+#define GHOST_B200_VARIANT_PERMUTATION 1   /* swap moves (Model::permutation_problem) */
+#define GHOST_B200_VARIANT_LINEAR_EQ_ONLY 2 /* every live constraint is a LinearEquationEq: no kind dispatch */
+#define GHOST_B200_VARIANT_X16 4           /* assignment stored in 16 bits */
+#define GHOST_B200_VARIANT_F32 8           /* swap deltas evaluated in fp32 on the FMA pipe (exact: all magnitudes < 2^22) */
+int ghost_b200_model_variant(const GhostModel* model, int32_t threads_per_walker, int32_t* variant);
 
 /* Fill opts with ghost::Options() defaults (src/options.cpp:36-50) and resolve the -1 ones
  * for a model of V variables as include/solver.hpp:451-473 does. */

@@ -121,6 +121,26 @@ def _cs_linear():
     return m
 
 
+def weighted_permutation_model() -> ModelDesc:
+    """Permutation problem whose live constraints are all LinearEquationEq, with non-unit and negative
+    coefficients and pairs of variables that share a constraint with different coefficients: the model
+    the specialised swap evaluations (packed rows; fp32) must get right beyond the unit-coefficient
+    magic square."""
+    m = ModelDesc(permutation_problem=True, name="weighted_perm")
+    n = 12
+    for i in range(n):
+        m.add_variable(domain=list(range(1, n + 1)), index=i)
+    m.all_different(range(n))
+    m.linear(md.LINEAR_EQ, [0, 1, 2, 3], 20, [2, -1, 3, 1])
+    m.linear(md.LINEAR_EQ, [2, 3, 4, 5, 6], 15, [1, 2, -2, 1, 1])
+    m.linear(md.LINEAR_EQ, [0, 4, 8, 9], 26, [1, 1, 1, 1])
+    m.linear(md.LINEAR_EQ, [1, 5, 9, 10, 11], 10, [3, -1, 2, 1, -3])
+    m.linear(md.LINEAR_EQ, [0, 2, 6, 10], 12, [-1, 2, 1, 1])
+    m.linear(md.LINEAR_EQ, [7, 8], 1, [1, -1])
+    m.linear(md.LINEAR_EQ, [0, 2, 11], 17, [5, -4, 7])
+    return m
+
+
 def _cs_alldiff():
     m = ModelDesc(permutation_problem=True, name="cs_alldiff")
     for i in range(5):
@@ -195,4 +215,6 @@ def model_by_name(name):
         return all_equal_model()
     if name == "mixed_perm_eq":
         return all_equal_permutation_model()
+    if name == "weighted_perm":
+        return weighted_permutation_model()
     return problems.by_name(name)

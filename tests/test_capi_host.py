@@ -160,3 +160,21 @@ def test_ctypes_mirrors_have_the_c_sizes():
     assert list(out)[:4] == [C.sizeof(GhostModelDescStruct), C.sizeof(GhostSearchOptsStruct), C.sizeof(GhostCountersStruct),
                              C.sizeof(GhostResultStruct)]
     assert out[4] == 8 * capi.SUMMARY_WORDS and out[5] == C.sizeof(C.c_void_p)
+
+
+def test_model_variant_bits(monkeypatch):
+    """ghost_b200_model_variant (host only): the magic square is a permutation problem of LinearEquationEq with
+    16-bit values and qualifies for the fp32 swap evaluation on one-warp walkers; n-queens does not; the
+    GHOST_B200_NO_F32 knob (read at lowering) keeps the int32 evaluation."""
+    from ghost_b200 import capi, problems
+    m = capi.Model(problems.by_name("magic_square:6"))
+    assert m.variant(32) == 1 | 2 | 4 | 8
+    assert m.variant(64) == 1 | 2 | 4
+    m.close()
+    m = capi.Model(problems.by_name("n_queens:8"))
+    assert m.variant(0) & 8 == 0 and m.variant(0) & 1 == 0
+    m.close()
+    monkeypatch.setenv("GHOST_B200_NO_F32", "1")
+    m = capi.Model(problems.by_name("magic_square:6"))
+    assert m.variant(32) == 1 | 2 | 4
+    m.close()
