@@ -103,7 +103,7 @@ extern "C" int ghost_b200_model_variant(const GhostModel* gm, int32_t threads_pe
 	const DevModel& m = gm->low.dev;
 	const int T = gm->low.effective_threads_per_walker(threads_per_walker);
 	int v = (m.permutation ? GHOST_B200_VARIANT_PERMUTATION : 0) | (m.eq_only ? GHOST_B200_VARIANT_LINEAR_EQ_ONLY : 0) | (m.x16 ? GHOST_B200_VARIANT_X16 : 0);
-	if (T == 32 && v == 7 && m.f32_ok) v |= GHOST_B200_VARIANT_F32; // the rule of GB_DISPATCH (launch_impl.cuh)
+	if (T == 32 && v == 7 && m.f32_ok) v |= GHOST_B200_VARIANT_F32 | (m.sg_ok ? GHOST_B200_VARIANT_GRID : 0); // the rule of GB_DISPATCH (launch_impl.cuh)
 	*variant = v;
 	return GHOST_B200_OK;
 }

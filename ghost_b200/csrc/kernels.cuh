@@ -225,16 +225,24 @@ __device__ inline void copy_best(const DevModel& m, const WS& s, int* best_x)
 	for (int v = Group<T>::tid(); v < m.V; v += T) best_x[v] = s.x[v];
 }
 
+// One out-of-line copy of the full recomputation for the cold path (two call sites, projection on or off)
+template <int T, bool EQ, bool F32, class WS>
+static __device__ __noinline__ int recompute_all_cold(const DevModel& m, const WalkerLayout& L, unsigned char* base, bool project)
+{
+	const WS s = make_ws<WS>(base, L);   // rebuilt here: handing the view over by reference would pin it in local memory
+	return recompute_all_impl<T, EQ, F32>(m, s, s.red, project);
+}
+
 // SearchUnit::initialize_data_structures (search_unit.hpp:274-317)
 template <int T, bool EQ, bool F32, class WS>
-__device__ inline void initialize_data_structures(const DevModel& m, const WS& s, WalkerRegs& r, int* best_x)
+__device__ inline void initialize_data_structures(const DevModel& m, const WalkerLayout& L, unsigned char* base, const WS& s, WalkerRegs& r, int* best_x)
 {
 	typedef Group<T> G;
 	MV mv(m);
 	r.must_compute = 1;
 	for (int v = G::tid(); v < m.V; v += T) s.tabu[v] = 0;
 	r.tabu_base = r.local_moves;
-	r.cur_sat = recompute_all<T, true, EQ, F32>(m, s, s.red);
+	r.cur_sat = recompute_all_cold<T, EQ, F32, WS>(m, L, base, true);
 	if (r.best_sat > r.cur_sat) { r.best_sat = r.cur_sat; r.best_pending = 1; }
 	if (m.objective != GHOST_OBJ_NONE) {
 		long long part = 0;
@@ -252,7 +260,7 @@ __device__ inline void initialize_data_structures(const DevModel& m, const WS& s
 // best_values buffer (it is cleared by initialize_data_structures right after).
 // Deviation D1: best_x follows best_sat here too.
 template <int T, bool EQ, bool F32, class WS>
-__device__ inline void set_initial_configuration(const DevModel& m, const WS& s, WalkerRegs& r, Rng& rng, int samplings, int* best_x)
+__device__ inline void set_initial_configuration(const DevModel& m, const WalkerLayout& L, unsigned char* base, const WS& s, WalkerRegs& r, Rng& rng, int samplings, int* best_x)
 {
 	typedef Group<T> G;
 	int best_so_far = GB_INT_MAX, current;
@@ -260,7 +268,7 @@ __device__ inline void set_initial_configuration(const DevModel& m, const WS& s,
 	int loops = 0;
 	do {
 		if (m.permutation) random_permutations<T>(m, s, rng, -1); else monte_carlo_sampling<T>(m, s, rng, -1);
-		current = recompute_all<T, false, EQ, F32>(m, s, s.red); // total only: err_var holds the best sample
+		current = recompute_all_cold<T, EQ, F32, WS>(m, L, base, false); // total only: err_var holds the best sample
 		if (best_so_far > current) {
 			best_so_far = current;
 			if (r.best_sat > best_so_far) { r.best_sat = best_so_far; copy_best<T>(m, s, best_x); r.best_pending = 0; }
@@ -274,7 +282,7 @@ __device__ inline void set_initial_configuration(const DevModel& m, const WS& s,
 
 // SearchUnit::initialize_variable_values (search_unit.hpp:259-272)
 template <int T, bool EQ, bool F32, class WS>
-__device__ inline void initialize_variable_values(const DevModel& m, const WS& s, WalkerRegs& r, Rng& rng, const SearchParams& p, int* best_x)
+__device__ inline void initialize_variable_values(const DevModel& m, const WalkerLayout& L, unsigned char* base, const WS& s, WalkerRegs& r, Rng& rng, const SearchParams& p, int* best_x)
 {
 	typedef Group<T> G;
 	MV mv(m);
@@ -283,7 +291,7 @@ __device__ inline void initialize_variable_values(const DevModel& m, const WS& s
 		for (int v = G::tid(); v < m.V; v += T) s.x[v] = mv.ld(m.o.start, v);
 		G::sync();
 	} else
-		set_initial_configuration<T, EQ, F32>(m, s, r, rng, p.nsamplings, best_x);
+		set_initial_configuration<T, EQ, F32>(m, L, base, s, r, rng, p.nsamplings, best_x);
 }
 
 // SearchUnit::local_move (search_unit.hpp:516-541)
@@ -358,13 +366,14 @@ static __device__ __noinline__ ColdState walker_reinit(const DevModel& m, const 
 		// padding of the scan arrays up to a multiple of 32 variables: tabu for ever, error 0
 		for (int v = m.V + tid; v < L.nchunks_v * 32; v += T) { s.tabu[v] = 0xFFFFu; s.err_var[v] = 0; s.x[v] = 0; }
 		G::sync();
-		initialize_variable_values<T, EQ, F32>(m, s, r, rng, p, best_x);
 	} else if (mode == GB_COLD_RESTART) {
 		if (tid == 0) s.counters[K_RESTARTS] += 1;
-		initialize_variable_values<T, EQ, F32>(m, s, r, rng, p, best_x);
-	} else if (PERM) random_permutations<T>(m, s, rng, p.nreset);
+	}
+	// one call site each (not one per mode): the cold path is several times the size of the hot one as it is
+	if (mode != GB_COLD_PERTURB) initialize_variable_values<T, EQ, F32>(m, L, base, s, r, rng, p, best_x);
+	else if (PERM) random_permutations<T>(m, s, rng, p.nreset);
 	else monte_carlo_sampling<T>(m, s, rng, p.nreset);
-	initialize_data_structures<T, EQ, F32>(m, s, r, best_x);
+	initialize_data_structures<T, EQ, F32>(m, L, base, s, r, best_x);
 	if (mode == GB_COLD_FIRST) r.best_pending = 1; // search_unit.hpp:714-717: final_solution = the initial assignment
 	c.must_compute = r.must_compute; c.tabu_base = r.tabu_base; c.cur_sat = r.cur_sat; c.best_sat = r.best_sat;
 	c.best_pending = r.best_pending; c.resume_pending = r.resume_pending;
@@ -373,7 +382,7 @@ static __device__ __noinline__ ColdState walker_reinit(const DevModel& m, const 
 }
 
 // F32: the fp32 form of the LinearEq-only swap evaluation (walker.cuh, evaluate_f32); T == 32, PERM, EQ, 16-bit x only
-template <int T, bool PERM, bool EQ, class XT, bool F32 = false>
+template <int T, bool PERM, bool EQ, class XT, bool F32 = false, int FS = 0>
 __global__ void __launch_bounds__(T == 32 ? 128 : T, (GB_WARPS_PER_SM * 32) / (T == 32 ? 128 : T))
 search_kernel(const __grid_constant__ DevModel m, const __grid_constant__ WalkerLayout L, const __grid_constant__ SearchParams p)
 {
@@ -487,7 +496,7 @@ search_kernel(const __grid_constant__ DevModel m, const __grid_constant__ Walker
 			if (T == 32) { if (tid == (v >> 5)) cq.bits &= ~(1u << (v & 31)); }
 			else if (tid == 0) s.cand_bits[v >> 5] &= ~(1u << (v & 31));
 			int gkey, nties;
-			const int mine = evaluate_candidates<T, PERM, EQ, F32>(m, s, v, nh, bias, L.nchunks_c, nullptr, vq);
+			const int mine = evaluate_candidates<T, PERM, EQ, F32, FS>(m, s, v, nh, bias, L.nchunks_c, nullptr, vq);
 			evals_lane += mine;
 			G::sync();
 			// AdaptiveSearchValueHeuristic::select_value (adaptive_search_value_heuristic.cpp:43-81)
@@ -511,6 +520,7 @@ search_kernel(const __grid_constant__ DevModel m, const __grid_constant__ Walker
 					k = cf > 0 ? 0 : cf < 0 ? nties - 1 : (int)below(rnd.y, (uint32_t)nties);
 				} else k = (int)below(rnd.y, (uint32_t)nties);
 				int slot = T == 32 ? regs_pick_kth(vq, gkey, k, nties) : pick_kth(s.val_key, s.val_bits, L.nchunks_c, gkey, k);
+				if (F32 && (FS > 10 || (FS == 0 && m.sg_ok))) slot = sg_slot_to_var(m, slot); // tie masks of the grid loop are in (group, lane) coordinates
 				new_value = PERM ? slot : mv.dom_value(v, slot);
 			}
 			trace_var = v; trace_val = new_value; trace_min = gmin;

@@ -12,21 +12,45 @@ static cudaError_t allow_smem(K kernel, size_t smem)
 	return cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
 }
 
+template <bool PERM, bool EQ, class XT, bool F32, int FS>
+static cudaError_t do_search_fs(int grid, int block, size_t smem, cudaStream_t st, const DevModel& m, const WalkerLayout& L, const SearchParams& p)
+{
+	cudaError_t e = allow_smem(search_kernel<GB_T, PERM, EQ, XT, F32, FS>, smem);
+	if (e != cudaSuccess) return e;
+	search_kernel<GB_T, PERM, EQ, XT, F32, FS><<<grid, block, smem, st>>>(m, L, p);
+	return cudaGetLastError();
+}
 template <bool PERM, bool EQ, class XT, bool F32 = false>
 static cudaError_t do_search(int grid, int block, size_t smem, cudaStream_t st, const DevModel& m, const WalkerLayout& L, const SearchParams& p)
 {
-	cudaError_t e = allow_smem(search_kernel<GB_T, PERM, EQ, XT, F32>, smem);
-	if (e != cudaSuccess) return e;
-	search_kernel<GB_T, PERM, EQ, XT, F32><<<grid, block, smem, st>>>(m, L, p);
-	return cudaGetLastError();
+#ifndef GB_NO_FS
+	if (F32 && m.sg_ok) { // the structured-grid loop (see evaluate_candidates_f32)
+		switch (m.ell_stride) {
+		case 1: return do_search_fs<PERM, EQ, XT, F32, F32 ? 11 : 0>(grid, block, smem, st, m, L, p);
+		case 2: return do_search_fs<PERM, EQ, XT, F32, F32 ? 12 : 0>(grid, block, smem, st, m, L, p);
+		case 3: return do_search_fs<PERM, EQ, XT, F32, F32 ? 13 : 0>(grid, block, smem, st, m, L, p);
+		default: return do_search_fs<PERM, EQ, XT, F32, F32 ? 14 : 0>(grid, block, smem, st, m, L, p);
+		}
+	}
+	if (F32) { // one kernel per row length of the packed rows (see evaluate_candidates_f32)
+		switch (m.ell_stride) {
+		case 1: return do_search_fs<PERM, EQ, XT, F32, F32 ? 1 : 0>(grid, block, smem, st, m, L, p);
+		case 2: return do_search_fs<PERM, EQ, XT, F32, F32 ? 2 : 0>(grid, block, smem, st, m, L, p);
+		case 3: return do_search_fs<PERM, EQ, XT, F32, F32 ? 3 : 0>(grid, block, smem, st, m, L, p);
+		default: return do_search_fs<PERM, EQ, XT, F32, F32 ? 4 : 0>(grid, block, smem, st, m, L, p);
+		}
+	}
+#endif
+	return do_search_fs<PERM, EQ, XT, F32, 0>(grid, block, smem, st, m, L, p);
 }
 // resident CTAs per SM of the search kernel this model dispatches to (registers, shared memory, threads)
 template <bool PERM, bool EQ, class XT, bool F32 = false>
 static cudaError_t do_occupancy(int block, size_t smem, int* ctas_per_sm)
 {
-	cudaError_t e = allow_smem(search_kernel<GB_T, PERM, EQ, XT, F32>, smem);
+	// (the row-length instantiations of the fp32 kernel share registers / shared memory figures with this one)
+	cudaError_t e = allow_smem(search_kernel<GB_T, PERM, EQ, XT, F32, 0>, smem);
 	if (e != cudaSuccess) return e;
-	return cudaOccupancyMaxActiveBlocksPerMultiprocessor(ctas_per_sm, search_kernel<GB_T, PERM, EQ, XT, F32>, block, smem);
+	return cudaOccupancyMaxActiveBlocksPerMultiprocessor(ctas_per_sm, search_kernel<GB_T, PERM, EQ, XT, F32, 0>, block, smem);
 }
 template <bool PERM, bool EQ, class XT, bool F32 = false>
 static cudaError_t do_eval(int grid, int block, size_t smem, cudaStream_t st, const DevModel& m, const WalkerLayout& L, int W,

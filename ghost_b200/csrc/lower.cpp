@@ -323,11 +323,12 @@ int lower_model(const GhostModelDesc* d, LoweredModel* out, std::string* why)
 			const uint32_t mant = e <= 10 ? (mag << (10 - e)) & 0x3FFu : (mag >> (e - 10)) & 0x3FFu;
 			return sign | (static_cast<uint32_t>(e + 15) << 10) | mant;
 		};
-		std::vector<int32_t> ell_f32(f32_ok ? static_cast<size_t>(vpad_rows) * stride_eq : 0);
-		for (int v = 0; f32_ok && v < vpad_rows; ++v)
+		// one more all-dummy chunk of rows: the fp32 loop evaluates two chunks per pass
+		std::vector<int32_t> ell_f32(f32_ok ? static_cast<size_t>(vpad_rows + 32) * stride_eq : 0);
+		for (int v = 0; f32_ok && v < vpad_rows + 32; ++v)
 			for (int k = 0; k < stride_eq; ++k) {
 				uint32_t off = static_cast<uint32_t>(C) * 8u, coef = 0;
-				if (k < stride) {
+				if (k < stride && v < vpad_rows) {
 					size_t i = (static_cast<size_t>(v) * stride + k) * 2;
 					off = static_cast<uint32_t>(ell[i] & 0xFFFFF) * 8u;
 					coef = half_bits(ell[i + 1]);
@@ -349,6 +350,88 @@ int lower_model(const GhostModelDesc* d, LoweredModel* out, std::string* why)
 		o.c2v_pos = put(packed);
 	}
 	o.has_ctr = put(has_ctr);
+	// ---- structured grid -------------------------------------------------------------------------------------
+	// Matrix-shaped models (magic squares, Latin-square sums, ...): with the variables cut into consecutive groups of
+	// CW, every variable (g, l) is in U_g, a constraint common to its whole group, and in L_l, a constraint common to
+	// position l of every group, both with one common coefficient; few cells carry anything else (the diagonals).
+	// The fp32 evaluation then keeps L_l's state in a register of lane l for the whole candidate loop and broadcasts
+	// U_g's once per chunk, instead of a row load and a shared-memory gather per candidate and constraint; the few
+	// irregular cells are evaluated separately by the lane that owns their chunk's summary (walker.cuh, evaluate_sg).
+	int sg_ok = 0, sg_cw = 0, sg_groups = 0, sg_xn = 0, sg_au = 0, sg_al = 0;
+	{
+		std::vector<int32_t> sg(32 * 4, 0);
+		// (groups narrower than half a warp would leave most lanes idle: the plain loop is the better one then)
+		for (int cw = 32; f32_ok && !sg_ok && cw >= 16 && !std::getenv("GHOST_B200_NO_SG"); --cw) {
+			const int G = (V + cw - 1) / cw;
+			if (G > 32 || G < 2) continue;
+			// constraints (with coefficient) common to a set of variables
+			auto common = [&](const std::vector<int>& vars) {
+				std::vector<std::pair<int, int>> acc = live[vars[0]];
+				for (size_t i = 1; i < vars.size() && !acc.empty(); ++i) {
+					std::vector<std::pair<int, int>> keep;
+					for (auto& pr : acc) if (std::find(live[vars[i]].begin(), live[vars[i]].end(), pr) != live[vars[i]].end()) keep.push_back(pr);
+					acc.swap(keep);
+				}
+				return acc;
+			};
+			std::vector<int> U(G, -1), Lc(cw, -1);
+			int au = 0, al = 0;
+			bool ok_grid = true;
+			for (int g = 0; g < G && ok_grid; ++g) {
+				std::vector<int> vars;
+				for (int l = 0; l < cw && g * cw + l < V; ++l) vars.push_back(g * cw + l);
+				auto acc = common(vars);
+				if (g == 0 && !acc.empty()) au = acc[0].second;
+				for (auto& pr : acc) if (pr.second == au && U[g] < 0) U[g] = pr.first;
+				if (U[g] < 0) ok_grid = false;
+			}
+			for (int l = 0; l < cw && ok_grid; ++l) {
+				std::vector<int> vars;
+				for (int g = 0; g < G && g * cw + l < V; ++g) vars.push_back(g * cw + l);
+				auto acc = common(vars);
+				bool first = true;
+				for (auto& pr : acc) {
+					if (std::find(U.begin(), U.end(), pr.first) != U.end()) continue; // a group constraint (e.g. one over all variables)
+					if (l == 0 && first) { al = pr.second; first = false; }
+					if (pr.second == al && Lc[l] < 0) Lc[l] = pr.first;
+				}
+				if (Lc[l] < 0) ok_grid = false;
+			}
+			if (!ok_grid || au == 0 || al == 0) continue;
+			// the cells with further constraints, per group
+			int xn = 0;
+			std::vector<std::vector<int>> extra(G);
+			for (int v = 0; v < V && ok_grid; ++v) {
+				const int g = v / cw, l = v % cw;
+				bool has_u = false, has_l = false;
+				size_t others = 0;
+				for (auto& pr : live[v]) {
+					if (pr.first == U[g] && !has_u) has_u = true;
+					else if (pr.first == Lc[l] && !has_l) has_l = true;
+					else ++others;
+				}
+				if (!has_u || !has_l) ok_grid = false;
+				if (others > 0) extra[g].push_back(l);
+			}
+			for (int g = 0; g < G; ++g) { if (extra[g].size() > 4) ok_grid = false; xn = std::max<int>(xn, static_cast<int>(extra[g].size())); }
+			if (!ok_grid) continue;
+			for (int lane = 0; lane < 32; ++lane) {
+				sg[lane * 4 + 0] = (lane < G ? U[lane] : C) * 8;
+				sg[lane * 4 + 1] = (lane < cw ? Lc[lane] : C) * 8;
+				uint32_t skip = 0, packed = 0xFFFFFFFFu;
+				for (int g = 0; g < 32; ++g) {
+					const bool cell = g < G && lane < cw && g * cw + lane < V;
+					const bool irregular = cell && std::find(extra[g].begin(), extra[g].end(), lane) != extra[g].end();
+					if (!cell || irregular) skip |= 1u << g;
+				}
+				if (lane < G) for (size_t e = 0; e < extra[lane].size(); ++e) packed = (packed & ~(0xFFu << (8 * e))) | (static_cast<uint32_t>(extra[lane][e]) << (8 * e));
+				sg[lane * 4 + 2] = static_cast<int32_t>(skip);
+				sg[lane * 4 + 3] = static_cast<int32_t>(packed);
+			}
+			sg_ok = 1; sg_cw = cw; sg_groups = G; sg_xn = xn; sg_au = au; sg_al = al;
+		}
+		o.sg = put(sg);
+	}
 	o.total = static_cast<int>(blob.size());
 
 	DevModel& m = L.dev;
@@ -372,6 +455,7 @@ int lower_model(const GhostModelDesc* d, LoweredModel* out, std::string* why)
 	m.x16 = (min_value >= 0 && max_value <= 65535) ? 1 : 0;
 	m.v128 = V & ~127;
 	m.f32_ok = f32_ok ? 1 : 0;
+	m.sg_ok = sg_ok; m.sg_cw = sg_cw; m.sg_groups = sg_groups; m.sg_xn = sg_xn; m.sg_au = sg_au; m.sg_al = sg_al;
 	return GHOST_B200_OK;
 }
 
@@ -386,7 +470,7 @@ WalkerLayout LoweredModel::layout(int /*threads_per_walker*/, int nreset) const
 	w.nchunks_v = (m.V + 31) / 32;
 	w.nchunks_c = (m.max_candidates + 31) / 32;
 	const int vpad = w.nchunks_v * 32;
-	w.x = take((m.x16 ? 2 : 4) * vpad);  // padded: a chunk of swap partners is read without a clamp   // scan without bounds tests: padded, the padding is always tabu
+	w.x = take((m.x16 ? 2 : 4) * (vpad + 64));  // + two chunks: the fp32 evaluations read two chunks per pass, the grid form up to 32 slots past a group  // padded: a chunk of swap partners is read without a clamp   // scan without bounds tests: padded, the padding is always tabu
 	w.err_var = take(4 * vpad);
 	w.tabu = take(2 * vpad);
 	w.cs = take(8 * (m.C + 1));  // + the all-zero dummy constraint that pads the ELL rows
@@ -399,8 +483,10 @@ WalkerLayout LoweredModel::layout(int /*threads_per_walker*/, int nreset) const
 	// sampling scratch lives in arrays that are dead while a reset samples: the tabu list (cleared by
 	// initialize_data_structures afterwards) and the projected errors (recomputed afterwards)
 	w.flags = w.tabu;
-	w.val_key = take(4 * w.nchunks_c);
-	w.val_bits = take(4 * w.nchunks_c);
+	// chunk summaries of the value evaluation; one-warp walkers use the two arrays as ONE staging area of
+	// {key, bits} pairs for the variable scan and the fp32 evaluation (hence the common size, 32 + 2 chunks)
+	w.val_key = take(4 * (std::max(std::max(w.nchunks_c, w.nchunks_v), 32) + 2));
+	w.val_bits = take(4 * (std::max(std::max(w.nchunks_c, w.nchunks_v), 32) + 2));
 	w.hoist = take(16 * m.max_degree);
 	w.upd = take(4 * 2 * 2 * m.max_degree);
 	w.sample = (8 * std::max(1, nreset) <= 4 * m.V) ? w.err_var : take(4 * 2 * std::max(1, nreset));

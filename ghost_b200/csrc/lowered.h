@@ -31,6 +31,10 @@ struct BlobOffsets {
 	int ell_f32;               // the same rows for the fp32 evaluation (DevModel::f32_ok), 4 bytes per entry: high half = byte
 	                           // offset of the constraint's state in shared memory (8 * id), low half = coefficient as an
 	                           // IEEE half (exact: |a| <= 2048); ell_eq_stride entries per row
+	int sg;                    // structured grid (DevModel::sg_ok): int4 per lane {byte offset of the state of group `lane`'s common
+	                           // constraint, byte offset of the state of lane `lane`'s common constraint, bit g set = cell (g, lane)
+	                           // is NOT evaluated by the main loop, the lanes (4 x 8 bits, 0xFF = none) of group `lane`'s cells
+	                           // that carry further constraints}
 	int c2v_pos;               // uint16 per scope entry: scan_pos() of the variable (projection scatter)
 	int has_ctr;               // [ceil(V/32)] bit v%32 set iff variable v appears in some constraint
 	int total;
@@ -61,6 +65,12 @@ struct DevModel {
 	                           // constraint a LinearEquationEq, one common domain, pairwise distinct start values, at most four
 	                           // live constraints per variable, and every intermediate magnitude so far below 2^24 that each
 	                           // fp32 operation is exact on these integers (lower.cpp states the bound)
+	int sg_ok;                 // f32_ok and the variables form a grid (lower.cpp, "structured grid"): consecutive groups of sg_cw
+	                           // variables, each group inside ONE common constraint, each position l of every group inside ONE
+	                           // common constraint (rows and columns of a matrix model); at most 4 cells per group carry more
+	int sg_cw, sg_groups;      // variables per group (<= 32), number of groups (<= 32)
+	int sg_xn;                 // largest number of such cells in a group (passes of the second loop)
+	int sg_au, sg_al;          // the common coefficient of the group constraints / of the position constraints
 };
 
 // device-only constraint kind: an AllDifferent over all variables of a permutation problem

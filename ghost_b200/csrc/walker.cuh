@@ -389,8 +389,8 @@ __device__ inline int constraint_delta(const MV& mv, const WS& s, int c, int va,
 // EQ: every live constraint is a LinearEquationEq (plus, possibly, the static AllDifferent of a
 // permutation problem, whose entries carry coefficient 0): no kind lookups, no count tables.
 // F32: the linear constraints' T is left as an fp32 number (the fp32 evaluation below reads it as such).
-template <int T, bool PROJECT, bool EQ = false, bool F32 = false, class WS>
-__device__ inline int recompute_all(const DevModel& m, const WS& s, int* red)
+template <int T, bool EQ, bool F32, class WS>
+__device__ __forceinline__ int recompute_all_impl(const DevModel& m, const WS& s, int* red, const bool PROJECT)
 {
 	typedef Group<T> G;
 	MV mv(m);
@@ -461,6 +461,8 @@ __device__ inline int recompute_all(const DevModel& m, const WS& s, int* red)
 	G::sync();
 	return total;
 }
+template <int T, bool PROJECT, bool EQ = false, bool F32 = false, class WS>
+__device__ __forceinline__ int recompute_all(const DevModel& m, const WS& s, int* red) { return recompute_all_impl<T, EQ, F32>(m, s, red, PROJECT); }
 
 // ---------------------------------------------------------------------------------------------
 // Candidate sets are kept as (key, bitmask) per chunk of 32 slots: the set is every set bit of
@@ -582,17 +584,17 @@ __device__ __forceinline__ void commit_scan_chunk(const WS& s, ChunkRegs& q, int
 // both arrays are padded to a multiple of 32 entries (padding: always tabu), so no chunk needs a
 // bounds test.
 // ---------------------------------------------------------------------------------------------
-template <int T, class WS>
-__device__ inline int scan_candidates(const DevModel& m, const WS& s, int nchunks_v, int local_moves,
-                                      bool free_vars_ok, int* red, int* worst_out, int* ntabu_out, ChunkRegs& q)
+// One pass over the variables: chunk summaries into q / (cand_key, cand_bits), returns this lane's tabu count.
+// USE_MASK: variables that appear in no constraint are not candidates (…candidates_heuristic.cpp:45-46) and the
+// model has some; a template axis because the predicated form costs every model five instructions per block.
+template <int T, bool USE_MASK, class WS>
+__device__ __forceinline__ int scan_pass(const DevModel& m, const WS& s, int nchunks_v, int local_moves, ChunkRegs& q)
 {
 	typedef Group<T> G;
 	MV mv(m);
 	const int lane = threadIdx.x & 31;
-	const bool use_mask = !free_vars_ok && !m.all_have_ctr;
 	const int nblocks = m.v128 >> 7;
 	int ntabu = 0; // per lane
-	q.key = -1; q.bits = 0u;
 	const int4* e4 = reinterpret_cast<const int4*>(s.err_var);
 	const uint2* t4 = reinterpret_cast<const uint2*>(s.tabu);
 #ifndef GB_UNROLL2   // not unrolled: the loop body has to stay small enough for the per-scheduler instruction cache (measured)
@@ -605,26 +607,72 @@ __device__ inline int scan_candidates(const DevModel& m, const WS& s, int nchunk
 		const bool k2 = (int)(t.y & 0xFFFFu) > local_moves, k3 = (int)(t.y >> 16) > local_moves;
 		ntabu += (k0 ? 1 : 0) + (k1 ? 1 : 0) + (k2 ? 1 : 0) + (k3 ? 1 : 0);
 		int e0 = k0 ? -1 : e.x, e1 = k1 ? -1 : e.y, e2 = k2 ? -1 : e.z, e3 = k3 ? -1 : e.w;
-		if (use_mask) {
+		if (USE_MASK) {
 			const int4 h = __ldg(reinterpret_cast<const int4*>(m.blob + m.o.has_ctr) + b);
 			if (!(((unsigned)h.x >> lane) & 1u)) e0 = -1;
 			if (!(((unsigned)h.y >> lane) & 1u)) e1 = -1;
 			if (!(((unsigned)h.z >> lane) & 1u)) e2 = -1;
 			if (!(((unsigned)h.w >> lane) & 1u)) e3 = -1;
 		}
-		commit_scan_chunk<T>(s, q, 4 * b + 0, e0);
-		commit_scan_chunk<T>(s, q, 4 * b + 1, e1);
-		commit_scan_chunk<T>(s, q, 4 * b + 2, e2);
-		commit_scan_chunk<T>(s, q, 4 * b + 3, e3);
+#ifndef GB_SCAN_SPLIT
+		if (T == 32) {
+#else
+		if (false) {
+#endif
+			// ONE warp reduction for the block's four chunks: a chunk that does not attain the block's largest
+			// error gets an empty mask (only chunks whose key equals the global maximum matter); lane 0 stages
+			// the four {key, bits} summaries, the owning lanes pick them up after the loop
+			const int c = __reduce_max_sync(0xffffffffu, max(max(e0, e1), max(e2, e3)));
+			const unsigned b0 = __ballot_sync(0xffffffffu, e0 == c), b1 = __ballot_sync(0xffffffffu, e1 == c);
+			const unsigned b2 = __ballot_sync(0xffffffffu, e2 == c), b3 = __ballot_sync(0xffffffffu, e3 == c);
+			if (lane == 0) {
+				int4* stage = reinterpret_cast<int4*>(s.val_key);
+				stage[2 * b] = make_int4(c, (int)b0, c, (int)b1);
+				stage[2 * b + 1] = make_int4(c, (int)b2, c, (int)b3);
+			}
+		} else {
+			commit_scan_chunk<T>(s, q, 4 * b + 0, e0);
+			commit_scan_chunk<T>(s, q, 4 * b + 1, e1);
+			commit_scan_chunk<T>(s, q, 4 * b + 2, e2);
+			commit_scan_chunk<T>(s, q, 4 * b + 3, e3);
+		}
 	}
 	for (int ch = 4 * nblocks + G::warp(); ch < nchunks_v; ch += G::NW) { // the tail, natural order
 		const int i = ch * 32 + lane;
 		const bool k = (int)s.tabu[i] > local_moves;
 		ntabu += k ? 1 : 0;
 		int e = k ? -1 : s.err_var[i];
-		if (use_mask && !(((unsigned)mv.ld(m.o.has_ctr, ch) >> lane) & 1u)) e = -1;
-		commit_scan_chunk<T>(s, q, ch, e);
+		if (USE_MASK && !(((unsigned)mv.ld(m.o.has_ctr, ch) >> lane) & 1u)) e = -1;
+#ifndef GB_SCAN_SPLIT
+		if (T == 32) {
+			const int c = __reduce_max_sync(0xffffffffu, e);
+			const unsigned bb = __ballot_sync(0xffffffffu, e == c);
+			if (lane == 0) reinterpret_cast<int2*>(s.val_key)[ch] = make_int2(c, (int)bb);
+		} else
+#endif
+			commit_scan_chunk<T>(s, q, ch, e);
 	}
+#ifndef GB_SCAN_SPLIT
+	if (T == 32) {
+#else
+	if (false) {
+#endif
+		__syncwarp();
+		const int2 mine = reinterpret_cast<const int2*>(s.val_key)[lane];   // staged {key, bits}; stale words beyond the last chunk
+		q.key = lane < nchunks_v ? mine.x : -1;
+		q.bits = lane < nchunks_v ? (unsigned)mine.y : 0u;
+	}
+	return ntabu;
+}
+
+template <int T, class WS>
+__device__ inline int scan_candidates(const DevModel& m, const WS& s, int nchunks_v, int local_moves,
+                                      bool free_vars_ok, int* red, int* worst_out, int* ntabu_out, ChunkRegs& q)
+{
+	typedef Group<T> G;
+	const bool use_mask = !free_vars_ok && !m.all_have_ctr;
+	q.key = -1; q.bits = 0u;
+	int ntabu = use_mask ? scan_pass<T, true>(m, s, nchunks_v, local_moves, q) : scan_pass<T, false>(m, s, nchunks_v, local_moves, q);
 	int worst, ncand;
 	if (T == 32) {
 		ntabu = __reduce_add_sync(0xffffffffu, ntabu);
@@ -1028,73 +1076,201 @@ __device__ inline void unmark_variable_f32(const DevModel& m, const WS& s, int v
 	}
 }
 
-// NH = hoisted register pairs evaluated per candidate (2 or 4, absent ones are 0*dx + 0), S = entries per row
-// (a row of three is stored in four words: one 128-bit load)
+// The selected variable's side of a candidate's sum, in registers: (a_v, T) of its hoisted constraints (absent
+// ones are 0*dx + 0), x_v as an integer and as 2^23 + x_v, and the start of every sum (bias + 1.5 * 2^23).
+// NH = hoisted pairs evaluated per candidate (2 or 4).
+template <int NH>
+struct HoistF32 { float a0, t0, a1, t1, a2, t2, a3, t3, xvo, base; int xv; };
+template <int NH, class WS>
+__device__ __forceinline__ HoistF32<NH> load_hoist_f32(const WS& s, int v, int nh, int bias)
+{
+	HoistF32<NH> h;
+	int xv = s.x[v];
+	asm("" : "+r"(xv));
+	h.xv = xv;
+	h.xvo = __int_as_float(0x4B000000 | xv);
+	h.a0 = h.t0 = h.a1 = h.t1 = h.a2 = h.t2 = h.a3 = h.t3 = 0.f;
+	if (nh > 0) { const int4 e = s.hoist[0]; h.a0 = __int_as_float(e.y); h.t0 = __int_as_float(e.z); }
+	if (nh > 1) { const int4 e = s.hoist[1]; h.a1 = __int_as_float(e.y); h.t1 = __int_as_float(e.z); }
+	if (NH > 2 && nh > 2) { const int4 e = s.hoist[2]; h.a2 = __int_as_float(e.y); h.t2 = __int_as_float(e.z); }
+	if (NH > 2 && nh > 3) { const int4 e = s.hoist[3]; h.a3 = __int_as_float(e.y); h.t3 = __int_as_float(e.z); }
+	h.base = (float)bias + GB_F32_BASE;
+	return h;
+}
+// |T - a_v*dx| of the hoisted constraints on top of the base: the selected variable's constraints with x_v replaced by x_j
+template <int NH>
+__device__ __forceinline__ float hoisted_sum_f32(const HoistF32<NH>& h, float dx)
+{
+	float sum = h.base + fabsf(fmaf(-h.a0, dx, h.t0));
+	sum += fabsf(fmaf(-h.a1, dx, h.t1));
+	if (NH > 2) { sum += fabsf(fmaf(-h.a2, dx, h.t2)); sum += fabsf(fmaf(-h.a3, dx, h.t3)); }
+	return sum;
+}
+
+// Key (bits of 1.5 * 2^23 + sum, or INT_MAX) of the swap with the variable in `slot`, every constraint of the
+// partner taken from its packed row.  S = entries per row (a row of three is stored in four words: one 128-bit load).
+template <int NH, int S, class WS>
+__device__ __forceinline__ int f32_slot_key(const DevModel& m, const WS& s, const HoistF32<NH>& h, int slot, int nslots, int* out)
+{
+	const unsigned* ell = reinterpret_cast<const unsigned*>(m.blob + m.o.ell_f32);
+	const unsigned char* cs_bytes = reinterpret_cast<const unsigned char*>(s.cs);
+	constexpr int SW = S == 3 ? 4 : S;
+	unsigned e[SW];
+	// the partner's row first: this load does not depend on the walker's state
+	if (SW == 1) e[0] = __ldg(ell + slot);
+	else if (SW == 2) { const uint2 r = __ldg(reinterpret_cast<const uint2*>(ell) + slot); e[0] = r.x; e[SW > 1 ? 1 : 0] = r.y; }
+	else { const uint4 r = __ldg(reinterpret_cast<const uint4*>(ell) + slot); e[0] = r.x; e[SW > 1 ? 1 : 0] = r.y; e[SW > 2 ? 2 : 0] = r.z; e[SW > 2 ? 3 : 0] = r.w; }
+	int d = s.x[slot];                                   // padded: no clamp
+	asm("" : "+r"(d));
+	const float dx = h.xvo - __int_as_float(0x4B000000 | d);   // x_v - x_j, exact
+	float sum = hoisted_sum_f32(h, dx);
+	float part = 0.f;   // a second accumulator: the two chains overlap (any association is exact here)
+#pragma unroll
+	for (int k = 0; k < S; ++k) {
+		const unsigned f = e[k];                         // state offset << 16 | a_j as a half
+		const float2 st = *reinterpret_cast<const float2*>(cs_bytes + (f >> 16)); // {T, a_v}
+		const float aj = half_bits_to_float(f);
+		// Partner's own constraint (a_v = 0; search_unit.hpp:881-885): |T + a_j*dx| - |T|.  Shared with v
+		// (872-874): the hoisted single-variable term |T - a_v*dx| is replaced by |T - a_v*dx + a_j*dx|.
+		const float u1 = fmaf(-st.y, dx, st.x);
+		const float u2 = fmaf(aj, dx, u1);
+		part += fabsf(u2);
+		part -= fabsf(u1);
+	}
+	sum += part;
+	const bool ok = d != h.xv && slot < nslots;          // search_unit.hpp:855-860 (the values are pairwise distinct)
+	const int key = ok ? __float_as_int(sum) : GB_INT_MAX;
+	if (out && slot < m.max_candidates) out[slot] = ok ? key - GB_F32_BASE_BITS : GB_INT_MAX;
+	return key;
+}
+
+// Two chunks of 32 partners per loop pass: two independent dependency chains in flight, ONE warp reduction for
+// both (the pair's minimum; a chunk that does not attain it gets an empty tie mask, which is all the pick needs:
+// only chunks whose key equals the global minimum matter), and the pair's two summaries leave in one 128-bit
+// store by lane 0 into the (val_key, val_bits) region, read back as {key, bits}[chunk] after the loop by the
+// lane that owns the chunk.  The packed rows and the assignment are padded so that the second chunk of the last
+// pair needs no clamp.
+__device__ __forceinline__ void commit_pair(int4* summaries, int ch, int ka, int kb)
+{
+	const int cmin = __reduce_min_sync(0xffffffffu, min(ka, kb));
+	const unsigned ba = __ballot_sync(0xffffffffu, ka == cmin), bb = __ballot_sync(0xffffffffu, kb == cmin);
+	if ((threadIdx.x & 31) == 0) summaries[ch >> 1] = make_int4(cmin, (int)ba, cmin, (int)bb);
+}
+__device__ __forceinline__ void fetch_summary(const int4* summaries, int nchunks, ChunkRegs& q)
+{
+	const int lane = threadIdx.x & 31;
+	__syncwarp();
+	const int2 mine = reinterpret_cast<const int2*>(summaries)[lane];   // lanes beyond the last chunk read stale words: masked
+	q.key = lane < nchunks ? mine.x : GB_INT_MAX;
+	q.bits = lane < nchunks ? (unsigned)mine.y : 0u;
+}
+
 template <int NH, int S, class WS>
 __device__ inline int evaluate_f32(const DevModel& m, const WS& s, int v, int nh, int bias, int nchunks_c, int* out, ChunkRegs& q)
 {
 	const int lane = threadIdx.x & 31;
-	int xv = s.x[v];
-	asm("" : "+r"(xv));
-	const float xvo = __int_as_float(0x4B000000 | xv);
-	float a0 = 0.f, t0 = 0.f, a1 = 0.f, t1 = 0.f, a2 = 0.f, t2 = 0.f, a3 = 0.f, t3 = 0.f;
-	if (nh > 0) { const int4 h = s.hoist[0]; a0 = __int_as_float(h.y); t0 = __int_as_float(h.z); }
-	if (nh > 1) { const int4 h = s.hoist[1]; a1 = __int_as_float(h.y); t1 = __int_as_float(h.z); }
-	if (NH > 2 && nh > 2) { const int4 h = s.hoist[2]; a2 = __int_as_float(h.y); t2 = __int_as_float(h.z); }
-	if (NH > 2 && nh > 3) { const int4 h = s.hoist[3]; a3 = __int_as_float(h.y); t3 = __int_as_float(h.z); }
-	const float base = (float)bias + GB_F32_BASE;
+	const HoistF32<NH> h = load_hoist_f32<NH>(s, v, nh, bias);
 	const int nslots = m.V;
-	const unsigned* ell = reinterpret_cast<const unsigned*>(m.blob + m.o.ell_f32);
-	const unsigned char* cs_bytes = reinterpret_cast<const unsigned char*>(s.cs);
-	q.key = GB_INT_MAX; q.bits = 0u;
+	int4* summaries = reinterpret_cast<int4*>(s.val_key);   // {key, bits} per chunk, two chunks per int4
+#ifndef GB_F32_SINGLE
+#pragma unroll 1
+	for (int ch = 0; ch < nchunks_c; ch += 2) {
+		const int slot = ch * 32 + lane;
+		const int ka = f32_slot_key<NH, S>(m, s, h, slot, nslots, out), kb = f32_slot_key<NH, S>(m, s, h, slot + 32, nslots, out);
+		commit_pair(summaries, ch, ka, kb);
+	}
+#else
 #pragma unroll 1
 	for (int ch = 0; ch < nchunks_c; ++ch) {
-		const int slot = ch * 32 + lane;
-		constexpr int SW = S == 3 ? 4 : S;
-		unsigned e[SW];
-		// the partner's row first: this load does not depend on the walker's state
-		if (SW == 1) e[0] = __ldg(ell + slot);
-		else if (SW == 2) { const uint2 r = __ldg(reinterpret_cast<const uint2*>(ell) + slot); e[0] = r.x; e[SW > 1 ? 1 : 0] = r.y; }
-		else { const uint4 r = __ldg(reinterpret_cast<const uint4*>(ell) + slot); e[0] = r.x; e[SW > 1 ? 1 : 0] = r.y; e[SW > 2 ? 2 : 0] = r.z; e[SW > 2 ? 3 : 0] = r.w; }
-		int d = s.x[slot];                                   // padded: no clamp
-		asm("" : "+r"(d));
-		const float dx = xvo - __int_as_float(0x4B000000 | d);   // x_v - x_j, exact
-		// the selected variable's constraints with x_v replaced by x_j: |T - a_v*dx|
-		float sum = base + fabsf(fmaf(-a0, dx, t0));
-		sum += fabsf(fmaf(-a1, dx, t1));
-		if (NH > 2) { sum += fabsf(fmaf(-a2, dx, t2)); sum += fabsf(fmaf(-a3, dx, t3)); }
-		float part = 0.f;   // a second accumulator: the two chains overlap (any association is exact here)
-#pragma unroll
-		for (int k = 0; k < S; ++k) {
-			const unsigned f = e[k];                         // state offset << 16 | a_j as a half
-			const float2 st = *reinterpret_cast<const float2*>(cs_bytes + (f >> 16)); // {T, a_v}
-			const float aj = half_bits_to_float(f);
-			// Partner's own constraint (a_v = 0; search_unit.hpp:881-885): |T + a_j*dx| - |T|.  Shared with v
-			// (872-874): the hoisted single-variable term |T - a_v*dx| is replaced by |T - a_v*dx + a_j*dx|.
-			const float u1 = fmaf(-st.y, dx, st.x);
-			const float u2 = fmaf(aj, dx, u1);
-			part += fabsf(u2);
-			part -= fabsf(u1);
-		}
-		sum += part;
-		const bool ok = d != xv && slot < nslots;           // search_unit.hpp:855-860 (the values are pairwise distinct)
-		const int key = ok ? __float_as_int(sum) : GB_INT_MAX;
-		if (out && slot < m.max_candidates) out[slot] = ok ? key - GB_F32_BASE_BITS : GB_INT_MAX;
-		commit_value_chunk<32>(s, q, ch, key);
+		const int ka = f32_slot_key<NH, S>(m, s, h, ch * 32 + lane, nslots, out);
+		const int cmin = __reduce_min_sync(0xffffffffu, ka);
+		const unsigned ba = __ballot_sync(0xffffffffu, ka == cmin);
+		if (lane == 0) reinterpret_cast<int2*>(summaries)[ch] = make_int2(cmin, (int)ba);
 	}
+#endif
+	fetch_summary(summaries, nchunks_c, q);
 	// this lane's candidates: its slots below V, minus the selected variable itself
 	return ((m.V - lane + 31) >> 5) - (lane == (v & 31) ? 1 : 0);
 }
 
-template <class WS>
+// Structured grid (DevModel::sg_ok, lower.cpp): chunk g of the candidate loop is group g of the variables (sg_cw of
+// them, lanes beyond idle), so the group constraint U_g is the same for the whole chunk — its {T, a_v} sits in lane
+// g and is broadcast with two shuffles — and the position constraint L_l is the same for lane l in every chunk —
+// its {T, a_v} stays in two registers for the whole loop.  No row load, no gather: per candidate the x load, the
+// hoisted terms and two constraint terms with register operands.  Cells that carry more constraints (the diagonals
+// of a magic square) are skipped here and evaluated afterwards in full (f32_slot_key) by the lane that owns their
+// chunk's summary, which merges them in place.  Tie masks are in (group, lane) coordinates: sg_slot_to_var().
+__device__ __forceinline__ int sg_slot_to_var(const DevModel& m, int slot) { return (slot >> 5) * m.sg_cw + (slot & 31); }
+template <int NH, int S, class WS>
+__device__ inline int evaluate_sg(const DevModel& m, const WS& s, int v, int nh, int bias, int* out, ChunkRegs& q)
+{
+	const int lane = threadIdx.x & 31;
+	const HoistF32<NH> h = load_hoist_f32<NH>(s, v, nh, bias);
+	const unsigned char* cs_bytes = reinterpret_cast<const unsigned char*>(s.cs);
+	const int4 row = __ldg(reinterpret_cast<const int4*>(m.blob + m.o.sg) + lane);
+	const float2 stU = *reinterpret_cast<const float2*>(cs_bytes + row.x);   // {T, a_v} of group `lane`'s constraint
+	const float2 stL = *reinterpret_cast<const float2*>(cs_bytes + row.y);   // {T, a_v} of position `lane`'s constraint
+	const float au = (float)m.sg_au, al = (float)m.sg_al;
+	const unsigned skip = (unsigned)row.z;
+	const int cw = m.sg_cw, G = m.sg_groups;
+	int4* summaries = reinterpret_cast<int4*>(s.val_key);
+	auto cell_key = [&](int ch) -> int {
+		const int u = ch * cw + lane;
+		int d = s.x[u];                                      // padded by two chunks: no clamp
+		asm("" : "+r"(d));
+		const float dx = h.xvo - __int_as_float(0x4B000000 | d);
+		const float TU = __shfl_sync(0xffffffffu, stU.x, ch), aU = __shfl_sync(0xffffffffu, stU.y, ch);
+		float sum = hoisted_sum_f32(h, dx);
+		// as in f32_slot_key: |T - a_v*dx + a_j*dx| - |T - a_v*dx|, a_v = 0 unless the selected variable is in the constraint
+		const float u1 = fmaf(-aU, dx, TU), u2 = fmaf(au, dx, u1);
+		float part = fabsf(u2) - fabsf(u1);
+		const float w1 = fmaf(-stL.y, dx, stL.x), w2 = fmaf(al, dx, w1);
+		part += fabsf(w2) - fabsf(w1);
+		sum += part;
+		const bool cell = !((skip >> ch) & 1u);
+		const bool ok = cell && d != h.xv;
+		const int key = ok ? __float_as_int(sum) : GB_INT_MAX;
+		if (out && cell) out[u] = ok ? key - GB_F32_BASE_BITS : GB_INT_MAX;
+		return key;
+	};
+#pragma unroll 1
+	for (int ch = 0; ch < G; ch += 2) {
+		const int ka = cell_key(ch), kb = cell_key(ch + 1);
+		commit_pair(summaries, ch, ka, kb);
+	}
+	fetch_summary(summaries, G, q);
+	// the irregular cells of group `lane`, one per pass
+	for (int e = 0; e < m.sg_xn; ++e) {
+		const unsigned le = ((unsigned)row.w >> (8 * e)) & 0xFFu;
+		const bool has = le != 0xFFu;
+		const int u = has ? lane * cw + (int)le : 0;
+		const int key = f32_slot_key<NH, S>(m, s, h, u, has ? m.V : 0, has ? out : nullptr);
+		if (key < q.key) { q.key = key; q.bits = 1u << le; }
+		else if (key == q.key && has) q.bits |= 1u << le;
+	}
+	return lane == 0 ? m.V - 1 : 0;
+}
+
+// FS: what the kernel was instantiated for — 0: decided here at run time; 1..4: the plain fp32 loop for packed rows
+// of that length; 11..14: the structured-grid loop (rows of length FS - 10 for its irregular cells).  One
+// instantiation of the search kernel per case keeps the other loop bodies out of its code: the per-iteration path of
+// 24 warps in different phases has to stay inside the SM's instruction cache ("Instruction cache").
+template <int FS, class WS>
 __device__ inline int evaluate_candidates_f32(const DevModel& m, const WS& s, int v, int nh, int bias, int nchunks_c, int* out, ChunkRegs& q)
 {
-	if (nh <= 2) {
+	if (FS > 10) return evaluate_sg<4, (FS > 10 ? FS - 10 : 1)>(m, s, v, nh, bias, out, q);
+	if (FS > 0) {
+#ifdef GB_F32_TWO_NH
+		if (nh <= 2) return evaluate_f32<2, ((FS > 0 && FS < 10) ? FS : 1)>(m, s, v, nh, bias, nchunks_c, out, q);
+#endif
+		return evaluate_f32<4, ((FS > 0 && FS < 10) ? FS : 1)>(m, s, v, nh, bias, nchunks_c, out, q);
+	}
+	if (m.sg_ok) {
 		switch (m.ell_stride) { // warp-uniform
-		case 1: return evaluate_f32<2, 1>(m, s, v, nh, bias, nchunks_c, out, q);
-		case 2: return evaluate_f32<2, 2>(m, s, v, nh, bias, nchunks_c, out, q);
-		case 3: return evaluate_f32<2, 3>(m, s, v, nh, bias, nchunks_c, out, q);
-		default: return evaluate_f32<2, 4>(m, s, v, nh, bias, nchunks_c, out, q);
+		case 1: return evaluate_sg<4, 1>(m, s, v, nh, bias, out, q);
+		case 2: return evaluate_sg<4, 2>(m, s, v, nh, bias, out, q);
+		case 3: return evaluate_sg<4, 3>(m, s, v, nh, bias, out, q);
+		default: return evaluate_sg<4, 4>(m, s, v, nh, bias, out, q);
 		}
 	}
 	switch (m.ell_stride) {
@@ -1156,10 +1332,10 @@ __device__ inline void apply_move_f32(const DevModel& m, const WS& s, int v, int
 	__syncwarp();
 }
 
-template <int T, bool PERM, bool EQ, bool F32 = false, class WS>
+template <int T, bool PERM, bool EQ, bool F32 = false, int FS = 0, class WS>
 __device__ inline int evaluate_candidates(const DevModel& m, const WS& s, int v, int nh, int bias, int nchunks_c, int* out, ChunkRegs& q)
 {
-	if (F32) return evaluate_candidates_f32(m, s, v, nh, bias, nchunks_c, out, q);
+	if (F32) return evaluate_candidates_f32<FS>(m, s, v, nh, bias, nchunks_c, out, q);
 	if (EQ) return evaluate_candidates_eq<T, PERM>(m, s, v, nh, bias, nchunks_c, out, q);
 	typedef Group<T> G;
 	MV mv(m);

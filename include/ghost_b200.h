@@ -178,6 +178,8 @@ int ghost_b200_model_info(const GhostModel* model, int32_t* max_candidates, int6
 #define GHOST_B200_VARIANT_LINEAR_EQ_ONLY 2 /* every live constraint is a LinearEquationEq: no kind dispatch */
 #define GHOST_B200_VARIANT_X16 4           /* assignment stored in 16 bits */
 #define GHOST_B200_VARIANT_F32 8           /* swap deltas evaluated in fp32 on the FMA pipe (exact: all magnitudes < 2^22) */
+#define GHOST_B200_VARIANT_GRID 16         /* ... and the variables form a grid of group / position constraints (rows and
+                                            * columns of a matrix model): their state stays in registers in the candidate loop */
 int ghost_b200_model_variant(const GhostModel* model, int32_t threads_per_walker, int32_t* variant);
 
 /* Fill opts with ghost::Options() defaults (src/options.cpp:36-50) and resolve the -1 ones

@@ -174,6 +174,13 @@ def test_model_variant_bits(monkeypatch):
     m = capi.Model(problems.by_name("n_queens:8"))
     assert m.variant(0) & 8 == 0 and m.variant(0) & 1 == 0
     m.close()
+    m = capi.Model(problems.by_name("magic_square:30"))   # rows and columns: the structured-grid loop
+    assert m.variant(32) == 1 | 2 | 4 | 8 | 16
+    m.close()
+    monkeypatch.setenv("GHOST_B200_NO_SG", "1")
+    m = capi.Model(problems.by_name("magic_square:30"))
+    assert m.variant(32) == 1 | 2 | 4 | 8
+    m.close()
     monkeypatch.setenv("GHOST_B200_NO_F32", "1")
     m = capi.Model(problems.by_name("magic_square:6"))
     assert m.variant(32) == 1 | 2 | 4

@@ -15,21 +15,27 @@ from tests.test_gpu_search import _check_against_oracle
 
 pytestmark = pytest.mark.gpu
 
-F32 = 8
+F32, GRID = 8, 16
 GOLDEN_DIR = os.path.join(os.path.dirname(__file__), "golden")
 
 
-@pytest.fixture(params=["fp32", "int32"])
+@pytest.fixture(params=["default", "fp32", "int32"])
 def path(request, monkeypatch):
+    """default: what the model qualifies for (fp32, and the structured-grid loop for a magic square of order 16..32);
+    fp32: the plain fp32 loop (GHOST_B200_NO_SG); int32: the integer evaluation (GHOST_B200_NO_F32)."""
+    monkeypatch.delenv("GHOST_B200_NO_F32", raising=False)
+    monkeypatch.delenv("GHOST_B200_NO_SG", raising=False)
     if request.param == "int32":
         monkeypatch.setenv("GHOST_B200_NO_F32", "1")
-    else:
-        monkeypatch.delenv("GHOST_B200_NO_F32", raising=False)
+    if request.param == "fp32":
+        monkeypatch.setenv("GHOST_B200_NO_SG", "1")
     return request.param
 
 
-def _variant_is(model, path):
-    assert bool(model.variant(32) & F32) == (path == "fp32"), (path, model.variant(32))
+def _variant_is(model, path, grid=False):
+    v = model.variant(32)
+    assert bool(v & F32) == (path != "int32"), (path, v)
+    assert bool(v & GRID) == (path == "default" and grid), (path, v)
 
 
 @pytest.mark.parametrize("name", ["magic_square_3", "magic_square_6", "magic_square_30", "weighted_perm"])
@@ -38,7 +44,7 @@ def test_both_paths_match_reference_vectors(name, path):
     with open(os.path.join(GOLDEN_DIR, name + ".json")) as f:
         g = json.load(f)
     model = capi.Model(model_by_name(g["model"]))
-    _variant_is(model, path)
+    _variant_is(model, path, grid=name == "magic_square_30")
     xs = np.array([c["x"] for c in g["cases"]], dtype=np.int32)
     sel = np.array([c["var"] for c in g["cases"]], dtype=np.int32)
     got = model.eval_moves(xs, sel)
@@ -49,14 +55,17 @@ def test_both_paths_match_reference_vectors(name, path):
     model.close()
 
 
-@pytest.mark.parametrize("name", ["magic_square:4", "magic_square:7", "magic_square:10", "weighted_perm"])
+@pytest.mark.parametrize("name", ["magic_square:4", "magic_square:7", "magic_square:10", "weighted_perm", "magic_square:16",
+                                  "magic_square:17"])
 def test_both_paths_follow_the_oracle(name, path, oracle_built):
+    """Orders 16 and 17 are grids (an odd order has a centre cell on both diagonals: two further constraints)."""
     from ghost_b200 import capi
     desc = model_by_name(name)
     m = capi.Model(desc)
-    _variant_is(m, path)
+    big = name in ("magic_square:16", "magic_square:17")
+    _variant_is(m, path, grid=big)
     m.close()
-    _check_against_oracle(desc, oracle_built, iterations=800, walkers=16, seed=77)
+    _check_against_oracle(desc, oracle_built, iterations=300 if big else 800, walkers=6 if big else 16, seed=77)
 
 
 def test_every_selected_variable_of_the_benchmark_model(path, oracle_built):
@@ -66,7 +75,7 @@ def test_every_selected_variable_of_the_benchmark_model(path, oracle_built):
     desc = model_by_name("magic_square:30")
     port = oracle_built.OraclePort(desc)
     model = capi.Model(desc)
-    _variant_is(model, path)
+    _variant_is(model, path, grid=True)
     rng = np.random.default_rng(3)
     n = 40
     xs = np.stack([random_assignment(desc, rng) for _ in range(n)])
@@ -92,4 +101,26 @@ def test_duplicate_start_values_keep_the_int32_path():
     m.linear(md.LINEAR_EQ, [0, 1, 2], 9)
     model = capi.Model(m)
     assert not (model.variant(32) & F32)
+    model.close()
+
+
+@pytest.mark.parametrize("order", [16, 21, 32])
+def test_grid_candidate_sums_against_the_oracle(order, path, oracle_built):
+    """Every candidate sum of random (assignment, variable) pairs on grids of several widths: the cells on the
+    diagonals (evaluated by the second loop) and, for an odd order, the centre cell as the selected variable."""
+    from ghost_b200 import capi
+    desc = model_by_name(f"magic_square:{order}")
+    port = oracle_built.OraclePort(desc)
+    model = capi.Model(desc)
+    _variant_is(model, path, grid=True)
+    rng = np.random.default_rng(order)
+    n = 12
+    xs = np.stack([random_assignment(desc, rng) for _ in range(n)])
+    sel = rng.integers(0, desc.num_variables, size=n).astype(np.int32)
+    sel[:3] = [0, order - 1, (order // 2) * order + order // 2]
+    got = model.eval_moves(xs, sel)
+    for w in range(n):
+        want = port.eval_moves(xs[w], int(sel[w]))
+        cd = np.where(np.isnan(want["cand_delta"]), NOT_A_CANDIDATE, np.nan_to_num(want["cand_delta"])).astype(np.int64)
+        assert np.array_equal(got["cand_delta"][w].astype(np.int64), cd), w
     model.close()
