@@ -244,7 +244,7 @@ __device__ inline void initialize_data_structures(const DevModel& m, const Walke
 	r.tabu_base = r.local_moves;
 	r.cur_sat = recompute_all_cold<T, EQ, F32, WS>(m, L, base, true);
 	if (r.best_sat > r.cur_sat) { r.best_sat = r.cur_sat; r.best_pending = 1; }
-	if (m.objective != GHOST_OBJ_NONE) {
+	if (!F32 && m.objective != GHOST_OBJ_NONE) {
 		long long part = 0;
 		for (int v = G::tid(); v < m.V; v += T) part += (long long)mv.obj_coef(v) * s.x[v];
 		r.obj_sum = G::sum64(part, s.red + 16);
@@ -304,7 +304,7 @@ __device__ inline void local_move(const DevModel& m, const WS& s, WalkerRegs& r,
 	r.cur_sat += delta;
 	if (Group<T>::tid() == 0) { s.tabu[scan_pos(m, v)] = (unsigned short)(p.tabu_selected + r.local_moves - r.tabu_base); s.counters[K_MOVES] += 1; }
 	r.must_compute = 1;
-	if (m.objective != GHOST_OBJ_NONE) {
+	if (!F32 && m.objective != GHOST_OBJ_NONE) {
 		if (m.permutation) {
 			int xv = s.x[v], xj = s.x[new_value];
 			r.obj_sum += (long long)mv.obj_coef(v) * (xj - xv) + (long long)mv.obj_coef(new_value) * (xv - xj);
@@ -396,7 +396,8 @@ search_kernel(const __grid_constant__ DevModel m, const __grid_constant__ Walker
 	const WS s = make_ws<WS>(smem_raw + (size_t)local * L.total_bytes, L);
 	const int tid = G::tid();
 	MV mv(m);
-	const bool optimization = m.objective != GHOST_OBJ_NONE;
+	// the fp32 kernels run satisfaction problems only (lower.cpp, f32_ok): their objective bookkeeping is compiled out
+	const bool optimization = F32 ? false : m.objective != GHOST_OBJ_NONE;
 	int* best_x = p.best_x + (size_t)w * m.V;
 	unsigned char* gstate = p.state + (size_t)w * L.persist_bytes;
 	WalkerScalars* gs = p.scalars + w;

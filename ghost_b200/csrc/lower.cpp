@@ -304,7 +304,7 @@ int lower_model(const GhostModelDesc* d, LoweredModel* out, std::string* why)
 	// candidate's sum has at most 4 + 2*4 + 4 terms and is accumulated on top of the constant 1.5*2^23 (its bit
 	// pattern is then the integer sum plus a constant: the arg-min needs no conversion), which needs every partial
 	// sum inside (-2^22, 2^22).
-	bool f32_ok = eq_only && d->permutation_problem && identical && stride <= 4 && min_value >= 0 && max_value <= 65535 && V <= 1024;
+	bool f32_ok = eq_only && d->permutation_problem && identical && ok == GHOST_OBJ_NONE && stride <= 4 && min_value >= 0 && max_value <= 65535 && V <= 1024;
 	if (f32_ok) {
 		const int64_t B = max_T_bound + 2 * max_abs_coef * (max_value - min_value);
 		if (max_abs_coef > 2048 || 16 * B >= (1LL << 22)) f32_ok = false;

@@ -36,7 +36,12 @@ namespace ghost_b200 {
 #endif
 static __device__ GB_OUTLINE uint4 philox4x32_10(uint4 c, uint2 k)
 {
+	// rolled: 20 more executed instructions per call, 55 fewer in the instruction cache (see GB_OUTLINE above)
+#ifndef GB_PHILOX_UNROLLED
+#pragma unroll 1
+#else
 #pragma unroll
+#endif
 	for (int r = 0; r < 10; ++r) {
 		uint32_t hi0 = __umulhi(0xD2511F53u, c.x), lo0 = 0xD2511F53u * c.x;
 		uint32_t hi1 = __umulhi(0xCD9E8D57u, c.z), lo1 = 0xCD9E8D57u * c.z;
@@ -1233,18 +1238,32 @@ __device__ inline int evaluate_sg(const DevModel& m, const WS& s, int v, int nh,
 		if (out && cell) out[u] = ok ? key - GB_F32_BASE_BITS : GB_INT_MAX;
 		return key;
 	};
+#ifdef GB_SG_PAIR   // measured: the pair loop executes fewer instructions and is slower (instruction cache)
 #pragma unroll 1
 	for (int ch = 0; ch < G; ch += 2) {
 		const int ka = cell_key(ch), kb = cell_key(ch + 1);
 		commit_pair(summaries, ch, ka, kb);
 	}
+#else
+#pragma unroll 1
+	for (int ch = 0; ch < G; ++ch) {
+		const int ka = cell_key(ch);
+		const int cmin = __reduce_min_sync(0xffffffffu, ka);
+		const unsigned ba = __ballot_sync(0xffffffffu, ka == cmin);
+		if (lane == 0) reinterpret_cast<int2*>(summaries)[ch] = make_int2(cmin, (int)ba);
+	}
+#endif
 	fetch_summary(summaries, G, q);
 	// the irregular cells of group `lane`, one per pass
 	for (int e = 0; e < m.sg_xn; ++e) {
 		const unsigned le = ((unsigned)row.w >> (8 * e)) & 0xFFu;
 		const bool has = le != 0xFFu;
 		const int u = has ? lane * cw + (int)le : 0;
+#ifdef GB_SG_EXTRA_NH
 		const int key = f32_slot_key<NH, S>(m, s, h, u, has ? m.V : 0, has ? out : nullptr);
+#else
+		const int key = f32_slot_key<NH, S>(m, s, h, u, has ? m.V : 0, has ? out : nullptr);
+#endif
 		if (key < q.key) { q.key = key; q.bits = 1u << le; }
 		else if (key == q.key && has) q.bits |= 1u << le;
 	}
