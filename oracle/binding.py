@@ -71,6 +71,13 @@ def _load_port():
         lib.oracle_resolve_opts.argtypes = [C.c_int32, C.POINTER(GhostSearchOptsStruct)]
         lib.oracle_philox4x32_10.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
         lib.oracle_complete_search.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        lib.oracle_stepper_create.restype = C.c_void_p
+        lib.oracle_stepper_create.argtypes = [C.c_void_p, C.POINTER(GhostSearchOptsStruct), C.c_void_p]
+        lib.oracle_stepper_destroy.argtypes = [C.c_void_p]
+        lib.oracle_stepper_sync.argtypes = [C.c_void_p, C.c_void_p]
+        lib.oracle_stepper_peek.argtypes = [C.c_void_p] + [C.c_void_p] * 8
+        lib.oracle_stepper_step.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.POINTER(OracleTraceRow), C.c_void_p,
+                                            C.c_void_p, C.POINTER(GhostCountersStruct)]
         _port = lib
     return _port
 
@@ -146,6 +153,46 @@ class OraclePort:
                 for r in trace[:min(tl.value, trace_cap)]]
         return dict(best_x=best_x, final_x=final_x, best_sat=bs.value, best_opt=bo.value, counters=k.as_dict(),
                     trace=rows)
+
+
+class OracleStepper:
+    """One oracle walker advanced an iteration at a time with the caller's choices (decision replay against the
+    reference's GHOST_TRACE output; oracle/ghost_oracle.c, oracle_stepper_*)."""
+
+    def __init__(self, port: OraclePort, opts: GhostSearchOptsStruct, x0):
+        self.port, self.lib = port, port.lib
+        x0 = np.ascontiguousarray(x0, dtype=np.int32)
+        self.h = self.lib.oracle_stepper_create(port.h, C.byref(opts), x0.ctypes.data)
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.lib.oracle_stepper_destroy(self.h)
+            self.h = None
+
+    def sync(self, x):
+        x = np.ascontiguousarray(x, dtype=np.int32)
+        self.lib.oracle_stepper_sync(self.h, x.ctypes.data)
+
+    def peek(self):
+        V = self.port.V
+        x = np.zeros(V, dtype=np.int32); cand = np.zeros(V, dtype=np.int32); tabu = np.zeros(2 * V, dtype=np.int32)
+        nc, nt, wr = C.c_int32(0), C.c_int32(0), C.c_int32(0)
+        lm, err = C.c_int64(0), C.c_double(0)
+        self.lib.oracle_stepper_peek(self.h, x.ctypes.data, cand.ctypes.data, C.addressof(nc), tabu.ctypes.data, C.addressof(nt),
+                                     C.addressof(lm), C.addressof(err), C.addressof(wr))
+        return dict(x=x, candidates=cand[:nc.value].tolist(), tabu={int(tabu[2 * i]): int(tabu[2 * i + 1]) for i in range(nt.value)},
+                    local_moves=lm.value, current_sat_error=err.value, would_reset=bool(wr.value))
+
+    def step(self, variable, value, force_on_plateau):
+        row = OracleTraceRow()
+        ties = np.zeros(max(self.port.max_candidates, self.port.V) + 2, dtype=np.int32)
+        nt = C.c_int32(0)
+        k = GhostCountersStruct()
+        rc = self.lib.oracle_stepper_step(self.h, int(variable), int(value), int(force_on_plateau), C.byref(row), ties.ctypes.data,
+                                          C.addressof(nt), C.byref(k))
+        return dict(rc=rc, variable=row.variable, new_value=row.new_value, branch=row.branch, min_conflict=row.min_conflict,
+                    num_candidates=row.num_candidates, current_sat_error=row.current_sat_error, ties=ties[:nt.value].tolist(),
+                    counters=k.as_dict())
 
 
 _ref = None

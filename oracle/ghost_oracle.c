@@ -537,6 +537,16 @@ static void random_permutations(Walker* w, int nb_var)
  * reference does not copy it to final_solution, so final_solution can lag best_sat_error after a
  * restart; here best_x is updated together with best_sat so that the returned assignment always
  * has the returned error. */
+/* Deviation D1.  The reference lowers data.best_sat_error here (search_unit.hpp:180-188)
+ * WITHOUT copying the sample into final_solution; initialize_data_structures (285-293) then finds
+ * best_sat_error == current_sat_error and does not copy either, so after a restart the assignment a
+ * search returns can be an older, worse one than the error it reports (at the first initialisation the
+ * copy of 714-717 hides it).  The CUDA walkers and, by default, this restatement keep the best assignment
+ * in step with the best error.  oracle_set_faithful_d1(1) switches the restatement to the reference's
+ * behaviour so that a test can show the difference (tests/test_distribution.py). */
+static int g_faithful_d1 = 0;
+void oracle_set_faithful_d1(int on) { g_faithful_d1 = on; }
+
 static void set_initial_configuration(Walker* w, int samplings)
 {
 	const OracleModel* m = w->m;
@@ -552,7 +562,7 @@ static void set_initial_configuration(Walker* w, int samplings)
 			best_so_far = current;
 			if (w->best_sat > best_so_far) {
 				w->best_sat = best_so_far;
-				memcpy(w->best_x, w->x, sizeof(int32_t) * m->V); /* D1 */
+				if (!g_faithful_d1) memcpy(w->best_x, w->x, sizeof(int32_t) * m->V); /* D1 */
 			}
 			memcpy(best_values, w->x, sizeof(int32_t) * m->V);
 		}
@@ -892,6 +902,133 @@ void oracle_resolve_opts(int32_t V, GhostSearchOpts* o)
 }
 
 /* SearchUnit::local_search, include/search_unit.hpp:685-1201 */
+/* The choices of one iteration taken from the caller instead of the Philox stream (decision replay
+ * against the reference's own GHOST_TRACE output, tests/test_decision_replay.py): the variable picked
+ * among the candidates (search_unit.hpp:806), the value / swap partner picked among the ties
+ * (adaptive_search_value_heuristic.cpp:80, objective.cpp:100-117) and the plateau coin (547). */
+typedef struct Forced { int32_t variable, value, force_on_plateau; } Forced;
+
+/* ONE pass of the while body of SearchUnit::local_search (include/search_unit.hpp:731-1189).
+ * Returns 0 after an evaluated iteration, 1 after a reset iteration, and with forced choices
+ * -1 if the variable is not in the candidate list, -2 if the value is not among the ties (for a
+ * non-permutation COP: not among the ties of lowest objective cost).  `ties` receives the tie list
+ * (ascending), *nties its length. */
+static int walker_iteration(Walker* w, const Forced* forced, OracleTraceRow* row, int32_t* ties, int32_t* nties_out)
+{
+	const OracleModel* m = w->m;
+	const int optimization = is_optimization(m);
+	++w->k.search_iterations;
+	memset(row, 0, sizeof *row);
+	row->iteration = w->k.search_iterations;
+	if (nties_out) *nties_out = 0;
+
+	if (w->must_compute) compute_variable_candidates(w); /* 749-750 */
+
+	int ntabu = 0; /* 761-763 */
+	for (int v = 0; v < m->V; ++v) if (w->tabu[v] > w->k.local_moves) ++ntabu;
+	if (ntabu >= w->opt.reset_threshold || w->ncand == 0) {
+		reset(w); /* 769-770 */
+		row->variable = -1; row->branch = 0; row->current_sat_error = w->cur_sat;
+		return 1;
+	}
+
+	/* one RNG event per evaluated iteration: word 0 picks the variable (806), word 1 the
+	 * value among ties (adaptive_search_value_heuristic.cpp:80 / objective.cpp:100-101,
+	 * 111-117), word 2 the plateau coin (547) */
+	uint32_t rnd[4];
+	rng_block(&w->rng, w->rng.next_event++, 0, rnd);
+
+	int pick = (int)below(rnd[0], (uint32_t)w->ncand);
+	if (forced) {
+		pick = -1;
+		for (int i = 0; i < w->ncand; ++i) if (w->cand[i] == forced->variable) pick = i;
+		if (pick < 0) { --w->k.search_iterations; return -1; }
+	}
+	int v = w->cand[pick];
+	/* erase, keeping the ascending order of the vector (826-828) */
+	for (int i = pick; i + 1 < w->ncand; ++i) w->cand[i] = w->cand[i + 1];
+	--w->ncand;
+
+	double min_conflict;
+	int32_t ncandidates = 0;
+	int nties = evaluate_candidates(w, v, NULL, ties, &min_conflict, &ncandidates); /* 831-891 */
+	w->k.candidates_evaluated += ncandidates;
+	if (nties_out) *nties_out = nties;
+
+	int new_value;
+	if (nties == 0) new_value = v; /* adaptive_search_value_heuristic.cpp:68-69 */
+	else if (optimization && !m->permutation) new_value = heuristic_value(w, v, ties, nties, rnd[1]);
+	else new_value = ties[below(rnd[1], (uint32_t)nties)];
+	if (forced && nties > 0) {
+		int found = 0;
+		for (int i = 0; i < nties; ++i) if (ties[i] == forced->value) found = 1;
+		if (found && optimization && !m->permutation) {
+			/* Objective::expert_heuristic_value keeps the tied values of lowest cost (objective.cpp:69-109) */
+			const int32_t backup = w->x[v];
+			double best = DBL_MAX, mine;
+			for (int i = 0; i < nties; ++i) { w->x[v] = ties[i]; double c = objective_cost(w); if (c < best) best = c; }
+			w->x[v] = forced->value; mine = objective_cost(w);
+			w->x[v] = backup;
+			if (mine != best) found = 0;
+		}
+		if (!found) return -2;
+		new_value = forced->value;
+	}
+
+	row->variable = v; row->new_value = new_value; row->min_conflict = min_conflict;
+	row->num_candidates = ncandidates;
+
+	int plateau = 0;
+	if (min_conflict < 0.0) { /* 1042-1050 */
+		local_move(w, v, new_value, min_conflict);
+		if (optimization) w->cur_opt = objective_cost(w);
+		row->branch = 1;
+	} else if (min_conflict == 0.0) {
+		if (optimization && w->opt.enable_optimization_guidance) { /* 1061-1135 */
+			double cand_opt = candidate_opt_cost(w, v, new_value);
+			if (w->cur_opt > cand_opt) {
+				local_move(w, v, new_value, min_conflict);
+				w->cur_opt = cand_opt;
+				row->branch = 2;
+			} else if (w->cur_opt == cand_opt) plateau = 1;
+			else {
+				/* local_minimum_management, 565-582 */
+				w->must_compute = 0;
+				if (w->ncand == 0) { w->tabu[v] = w->opt.tabu_time_local_min + (int32_t)w->k.local_moves; ++w->k.local_minimum; row->branch = 5; }
+				else row->branch = 6;
+			}
+		} else plateau = 1; /* 1136-1145 */
+	} else { /* 1147-1163 */
+		w->must_compute = 0;
+		if (w->ncand == 0) { w->tabu[v] = w->opt.tabu_time_local_min + (int32_t)w->k.local_moves; ++w->k.local_minimum; row->branch = 5; }
+		else row->branch = 6;
+	}
+	if (plateau) { /* plateau_management, 545-561 */
+		int force = (int)below(rnd[2], 100u) + 1 <= w->opt.percent_chance_force_trying_on_plateau;
+		if (forced) force = forced->force_on_plateau;
+		if (force) {
+			w->tabu[v] = w->opt.tabu_time_local_min + (int32_t)w->k.local_moves;
+			w->must_compute = 1;
+			++w->k.plateau_force_trying_another_variable;
+			row->branch = 4;
+		} else {
+			local_move(w, v, new_value, 0);
+			++w->k.plateau_moves;
+			row->branch = 3;
+		}
+	}
+
+	if (w->best_sat > w->cur_sat) { /* 1166-1176 */
+		w->best_sat = w->cur_sat;
+		memcpy(w->best_x, w->x, sizeof(int32_t) * m->V);
+	} else if (optimization && w->cur_sat == 0.0 && w->best_opt > w->cur_opt) { /* 1177-1188 */
+		w->best_opt = w->cur_opt;
+		memcpy(w->best_x, w->x, sizeof(int32_t) * m->V);
+	}
+	row->current_sat_error = w->cur_sat;
+	return 0;
+}
+
 int oracle_search(const OracleModel* m, const GhostSearchOpts* opts, uint64_t walker_id,
                   int64_t max_iterations, int32_t* best_x, double* best_sat, double* best_opt,
                   GhostCounters* counters, int32_t* final_x,
@@ -911,93 +1048,8 @@ int oracle_search(const OracleModel* m, const GhostSearchOpts* opts, uint64_t wa
 
 	while (w->k.search_iterations < max_iterations
 	       && (w->best_sat > 0.0 || (w->best_sat == 0.0 && optimization))) { /* 728-730 */
-		++w->k.search_iterations;
-		OracleTraceRow row; memset(&row, 0, sizeof row);
-		row.iteration = w->k.search_iterations;
-
-		if (w->must_compute) compute_variable_candidates(w); /* 749-750 */
-
-		int ntabu = 0; /* 761-763 */
-		for (int v = 0; v < m->V; ++v) if (w->tabu[v] > w->k.local_moves) ++ntabu;
-		if (ntabu >= w->opt.reset_threshold || w->ncand == 0) {
-			reset(w); /* 769-770 */
-			row.variable = -1; row.branch = 0; row.current_sat_error = w->cur_sat;
-			if (trace && ntrace < trace_cap) trace[ntrace] = row;
-			++ntrace;
-			continue;
-		}
-
-		/* one RNG event per evaluated iteration: word 0 picks the variable (806), word 1 the
-		 * value among ties (adaptive_search_value_heuristic.cpp:80 / objective.cpp:100-101,
-		 * 111-117), word 2 the plateau coin (547) */
-		uint32_t rnd[4];
-		rng_block(&w->rng, w->rng.next_event++, 0, rnd);
-
-		int pick = (int)below(rnd[0], (uint32_t)w->ncand);
-		int v = w->cand[pick];
-		/* erase, keeping the ascending order of the vector (826-828) */
-		for (int i = pick; i + 1 < w->ncand; ++i) w->cand[i] = w->cand[i + 1];
-		--w->ncand;
-
-		double min_conflict;
-		int32_t ncandidates = 0;
-		int nties = evaluate_candidates(w, v, NULL, ties, &min_conflict, &ncandidates); /* 831-891 */
-		w->k.candidates_evaluated += ncandidates;
-
-		int new_value;
-		if (nties == 0) new_value = v; /* adaptive_search_value_heuristic.cpp:68-69 */
-		else if (optimization && !m->permutation) new_value = heuristic_value(w, v, ties, nties, rnd[1]);
-		else new_value = ties[below(rnd[1], (uint32_t)nties)];
-
-		row.variable = v; row.new_value = new_value; row.min_conflict = min_conflict;
-		row.num_candidates = ncandidates;
-
-		int plateau = 0;
-		if (min_conflict < 0.0) { /* 1042-1050 */
-			local_move(w, v, new_value, min_conflict);
-			if (optimization) w->cur_opt = objective_cost(w);
-			row.branch = 1;
-		} else if (min_conflict == 0.0) {
-			if (optimization && w->opt.enable_optimization_guidance) { /* 1061-1135 */
-				double cand_opt = candidate_opt_cost(w, v, new_value);
-				if (w->cur_opt > cand_opt) {
-					local_move(w, v, new_value, min_conflict);
-					w->cur_opt = cand_opt;
-					row.branch = 2;
-				} else if (w->cur_opt == cand_opt) plateau = 1;
-				else {
-					/* local_minimum_management, 565-582 */
-					w->must_compute = 0;
-					if (w->ncand == 0) { w->tabu[v] = w->opt.tabu_time_local_min + (int32_t)w->k.local_moves; ++w->k.local_minimum; row.branch = 5; }
-					else row.branch = 6;
-				}
-			} else plateau = 1; /* 1136-1145 */
-		} else { /* 1147-1163 */
-			w->must_compute = 0;
-			if (w->ncand == 0) { w->tabu[v] = w->opt.tabu_time_local_min + (int32_t)w->k.local_moves; ++w->k.local_minimum; row.branch = 5; }
-			else row.branch = 6;
-		}
-		if (plateau) { /* plateau_management, 545-561 */
-			if ((int)below(rnd[2], 100u) + 1 <= w->opt.percent_chance_force_trying_on_plateau) {
-				w->tabu[v] = w->opt.tabu_time_local_min + (int32_t)w->k.local_moves;
-				w->must_compute = 1;
-				++w->k.plateau_force_trying_another_variable;
-				row.branch = 4;
-			} else {
-				local_move(w, v, new_value, 0);
-				++w->k.plateau_moves;
-				row.branch = 3;
-			}
-		}
-
-		if (w->best_sat > w->cur_sat) { /* 1166-1176 */
-			w->best_sat = w->cur_sat;
-			memcpy(w->best_x, w->x, sizeof(int32_t) * m->V);
-		} else if (optimization && w->cur_sat == 0.0 && w->best_opt > w->cur_opt) { /* 1177-1188 */
-			w->best_opt = w->cur_opt;
-			memcpy(w->best_x, w->x, sizeof(int32_t) * m->V);
-		}
-		row.current_sat_error = w->cur_sat;
+		OracleTraceRow row;
+		walker_iteration(w, NULL, &row, ties, NULL);
 		if (trace && ntrace < trace_cap) trace[ntrace] = row;
 		++ntrace;
 	}
@@ -1010,6 +1062,71 @@ int oracle_search(const OracleModel* m, const GhostSearchOpts* opts, uint64_t wa
 	if (trace_len) *trace_len = ntrace;
 	walker_destroy(w);
 	return 0;
+}
+
+/* ---- decision replay: the same iteration, its random choices supplied by the caller ------------
+ * The reference compiled with GHOST_TRACE prints, per iteration, what it saw and what it chose
+ * (include/search_unit.hpp:741-746, 773-779, 808-819, 893-1003, 1042-1164).  A stepper holds one
+ * walker; the test feeds it the reference's choices one iteration at a time and compares what the
+ * restatement sees (candidate variables, tabu list, current error, ties, branch) with what the
+ * reference printed.  After a reset of the reference (whose random perturbation cannot be
+ * reproduced: it draws from std::mt19937) the walker is re-synchronised on the printed assignment. */
+struct OracleStepper { Walker* w; };
+
+OracleStepper* oracle_stepper_create(const OracleModel* m, const GhostSearchOpts* resolved_opts, const int32_t* x0)
+{
+	OracleStepper* s = (OracleStepper*)calloc(1, sizeof *s);
+	Walker* w = walker_create(m, resolved_opts, 0);
+	s->w = w;
+	w->best_sat = DBL_MAX; w->best_opt = DBL_MAX; /* 708-709 */
+	memcpy(w->x, x0, sizeof(int32_t) * m->V);     /* the reference's assignment after its own initial sampling */
+	initialize_data_structures(w);                /* 712 */
+	memcpy(w->best_x, w->x, sizeof(int32_t) * m->V);
+	return s;
+}
+void oracle_stepper_destroy(OracleStepper* s) { if (s) { walker_destroy(s->w); free(s); } }
+
+/* the reference went through reset(): same end state, initialize_data_structures() on its assignment (366) */
+void oracle_stepper_sync(OracleStepper* s, const int32_t* x)
+{
+	memcpy(s->w->x, x, sizeof(int32_t) * s->w->m->V);
+	initialize_data_structures(s->w);
+}
+
+/* What the next iteration starts from: the candidate variables as they are AFTER the recomputation the
+ * iteration would do (749-750), the tabu list (entries with tabu_until > local_moves: [variable,
+ * until] pairs), counters, and whether the iteration would reset (761-771). */
+int oracle_stepper_peek(OracleStepper* s, int32_t* x, int32_t* candidates, int32_t* num_candidates,
+                        int32_t* tabu_pairs, int32_t* num_tabu, int64_t* local_moves, double* current_sat_error,
+                        int32_t* would_reset)
+{
+	Walker* w = s->w;
+	const OracleModel* m = w->m;
+	if (w->must_compute) { compute_variable_candidates(w); w->must_compute = 0; } /* idempotent: the iteration finds the same list */
+	if (x) memcpy(x, w->x, sizeof(int32_t) * m->V);
+	if (candidates) memcpy(candidates, w->cand, sizeof(int32_t) * w->ncand);
+	if (num_candidates) *num_candidates = w->ncand;
+	int nt = 0;
+	for (int v = 0; v < m->V; ++v) if (w->tabu[v] > w->k.local_moves) {
+		if (tabu_pairs) { tabu_pairs[2 * nt] = v; tabu_pairs[2 * nt + 1] = w->tabu[v]; }
+		++nt;
+	}
+	if (num_tabu) *num_tabu = nt;
+	if (local_moves) *local_moves = w->k.local_moves;
+	if (current_sat_error) *current_sat_error = w->cur_sat;
+	if (would_reset) *would_reset = (nt >= w->opt.reset_threshold || w->ncand == 0) ? 1 : 0;
+	return 0;
+}
+
+/* One iteration with the given choices; see walker_iteration for the return value. */
+int oracle_stepper_step(OracleStepper* s, int32_t variable, int32_t value, int32_t force_on_plateau,
+                        OracleTraceRow* row, int32_t* ties, int32_t* num_ties, GhostCounters* counters)
+{
+	Forced f; f.variable = variable; f.value = value; f.force_on_plateau = force_on_plateau;
+	OracleTraceRow local;
+	int rc = walker_iteration(s->w, &f, row ? row : &local, ties ? ties : s->w->scratch_b, num_ties);
+	if (counters) *counters = s->w->k;
+	return rc;
 }
 
 /* ==========================================================================================

@@ -64,6 +64,23 @@ int oracle_search(const OracleModel* m, const GhostSearchOpts* opts, uint64_t wa
                   GhostCounters* counters, int32_t* final_x,
                   OracleTraceRow* trace, int64_t trace_cap, int64_t* trace_len);
 
+/* Decision replay against the reference's own GHOST_TRACE output (tests/test_decision_replay.py):
+ * one walker advanced one iteration at a time, the three random choices of the iteration (picked
+ * variable, picked value / swap partner, plateau coin) supplied by the caller; see ghost_oracle.c. */
+typedef struct OracleStepper OracleStepper;
+OracleStepper* oracle_stepper_create(const OracleModel* m, const GhostSearchOpts* resolved_opts, const int32_t* x0);
+void oracle_stepper_destroy(OracleStepper* s);
+void oracle_stepper_sync(OracleStepper* s, const int32_t* x);
+int oracle_stepper_peek(OracleStepper* s, int32_t* x, int32_t* candidates, int32_t* num_candidates,
+                        int32_t* tabu_pairs, int32_t* num_tabu, int64_t* local_moves, double* current_sat_error,
+                        int32_t* would_reset);
+int oracle_stepper_step(OracleStepper* s, int32_t variable, int32_t value, int32_t force_on_plateau,
+                        OracleTraceRow* row, int32_t* ties, int32_t* num_ties, GhostCounters* counters);
+
+/* 1: reproduce the reference's handling of the best assignment during (re)start sampling, which the product
+ * deliberately does not follow (deviation D1, see ghost_oracle.c); 0 (default): best assignment follows best error. */
+void oracle_set_faithful_d1(int on);
+
 /* Σ error() of an assignment (the reference's constraint checker, src/constraint.cpp:57) and the
  * objective cost (sign as the user sees it). */
 int oracle_check(const OracleModel* m, const int32_t* x, double* sat_error, double* objective);
