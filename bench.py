@@ -32,11 +32,60 @@ if ROOT not in sys.path:
 WORKLOAD = "magic_square:30"
 METRIC = "candidate_move_evals_per_sec"
 UNIT = "evals/s"
-# SURVEY.md §8d, algorithmic work of one magic-square swap candidate: the shared AllDifferent
-# (delta 0: 1 op), four LinearEquationEq sides (row+column of the selected variable and of the
-# partner: 5 ops each, the partner's two gather 20 B each), accumulate + argmin (#constraints + 2).
-OPS_PER_EVAL = 28.0
-SMEM_BYTES_PER_EVAL = 44.0
+def algorithmic_work(desc):
+    """algorithmic lane-ops and shared-memory bytes of ONE candidate evaluation of this model, averaged
+    over (selected variable, candidate) pairs with every variable equally likely to be selected.  Per constraint touching
+    the candidate: AllDifferent single change 3 ops / 4 B, AllDifferent (or AllEqual) with both swapped variables in
+    scope 1 op / 0 B, a linear kind on the selected variable's side 5 ops / 0 B (its invariants are hoisted), on the
+    partner's side 5 ops / 20 B, FixValue 3 ops; plus one accumulate per constraint, 2 ops for the arg-min and 4 B for
+    the candidate's value.  The abs-difference extension kind is charged like an AllDifferent per touched difference
+    (2).  magic_square:30 -> 28.5 ops, 44 B; n_queens:100 -> 13.2 ops, 8 B; a knapsack with m rows -> 6m + 2 ops, 4 B."""
+    import numpy as np
+    V = desc.num_variables
+    rows = [[] for _ in range(V)]
+    for c, (kind, vs, _, _) in enumerate(desc.constraints):
+        for v in vs:
+            rows[v].append((c, kind, len(vs)))
+    linear = {1, 2, 3, 4, 5, 6}
+
+    def side(kind, partner):
+        if kind in linear:
+            return (5, 20 if partner else 0)
+        if kind in (0, 10):
+            return (3, 4)
+        if kind == 7:
+            return (3, 0)
+        if kind == 9:
+            return (6, 8)
+        return (0, 0)
+
+    ops_total = bytes_total = pairs = 0.0
+    if not desc.permutation_problem:
+        for v in range(V):
+            n = len(desc.domains[v]) - 1
+            o = sum(side(k, False)[0] for _, k, _ in rows[v]) + len(rows[v]) + 2
+            b = sum(side(k, False)[1] for _, k, _ in rows[v]) + 4
+            ops_total += n * o; bytes_total += n * b; pairs += n
+        return ops_total / max(pairs, 1), bytes_total / max(pairs, 1)
+    # permutation: every other variable is a partner; a constraint holding both is evaluated once, as a two-variable change
+    member = [set(c for c, _, _ in r) for r in rows]
+    own = [(sum(side(k, False)[0] + 1 for _, k, _ in r), sum(side(k, False)[1] for _, k, _ in r)) for r in rows]
+    par = [(sum(side(k, True)[0] + 1 for _, k, _ in r), sum(side(k, True)[1] for _, k, _ in r)) for r in rows]
+    sample = range(V) if V <= 256 else np.random.default_rng(0).choice(V, 256, replace=False)
+    for v in sample:
+        for j in range(V):
+            if j == v:
+                continue
+            o, b = own[v][0] + par[j][0] + 2, own[v][1] + par[j][1] + 4
+            for c, k, _ in rows[j]:
+                if c in member[v]:   # shared: not a partner-side gather, and an AllDifferent / AllEqual swap inside is delta 0
+                    so, sb = side(k, True)
+                    o -= so + 1; b -= sb
+                    if k in (0, 10):
+                        o -= side(k, False)[0] - 1
+                        b -= side(k, False)[1]
+            ops_total += o; bytes_total += b; pairs += 1
+    return ops_total / max(pairs, 1), bytes_total / max(pairs, 1)
 
 
 def physical_cores():
@@ -178,6 +227,7 @@ def main():
     ap.add_argument("--ref-budget", type=float, default=60.0, help="cap on the reference arm's total CPU time")
     ap.add_argument("--cpu-seconds", type=float, default=10.0)
     ap.add_argument("--e2e-seconds", type=float, default=1.0)
+    ap.add_argument("--e2e-calls", type=int, default=5)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--tts-seeds", type=int, default=21, help="time-to-solution runs (0: skip)")
     ap.add_argument("--tts-timeout", type=float, default=10.0)
@@ -296,13 +346,15 @@ def main():
 
     # ---- roofline of the search kernel (the only kernel of a step): measured denominators
     issue_peak, smem_peak = capi.microbench()
+    OPS_PER_EVAL, SMEM_BYTES_PER_EVAL = algorithmic_work(desc)
     evals_rank = evals_rank / (ms_rank * 1e-3)
     persist = None
     roofline = {
         "bound": "issue", "kernel": f"search_kernel<{res0['threads_per_walker']}>",
         "achieved": evals_rank * OPS_PER_EVAL / 1e12, "peak": issue_peak / 1e12, "unit": "Tlane-op/s",
         "frac": evals_rank * OPS_PER_EVAL / issue_peak,
-        "peak_source": "ghost_b200_microbench (IMAD/IADD3/LOP3 chains, measured in this run)",
+        "peak_source": "ghost_b200_microbench (IMAD/IADD3/LOP3 chains, measured in this run); theoretical "
+                       "148 SM x 128 lanes x 1.965 GHz = 37.2",
         "algorithmic_ops_per_eval": OPS_PER_EVAL,
         "smem": {"achieved": evals_rank * SMEM_BYTES_PER_EVAL / 1e9, "peak": smem_peak / 1e9, "unit": "GB/s",
                  "frac": evals_rank * SMEM_BYTES_PER_EVAL / smem_peak, "algorithmic_bytes_per_eval": SMEM_BYTES_PER_EVAL},
@@ -310,8 +362,8 @@ def main():
     }
     try:
         # dram__bytes_read.sum + dram__bytes_write.sum of one `ncu --set full` capture of this kernel on this
-        # workload (profiles/r1_search_kernel_ncu.txt); per launch
-        tr = json.load(open(os.path.join(ROOT, "profiles", "r1_traffic.json")))
+        # workload (profiles/r2_search_kernel_ncu.txt); per launch
+        tr = json.load(open(os.path.join(ROOT, "profiles", "r2_traffic.json")))
         if args.workload == tr.get("workload") and W == tr.get("walkers") and args.epoch == tr.get("epoch_iterations"):
             roofline["traffic"] = tr["dram_bytes_per_launch"]
             roofline["traffic_source"] = tr["source"]
@@ -343,21 +395,34 @@ def main():
         e2e_model_bytes = 0
         runs = []
         e2e_devices = world if torch.cuda.device_count() >= world else 1
-        for rep_i in range(3):   # median of three calls: one slow host-side hiccup must not decide the number
+        cold = None
+        if e2e_devices > 1:
+            # the first search_devices call of a process creates the CUDA contexts of the other devices (seconds): it is
+            # reported on its own, not mixed into the figure
+            o0 = default_opts(seed=6, number_walkers=W, threads_per_walker=args.threads_per_walker, stop_on_first_solution=0,
+                              timeout_us=0.05e6, epoch_iterations=args.epoch)
+            t0 = time.perf_counter()
+            capi.search_devices(desc, o0, e2e_devices)
+            cold = time.perf_counter() - t0
+        for rep_i in range(args.e2e_calls):
             o2 = default_opts(seed=7 + rep_i, number_walkers=W, threads_per_walker=args.threads_per_walker, stop_on_first_solution=0,
                               timeout_us=args.e2e_seconds * 1e6, epoch_iterations=args.epoch)
             t0 = time.perf_counter()
             if e2e_devices > 1:
                 # the job's N GPUs through the one-call API: rank 0 drives them all, the other ranks are idle by now
                 r2 = capi.search_devices(desc, o2, e2e_devices)
+                phases = None
+                t_model = 0.0
             else:
                 m2 = capi.Model(desc)
+                t_model = time.perf_counter() - t0
                 r2 = m2.search(o2)
+                phases = capi.search_phases()
                 m2.close()
             dt = time.perf_counter() - t0
-            runs.append((r2["total"]["candidates_evaluated"] / dt, dt, r2))
+            runs.append((r2["total"]["candidates_evaluated"] / dt, dt, r2, phases, t_model))
         runs.sort(key=lambda t: t[0])
-        _, dt, r2 = runs[1]
+        _, dt, r2, phases, t_model = runs[len(runs) // 2]
         a = desc.arrays()
         e2e_model_bytes = int(sum(v.nbytes for v in a.values() if hasattr(v, "nbytes")))
         e2e_model_bytes *= e2e_devices
@@ -366,8 +431,16 @@ def main():
                        "h2d_bytes_per_step": e2e_model_bytes, "d2h_bytes_per_step": d2h,
                        "call": ("ghost_b200_search" if e2e_devices == 1 else f"ghost_b200_search_devices over {e2e_devices} GPUs") +
                                " (model_create + upload + walker set-up + search + result)", "gpus": e2e_devices,
-                       "seconds": dt, "kernel_launches": r2["kernel_launches"], "runs": [round(t[0], 1) for t in runs],
-                       "note": "median of 3 calls"}
+                       "seconds": dt, "budget_s": args.e2e_seconds, "kernel_launches": r2["kernel_launches"],
+                       "runs": [round(t[0], 1) for t in runs], "run_seconds": [round(t[1], 4) for t in runs],
+                       "min": runs[0][0], "median": runs[len(runs) // 2][0], "max": runs[-1][0],
+                       "note": f"median of {len(runs)} calls"}
+        if phases is not None:
+            line["e2e"]["phases_ms"] = {"python_model_create": round(1e3 * t_model, 3), "search_begin": round(phases[0], 3),
+                                        "epochs": round(phases[1], 3), "result": round(phases[2], 3), "search_end": round(phases[3], 3),
+                                        "kernels": round(r2["kernel_time_us"] / 1e3, 3)}
+        if cold is not None:
+            line["e2e"]["cold_first_call_s"] = round(cold, 3)
         # ---- time-to-solution (the third part of BASELINE.json's metric): wall time of the blocking call
         # from host descriptor to the first walker with satisfaction error 0, median over seeds
         if world == 1 and args.tts_seeds > 0:

@@ -49,6 +49,8 @@ def _load():
     lib.ghost_b200_eval_moves.argtypes = [vp, i32, vp, vp, vp, vp, vp]
     lib.ghost_b200_eval_moves_device.argtypes = [vp, i32, vp, vp, vp, vp, vp, vp]
     lib.ghost_b200_search.argtypes = [vp, C.POINTER(GhostSearchOptsStruct), C.POINTER(GhostResultStruct)]
+    lib.ghost_b200_search_phases.argtypes = [C.POINTER(C.c_double)] * 4
+    lib.ghost_b200_search_phases.restype = None
     lib.ghost_b200_search_begin.argtypes = [vp, C.POINTER(GhostSearchOptsStruct), C.POINTER(vp)]
     lib.ghost_b200_search_epoch.argtypes = [vp, i32, vp]
     lib.ghost_b200_search_best_key.argtypes = [vp, C.POINTER(C.c_uint64)]
@@ -87,6 +89,13 @@ def _check(rc):
 
 def version():
     return lib.ghost_b200_version().decode()
+
+
+def search_phases():
+    """Host milliseconds of the last ghost_b200_search() of this thread: (begin, epochs, result, end)."""
+    v = [C.c_double() for _ in range(4)]
+    lib.ghost_b200_search_phases(*[C.byref(x) for x in v])
+    return tuple(x.value for x in v)
 
 
 def microbench():

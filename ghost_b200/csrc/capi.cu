@@ -501,6 +501,25 @@ extern "C" int ghost_b200_search_trace(GhostSearch* s, int32_t* rows, int32_t ca
 	return GHOST_B200_OK;
 }
 
+// Launch length of a timeout-driven search.  The reference tests the clock in every iteration
+// (search_unit.hpp:728-730) and is used with budgets from 500 us up; here the clock is read between launches, so the
+// first launches are short (16 iterations) and the length then doubles while one launch stays below half of what is
+// left of the budget (capped by opts.epoch_iterations when the caller gave one, else 4096).
+static int next_epoch_length(int epoch, int cap, double remaining_ms, double ms_per_iteration)
+{
+	const int fit = (int)std::max(1.0, std::min((double)cap, 0.5 * remaining_ms / ms_per_iteration));
+	return std::min(std::min(std::max(fit, 1), std::max(epoch * 2, 16)), cap);
+}
+
+static thread_local double g_phase_ms[4] = { 0, 0, 0, 0 };
+extern "C" void ghost_b200_search_phases(double* begin_ms, double* epochs_ms, double* result_ms, double* end_ms)
+{
+	if (begin_ms) *begin_ms = g_phase_ms[0];
+	if (epochs_ms) *epochs_ms = g_phase_ms[1];
+	if (result_ms) *result_ms = g_phase_ms[2];
+	if (end_ms) *end_ms = g_phase_ms[3];
+}
+
 extern "C" int ghost_b200_search(GhostModel* gm, const GhostSearchOpts* opts, GhostResult* res)
 {
 	if (!gm || !opts || !res) return set_error(GHOST_B200_ERR_INVALID, "null argument to search");
@@ -512,8 +531,9 @@ extern "C" int ghost_b200_search(GhostModel* gm, const GhostSearchOpts* opts, Gh
 	if (opts->elastic_epochs == 0 && opts->timeout_us > 0 && opts->max_iterations <= 0) s->elastic = 1; // auto, see the header
 	const auto tp1 = std::chrono::steady_clock::now();
 	const bool optimization = gm->low.dev.objective != GHOST_OBJ_NONE;
-	int epoch = s->opts.epoch_iterations > 0 ? s->opts.epoch_iterations : 256;
 	const double budget_us = s->opts.timeout_us;
+	const int cap = s->opts.epoch_iterations > 0 ? s->opts.epoch_iterations : (budget_us > 0 ? 4096 : 256);
+	int epoch = budget_us > 0 ? std::min(16, cap) : cap;
 	int64_t done_iterations = 0;
 	for (;;) {
 		cudaEventRecord(s->ev0, nullptr);
@@ -536,23 +556,17 @@ extern "C" int ghost_b200_search(GhostModel* gm, const GhostSearchOpts* opts, Gh
 		if (budget_us > 0 && elapsed >= budget_us) break;
 		if (s->opts.max_iterations > 0 && done_iterations >= s->opts.max_iterations) break;
 		if (budget_us <= 0 && s->opts.max_iterations <= 0) break; // nothing bounds the search: one epoch
-		// adapt the epoch so that one launch stays well below the remaining budget
-		if (budget_us > 0 && ms > 0.f) {
-			double remaining_ms = (budget_us - elapsed) / 1000.0;
-			double per_it = ms / epoch;
-			int fit = (int)std::max(1.0, std::min(4096.0, 0.5 * remaining_ms / per_it));
-			epoch = std::min(std::max(fit, 1), std::max(epoch * 2, 16));
-		}
+		// (the first launch also carries the initial sampling: its per-iteration time is an overestimate, which errs short)
+		if (budget_us > 0 && ms > 0.f) epoch = next_epoch_length(epoch, cap, (budget_us - elapsed) / 1000.0, ms / epoch);
 	}
 	const auto tp2 = std::chrono::steady_clock::now();
 	rc = ghost_b200_search_result(s, res);
 	const auto tp3 = std::chrono::steady_clock::now();
 	ghost_b200_search_end(s);
-	if (timing) {
-		auto ms = [](std::chrono::steady_clock::time_point a, std::chrono::steady_clock::time_point b) { return std::chrono::duration<double, std::milli>(b - a).count(); };
-		std::fprintf(stderr, "ghost_b200_search: begin %.2f ms, epochs %.2f ms, result %.2f ms, end %.2f ms\n", ms(tp0, tp1), ms(tp1, tp2), ms(tp2, tp3),
-		             ms(tp3, std::chrono::steady_clock::now()));
-	}
+	auto msf = [](std::chrono::steady_clock::time_point a, std::chrono::steady_clock::time_point b) { return std::chrono::duration<double, std::milli>(b - a).count(); };
+	g_phase_ms[0] = msf(tp0, tp1); g_phase_ms[1] = msf(tp1, tp2); g_phase_ms[2] = msf(tp2, tp3); g_phase_ms[3] = msf(tp3, std::chrono::steady_clock::now());
+	if (timing)
+		std::fprintf(stderr, "ghost_b200_search: begin %.2f ms, epochs %.2f ms, result %.2f ms, end %.2f ms\n", g_phase_ms[0], g_phase_ms[1], g_phase_ms[2], g_phase_ms[3]);
 	return rc;
 }
 
@@ -618,8 +632,9 @@ extern "C" int ghost_b200_search_devices(const GhostModelDesc* desc, const Ghost
 		}
 	}
 	const bool optimization = gm[0]->low.dev.objective != GHOST_OBJ_NONE;
-	int epoch = ss[0]->opts.epoch_iterations > 0 ? ss[0]->opts.epoch_iterations : 256;
 	const double budget_us = ss[0]->opts.timeout_us;
+	const int cap = ss[0]->opts.epoch_iterations > 0 ? ss[0]->opts.epoch_iterations : (budget_us > 0 ? 4096 : 256);
+	int epoch = budget_us > 0 ? std::min(16, cap) : cap;
 	int64_t done_iterations = 0, launches = 0;
 	double kernel_ms = 0.0;
 	std::vector<uint64_t> key(n, ~0ull);
@@ -649,11 +664,7 @@ extern "C" int ghost_b200_search_devices(const GhostModelDesc* desc, const Ghost
 		if (budget_us > 0 && elapsed >= budget_us) break;
 		if (opts->max_iterations > 0 && done_iterations >= opts->max_iterations) break;
 		if (budget_us <= 0 && opts->max_iterations <= 0) break;
-		if (budget_us > 0 && slowest > 0.f) {
-			const double remaining_ms = (budget_us - elapsed) / 1000.0, per_it = slowest / epoch;
-			const int fit = (int)std::max(1.0, std::min(4096.0, 0.5 * remaining_ms / per_it));
-			epoch = std::min(std::max(fit, 1), std::max(epoch * 2, 16));
-		}
+		if (budget_us > 0 && slowest > 0.f) epoch = next_epoch_length(epoch, cap, (budget_us - elapsed) / 1000.0, slowest / epoch);
 	}
 	// the winner: lowest quality, lowest device among equals (solver.hpp:665-723 picks the first best thread)
 	int win = 0;

@@ -13,6 +13,7 @@
 #include "lowered.h"
 
 #include <algorithm>
+#include <atomic>
 #include <cmath>
 #include <cstdlib>
 #include <cstring>
@@ -41,7 +42,9 @@ int lower_model(const GhostModelDesc* d, LoweredModel* out, std::string* why)
 	const int V = d->num_variables, C = d->num_constraints;
 	if (V <= 0) return fail(GHOST_B200_ERR_INVALID, "model has no variable");
 	if (C <= 0) return fail(GHOST_B200_ERR_INVALID, "model has no constraint (pass one PURE_OPTIMIZATION constraint, as ModelBuilder::build_model does)");
-	if (V > 65535 * 32) return fail(GHOST_B200_ERR_UNSUPPORTED, "too many variables");
+	// size limits of the packed tables, checked before anything is built
+	if (V > 65535) return fail(GHOST_B200_ERR_UNSUPPORTED, "more than 65535 variables (scope lists are stored as 16-bit positions)");
+	if (C >= GB_ELL_END) return fail(GHOST_B200_ERR_UNSUPPORTED, "too many constraints (20-bit constraint ids in the row tables)");
 	if (!d->dom_offset || !d->dom_values || !d->start_value || !d->ctr_kind || !d->ctr_offset || !d->ctr_vars)
 		return fail(GHOST_B200_ERR_INVALID, "null array in descriptor");
 	if (d->dom_offset[0] != 0 || d->ctr_offset[0] != 0) return fail(GHOST_B200_ERR_INVALID, "offset arrays must start at 0");
@@ -207,6 +210,8 @@ int lower_model(const GhostModelDesc* d, LoweredModel* out, std::string* why)
 	// ---- blob
 	LoweredModel& L = *out;
 	L = LoweredModel();
+	static std::atomic<uint64_t> next_uid{1};
+	L.uid = next_uid.fetch_add(1);
 	L.V = V; L.C = C;
 	L.desc.dom_off.assign(d->dom_offset, d->dom_offset + V + 1);
 	L.desc.dom_val.assign(d->dom_values, d->dom_values + d->dom_offset[V]);
@@ -277,7 +282,6 @@ int lower_model(const GhostModelDesc* d, LoweredModel* out, std::string* why)
 			ell[(static_cast<size_t>(v) * stride + k) * 2 + 1] = w1;
 		}
 	}
-	if (C >= GB_ELL_END) return fail(GHOST_B200_ERR_UNSUPPORTED, "too many constraints");
 	o.ell = put(ell);
 	// Packed rows of the LinearEq-only paths: 16-bit state offset + 16-bit coefficient per entry, a whole
 	// row in one aligned load.  The table (4 B x stride x V) is what the candidate loop streams through
@@ -346,7 +350,6 @@ int lower_model(const GhostModelDesc* d, LoweredModel* out, std::string* why)
 			uint32_t pos = v < v128 ? static_cast<uint32_t>((v & ~127) | ((v & 31) << 2) | ((v >> 5) & 3)) : static_cast<uint32_t>(v);
 			packed[i / 2] |= static_cast<int32_t>(pos << ((i & 1) * 16));
 		}
-		if (V > 65535) return fail(GHOST_B200_ERR_UNSUPPORTED, "more than 65535 variables");
 		o.c2v_pos = put(packed);
 	}
 	o.has_ctr = put(has_ctr);

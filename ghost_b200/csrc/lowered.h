@@ -139,6 +139,7 @@ struct LoweredModel {
 	int V = 0, C = 0;
 	std::vector<int32_t> start;
 	int64_t error_bound = 0;    // upper bound of the total satisfaction error (must fit int32)
+	uint64_t uid = 0;           // unique per lowering in this process (what a device-side copy of the blob is tagged with)
 	WalkerLayout layout(int threads_per_walker, int nreset) const;
 	int default_threads_per_walker() const;
 	int effective_threads_per_walker(int requested) const;

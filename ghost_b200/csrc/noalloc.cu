@@ -39,12 +39,10 @@ std::mutex g_setup_mutex;
 unsigned char* g_scratch_addr[kMaxDevices] = {};   // device address of g_noalloc_scratch, per device
 int g_sm_count[kMaxDevices] = {};
 int g_smem_optin[kMaxDevices] = {};
-
-thread_local std::string g_noalloc_error;
+uint64_t g_blob_uid[kMaxDevices] = {};             // LoweredModel::uid of the model blob the array holds (0: none)
 
 int fail(int code, const std::string& msg)
 {
-	g_noalloc_error = msg;
 	ghost_b200_internal_set_error(code, msg.c_str());
 	return code;
 }
@@ -162,8 +160,20 @@ extern "C" int ghost_b200_search_noalloc(GhostModel* model, const GhostSearchOpt
 		            " (use fewer walkers, or ghost_b200_search_begin which allocates)");
 
 	cudaStream_t st = static_cast<cudaStream_t>(stream);
-	cudaError_t e = cudaMemcpyAsync(base, low->blob.data(), blob_bytes, cudaMemcpyHostToDevice, st);
-	if (e != cudaSuccess) return fail(GHOST_B200_ERR_CUDA, std::string("cudaMemcpyAsync(model): ") + cudaGetErrorString(e));
+	cudaError_t e = cudaSuccess;
+	{
+		// The lowered model goes to the head of the array ONCE per (model, device): the host copy is ordinary
+		// pageable memory, and a copy from pageable memory is staged by the runtime — it waits for the work
+		// already queued on the stream and returns only when the source has been read.  Calls that find their
+		// model already in place (the per-frame case: same model, new options / seed) queue kernels only.
+		std::lock_guard<std::mutex> lock(g_setup_mutex);
+		if (g_blob_uid[dev] != low->uid) {
+			g_blob_uid[dev] = 0;
+			e = cudaMemcpyAsync(base, low->blob.data(), blob_bytes, cudaMemcpyHostToDevice, st);
+			if (e != cudaSuccess) return fail(GHOST_B200_ERR_CUDA, std::string("cudaMemcpyAsync(model): ") + cudaGetErrorString(e));
+			g_blob_uid[dev] = low->uid;
+		}
+	}
 
 	DevModel m = low->dev;
 	m.blob = reinterpret_cast<const int32_t*>(base);

@@ -93,6 +93,12 @@ def search_multi(search, coord: Coordinator, optimization: bool, epoch_iteration
     """Epoch loop over any object with .epoch(n), .best_key() and .result() (ghost_b200.capi.Search on
     a GPU; a stub in the CPU tests).  Returns (found, winner_rank, best_quality, solution, epochs)."""
     coord.share_stop_flag(search)
+    # Nothing bounds the search of a COP (or of a CSP whose first solution does not stop it) without a timeout or an
+    # epoch cap: one epoch then, as ghost_b200_search does (capi.cu, "nothing bounds the search"), instead of every
+    # rank spinning for ever.  A CSP that stops at its first solution keeps running: that is the reference's own
+    # behaviour with an infinite timeout.
+    if timeout_us <= 0 and not max_epochs and (optimization or not stop_on_first_solution):
+        max_epochs = 1
     t0 = time.perf_counter()
     epochs = 0
     quality, winner = INT64_MAX >> KEY_WALKER_BITS, 0

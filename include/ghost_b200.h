@@ -114,7 +114,10 @@ typedef struct GhostSearchOpts {
 	/* additions */
 	int32_t number_walkers;       /* parallel restarts on this GPU; <=0: fill the GPU          */
 	int32_t threads_per_walker;   /* 0 = choose from the model; else 32, 64, 128 or 256       */
-	int32_t epoch_iterations;     /* iterations per walker per kernel launch; <=0: default     */
+	int32_t epoch_iterations;     /* iterations per walker per kernel launch; <=0: default.  In the timeout-driven    */
+	                              /* blocking calls this is the LONGEST launch: they start at 16 iterations and      */
+	                              /* double while a launch stays below half of the remaining budget (the clock of    */
+	                              /* search_unit.hpp:729 is read between launches)                                   */
 	int32_t stop_on_first_solution; /* CSP: stop all walkers once one has sat error 0           */
 	uint64_t seed;                /* Philox key                                                */
 	uint64_t first_walker_id;     /* global id of this GPU's walker 0 (multi-GPU sharding)     */
@@ -213,6 +216,10 @@ int ghost_b200_eval_moves_device(GhostModel* model, int32_t num_walkers,
 /* Blocking search on the current device: what Solver::fast_search calls instead of spawning
  * SearchUnits (include/solver.hpp:517-524, 552-587). */
 int ghost_b200_search(GhostModel* model, const GhostSearchOpts* opts, GhostResult* result);
+/* Host wall time of the four phases of the calling thread's last ghost_b200_search(): walker-pool set-up (allocation,
+ * model upload), the launches with their clock tests, the result read-back, the release.  A diagnostic with no
+ * counterpart in the reference (bench.py reports it next to its end-to-end figure). */
+void ghost_b200_search_phases(double* begin_ms, double* epochs_ms, double* result_ms, double* end_ms);
 
 /* The same blocking search over `device_count` GPUs of this process (devices 0..device_count-1;
  * 0 = every visible device): what Options::parallel_runs is to threads (include/solver.hpp:548-587,
@@ -304,8 +311,14 @@ void ghost_b200_solutions_destroy(GhostSolutionSet* set);
  * epochs of how many iterations to run, and two DEVICE output buffers it owns:
  *   d_best_x  [number_walkers][V] int32 — each walker's best assignment;
  *   d_summary [number_walkers]          — best errors and counters of each walker (may be NULL).
- * The work is queued on `stream` (a cudaStream_t passed as void*) and the call returns without
- * synchronising; read the outputs after synchronising that stream.
+ * The work is queued on `stream` (a cudaStream_t passed as void*); read the outputs after synchronising
+ * that stream.  The first call with a given model on a device also copies the lowered model into the
+ * array: that copy comes from ordinary (pageable) host memory, so the call waits for the work already
+ * queued on `stream` and returns once the copy has been staged.  Later calls with the same model (new
+ * options, new seed: the per-frame case) find it in place, queue kernels only and return at once; a
+ * call with another model replaces it.
+ * Every epoch runs exactly iterations_per_epoch iterations per walker: opts->elastic_epochs and the
+ * GHOST_B200_TRACE diagnostic of ghost_b200_search_begin() have no effect here.
  *
  * Limits and sharing:
  *  - the built-in array is GHOST_B200_NOALLOC_SCRATCH_BYTES on every GPU that loads the library,

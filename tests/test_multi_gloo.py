@@ -64,6 +64,11 @@ def _worker(rank, world, port, scenario, out_dir):
         keys = [[_key(unsolved, 0)] * 3, [_key((1 << 37) - 500, 4), _key((1 << 37) - 900, 4), _key((1 << 37) - 900, 4)]][rank]
         found, winner, q, solution, epochs = multi.search_multi(StubSearch(keys, np.full(2, 7 * rank, dtype=np.int32)), coord, True, 5, 0.0, max_epochs=3)
         res = dict(found=found, winner=winner, q=q, solution=solution.tolist(), epochs=epochs)
+    elif scenario == "unbounded":
+        # a COP with neither a timeout nor an epoch cap: one epoch, not an endless loop (capi.cu applies the same rule)
+        keys = [[_key((1 << 37) - 5, 1)] * 4, [_key((1 << 37) - 6, 2)] * 4][rank]
+        found, winner, q, solution, epochs = multi.search_multi(StubSearch(keys, np.full(2, rank, dtype=np.int32)), coord, True, 5, 0.0)
+        res = dict(found=found, winner=winner, epochs=epochs)
     elif scenario == "misc":
         res = dict(first=coord.first_walker_id(4096),
                    total=coord.sum_counters({"search_iterations": 10 * (rank + 1), "candidates_evaluated": 1000 + rank}),
@@ -94,6 +99,11 @@ def test_cop_runs_to_the_budget_and_keeps_the_best_cost(tmp_path):
     r0, r1 = _run("cop", tmp_path)
     assert r0 == r1 and r0["found"] and r0["winner"] == 1 and r0["epochs"] == 3
     assert r0["q"] == (1 << 37) - 900 and r0["solution"] == [7, 7]
+
+
+def test_unbounded_cop_runs_one_epoch(tmp_path):
+    r0, r1 = _run("unbounded", tmp_path)
+    assert r0 == r1 and r0["epochs"] == 1 and r0["found"] and r0["winner"] == 1
 
 
 def test_sharding_and_sums(tmp_path):

@@ -77,6 +77,26 @@ def test_noalloc_matches_allocating_search_twice_in_a_row():
     model.close()
 
 
+def test_noalloc_same_model_again_skips_the_upload_and_matches_the_oracle(oracle_built):
+    """The per-frame case: one model, a new seed each call.  Only the first call copies the lowered model into the
+    array; the later ones must find it intact under the walkers they pile on top of it.  Checked against the
+    allocating entry points and, directly, against the oracle's walkers."""
+    from ghost_b200 import capi
+    desc = model_by_name("magic_square:6")
+    model = capi.Model(desc)
+    port = oracle_built.OraclePort(desc)
+    for seed in (21, 22, 23):
+        opts = default_opts(stop_on_first_solution=0, seed=seed, number_walkers=12, max_iterations=120)
+        port.resolve_opts(opts)
+        best_x, summary = _noalloc_run(model, opts, 1, 120)
+        _same(_reference_run(model, opts, 1, 120), best_x, summary, 12)
+        for w in range(12):
+            want = port.search(opts, w, 120)
+            assert np.array_equal(best_x[w], want["best_x"]), (seed, w)
+            assert int(summary[w, 2]) == want["counters"]["search_iterations"]
+    model.close()
+
+
 def test_noalloc_refuses_what_does_not_fit():
     import torch
     from ghost_b200 import capi
