@@ -20,6 +20,7 @@
 //   AllEqual                two assigned variables of its scope differ (all_equal.cpp:47-60);
 //   FixValue                an assigned variable differs from the value (fix_value.cpp:46-52);
 //   AllDifferentAbsDiff     two complete adjacent differences are equal (extension kind).
+//   AllDifferentOffset      an earlier variable of the scope has the same shifted value (extension kind).
 // When a constraint's last variable is assigned the test is exact, hence every leaf is a solution and
 // every solution is reached (the bounds are necessary conditions).
 #include <cuda_runtime.h>
@@ -73,6 +74,9 @@ __device__ bool cs_feasible(const CsModel& M, const int* x, int k)
 		} else if (kind == GHOST_KIND_ALL_DIFFERENT) {
 			const int xk = x[k];
 			for (int i = b; i < e; ++i) { const int v = M.cvar[i]; if (v < k && x[v] == xk) return false; }
+		} else if (kind == GHOST_KIND_ALL_DIFFERENT_OFFSET) {
+			const int sk = x[k] + M.ccoef[b + M.v2c_pos[r]];   // shifted value of variable k
+			for (int i = b; i < e; ++i) { const int v = M.cvar[i]; if (v < k && x[v] + M.ccoef[i] == sk) return false; }
 		} else if (kind == GHOST_KIND_ALL_EQUAL) {
 			const int xk = x[k];
 			for (int i = b; i < e; ++i) { const int v = M.cvar[i]; if (v < k && x[v] != xk) return false; }

@@ -24,7 +24,7 @@ namespace ghost_b200 {
 
 static bool is_linear(int k) { return k >= GHOST_KIND_LINEAR_EQ && k <= GHOST_KIND_LINEAR_G; }
 // kinds that keep a value-count table
-static bool is_alldiff_like(int k) { return k == GHOST_KIND_ALL_DIFFERENT || k == GHOST_KIND_ALL_DIFFERENT_ABS_DIFF || k == GHOST_KIND_ALL_EQUAL; }
+static bool is_alldiff_like(int k) { return k == GHOST_KIND_ALL_DIFFERENT || k == GHOST_KIND_ALL_DIFFERENT_ABS_DIFF || k == GHOST_KIND_ALL_EQUAL || k == GHOST_KIND_ALL_DIFFERENT_OFFSET; }
 
 static bool as_int(double d, int64_t* out)
 {
@@ -107,8 +107,18 @@ int lower_model(const GhostModelDesc* d, LoweredModel* out, std::string* why)
 			c2v[i] = v;
 			ent_ctr[i] = c;
 			int64_t vlo = dom_lo[v], vhi = dom_vals[dom_off[v + 1] - 1];
-			lo = std::min(lo, vlo); hi = std::max(hi, vhi);
 			int second = 0;
+			if (k == GHOST_KIND_ALL_DIFFERENT_OFFSET) {
+				// the count table is indexed by the shifted value x + o
+				int64_t off;
+				double given = d->ctr_coefs ? d->ctr_coefs[i] : 0.0;
+				if (!as_int(given, &off) || std::llabs((long long)off) > (1 << 20))
+					return fail(GHOST_B200_ERR_UNSUPPORTED, "constraint " + std::to_string(c) + ": offset " + std::to_string(given) + " is not a (small) integer");
+				second = static_cast<int32_t>(off);
+				ent_coef[i] = second;
+				vlo += off; vhi += off;
+			}
+			lo = std::min(lo, vlo); hi = std::max(hi, vhi);
 			if (is_linear(k)) {
 				int64_t a;
 				double coef = d->ctr_coefs ? d->ctr_coefs[i] : 1.0;
@@ -269,6 +279,7 @@ int lower_model(const GhostModelDesc* d, LoweredModel* out, std::string* why)
 				case GHOST_KIND_LINEAR_L:   cls = GB_CLS_LINEAR; wbits = 5; break;
 				case GHOST_KIND_LINEAR_G:   cls = GB_CLS_LINEAR; wbits = 6; break;
 				case GHOST_KIND_ALL_DIFFERENT: cls = GB_CLS_ALLDIFF; break;
+				case GHOST_KIND_ALL_DIFFERENT_OFFSET: cls = GB_CLS_ALLDIFF_OFF; break;
 				case GHOST_KIND_FIX_VALUE: cls = GB_CLS_FIX; break;
 				case GHOST_KIND_ALL_DIFFERENT_ABS_DIFF: cls = GB_CLS_ABSDIFF; break;
 				case GHOST_KIND_ALL_EQUAL: cls = GB_CLS_ALLEQ; break;

@@ -20,7 +20,7 @@ struct BlobOffsets {
 	int v2c_off, v2c;          // v2c: 2 words per entry {constraint id, coefficient | scope position}
 	int kind, rhs, cnt_tab;    // cnt_tab[c] = cnt_off[c] - cnt_base[c]  (index = cnt_tab[c] + value)
 	int c2v_off, c2v, ent_ctr; // ent_ctr[i] = constraint owning scope entry i
-	int ent_coef;              // coefficient of scope entry i (linear), 0 otherwise
+	int ent_coef;              // coefficient of scope entry i (linear), offset (AllDifferentOffset), 0 otherwise
 	int cnt_owner;             // [cnt_total] constraint owning count-table slot t
 	int cnt_lo, cnt_n;         // [C] first slot and number of slots of the constraint's count table (0, 0: none)
 	int obj_coef;              // dense [V]
@@ -78,7 +78,8 @@ struct DevModel {
 enum : int { GB_KIND_STATIC = 16 };
 
 // ELL entry encoding (word 0)
-enum : int { GB_ELL_END = 0xFFFFF, GB_CLS_LINEAR = 0, GB_CLS_ALLDIFF = 1, GB_CLS_FIX = 2, GB_CLS_ABSDIFF = 3, GB_CLS_ZERO = 4, GB_CLS_ALLEQ = 5 };
+enum : int { GB_ELL_END = 0xFFFFF, GB_CLS_LINEAR = 0, GB_CLS_ALLDIFF = 1, GB_CLS_FIX = 2, GB_CLS_ABSDIFF = 3, GB_CLS_ZERO = 4, GB_CLS_ALLEQ = 5,
+               GB_CLS_ALLDIFF_OFF = 6 /* AllDifferentOffset: as ALLDIFF, the entry's second word is the variable's offset */ };
 enum : int { GB_MARK_SKIP = 1 << 20 };
 
 // Per-walker shared-memory layout, byte offsets from the walker's base.

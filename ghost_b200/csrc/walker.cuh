@@ -318,6 +318,28 @@ __device__ inline void alleq_refresh(const DevModel& m, const WS& s, int c)
 	}
 }
 
+// AllDifferentOffset, two variables of the scope changing at once (a swap of a permutation problem): the counts
+// of up to four shifted values move; the delta is the true change of sum C(count, 2), each distinct key once.
+// (For a stock AllDifferent the swap leaves every count alone: delta 0, no call.)
+template <class WS>
+__device__ __forceinline__ int alldiff_four_key_delta(const WS& s, int k0, int k1, int k2, int k3)
+{
+	// k0 -1, k1 +1, k2 -1, k3 +1 (indices into the count table)
+	const int keys[4] = { k0, k1, k2, k3 };
+	int diff = 0;
+#pragma unroll
+	for (int i = 0; i < 4; ++i) {
+		bool seen = false;
+		int total = 0;
+#pragma unroll
+		for (int j = 0; j < 4; ++j) {
+			if (keys[j] == keys[i]) { total += (j & 1) ? 1 : -1; if (j < i) seen = true; }
+		}
+		if (!seen && total != 0) { const int cur = s.cnt(keys[i]); diff += binom2(cur + total) - binom2(cur); }
+	}
+	return diff;
+}
+
 // ---------------------------------------------------------------------------------------------
 // Delta of ONE constraint for a change of variable va (row entry second field = ea) to na, and,
 // when vb >= 0, of vb (second field eb) to nb.  Restates optional_delta_error of the stock
@@ -361,6 +383,13 @@ __device__ inline int constraint_delta(const MV& mv, const WS& s, int c, int va,
 		int d = abs(na - k) - abs(s.x[va] - k);
 		if (vb >= 0) d += abs(nb - k) - abs(s.x[vb] - k);
 		return d;
+	}
+	if (kind == GHOST_KIND_ALL_DIFFERENT_OFFSET) {
+		// ea / eb = the variables' offsets; the count table is indexed by x + offset
+		const int tab = mv.cnt_tab(c), oa = s.x[va];
+		if (vb >= 0) return alldiff_four_key_delta(s, tab + ea + oa, tab + ea + na, tab + eb + s.x[vb], tab + eb + nb);
+		if (na == oa) return 0;
+		return s.cnt(tab + ea + na) - (s.cnt(tab + ea + oa) - 1);
 	}
 	if (kind == GHOST_KIND_ALL_DIFFERENT_ABS_DIFF) return absdiff_delta(mv, s, c, ea, na, vb >= 0 ? eb : -1, nb);
 	if (kind == GHOST_KIND_ALL_EQUAL) {
@@ -416,6 +445,7 @@ __device__ __forceinline__ int recompute_all_impl(const DevModel& m, const WS& s
 			if (kind_is_linear(kind)) val = mv.ld(m.o.ent_coef, i) * xu;
 			else if (kind == GHOST_KIND_FIX_VALUE) val = abs(xu - mv.rhs(c));
 			else if (kind == GHOST_KIND_ALL_DIFFERENT || kind == GHOST_KIND_ALL_EQUAL) s.cnt_add(mv.cnt_tab(c) + xu, 1);
+			else if (kind == GHOST_KIND_ALL_DIFFERENT_OFFSET) s.cnt_add(mv.cnt_tab(c) + xu + mv.ld(m.o.ent_coef, i), 1);
 			else if (kind == GHOST_KIND_ALL_DIFFERENT_ABS_DIFF) {
 				if (i + 1 < mv.scope_begin(c + 1)) s.cnt_add(mv.cnt_tab(c) + abs(s.x[mv.scope_var(i + 1)] - xu), 1);
 			}
@@ -732,8 +762,8 @@ __device__ inline int hoist_variable(const DevModel& m, const WS& s, int v, int*
 			if (cls == GB_CLS_LINEAR) {
 				h.y = e.y; h.z = s.T_of(c) - e.y * xv;
 				contrib = -s.err_of(c);
-			} else if (cls == GB_CLS_ALLDIFF) {
-				const int tab = mv.cnt_tab(c);
+			} else if (cls == GB_CLS_ALLDIFF || cls == GB_CLS_ALLDIFF_OFF) {
+				const int tab = mv.cnt_tab(c) + e.y;   // e.y: the variable's offset (0 for a stock AllDifferent)
 				const int sub = s.cnt(tab + xv) - 1;
 				h.y = tab; h.z = sub;
 				contrib = -sub;
@@ -825,7 +855,7 @@ __device__ __forceinline__ int hoisted_term(const MV& mv, const WS& s, const int
 {
 	int type = h.x & 0xF;
 	if (type == GB_CLS_LINEAR) return linear_error_w((h.x >> 4) & 7, h.z + h.y * d);
-	if (type == GB_CLS_ALLDIFF) return s.cnt(h.y + d);
+	if (type == GB_CLS_ALLDIFF || type == GB_CLS_ALLDIFF_OFF) return s.cnt(h.y + d);
 	if (type == GB_CLS_FIX) return abs(d - h.y);
 	if (type == GB_CLS_ABSDIFF) return absdiff_delta(mv, s, h.x >> 8, h.y, d, -1, 0);
 	if (type == GB_CLS_ALLEQ) return -max(s.cnt(h.y + d) + 1, h.z);
@@ -866,8 +896,8 @@ __device__ __forceinline__ bool candidate_sum(const DevModel& m, const MV& mv, c
 		if (st.w == 0) {
 			// constraint of the partner only: {j} -> {x_v}  (search_unit.hpp:881-885)
 			if (cls == GB_CLS_LINEAR) sum += linear_error_w(ell_w(e.x), st.x + e.y * dx) - st.z;
-			else if (cls == GB_CLS_ALLDIFF) {
-				int tab = mv.cnt_tab(c);
+			else if (cls == GB_CLS_ALLDIFF || cls == GB_CLS_ALLDIFF_OFF) {
+				int tab = mv.cnt_tab(c) + e.y;
 				sum += s.cnt(tab + xv) - (s.cnt(tab + xj) - 1);
 			} else if (cls == GB_CLS_FIX) {
 				int kk = mv.rhs(c);
@@ -882,6 +912,11 @@ __device__ __forceinline__ bool candidate_sum(const DevModel& m, const MV& mv, c
 				int w = ell_w(e.x), t1 = h.z + h.y * xj;
 				sum += linear_error_w(w, t1 + e.y * dx) - linear_error_w(w, t1);
 			} else if (cls == GB_CLS_ALLDIFF) sum -= s.cnt(h.y + xj) - h.z;
+			else if (cls == GB_CLS_ALLDIFF_OFF) {
+				// the hoisted single-variable delta out, the swap's own delta in (h.y = table + offset of v)
+				const int tabj = mv.cnt_tab(c) + e.y;
+				sum += alldiff_four_key_delta(s, h.y + xv, h.y + xj, tabj + xj, tabj + xv) - (s.cnt(h.y + xj) - h.z);
+			}
 			else if (cls == GB_CLS_FIX) sum += abs(xv - h.y) - abs(xj - h.y);
 			else if (cls == GB_CLS_ABSDIFF) sum += absdiff_delta(mv, s, c, h.y, xj, e.y, xv) - absdiff_delta(mv, s, c, h.y, xj, -1, 0);
 			else if (cls == GB_CLS_ALLEQ) sum += max(s.cnt(h.y + xj) + 1, h.z) - alleq_max1(st.x); // the swap changes nothing
@@ -1363,6 +1398,26 @@ __device__ inline int evaluate_candidates(const DevModel& m, const WS& s, int v,
 	const int nslots = PERM ? m.V : mv.dom_size(v);
 	int mine = 0;
 	q.key = GB_INT_MAX; q.bits = 0u;
+	if (!PERM && T == 32 && nslots <= 4 && nh > 2) {
+		// A handful of candidates over many constraints (binary domains: the knapsack rows): candidates across lanes
+		// would leave one lane summing nh terms while 31 wait ("low candidate counts").  Here the lanes
+		// take the CONSTRAINTS of one candidate, a warp reduction adds them up, and lane k keeps candidate k's sum.
+		int sum = GB_INT_MAX;
+		for (int k = 0; k < nslots; ++k) {                       // warp-uniform
+			const int d = mv.dom_value(v, k);
+			int total = GB_INT_MAX;
+			if (d != xv) {                                       // search_unit.hpp:833
+				int part = 0;
+				for (int t = lane; t < nh; t += 32) part += hoisted_term(mv, s, s.hoist[t], d);
+				total = __reduce_add_sync(0xffffffffu, part) + bias;
+				if (lane == k) { sum = total; mine = 1; }
+			}
+			if (out && lane == 0) out[k] = total;
+		}
+		if (out) for (int k = nslots + lane; k < m.max_candidates; k += 32) out[k] = GB_INT_MAX;
+		commit_value_chunk<T>(s, q, 0, sum);
+		return mine;
+	}
 	for (int ch = G::warp(); ch < nchunks_c; ch += G::NW) {
 		int slot = ch * 32 + lane;
 		int sum = GB_INT_MAX;
@@ -1511,6 +1566,10 @@ __device__ inline void apply_move(const DevModel& m, const WS& s, int v, int new
 			int kind = mv.kind(c);
 			if (kind == GHOST_KIND_ALL_DIFFERENT || kind == GHOST_KIND_ALL_EQUAL) {
 				if (!both && nv_new != xv) { int tab = mv.cnt_tab(c); s.cnt_add(tab + xv, -1); s.cnt_add(tab + nv_new, +1); }
+			} else if (kind == GHOST_KIND_ALL_DIFFERENT_OFFSET) {
+				const int tab = mv.cnt_tab(c);
+				if (nv_new != xv) { s.cnt_add(tab + e.y + xv, -1); s.cnt_add(tab + e.y + nv_new, +1); }
+				if (both && xj != xv) { s.cnt_add(tab + eb + xj, -1); s.cnt_add(tab + eb + xv, +1); } // the partner's shifted value moves too
 			} else if (kind_is_linear(kind)) {
 				s.T_of(c) += e.y * (nv_new - xv) + (both ? eb * (xv - xj) : 0);
 			}
@@ -1523,6 +1582,8 @@ __device__ inline void apply_move(const DevModel& m, const WS& s, int v, int new
 			int kind = mv.kind(c);
 			if (kind == GHOST_KIND_ALL_DIFFERENT || kind == GHOST_KIND_ALL_EQUAL) {
 				if (xv != xj) { int tab = mv.cnt_tab(c); s.cnt_add(tab + xj, -1); s.cnt_add(tab + xv, +1); }
+			} else if (kind == GHOST_KIND_ALL_DIFFERENT_OFFSET) {
+				if (xv != xj) { int tab = mv.cnt_tab(c) + e.y; s.cnt_add(tab + xj, -1); s.cnt_add(tab + xv, +1); }
 			} else if (kind_is_linear(kind)) s.T_of(c) += e.y * (xv - xj);
 			s.err_of(c) += delta;
 		}

@@ -24,6 +24,7 @@ FIX_VALUE = 7
 PURE_OPTIMIZATION = 8
 ALL_DIFFERENT_ABS_DIFF = 9
 ALL_EQUAL = 10
+ALL_DIFFERENT_OFFSET = 11
 KIND_USER = 100
 
 OBJ_NONE = 0
@@ -187,6 +188,13 @@ class ModelDesc:
 
     def all_equal(self, variables):
         self.constraints.append((ALL_EQUAL, list(variables), None, 0.0))
+
+    def all_different_offset(self, variables, offsets):
+        """Extension kind: x_i + offsets[i] pairwise different (offsets are integers)."""
+        variables = list(variables)
+        offsets = [float(int(o)) for o in offsets]
+        assert len(offsets) == len(variables)
+        self.constraints.append((ALL_DIFFERENT_OFFSET, variables, offsets, 0.0))
 
     def all_different_abs_diff(self, variables):
         self.constraints.append((ALL_DIFFERENT_ABS_DIFF, list(variables), None, 0.0))

@@ -46,6 +46,28 @@ def n_queens(n: int) -> ModelDesc:
     return m
 
 
+def n_queens_offset(n: int) -> ModelDesc:
+    """configs[0] as BASELINE.json words it, "3 x AllDifferent": q_i in [0,n-1], AllDifferent(q), AllDifferent(q_i + i),
+    AllDifferent(q_i - i) with the extension kind AllDifferentOffset — no auxiliary variables: V = n, C = 3."""
+    m = ModelDesc(permutation_problem=False, name=f"n_queens_offset_{n}")
+    q = [m.add_variable(0, n, index=i) for i in range(n)]
+    m.all_different(q)
+    m.all_different_offset(q, list(range(n)))
+    m.all_different_offset(q, [-i for i in range(n)])
+    return m
+
+
+def n_queens_permutation(n: int) -> ModelDesc:
+    """n-queens as a permutation problem (one queen per row AND column by construction): AllDifferent(q) never
+    changes under swaps, the two diagonal AllDifferentOffset constraints carry the search."""
+    m = ModelDesc(permutation_problem=True, name=f"n_queens_perm_{n}")
+    q = [m.add_variable(0, n, index=i) for i in range(n)]
+    m.all_different(q)
+    m.all_different_offset(q, list(range(n)))
+    m.all_different_offset(q, [-i for i in range(n)])
+    return m
+
+
 def costas_array(n: int) -> ModelDesc:
     """configs[4]: Costas array of order n.  s_i in [1,n]; e_{d,i} = s_{i+d} - s_i in [-(n-1), n-1]
     for d=1..n-1, i=1..n-d; AllDifferent(s), AllDifferent(e_{d,.}) for d=1..n-2,
@@ -101,6 +123,10 @@ def by_name(name: str) -> ModelDesc:
         return magic_square(int(arg))
     if kind == "n_queens":
         return n_queens(int(arg))
+    if kind == "n_queens_offset":
+        return n_queens_offset(int(arg))
+    if kind == "n_queens_perm":
+        return n_queens_permutation(int(arg))
     if kind == "costas":
         return costas_array(int(arg))
     if kind == "all_interval":

@@ -54,6 +54,11 @@ typedef enum GhostConstraintKind {
 	                                          error = sum_values C(count,2)                     */
 	GHOST_KIND_ALL_EQUAL = 10,        /* src/global_constraints/all_equal.cpp:47-95: error = scope size
 	                                     minus the count of the most frequent value                */
+	GHOST_KIND_ALL_DIFFERENT_OFFSET = 11, /* extension: the x_i + o_i of the scope pairwise different (the diagonals of
+	                                     n-queens: q_i + i, q_i - i).  Stock AllDifferent has no offsets
+	                                     (include/global_constraints/all_different.hpp:46-74); error and delta are
+	                                     its own (all_different.cpp:59-100) on the shifted values.  The integer
+	                                     offsets travel in ctr_coefs.                                             */
 	GHOST_KIND_USER = 100
 } GhostConstraintKind;
 

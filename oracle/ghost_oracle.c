@@ -93,7 +93,8 @@ static int cmp_i32(const void* a, const void* b)
 
 static int is_alldiff_like(int32_t kind) /* kinds that keep a value-count table */
 {
-	return kind == GHOST_KIND_ALL_DIFFERENT || kind == GHOST_KIND_ALL_DIFFERENT_ABS_DIFF || kind == GHOST_KIND_ALL_EQUAL;
+	return kind == GHOST_KIND_ALL_DIFFERENT || kind == GHOST_KIND_ALL_DIFFERENT_ABS_DIFF || kind == GHOST_KIND_ALL_EQUAL
+	    || kind == GHOST_KIND_ALL_DIFFERENT_OFFSET;
 }
 static int is_linear(int32_t kind) { return kind >= GHOST_KIND_LINEAR_EQ && kind <= GHOST_KIND_LINEAR_G; }
 
@@ -155,14 +156,16 @@ OracleModel* oracle_model_create(const GhostModelDesc* d)
 		int32_t lo = INT32_MAX, hi = INT32_MIN;
 		for (int i = m->coff[c]; i < m->coff[c + 1]; ++i) {
 			int v = m->cvars[i];
+			/* AllDifferentOffset counts the shifted values x + o */
+			int32_t off = m->kind[c] == GHOST_KIND_ALL_DIFFERENT_OFFSET ? (int32_t)m->ccoef[i] : 0;
 			if (m->dom_off[v + 1] > m->dom_off[v]) {
-				int32_t a = m->dom[m->dom_off[v]], b = m->dom[m->dom_off[v + 1] - 1];
+				int32_t a = m->dom[m->dom_off[v]] + off, b = m->dom[m->dom_off[v + 1] - 1] + off;
 				if (a < lo) lo = a;
 				if (b > hi) hi = b;
 			}
 			/* start values may lie outside the domain only if the user built it so; include them */
-			if (m->start[v] < lo) lo = m->start[v];
-			if (m->start[v] > hi) hi = m->start[v];
+			if (m->start[v] + off < lo) lo = m->start[v] + off;
+			if (m->start[v] + off > hi) hi = m->start[v] + off;
 		}
 		if (lo > hi) { lo = 0; hi = 0; }
 		if (m->kind[c] == GHOST_KIND_ALL_DIFFERENT_ABS_DIFF) { hi = hi - lo; lo = 0; }
@@ -252,11 +255,13 @@ static double ctr_error(Walker* w, int c)
 	const OracleModel* m = w->m;
 	int b = m->coff[c], e = m->coff[c + 1];
 	switch (m->kind[c]) {
-	case GHOST_KIND_ALL_DIFFERENT: {
-		/* all_different.cpp:59-75 */
+	case GHOST_KIND_ALL_DIFFERENT:
+	case GHOST_KIND_ALL_DIFFERENT_OFFSET: {
+		/* all_different.cpp:59-75; the extension kind counts x + o instead of x */
 		int32_t* cnt = w->count + m->cnt_off[c];
+		const int shifted = m->kind[c] == GHOST_KIND_ALL_DIFFERENT_OFFSET;
 		memset(cnt, 0, sizeof(int32_t) * m->cnt_size[c]);
-		for (int i = b; i < e; ++i) cnt[w->x[m->cvars[i]] - m->cnt_base[c]]++;
+		for (int i = b; i < e; ++i) cnt[w->x[m->cvars[i]] + (shifted ? (int32_t)m->ccoef[i] : 0) - m->cnt_base[c]]++;
 		double counter = 0;
 		for (int t = 0; t < m->cnt_size[c]; ++t)
 			if (cnt[t] > 1) counter += binomial_with_2(cnt[t]);
@@ -311,22 +316,41 @@ static int32_t* touched_slot(Touched* t, const int32_t* cnt, int32_t key)
 
 /* Constraint::simulate_delta -> delta_error -> optional_delta_error (src/constraint.cpp:91-96,
  * 67-89).  vars are GLOBAL ids (1 or 2 of them), vals their candidate values. */
+/* offset of variable var inside AllDifferentOffset constraint c */
+static int32_t scope_offset(const OracleModel* m, int c, int var)
+{
+	for (int p = m->coff[c]; p < m->coff[c + 1]; ++p) if (m->cvars[p] == var) return (int32_t)m->ccoef[p];
+	return 0;
+}
+
 static double ctr_delta(const Walker* w, int c, int n, const int32_t* vars, const int32_t* vals)
 {
 	const OracleModel* m = w->m;
 	switch (m->kind[c]) {
-	case GHOST_KIND_ALL_DIFFERENT: {
-		/* all_different.cpp:77-100 */
+	case GHOST_KIND_ALL_DIFFERENT:
+	case GHOST_KIND_ALL_DIFFERENT_OFFSET: {
+		/* all_different.cpp:77-100; the extension kind on the shifted values */
 		const int32_t* cnt = w->count + m->cnt_off[c];
 		int32_t base = m->cnt_base[c];
+		int32_t shift[2] = { 0, 0 };
+		if (m->kind[c] == GHOST_KIND_ALL_DIFFERENT_OFFSET)
+			for (int i = 0; i < n && i < 2; ++i) shift[i] = scope_offset(m, c, vars[i]);
 		Touched t; t.n = 0;
 		double diff = 0.0;
 		for (int i = 0; i < n; ++i) {
-			*touched_slot(&t, cnt, w->x[vars[i]] - base) -= 1;
-			*touched_slot(&t, cnt, vals[i] - base) += 1;
+			*touched_slot(&t, cnt, w->x[vars[i]] + shift[i] - base) -= 1;
+			*touched_slot(&t, cnt, vals[i] + shift[i] - base) += 1;
+		}
+		if (m->kind[c] == GHOST_KIND_ALL_DIFFERENT_OFFSET) {
+			/* the extension kind's delta is the true change of the error: every touched key once.  (The stock
+			 * loop below visits the (old, new) key of each change, all_different.cpp:88-97, and would count a
+			 * key twice when two changes land on the same shifted value — which a swap inside a stock
+			 * AllDifferent never produces, its counts do not move at all.) */
+			for (int k = 0; k < t.n; ++k) diff += binomial_with_2(t.copy[k]) - binomial_with_2(cnt[t.key[k]]);
+			return diff;
 		}
 		for (int i = 0; i < n; ++i) {
-			int32_t ko = w->x[vars[i]] - base, kn = vals[i] - base;
+			int32_t ko = w->x[vars[i]] + shift[i] - base, kn = vals[i] + shift[i] - base;
 			int32_t co = *touched_slot(&t, cnt, ko), cn = *touched_slot(&t, cnt, kn);
 			if (cnt[ko] != co) diff += binomial_with_2(co) - binomial_with_2(cnt[ko]);
 			if (cnt[kn] != cn) diff += binomial_with_2(cn) - binomial_with_2(cnt[kn]);
@@ -410,10 +434,11 @@ static double ctr_delta(const Walker* w, int c, int n, const int32_t* vars, cons
 static void ctr_update(Walker* w, int c, int var, int32_t new_value)
 {
 	const OracleModel* m = w->m;
-	if (m->kind[c] == GHOST_KIND_ALL_DIFFERENT || m->kind[c] == GHOST_KIND_ALL_EQUAL) { /* all_equal.cpp:87-95 alike */
+	if (m->kind[c] == GHOST_KIND_ALL_DIFFERENT || m->kind[c] == GHOST_KIND_ALL_EQUAL || m->kind[c] == GHOST_KIND_ALL_DIFFERENT_OFFSET) { /* all_equal.cpp:87-95 alike */
 		int32_t* cnt = w->count + m->cnt_off[c];
-		cnt[w->x[var] - m->cnt_base[c]] -= 1;
-		cnt[new_value - m->cnt_base[c]] += 1;
+		const int32_t shift = m->kind[c] == GHOST_KIND_ALL_DIFFERENT_OFFSET ? scope_offset(m, c, var) : 0;
+		cnt[w->x[var] + shift - m->cnt_base[c]] -= 1;
+		cnt[new_value + shift - m->cnt_base[c]] += 1;
 	} else if (is_linear(m->kind[c])) {
 		for (int p = m->coff[c]; p < m->coff[c + 1]; ++p)
 			if (m->cvars[p] == var) { w->cur_sum[c] += m->ccoef[p] * (new_value - w->x[var]); break; }

@@ -25,7 +25,7 @@ def test_host_api_cpu(tmp_path):
 
 
 def test_examples_compile(tmp_path):
-    for name in ("magic_square", "knapsack", "all_magic_squares"):
+    for name in ("magic_square", "knapsack", "all_magic_squares", "n_queens"):
         _compile(os.path.join(ROOT, "examples", name + ".cpp"), str(tmp_path / name))
 
 
@@ -63,6 +63,9 @@ def test_examples_run_on_gpu(tmp_path):
     exe = _compile(os.path.join(ROOT, "examples", "all_magic_squares.cpp"), str(tmp_path / "allmagic"))
     r = subprocess.run([exe, "4"], capture_output=True, text=True, timeout=120)
     assert r.returncode == 0 and "Solutions: 7040" in r.stdout, r.stdout + r.stderr
+    exe = _compile(os.path.join(ROOT, "examples", "n_queens.cpp"), str(tmp_path / "queens"))   # AllDifferentOffset, V = 100, C = 3
+    r = subprocess.run([exe, "100", "20"], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0 and "Solution found, cost 0, verified" in r.stdout, r.stdout + r.stderr
     exe = _compile(os.path.join(ROOT, "examples", "knapsack.cpp"), str(tmp_path / "knap"))
     r = subprocess.run([exe, "100", "5", "1"], capture_output=True, text=True, timeout=120)
     assert r.returncode == 0 and "Feasible" in r.stdout, r.stdout + r.stderr

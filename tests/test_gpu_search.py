@@ -54,13 +54,14 @@ def _check_against_oracle(desc, oracle_built, iterations, walkers, seed, threads
 
 @pytest.mark.parametrize("name", ["magic_square:4", "magic_square:7", "n_queens:8", "n_queens:20", "costas:6",
                                   "costas:9", "knapsack:20x3", "knapsack:50x5", "all_interval:10", "mixed",
-                                  "mixed_perm", "mixed_eq", "mixed_perm_eq"])
+                                  "mixed_perm", "mixed_eq", "mixed_perm_eq", "n_queens_offset:12", "n_queens_perm:11", "weighted_perm"])
 def test_trajectories_match_oracle(name, oracle_built):
     _check_against_oracle(model_by_name(name), oracle_built, iterations=600, walkers=12, seed=2024)
 
 
 @pytest.mark.parametrize("threads", [32, 64, 128, 256])
-@pytest.mark.parametrize("name", ["magic_square:7", "n_queens:20", "mixed_perm", "knapsack:50x5", "mixed_perm_eq"])
+@pytest.mark.parametrize("name", ["magic_square:7", "n_queens:20", "mixed_perm", "knapsack:50x5", "mixed_perm_eq", "n_queens_perm:11",
+                                  "n_queens_offset:12"])
 def test_trajectories_every_mapping(name, threads, oracle_built):
     _check_against_oracle(model_by_name(name), oracle_built, iterations=300, walkers=5, seed=5, threads=threads)
 
@@ -87,10 +88,34 @@ def test_custom_start_and_options(oracle_built):
                           enable_optimization_guidance=0)
 
 
-@pytest.mark.parametrize("name", ["magic_square:30", "n_queens:100", "costas:20", "knapsack:500x30"])
+@pytest.mark.parametrize("name", ["magic_square:30", "n_queens:100", "costas:20", "knapsack:500x30", "all_interval:500",
+                                  "n_queens_offset:100"])
 def test_trajectories_baseline_sizes(name, oracle_built):
-    """BASELINE.json's configurations at full size, few walkers and iterations (oracle speed)."""
-    _check_against_oracle(model_by_name(name), oracle_built, iterations=60, walkers=3, seed=77)
+    """BASELINE.json's five configurations at full size (and config 0 in its three-constraint form), few walkers and
+    iterations (oracle speed)."""
+    _check_against_oracle(model_by_name(name), oracle_built, iterations=40 if name == "all_interval:500" else 60, walkers=3, seed=77)
+
+
+def test_config3_population_4096_walkers_per_gpu(oracle_built):
+    """BASELINE.json config 3: all-interval series n = 500 with 4096 walkers on one device — more than one resident
+    wave.  Walkers sampled across the population follow the oracle; every walker has advanced."""
+    from ghost_b200 import capi
+    desc = model_by_name("all_interval:500")
+    W, iters = 4096, 12
+    port = oracle_built.OraclePort(desc)
+    opts = default_opts(seed=31, number_walkers=W, stop_on_first_solution=0, max_iterations=iters)
+    port.resolve_opts(opts)
+    model = capi.Model(desc)
+    s = model.begin(opts)
+    s.epoch(iters)
+    out = s.walkers(W)
+    s.end()
+    model.close()
+    assert all(c["search_iterations"] == iters for c in out["counters"])
+    for w in (0, 1, 2047, 4095):
+        want = port.search(opts, w, iters)
+        assert out["counters"][w] == want["counters"], w
+        assert np.array_equal(out["best_x"][w], want["best_x"]), w
 
 
 def test_config5_population_131072_walkers_per_gpu(oracle_built):
