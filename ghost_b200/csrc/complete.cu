@@ -20,6 +20,7 @@
 //   AllEqual                two assigned variables of its scope differ (all_equal.cpp:47-60);
 //   FixValue                an assigned variable differs from the value (fix_value.cpp:46-52);
 //   AllDifferentAbsDiff     two complete adjacent differences are equal (extension kind).
+//   AllDifferentLagDiff     two complete differences at the constraint's lag are equal (extension kind).
 //   AllDifferentOffset      an earlier variable of the scope has the same shifted value (extension kind).
 // When a constraint's last variable is assigned the test is exact, hence every leaf is a solution and
 // every solution is reached (the bounds are necessary conditions).
@@ -82,17 +83,19 @@ __device__ bool cs_feasible(const CsModel& M, const int* x, int k)
 			for (int i = b; i < e; ++i) { const int v = M.cvar[i]; if (v < k && x[v] != xk) return false; }
 		} else if (kind == GHOST_KIND_FIX_VALUE) {
 			if (x[k] != M.param[c]) return false;
-		} else if (kind == GHOST_KIND_ALL_DIFFERENT_ABS_DIFF) {
+		} else if (kind == GHOST_KIND_ALL_DIFFERENT_ABS_DIFF || kind == GHOST_KIND_ALL_DIFFERENT_LAG_DIFF) {
+			const bool absolute = kind == GHOST_KIND_ALL_DIFFERENT_ABS_DIFF;
+			const int lag = absolute ? 1 : M.param[c];
 			const int pos = M.v2c_pos[r], n = e - b;
-			for (int p = pos - 1; p <= pos; ++p) {
-				if (p < 0 || p + 1 >= n) continue;
-				const int u = M.cvar[b + p], w = M.cvar[b + p + 1];
+			for (int p = pos - lag; p <= pos; p += lag) {
+				if (p < 0 || p + lag >= n) continue;
+				const int u = M.cvar[b + p], w = M.cvar[b + p + lag];
 				if (u > k || w > k) continue;
-				const int dnew = abs(x[u] - x[w]);
-				for (int q = 0; q + 1 < n; ++q) {
+				const int dnew = absolute ? abs(x[u] - x[w]) : x[w] - x[u];
+				for (int q = 0; q + lag < n; ++q) {
 					if (q == p) continue;
-					const int u2 = M.cvar[b + q], w2 = M.cvar[b + q + 1];
-					if (u2 <= k && w2 <= k && abs(x[u2] - x[w2]) == dnew) return false;
+					const int u2 = M.cvar[b + q], w2 = M.cvar[b + q + lag];
+					if (u2 <= k && w2 <= k && (absolute ? abs(x[u2] - x[w2]) : x[w2] - x[u2]) == dnew) return false;
 				}
 			}
 		} // PureOptimization: error 0 always

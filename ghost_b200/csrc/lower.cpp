@@ -24,7 +24,8 @@ namespace ghost_b200 {
 
 static bool is_linear(int k) { return k >= GHOST_KIND_LINEAR_EQ && k <= GHOST_KIND_LINEAR_G; }
 // kinds that keep a value-count table
-static bool is_alldiff_like(int k) { return k == GHOST_KIND_ALL_DIFFERENT || k == GHOST_KIND_ALL_DIFFERENT_ABS_DIFF || k == GHOST_KIND_ALL_EQUAL || k == GHOST_KIND_ALL_DIFFERENT_OFFSET; }
+static bool is_alldiff_like(int k) { return k == GHOST_KIND_ALL_DIFFERENT || k == GHOST_KIND_ALL_DIFFERENT_ABS_DIFF || k == GHOST_KIND_ALL_EQUAL || k == GHOST_KIND_ALL_DIFFERENT_OFFSET || k == GHOST_KIND_ALL_DIFFERENT_LAG_DIFF; }
+static bool is_pair_diff(int k) { return k == GHOST_KIND_ALL_DIFFERENT_ABS_DIFF || k == GHOST_KIND_ALL_DIFFERENT_LAG_DIFF; }
 
 static bool as_int(double d, int64_t* out)
 {
@@ -129,7 +130,7 @@ int lower_model(const GhostModelDesc* d, LoweredModel* out, std::string* why)
 				second = static_cast<int32_t>(a);
 				lin_bound += std::llabs((long long)a) * std::max(std::llabs((long long)vlo), std::llabs((long long)vhi));
 				max_abs_coef = std::max<int64_t>(max_abs_coef, std::llabs((long long)a));
-			} else if (k == GHOST_KIND_ALL_DIFFERENT_ABS_DIFF) {
+			} else if (is_pair_diff(k)) {
 				second = i - b; // position in scope
 			}
 			rows[v].emplace_back(c, second);
@@ -174,6 +175,14 @@ int lower_model(const GhostModelDesc* d, LoweredModel* out, std::string* why)
 			if (n == 0) { lo = 0; hi = 0; }
 			int64_t base = lo, size = hi - lo + 1;
 			if (k == GHOST_KIND_ALL_DIFFERENT_ABS_DIFF) { base = 0; size = hi - lo + 1; has_abs_diff = true; }
+			if (k == GHOST_KIND_ALL_DIFFERENT_LAG_DIFF) {
+				// signed differences x[p+lag] - x[p]; the lag travels in the rhs section
+				int64_t lag;
+				double param = d->ctr_param ? d->ctr_param[c] : 0.0;
+				if (!as_int(param, &lag) || lag < 1 || lag > 65535) return fail(GHOST_B200_ERR_INVALID, "constraint " + std::to_string(c) + ": the lag of AllDifferentLagDiff must be an integer >= 1");
+				rhs[c] = static_cast<int32_t>(lag);
+				base = -(hi - lo); size = 2 * (hi - lo) + 1; has_abs_diff = true;
+			}
 			if (size > (1 << 20)) return fail(GHOST_B200_ERR_UNSUPPORTED, "constraint " + std::to_string(c) + ": value range too wide for a dense count table");
 			if (n > 65535) return fail(GHOST_B200_ERR_UNSUPPORTED, "AllDifferent scope beyond 65535");
 			cnt_tab[c] = static_cast<int32_t>(cnt_total - base);
@@ -228,7 +237,7 @@ int lower_model(const GhostModelDesc* d, LoweredModel* out, std::string* why)
 	L.desc.kind.assign(d->ctr_kind, d->ctr_kind + C);
 	L.desc.ctr_off = c2v_off; L.desc.ctr_var = c2v; L.desc.ctr_coef = ent_coef;
 	L.desc.ctr_param.assign(C, 0);
-	for (int c = 0; c < C; ++c) if (is_linear(d->ctr_kind[c]) || d->ctr_kind[c] == GHOST_KIND_FIX_VALUE) L.desc.ctr_param[c] = static_cast<int32_t>(std::llround(d->ctr_param ? d->ctr_param[c] : 0.0));
+	for (int c = 0; c < C; ++c) if (is_linear(d->ctr_kind[c]) || d->ctr_kind[c] == GHOST_KIND_FIX_VALUE || d->ctr_kind[c] == GHOST_KIND_ALL_DIFFERENT_LAG_DIFF) L.desc.ctr_param[c] = static_cast<int32_t>(std::llround(d->ctr_param ? d->ctr_param[c] : 0.0));
 	L.desc.obj_coef = obj_coef; L.desc.objective = ok;
 	L.start.assign(d->start_value, d->start_value + V);
 	L.error_bound = error_bound;
@@ -282,6 +291,7 @@ int lower_model(const GhostModelDesc* d, LoweredModel* out, std::string* why)
 				case GHOST_KIND_ALL_DIFFERENT_OFFSET: cls = GB_CLS_ALLDIFF_OFF; break;
 				case GHOST_KIND_FIX_VALUE: cls = GB_CLS_FIX; break;
 				case GHOST_KIND_ALL_DIFFERENT_ABS_DIFF: cls = GB_CLS_ABSDIFF; break;
+				case GHOST_KIND_ALL_DIFFERENT_LAG_DIFF: cls = GB_CLS_ABSDIFF; break;
 				case GHOST_KIND_ALL_EQUAL: cls = GB_CLS_ALLEQ; break;
 				default: cls = GB_CLS_ZERO; break;
 				}

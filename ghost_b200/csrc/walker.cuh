@@ -237,19 +237,22 @@ __device__ __forceinline__ int binom2(int n) { return (n * (n - 1)) >> 1; } // a
 // when pb >= 0): recount the <= 4 neighbouring |differences|.  Kept out of line: only models that
 // use the extension pay for it.
 // ---------------------------------------------------------------------------------------------
+// The two pair-difference kinds share one code path: AllDifferentAbsDiff is (lag 1, absolute values),
+// AllDifferentLagDiff (lag = its parameter, signed differences x[p+lag] - x[p]).
+__device__ __forceinline__ int pair_value(bool absolute, int first, int second) { return absolute ? abs(second - first) : second - first; }
 template <class XT>
 __device__ __noinline__ int absdiff_delta(const int32_t* blob, int c2v_off_sec, int c2v_sec, int cnt_tab_sec,
-                                          const XT* x, const unsigned* cnt32, int c, int pa, int na, int pb, int nb)
+                                          const XT* x, const unsigned* cnt32, int c, int pa, int na, int pb, int nb, int lag, bool absolute)
 {
 	int b = __ldg(blob + c2v_off_sec + c), n = __ldg(blob + c2v_off_sec + c + 1) - b, tab = __ldg(blob + cnt_tab_sec + c);
 	int pairs[4]; int np = 0;
 	auto add_pair = [&](int p) {
-		if (p < 0 || p + 1 >= n) return;
+		if (p < 0 || p + lag >= n) return;
 		for (int z = 0; z < np; ++z) if (pairs[z] == p) return;
 		pairs[np++] = p;
 	};
-	add_pair(pa - 1); add_pair(pa);
-	if (pb >= 0) { add_pair(pb - 1); add_pair(pb); }
+	add_pair(pa - lag); add_pair(pa);
+	if (pb >= 0) { add_pair(pb - lag); add_pair(pb); }
 	int keys[8], net[8]; int nk = 0;
 	auto touch = [&](int key, int d) {
 		for (int z = 0; z < nk; ++z) if (keys[z] == key) { net[z] += d; return; }
@@ -257,11 +260,11 @@ __device__ __noinline__ int absdiff_delta(const int32_t* blob, int c2v_off_sec, 
 	};
 	for (int z = 0; z < np; ++z) {
 		int p = pairs[z];
-		int oa = x[__ldg(blob + c2v_sec + b + p)], ob = x[__ldg(blob + c2v_sec + b + p + 1)];
+		int oa = x[__ldg(blob + c2v_sec + b + p)], ob = x[__ldg(blob + c2v_sec + b + p + lag)];
 		int va = (p == pa) ? na : (p == pb ? nb : oa);
-		int vb = (p + 1 == pa) ? na : (p + 1 == pb ? nb : ob);
-		touch(abs(ob - oa), -1);
-		touch(abs(vb - va), +1);
+		int vb = (p + lag == pa) ? na : (p + lag == pb ? nb : ob);
+		touch(pair_value(absolute, oa, ob), -1);
+		touch(pair_value(absolute, va, vb), +1);
 	}
 	int diff = 0;
 	for (int z = 0; z < nk; ++z) {
@@ -273,7 +276,8 @@ __device__ __noinline__ int absdiff_delta(const int32_t* blob, int c2v_off_sec, 
 template <class WS>
 __device__ __forceinline__ int absdiff_delta(const MV& mv, const WS& s, int c, int pa, int na, int pb, int nb)
 {
-	return absdiff_delta(mv.m.blob, mv.m.o.c2v_off, mv.m.o.c2v, mv.m.o.cnt_tab, s.x, s.cnt32, c, pa, na, pb, nb);
+	const bool absolute = mv.kind(c) == GHOST_KIND_ALL_DIFFERENT_ABS_DIFF;
+	return absdiff_delta(mv.m.blob, mv.m.o.c2v_off, mv.m.o.c2v, mv.m.o.cnt_tab, s.x, s.cnt32, c, pa, na, pb, nb, absolute ? 1 : mv.rhs(c), absolute);
 }
 
 // AllEqual (src/global_constraints/all_equal.cpp:47-95): error = scope size - largest count; the delta of
@@ -391,7 +395,7 @@ __device__ inline int constraint_delta(const MV& mv, const WS& s, int c, int va,
 		if (na == oa) return 0;
 		return s.cnt(tab + ea + na) - (s.cnt(tab + ea + oa) - 1);
 	}
-	if (kind == GHOST_KIND_ALL_DIFFERENT_ABS_DIFF) return absdiff_delta(mv, s, c, ea, na, vb >= 0 ? eb : -1, nb);
+	if (kind == GHOST_KIND_ALL_DIFFERENT_ABS_DIFF || kind == GHOST_KIND_ALL_DIFFERENT_LAG_DIFF) return absdiff_delta(mv, s, c, ea, na, vb >= 0 ? eb : -1, nb);
 	if (kind == GHOST_KIND_ALL_EQUAL) {
 		const int tab = mv.cnt_tab(c), oa = s.x[va];
 		if (vb >= 0) {
@@ -446,8 +450,10 @@ __device__ __forceinline__ int recompute_all_impl(const DevModel& m, const WS& s
 			else if (kind == GHOST_KIND_FIX_VALUE) val = abs(xu - mv.rhs(c));
 			else if (kind == GHOST_KIND_ALL_DIFFERENT || kind == GHOST_KIND_ALL_EQUAL) s.cnt_add(mv.cnt_tab(c) + xu, 1);
 			else if (kind == GHOST_KIND_ALL_DIFFERENT_OFFSET) s.cnt_add(mv.cnt_tab(c) + xu + mv.ld(m.o.ent_coef, i), 1);
-			else if (kind == GHOST_KIND_ALL_DIFFERENT_ABS_DIFF) {
-				if (i + 1 < mv.scope_begin(c + 1)) s.cnt_add(mv.cnt_tab(c) + abs(s.x[mv.scope_var(i + 1)] - xu), 1);
+			else if (kind == GHOST_KIND_ALL_DIFFERENT_ABS_DIFF || kind == GHOST_KIND_ALL_DIFFERENT_LAG_DIFF) {
+				const bool absolute = kind == GHOST_KIND_ALL_DIFFERENT_ABS_DIFF;
+				const int lag = absolute ? 1 : mv.rhs(c);
+				if (i + lag < mv.scope_begin(c + 1)) s.cnt_add(mv.cnt_tab(c) + pair_value(absolute, xu, s.x[mv.scope_var(i + lag)]), 1);
 			}
 		}
 		// inclusive segmented scan by constraint id
@@ -1626,25 +1632,29 @@ __device__ inline void apply_move(const DevModel& m, const WS& s, int v, int new
 		// refresh the |difference| tables of the extension kind from the new assignment
 		for (int k = tid; k < naff; k += T) {
 			int c = s.upd[2 * k];
-			if (c < 0 || mv.kind(c) != GHOST_KIND_ALL_DIFFERENT_ABS_DIFF) continue;
+			if (c < 0) continue;
+			const int kd = mv.kind(c);
+			if (kd != GHOST_KIND_ALL_DIFFERENT_ABS_DIFF && kd != GHOST_KIND_ALL_DIFFERENT_LAG_DIFF) continue;
+			const bool absolute = kd == GHOST_KIND_ALL_DIFFERENT_ABS_DIFF;
+			const int lag = absolute ? 1 : mv.rhs(c);
 			int b = mv.scope_begin(c), n = mv.scope_begin(c + 1) - b, tab = mv.cnt_tab(c);
 			int2 e = (k < degv) ? mv.row_entry(rbv + k) : mv.row_entry(rbj + (k - degv));
 			int pa = e.y, pb = -1;
 			if (k < degv && m.permutation)
 				for (int r = rbj; r < rbj + degj; ++r) { int2 f = mv.row_entry(r); if (f.x == c) { pb = f.y; break; } }
 			int pairs[4]; int np = 0;
-			auto add_pair = [&](int p) { if (p < 0 || p + 1 >= n) return; for (int z = 0; z < np; ++z) if (pairs[z] == p) return; pairs[np++] = p; };
-			add_pair(pa - 1); add_pair(pa);
-			if (pb >= 0) { add_pair(pb - 1); add_pair(pb); }
+			auto add_pair = [&](int p) { if (p < 0 || p + lag >= n) return; for (int z = 0; z < np; ++z) if (pairs[z] == p) return; pairs[np++] = p; };
+			add_pair(pa - lag); add_pair(pa);
+			if (pb >= 0) { add_pair(pb - lag); add_pair(pb); }
 			int va = (k < degv) ? v : j, vb2 = (k < degv) ? j : -1;
 			for (int z = 0; z < np; ++z) {
-				int ua = mv.scope_var(b + pairs[z]), ub = mv.scope_var(b + pairs[z] + 1);
+				int ua = mv.scope_var(b + pairs[z]), ub = mv.scope_var(b + pairs[z] + lag);
 				int na = s.x[ua], nb = s.x[ub];
 				// old values: undo the write
 				int oa = (ua == va) ? (k < degv ? xv : xj) : ((ua == vb2 && pb >= 0) ? xj : na);
 				int ob = (ub == va) ? (k < degv ? xv : xj) : ((ub == vb2 && pb >= 0) ? xj : nb);
-				s.cnt_add(tab + abs(ob - oa), -1);
-				s.cnt_add(tab + abs(nb - na), +1);
+				s.cnt_add(tab + pair_value(absolute, oa, ob), -1);
+				s.cnt_add(tab + pair_value(absolute, na, nb), +1);
 			}
 		}
 		G::sync();

@@ -25,6 +25,7 @@ PURE_OPTIMIZATION = 8
 ALL_DIFFERENT_ABS_DIFF = 9
 ALL_EQUAL = 10
 ALL_DIFFERENT_OFFSET = 11
+ALL_DIFFERENT_LAG_DIFF = 12
 KIND_USER = 100
 
 OBJ_NONE = 0
@@ -195,6 +196,10 @@ class ModelDesc:
         offsets = [float(int(o)) for o in offsets]
         assert len(offsets) == len(variables)
         self.constraints.append((ALL_DIFFERENT_OFFSET, variables, offsets, 0.0))
+
+    def all_different_lag_diff(self, variables, lag):
+        """Extension kind: the x[i+lag] - x[i] of the scope pairwise different (one row of a Costas difference triangle)."""
+        self.constraints.append((ALL_DIFFERENT_LAG_DIFF, list(variables), None, float(int(lag))))
 
     def all_different_abs_diff(self, variables):
         self.constraints.append((ALL_DIFFERENT_ABS_DIFF, list(variables), None, 0.0))

@@ -88,6 +88,54 @@ class Coordinator:
         return bool(t.item())
 
 
+def search_multi_overlapped(search, coord: Coordinator, optimization: bool, epoch_iterations: int, timeout_us: float,
+                            max_epochs: int = 0, stop_on_first_solution: bool = True):
+    """The same loop on GPUs with the exchange OFF the walkers' critical path: epoch e+1 is queued on the compute
+    stream before the host looks at epoch e's result; the 8-byte key export and its all-reduce run on a side stream
+    behind an event recorded after epoch e.  The stop decision is therefore one epoch stale — harmless: a solved CSP
+    has already raised the job-wide stop flag from inside the kernel (the walkers of every rank poll it through
+    NVLink), so the epoch in flight ends within a few iterations.  `search` is a ghost_b200.capi.Search."""
+    coord.share_stop_flag(search)
+    if timeout_us <= 0 and not max_epochs and (optimization or not stop_on_first_solution):
+        max_epochs = 1
+    compute = torch.cuda.current_stream()
+    side = torch.cuda.Stream()
+    done = torch.cuda.Event()
+    key = torch.zeros(1, dtype=torch.int64, device=coord.device)
+    t0 = time.perf_counter()
+    epochs = launched = 0
+    quality, winner = INT64_MAX >> KEY_WALKER_BITS, 0
+
+    def launch():
+        nonlocal launched
+        search.epoch(epoch_iterations, compute.cuda_stream)
+        launched += 1
+
+    launch()
+    while True:
+        done.record(compute)                     # end of epoch `epochs + 1`
+        more = not (max_epochs and launched >= max_epochs)
+        if more:
+            launch()                             # the next epoch is in the queue before anybody waits
+        side.wait_event(done)
+        with torch.cuda.stream(side):            # every collective of the loop on the side stream: none queues behind an epoch
+            search.export_key(key.data_ptr(), side.cuda_stream)
+            quality, winner = coord.elect(key)   # all-reduce(min); reads the result
+            out_of_time = coord.any_true(timeout_us > 0 and (time.perf_counter() - t0) * 1e6 >= timeout_us)
+        epochs += 1
+        solved_csp = (not optimization) and quality == 0
+        stop = (solved_csp and stop_on_first_solution) or out_of_time or not more
+        if stop:
+            if more:
+                search.request_stop()            # the epoch in flight: end it now (a solved CSP has done so already)
+            break
+    compute.synchronize()
+    res = search.result()
+    solution = coord.broadcast_solution(res["solution"], winner)
+    found = quality < (1 << 38) if optimization else quality == 0
+    return found, winner, quality, solution, epochs
+
+
 def search_multi(search, coord: Coordinator, optimization: bool, epoch_iterations: int, timeout_us: float,
                  max_epochs: int = 0, stop_on_first_solution: bool = True):
     """Epoch loop over any object with .epoch(n), .best_key() and .result() (ghost_b200.capi.Search on

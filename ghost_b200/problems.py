@@ -87,6 +87,18 @@ def costas_array(n: int) -> ModelDesc:
     return m
 
 
+def costas_lag(n: int) -> ModelDesc:
+    """configs[4] without auxiliary variables: s a permutation of 1..n, and for every lag d = 1..n-2 the differences
+    s_{i+d} - s_i pairwise different (extension kind AllDifferentLagDiff) — the difference-triangle model local search
+    is known to solve (cf. Diaz et al., "Constraint-based local search for the Costas array problem"); V = n, C = n - 1."""
+    m = ModelDesc(permutation_problem=True, name=f"costas_lag_{n}")
+    s = [m.add_variable(1, n, index=i) for i in range(n)]
+    m.all_different(s)
+    for d in range(1, n - 1):
+        m.all_different_lag_diff(s, d)
+    return m
+
+
 def all_interval(n: int) -> ModelDesc:
     """configs[2]: all-interval series.  s permutation of 0..n-1 with AllDifferent(s) and the
     extension kind AllDifferentAbsDiff(s) (|s_{i+1}-s_i| pairwise different) — GHOST ships no
@@ -127,6 +139,8 @@ def by_name(name: str) -> ModelDesc:
         return n_queens_offset(int(arg))
     if kind == "n_queens_perm":
         return n_queens_permutation(int(arg))
+    if kind == "costas_lag":
+        return costas_lag(int(arg))
     if kind == "costas":
         return costas_array(int(arg))
     if kind == "all_interval":

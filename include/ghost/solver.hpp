@@ -25,6 +25,7 @@
 #include "global_constraints/all_different.hpp"
 #include "global_constraints/all_different_abs_diff.hpp"
 #include "global_constraints/all_different_offset.hpp"
+#include "global_constraints/all_different_lag_diff.hpp"
 #include "global_constraints/fix_value.hpp"
 #include "global_constraints/linear_equation_eq.hpp"
 #include "global_constraints/linear_equation_neq.hpp"

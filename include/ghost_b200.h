@@ -59,6 +59,9 @@ typedef enum GhostConstraintKind {
 	                                     (include/global_constraints/all_different.hpp:46-74); error and delta are
 	                                     its own (all_different.cpp:59-100) on the shifted values.  The integer
 	                                     offsets travel in ctr_coefs.                                             */
+	GHOST_KIND_ALL_DIFFERENT_LAG_DIFF = 12, /* extension: the signed differences x[i+lag] - x[i] over the scope, in scope
+	                                     order, pairwise different (row `lag` of the difference triangle of a Costas
+	                                     array); error = sum_values C(count,2) as AllDifferent's; lag >= 1 in ctr_param  */
 	GHOST_KIND_USER = 100
 } GhostConstraintKind;
 

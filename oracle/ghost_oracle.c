@@ -85,6 +85,7 @@ struct OracleModel {
 	int32_t  max_candidates;
 };
 
+static int pair_lag(const struct OracleModel* m, int c) { return m->kind[c] == GHOST_KIND_ALL_DIFFERENT_LAG_DIFF ? (int)m->cparam[c] : 1; }
 static int cmp_i32(const void* a, const void* b)
 {
 	int32_t x = *(const int32_t*)a, y = *(const int32_t*)b;
@@ -94,8 +95,12 @@ static int cmp_i32(const void* a, const void* b)
 static int is_alldiff_like(int32_t kind) /* kinds that keep a value-count table */
 {
 	return kind == GHOST_KIND_ALL_DIFFERENT || kind == GHOST_KIND_ALL_DIFFERENT_ABS_DIFF || kind == GHOST_KIND_ALL_EQUAL
-	    || kind == GHOST_KIND_ALL_DIFFERENT_OFFSET;
+	    || kind == GHOST_KIND_ALL_DIFFERENT_OFFSET || kind == GHOST_KIND_ALL_DIFFERENT_LAG_DIFF;
 }
+/* the two pair-difference kinds: |x[p+1] - x[p]| (ABS_DIFF) and x[p+lag] - x[p] (LAG_DIFF, lag = its parameter) */
+static int is_pair_diff(int32_t kind) { return kind == GHOST_KIND_ALL_DIFFERENT_ABS_DIFF || kind == GHOST_KIND_ALL_DIFFERENT_LAG_DIFF; }
+static int pair_lag(const struct OracleModel* m, int c);
+static int32_t pair_value(int32_t kind, int32_t first, int32_t second) { return kind == GHOST_KIND_ALL_DIFFERENT_ABS_DIFF ? abs(second - first) : second - first; }
 static int is_linear(int32_t kind) { return kind >= GHOST_KIND_LINEAR_EQ && kind <= GHOST_KIND_LINEAR_G; }
 
 OracleModel* oracle_model_create(const GhostModelDesc* d)
@@ -169,6 +174,7 @@ OracleModel* oracle_model_create(const GhostModelDesc* d)
 		}
 		if (lo > hi) { lo = 0; hi = 0; }
 		if (m->kind[c] == GHOST_KIND_ALL_DIFFERENT_ABS_DIFF) { hi = hi - lo; lo = 0; }
+		if (m->kind[c] == GHOST_KIND_ALL_DIFFERENT_LAG_DIFF) { hi = hi - lo; lo = -hi; } /* signed differences */
 		m->cnt_off[c] = m->cnt_total;
 		m->cnt_base[c] = lo;
 		m->cnt_size[c] = hi - lo + 1;
@@ -267,11 +273,13 @@ static double ctr_error(Walker* w, int c)
 			if (cnt[t] > 1) counter += binomial_with_2(cnt[t]);
 		return counter;
 	}
-	case GHOST_KIND_ALL_DIFFERENT_ABS_DIFF: {
-		/* extension: same SOFT_ALLDIFF measure on the |x[i+1]-x[i]| of the scope */
+	case GHOST_KIND_ALL_DIFFERENT_ABS_DIFF:
+	case GHOST_KIND_ALL_DIFFERENT_LAG_DIFF: {
+		/* extensions: same SOFT_ALLDIFF measure on the |x[i+1]-x[i]|, resp. the x[i+lag]-x[i], of the scope */
 		int32_t* cnt = w->count + m->cnt_off[c];
+		const int lag = pair_lag(m, c);
 		memset(cnt, 0, sizeof(int32_t) * m->cnt_size[c]);
-		for (int i = b; i + 1 < e; ++i) cnt[abs(w->x[m->cvars[i + 1]] - w->x[m->cvars[i]])]++;
+		for (int i = b; i + lag < e; ++i) cnt[pair_value(m->kind[c], w->x[m->cvars[i]], w->x[m->cvars[i + lag]]) - m->cnt_base[c]]++;
 		double counter = 0;
 		for (int t = 0; t < m->cnt_size[c]; ++t)
 			if (cnt[t] > 1) counter += binomial_with_2(cnt[t]);
@@ -357,19 +365,22 @@ static double ctr_delta(const Walker* w, int c, int n, const int32_t* vars, cons
 		}
 		return diff;
 	}
-	case GHOST_KIND_ALL_DIFFERENT_ABS_DIFF: {
-		/* extension: remove the |differences| of every scope pair touching a changed variable,
+	case GHOST_KIND_ALL_DIFFERENT_ABS_DIFF:
+	case GHOST_KIND_ALL_DIFFERENT_LAG_DIFF: {
+		/* extensions: remove the differences of every scope pair touching a changed variable,
 		 * add the new ones, compare C(count,2) over the touched keys (each key once). */
 		const int32_t* cnt = w->count + m->cnt_off[c];
+		const int lag = pair_lag(m, c);
+		const int32_t kind = m->kind[c], base = m->cnt_base[c];
 		int b = m->coff[c], e = m->coff[c + 1];
 		int32_t pairs[8]; int np = 0;
 		for (int i = 0; i < n; ++i)
 			for (int p = b; p < e; ++p)
 				if (m->cvars[p] == vars[i]) {
-					int cand[2] = { p - 1, p };
+					int cand[2] = { p - lag, p };
 					for (int q = 0; q < 2; ++q) {
 						int pp = cand[q];
-						if (pp < b || pp + 1 >= e) continue;
+						if (pp < b || pp + lag >= e) continue;
 						int seen = 0;
 						for (int z = 0; z < np; ++z) if (pairs[z] == pp) seen = 1;
 						if (!seen) pairs[np++] = pp;
@@ -377,11 +388,11 @@ static double ctr_delta(const Walker* w, int c, int n, const int32_t* vars, cons
 				}
 		Touched t; t.n = 0;
 		for (int z = 0; z < np; ++z) {
-			int va = m->cvars[pairs[z]], vb = m->cvars[pairs[z] + 1];
+			int va = m->cvars[pairs[z]], vb = m->cvars[pairs[z] + lag];
 			int32_t oa = w->x[va], ob = w->x[vb], na = oa, nb = ob;
 			for (int i = 0; i < n; ++i) { if (vars[i] == va) na = vals[i]; if (vars[i] == vb) nb = vals[i]; }
-			*touched_slot(&t, cnt, abs(ob - oa)) -= 1;
-			*touched_slot(&t, cnt, abs(nb - na)) += 1;
+			*touched_slot(&t, cnt, pair_value(kind, oa, ob) - base) -= 1;
+			*touched_slot(&t, cnt, pair_value(kind, na, nb) - base) += 1;
 		}
 		double diff = 0.0;
 		for (int i = 0; i < t.n; ++i)
@@ -751,11 +762,12 @@ static void abs_diff_rebuild(Walker* w)
 	/* extension kind: refresh the difference counts after values were written */
 	const OracleModel* m = w->m;
 	for (int c = 0; c < m->C; ++c)
-		if (m->kind[c] == GHOST_KIND_ALL_DIFFERENT_ABS_DIFF) {
+		if (is_pair_diff(m->kind[c])) {
 			int32_t* cnt = w->count + m->cnt_off[c];
+			const int lag = pair_lag(m, c);
 			memset(cnt, 0, sizeof(int32_t) * m->cnt_size[c]);
-			for (int i = m->coff[c]; i + 1 < m->coff[c + 1]; ++i)
-				cnt[abs(w->x[m->cvars[i + 1]] - w->x[m->cvars[i]])]++;
+			for (int i = m->coff[c]; i + lag < m->coff[c + 1]; ++i)
+				cnt[pair_value(m->kind[c], w->x[m->cvars[i]], w->x[m->cvars[i + lag]]) - m->cnt_base[c]]++;
 		}
 }
 

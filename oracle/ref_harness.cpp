@@ -119,6 +119,42 @@ public:
 	HarnessAllDifferentAbsDiff( const std::vector<int>& ids ) : Constraint( ids ) { }
 };
 
+/* AllDifferentLagDiff: the x[i+lag] - x[i] of the scope must be pairwise different (one row of the difference triangle
+ * of a Costas array); SOFT_ALLDIFF measure on those differences.  No cache: the delta recounts from the scope. */
+class HarnessAllDifferentLagDiff : public Constraint
+{
+	int _lag;
+	double pairs( const std::vector<int>& values ) const
+	{
+		std::map<int,int> count;
+		for( size_t i = 0 ; i + _lag < values.size() ; ++i )
+			++count[ values[i+_lag] - values[i] ];
+		double e = 0;
+		for( auto& kv : count )
+			if( kv.second > 1 )
+				e += static_cast<double>( kv.second ) * ( kv.second - 1 ) / 2;
+		return e;
+	}
+	double required_error( const std::vector<Variable*>& variables ) const override
+	{
+		std::vector<int> values;
+		for( auto v : variables ) values.push_back( v->get_value() );
+		return pairs( values );
+	}
+	double optional_delta_error( const std::vector<Variable*>& variables,
+	                             const std::vector<int>& indexes,
+	                             const std::vector<int>& candidate_values ) const override
+	{
+		std::vector<int> values;
+		for( auto v : variables ) values.push_back( v->get_value() );
+		double before = pairs( values );
+		for( size_t i = 0 ; i < indexes.size() ; ++i ) values[ indexes[i] ] = candidate_values[i];
+		return pairs( values ) - before;
+	}
+public:
+	HarnessAllDifferentLagDiff( const std::vector<int>& ids, int lag ) : Constraint( ids ), _lag( lag ) { }
+};
+
 /* AllDifferentOffset: the x_i + o_i of the scope must be pairwise different (n-queens diagonals); the error is
  * AllDifferent's own measure (src/global_constraints/all_different.cpp:59-75) on the shifted values.  No cache:
  * the delta recounts from the scope, as a user who does not override conditional_update_data_structures gets. */
@@ -242,6 +278,7 @@ public:
 			case GHOST_KIND_FIX_VALUE:  constraints.emplace_back( std::make_shared<FixValue>( ids, static_cast<int>( p ) ) ); break;
 			case GHOST_KIND_ALL_DIFFERENT_ABS_DIFF: constraints.emplace_back( std::make_shared<HarnessAllDifferentAbsDiff>( ids ) ); break;
 			case GHOST_KIND_ALL_EQUAL: constraints.emplace_back( std::make_shared<AllEqual>( ids ) ); break;
+			case GHOST_KIND_ALL_DIFFERENT_LAG_DIFF: constraints.emplace_back( std::make_shared<HarnessAllDifferentLagDiff>( ids, static_cast<int>( p ) ) ); break;
 			case GHOST_KIND_ALL_DIFFERENT_OFFSET: constraints.emplace_back( std::make_shared<HarnessAllDifferentOffset>( ids, coef ) ); break;
 			case GHOST_KIND_PURE_OPTIMIZATION: break; /* build_model() inserts PureOptimization when there is no constraint */
 			default: break;

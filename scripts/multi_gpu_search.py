@@ -27,6 +27,8 @@ def main():
     ap.add_argument("--epoch", type=int, default=64)
     ap.add_argument("--timeout", type=float, default=20.0)
     ap.add_argument("--seed", type=int, default=1)
+    ap.add_argument("--seeds", type=int, default=1, help="runs (seed, seed+1, ...): median time to solution")
+    ap.add_argument("--out", default="", help="rank 0 writes the JSON line here too")
     args = ap.parse_args()
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local_rank)
@@ -37,19 +39,38 @@ def main():
     model = capi.Model(desc)
     opts = default_opts(seed=args.seed, number_walkers=args.walkers, first_walker_id=coord.first_walker_id(args.walkers),
                         stop_on_first_solution=1)
-    search = model.begin(opts)
-    t0 = time.perf_counter()
-    found, winner, quality, solution, epochs = multi.search_multi(
-        search, coord, desc.objective_kind != 0, args.epoch, args.timeout * 1e6)
-    dt = time.perf_counter() - t0
-    total = coord.sum_counters(search.result()["total"])
+    runs = []
+    total_evals = total_iters = total_s = 0.0
+    for k in range(args.seeds):
+        opts.seed = args.seed + k
+        search = model.begin(opts)
+        if dist.is_initialized():
+            dist.barrier()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        found, winner, quality, solution, epochs = multi.search_multi_overlapped(
+            search, coord, desc.objective_kind != 0, args.epoch, args.timeout * 1e6)
+        dt = time.perf_counter() - t0
+        total = coord.sum_counters(search.result()["total"])
+        total_evals += total["candidates_evaluated"]; total_iters += total["search_iterations"]; total_s += dt
+        err = None
+        if coord.rank == 0:
+            from oracle import binding  # checker only
+            err, _ = binding.OraclePort(desc).check(solution)
+            assert (err == 0.0) == bool(found) or desc.objective_kind != 0, (err, found)
+        runs.append(dict(seed=opts.seed, found=bool(found), seconds=dt, epochs=epochs, winner_rank=winner, checked_error=err))
+        search.end()
     if coord.rank == 0:
-        from oracle import binding  # checker only
-        err, obj = binding.OraclePort(desc).check(solution)
-        print(json.dumps({"workload": args.workload, "world": coord.world, "found": bool(found), "winner_rank": winner,
-                          "quality": quality, "checked_error": err, "objective": obj, "epochs": epochs, "seconds": dt,
-                          "evals_per_s": total["candidates_evaluated"] / dt, "iters_per_s": total["search_iterations"] / dt}))
-    search.end()
+        times = sorted(r["seconds"] if r["found"] else float("inf") for r in runs)
+        line = {"workload": args.workload, "world": coord.world, "walkers_per_gpu": args.walkers, "epoch_iterations": args.epoch,
+                "exchange": "per-epoch NCCL all-reduce(min) of the packed best key on a side stream; job-wide stop flag over CUDA IPC",
+                "time_to_solution": {"median_s": times[len(times) // 2], "min_s": times[0], "max_s": times[-1], "seeds": len(runs),
+                                     "solved": sum(r["found"] for r in runs), "timeout_s": args.timeout},
+                "evals_per_s": total_evals / total_s, "iters_per_s": total_iters / total_s, "runs": runs}
+        print(json.dumps(line))
+        if args.out:
+            with open(args.out, "w") as f:
+                f.write(json.dumps(line) + "\n")
     model.close()
     if dist.is_initialized():
         dist.destroy_process_group()

@@ -25,7 +25,7 @@ from tests.helpers import model_by_name, random_assignment  # noqa: E402
 
 MODELS = ["magic_square:3", "magic_square:6", "n_queens:8", "costas:5", "knapsack:12x3", "all_interval:8", "mixed",
           "mixed_perm", "magic_square:30", "n_queens:100", "costas:20", "mixed_eq", "mixed_perm_eq", "weighted_perm", "n_queens_offset:8",
-          "n_queens_perm:9", "n_queens_offset:100"]
+          "n_queens_perm:9", "n_queens_offset:100", "costas_lag:8", "costas_lag:20"]
 CASES = {"magic_square:30": 3, "n_queens:100": 4, "costas:20": 4, "n_queens_offset:100": 6}
 
 

@@ -9,7 +9,7 @@ from ghost_b200 import problems
 from ghost_b200.modeldesc import NOT_A_CANDIDATE, ModelDesc
 
 SMALL_MODELS = ["magic_square:4", "magic_square:7", "n_queens:8", "n_queens:20", "costas:6", "costas:9",
-                "knapsack:20x3", "knapsack:50x5", "all_interval:10", "n_queens_offset:12", "n_queens_perm:11"]
+                "knapsack:20x3", "knapsack:50x5", "all_interval:10", "n_queens_offset:12", "n_queens_perm:11", "costas_lag:9"]
 
 
 def random_assignment(desc: ModelDesc, rng: np.random.Generator):
@@ -201,7 +201,7 @@ COMPLETE_MODELS = {
 
 # models whose full solution list from the reference is committed in tests/golden/complete/solutions.json
 COMPLETE_GOLDEN = list(COMPLETE_MODELS) + ["n_queens:6", "all_interval:7", "costas:5", "knapsack:12x3", "magic_square:3",
-                                            "mixed_perm_eq", "n_queens_offset:6", "n_queens_perm:7"]
+                                            "mixed_perm_eq", "n_queens_offset:6", "n_queens_perm:7", "costas_lag:6"]
 
 
 def model_by_name(name):

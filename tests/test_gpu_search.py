@@ -54,14 +54,14 @@ def _check_against_oracle(desc, oracle_built, iterations, walkers, seed, threads
 
 @pytest.mark.parametrize("name", ["magic_square:4", "magic_square:7", "n_queens:8", "n_queens:20", "costas:6",
                                   "costas:9", "knapsack:20x3", "knapsack:50x5", "all_interval:10", "mixed",
-                                  "mixed_perm", "mixed_eq", "mixed_perm_eq", "n_queens_offset:12", "n_queens_perm:11", "weighted_perm"])
+                                  "mixed_perm", "mixed_eq", "mixed_perm_eq", "n_queens_offset:12", "n_queens_perm:11", "weighted_perm", "costas_lag:9"])
 def test_trajectories_match_oracle(name, oracle_built):
     _check_against_oracle(model_by_name(name), oracle_built, iterations=600, walkers=12, seed=2024)
 
 
 @pytest.mark.parametrize("threads", [32, 64, 128, 256])
 @pytest.mark.parametrize("name", ["magic_square:7", "n_queens:20", "mixed_perm", "knapsack:50x5", "mixed_perm_eq", "n_queens_perm:11",
-                                  "n_queens_offset:12"])
+                                  "n_queens_offset:12", "costas_lag:9"])
 def test_trajectories_every_mapping(name, threads, oracle_built):
     _check_against_oracle(model_by_name(name), oracle_built, iterations=300, walkers=5, seed=5, threads=threads)
 
@@ -89,7 +89,7 @@ def test_custom_start_and_options(oracle_built):
 
 
 @pytest.mark.parametrize("name", ["magic_square:30", "n_queens:100", "costas:20", "knapsack:500x30", "all_interval:500",
-                                  "n_queens_offset:100"])
+                                  "n_queens_offset:100", "costas_lag:20"])
 def test_trajectories_baseline_sizes(name, oracle_built):
     """BASELINE.json's five configurations at full size (and config 0 in its three-constraint form), few walkers and
     iterations (oracle speed)."""
