@@ -240,36 +240,50 @@ __device__ __forceinline__ int binom2(int n) { return (n * (n - 1)) >> 1; } // a
 // The two pair-difference kinds share one code path: AllDifferentAbsDiff is (lag 1, absolute values),
 // AllDifferentLagDiff (lag = its parameter, signed differences x[p+lag] - x[p]).
 __device__ __forceinline__ int pair_value(bool absolute, int first, int second) { return absolute ? abs(second - first) : second - first; }
+// Delta of changing scope position pa to na and, when pb >= 0, pb to nb.  At most four pairs (p, p + lag) are touched:
+// those starting at pa - lag, pa, pb - lag, pb.  Their old differences are taken out of the counts and the new ones put
+// in ONE AT A TIME: removing a value whose count is c lowers sum C(count,2) by c - 1, adding one raises it by c, the
+// effective count being the table's minus the removals so far plus the additions so far of that value — all in
+// registers, no scratch arrays.  A pair that does not exist (or is the duplicate that arises when |pa - pb| = lag) is
+// replaced by "remove 0, add 0", which cancels.
 template <class XT>
 __device__ __noinline__ int absdiff_delta(const int32_t* blob, int c2v_off_sec, int c2v_sec, int cnt_tab_sec,
                                           const XT* x, const unsigned* cnt32, int c, int pa, int na, int pb, int nb, int lag, bool absolute)
 {
-	int b = __ldg(blob + c2v_off_sec + c), n = __ldg(blob + c2v_off_sec + c + 1) - b, tab = __ldg(blob + cnt_tab_sec + c);
-	int pairs[4]; int np = 0;
-	auto add_pair = [&](int p) {
-		if (p < 0 || p + lag >= n) return;
-		for (int z = 0; z < np; ++z) if (pairs[z] == p) return;
-		pairs[np++] = p;
-	};
-	add_pair(pa - lag); add_pair(pa);
-	if (pb >= 0) { add_pair(pb - lag); add_pair(pb); }
-	int keys[8], net[8]; int nk = 0;
-	auto touch = [&](int key, int d) {
-		for (int z = 0; z < nk; ++z) if (keys[z] == key) { net[z] += d; return; }
-		keys[nk] = key; net[nk] = d; ++nk;
-	};
-	for (int z = 0; z < np; ++z) {
-		int p = pairs[z];
-		int oa = x[__ldg(blob + c2v_sec + b + p)], ob = x[__ldg(blob + c2v_sec + b + p + lag)];
-		int va = (p == pa) ? na : (p == pb ? nb : oa);
-		int vb = (p + lag == pa) ? na : (p + lag == pb ? nb : ob);
-		touch(pair_value(absolute, oa, ob), -1);
-		touch(pair_value(absolute, va, vb), +1);
+	const int b = __ldg(blob + c2v_off_sec + c), n = __ldg(blob + c2v_off_sec + c + 1) - b;
+	const unsigned short* cnt = reinterpret_cast<const unsigned short*>(cnt32) + __ldg(blob + cnt_tab_sec + c);
+	int first[4] = { pa - lag, pa, pb - lag, pb };
+	if (pb < 0) { first[2] = -1; first[3] = -1; }
+	else { if (pb - lag == pa) first[2] = -1; if (pa - lag == pb) first[0] = -1; }
+	int ko[4], kn[4];
+#pragma unroll
+	for (int z = 0; z < 4; ++z) {
+		const int p = first[z];
+		ko[z] = 0; kn[z] = 0;
+		if (p >= 0 && p + lag < n) {
+			const int oa = x[__ldg(blob + c2v_sec + b + p)], ob = x[__ldg(blob + c2v_sec + b + p + lag)];
+			const int va = (p == pa) ? na : (p == pb ? nb : oa);
+			const int vb = (p + lag == pa) ? na : (p + lag == pb ? nb : ob);
+			ko[z] = pair_value(absolute, oa, ob);
+			kn[z] = pair_value(absolute, va, vb);
+		}
 	}
 	int diff = 0;
-	for (int z = 0; z < nk; ++z) {
-		int cur = reinterpret_cast<const unsigned short*>(cnt32)[tab + keys[z]];
-		diff += binom2(cur + net[z]) - binom2(cur);
+#pragma unroll
+	for (int i = 0; i < 4; ++i) {
+		int ceff = cnt[ko[i]];
+#pragma unroll
+		for (int j = 0; j < i; ++j) ceff -= ko[j] == ko[i] ? 1 : 0;
+		diff -= ceff - 1;
+	}
+#pragma unroll
+	for (int i = 0; i < 4; ++i) {
+		int ceff = cnt[kn[i]];
+#pragma unroll
+		for (int j = 0; j < 4; ++j) ceff -= ko[j] == kn[i] ? 1 : 0;
+#pragma unroll
+		for (int j = 0; j < i; ++j) ceff += kn[j] == kn[i] ? 1 : 0;
+		diff += ceff;
 	}
 	return diff;
 }
@@ -764,7 +778,7 @@ __device__ inline int hoist_variable(const DevModel& m, const WS& s, int v, int*
 		int contrib = 0;
 		if (valid) {
 			const int cls = ell_cls(e.x);
-			int4 h = make_int4(cls | (ell_w(e.x) << 4) | (c << 8), 0, 0, 0);
+			int4 h = make_int4(cls | (ell_w(e.x) << 4) | (c << 8), 0, 0, ell_universal(e.x) ? 1 : 0);   // .w: the scope is every variable
 			if (cls == GB_CLS_LINEAR) {
 				h.y = e.y; h.z = s.T_of(c) - e.y * xv;
 				contrib = -s.err_of(c);
@@ -892,7 +906,13 @@ __device__ __forceinline__ bool candidate_sum(const DevModel& m, const MV& mv, c
 	int sum = bias;
 	const int dx = xv - xj;
 	const int2* row = mv.ell_row(j);
-	for (int k = 0; k < nh; ++k) sum += hoisted_term(mv, s, s.hoist[k], xj);
+	for (int k = 0; k < nh; ++k) {
+		const int4 h = s.hoist[k];
+		// a pair-difference constraint over ALL variables holds the partner too: its single-variable term would only be
+		// taken out again by the two-variable one below (two recounts out of three saved on a Costas model)
+		if ((h.x & 0xF) == GB_CLS_ABSDIFF && h.w) continue;
+		sum += hoisted_term(mv, s, h, xj);
+	}
 	for (int k = 0; k < m.ell_stride; ++k) {
 		int2 e = __ldg(row + k);
 		int c = ell_ctr(e.x);
@@ -924,7 +944,7 @@ __device__ __forceinline__ bool candidate_sum(const DevModel& m, const MV& mv, c
 				sum += alldiff_four_key_delta(s, h.y + xv, h.y + xj, tabj + xj, tabj + xv) - (s.cnt(h.y + xj) - h.z);
 			}
 			else if (cls == GB_CLS_FIX) sum += abs(xv - h.y) - abs(xj - h.y);
-			else if (cls == GB_CLS_ABSDIFF) sum += absdiff_delta(mv, s, c, h.y, xj, e.y, xv) - absdiff_delta(mv, s, c, h.y, xj, -1, 0);
+			else if (cls == GB_CLS_ABSDIFF) sum += absdiff_delta(mv, s, c, h.y, xj, e.y, xv) - (h.w ? 0 : absdiff_delta(mv, s, c, h.y, xj, -1, 0));
 			else if (cls == GB_CLS_ALLEQ) sum += max(s.cnt(h.y + xj) + 1, h.z) - alleq_max1(st.x); // the swap changes nothing
 		}
 	}
