@@ -51,6 +51,8 @@ struct GhostSearch {
 	int* d_stop_peer = nullptr;     // another search's stop flag, mapped over NVLink; used instead of d_stop when set
 	bool stop_peer_is_ipc = false;  // mapped from another process (CUDA IPC) rather than a peer device of this one
 	unsigned long long* d_best_key = nullptr;
+	int* d_elite_x = nullptr;             // cooperative walkers: best assignment so far [V] + its key
+	unsigned long long* d_elite_key = nullptr;
 	int* d_trace = nullptr; int* d_trace_len = nullptr; int trace_cap = 0;
 	cudaEvent_t ev0 = nullptr, ev1 = nullptr;
 	double kernel_ms = 0.0;
@@ -259,7 +261,7 @@ extern "C" void ghost_b200_search_end(GhostSearch* s)
 	if (!s) return;
 	if (s->d_stop_peer && s->stop_peer_is_ipc) cudaIpcCloseMemHandle(s->d_stop_peer);
 	cudaFree(s->d_state); cudaFree(s->d_scalars); cudaFree(s->d_best_x); cudaFree(s->d_stop); cudaFree(s->d_finished);
-	cudaFree(s->d_best_key); cudaFree(s->d_trace); cudaFree(s->d_trace_len);
+	cudaFree(s->d_best_key); cudaFree(s->d_trace); cudaFree(s->d_trace_len); cudaFree(s->d_elite_x); cudaFree(s->d_elite_key);
 	if (s->ev0) cudaEventDestroy(s->ev0);
 	if (s->ev1) cudaEventDestroy(s->ev1);
 	delete s;
@@ -319,6 +321,12 @@ extern "C" int ghost_b200_search_begin(GhostModel* gm, const GhostSearchOpts* op
 	TRY_OR_END(cudaMalloc(&s->d_finished, sizeof(int)));
 	TRY_OR_END(cudaMemset(s->d_finished, 0, sizeof(int)));
 	TRY_OR_END(cudaMemset(s->d_best_key, 0xff, sizeof(unsigned long long)));
+	if (s->opts.elite_restart_percent > 0) {
+		if (s->opts.elite_restart_percent > 100) s->opts.elite_restart_percent = 100;
+		TRY_OR_END(cudaMalloc(&s->d_elite_x, (size_t)m.V * sizeof(int)));
+		TRY_OR_END(cudaMalloc(&s->d_elite_key, sizeof(unsigned long long)));
+		TRY_OR_END(cudaMemset(s->d_elite_key, 0xff, sizeof(unsigned long long)));
+	}
 	if (s->opts.resume_search) {
 		std::vector<WalkerScalars> init(W);
 		std::memset(init.data(), 0, W * sizeof(WalkerScalars));
@@ -362,7 +370,12 @@ extern "C" int ghost_b200_search_epoch(GhostSearch* s, int32_t iterations, void*
 	p.elastic = (s->elastic && s->walkers <= s->resident_walkers) ? 1 : 0;
 	if (p.elastic) CUDA_TRY(cudaMemsetAsync(s->d_finished, 0, sizeof(int), (cudaStream_t)stream));
 	p.trace = s->d_trace; p.trace_cap = s->trace_cap; p.trace_walker = 0; p.trace_len = s->d_trace_len;
+	p.elite_x = s->d_elite_x; p.elite_key = s->d_elite_key; p.elite_percent = s->d_elite_x ? o.elite_restart_percent : 0;
 	CUDA_TRY(launch_search(s->T, s->grid, s->block, s->smem, (cudaStream_t)stream, s->model->low.dev, s->layout, p));
+	if (s->d_elite_x) {
+		elite_update_kernel<<<1, 256, 0, (cudaStream_t)stream>>>(s->d_best_key, s->d_best_x, s->model->low.V, s->d_elite_x, s->d_elite_key);
+		CUDA_TRY(cudaGetLastError());
+	}
 	s->launches += 1;
 	return GHOST_B200_OK;
 }

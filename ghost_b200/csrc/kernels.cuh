@@ -24,6 +24,9 @@ struct SearchParams {
 	int* finished;                  // elastic epochs: walkers of this launch that have done their nominal share
 	int elastic;                    // see GhostSearchOpts::elastic_epochs (only set when the whole grid is co-resident)
 	unsigned long long* best_key;   // one packed key, atomicMin
+	const int* elite_x;             // cooperative walkers: the best assignment of the search so far [V] ...
+	const unsigned long long* elite_key; // ... and its packed quality key (all ones: none yet); see GhostSearchOpts::elite_restart_percent
+	int elite_percent;
 	int* trace;                     // optional [trace_cap][8] rows of walker trace_walker
 	int trace_cap, trace_walker;
 	int* trace_len;
@@ -369,8 +372,19 @@ static __device__ __noinline__ ColdState walker_reinit(const DevModel& m, const 
 	} else if (mode == GB_COLD_RESTART) {
 		if (tid == 0) s.counters[K_RESTARTS] += 1;
 	}
+	// Cooperative walkers: a restart may start from the best assignment of the whole search instead of a fresh sample
+	// (one more Philox event, drawn only when the option is on: with 0 percent the trajectories are the oracle's)
+	bool from_elite = false;
+	if (mode == GB_COLD_RESTART && p.elite_percent > 0 && *p.elite_key != ~0ULL) {
+		const uint4 coin = rng.block(rng.next_event++, 0);
+		from_elite = (int)below(coin.x, 100u) < p.elite_percent;
+	}
+	if (from_elite) {
+		for (int v = tid; v < m.V; v += T) s.x[v] = p.elite_x[v];
+		G::sync();
+	}
 	// one call site each (not one per mode): the cold path is several times the size of the hot one as it is
-	if (mode != GB_COLD_PERTURB) initialize_variable_values<T, EQ, F32>(m, L, base, s, r, rng, p, best_x);
+	else if (mode != GB_COLD_PERTURB) initialize_variable_values<T, EQ, F32>(m, L, base, s, r, rng, p, best_x);
 	else if (PERM) random_permutations<T>(m, s, rng, p.nreset);
 	else monte_carlo_sampling<T>(m, s, rng, p.nreset);
 	initialize_data_structures<T, EQ, F32>(m, L, base, s, r, best_x);
@@ -612,6 +626,19 @@ search_kernel(const __grid_constant__ DevModel m, const __grid_constant__ Walker
 		k[K_ITER] = r.iterations;
 		atomicMin(p.best_key, quality_key(optimization, r.best_sat, r.best_opt, w));
 	}
+}
+
+// Cooperative walkers: after a launch, keep the best assignment of the whole search (the launch's winner is in the
+// packed best key; its assignment is current in best_x).  One block.
+static __global__ void elite_update_kernel(const unsigned long long* __restrict__ best_key, const int* __restrict__ best_x, int V,
+                                    int* __restrict__ elite_x, unsigned long long* __restrict__ elite_key)
+{
+	const unsigned long long k = *best_key;
+	if (k == ~0ULL || (k >> 24) >= (*elite_key >> 24)) return;   // uniform over the block
+	const int* src = best_x + (size_t)(k & 0xFFFFFF) * V;
+	for (int v = threadIdx.x; v < V; v += blockDim.x) elite_x[v] = src[v];
+	__syncthreads();
+	if (threadIdx.x == 0) *elite_key = k;
 }
 
 // =================================================================================================

@@ -77,7 +77,7 @@ class GhostSearchOptsStruct(C.Structure):
         ("timeout_us", C.c_double),
         ("max_iterations", C.c_int64),
         ("elastic_epochs", C.c_int32),
-        ("reserved1", C.c_int32),
+        ("elite_restart_percent", C.c_int32),
     ]
 
 
@@ -133,7 +133,7 @@ def default_opts(**overrides) -> GhostSearchOptsStruct:
     o.timeout_us = 0.0
     o.max_iterations = 0
     o.elastic_epochs = 0
-    o.reserved1 = 0
+    o.elite_restart_percent = 0
     for k, v in overrides.items():
         if not hasattr(o, k):
             raise AttributeError(k)

@@ -137,7 +137,11 @@ typedef struct GhostSearchOpts {
 	                              /* how far each one gets per launch varies.  0: auto = on in the blocking,      */
 	                              /* timeout-driven ghost_b200_search / _search_devices, off in the stepwise      */
 	                              /* calls (exactly `iterations` per walker).  -1: off everywhere.                */
-	int32_t reserved1;
+	int32_t elite_restart_percent; /* cooperative walkers: at a RESTART (search_unit.hpp:333-350, every   */
+	                              /* restart_threshold-th reset) a walker starts, with this probability in percent, from     */
+	                              /* the best assignment any walker of the search has reached so far instead of sampling a   */
+	                              /* fresh one (153-198).  0 (default): off — trajectories are then those of independent     */
+	                              /* runs, as in the reference and the oracle.                                               */
 } GhostSearchOpts;
 
 /* Counters: the seven of SearchUnitData (include/search_unit_data.hpp:67-73) plus the

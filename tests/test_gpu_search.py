@@ -291,3 +291,32 @@ def test_search_devices_stops_on_first_solution():
     assert r["found"] and r["final_cost"] == 0.0
     x = r["solution"].reshape(6, 6)
     assert sorted(r["solution"].tolist()) == list(range(1, 37)) and set(x.sum(0)) == {111} and set(x.sum(1)) == {111}
+
+
+def test_elite_restart_cooperative_walkers(oracle_built):
+    """GhostSearchOpts::elite_restart_percent (SURVEY §8(f) row 4): restarting walkers start from the best assignment of
+    the whole search with the given probability.  Off by default (every other test here runs with 0 and equals the
+    oracle's independent walkers); on, the search still returns assignments the checker accepts, restarts do happen,
+    and a walker that restarted from the elite cannot be worse than the elite was."""
+    from ghost_b200 import capi
+    desc = model_by_name("costas_lag:13")
+    port = oracle_built.OraclePort(desc)
+    model = capi.Model(desc)
+    assert default_opts().elite_restart_percent == 0
+    opts = default_opts(seed=4, number_walkers=256, stop_on_first_solution=0, restart_threshold=2, elite_restart_percent=60)
+    s = model.begin(opts)
+    for _ in range(30):
+        s.epoch(64)
+    out = s.walkers(256)
+    res = s.result()
+    s.end()
+    assert res["total"]["restarts"] > 0
+    for w in range(0, 256, 17):
+        e, _ = port.check(out["best_x"][w])
+        assert e == float(out["best_sat"][w])          # each walker's best assignment scores its best error
+    # the blocking call with the option on finds a Costas array the checker accepts
+    r = model.search(default_opts(seed=5, number_walkers=2048, timeout_us=20e6, restart_threshold=3, elite_restart_percent=50))
+    assert r["found"]
+    e, _ = port.check(r["solution"])
+    assert e == 0.0
+    model.close()
