@@ -440,9 +440,11 @@ def main():
                                " (model_create + upload + walker set-up + search + result)", "gpus": e2e_devices,
                        "seconds": dt, "budget_s": args.e2e_seconds, "kernel_launches": r2["kernel_launches"],
                        "runs": [round(t[0], 1) for t in runs], "run_seconds": [round(t[1], 4) for t in runs],
+                       "run_phases_ms": [[round(1e3 * t[4], 1)] + [round(x, 1) for x in t[3]] for t in runs if t[3] is not None],
                        "min": runs[0][0], "median": runs[len(runs) // 2][0], "max": runs[-1][0],
                        "note": f"median of {len(runs)} calls"}
         if phases is not None:
+            line["e2e"]["run_phases_ms_columns"] = ["python_model_create", "search_begin", "epochs", "result", "search_end"]
             line["e2e"]["phases_ms"] = {"python_model_create": round(1e3 * t_model, 3), "search_begin": round(phases[0], 3),
                                         "epochs": round(phases[1], 3), "result": round(phases[2], 3), "search_end": round(phases[3], 3),
                                         "kernels": round(r2["kernel_time_us"] / 1e3, 3)}

@@ -1320,11 +1320,7 @@ __device__ inline int evaluate_sg(const DevModel& m, const WS& s, int v, int nh,
 		const unsigned le = ((unsigned)row.w >> (8 * e)) & 0xFFu;
 		const bool has = le != 0xFFu;
 		const int u = has ? lane * cw + (int)le : 0;
-#ifdef GB_SG_EXTRA_NH
 		const int key = f32_slot_key<NH, S>(m, s, h, u, has ? m.V : 0, has ? out : nullptr);
-#else
-		const int key = f32_slot_key<NH, S>(m, s, h, u, has ? m.V : 0, has ? out : nullptr);
-#endif
 		if (key < q.key) { q.key = key; q.bits = 1u << le; }
 		else if (key == q.key && has) q.bits |= 1u << le;
 	}

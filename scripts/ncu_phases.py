@@ -10,12 +10,15 @@ import bisect, csv, os, re, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 PHASE_OF = {  # device function -> phase
     "philox4x32_10": "philox", "block": "philox", "word": "philox", "below": "philox",
-    "scan_candidates": "scan", "commit_scan_chunk": "scan", "scan_pos": "scan",
+    "scan_candidates": "scan", "commit_scan_chunk": "scan", "scan_pos": "scan", "scan_pass": "scan",
     "regs_count": "pick", "regs_pick_kth_impl": "pick", "regs_pick_kth": "pick", "pick_kth": "pick", "chunks_count": "pick",
     "chunks_min": "pick", "chunks_max": "pick",
     "hoist_variable": "hoist", "hoist_variable_eq": "hoist", "unmark_variable": "hoist", "unmark_variable_eq": "hoist",
     "evaluate_candidates_eq_s": "evaluate", "evaluate_candidates_eq": "evaluate", "evaluate_candidates": "evaluate",
-    "evaluate_structured": "evaluate", "evaluate_candidates_f32": "evaluate",
+    "evaluate_structured": "evaluate", "evaluate_candidates_f32": "evaluate", "evaluate_sg": "evaluate", "evaluate_f32": "evaluate",
+    "hoisted_sum_f32": "evaluate", "f32_slot_key": "evaluate (irregular cells)", "load_hoist_f32": "evaluate", "fetch_summary": "evaluate",
+    "commit_pair": "evaluate", "sg_slot_to_var": "pick", "hoist_variable_f32": "hoist", "unmark_variable_f32": "hoist",
+    "recompute_all_impl": "reset", "recompute_all_cold": "reset", "absdiff_delta": "evaluate", "pair_value": "evaluate", "binom2": "evaluate",
     "candidate_sum": "evaluate", "hoisted_term": "evaluate", "commit_value_chunk": "evaluate",
     "apply_move_eq": "move", "apply_move": "move", "local_move": "move", "constraint_delta": "move", "apply_move_f32": "move",
     "recompute_all": "reset", "walker_reinit": "reset", "initialize_data_structures": "reset", "set_initial_configuration": "reset",
