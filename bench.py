@@ -277,18 +277,25 @@ def main():
     flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device="cuda")  # > 126 MB L2
 
     side = torch.cuda.Stream()
-    epoch_done = torch.cuda.Event()
+    epoch_done, exchange_done = torch.cuda.Event(), torch.cuda.Event()
 
     def step():
+        if world > 1:
+            # The previous step's exchange must not share the GPU with this epoch: the population is exactly one resident
+            # wave and its epochs are elastic (every walker waits for the slowest), so a CTA that cannot start because an
+            # NCCL kernel holds its SM stalls the whole launch.  The exchange has normally finished long before (it runs
+            # beside the L2 flush between steps): this wait costs nothing then.
+            stream.wait_event(exchange_done)
         search.epoch(args.epoch, sptr)
         if world > 1:
             # the path's one exchange step: best cost of the epoch, min over GPUs (NCCL over NVLink) — on a side stream
-            # behind an event, so that the next epoch does not queue behind it (ghost_b200/multi.py does the same)
+            # behind an event, so that the host queues the next step without waiting for it
             epoch_done.record(stream)
             side.wait_event(epoch_done)
             with torch.cuda.stream(side):
                 search.export_key(key.data_ptr(), side.cuda_stream)
                 dist.all_reduce(key, op=dist.ReduceOp.MIN)
+                exchange_done.record(side)
 
     def counters():
         torch.cuda.synchronize()
