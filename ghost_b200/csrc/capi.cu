@@ -280,7 +280,8 @@ extern "C" int ghost_b200_search_begin(GhostModel* gm, const GhostSearchOpts* op
 	ghost_b200_resolve_opts(gm, &s->opts);
 	const DevModel& m = gm->low.dev;
 	if (s->opts.number_variables_to_reset > m.V) s->opts.number_variables_to_reset = m.V;
-	s->layout = gm->low.layout(s->opts.threads_per_walker, s->opts.number_variables_to_reset);
+	if (s->opts.strategy != GHOST_STRATEGY_ADAPTIVE_SEARCH && s->opts.strategy != GHOST_STRATEGY_ANTIDOTE) { delete s; return set_error(GHOST_B200_ERR_INVALID, "strategy must be GHOST_STRATEGY_ADAPTIVE_SEARCH or GHOST_STRATEGY_ANTIDOTE"); }
+	s->layout = gm->low.layout(s->opts.threads_per_walker, s->opts.number_variables_to_reset, s->opts.strategy);
 	LaunchCfg cfg;
 	rc = pick_launch(gm, s->layout, s->opts.threads_per_walker, &cfg);
 	if (rc) { delete s; return rc; }
@@ -300,6 +301,13 @@ extern "C" int ghost_b200_search_begin(GhostModel* gm, const GhostSearchOpts* op
 		if (oe != cudaSuccess || ctas_per_sm < 1) { delete s; return set_error(GHOST_B200_ERR_CUDA, std::string("occupancy query: ") + cudaGetErrorString(oe)); }
 		s->resident_walkers = gm->sm_count * ctas_per_sm * cfg.walkers_per_cta;
 		if (s->opts.number_walkers <= 0) s->opts.number_walkers = s->resident_walkers;
+	}
+	if (s->opts.strategy == GHOST_STRATEGY_ANTIDOTE) {
+		// weighted draws over all variables / all candidates with one Philox word: the weight sums must fit 32 bits, and the
+		// per-chunk bookkeeping of the Antidote kernels lives in one warp
+		if (cfg.T != 32) { delete s; return set_error(GHOST_B200_ERR_UNSUPPORTED, "the Antidote strategy runs one warp per walker: at most 1024 variables and 1024 candidates"); }
+		const double cap = 4294967295.0;
+		if ((double)gm->low.error_bound * std::max(m.V, m.max_candidates) > cap) { delete s; return set_error(GHOST_B200_ERR_UNSUPPORTED, "the Antidote strategy needs (error bound x variables) below 2^32"); }
 	}
 	s->elastic = s->opts.elastic_epochs == 1 ? 1 : 0;
 	s->walkers = s->opts.number_walkers;
@@ -370,6 +378,7 @@ extern "C" int ghost_b200_search_epoch(GhostSearch* s, int32_t iterations, void*
 	p.elastic = (s->elastic && s->walkers <= s->resident_walkers) ? 1 : 0;
 	if (p.elastic) CUDA_TRY(cudaMemsetAsync(s->d_finished, 0, sizeof(int), (cudaStream_t)stream));
 	p.trace = s->d_trace; p.trace_cap = s->trace_cap; p.trace_walker = 0; p.trace_len = s->d_trace_len;
+	p.strategy = o.strategy;
 	p.elite_x = s->d_elite_x; p.elite_key = s->d_elite_key; p.elite_percent = s->d_elite_x ? o.elite_restart_percent : 0;
 	CUDA_TRY(launch_search(s->T, s->grid, s->block, s->smem, (cudaStream_t)stream, s->model->low.dev, s->layout, p));
 	if (s->d_elite_x) {

@@ -27,6 +27,7 @@ struct SearchParams {
 	const int* elite_x;             // cooperative walkers: the best assignment of the search so far [V] ...
 	const unsigned long long* elite_key; // ... and its packed quality key (all ones: none yet); see GhostSearchOpts::elite_restart_percent
 	int elite_percent;
+	int strategy;                   // GhostStrategy
 	int* trace;                     // optional [trace_cap][8] rows of walker trace_walker
 	int trace_cap, trace_walker;
 	int* trace_len;
@@ -396,7 +397,8 @@ static __device__ __noinline__ ColdState walker_reinit(const DevModel& m, const 
 }
 
 // F32: the fp32 form of the LinearEq-only swap evaluation (walker.cuh, evaluate_f32); T == 32, PERM, EQ, 16-bit x only
-template <int T, bool PERM, bool EQ, class XT, bool F32 = false, int FS = 0>
+// STRAT: GhostStrategy (1 = the Antidote heuristic set, walker.cuh; T == 32 and not F32)
+template <int T, bool PERM, bool EQ, class XT, bool F32 = false, int FS = 0, int STRAT = 0>
 __global__ void __launch_bounds__(T == 32 ? 128 : T, (GB_WARPS_PER_SM * 32) / (T == 32 ? 128 : T))
 search_kernel(const __grid_constant__ DevModel m, const __grid_constant__ WalkerLayout L, const __grid_constant__ SearchParams p)
 {
@@ -432,6 +434,7 @@ search_kernel(const __grid_constant__ DevModel m, const __grid_constant__ Walker
 		for (int i = 0; i < 8; ++i) s.counters[i] = k[i];
 		s.cs[m.C] = make_int2(0, 0); s.cem[m.C] = make_int2(0, 0); // the dummy constraint that pads the ELL rows
 	}
+	if (STRAT == 1) for (int k = m.max_candidates + tid; k < L.nchunks_c * 32; k += T) s.sums[k] = GB_INT_MAX; // slots beyond the last candidate
 
 	unsigned char* const walker_base = smem_raw + (size_t)local * L.total_bytes;
 	auto reinit = [&](int mode) {
@@ -488,7 +491,16 @@ search_kernel(const __grid_constant__ DevModel m, const __grid_constant__ Walker
 			G::sync();
 		}
 
-		if (r.must_compute)
+		uint4 rnd_early = make_uint4(0, 0, 0, 0);
+		int v_antidote = -1;
+		if (STRAT == 1) {
+			// the weight vector is rebuilt after a move (nothing erased), kept otherwise; it is sampled in EVERY iteration.
+			// The Philox block of the iteration is drawn here (the oracle draws it after the reset test: a reset iteration
+			// then gives the event back)
+			if (r.must_compute) cq.bits = 0u;
+			rnd_early = rng.block(rng.next_event, 0);
+			v_antidote = antidote_select(m, s, L.nchunks_v, r.local_moves - r.tabu_base, rnd_early.x, cq, &r.n_tabu, &r.ncand);
+		} else if (r.must_compute)
 			r.ncand = scan_candidates<T>(m, s, L.nchunks_v, r.local_moves - r.tabu_base, optimization && r.cur_sat == 0, s.red, &r.cand_max, &r.n_tabu, cq);
 
 		int trace_var = -1, trace_val = 0, trace_branch = 0, trace_ncand = 0, trace_min = 0;
@@ -499,19 +511,27 @@ search_kernel(const __grid_constant__ DevModel m, const __grid_constant__ Walker
 			if (r.best_pending) { copy_best<T>(m, s, best_x); r.best_pending = 0; G::sync(); }
 			reinit(p.restart_threshold > 0 && (r.resets % p.restart_threshold == 0) ? GB_COLD_RESTART : GB_COLD_PERTURB);
 		} else {
-			const uint4 rnd = rng.block(rng.next_event++, 0);
-			// UniformVariableHeuristic::select_variable (uniform_variable_heuristic.cpp:38-41)
-			const int kv = (int)below(rnd.x, (uint32_t)r.ncand);
-			const int v = T == 32 ? regs_pick_kth(cq, r.cand_max, kv, r.ncand) : pick_kth(s.cand_key, s.cand_bits, L.nchunks_v, r.cand_max, kv);
-			--r.ncand;
+			const uint4 rnd = STRAT == 1 ? rnd_early : rng.block(rng.next_event, 0);
+			++rng.next_event;
+			int v;
+			if (STRAT == 1) {
+				v = v_antidote;
+				r.ncand -= antidote_erase(m, s, L.nchunks_v, r.local_moves - r.tabu_base, v, cq);   // search_unit.hpp:825-828
+			} else {
+				// UniformVariableHeuristic::select_variable (uniform_variable_heuristic.cpp:38-41)
+				const int kv = (int)below(rnd.x, (uint32_t)r.ncand);
+				v = T == 32 ? regs_pick_kth(cq, r.cand_max, kv, r.ncand) : pick_kth(s.cand_key, s.cand_bits, L.nchunks_v, r.cand_max, kv);
+				--r.ncand;
+			}
 			int bias;
 			const int nh = F32 ? hoist_variable_f32(m, s, v, &bias) : EQ ? hoist_variable_eq<T, PERM>(m, s, v, &bias) : hoist_variable<T>(m, s, v, &bias);
 			G::sync();
 			// search_unit.hpp:826-828
-			if (T == 32) { if (tid == (v >> 5)) cq.bits &= ~(1u << (v & 31)); }
+			if (STRAT == 1) { }
+			else if (T == 32) { if (tid == (v >> 5)) cq.bits &= ~(1u << (v & 31)); }
 			else if (tid == 0) s.cand_bits[v >> 5] &= ~(1u << (v & 31));
 			int gkey, nties;
-			const int mine = evaluate_candidates<T, PERM, EQ, F32, FS>(m, s, v, nh, bias, L.nchunks_c, nullptr, vq);
+			const int mine = evaluate_candidates<T, PERM, EQ, F32, FS>(m, s, v, nh, bias, L.nchunks_c, STRAT == 1 ? s.sums : nullptr, vq);
 			evals_lane += mine;
 			G::sync();
 			// AdaptiveSearchValueHeuristic::select_value (adaptive_search_value_heuristic.cpp:43-81)
@@ -524,9 +544,16 @@ search_kernel(const __grid_constant__ DevModel m, const __grid_constant__ Walker
 			}
 			if (gkey == GB_INT_MAX) nties = 0;
 			// the fp32 evaluation hands back the bits of (1.5 * 2^23 + sum): an integer offset away from the sum
-			const int gmin = (F32 && gkey != GB_INT_MAX) ? gkey - GB_F32_BASE_BITS : gkey;
+			int gmin = (F32 && gkey != GB_INT_MAX) ? gkey - GB_F32_BASE_BITS : gkey;
 			int new_value = v;
-			if (nties > 0) {
+			if (STRAT == 1) {
+				// AntidoteSearchValueHeuristic::select_value: the branch below is decided by the CHOSEN candidate's delta
+				int chosen = GB_INT_MAX;
+				const int slot = antidote_value(s.sums, L.nchunks_c, rnd.y, &chosen);
+				gmin = slot >= 0 ? chosen : GB_INT_MAX;
+				if (slot >= 0) new_value = PERM ? slot : mv.dom_value(v, slot);
+				G::sync();
+			} else if (nties > 0) {
 				int k;
 				if (optimization && !PERM) {
 					// Objective::expert_heuristic_value (objective.cpp:69-109) for a linear objective:

@@ -23,6 +23,12 @@ static cudaError_t do_search_fs(int grid, int block, size_t smem, cudaStream_t s
 template <bool PERM, bool EQ, class XT, bool F32 = false>
 static cudaError_t do_search(int grid, int block, size_t smem, cudaStream_t st, const DevModel& m, const WalkerLayout& L, const SearchParams& p)
 {
+	if (GB_T == 32 && p.strategy == GHOST_STRATEGY_ANTIDOTE) {   // the Antidote heuristic set: integer evaluation, one warp per walker
+		cudaError_t e = allow_smem(search_kernel<GB_T, PERM, EQ, XT, false, 0, GB_T == 32 ? 1 : 0>, smem);
+		if (e != cudaSuccess) return e;
+		search_kernel<GB_T, PERM, EQ, XT, false, 0, GB_T == 32 ? 1 : 0><<<grid, block, smem, st>>>(m, L, p);
+		return cudaGetLastError();
+	}
 #ifndef GB_NO_FS
 	if (F32 && m.sg_ok) { // the structured-grid loop (see evaluate_candidates_f32)
 		switch (m.ell_stride) {

@@ -485,7 +485,7 @@ int lower_model(const GhostModelDesc* d, LoweredModel* out, std::string* why)
 
 static int align_up(int x, int a) { return (x + a - 1) / a * a; }
 
-WalkerLayout LoweredModel::layout(int /*threads_per_walker*/, int nreset) const
+WalkerLayout LoweredModel::layout(int /*threads_per_walker*/, int nreset, int strategy) const
 {
 	const DevModel& m = dev;
 	WalkerLayout w{};
@@ -515,6 +515,7 @@ WalkerLayout LoweredModel::layout(int /*threads_per_walker*/, int nreset) const
 	w.upd = take(4 * 2 * 2 * m.max_degree);
 	w.sample = (8 * std::max(1, nreset) <= 4 * m.V) ? w.err_var : take(4 * 2 * std::max(1, nreset));
 	w.red = take(4 * 32);   // [0,8) per-warp partials, [8] stop-flag broadcast, [16,32) 64-bit partials
+	w.sums = strategy == GHOST_STRATEGY_ANTIDOTE ? take(4 * 32 * w.nchunks_c) : w.red;
 	w.total_bytes = at;
 	return w;
 }

@@ -97,6 +97,7 @@ struct WalkerLayout {
 	int upd;                            // int32 [2*max_degree * 2]
 	int sample;                         // int32 [2 * nreset]
 	int red;                            // int32 [64] cross-warp scratch
+	int sums;                           // int32 [nchunks_c * 32] cumulated delta of every candidate slot (Antidote strategy only)
 	int persist_bytes;                  // x..cnt(+cand chunks) prefix that is saved between epochs
 	int total_bytes;
 	int nchunks_v, nchunks_c;
@@ -141,7 +142,7 @@ struct LoweredModel {
 	std::vector<int32_t> start;
 	int64_t error_bound = 0;    // upper bound of the total satisfaction error (must fit int32)
 	uint64_t uid = 0;           // unique per lowering in this process (what a device-side copy of the blob is tagged with)
-	WalkerLayout layout(int threads_per_walker, int nreset) const;
+	WalkerLayout layout(int threads_per_walker, int nreset, int strategy = 0) const;
 	int default_threads_per_walker() const;
 	int effective_threads_per_walker(int requested) const;
 };

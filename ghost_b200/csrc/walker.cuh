@@ -134,6 +134,7 @@ struct WST {
 	unsigned char* flags;
 	int* val_key; unsigned* val_bits;
 	int4* hoist; int* upd; int* sample; int* red;
+	int* sums;                  // Antidote strategy: cumulated delta of every candidate slot
 	__device__ __forceinline__ int cnt(int idx) const { return reinterpret_cast<const unsigned short*>(cnt32)[idx]; }
 	__device__ __forceinline__ void cnt_add(int idx, int d) const
 	{
@@ -165,6 +166,7 @@ __device__ __forceinline__ WS make_ws(unsigned char* base_in, const WalkerLayout
 	s.val_key = (int*)(base + L.val_key); s.val_bits = (unsigned*)(base + L.val_bits);
 	s.hoist = (int4*)(base + L.hoist); s.upd = (int*)(base + L.upd); s.sample = (int*)(base + L.sample);
 	s.red = (int*)(base + L.red);
+	s.sums = (int*)(base + L.sums);
 	return s;
 }
 
@@ -1087,6 +1089,122 @@ __device__ inline int evaluate_candidates_eq(const DevModel& m, const WS& s, int
 	case 4: return evaluate_candidates_eq_s<T, PERM, 4, false>(m, s, v, nh, bias, nchunks_c, out, q);
 	default: return evaluate_candidates_eq_s<T, PERM, 0, false>(m, s, v, nh, bias, nchunks_c, out, q);
 	}
+}
+
+// ---------------------------------------------------------------------------------------------
+// The Antidote heuristic set (GhostSearchOpts::strategy = GHOST_STRATEGY_ANTIDOTE; one-warp walkers).
+//  * candidates: every variable, weighted by its projected error, tabu ones by 0
+//    (antidote_search_variable_candidates_heuristic.cpp:39-48);
+//  * variable: drawn in proportion to the weights; the INDEX drawn is the variable (…variable_heuristic.cpp:39-43);
+//  * the loop then erases from the weight vector the first entry whose VALUE equals that index
+//    (search_unit.hpp:825-828 — written for the default heuristic, whose vector holds variable ids), and while no
+//    move happens the shrunken vector is sampled again: the kernel keeps the erased ORIGINAL positions as one bit
+//    mask per chunk (lane ch holds chunk ch's, in the register pair that carries the candidate summaries of the
+//    default strategy) and maps a drawn position to its index in the shrunken vector by counting the bits before it;
+//  * value: drawn in proportion to max(0, -cumulated delta), uniformly over all candidates when none improves;
+//    the branch that follows is decided by the CHOSEN candidate's delta (…value_heuristic.cpp:50-74).
+// The oracle restates the same with the same Philox words (ghost_oracle.c, sample_weighted).
+// ---------------------------------------------------------------------------------------------
+// weight of original position id in the current vector, -1 if it is not in it (erased, or padding)
+template <class WS>
+__device__ __forceinline__ int antidote_weight(const DevModel& m, const WS& s, int id, int lm_rel, unsigned erased_bits)
+{
+	const int lane = threadIdx.x & 31;
+	if (id >= m.V || ((erased_bits >> lane) & 1u)) return -1;
+	const int pos = scan_pos(m, id);
+	return (int)s.tabu[pos] > lm_rel ? 0 : s.err_var[pos];
+}
+__device__ __forceinline__ unsigned warp_inclusive_sum(unsigned v)
+{
+	const int lane = threadIdx.x & 31;
+#pragma unroll
+	for (int off = 1; off < 32; off <<= 1) { const unsigned t = __shfl_up_sync(0xffffffffu, v, off); if (lane >= off) v += t; }
+	return v;
+}
+// One pass over the vector: tabu count, vector length, and the drawn index (-1: the vector is empty).
+template <class WS>
+__device__ inline int antidote_select(const DevModel& m, const WS& s, int nchunks_v, int lm_rel, uint32_t word, const ChunkRegs& q,
+                                      int* ntabu_out, int* nvec_out)
+{
+	const int lane = threadIdx.x & 31;
+	unsigned my_sum = 0, my_cnt = 0;
+	int ntabu = 0;
+	for (int ch = 0; ch < nchunks_v; ++ch) {
+		const int id = ch * 32 + lane;
+		const unsigned er = __shfl_sync(0xffffffffu, q.bits, ch);
+		const int w = antidote_weight(m, s, id, lm_rel, er);
+		if (id < m.V && (int)s.tabu[scan_pos(m, id)] > lm_rel) ++ntabu;
+		const unsigned sum = __reduce_add_sync(0xffffffffu, (unsigned)(w > 0 ? w : 0));
+		const unsigned cnt = __popc(__ballot_sync(0xffffffffu, w >= 0));
+		if (lane == ch) { my_sum = sum; my_cnt = cnt; }
+	}
+	const unsigned total = __reduce_add_sync(0xffffffffu, my_sum);
+	const int nvec = (int)__reduce_add_sync(0xffffffffu, my_cnt);
+	*ntabu_out = __reduce_add_sync(0xffffffffu, ntabu);
+	*nvec_out = nvec;
+	if (nvec == 0) return -1;
+	if (total == 0) return 0;   // a vector of zeros: index 0 (what std::discrete_distribution returns for NaN probabilities)
+	const unsigned pick = below(word, total);
+	const unsigned incl = warp_inclusive_sum(my_sum), incl_cnt = warp_inclusive_sum(my_cnt);
+	const int ch = __ffs(__ballot_sync(0xffffffffu, incl > pick)) - 1;
+	const unsigned before = __shfl_sync(0xffffffffu, incl - my_sum, ch), cnt_before = __shfl_sync(0xffffffffu, incl_cnt - my_cnt, ch);
+	const unsigned er = __shfl_sync(0xffffffffu, q.bits, ch);
+	const int w = antidote_weight(m, s, ch * 32 + lane, lm_rel, er);
+	const unsigned incl_w = warp_inclusive_sum((unsigned)(w > 0 ? w : 0));
+	const int l = __ffs(__ballot_sync(0xffffffffu, incl_w > pick - before)) - 1;
+	const unsigned present = __ballot_sync(0xffffffffu, w >= 0);
+	return (int)cnt_before + __popc(present & ((1u << l) - 1u));
+}
+// search_unit.hpp:825-828 on the weight vector: erase the first entry whose weight equals `value`.  Returns 1 if one was erased.
+template <class WS>
+__device__ inline int antidote_erase(const DevModel& m, const WS& s, int nchunks_v, int lm_rel, int value, ChunkRegs& q)
+{
+	const int lane = threadIdx.x & 31;
+	for (int ch = 0; ch < nchunks_v; ++ch) {
+		const unsigned er = __shfl_sync(0xffffffffu, q.bits, ch);
+		const int w = antidote_weight(m, s, ch * 32 + lane, lm_rel, er);
+		const unsigned hit = __ballot_sync(0xffffffffu, w >= 0 && w == value);
+		if (hit) {
+			if (lane == ch) q.bits |= 1u << (__ffs(hit) - 1);
+			return 1;
+		}
+	}
+	return 0;
+}
+// AntidoteSearchValueHeuristic::select_value over the cumulated deltas of every slot (INT_MAX: not a candidate).
+// Returns the chosen slot (-1: no candidate) and its delta.
+__device__ inline int antidote_value(const int* sums, int nchunks_c, uint32_t word, int* delta_out)
+{
+	const int lane = threadIdx.x & 31;
+	unsigned my_w = 0, my_c = 0;
+	for (int ch = 0; ch < nchunks_c; ++ch) {
+		const int sum = sums[ch * 32 + lane];
+		const bool isc = sum != GB_INT_MAX;
+		const unsigned w = __reduce_add_sync(0xffffffffu, (unsigned)(isc && sum < 0 ? -sum : 0));
+		const unsigned c = __popc(__ballot_sync(0xffffffffu, isc));
+		if (lane == ch) { my_w = w; my_c = c; }
+	}
+	const unsigned total_w = __reduce_add_sync(0xffffffffu, my_w), nc = __reduce_add_sync(0xffffffffu, my_c);
+	if (nc == 0) return -1;
+	int slot;
+	if (total_w == 0) {   // no candidate improves: uniform over all of them (…value_heuristic.cpp:67-68)
+		const unsigned k = below(word, nc);
+		const unsigned incl = warp_inclusive_sum(my_c);
+		const int ch = __ffs(__ballot_sync(0xffffffffu, incl > k)) - 1;
+		const unsigned before = __shfl_sync(0xffffffffu, incl - my_c, ch);
+		const unsigned isc = __ballot_sync(0xffffffffu, sums[ch * 32 + lane] != GB_INT_MAX);
+		slot = ch * 32 + __fns(isc, 0, (int)(k - before) + 1);
+	} else {
+		const unsigned pick = below(word, total_w);
+		const unsigned incl = warp_inclusive_sum(my_w);
+		const int ch = __ffs(__ballot_sync(0xffffffffu, incl > pick)) - 1;
+		const unsigned before = __shfl_sync(0xffffffffu, incl - my_w, ch);
+		const int sum = sums[ch * 32 + lane];
+		const unsigned incl_w = warp_inclusive_sum((unsigned)(sum != GB_INT_MAX && sum < 0 ? -sum : 0));
+		slot = ch * 32 + __ffs(__ballot_sync(0xffffffffu, incl_w > pick - before)) - 1;
+	}
+	*delta_out = sums[slot];
+	return slot;
 }
 
 // ---------------------------------------------------------------------------------------------

@@ -34,6 +34,9 @@ OBJ_LINEAR_MAXIMIZE = 2
 
 NOT_A_CANDIDATE = 2**31 - 1
 
+STRATEGY_ADAPTIVE_SEARCH = 0
+STRATEGY_ANTIDOTE = 1
+
 
 class GhostModelDescStruct(C.Structure):
     _fields_ = [
@@ -78,6 +81,8 @@ class GhostSearchOptsStruct(C.Structure):
         ("max_iterations", C.c_int64),
         ("elastic_epochs", C.c_int32),
         ("elite_restart_percent", C.c_int32),
+        ("strategy", C.c_int32),
+        ("reserved2", C.c_int32),
     ]
 
 
@@ -134,6 +139,8 @@ def default_opts(**overrides) -> GhostSearchOptsStruct:
     o.max_iterations = 0
     o.elastic_epochs = 0
     o.elite_restart_percent = 0
+    o.strategy = 0
+    o.reserved2 = 0
     for k, v in overrides.items():
         if not hasattr(o, k):
             raise AttributeError(k)

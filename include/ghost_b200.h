@@ -142,7 +142,21 @@ typedef struct GhostSearchOpts {
 	                              /* the best assignment any walker of the search has reached so far instead of sampling a   */
 	                              /* fresh one (153-198).  0 (default): off — trajectories are then those of independent     */
 	                              /* runs, as in the reference and the oracle.                                               */
+	int32_t strategy;             /* GhostStrategy: which of the reference's heuristic sets runs (default 0)                  */
+	int32_t reserved2;
 } GhostSearchOpts;
+
+/* The heuristic sets of the reference (include/search_unit.hpp:605-655 wires four strategy objects into a SearchUnit).
+ * ADAPTIVE_SEARCH is what Solver::fast_search always builds (include/solver.hpp:517-518, 571-572): uniform pick among
+ * the worst non-tabu variables, min-conflict value with uniform tie-break, error projection by summation.
+ * ANTIDOTE keeps that projection and replaces the three picks (src/algorithms/antidote_search_*.cpp): every variable is
+ * a candidate with its projected error as weight (tabu ones: 0), the variable is drawn in proportion to those weights,
+ * the value in proportion to its improvement max(0, -delta) (uniformly if no candidate improves).  Runs on the generic
+ * kernels (one warp per walker); the Culprit error projection is not built. */
+typedef enum GhostStrategy {
+	GHOST_STRATEGY_ADAPTIVE_SEARCH = 0,
+	GHOST_STRATEGY_ANTIDOTE = 1
+} GhostStrategy;
 
 /* Counters: the seven of SearchUnitData (include/search_unit_data.hpp:67-73) plus the
  * metric's numerator. */

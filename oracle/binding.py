@@ -280,12 +280,12 @@ class RefModel:
         return dict(found=found, cost=cost.value, solution=sol, elapsed_us=el.value)
 
 
-def run_ref_bench(desc: ModelDesc, timeout_us: float, parallel: bool, threads: int, workdir: str, exe=REF_BENCH):
+def run_ref_bench(desc: ModelDesc, timeout_us: float, parallel: bool, threads: int, workdir: str, exe=REF_BENCH, strategy: int = 0):
     """Run the GHOST_BENCH executable and parse the reference's own report
     (reference include/solver.hpp:764-833)."""
     path = os.path.join(workdir, f"{desc.name or 'model'}.desc")
     desc.dump(path)
-    out = subprocess.run([exe, path, str(float(timeout_us)), "1" if parallel else "0", str(int(threads))],
+    out = subprocess.run([exe, path, str(float(timeout_us)), "1" if parallel else "0", str(int(threads)), "0", str(int(strategy))],
                          check=True, capture_output=True, text=True).stdout
     rep = {"raw": out}
     import re
@@ -294,7 +294,10 @@ def run_ref_bench(desc: ModelDesc, timeout_us: float, parallel: bool, threads: i
                      ("resets", r"Number of resets: (\d+)"),
                      ("total_iterations", r"Total number of search iterations: (\d+)"),
                      ("total_resets", r"Total number of resets: (\d+)"),
-                     ("sat_error", r"Satisfaction error: ([0-9.e+]+)")]:
+                     ("sat_error", r"Satisfaction error: ([0-9.e+]+)"),
+                     ("antidote_sat_error", r"HARNESS antidote best_sat_error=([0-9.e+]+)"),
+                     ("antidote_iterations", r"HARNESS antidote best_sat_error=[0-9.e+]+ iterations=(\d+)"),
+                     ("antidote_resets", r"HARNESS antidote .* resets=(\d+)")]:
         mm = re.search(pat, out)
         if mm:
             rep[key] = float(mm.group(1))

@@ -217,6 +217,10 @@ typedef struct Walker {
 	/* scratch */
 	int32_t* scratch_a; int32_t* scratch_b; uint8_t* flag; int32_t* sample;
 	double* deltas;        /* per-constraint deltas of one candidate */
+	/* Antidote strategy: variable_candidates is the VECTOR OF WEIGHTS (projected errors, tabu ones zeroed), not a list of
+	 * ids (antidote_search_variable_candidates_heuristic.cpp:39-48); it shrinks by the erase of search_unit.hpp:825-828 */
+	double* wvec; int32_t nvec;
+	double* cand_sum;      /* cumulated delta of every candidate slot (Antidote value heuristic needs them all) */
 } Walker;
 
 static int in_domain(const OracleModel* m, int v, int32_t value)
@@ -874,11 +878,14 @@ static Walker* walker_create(const OracleModel* m, const GhostSearchOpts* opts, 
 	w->sample = (int32_t*)calloc(big + 2, sizeof(int32_t));
 	w->flag = (uint8_t*)calloc(V, 1);
 	w->deltas = (double*)calloc(2 * C + 2, sizeof(double));
+	w->wvec = (double*)calloc(V, sizeof(double));
+	w->cand_sum = (double*)calloc(big + 2, sizeof(double));
 	return w;
 }
 static void walker_destroy(Walker* w)
 {
 	free(w->x); free(w->cur_err); free(w->cur_sum); free(w->count); free(w->tabu); free(w->err_var);
+	free(w->wvec); free(w->cand_sum);
 	free(w->best_x); free(w->cand); free(w->scratch_a); free(w->scratch_b); free(w->sample);
 	free(w->flag); free(w->deltas); free(w);
 }
@@ -939,6 +946,29 @@ void oracle_resolve_opts(int32_t V, GhostSearchOpts* o)
 }
 
 /* SearchUnit::local_search, include/search_unit.hpp:685-1201 */
+/* AntidoteSearchVariableCandidatesHeuristic::compute_variable_candidates
+ * (src/algorithms/antidote_search_variable_candidates_heuristic.cpp:39-48): the error vector with tabu variables zeroed */
+static void antidote_candidates(Walker* w)
+{
+	const OracleModel* m = w->m;
+	for (int v = 0; v < m->V; ++v) w->wvec[v] = w->tabu[v] > w->k.local_moves ? 0.0 : w->err_var[v];
+	w->nvec = m->V;
+}
+/* rng.variate<int, std::discrete_distribution>(weights) restated on one Philox word: index i with probability
+ * weights[i] / total — the first i whose running sum exceeds floor(word * total / 2^32).  The weights are
+ * integer-valued (errors of integer models); a vector of zeros gives index 0, which is what libstdc++'s
+ * discrete_distribution does with NaN probabilities (std::lower_bound finds nothing smaller). */
+static int sample_weighted(const double* weights, int n, uint32_t word)
+{
+	double total = 0.0;
+	for (int i = 0; i < n; ++i) total += weights[i];
+	if (!(total > 0.0)) return 0;
+	uint32_t pick = below(word, (uint32_t)total);
+	double run = 0.0;
+	for (int i = 0; i < n; ++i) { run += weights[i]; if (run > (double)pick) return i; }
+	return n - 1;
+}
+
 /* The choices of one iteration taken from the caller instead of the Philox stream (decision replay
  * against the reference's own GHOST_TRACE output, tests/test_decision_replay.py): the variable picked
  * among the candidates (search_unit.hpp:806), the value / swap partner picked among the ties
@@ -959,11 +989,12 @@ static int walker_iteration(Walker* w, const Forced* forced, OracleTraceRow* row
 	row->iteration = w->k.search_iterations;
 	if (nties_out) *nties_out = 0;
 
-	if (w->must_compute) compute_variable_candidates(w); /* 749-750 */
+	const int antidote = w->opt.strategy == GHOST_STRATEGY_ANTIDOTE;
+	if (w->must_compute) { if (antidote) antidote_candidates(w); else compute_variable_candidates(w); } /* 749-750 */
 
 	int ntabu = 0; /* 761-763 */
 	for (int v = 0; v < m->V; ++v) if (w->tabu[v] > w->k.local_moves) ++ntabu;
-	if (ntabu >= w->opt.reset_threshold || w->ncand == 0) {
+	if (ntabu >= w->opt.reset_threshold || (antidote ? w->nvec == 0 : w->ncand == 0)) {
 		reset(w); /* 769-770 */
 		row->variable = -1; row->branch = 0; row->current_sat_error = w->cur_sat;
 		return 1;
@@ -975,28 +1006,85 @@ static int walker_iteration(Walker* w, const Forced* forced, OracleTraceRow* row
 	uint32_t rnd[4];
 	rng_block(&w->rng, w->rng.next_event++, 0, rnd);
 
-	int pick = (int)below(rnd[0], (uint32_t)w->ncand);
-	if (forced) {
-		pick = -1;
-		for (int i = 0; i < w->ncand; ++i) if (w->cand[i] == forced->variable) pick = i;
-		if (pick < 0) { --w->k.search_iterations; return -1; }
+	int v;
+	if (antidote) {
+		/* AntidoteSearchVariableHeuristic::select_variable (antidote_search_variable_heuristic.cpp:39-43): the INDEX
+		 * drawn from the weight vector is the variable */
+		v = sample_weighted(w->wvec, w->nvec, rnd[0]);
+		if (forced) {
+			double total = 0.0;
+			for (int i = 0; i < w->nvec; ++i) total += w->wvec[i];
+			if (forced->variable < 0 || forced->variable >= w->nvec
+			    || (total > 0.0 ? !(w->wvec[forced->variable] > 0.0) : forced->variable != 0)) { --w->k.search_iterations; return -1; }
+			v = forced->variable;
+		}
+		/* search_unit.hpp:825-828: std::find looks for the variable's index AS A VALUE of the vector — with Antidote's
+		 * weights that erases the first entry whose weight happens to equal the index, if there is one */
+		for (int i = 0; i < w->nvec; ++i)
+			if (w->wvec[i] == (double)v) { for (int t = i; t + 1 < w->nvec; ++t) w->wvec[t] = w->wvec[t + 1]; --w->nvec; break; }
+	} else {
+		int pick = (int)below(rnd[0], (uint32_t)w->ncand);
+		if (forced) {
+			pick = -1;
+			for (int i = 0; i < w->ncand; ++i) if (w->cand[i] == forced->variable) pick = i;
+			if (pick < 0) { --w->k.search_iterations; return -1; }
+		}
+		v = w->cand[pick];
+		/* erase, keeping the ascending order of the vector (826-828) */
+		for (int i = pick; i + 1 < w->ncand; ++i) w->cand[i] = w->cand[i + 1];
+		--w->ncand;
 	}
-	int v = w->cand[pick];
-	/* erase, keeping the ascending order of the vector (826-828) */
-	for (int i = pick; i + 1 < w->ncand; ++i) w->cand[i] = w->cand[i + 1];
-	--w->ncand;
+	const int cand_empty = antidote ? w->nvec == 0 : w->ncand == 0;
 
 	double min_conflict;
 	int32_t ncandidates = 0;
-	int nties = evaluate_candidates(w, v, NULL, ties, &min_conflict, &ncandidates); /* 831-891 */
+	int nties = evaluate_candidates(w, v, antidote ? w->cand_sum : NULL, ties, &min_conflict, &ncandidates); /* 831-891 */
 	w->k.candidates_evaluated += ncandidates;
 	if (nties_out) *nties_out = nties;
 
 	int new_value;
-	if (nties == 0) new_value = v; /* adaptive_search_value_heuristic.cpp:68-69 */
+	if (antidote) {
+		/* AntidoteSearchValueHeuristic::select_value (antidote_search_value_heuristic.cpp:50-74): candidates in key order,
+		 * weight max(0, -cumulated delta); uniform over all candidates when none improves; min_conflict becomes the
+		 * CHOSEN candidate's cumulated delta.  (No candidate at all is undefined behaviour there — max_element of an
+		 * empty range; here: the variable keeps its value and the iteration counts as a local minimum.) */
+		const int slots = num_candidate_slots(m, v);
+		int32_t* keys = w->scratch_a; double* wts = w->deltas; /* deltas is free again; it holds 2C+2 doubles: use cand-sized scratch below */
+		(void)wts;
+		int nc = 0; double maxw = 0.0, total = 0.0;
+		for (int k = 0; k < slots; ++k) {
+			if (isnan(w->cand_sum[k])) continue;
+			int32_t key; is_candidate(w, v, k, &key);
+			keys[nc] = key;
+			double wt = w->cand_sum[k] >= 0 ? 0.0 : -w->cand_sum[k];
+			w->cand_sum[nc] = w->cand_sum[k];       /* compact in place (nc <= k) */
+			if (wt > maxw) maxw = wt;
+			total += wt;
+			++nc;
+		}
+		if (nc == 0) { new_value = v; min_conflict = DBL_MAX; }
+		else {
+			int idx;
+			if (maxw == 0.0) idx = (int)below(rnd[1], (uint32_t)nc);
+			else {
+				uint32_t pick = below(rnd[1], (uint32_t)total);
+				double run = 0.0; idx = nc - 1;
+				for (int i = 0; i < nc; ++i) { double wt = w->cand_sum[i] >= 0 ? 0.0 : -w->cand_sum[i]; run += wt; if (run > (double)pick) { idx = i; break; } }
+			}
+			if (forced) {
+				idx = -1;
+				for (int i = 0; i < nc; ++i) if (keys[i] == forced->value) idx = i;
+				if (idx < 0) return -2;
+				if (maxw > 0.0 && !(w->cand_sum[idx] < 0)) return -2;   /* a weight-0 candidate cannot be drawn */
+			}
+			new_value = keys[idx];
+			min_conflict = w->cand_sum[idx];
+		}
+	}
+	else if (nties == 0) new_value = v; /* adaptive_search_value_heuristic.cpp:68-69 */
 	else if (optimization && !m->permutation) new_value = heuristic_value(w, v, ties, nties, rnd[1]);
 	else new_value = ties[below(rnd[1], (uint32_t)nties)];
-	if (forced && nties > 0) {
+	if (!antidote && forced && nties > 0) {
 		int found = 0;
 		for (int i = 0; i < nties; ++i) if (ties[i] == forced->value) found = 1;
 		if (found && optimization && !m->permutation) {
@@ -1031,13 +1119,13 @@ static int walker_iteration(Walker* w, const Forced* forced, OracleTraceRow* row
 			else {
 				/* local_minimum_management, 565-582 */
 				w->must_compute = 0;
-				if (w->ncand == 0) { w->tabu[v] = w->opt.tabu_time_local_min + (int32_t)w->k.local_moves; ++w->k.local_minimum; row->branch = 5; }
+				if (cand_empty) { w->tabu[v] = w->opt.tabu_time_local_min + (int32_t)w->k.local_moves; ++w->k.local_minimum; row->branch = 5; }
 				else row->branch = 6;
 			}
 		} else plateau = 1; /* 1136-1145 */
 	} else { /* 1147-1163 */
 		w->must_compute = 0;
-		if (w->ncand == 0) { w->tabu[v] = w->opt.tabu_time_local_min + (int32_t)w->k.local_moves; ++w->k.local_minimum; row->branch = 5; }
+		if (cand_empty) { w->tabu[v] = w->opt.tabu_time_local_min + (int32_t)w->k.local_moves; ++w->k.local_minimum; row->branch = 5; }
 		else row->branch = 6;
 	}
 	if (plateau) { /* plateau_management, 545-561 */
@@ -1139,7 +1227,8 @@ int oracle_stepper_peek(OracleStepper* s, int32_t* x, int32_t* candidates, int32
 {
 	Walker* w = s->w;
 	const OracleModel* m = w->m;
-	if (w->must_compute) { compute_variable_candidates(w); w->must_compute = 0; } /* idempotent: the iteration finds the same list */
+	const int antidote = w->opt.strategy == GHOST_STRATEGY_ANTIDOTE;
+	if (w->must_compute) { if (antidote) antidote_candidates(w); else compute_variable_candidates(w); w->must_compute = 0; } /* idempotent: the iteration finds the same list */
 	if (x) memcpy(x, w->x, sizeof(int32_t) * m->V);
 	if (candidates) memcpy(candidates, w->cand, sizeof(int32_t) * w->ncand);
 	if (num_candidates) *num_candidates = w->ncand;
@@ -1151,7 +1240,7 @@ int oracle_stepper_peek(OracleStepper* s, int32_t* x, int32_t* candidates, int32
 	if (num_tabu) *num_tabu = nt;
 	if (local_moves) *local_moves = w->k.local_moves;
 	if (current_sat_error) *current_sat_error = w->cur_sat;
-	if (would_reset) *would_reset = (nt >= w->opt.reset_threshold || w->ncand == 0) ? 1 : 0;
+	if (would_reset) *would_reset = (nt >= w->opt.reset_threshold || (antidote ? w->nvec == 0 : w->ncand == 0)) ? 1 : 0;
 	return 0;
 }
 

@@ -46,6 +46,9 @@
 #include "global_constraints/linear_equation_l.hpp"
 #include "global_constraints/linear_equation_g.hpp"
 #include "algorithms/adaptive_search_error_projection_algorithm.hpp"
+#include "algorithms/antidote_search_variable_heuristic.hpp"
+#include "algorithms/antidote_search_variable_candidates_heuristic.hpp"
+#include "algorithms/antidote_search_value_heuristic.hpp"
 
 #include "../include/ghost_b200.h"
 
@@ -571,7 +574,7 @@ extern "C" int ref_complete_search( const GhostModelDesc* d, int64_t max_solutio
  *         reference itself prints.  usage: ref_bench desc.txt timeout_us parallel threads [custom_start] */
 int main( int argc, char** argv )
 {
-	if( argc < 5 ) { std::fprintf( stderr, "usage: %s desc.txt timeout_us parallel_runs threads [custom_start]\n", argv[0] ); return 2; }
+	if( argc < 5 ) { std::fprintf( stderr, "usage: %s desc.txt timeout_us parallel_runs threads [custom_start [strategy: 0 adaptive search, 1 antidote]]\n", argv[0] ); return 2; }
 	auto desc = std::make_shared<DescCopy>();
 	if( !desc->load( argv[1] ) ) { std::fprintf( stderr, "cannot read %s\n", argv[1] ); return 2; }
 	DescBuilder builder( desc );
@@ -582,6 +585,31 @@ int main( int argc, char** argv )
 	if( argc > 5 ) options.custom_starting_point = std::atoi( argv[5] ) != 0;
 	double cost = 0;
 	std::vector<int> solution;
+	if( argc > 6 && std::atoi( argv[6] ) == 1 )
+	{
+		/* The Antidote heuristic set.  Solver::fast_search never builds it (include/solver.hpp:499-518), so the SearchUnit
+		 * is constructed here the way fast_search does for the default set, with the option defaults resolved as at
+		 * include/solver.hpp:451-473, and run with its own local_search (and its own GHOST_TRACE output). */
+		const int V = desc->V;
+		if( options.tabu_time_local_min < 0 ) options.tabu_time_local_min = std::max( std::min( 5, V - 1 ), static_cast<int>( std::ceil( V / 5 ) ) ) + 1;
+		if( options.tabu_time_selected < 0 ) options.tabu_time_selected = 0;
+		if( options.percent_chance_force_trying_on_plateau < 0 || options.percent_chance_force_trying_on_plateau > 100 ) options.percent_chance_force_trying_on_plateau = 10;
+		if( options.reset_threshold < 0 ) options.reset_threshold = options.tabu_time_local_min;
+		if( options.restart_threshold < 0 ) options.restart_threshold = V;
+		if( options.number_variables_to_reset < 0 ) options.number_variables_to_reset = std::max( 2, static_cast<int>( std::ceil( V * 0.1 ) ) );
+		if( options.number_start_samplings < 0 ) options.number_start_samplings = 10;
+		SearchUnit unit( Access::build( builder ), options,
+		                 std::make_unique<algorithms::AntidoteSearchVariableHeuristic>(),
+		                 std::make_unique<algorithms::AntidoteSearchVariableCandidatesHeuristic>(),
+		                 std::make_unique<algorithms::AntidoteSearchValueHeuristic>(),
+		                 std::make_unique<algorithms::AdaptiveSearchErrorProjection>() );
+		unit.local_search( std::atof( argv[2] ) );
+		std::cout << "HARNESS antidote best_sat_error=" << unit.data.best_sat_error << " iterations=" << unit.data.search_iterations
+		          << " resets=" << unit.data.resets << "\nHARNESS solution:";
+		for( int v : unit.final_solution ) std::cout << " " << v;
+		std::cout << "\n";
+		return 0;
+	}
 	bool found = solver.fast_search( cost, solution, std::atof( argv[2] ), options );
 	std::cout << "HARNESS found=" << found << " cost=" << cost << " threads=" << options.number_threads << "\nHARNESS solution:";
 	for( int v : solution ) std::cout << " " << v;

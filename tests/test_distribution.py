@@ -76,3 +76,33 @@ def test_deviation_d1_best_assignment_follows_best_error(oracle_built):
         assert mismatches() > 0, "the reference's behaviour should leave some walkers with a stale best assignment"
     finally:
         lib.oracle_set_faithful_d1(0)
+
+
+def test_antidote_strategy_in_distribution(ref_built):
+    """The Antidote heuristic set (GHOST_STRATEGY_ANTIDOTE) in distribution: oracle walkers vs the reference's SearchUnit
+    built with its Antidote heuristics (oracle/ref_harness.cpp) on the 4x4 magic square.  Antidote never marks a
+    variable tabu at a local minimum (its candidate vector is never empty, search_unit.hpp:565-582), so most runs end
+    stuck — on both sides: the fraction that solves (observed: 40 of 300 for the reference AND for the restatement)
+    and the iterations of those that do are compared."""
+    if not os.path.exists(ref_built.REF_BENCH):
+        pytest.skip("ref_bench not built")
+    desc = model_by_name("magic_square:4")
+    port = ref_built.OraclePort(desc)
+    o = port.resolve_opts(default_opts(seed=77, strategy=1))
+    n = 200
+    oi = []
+    for w in range(n):
+        r = port.search(o, w, 20_000)
+        if r["best_sat"] == 0.0:
+            oi.append(r["counters"]["search_iterations"])
+    ri = []
+    with tempfile.TemporaryDirectory() as d:
+        for _ in range(n):
+            rep = ref_built.run_ref_bench(desc, 0.15e6, False, 1, d, strategy=1)
+            if rep.get("antidote_sat_error") == 0.0:
+                ri.append(rep["antidote_iterations"])
+    # solved fractions: two proportions around 0.13, n = 200 each: standard error of the difference ~ 0.034
+    assert abs(len(oi) - len(ri)) <= 0.14 * n, (len(oi), len(ri))
+    assert len(oi) >= 8 and len(ri) >= 8
+    p = ks_2samp(oi, ri).pvalue
+    assert p > 1e-3, ("antidote iterations to solution", p, np.median(oi), np.median(ri))

@@ -320,3 +320,17 @@ def test_elite_restart_cooperative_walkers(oracle_built):
     e, _ = port.check(r["solution"])
     assert e == 0.0
     model.close()
+
+
+@pytest.mark.parametrize("name", ["magic_square:5", "n_queens:8", "costas_lag:9", "knapsack:20x3", "mixed", "mixed_perm", "n_queens_offset:12",
+                                  "magic_square:16", "all_interval:10"])
+def test_antidote_strategy_trajectories_match_oracle(name, oracle_built):
+    """GHOST_STRATEGY_ANTIDOTE (weighted variable draw over the whole error vector, the erase of search_unit.hpp:825-828
+    on that vector, weighted value draw): the CUDA walkers against the oracle, whose Antidote restatement is pinned to the
+    reference's own Antidote heuristics by tests/test_decision_replay.py and tests/test_distribution.py."""
+    _check_against_oracle(model_by_name(name), oracle_built, iterations=500, walkers=8, seed=321, strategy=1)
+
+
+def test_antidote_strategy_survives_epochs(oracle_built):
+    """The erased positions of the weight vector are walker state: 10 launches of 40 iterations == one of 400."""
+    _check_against_oracle(model_by_name("n_queens:8"), oracle_built, iterations=400, walkers=6, seed=11, epochs=10, strategy=1)
