@@ -139,6 +139,8 @@ namespace ghost
 			o.number_walkers = options.number_walkers;
 			o.threads_per_walker = options.threads_per_walker;
 			o.epoch_iterations = options.epoch_iterations;
+			o.strategy = options.strategy;
+			o.elite_restart_percent = options.elite_restart_percent;
 			o.seed = options.seed ? options.seed : (static_cast<uint64_t>(std::random_device{}()) << 32) ^ std::random_device{}();
 			o.timeout_us = timeout;
 			o.stop_on_first_solution = 1;
