@@ -36,6 +36,7 @@ NOT_A_CANDIDATE = 2**31 - 1
 
 STRATEGY_ADAPTIVE_SEARCH = 0
 STRATEGY_ANTIDOTE = 1
+STRATEGY_CULPRIT = 2
 
 
 class GhostModelDescStruct(C.Structure):

@@ -152,10 +152,14 @@ typedef struct GhostSearchOpts {
  * ANTIDOTE keeps that projection and replaces the three picks (src/algorithms/antidote_search_*.cpp): every variable is
  * a candidate with its projected error as weight (tabu ones: 0), the variable is drawn in proportion to those weights,
  * the value in proportion to its improvement max(0, -delta) (uniformly if no candidate improves).  Runs on the generic
- * kernels (one warp per walker); the Culprit error projection is not built. */
+ * kernels (one warp per walker). */
 typedef enum GhostStrategy {
 	GHOST_STRATEGY_ADAPTIVE_SEARCH = 0,
-	GHOST_STRATEGY_ANTIDOTE = 1
+	GHOST_STRATEGY_ANTIDOTE = 1,
+	GHOST_STRATEGY_CULPRIT = 2       /* the default picks over the Culprit Search error projection
+	                                    (src/algorithms/culprit_search_error_projection_algorithm.cpp:50-151): a constraint's
+	                                    error is shared out among the variables in proportion to how much moving each
+	                                    to a neighbouring value of its domain would lower it; fp64 */
 } GhostStrategy;
 
 /* Counters: the seven of SearchUnitData (include/search_unit_data.hpp:67-73) plus the

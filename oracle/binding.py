@@ -76,6 +76,8 @@ def _load_port():
         lib.oracle_stepper_destroy.argtypes = [C.c_void_p]
         lib.oracle_stepper_sync.argtypes = [C.c_void_p, C.c_void_p]
         lib.oracle_stepper_peek.argtypes = [C.c_void_p] + [C.c_void_p] * 8
+        lib.oracle_stepper_errors.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        lib.oracle_stepper_errors.restype = None
         lib.oracle_stepper_step.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.POINTER(OracleTraceRow), C.c_void_p,
                                             C.c_void_p, C.POINTER(GhostCountersStruct)]
         _port = lib
@@ -182,6 +184,11 @@ class OracleStepper:
                                      C.addressof(lm), C.addressof(err), C.addressof(wr))
         return dict(x=x, candidates=cand[:nc.value].tolist(), tabu={int(tabu[2 * i]): int(tabu[2 * i + 1]) for i in range(nt.value)},
                     local_moves=lm.value, current_sat_error=err.value, would_reset=bool(wr.value))
+
+    def errors(self):
+        ve = np.zeros(self.port.V, dtype=np.float64); ce = np.zeros(self.port.C, dtype=np.float64)
+        self.lib.oracle_stepper_errors(self.h, ve.ctypes.data, ce.ctypes.data)
+        return ve, ce
 
     def step(self, variable, value, force_on_plateau):
         row = OracleTraceRow()

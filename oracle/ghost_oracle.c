@@ -221,6 +221,10 @@ typedef struct Walker {
 	 * ids (antidote_search_variable_candidates_heuristic.cpp:39-48); it shrinks by the erase of search_unit.hpp:825-828 */
 	double* wvec; int32_t nvec;
 	double* cand_sum;      /* cumulated delta of every candidate slot (Antidote value heuristic needs them all) */
+	/* Culprit Search projection: CulpritSearchErrorProjection::_error_variables_by_constraints, a dense C x V table in the
+	 * reference; row c holds one value per scope entry (culprit[p], p indexing cvars) and ONE common value for every
+	 * variable outside the scope (culprit_out[c]) — see culprit_on_constraint */
+	double* culprit; double* culprit_out;
 } Walker;
 
 static int in_domain(const OracleModel* m, int v, int32_t value)
@@ -494,13 +498,108 @@ static double compute_constraints_errors(Walker* w)
 
 /* AdaptiveSearchErrorProjection::compute_variable_errors,
  * src/algorithms/adaptive_search_error_projection_algorithm.cpp:40-49 */
+static void culprit_compute_variable_errors(Walker* w);
 static void compute_variable_errors(Walker* w)
 {
 	const OracleModel* m = w->m;
+	if (w->opt.strategy == GHOST_STRATEGY_CULPRIT) { culprit_compute_variable_errors(w); return; }
 	for (int v = 0; v < m->V; ++v) {
 		w->err_var[v] = 0.;
 		for (int i = m->v2c_off[v]; i < m->v2c_off[v + 1]; ++i) w->err_var[v] += w->cur_err[m->v2c[i]];
 	}
+}
+
+/* ---- Culprit Search error projection (GHOST_STRATEGY_CULPRIT) ------------------------------
+ * src/algorithms/culprit_search_error_projection_algorithm.cpp.  Forward declaration: ctr_delta is above. */
+
+/* Variable::get_partial_domain(3) (src/variable.cpp:69-136), element 0 and element 2 of what it returns: the domain
+ * neighbours of the current value in the order the user gave the domain — except at the two ends, where the window
+ * wraps around and the two elements are NOT previous / next (last value: {d[0], d[n-2], d[n-1]} -> d[0] and the value
+ * itself; first value: {d[0], d[1], d[n-1]} -> the value itself and d[n-1]); a domain of exactly three values is
+ * returned whole, whatever the current value. */
+static void partial_domain_ends(const OracleModel* m, int var, int32_t current, int32_t* first, int32_t* third)
+{
+	const int32_t* d = m->dom_given + m->dom_off[var];
+	const int n = m->dom_off[var + 1] - m->dom_off[var];
+	int index = 0;
+	while (index < n && d[index] != current) ++index;
+	if (n <= 3) { *first = d[0]; *third = d[n - 1]; return; }
+	const int start = index - 1;
+	if (start >= 0) {
+		if (index + 2 <= n) { *first = d[start]; *third = d[start + 2]; }
+		else { *first = d[0]; *third = d[n - 1]; }          /* {d[0], d[n-2], d[n-1]} */
+	} else { *first = d[0]; *third = d[n - 1]; }            /* {d[0], d[1], d[n-1]} */
+}
+
+/* CulpritSearchErrorProjection::compute_variable_errors_on_constraint (…:50-110).  The reference fills a vector of V
+ * entries: the scope variables get the sum of two simulated deltas, all OTHER variables stay 0; then every entry x
+ * becomes max - x (max over all V entries), and the entries are scaled to sum to the constraint's error.  So a variable
+ * outside the scope ends with max / sum * error: not zero whenever max > 0. */
+static void culprit_on_constraint(Walker* w, int c)
+{
+	const OracleModel* m = w->m;
+	const int b = m->coff[c], e = m->coff[c + 1], outside = m->V - (e - b);
+	for (int p = b; p < e; ++p) w->culprit[p] = 0.;
+	w->culprit_out[c] = 0.;
+	if (!(w->cur_err[c] > 0)) return;
+	for (int p = b; p < e; ++p) {
+		int32_t var = m->cvars[p];
+		const int n = m->dom_off[var + 1] - m->dom_off[var];
+		int32_t vars[1] = { var }, vals[1];
+		if (n > 2) {
+			int32_t first, third;
+			partial_domain_ends(m, var, w->x[var], &first, &third);
+			vals[0] = first; double a = ctr_delta(w, c, 1, vars, vals);
+			vals[0] = third; w->culprit[p] = a + ctr_delta(w, c, 1, vars, vals);
+		} else if (n == 2) {
+			const int32_t* d = m->dom_given + m->dom_off[var];
+			vals[0] = d[0] == w->x[var] ? d[1] : d[0];
+			w->culprit[p] = ctr_delta(w, c, 1, vars, vals);
+		} else {
+			vals[0] = w->x[var];
+			w->culprit[p] = ctr_delta(w, c, 1, vars, vals);
+		}
+	}
+	double max = outside > 0 ? 0. : w->culprit[b];
+	for (int p = b; p < e; ++p) if (w->culprit[p] > max) max = w->culprit[p];
+	double sum = 0.;
+	for (int p = b; p < e; ++p) { w->culprit[p] = -w->culprit[p] + max; sum += w->culprit[p]; }
+	double out = outside > 0 ? -0. + max : 0.;
+	/* std::accumulate walks the V entries in variable order; every term is an integer-valued double here, so the order of
+	 * the additions does not matter */
+	sum += out * outside;
+	for (int p = b; p < e; ++p) w->culprit[p] = w->culprit[p] == 0 ? 0 : (w->culprit[p] / sum) * w->cur_err[c];
+	w->culprit_out[c] = (outside > 0 && out != 0) ? (out / sum) * w->cur_err[c] : 0.;
+}
+/* Row c of the table combined into the projected errors.  mode +1: err[v] = row[v] + err[v] (std::plus, …:122-127, 145-150);
+ * mode -1: err[v] = row[v] - err[v] — the "remove" step of update_variable_errors (…:136-141) hands std::transform the row
+ * as FIRST and the error vector as SECOND range with std::minus, so it computes row - error, not error - row.  Restated as
+ * written: after an update the projected errors are new_row + old_row - old_errors. */
+static void culprit_apply(Walker* w, int c, int mode)
+{
+	const OracleModel* m = w->m;
+	const int b = m->coff[c], e = m->coff[c + 1];
+	memset(w->flag, 0, m->V);
+	for (int p = b; p < e; ++p) {
+		const int v = m->cvars[p];
+		w->flag[v] = 1;
+		w->err_var[v] = mode > 0 ? w->culprit[p] + w->err_var[v] : w->culprit[p] - w->err_var[v];
+	}
+	for (int v = 0; v < m->V; ++v) if (!w->flag[v]) w->err_var[v] = mode > 0 ? w->culprit_out[c] + w->err_var[v] : w->culprit_out[c] - w->err_var[v];
+}
+/* CulpritSearchErrorProjection::compute_variable_errors (…:112-129) */
+static void culprit_compute_variable_errors(Walker* w)
+{
+	const OracleModel* m = w->m;
+	for (int v = 0; v < m->V; ++v) w->err_var[v] = 0.;
+	for (int c = 0; c < m->C; ++c) { culprit_on_constraint(w, c); culprit_apply(w, c, +1); }
+}
+/* CulpritSearchErrorProjection::update_variable_errors (…:131-151) */
+static void culprit_update_variable_errors(Walker* w, int c)
+{
+	culprit_apply(w, c, -1);
+	culprit_on_constraint(w, c);
+	culprit_apply(w, c, +1);
 }
 
 /* ---- sampling ---------------------------------------------------------------------------- */
@@ -785,7 +884,10 @@ static void update_errors(Walker* w, int v, int new_value)
 		for (int i = 0; i < n; ++i) {
 			int c = affected[i];
 			w->cur_err[c] += w->deltas[i];
-			for (int p = m->coff[c]; p < m->coff[c + 1]; ++p) w->err_var[m->cvars[p]] += w->deltas[i];
+			/* the projection is updated BEFORE the constraint's cache and the variable's value (search_unit.hpp:457-465):
+			 * Culprit's simulated deltas therefore see the new error with the old sums / counts / assignment */
+			if (w->opt.strategy == GHOST_STRATEGY_CULPRIT) culprit_update_variable_errors(w, c);
+			else for (int p = m->coff[c]; p < m->coff[c + 1]; ++p) w->err_var[m->cvars[p]] += w->deltas[i];
 			ctr_update(w, c, v, new_value);
 		}
 		return;
@@ -795,7 +897,8 @@ static void update_errors(Walker* w, int v, int new_value)
 	for (int i = 0; i < n; ++i) {
 		int c = affected[i];
 		w->cur_err[c] += w->deltas[i];
-		for (int p = m->coff[c]; p < m->coff[c + 1]; ++p) w->err_var[m->cvars[p]] += w->deltas[i];
+		if (w->opt.strategy == GHOST_STRATEGY_CULPRIT) culprit_update_variable_errors(w, c);
+		else for (int p = m->coff[c]; p < m->coff[c + 1]; ++p) w->err_var[m->cvars[p]] += w->deltas[i];
 		if (ctr_has_variable(m, c, v)) {
 			ctr_update(w, c, v, next_value);
 			if (ctr_has_variable(m, c, j)) ctr_update(w, c, j, current_value);
@@ -879,13 +982,15 @@ static Walker* walker_create(const OracleModel* m, const GhostSearchOpts* opts, 
 	w->flag = (uint8_t*)calloc(V, 1);
 	w->deltas = (double*)calloc(2 * C + 2, sizeof(double));
 	w->wvec = (double*)calloc(V, sizeof(double));
+	w->culprit = (double*)calloc(m->coff[m->C] > 0 ? m->coff[m->C] : 1, sizeof(double));
+	w->culprit_out = (double*)calloc(C, sizeof(double));
 	w->cand_sum = (double*)calloc(big + 2, sizeof(double));
 	return w;
 }
 static void walker_destroy(Walker* w)
 {
 	free(w->x); free(w->cur_err); free(w->cur_sum); free(w->count); free(w->tabu); free(w->err_var);
-	free(w->wvec); free(w->cand_sum);
+	free(w->wvec); free(w->cand_sum); free(w->culprit); free(w->culprit_out);
 	free(w->best_x); free(w->cand); free(w->scratch_a); free(w->scratch_b); free(w->sample);
 	free(w->flag); free(w->deltas); free(w);
 }
@@ -1242,6 +1347,13 @@ int oracle_stepper_peek(OracleStepper* s, int32_t* x, int32_t* candidates, int32
 	if (current_sat_error) *current_sat_error = w->cur_sat;
 	if (would_reset) *would_reset = (nt >= w->opt.reset_threshold || (antidote ? w->nvec == 0 : w->ncand == 0)) ? 1 : 0;
 	return 0;
+}
+
+/* the projected errors of the walker (SearchUnitData::error_variables) and the constraint errors */
+void oracle_stepper_errors(OracleStepper* s, double* var_error, double* ctr_error)
+{
+	if (var_error) memcpy(var_error, s->w->err_var, sizeof(double) * s->w->m->V);
+	if (ctr_error) memcpy(ctr_error, s->w->cur_err, sizeof(double) * s->w->m->C);
 }
 
 /* One iteration with the given choices; see walker_iteration for the return value. */

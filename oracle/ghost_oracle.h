@@ -74,6 +74,7 @@ void oracle_stepper_sync(OracleStepper* s, const int32_t* x);
 int oracle_stepper_peek(OracleStepper* s, int32_t* x, int32_t* candidates, int32_t* num_candidates,
                         int32_t* tabu_pairs, int32_t* num_tabu, int64_t* local_moves, double* current_sat_error,
                         int32_t* would_reset);
+void oracle_stepper_errors(OracleStepper* s, double* var_error, double* ctr_error);
 int oracle_stepper_step(OracleStepper* s, int32_t variable, int32_t value, int32_t force_on_plateau,
                         OracleTraceRow* row, int32_t* ties, int32_t* num_ties, GhostCounters* counters);
 

@@ -47,6 +47,10 @@
 #include "global_constraints/linear_equation_g.hpp"
 #include "algorithms/adaptive_search_error_projection_algorithm.hpp"
 #include "algorithms/antidote_search_variable_heuristic.hpp"
+#include "algorithms/culprit_search_error_projection_algorithm.hpp"
+#include "algorithms/uniform_variable_heuristic.hpp"
+#include "algorithms/adaptive_search_variable_candidates_heuristic.hpp"
+#include "algorithms/adaptive_search_value_heuristic.hpp"
 #include "algorithms/antidote_search_variable_candidates_heuristic.hpp"
 #include "algorithms/antidote_search_value_heuristic.hpp"
 
@@ -574,7 +578,7 @@ extern "C" int ref_complete_search( const GhostModelDesc* d, int64_t max_solutio
  *         reference itself prints.  usage: ref_bench desc.txt timeout_us parallel threads [custom_start] */
 int main( int argc, char** argv )
 {
-	if( argc < 5 ) { std::fprintf( stderr, "usage: %s desc.txt timeout_us parallel_runs threads [custom_start [strategy: 0 adaptive search, 1 antidote]]\n", argv[0] ); return 2; }
+	if( argc < 5 ) { std::fprintf( stderr, "usage: %s desc.txt timeout_us parallel_runs threads [custom_start [strategy: 0 adaptive search, 1 antidote, 2 culprit projection]]\n", argv[0] ); return 2; }
 	auto desc = std::make_shared<DescCopy>();
 	if( !desc->load( argv[1] ) ) { std::fprintf( stderr, "cannot read %s\n", argv[1] ); return 2; }
 	DescBuilder builder( desc );
@@ -585,7 +589,8 @@ int main( int argc, char** argv )
 	if( argc > 5 ) options.custom_starting_point = std::atoi( argv[5] ) != 0;
 	double cost = 0;
 	std::vector<int> solution;
-	if( argc > 6 && std::atoi( argv[6] ) == 1 )
+	const int strategy = argc > 6 ? std::atoi( argv[6] ) : 0;
+	if( strategy == 1 || strategy == 2 )
 	{
 		/* The Antidote heuristic set.  Solver::fast_search never builds it (include/solver.hpp:499-518), so the SearchUnit
 		 * is constructed here the way fast_search does for the default set, with the option defaults resolved as at
@@ -598,11 +603,26 @@ int main( int argc, char** argv )
 		if( options.restart_threshold < 0 ) options.restart_threshold = V;
 		if( options.number_variables_to_reset < 0 ) options.number_variables_to_reset = std::max( 2, static_cast<int>( std::ceil( V * 0.1 ) ) );
 		if( options.number_start_samplings < 0 ) options.number_start_samplings = 10;
-		SearchUnit unit( Access::build( builder ), options,
-		                 std::make_unique<algorithms::AntidoteSearchVariableHeuristic>(),
-		                 std::make_unique<algorithms::AntidoteSearchVariableCandidatesHeuristic>(),
-		                 std::make_unique<algorithms::AntidoteSearchValueHeuristic>(),
-		                 std::make_unique<algorithms::AdaptiveSearchErrorProjection>() );
+		/* 1: the three Antidote heuristics over the default projection; 2: the default heuristics over the Culprit projection */
+		std::unique_ptr<algorithms::VariableHeuristic> vh;
+		std::unique_ptr<algorithms::VariableCandidatesHeuristic> vch;
+		std::unique_ptr<algorithms::ValueHeuristic> valh;
+		std::unique_ptr<algorithms::ErrorProjection> ep;
+		if( strategy == 1 )
+		{
+			vh = std::make_unique<algorithms::AntidoteSearchVariableHeuristic>();
+			vch = std::make_unique<algorithms::AntidoteSearchVariableCandidatesHeuristic>();
+			valh = std::make_unique<algorithms::AntidoteSearchValueHeuristic>();
+			ep = std::make_unique<algorithms::AdaptiveSearchErrorProjection>();
+		}
+		else
+		{
+			vh = std::make_unique<algorithms::UniformVariableHeuristic>();
+			vch = std::make_unique<algorithms::AdaptiveSearchVariableCandidatesHeuristic>();
+			valh = std::make_unique<algorithms::AdaptiveSearchValueHeuristic>();
+			ep = std::make_unique<algorithms::CulpritSearchErrorProjection>();
+		}
+		SearchUnit unit( Access::build( builder ), options, std::move( vh ), std::move( vch ), std::move( valh ), std::move( ep ) );
 		unit.local_search( std::atof( argv[2] ) );
 		std::cout << "HARNESS antidote best_sat_error=" << unit.data.best_sat_error << " iterations=" << unit.data.search_iterations
 		          << " resets=" << unit.data.resets << "\nHARNESS solution:";

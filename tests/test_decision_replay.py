@@ -99,7 +99,7 @@ def _replay(name, ref_built, tmp_path, timeout_us, min_iterations, need=(), stra
             p = st.peek()
             assert not p["would_reset"], (name, r["it"], "the oracle would reset, the reference did not")
             assert np.array_equal(p["x"], r["x"]), (name, r["it"], "assignment")
-            if strategy == 0:   # (the Antidote trace prints a sampled histogram of its weight vector, not the vector)
+            if strategy != 1:   # (the Antidote trace prints a sampled histogram of its weight vector, not the vector)
                 assert p["candidates"] == r["candidates"], (name, r["it"], "candidate variables", p["candidates"], r["candidates"])
             assert p["tabu"] == r["tabu"], (name, r["it"], "tabu list", p["tabu"], r["tabu"])
             assert p["local_moves"] == r["local_moves"], (name, r["it"])
@@ -109,7 +109,7 @@ def _replay(name, ref_built, tmp_path, timeout_us, min_iterations, need=(), stra
             s = st.step(r["var"], value, force)
             assert s["rc"] == 0, (name, r["it"], "choice rejected", s["rc"], r["var"], value)
             assert s["counters"]["search_iterations"] == r["it"], (name, r["it"], "iteration counter (resets included)")
-            if strategy == 0:
+            if strategy != 1:
                 assert s["ties"] == r["ties"], (name, r["it"], "ties", s["ties"], r["ties"])
             if r["ties"] or (strategy == 1 and r["delta"] is not None):
                 assert s["min_conflict"] == r["delta"], (name, r["it"])
@@ -163,4 +163,21 @@ def test_replay_antidote_strategy(name, timeout_us, ref_built, tmp_path):
     longer the variable's own entry —, the picked value must be drawable, its delta, the branch, the tabu list, the move
     counter and every resulting assignment must agree."""
     seen = _replay(name, ref_built, tmp_path, timeout_us, 40, need=(1,), strategy=1)
+    assert seen["iterations"] >= 40
+
+
+@pytest.mark.parametrize("name,timeout_us", [("magic_square:4", 60000), ("n_queens:8", 60000), ("knapsack:12x3", 30000), ("mixed", 40000),
+                                              ("costas_lag:8", 60000)])
+def test_replay_culprit_projection(name, timeout_us, ref_built, tmp_path):
+    """GHOST_STRATEGY_CULPRIT: the default heuristics over the reference's Culprit Search error projection (the harness builds
+    the SearchUnit with CulpritSearchErrorProjection).  The candidate list printed at every iteration is the arg-max set of the
+    projected errors — fractional doubles here — so its equality checks the projection bit for bit, including what the
+    reference's code does by accident: variables OUTSIDE a constraint's scope receive a share of its error (their entry of
+    the V-long vector is 0 before the "max - x" transform, culprit_search_error_projection_algorithm.cpp:94-100), and the
+    update step computes row - errors instead of errors - row (std::transform operand order, 136-141)."""
+    # (no permutation problem with DIFFERENT domains here or above: the reference's fourth eligibility test of a swap partner
+    #  compares iterators of three temporary copies of the domain — search_unit.hpp:858-860, get_full_domain() returns by
+    #  value — which is undefined behaviour and in practice always true; the restatement implements the stated intent,
+    #  "x_v is in D(j)", see DESIGN.md §5)
+    seen = _replay(name, ref_built, tmp_path, timeout_us, 40, need=(1,), strategy=2)
     assert seen["iterations"] >= 40
