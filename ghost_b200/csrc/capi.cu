@@ -280,7 +280,10 @@ extern "C" int ghost_b200_search_begin(GhostModel* gm, const GhostSearchOpts* op
 	ghost_b200_resolve_opts(gm, &s->opts);
 	const DevModel& m = gm->low.dev;
 	if (s->opts.number_variables_to_reset > m.V) s->opts.number_variables_to_reset = m.V;
-	if (s->opts.strategy != GHOST_STRATEGY_ADAPTIVE_SEARCH && s->opts.strategy != GHOST_STRATEGY_ANTIDOTE) { delete s; return set_error(GHOST_B200_ERR_INVALID, "strategy must be GHOST_STRATEGY_ADAPTIVE_SEARCH or GHOST_STRATEGY_ANTIDOTE"); }
+	if (s->opts.strategy != GHOST_STRATEGY_ADAPTIVE_SEARCH && s->opts.strategy != GHOST_STRATEGY_ANTIDOTE && s->opts.strategy != GHOST_STRATEGY_CULPRIT) {
+		delete s;
+		return set_error(GHOST_B200_ERR_INVALID, "strategy must be GHOST_STRATEGY_ADAPTIVE_SEARCH, GHOST_STRATEGY_ANTIDOTE or GHOST_STRATEGY_CULPRIT");
+	}
 	s->layout = gm->low.layout(s->opts.threads_per_walker, s->opts.number_variables_to_reset, s->opts.strategy);
 	LaunchCfg cfg;
 	rc = pick_launch(gm, s->layout, s->opts.threads_per_walker, &cfg);
@@ -308,6 +311,16 @@ extern "C" int ghost_b200_search_begin(GhostModel* gm, const GhostSearchOpts* op
 		if (cfg.T != 32) { delete s; return set_error(GHOST_B200_ERR_UNSUPPORTED, "the Antidote strategy runs one warp per walker: at most 1024 variables and 1024 candidates"); }
 		const double cap = 4294967295.0;
 		if ((double)gm->low.error_bound * std::max(m.V, m.max_candidates) > cap) { delete s; return set_error(GHOST_B200_ERR_UNSUPPORTED, "the Antidote strategy needs (error bound x variables) below 2^32"); }
+	}
+	if (s->opts.strategy == GHOST_STRATEGY_CULPRIT && cfg.T != 32) {
+		delete s;
+		return set_error(GHOST_B200_ERR_UNSUPPORTED, "the Culprit strategy runs one warp per walker: at most 1024 variables and 1024 candidates");
+	}
+	if (s->opts.strategy == GHOST_STRATEGY_CULPRIT && m.static_error > 0) {
+		// the projection simulates single-value changes on every constraint in error; the constant AllDifferent of a
+		// permutation problem keeps no count table to simulate them on
+		delete s;
+		return set_error(GHOST_B200_ERR_UNSUPPORTED, "the Culprit strategy needs distinct start values in a permutation problem with an AllDifferent over all variables");
 	}
 	s->elastic = s->opts.elastic_epochs == 1 ? 1 : 0;
 	s->walkers = s->opts.number_walkers;

@@ -299,7 +299,7 @@ __device__ inline void initialize_variable_values(const DevModel& m, const Walke
 }
 
 // SearchUnit::local_move (search_unit.hpp:516-541)
-template <int T, bool PERM, bool EQ, bool F32, class WS>
+template <int T, bool PERM, bool EQ, bool F32, int STRAT = 0, class WS>
 __device__ inline void local_move(const DevModel& m, const WS& s, WalkerRegs& r, const SearchParams& p, int* best_x, int v, int new_value, int delta, int nh)
 {
 	MV mv(m);
@@ -317,7 +317,7 @@ __device__ inline void local_move(const DevModel& m, const WS& s, WalkerRegs& r,
 	}
 	if (F32) apply_move_f32(m, s, v, new_value, nh);
 	else if (EQ) apply_move_eq<T, PERM>(m, s, v, new_value, nh);
-	else apply_move<T>(m, s, v, new_value);
+	else apply_move<T, STRAT == 2>(m, s, v, new_value);
 }
 
 // =================================================================================================
@@ -349,7 +349,7 @@ struct ColdState {
 };
 enum { GB_COLD_FIRST = 0, GB_COLD_RESTART = 1, GB_COLD_PERTURB = 2 };
 
-template <int T, bool PERM, bool EQ, class XT, bool F32>
+template <int T, bool PERM, bool EQ, class XT, bool F32, int STRAT = 0>
 static __device__ __noinline__ ColdState walker_reinit(const DevModel& m, const WalkerLayout& L, const SearchParams& p,
                                                        unsigned char* base, int* best_x, unsigned long long walker, int mode, ColdState c)
 {
@@ -389,6 +389,7 @@ static __device__ __noinline__ ColdState walker_reinit(const DevModel& m, const 
 	else if (PERM) random_permutations<T>(m, s, rng, p.nreset);
 	else monte_carlo_sampling<T>(m, s, rng, p.nreset);
 	initialize_data_structures<T, EQ, F32>(m, L, base, s, r, best_x);
+	if (STRAT == 2) culprit_compute_variable_errors(m, L, s); // ErrorProjection::compute_variable_errors (search_unit.hpp:305-308)
 	if (mode == GB_COLD_FIRST) r.best_pending = 1; // search_unit.hpp:714-717: final_solution = the initial assignment
 	c.must_compute = r.must_compute; c.tabu_base = r.tabu_base; c.cur_sat = r.cur_sat; c.best_sat = r.best_sat;
 	c.best_pending = r.best_pending; c.resume_pending = r.resume_pending;
@@ -397,7 +398,7 @@ static __device__ __noinline__ ColdState walker_reinit(const DevModel& m, const 
 }
 
 // F32: the fp32 form of the LinearEq-only swap evaluation (walker.cuh, evaluate_f32); T == 32, PERM, EQ, 16-bit x only
-// STRAT: GhostStrategy (1 = the Antidote heuristic set, walker.cuh; T == 32 and not F32)
+// STRAT: GhostStrategy (1 = the Antidote heuristic set, 2 = the Culprit error projection, walker.cuh; T == 32 and not F32)
 template <int T, bool PERM, bool EQ, class XT, bool F32 = false, int FS = 0, int STRAT = 0>
 __global__ void __launch_bounds__(T == 32 ? 128 : T, (GB_WARPS_PER_SM * 32) / (T == 32 ? 128 : T))
 search_kernel(const __grid_constant__ DevModel m, const __grid_constant__ WalkerLayout L, const __grid_constant__ SearchParams p)
@@ -443,7 +444,7 @@ search_kernel(const __grid_constant__ DevModel m, const __grid_constant__ Walker
 		c.best_sat = r.best_sat; c.best_pending = r.best_pending; c.resume_pending = r.resume_pending;
 		c.cur_opt = r.cur_opt; c.best_opt = r.best_opt; c.obj_sum = r.obj_sum; c.next_event = rng.next_event;
 		G::sync();
-		c = walker_reinit<T, PERM, EQ, XT, F32>(m, L, p, walker_base, best_x, rng.walker, mode, c);
+		c = walker_reinit<T, PERM, EQ, XT, F32, STRAT == 2 ? 2 : 0>(m, L, p, walker_base, best_x, rng.walker, mode, c);
 		r.must_compute = c.must_compute; r.tabu_base = c.tabu_base; r.cur_sat = c.cur_sat; r.best_sat = c.best_sat;
 		r.best_pending = c.best_pending; r.resume_pending = c.resume_pending;
 		r.cur_opt = c.cur_opt; r.best_opt = c.best_opt; r.obj_sum = c.obj_sum; rng.next_event = c.next_event;
@@ -500,6 +501,11 @@ search_kernel(const __grid_constant__ DevModel m, const __grid_constant__ Walker
 			if (r.must_compute) cq.bits = 0u;
 			rnd_early = rng.block(rng.next_event, 0);
 			v_antidote = antidote_select(m, s, L.nchunks_v, r.local_moves - r.tabu_base, rnd_early.x, cq, &r.n_tabu, &r.ncand);
+		} else if (STRAT == 2) {
+			if (r.must_compute) {
+				r.ncand = scan_candidates_culprit(m, s, L.nchunks_v, r.local_moves - r.tabu_base, optimization && r.cur_sat == 0, &r.n_tabu, cq);
+				r.cand_max = 0;
+			}
 		} else if (r.must_compute)
 			r.ncand = scan_candidates<T>(m, s, L.nchunks_v, r.local_moves - r.tabu_base, optimization && r.cur_sat == 0, s.red, &r.cand_max, &r.n_tabu, cq);
 
@@ -570,7 +576,7 @@ search_kernel(const __grid_constant__ DevModel m, const __grid_constant__ Walker
 
 			int plateau = 0, local_min = 0;
 			if (gmin < 0) { // search_unit.hpp:1042-1050
-				local_move<T, PERM, EQ, F32>(m, s, r, p, best_x, v, new_value, gmin, nh);
+				local_move<T, PERM, EQ, F32, STRAT>(m, s, r, p, best_x, v, new_value, gmin, nh);
 				if (optimization) r.cur_opt = internal_cost(m, r.obj_sum);
 				trace_branch = 1;
 			} else if (gmin == 0) {
@@ -581,7 +587,7 @@ search_kernel(const __grid_constant__ DevModel m, const __grid_constant__ Walker
 						obj2 = r.obj_sum + (long long)mv.obj_coef(v) * (xj - xv) + (long long)mv.obj_coef(new_value) * (xv - xj);
 					} else obj2 = r.obj_sum + (long long)mv.obj_coef(v) * (new_value - s.x[v]);
 					long long cand_opt = internal_cost(m, obj2);
-					if (r.cur_opt > cand_opt) { local_move<T, PERM, EQ, F32>(m, s, r, p, best_x, v, new_value, 0, nh); r.cur_opt = cand_opt; trace_branch = 2; }
+					if (r.cur_opt > cand_opt) { local_move<T, PERM, EQ, F32, STRAT>(m, s, r, p, best_x, v, new_value, 0, nh); r.cur_opt = cand_opt; trace_branch = 2; }
 					else if (r.cur_opt == cand_opt) plateau = 1;
 					else local_min = 1;
 				} else plateau = 1; // 1136-1145
@@ -593,7 +599,7 @@ search_kernel(const __grid_constant__ DevModel m, const __grid_constant__ Walker
 					r.must_compute = 1;
 					trace_branch = 4;
 				} else {
-					local_move<T, PERM, EQ, F32>(m, s, r, p, best_x, v, new_value, 0, nh);
+					local_move<T, PERM, EQ, F32, STRAT>(m, s, r, p, best_x, v, new_value, 0, nh);
 					if (tid == 0) s.counters[K_PLATEAU] += 1;
 					trace_branch = 3;
 				}

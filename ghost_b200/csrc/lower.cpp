@@ -86,7 +86,7 @@ int lower_model(const GhostModelDesc* d, LoweredModel* out, std::string* why)
 	bool has_all_equal = false;
 	std::vector<std::vector<std::pair<int, int>>> rows(V); // (constraint, coefficient|position)
 	int cnt_total = 0;
-	int64_t error_bound = 0;
+	int64_t error_bound = 0, static_error = 0;
 	int64_t max_T_bound = 0, max_abs_coef = 0;   // over the linear constraints: |sum - rhs| and |coefficient|
 	bool has_abs_diff = false;
 	for (int c = 0; c < C; ++c) {
@@ -169,6 +169,7 @@ int lower_model(const GhostModelDesc* d, LoweredModel* out, std::string* why)
 			}
 			kind[c] = GB_KIND_STATIC;
 			rhs[c] = static_cast<int32_t>(err);
+			static_error += err;
 			error_bound += err;
 		} else if (is_alldiff_like(k)) {
 			int64_t n = e - b;
@@ -374,6 +375,12 @@ int lower_model(const GhostModelDesc* d, LoweredModel* out, std::string* why)
 		o.c2v_pos = put(packed);
 	}
 	o.has_ctr = put(has_ctr);
+	bool given_sorted = true;
+	{
+		std::vector<int32_t> given(d->dom_values, d->dom_values + d->dom_offset[V]);
+		given_sorted = given == dom_vals;
+		o.dom_given = put(given);
+	}
 	// ---- structured grid -------------------------------------------------------------------------------------
 	// Matrix-shaped models (magic squares, Latin-square sums, ...): with the variables cut into consecutive groups of
 	// CW, every variable (g, l) is in U_g, a constraint common to its whole group, and in L_l, a constraint common to
@@ -478,6 +485,8 @@ int lower_model(const GhostModelDesc* d, LoweredModel* out, std::string* why)
 	for (int v = 0; v < V; ++v) if (rows[v].empty()) m.all_have_ctr = 0;
 	m.x16 = (min_value >= 0 && max_value <= 65535) ? 1 : 0;
 	m.v128 = V & ~127;
+	m.given_sorted = given_sorted ? 1 : 0;
+	m.static_error = static_cast<int>(std::min<int64_t>(static_error, INT32_MAX));
 	m.f32_ok = f32_ok ? 1 : 0;
 	m.sg_ok = sg_ok; m.sg_cw = sg_cw; m.sg_groups = sg_groups; m.sg_xn = sg_xn; m.sg_au = sg_au; m.sg_al = sg_al;
 	return GHOST_B200_OK;
@@ -502,6 +511,12 @@ WalkerLayout LoweredModel::layout(int /*threads_per_walker*/, int nreset, int st
 	w.cand_key = take(4 * w.nchunks_v);
 	w.cand_bits = take(4 * w.nchunks_v);
 	w.cnt = take(2 * std::max(1, m.cnt_total));
+	if (strategy == GHOST_STRATEGY_CULPRIT) {
+		w.errd = take(8 * vpad);
+		w.culprit = take(8 * std::max(1, m.nnz));
+		w.culprit_out = take(8 * std::max(1, m.C));
+		w.cpos = take(2 * vpad);
+	}
 	w.persist_bytes = at;
 	w.counters = take(8 * 8);
 	// sampling scratch lives in arrays that are dead while a reset samples: the tabu list (cleared by

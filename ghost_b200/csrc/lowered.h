@@ -37,6 +37,8 @@ struct BlobOffsets {
 	                           // that carry further constraints}
 	int c2v_pos;               // uint16 per scope entry: scan_pos() of the variable (projection scatter)
 	int has_ctr;               // [ceil(V/32)] bit v%32 set iff variable v appears in some constraint
+	int dom_given;             // the domain values in the order of the descriptor (Culprit projection: Variable::get_partial_domain
+	                           // works on the domain as the user gave it), same offsets as dom_vals
 	int total;
 };
 
@@ -71,6 +73,9 @@ struct DevModel {
 	int sg_cw, sg_groups;      // variables per group (<= 32), number of groups (<= 32)
 	int sg_xn;                 // largest number of such cells in a group (passes of the second loop)
 	int sg_au, sg_al;          // the common coefficient of the group constraints / of the position constraints
+	int given_sorted;          // every domain was given in ascending order (dom_given == dom_vals)
+	int static_error;          // total error of the constraints lowered to GB_KIND_STATIC (an AllDifferent over all variables of a
+	                           // permutation problem whose start values repeat: constant, but not 0)
 };
 
 // device-only constraint kind: an AllDifferent over all variables of a permutation problem
@@ -98,6 +103,13 @@ struct WalkerLayout {
 	int sample;                         // int32 [2 * nreset]
 	int red;                            // int32 [64] cross-warp scratch
 	int sums;                           // int32 [nchunks_c * 32] cumulated delta of every candidate slot (Antidote strategy only)
+	// Culprit strategy only (all inside the persisted prefix): projected errors in fp64, the rows of the reference's
+	// _error_variables_by_constraints table (one value per scope entry + one for all variables outside the scope),
+	// and a scratch map variable -> scope entry of the constraint being applied
+	int errd;                           // double [V padded to 32]
+	int culprit;                        // double [nnz]
+	int culprit_out;                    // double [C]
+	int cpos;                           // int16 [V padded]
 	int persist_bytes;                  // x..cnt(+cand chunks) prefix that is saved between epochs
 	int total_bytes;
 	int nchunks_v, nchunks_c;

@@ -133,6 +133,8 @@ extern "C" int ghost_b200_search_noalloc(GhostModel* model, const GhostSearchOpt
 	GhostSearchOpts o = *opts_in;
 	ghost_b200_resolve_opts(model, &o);
 	if (o.number_variables_to_reset > low->V) o.number_variables_to_reset = low->V;
+	if (o.strategy != GHOST_STRATEGY_ADAPTIVE_SEARCH || o.elite_restart_percent != 0)
+		return fail(GHOST_B200_ERR_UNSUPPORTED, "search_noalloc runs the default strategy without cooperative restarts (use ghost_b200_search_begin for the others)");
 	const WalkerLayout L = low->layout(o.threads_per_walker, o.number_variables_to_reset);
 	int T = low->effective_threads_per_walker(o.threads_per_walker);
 	if (!(T == 32 || T == 64 || T == 128 || T == 256))

@@ -16,6 +16,7 @@
 #include <stdint.h>
 
 #include "lowered.h"
+#include <math_constants.h>
 
 namespace ghost_b200 {
 
@@ -135,6 +136,8 @@ struct WST {
 	int* val_key; unsigned* val_bits;
 	int4* hoist; int* upd; int* sample; int* red;
 	int* sums;                  // Antidote strategy: cumulated delta of every candidate slot
+	// Culprit strategy: projected errors (fp64, natural variable order), the table rows, variable -> scope entry scratch
+	double* errd; double* culprit; double* culprit_out; unsigned short* cpos;
 	__device__ __forceinline__ int cnt(int idx) const { return reinterpret_cast<const unsigned short*>(cnt32)[idx]; }
 	__device__ __forceinline__ void cnt_add(int idx, int d) const
 	{
@@ -167,6 +170,8 @@ __device__ __forceinline__ WS make_ws(unsigned char* base_in, const WalkerLayout
 	s.hoist = (int4*)(base + L.hoist); s.upd = (int*)(base + L.upd); s.sample = (int*)(base + L.sample);
 	s.red = (int*)(base + L.red);
 	s.sums = (int*)(base + L.sums);
+	s.errd = (double*)(base + L.errd); s.culprit = (double*)(base + L.culprit); s.culprit_out = (double*)(base + L.culprit_out);
+	s.cpos = (unsigned short*)(base + L.cpos);
 	return s;
 }
 
@@ -1208,6 +1213,191 @@ __device__ inline int antidote_value(const int* sums, int nchunks_c, uint32_t wo
 }
 
 // ---------------------------------------------------------------------------------------------
+// Culprit Search error projection (GhostSearchOpts::strategy == GHOST_STRATEGY_CULPRIT; one warp per walker).
+// Reference: src/algorithms/culprit_search_error_projection_algorithm.cpp; restated in oracle/ghost_oracle.c
+// (culprit_on_constraint / culprit_apply / culprit_update_variable_errors), which the decision-replay tests pin
+// against the reference's own traces.  Per constraint c the reference keeps a row of V doubles: for a scope
+// variable the sum of the error deltas of moving it to the two neighbouring values of its current one in the
+// domain AS GIVEN (Variable::get_partial_domain(3)), turned into max - x and scaled so that the row sums to the
+// constraint's error; a variable OUTSIDE the scope gets the same treatment of a 0 entry, i.e. max / sum * error.
+// Here a row is one double per scope entry (s.culprit, indexed like c2v) plus one for everything outside
+// (s.culprit_out[c]).  The projected errors are doubles (s.errd); every operation that rounds (the division, the
+// product, the sums of rows into errors) is written with the _rn intrinsics in the reference's order, so the
+// values — and with them the arg-max ties of the candidate scan — are the reference's bit for bit.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ double warp_max_f64(double v)
+{
+#pragma unroll
+	for (int off = 16; off > 0; off >>= 1) v = fmax(v, __shfl_xor_sync(0xffffffffu, v, off));
+	return v;
+}
+__device__ __forceinline__ double warp_sum_f64(double v) // exact here: every term is an integer-valued double far below 2^53
+{
+#pragma unroll
+	for (int off = 16; off > 0; off >>= 1) v = __dadd_rn(v, __shfl_xor_sync(0xffffffffu, v, off));
+	return v;
+}
+
+// Variable::get_partial_domain(3) around the current value (variable.cpp:60-86), first and last entry of what it
+// returns — see partial_domain_ends in the oracle for the two wrap-around cases the reference's iterator arithmetic produces
+__device__ inline void culprit_partial_ends(const DevModel& m, const MV& mv, int var, int n, int cur, int* first, int* third)
+{
+	const int off = mv.ld(m.o.dom_off, var);
+	const bool arithmetic = m.given_sorted && m.contiguous_domains;
+	const int sec = m.given_sorted ? m.o.dom_vals : m.o.dom_given;
+	const int lo = mv.dom_lo(var);
+	*first = arithmetic ? lo : mv.ld(sec, off);
+	*third = arithmetic ? lo + n - 1 : mv.ld(sec, off + n - 1);
+	if (n <= 3) return;
+	int index;
+	if (arithmetic) index = cur - lo;
+	else if (m.given_sorted) {
+		int b = 0, e = n;
+		while (b < e) { const int mid = (b + e) >> 1; if (mv.ld(sec, off + mid) < cur) b = mid + 1; else e = mid; }
+		index = b;
+	} else {
+		index = 0;
+		while (index < n && mv.ld(sec, off + index) != cur) ++index;
+	}
+	if (index >= 1 && index + 2 <= n) {
+		*first = arithmetic ? cur - 1 : mv.ld(sec, off + index - 1);
+		*third = arithmetic ? cur + 1 : mv.ld(sec, off + index + 1);
+	}
+}
+
+// CulpritSearchErrorProjection::compute_variable_errors_on_constraint (…:50-110): row c from the constraint's
+// current error, its cache and the assignment.  Lanes over the scope entries; ends with a warp barrier.
+template <class WS>
+__device__ inline void culprit_on_constraint(const DevModel& m, const WS& s, int c)
+{
+	MV mv(m);
+	const int lane = threadIdx.x & 31;
+	const int b = mv.scope_begin(c), e = mv.scope_begin(c + 1), outside = m.V - (e - b);
+	const int err = s.err_of(c);
+	if (err <= 0) { // uniform over the warp
+		for (int p = b + lane; p < e; p += 32) s.culprit[p] = 0.;
+		if (lane == 0) s.culprit_out[c] = 0.;
+		__syncwarp();
+		return;
+	}
+	const int kind = mv.kind(c);
+	const bool by_position = kind == GHOST_KIND_ALL_DIFFERENT_ABS_DIFF || kind == GHOST_KIND_ALL_DIFFERENT_LAG_DIFF;
+	double mx = -CUDART_INF;
+	for (int p = b + lane; p < e; p += 32) {
+		const int var = mv.scope_var(p), n = mv.dom_size(var), cur = s.x[var];
+		const int ea = by_position ? p - b : mv.ld(m.o.ent_coef, p);
+		int sum;
+		if (n > 2) {
+			int first, third;
+			culprit_partial_ends(m, mv, var, n, cur, &first, &third);
+			sum = constraint_delta(mv, s, c, var, ea, first, -1, 0, 0) + constraint_delta(mv, s, c, var, ea, third, -1, 0, 0);
+		} else if (n == 2) {
+			const int off = mv.ld(m.o.dom_off, var);
+			const int d0 = mv.ld(m.o.dom_given, off), d1 = mv.ld(m.o.dom_given, off + 1);
+			sum = constraint_delta(mv, s, c, var, ea, d0 == cur ? d1 : d0, -1, 0, 0);
+		} else
+			sum = constraint_delta(mv, s, c, var, ea, cur, -1, 0, 0);
+		const double val = (double)sum;
+		s.culprit[p] = val;
+		mx = fmax(mx, val);
+	}
+	mx = warp_max_f64(mx);
+	if (outside > 0) mx = fmax(mx, 0.); // the entries of the variables outside the scope are 0 and take part in the maximum
+	double part = 0.;
+	for (int p = b + lane; p < e; p += 32) { const double t = __dadd_rn(-s.culprit[p], mx); s.culprit[p] = t; part = __dadd_rn(part, t); }
+	const double out = outside > 0 ? mx : 0.;
+	const double sum = __dadd_rn(warp_sum_f64(part), __dmul_rn(out, (double)outside));
+	const double derr = (double)err;
+	for (int p = b + lane; p < e; p += 32) { const double t = s.culprit[p]; s.culprit[p] = t == 0. ? 0. : __dmul_rn(__ddiv_rn(t, sum), derr); }
+	if (lane == 0) s.culprit_out[c] = (outside > 0 && out != 0.) ? __dmul_rn(__ddiv_rn(out, sum), derr) : 0.;
+	__syncwarp();
+}
+
+// s.cpos[v] = scope entry of v in constraint c, 0xFFFF outside the scope.  Ends with a warp barrier.
+template <class WS>
+__device__ inline void culprit_map_scope(const DevModel& m, const WS& s, int c)
+{
+	MV mv(m);
+	const int lane = threadIdx.x & 31;
+	const int b = mv.scope_begin(c), e = mv.scope_begin(c + 1);
+	for (int v = lane; v < m.V; v += 32) s.cpos[v] = 0xFFFFu;
+	__syncwarp();
+	for (int p = b + lane; p < e; p += 32) s.cpos[mv.scope_var(p)] = (unsigned short)(p - b);
+	__syncwarp();
+}
+// Row c combined into the projected errors over ALL variables (s.cpos maps c's scope).  ADD: err = row + err
+// (std::plus, …:122-127, 145-150); otherwise err = row - err: the "remove" step of update_variable_errors (…:136-141)
+// hands std::transform the row as first and the errors as second range with std::minus — restated as written.
+template <bool ADD, class WS>
+__device__ inline void culprit_apply(const DevModel& m, const WS& s, int c)
+{
+	MV mv(m);
+	const int lane = threadIdx.x & 31;
+	const int b = mv.scope_begin(c);
+	const double out = s.culprit_out[c];
+	for (int v = lane; v < m.V; v += 32) {
+		const unsigned q = s.cpos[v];
+		const double row = q == 0xFFFFu ? out : s.culprit[b + (int)q];
+		s.errd[v] = ADD ? __dadd_rn(row, s.errd[v]) : __dsub_rn(row, s.errd[v]);
+	}
+	__syncwarp();
+}
+// CulpritSearchErrorProjection::compute_variable_errors (…:112-129)
+template <class WS>
+__device__ inline void culprit_compute_variable_errors(const DevModel& m, const WalkerLayout& L, const WS& s)
+{
+	const int lane = threadIdx.x & 31;
+	for (int v = lane; v < L.nchunks_v * 32; v += 32) s.errd[v] = 0.;
+	__syncwarp();
+	for (int c = 0; c < m.C; ++c) {
+		culprit_on_constraint(m, s, c);
+		culprit_map_scope(m, s, c);
+		culprit_apply<true>(m, s, c);
+	}
+}
+// CulpritSearchErrorProjection::update_variable_errors (…:131-152) for one constraint whose error has just changed
+template <class WS>
+__device__ inline void culprit_update_variable_errors(const DevModel& m, const WS& s, int c)
+{
+	culprit_map_scope(m, s, c);
+	culprit_apply<false>(m, s, c);
+	culprit_on_constraint(m, s, c);
+	culprit_apply<true>(m, s, c);
+}
+
+// AdaptiveSearchVariableCandidatesHeuristic::compute_variable_candidates over the fp64 projected errors: the
+// eligible variables whose error is the largest one and at least -1 (the heuristic's `worst` starts at -1 and the
+// Culprit errors can be negative), compared as doubles.  The summaries come back in the default strategy's form
+// with key 0 for a chunk that attains the maximum and -1 otherwise, so picking, erasing and persisting a candidate
+// set are the default code with cand_max = 0.
+template <class WS>
+__device__ inline int scan_candidates_culprit(const DevModel& m, const WS& s, int nchunks_v, int local_moves, bool free_vars_ok,
+                                              int* ntabu_out, ChunkRegs& q)
+{
+	MV mv(m);
+	const int lane = threadIdx.x & 31;
+	const bool use_mask = !free_vars_ok && !m.all_have_ctr;
+	double my_key = -CUDART_INF; unsigned my_bits = 0u; int ntabu = 0;
+	for (int ch = 0; ch < nchunks_v; ++ch) {
+		const int v = ch * 32 + lane;
+		const bool k = (int)s.tabu[scan_pos(m, v)] > local_moves;   // padding entries are tabu for ever
+		ntabu += k ? 1 : 0;
+		double e = k ? -CUDART_INF : s.errd[v];
+		if (use_mask && !(((unsigned)mv.ld(m.o.has_ctr, ch) >> lane) & 1u)) e = -CUDART_INF;
+		const double c = warp_max_f64(e);
+		const unsigned bb = __ballot_sync(0xffffffffu, e == c);
+		if (lane == ch) { my_key = c; my_bits = bb; }
+	}
+	ntabu = __reduce_add_sync(0xffffffffu, ntabu) - (nchunks_v * 32 - m.V);
+	const double worst = warp_max_f64(my_key);
+	const bool any = worst >= -1.;
+	q.key = (any && my_key == worst) ? 0 : -1;
+	q.bits = my_bits;
+	*ntabu_out = ntabu;
+	return any ? regs_count(q, 0) : 0;
+}
+
+// ---------------------------------------------------------------------------------------------
 // fp32 form of the swap evaluation (DevModel::f32_ok: permutation problem, LinearEquationEq only, one
 // common domain, distinct start values, <= 4 live constraints per variable, one warp per walker).
 //
@@ -1681,7 +1871,10 @@ __device__ inline void apply_move_eq(const DevModel& m, const WS& s, int v, int 
 // shared-memory scatter.  Ends with a barrier.  `new_value` is the swap partner in permutation
 // mode, the value otherwise.
 // ---------------------------------------------------------------------------------------------
-template <int T, class WS>
+// CULPRIT: the Culprit projection is updated per affected constraint, in the reference's order, from the constraint's
+// NEW error with its OLD cache and the OLD assignment (search_unit.hpp:457-465 updates the projection before the
+// constraint): the deltas are computed first, the caches are touched in a second pass after the projection.
+template <int T, bool CULPRIT = false, class WS>
 __device__ inline void apply_move(const DevModel& m, const WS& s, int v, int new_value)
 {
 	typedef Group<T> G;
@@ -1693,6 +1886,29 @@ __device__ inline void apply_move(const DevModel& m, const WS& s, int v, int new
 	if (m.permutation) { j = new_value; xj = s.x[j]; rbj = mv.row_begin(j); degj = mv.row_begin(j + 1) - rbj; }
 	const int nv_new = m.permutation ? xj : new_value;
 	const int naff = degv + degj;
+	// the cache of a constraint of v's row / of the partner's row follows the move (FORCE: the Culprit second pass)
+	auto first_row_cache = [&](int c, int ey, bool both, int eb, bool force) {
+		if (CULPRIT && !force) return;
+		const int kind = mv.kind(c);
+		if (kind == GHOST_KIND_ALL_DIFFERENT || kind == GHOST_KIND_ALL_EQUAL) {
+			if (!both && nv_new != xv) { int tab = mv.cnt_tab(c); s.cnt_add(tab + xv, -1); s.cnt_add(tab + nv_new, +1); }
+		} else if (kind == GHOST_KIND_ALL_DIFFERENT_OFFSET) {
+			const int tab = mv.cnt_tab(c);
+			if (nv_new != xv) { s.cnt_add(tab + ey + xv, -1); s.cnt_add(tab + ey + nv_new, +1); }
+			if (both && xj != xv) { s.cnt_add(tab + eb + xj, -1); s.cnt_add(tab + eb + xv, +1); } // the partner's shifted value moves too
+		} else if (kind_is_linear(kind)) {
+			s.T_of(c) += ey * (nv_new - xv) + (both ? eb * (xv - xj) : 0);
+		}
+	};
+	auto second_row_cache = [&](int c, int ey, bool force) {
+		if (CULPRIT && !force) return;
+		const int kind = mv.kind(c);
+		if (kind == GHOST_KIND_ALL_DIFFERENT || kind == GHOST_KIND_ALL_EQUAL) {
+			if (xv != xj) { int tab = mv.cnt_tab(c); s.cnt_add(tab + xj, -1); s.cnt_add(tab + xv, +1); }
+		} else if (kind == GHOST_KIND_ALL_DIFFERENT_OFFSET) {
+			if (xv != xj) { int tab = mv.cnt_tab(c) + ey; s.cnt_add(tab + xj, -1); s.cnt_add(tab + xv, +1); }
+		} else if (kind_is_linear(kind)) s.T_of(c) += ey * (xv - xj);
+	};
 	for (int k = tid; k < naff; k += T) {
 		int c, delta;
 		if (k < degv) {
@@ -1703,33 +1919,43 @@ __device__ inline void apply_move(const DevModel& m, const WS& s, int v, int new
 				for (int r = rbj; r < rbj + degj; ++r) { int2 f = mv.row_entry(r); if (f.x == c) { both = true; eb = f.y; break; } }
 			}
 			delta = constraint_delta(mv, s, c, v, e.y, nv_new, both ? j : -1, eb, xv);
-			int kind = mv.kind(c);
-			if (kind == GHOST_KIND_ALL_DIFFERENT || kind == GHOST_KIND_ALL_EQUAL) {
-				if (!both && nv_new != xv) { int tab = mv.cnt_tab(c); s.cnt_add(tab + xv, -1); s.cnt_add(tab + nv_new, +1); }
-			} else if (kind == GHOST_KIND_ALL_DIFFERENT_OFFSET) {
-				const int tab = mv.cnt_tab(c);
-				if (nv_new != xv) { s.cnt_add(tab + e.y + xv, -1); s.cnt_add(tab + e.y + nv_new, +1); }
-				if (both && xj != xv) { s.cnt_add(tab + eb + xj, -1); s.cnt_add(tab + eb + xv, +1); } // the partner's shifted value moves too
-			} else if (kind_is_linear(kind)) {
-				s.T_of(c) += e.y * (nv_new - xv) + (both ? eb * (xv - xj) : 0);
-			}
+			first_row_cache(c, e.y, both, eb, false);
 			s.err_of(c) += delta;
 		} else {
 			int2 e = mv.row_entry(rbj + (k - degv));
 			c = e.x;
-			if (s.mark_of(c) != 0) { s.upd[2 * k] = -1; continue; } // shared with v: handled above
+			bool shared = s.mark_of(c) != 0; // shared with v: handled above
+			if (CULPRIT && !shared) // (the marks leave out the constraints whose delta is always 0; here every constraint must count once)
+				for (int r = rbv; r < rbv + degv; ++r) if (mv.row_entry(r).x == c) { shared = true; break; }
+			if (shared) { s.upd[2 * k] = -1; continue; }
 			delta = constraint_delta(mv, s, c, j, e.y, xv, -1, 0, 0);
-			int kind = mv.kind(c);
-			if (kind == GHOST_KIND_ALL_DIFFERENT || kind == GHOST_KIND_ALL_EQUAL) {
-				if (xv != xj) { int tab = mv.cnt_tab(c); s.cnt_add(tab + xj, -1); s.cnt_add(tab + xv, +1); }
-			} else if (kind == GHOST_KIND_ALL_DIFFERENT_OFFSET) {
-				if (xv != xj) { int tab = mv.cnt_tab(c) + e.y; s.cnt_add(tab + xj, -1); s.cnt_add(tab + xv, +1); }
-			} else if (kind_is_linear(kind)) s.T_of(c) += e.y * (xv - xj);
+			second_row_cache(c, e.y, false);
 			s.err_of(c) += delta;
 		}
 		s.upd[2 * k] = c; s.upd[2 * k + 1] = delta;
 	}
 	G::sync();
+	if (CULPRIT) {
+		for (int k = 0; k < naff; ++k) {
+			const int c = s.upd[2 * k];
+			if (c >= 0) culprit_update_variable_errors(m, s, c);
+		}
+		for (int k = tid; k < naff; k += T) {
+			if (s.upd[2 * k] < 0) continue;
+			if (k < degv) {
+				const int2 e = mv.row_entry(rbv + k);
+				int eb = 0; bool both = false;
+				if (m.permutation) {
+					for (int r = rbj; r < rbj + degj; ++r) { int2 f = mv.row_entry(r); if (f.x == e.x) { both = true; eb = f.y; break; } }
+				}
+				first_row_cache(e.x, e.y, both, eb, true);
+			} else {
+				const int2 e = mv.row_entry(rbj + (k - degv));
+				second_row_cache(e.x, e.y, true);
+			}
+		}
+		G::sync();
+	}
 	// projection update (…projection_algorithm.cpp:51-58).  A constraint with a short scope (the binary
 	// and ternary links of the n-queens / Costas models) is scattered by ONE thread, all of them at once;
 	// a long scope (AllDifferent, knapsack rows) by the whole group.

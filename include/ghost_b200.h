@@ -348,7 +348,9 @@ void ghost_b200_solutions_destroy(GhostSolutionSet* set);
  * options, new seed: the per-frame case) find it in place, queue kernels only and return at once; a
  * call with another model replaces it.
  * Every epoch runs exactly iterations_per_epoch iterations per walker: opts->elastic_epochs and the
- * GHOST_B200_TRACE diagnostic of ghost_b200_search_begin() have no effect here.
+ * GHOST_B200_TRACE diagnostic of ghost_b200_search_begin() have no effect here; the call runs the default
+ * strategy only (opts->strategy other than GHOST_STRATEGY_ADAPTIVE_SEARCH, or a non-zero
+ * opts->elite_restart_percent, is refused with GHOST_B200_ERR_UNSUPPORTED).
  *
  * Limits and sharing:
  *  - the built-in array is GHOST_B200_NOALLOC_SCRATCH_BYTES on every GPU that loads the library,

@@ -9,11 +9,12 @@ from oracle import binding
 name = sys.argv[1] if len(sys.argv) > 1 else "magic_square:4"
 iters = int(sys.argv[2]) if len(sys.argv) > 2 else 600
 threads = int(sys.argv[3]) if len(sys.argv) > 3 else 0
+strategy = int(sys.argv[4]) if len(sys.argv) > 4 else 0
 os.environ["GHOST_B200_TRACE"] = str(iters)
 from ghost_b200 import capi
 desc = model_by_name(name)
 port = binding.OraclePort(desc)
-opts = default_opts(seed=2024, number_walkers=1, threads_per_walker=threads, stop_on_first_solution=0, max_iterations=iters)
+opts = default_opts(seed=2024, number_walkers=1, threads_per_walker=threads, stop_on_first_solution=0, max_iterations=iters, strategy=strategy)
 port.resolve_opts(opts)
 model = capi.Model(desc)
 s = model.begin(opts)

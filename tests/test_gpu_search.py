@@ -334,3 +334,27 @@ def test_antidote_strategy_trajectories_match_oracle(name, oracle_built):
 def test_antidote_strategy_survives_epochs(oracle_built):
     """The erased positions of the weight vector are walker state: 10 launches of 40 iterations == one of 400."""
     _check_against_oracle(model_by_name("n_queens:8"), oracle_built, iterations=400, walkers=6, seed=11, epochs=10, strategy=1)
+
+
+@pytest.mark.parametrize("name", ["magic_square:5", "n_queens:8", "costas_lag:9", "knapsack:20x3", "mixed", "mixed_perm", "n_queens_offset:12",
+                                  "magic_square:16", "all_interval:10", "mixed_eq", "costas:6", "n_queens_perm:11", "weighted_perm"])
+def test_culprit_strategy_trajectories_match_oracle(name, oracle_built):
+    """GHOST_STRATEGY_CULPRIT (the default picks over the Culprit Search error projection, fp64): the CUDA walkers against
+    the oracle, whose restatement of the projection is pinned to the reference's CulpritSearchErrorProjection by the decision
+    replay of tests/test_decision_replay.py.  Equal trajectories mean equal candidate sets in every iteration, i.e. the
+    projected errors tie and order exactly as the oracle's doubles do."""
+    _check_against_oracle(model_by_name(name), oracle_built, iterations=500, walkers=8, seed=77, strategy=2)
+
+
+def test_culprit_strategy_survives_epochs(oracle_built):
+    """The table rows and the projected errors are walker state: 10 launches of 40 iterations == one of 400."""
+    _check_against_oracle(model_by_name("costas_lag:9"), oracle_built, iterations=400, walkers=6, seed=12, epochs=10, strategy=2)
+
+
+def test_culprit_strategy_unsorted_domains(oracle_built):
+    """Variable::get_partial_domain works on the domain in the order the user gave it: a model whose domains are listed
+    out of order takes the search path instead of the arithmetic one."""
+    desc = model_by_name("n_queens:8")
+    rng = np.random.default_rng(5)
+    desc.domains = [list(rng.permutation(np.asarray(d))) for d in desc.domains]
+    _check_against_oracle(desc, oracle_built, iterations=400, walkers=6, seed=13, strategy=2)
