@@ -300,13 +300,14 @@ __device__ inline void initialize_variable_values(const DevModel& m, const Walke
 
 // SearchUnit::local_move (search_unit.hpp:516-541)
 template <int T, bool PERM, bool EQ, bool F32, int STRAT = 0, class WS>
-__device__ inline void local_move(const DevModel& m, const WS& s, WalkerRegs& r, const SearchParams& p, int* best_x, int v, int new_value, int delta, int nh)
+__device__ inline void local_move(const DevModel& m, const WS& s, WalkerRegs& r, const SearchParams& p, int* best_x, int v, int new_value, int delta, int nh, unsigned& tmask)
 {
 	MV mv(m);
 	if (r.best_pending && delta >= 0) { copy_best<T>(m, s, best_x); r.best_pending = 0; }
 	++r.local_moves;
 	r.cur_sat += delta;
 	if (Group<T>::tid() == 0) { s.tabu[scan_pos(m, v)] = (unsigned short)(p.tabu_selected + r.local_moves - r.tabu_base); s.counters[K_MOVES] += 1; }
+	if (F32) tabu_mark(m, s, v, p.tabu_selected, tmask);
 	r.must_compute = 1;
 	if (!F32 && m.objective != GHOST_OBJ_NONE) {
 		if (m.permutation) {
@@ -367,8 +368,9 @@ static __device__ __noinline__ ColdState walker_reinit(const DevModel& m, const 
 		// search_unit.hpp:708-717
 		r.best_sat = GB_INT_MAX; r.best_opt = GB_I64_MAX; r.cur_opt = GB_I64_MAX;
 		for (int v = tid; v < m.V; v += T) s.x[v] = mv.ld(m.o.start, v);
-		// padding of the scan arrays up to a multiple of 32 variables: tabu for ever, error 0
-		for (int v = m.V + tid; v < L.nchunks_v * 32; v += T) { s.tabu[v] = 0xFFFFu; s.err_var[v] = 0; s.x[v] = 0; }
+		// padding of the scan arrays up to a multiple of 32 variables: tabu for ever, error 0 (fp32 kernels: tabu is an offset of
+		// the error, walker.cuh)
+		for (int v = m.V + tid; v < L.nchunks_v * 32; v += T) { s.tabu[v] = 0xFFFFu; s.err_var[v] = F32 ? -GB_TABU_OFFSET : 0; s.x[v] = 0; }
 		G::sync();
 	} else if (mode == GB_COLD_RESTART) {
 		if (tid == 0) s.counters[K_RESTARTS] += 1;
@@ -429,6 +431,8 @@ search_kernel(const __grid_constant__ DevModel m, const __grid_constant__ Walker
 	ChunkRegs cq, vq;           // T == 32: candidate-variable / candidate-value chunk summaries, lane = chunk
 	cq.key = -1; cq.bits = 0u;
 	int evals_lane = 0;         // candidates evaluated by this lane since the last flush into the counters
+	unsigned rng_base = (unsigned)rng.next_event - 16u;   // fp32 kernels: first event of the cached Philox blocks (none yet)
+	unsigned tmask = 0u;        // fp32 kernels: the variables whose projected error carries the tabu offset (walker.cuh), lane = chunk
 	if (tid == 0) {
 		const long long* k = reinterpret_cast<const long long*>(&gs->k);
 #pragma unroll
@@ -448,6 +452,7 @@ search_kernel(const __grid_constant__ DevModel m, const __grid_constant__ Walker
 		r.must_compute = c.must_compute; r.tabu_base = c.tabu_base; r.cur_sat = c.cur_sat; r.best_sat = c.best_sat;
 		r.best_pending = c.best_pending; r.resume_pending = c.resume_pending;
 		r.cur_opt = c.cur_opt; r.best_opt = c.best_opt; r.obj_sum = c.obj_sum; rng.next_event = c.next_event;
+		tmask = 0u;   // initialize_data_structures clears the tabu list and rewrites the projected errors
 	};
 	if (GB_UNLIKELY(!gs->initialized)) {
 		reinit(GB_COLD_FIRST);
@@ -458,6 +463,7 @@ search_kernel(const __grid_constant__ DevModel m, const __grid_constant__ Walker
 		for (int i = tid; i < L.persist_bytes / 16; i += T) dst[i] = src[i];
 		G::sync();
 		if (T == 32 && tid < L.nchunks_v) { cq.key = s.cand_key[tid]; cq.bits = s.cand_bits[tid]; }
+		if (F32) tmask = tabu_mask_rebuild(m, s, L.nchunks_v, r.local_moves - r.tabu_base);
 	}
 
 	// Elastic epoch: after its nominal `iterations` a walker announces itself and keeps going until all
@@ -506,8 +512,10 @@ search_kernel(const __grid_constant__ DevModel m, const __grid_constant__ Walker
 				r.ncand = scan_candidates_culprit(m, s, L.nchunks_v, r.local_moves - r.tabu_base, optimization && r.cur_sat == 0, &r.n_tabu, cq);
 				r.cand_max = 0;
 			}
-		} else if (r.must_compute)
-			r.ncand = scan_candidates<T>(m, s, L.nchunks_v, r.local_moves - r.tabu_base, optimization && r.cur_sat == 0, s.red, &r.cand_max, &r.n_tabu, cq);
+		} else if (r.must_compute) {
+			if (F32) r.n_tabu = tabu_expire(m, s, r.local_moves - r.tabu_base, tmask);
+			r.ncand = scan_candidates<T, F32>(m, s, L.nchunks_v, r.local_moves - r.tabu_base, optimization && r.cur_sat == 0, s.red, &r.cand_max, &r.n_tabu, cq);
+		}
 
 		int trace_var = -1, trace_val = 0, trace_branch = 0, trace_ncand = 0, trace_min = 0;
 		if (GB_UNLIKELY(r.n_tabu >= p.reset_threshold || r.ncand == 0)) {
@@ -517,7 +525,24 @@ search_kernel(const __grid_constant__ DevModel m, const __grid_constant__ Walker
 			if (r.best_pending) { copy_best<T>(m, s, best_x); r.best_pending = 0; G::sync(); }
 			reinit(p.restart_threshold > 0 && (r.resets % p.restart_threshold == 0) ? GB_COLD_RESTART : GB_COLD_PERTURB);
 		} else {
-			const uint4 rnd = STRAT == 1 ? rnd_early : rng.block(rng.next_event, 0);
+			uint4 rnd;
+			if (F32) {
+				// the Philox blocks of the next 16 events are computed at once, one event per lane, and parked in the shared
+				// memory that holds the candidate summaries between launches (dead while the launch runs): an iteration
+				// reads its block with one broadcast load instead of running the generator (147 instructions)
+				uint4* cache = reinterpret_cast<uint4*>(s.cand_key);
+				unsigned idx = (unsigned)rng.next_event - rng_base;
+				if (idx >= 16u) {
+					rng_base = (unsigned)rng.next_event;
+					const uint4 mine = rng.block(rng.next_event + (unsigned)(tid & 15), 0);
+					__syncwarp();
+					if (tid < 16) cache[tid] = mine;
+					__syncwarp();
+					idx = 0u;
+				}
+				rnd = cache[idx];
+			} else
+				rnd = STRAT == 1 ? rnd_early : rng.block(rng.next_event, 0);
 			++rng.next_event;
 			int v;
 			if (STRAT == 1) {
@@ -576,7 +601,7 @@ search_kernel(const __grid_constant__ DevModel m, const __grid_constant__ Walker
 
 			int plateau = 0, local_min = 0;
 			if (gmin < 0) { // search_unit.hpp:1042-1050
-				local_move<T, PERM, EQ, F32, STRAT>(m, s, r, p, best_x, v, new_value, gmin, nh);
+				local_move<T, PERM, EQ, F32, STRAT>(m, s, r, p, best_x, v, new_value, gmin, nh, tmask);
 				if (optimization) r.cur_opt = internal_cost(m, r.obj_sum);
 				trace_branch = 1;
 			} else if (gmin == 0) {
@@ -587,7 +612,7 @@ search_kernel(const __grid_constant__ DevModel m, const __grid_constant__ Walker
 						obj2 = r.obj_sum + (long long)mv.obj_coef(v) * (xj - xv) + (long long)mv.obj_coef(new_value) * (xv - xj);
 					} else obj2 = r.obj_sum + (long long)mv.obj_coef(v) * (new_value - s.x[v]);
 					long long cand_opt = internal_cost(m, obj2);
-					if (r.cur_opt > cand_opt) { local_move<T, PERM, EQ, F32, STRAT>(m, s, r, p, best_x, v, new_value, 0, nh); r.cur_opt = cand_opt; trace_branch = 2; }
+					if (r.cur_opt > cand_opt) { local_move<T, PERM, EQ, F32, STRAT>(m, s, r, p, best_x, v, new_value, 0, nh, tmask); r.cur_opt = cand_opt; trace_branch = 2; }
 					else if (r.cur_opt == cand_opt) plateau = 1;
 					else local_min = 1;
 				} else plateau = 1; // 1136-1145
@@ -596,10 +621,11 @@ search_kernel(const __grid_constant__ DevModel m, const __grid_constant__ Walker
 			if (plateau) { // plateau_management, 545-561
 				if ((int)below(rnd.z, 100u) + 1 <= p.plateau_percent) {
 					if (tid == 0) { s.tabu[scan_pos(m, v)] = (unsigned short)(p.tabu_local_min + r.local_moves - r.tabu_base); s.counters[K_FORCE] += 1; }
+					if (F32) tabu_mark(m, s, v, p.tabu_local_min, tmask);
 					r.must_compute = 1;
 					trace_branch = 4;
 				} else {
-					local_move<T, PERM, EQ, F32, STRAT>(m, s, r, p, best_x, v, new_value, 0, nh);
+					local_move<T, PERM, EQ, F32, STRAT>(m, s, r, p, best_x, v, new_value, 0, nh, tmask);
 					if (tid == 0) s.counters[K_PLATEAU] += 1;
 					trace_branch = 3;
 				}
@@ -608,6 +634,7 @@ search_kernel(const __grid_constant__ DevModel m, const __grid_constant__ Walker
 				r.must_compute = 0;
 				if (r.ncand == 0) {
 					if (tid == 0) { s.tabu[scan_pos(m, v)] = (unsigned short)(p.tabu_local_min + r.local_moves - r.tabu_base); s.counters[K_LOCALMIN] += 1; }
+					if (F32) tabu_mark(m, s, v, p.tabu_local_min, tmask);
 					if (p.tabu_local_min > 0) ++r.n_tabu;
 					trace_branch = 5;
 				} else trace_branch = 6;
@@ -640,6 +667,9 @@ search_kernel(const __grid_constant__ DevModel m, const __grid_constant__ Walker
 		const int tot = T == 32 ? __reduce_add_sync(0xffffffffu, evals_lane) : G::sum(evals_lane, s.red + 16);
 		if (tid == 0) s.counters[K_EVALS] += tot;
 	}
+	// fp32 kernels: leave the tabu offsets in step with the move counter (the next launch rebuilds its mask from the tabu
+	// entries); a no-op unless the last iteration moved, and then the next scan would do the same first thing
+	if (F32) tabu_expire(m, s, r.local_moves - r.tabu_base, tmask);
 	if (T == 32 && tid < L.nchunks_v) { s.cand_key[tid] = cq.key; s.cand_bits[tid] = cq.bits; }
 	G::sync();
 	{

@@ -649,7 +649,8 @@ __device__ __forceinline__ void commit_scan_chunk(const WS& s, ChunkRegs& q, int
 // One pass over the variables: chunk summaries into q / (cand_key, cand_bits), returns this lane's tabu count.
 // USE_MASK: variables that appear in no constraint are not candidates (…candidates_heuristic.cpp:45-46) and the
 // model has some; a template axis because the predicated form costs every model five instructions per block.
-template <int T, bool USE_MASK, class WS>
+// TQ: tabu variables carry err_var - GB_TABU_OFFSET (see "tabu as an offset" below): the pass reads no tabu entry, counts nothing
+template <int T, bool USE_MASK, bool TQ = false, class WS>
 __device__ __forceinline__ int scan_pass(const DevModel& m, const WS& s, int nchunks_v, int local_moves, ChunkRegs& q)
 {
 	typedef Group<T> G;
@@ -664,11 +665,14 @@ __device__ __forceinline__ int scan_pass(const DevModel& m, const WS& s, int nch
 #endif
 	for (int b = G::warp(); b < nblocks; b += G::NW) {
 		const int4 e = e4[b * 32 + lane];
-		const uint2 t = t4[b * 32 + lane];
-		const bool k0 = (int)(t.x & 0xFFFFu) > local_moves, k1 = (int)(t.x >> 16) > local_moves;
-		const bool k2 = (int)(t.y & 0xFFFFu) > local_moves, k3 = (int)(t.y >> 16) > local_moves;
-		ntabu += (k0 ? 1 : 0) + (k1 ? 1 : 0) + (k2 ? 1 : 0) + (k3 ? 1 : 0);
-		int e0 = k0 ? -1 : e.x, e1 = k1 ? -1 : e.y, e2 = k2 ? -1 : e.z, e3 = k3 ? -1 : e.w;
+		int e0 = e.x, e1 = e.y, e2 = e.z, e3 = e.w;
+		if (!TQ) {
+			const uint2 t = t4[b * 32 + lane];
+			const bool k0 = (int)(t.x & 0xFFFFu) > local_moves, k1 = (int)(t.x >> 16) > local_moves;
+			const bool k2 = (int)(t.y & 0xFFFFu) > local_moves, k3 = (int)(t.y >> 16) > local_moves;
+			ntabu += (k0 ? 1 : 0) + (k1 ? 1 : 0) + (k2 ? 1 : 0) + (k3 ? 1 : 0);
+			e0 = k0 ? -1 : e.x; e1 = k1 ? -1 : e.y; e2 = k2 ? -1 : e.z; e3 = k3 ? -1 : e.w;
+		}
 		if (USE_MASK) {
 			const int4 h = __ldg(reinterpret_cast<const int4*>(m.blob + m.o.has_ctr) + b);
 			if (!(((unsigned)h.x >> lane) & 1u)) e0 = -1;
@@ -701,9 +705,12 @@ __device__ __forceinline__ int scan_pass(const DevModel& m, const WS& s, int nch
 	}
 	for (int ch = 4 * nblocks + G::warp(); ch < nchunks_v; ch += G::NW) { // the tail, natural order
 		const int i = ch * 32 + lane;
-		const bool k = (int)s.tabu[i] > local_moves;
-		ntabu += k ? 1 : 0;
-		int e = k ? -1 : s.err_var[i];
+		int e = s.err_var[i];
+		if (!TQ) {
+			const bool k = (int)s.tabu[i] > local_moves;
+			ntabu += k ? 1 : 0;
+			if (k) e = -1;
+		}
 		if (USE_MASK && !(((unsigned)mv.ld(m.o.has_ctr, ch) >> lane) & 1u)) e = -1;
 #ifndef GB_SCAN_SPLIT
 		if (T == 32) {
@@ -727,15 +734,72 @@ __device__ __forceinline__ int scan_pass(const DevModel& m, const WS& s, int nch
 	return ntabu;
 }
 
-template <int T, class WS>
+// ---------------------------------------------------------------------------------------------
+// Tabu as an offset (the fp32 kernels, whose projected errors lower.cpp bounds below 2^24): while a variable is tabu
+// its projected error carries -GB_TABU_OFFSET, so the candidate scan is a plain arg-max that reads no tabu entry — a
+// tabu variable's key is negative, which the scan already treats as "not a candidate".  The projection updates are
+// additive and never notice.  Which variables carry the offset is a bit mask in registers (lane ch = variables
+// 32*ch .. 32*ch+31): marking sets the bit and subtracts the offset, tabu_expire() tests only the marked variables
+// (a few dozen at most: the reset threshold bounds them) against the move counter, gives the offset back and clears
+// the bit; the population of the mask is the tabu count of the reset test (search_unit.hpp:761-763).  The tabu array
+// itself stays as it is (expiry times; rebuilt into a mask when a launch resumes).
+// ---------------------------------------------------------------------------------------------
+#define GB_TABU_OFFSET (1 << 30)
+template <class WS>
+__device__ __forceinline__ int tabu_expire(const DevModel& m, const WS& s, int local_moves, unsigned& mask)
+{
+	const int lane = threadIdx.x & 31;
+	unsigned pending = mask;
+	while (__any_sync(0xffffffffu, pending != 0u)) {
+		if (pending != 0u) {
+			const int bit = __ffs(pending) - 1;
+			pending &= pending - 1u;
+			const int pos = scan_pos(m, lane * 32 + bit);
+			if ((int)s.tabu[pos] <= local_moves) { mask &= ~(1u << bit); atomicAdd(&s.err_var[pos], GB_TABU_OFFSET); }
+		}
+	}
+	__syncwarp();
+	return __reduce_add_sync(0xffffffffu, __popc(mask));
+}
+// mark variable v tabu (its tabu entry has just been written by lane 0); tenure 0 marks nothing
+template <class WS>
+__device__ __forceinline__ void tabu_mark(const DevModel& m, const WS& s, int v, int tenure, unsigned& mask)
+{
+	if (tenure <= 0) return;
+	const int lane = threadIdx.x & 31;
+	if (lane == (v >> 5)) mask |= 1u << (v & 31);
+	if (lane == 0) atomicSub(&s.err_var[scan_pos(m, v)], GB_TABU_OFFSET);   // (atomic: the projection scatter of a move may follow without a barrier)
+}
+// a launch resumes: the mask from the tabu entries (the offsets are in the persisted errors already)
+template <class WS>
+__device__ inline unsigned tabu_mask_rebuild(const DevModel& m, const WS& s, int nchunks_v, int local_moves)
+{
+	const int lane = threadIdx.x & 31;
+	unsigned mine = 0u;
+	for (int ch = 0; ch < nchunks_v; ++ch) {
+		const int v = ch * 32 + lane;
+		const unsigned b = __ballot_sync(0xffffffffu, v < m.V && (int)s.tabu[scan_pos(m, v)] > local_moves);
+		if (lane == ch) mine = b;
+	}
+	return mine;
+}
+
+template <int T, bool TQ = false, class WS>
 __device__ inline int scan_candidates(const DevModel& m, const WS& s, int nchunks_v, int local_moves,
                                       bool free_vars_ok, int* red, int* worst_out, int* ntabu_out, ChunkRegs& q)
 {
 	typedef Group<T> G;
 	const bool use_mask = !free_vars_ok && !m.all_have_ctr;
 	q.key = -1; q.bits = 0u;
-	int ntabu = use_mask ? scan_pass<T, true>(m, s, nchunks_v, local_moves, q) : scan_pass<T, false>(m, s, nchunks_v, local_moves, q);
+	int ntabu = use_mask ? scan_pass<T, true, TQ>(m, s, nchunks_v, local_moves, q) : scan_pass<T, false, TQ>(m, s, nchunks_v, local_moves, q);
 	int worst, ncand;
+	if (T == 32 && TQ) {
+		worst = __reduce_max_sync(0xffffffffu, q.key);
+		ncand = regs_count(q, worst);
+		if (worst < 0) ncand = 0;
+		*worst_out = worst;   // (the tabu count is the caller's: the population of its mask)
+		return ncand;
+	}
 	if (T == 32) {
 		ntabu = __reduce_add_sync(0xffffffffu, ntabu);
 		worst = __reduce_max_sync(0xffffffffu, q.key);
