@@ -1594,6 +1594,16 @@ __device__ __forceinline__ void commit_pair(int4* summaries, int ch, int ka, int
 	const unsigned ba = __ballot_sync(0xffffffffu, ka == cmin), bb = __ballot_sync(0xffffffffu, kb == cmin);
 	if ((threadIdx.x & 31) == 0) summaries[ch >> 1] = make_int4(cmin, (int)ba, cmin, (int)bb);
 }
+__device__ __forceinline__ void commit_quad(int4* summaries, int ch, int ka, int kb, int kc, int kd)
+{
+	const int cmin = __reduce_min_sync(0xffffffffu, min(min(ka, kb), min(kc, kd)));
+	const unsigned ba = __ballot_sync(0xffffffffu, ka == cmin), bb = __ballot_sync(0xffffffffu, kb == cmin);
+	const unsigned bc = __ballot_sync(0xffffffffu, kc == cmin), bd = __ballot_sync(0xffffffffu, kd == cmin);
+	if ((threadIdx.x & 31) == 0) {
+		summaries[ch >> 1] = make_int4(cmin, (int)ba, cmin, (int)bb);
+		summaries[(ch >> 1) + 1] = make_int4(cmin, (int)bc, cmin, (int)bd);
+	}
+}
 __device__ __forceinline__ void fetch_summary(const int4* summaries, int nchunks, ChunkRegs& q)
 {
 	const int lane = threadIdx.x & 31;
@@ -1652,9 +1662,14 @@ __device__ inline int evaluate_sg(const DevModel& m, const WS& s, int v, int nh,
 	const unsigned skip = (unsigned)row.z;
 	const int cw = m.sg_cw, G = m.sg_groups;
 	int4* summaries = reinterpret_cast<int4*>(s.val_key);
+	// the loop walks the groups in order: a running pointer into the assignment, and the skip mask bit-reversed so that the
+	// group's bit is the sign bit (one compare, chained with the value test, instead of shift + and + compare)
+	const typename WS::x_type* px = s.x + lane;
+	unsigned rm = __brev(skip);
 	auto cell_key = [&](int ch) -> int {
 		const int u = ch * cw + lane;
-		int d = s.x[u];                                      // padded by two chunks: no clamp
+		int d = *px;                                         // padded by two chunks: no clamp
+		px += cw;
 		asm("" : "+r"(d));
 		const float dx = h.xvo - __int_as_float(0x4B000000 | d);
 		const float TU = __shfl_sync(0xffffffffu, stU.x, ch), aU = __shfl_sync(0xffffffffu, stU.y, ch);
@@ -1665,20 +1680,42 @@ __device__ inline int evaluate_sg(const DevModel& m, const WS& s, int v, int nh,
 		const float w1 = fmaf(-stL.y, dx, stL.x), w2 = fmaf(al, dx, w1);
 		part += fabsf(w2) - fabsf(w1);
 		sum += part;
-		const bool cell = !((skip >> ch) & 1u);
-		const bool ok = cell && d != h.xv;
+		const bool cell = (int)rm >= 0;
+		const unsigned rm_now = rm;
+		rm <<= 1;
+		const bool ok = cell & (d != h.xv);
+#ifndef GB_SG_NO_CHAIN   // predicate chain spelled out: the compiler emits two selects otherwise
+		int key;
+		asm("{ .reg .pred p; setp.ge.s32 p, %2, 0; setp.ne.and.s32 p, %3, %4, p; selp.b32 %0, %1, 0x7fffffff, p; }"
+		    : "=r"(key) : "r"(__float_as_int(sum)), "r"((int)rm_now), "r"(d), "r"(h.xv));
+#else
 		const int key = ok ? __float_as_int(sum) : GB_INT_MAX;
+#endif
 		if (out && cell) out[u] = ok ? key - GB_F32_BASE_BITS : GB_INT_MAX;
 		return key;
 	};
-#ifdef GB_SG_PAIR   // measured: the pair loop executes fewer instructions and is slower (instruction cache)
+#ifdef GB_SG_QUAD
 #pragma unroll 1
+	for (int ch = 0; ch < G; ch += 4) {
+		const int ka = cell_key(ch), kb = cell_key(ch + 1), kc = cell_key(ch + 2), kd = cell_key(ch + 3);
+		commit_quad(summaries, ch, ka, kb, kc, kd);
+	}
+#elif !defined(GB_SG_SINGLE)   // two groups per pass with ONE reduction (measured faster once the per-iteration path had shrunk)
+#ifdef GB_SG_PAIR_U2
+#pragma unroll 2
+#else
+#pragma unroll 1
+#endif
 	for (int ch = 0; ch < G; ch += 2) {
 		const int ka = cell_key(ch), kb = cell_key(ch + 1);
 		commit_pair(summaries, ch, ka, kb);
 	}
 #else
+#ifdef GB_SG_UNROLL2
+#pragma unroll 2
+#else
 #pragma unroll 1
+#endif
 	for (int ch = 0; ch < G; ++ch) {
 		const int ka = cell_key(ch);
 		const int cmin = __reduce_min_sync(0xffffffffu, ka);
@@ -1706,6 +1743,9 @@ __device__ inline int evaluate_sg(const DevModel& m, const WS& s, int v, int nh,
 template <int FS, class WS>
 __device__ inline int evaluate_candidates_f32(const DevModel& m, const WS& s, int v, int nh, int bias, int nchunks_c, int* out, ChunkRegs& q)
 {
+#ifdef GB_SG_TWO_NH
+	if (FS > 10 && nh <= 2) return evaluate_sg<2, (FS > 10 ? FS - 10 : 1)>(m, s, v, nh, bias, out, q);
+#endif
 	if (FS > 10) return evaluate_sg<4, (FS > 10 ? FS - 10 : 1)>(m, s, v, nh, bias, out, q);
 	if (FS > 0) {
 #ifdef GB_F32_TWO_NH
