@@ -83,7 +83,11 @@ for rr in rows:
     if not hdr or len(rr) != len(hdr): continue
     if rr[0] != "": cur = (fname, int(rr[0])); continue
     if rr[2].startswith("0x"): sass.append((int(rr[2], 16), rr[3].strip(), int(rr[ii] or 0), cur))
-sass.sort()
+sass.sort(key=lambda x: (x[0], 0 if x[3] and x[3][0].endswith(".cuh") else 1))
+uniq = []   # an inlined instruction is listed once per file of its inline chain: keep the row that names our source
+for row in sass:
+    if not uniq or uniq[-1][0] != row[0]: uniq.append(row)
+sass = uniq
 addr = {a: i for i, (a, _, _, _) in enumerate(sass)}
 best = None
 for i, (a, t, n, _) in enumerate(sass):
@@ -97,7 +101,8 @@ for i, (a, t, n, _) in enumerate(sass):
 if best:
     with open(os.path.join(P, f"{R}_hot_loop.sass"), "w") as f:
         f.write(f"# The candidate loop of the structured-grid fp32 evaluation (walker.cuh evaluate_sg), as executed in the profiled launch:\n"
-                f"# {len(best)} instructions per chunk of 32 swap partners; columns: address, executions (warp level), source line, SASS\n")
+                f"# {len(best)} instructions per pass of TWO groups (64 swap partners, one warp reduction for both); columns: address,\n"
+                f"# executions (warp level), source line, SASS\n")
         base = best[0][0]
         for a, t, n, c in best:
             f.write(f"{a - base:5x} {n:>10} {c[0]}:{c[1]:<5} {t}\n")
