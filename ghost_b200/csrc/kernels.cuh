@@ -309,7 +309,7 @@ __device__ inline void local_move(const DevModel& m, const WS& s, WalkerRegs& r,
 	if (Group<T>::tid() == 0) { s.tabu[scan_pos(m, v)] = (unsigned short)(p.tabu_selected + r.local_moves - r.tabu_base); s.counters[K_MOVES] += 1; }
 	if (F32) tabu_mark(m, s, v, p.tabu_selected, tmask);
 	r.must_compute = 1;
-	if (!F32 && m.objective != GHOST_OBJ_NONE) {
+	if (!F32 && feat_on<WS>(GB_FEAT_OBJ) && m.objective != GHOST_OBJ_NONE) {
 		if (m.permutation) {
 			int xv = s.x[v], xj = s.x[new_value];
 			r.obj_sum += (long long)mv.obj_coef(v) * (xj - xv) + (long long)mv.obj_coef(new_value) * (xv - xj);
@@ -350,12 +350,12 @@ struct ColdState {
 };
 enum { GB_COLD_FIRST = 0, GB_COLD_RESTART = 1, GB_COLD_PERTURB = 2 };
 
-template <int T, bool PERM, bool EQ, class XT, bool F32, int STRAT = 0>
+template <int T, bool PERM, bool EQ, class XT, bool F32, int STRAT = 0, int FEAT = GB_FEAT_ALL>
 static __device__ __noinline__ ColdState walker_reinit(const DevModel& m, const WalkerLayout& L, const SearchParams& p,
                                                        unsigned char* base, int* best_x, unsigned long long walker, int mode, ColdState c)
 {
 	typedef Group<T> G;
-	typedef WST<XT> WS;
+	typedef WST<XT, FEAT> WS;
 	const WS s = make_ws<WS>(base, L);
 	MV mv(m);
 	const int tid = G::tid();
@@ -401,7 +401,8 @@ static __device__ __noinline__ ColdState walker_reinit(const DevModel& m, const 
 
 // F32: the fp32 form of the LinearEq-only swap evaluation (walker.cuh, evaluate_f32); T == 32, PERM, EQ, 16-bit x only
 // STRAT: GhostStrategy (1 = the Antidote heuristic set, 2 = the Culprit error projection, walker.cuh; T == 32 and not F32)
-template <int T, bool PERM, bool EQ, class XT, bool F32 = false, int FS = 0, int STRAT = 0>
+// FEAT: the constraint classes / options the generic code is compiled for (GB_FEAT_*, lowered.h; walker.cuh WST)
+template <int T, bool PERM, bool EQ, class XT, bool F32 = false, int FS = 0, int STRAT = 0, int FEAT = GB_FEAT_ALL>
 __global__ void __launch_bounds__(T == 32 ? 128 : T, (GB_WARPS_PER_SM * 32) / (T == 32 ? 128 : T))
 search_kernel(const __grid_constant__ DevModel m, const __grid_constant__ WalkerLayout L, const __grid_constant__ SearchParams p)
 {
@@ -411,12 +412,12 @@ search_kernel(const __grid_constant__ DevModel m, const __grid_constant__ Walker
 	const int local = (T == 32) ? (threadIdx.x >> 5) : 0;
 	const int w = blockIdx.x * walkers_per_cta + local;
 	if (w >= p.num_walkers) return; // whole group leaves together
-	typedef WST<XT> WS;
+	typedef WST<XT, FEAT> WS;
 	const WS s = make_ws<WS>(smem_raw + (size_t)local * L.total_bytes, L);
 	const int tid = G::tid();
 	MV mv(m);
 	// the fp32 kernels run satisfaction problems only (lower.cpp, f32_ok): their objective bookkeeping is compiled out
-	const bool optimization = F32 ? false : m.objective != GHOST_OBJ_NONE;
+	const bool optimization = (F32 || !(FEAT & GB_FEAT_OBJ)) ? false : m.objective != GHOST_OBJ_NONE;
 	int* best_x = p.best_x + (size_t)w * m.V;
 	unsigned char* gstate = p.state + (size_t)w * L.persist_bytes;
 	WalkerScalars* gs = p.scalars + w;
@@ -431,7 +432,7 @@ search_kernel(const __grid_constant__ DevModel m, const __grid_constant__ Walker
 	ChunkRegs cq, vq;           // T == 32: candidate-variable / candidate-value chunk summaries, lane = chunk
 	cq.key = -1; cq.bits = 0u;
 	int evals_lane = 0;         // candidates evaluated by this lane since the last flush into the counters
-	unsigned rng_base = (unsigned)rng.next_event - 16u;   // fp32 kernels: first event of the cached Philox blocks (none yet)
+	unsigned rng_base = (unsigned)rng.next_event - 16u;   // one-warp kernels: first event of the cached Philox blocks (none yet)
 	unsigned tmask = 0u;        // fp32 kernels: the variables whose projected error carries the tabu offset (walker.cuh), lane = chunk
 	if (tid == 0) {
 		const long long* k = reinterpret_cast<const long long*>(&gs->k);
@@ -448,7 +449,7 @@ search_kernel(const __grid_constant__ DevModel m, const __grid_constant__ Walker
 		c.best_sat = r.best_sat; c.best_pending = r.best_pending; c.resume_pending = r.resume_pending;
 		c.cur_opt = r.cur_opt; c.best_opt = r.best_opt; c.obj_sum = r.obj_sum; c.next_event = rng.next_event;
 		G::sync();
-		c = walker_reinit<T, PERM, EQ, XT, F32, STRAT == 2 ? 2 : 0>(m, L, p, walker_base, best_x, rng.walker, mode, c);
+		c = walker_reinit<T, PERM, EQ, XT, F32, STRAT == 2 ? 2 : 0, FEAT>(m, L, p, walker_base, best_x, rng.walker, mode, c);
 		r.must_compute = c.must_compute; r.tabu_base = c.tabu_base; r.cur_sat = c.cur_sat; r.best_sat = c.best_sat;
 		r.best_pending = c.best_pending; r.resume_pending = c.resume_pending;
 		r.cur_opt = c.cur_opt; r.best_opt = c.best_opt; r.obj_sum = c.obj_sum; rng.next_event = c.next_event;
@@ -526,9 +527,9 @@ search_kernel(const __grid_constant__ DevModel m, const __grid_constant__ Walker
 			reinit(p.restart_threshold > 0 && (r.resets % p.restart_threshold == 0) ? GB_COLD_RESTART : GB_COLD_PERTURB);
 		} else {
 			uint4 rnd;
-			if (F32) {
-				// the Philox blocks of the next 16 events are computed at once, one event per lane, and parked in the shared
-				// memory that holds the candidate summaries between launches (dead while the launch runs): an iteration
+			if (T == 32 && STRAT == 0) {
+				// (one-warp walkers) the Philox blocks of the next 16 events are computed at once, one event per lane, and parked in
+				// the shared memory that holds the candidate summaries between launches (dead while the launch runs): an iteration
 				// reads its block with one broadcast load instead of running the generator (147 instructions)
 				uint4* cache = reinterpret_cast<uint4*>(s.cand_key);
 				unsigned idx = (unsigned)rng.next_event - rng_base;

@@ -12,9 +12,27 @@ static cudaError_t allow_smem(K kernel, size_t smem)
 	return cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
 }
 
+// generic one-warp kernels compiled for a subset of the constraint classes (GB_FEAT_*): the smallest one that covers the model
+template <bool PERM, class XT, int FEAT>
+static cudaError_t do_search_feat(int grid, int block, size_t smem, cudaStream_t st, const DevModel& m, const WalkerLayout& L, const SearchParams& p)
+{
+	cudaError_t e = allow_smem(search_kernel<GB_T, PERM, false, XT, false, 0, 0, FEAT>, smem);
+	if (e != cudaSuccess) return e;
+	search_kernel<GB_T, PERM, false, XT, false, 0, 0, FEAT><<<grid, block, smem, st>>>(m, L, p);
+	return cudaGetLastError();
+}
+enum : int { GB_FEAT_SET_BASIC = GB_FEAT_ALLDIFF,                // AllDifferent + LinearEquationEq, no objective: n-queens, Costas (stock forms)
+             GB_FEAT_SET_LINEAR_OBJ = GB_FEAT_LINW | GB_FEAT_OBJ // linear (in)equalities under an objective: the knapsack
+};
 template <bool PERM, bool EQ, class XT, bool F32, int FS>
 static cudaError_t do_search_fs(int grid, int block, size_t smem, cudaStream_t st, const DevModel& m, const WalkerLayout& L, const SearchParams& p)
 {
+#ifndef GB_NO_FEAT
+	if (GB_T == 32 && !EQ && !F32 && FS == 0) {
+		if ((m.feat & ~GB_FEAT_SET_BASIC) == 0) return do_search_feat<PERM, XT, (GB_T == 32 && !EQ && !F32) ? GB_FEAT_SET_BASIC : GB_FEAT_ALL>(grid, block, smem, st, m, L, p);
+		if ((m.feat & ~GB_FEAT_SET_LINEAR_OBJ) == 0) return do_search_feat<PERM, XT, (GB_T == 32 && !EQ && !F32) ? GB_FEAT_SET_LINEAR_OBJ : GB_FEAT_ALL>(grid, block, smem, st, m, L, p);
+	}
+#endif
 	cudaError_t e = allow_smem(search_kernel<GB_T, PERM, EQ, XT, F32, FS>, smem);
 	if (e != cudaSuccess) return e;
 	search_kernel<GB_T, PERM, EQ, XT, F32, FS><<<grid, block, smem, st>>>(m, L, p);

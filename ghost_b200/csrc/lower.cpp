@@ -477,6 +477,19 @@ int lower_model(const GhostModelDesc* d, LoweredModel* out, std::string* why)
 	m.max_candidates = m.permutation ? V : max_dom;
 	m.max_degree = std::max(1, max_degree);
 	m.has_abs_diff = has_abs_diff ? 1 : 0;
+	{
+		int feat = ok != GHOST_OBJ_NONE ? GB_FEAT_OBJ : 0;
+		for (int c = 0; c < C; ++c) {
+			const int k = d->ctr_kind[c];
+			if (is_linear(k) && k != GHOST_KIND_LINEAR_EQ) feat |= GB_FEAT_LINW;
+			else if (k == GHOST_KIND_FIX_VALUE) feat |= GB_FEAT_FIX;
+			else if (is_pair_diff(k)) feat |= GB_FEAT_PAIRDIFF;
+			else if (k == GHOST_KIND_ALL_EQUAL) feat |= GB_FEAT_ALLEQ;
+			else if (k == GHOST_KIND_ALL_DIFFERENT_OFFSET) feat |= GB_FEAT_OFFSET;
+			else if (k == GHOST_KIND_ALL_DIFFERENT) feat |= GB_FEAT_ALLDIFF;
+		}
+		m.feat = feat;
+	}
 	m.has_all_equal = has_all_equal ? 1 : 0;
 	m.ell_stride = stride;
 	m.ell_eq_stride = stride_eq;

@@ -54,6 +54,7 @@ struct DevModel {
 	int cnt_total;             // total AllDifferent count-table slots
 	int max_candidates;        // max over variables of candidate slots (V for permutation problems)
 	int max_degree;            // max #constraints touching one variable
+	int feat;                  // GB_FEAT_* bits of what the model uses (walker.cuh): picks the generic kernel compiled for no more than that
 	int has_abs_diff;
 	int has_all_equal;
 	int ell_stride;            // entries per ELL row (max number of non-static constraints of a variable)
@@ -81,6 +82,12 @@ struct DevModel {
 // device-only constraint kind: an AllDifferent over all variables of a permutation problem
 // (constant error, delta 0 for every swap); its error is stored in the rhs section
 enum : int { GB_KIND_STATIC = 16 };
+// what a model uses (DevModel::feat) / what a generic kernel is compiled for (walker.cuh, WST::feat)
+enum : int { GB_FEAT_LINW = 1,      // linear kinds other than LinearEquationEq
+             GB_FEAT_FIX = 2, GB_FEAT_PAIRDIFF = 4, GB_FEAT_ALLEQ = 8, GB_FEAT_OFFSET = 16,
+             GB_FEAT_OBJ = 32,      // an objective function
+             GB_FEAT_ALLDIFF = 64,
+             GB_FEAT_ALL = 127 };
 
 // ELL entry encoding (word 0)
 enum : int { GB_ELL_END = 0xFFFFF, GB_CLS_LINEAR = 0, GB_CLS_ALLDIFF = 1, GB_CLS_FIX = 2, GB_CLS_ABSDIFF = 3, GB_CLS_ZERO = 4, GB_CLS_ALLEQ = 5,

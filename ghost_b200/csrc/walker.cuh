@@ -122,9 +122,14 @@ __device__ __forceinline__ int scan_pos(const DevModel& m, int v)
 
 // Shared-memory view of one walker; XT = unsigned short when every domain value is in [0, 65535]
 // (zero-extending 16-bit loads cost nothing, sign-extending ones an extra instruction), else int
-template <class XT>
+// FEAT: which constraint classes / options the kernel is compiled for (GB_FEAT_*).  The generic kernels carry the code of
+// every class on their per-iteration path; a model that uses two of them runs an instantiation that holds only those
+// (measured on n-queens 100: instruction-cache hit rate 70 % with everything compiled in).  The device functions read it
+// from the view type (feat_on<WS>), so their signatures do not change.
+template <class XT, int FEAT = GB_FEAT_ALL>
 struct WST {
 	typedef XT x_type;
+	static constexpr int feat = FEAT;
 	XT* x; int* err_var;
 	unsigned short* tabu;       // tabu_until - tabu_base, 16 bits (see WalkerRegs::tabu_base)
 	int2* cs;                   // per constraint {T = sum - rhs (linear kinds), a_v of the hoisted variable}
@@ -150,6 +155,7 @@ struct WST {
 	__device__ __forceinline__ int& mark_of(int c) const { return reinterpret_cast<int*>(cem + c)[1]; }
 };
 
+template <class WS> __device__ __forceinline__ constexpr bool feat_on(int f) { return (WS::feat & f) != 0; }
 template <class WS>
 __device__ __forceinline__ WS make_ws(unsigned char* base_in, const WalkerLayout& L)
 {
@@ -231,6 +237,9 @@ __device__ __forceinline__ int linear_error_w(int w, int t)
 	e += ((w & 4) && t == 0) ? 1 : 0;
 	return e;
 }
+// the same for a view type: a model whose linear constraints are all LinearEquationEq needs |t| only
+template <class WS>
+__device__ __forceinline__ int linear_error_f(int w, int t) { return feat_on<WS>(GB_FEAT_LINW) ? linear_error_w(w, t) : abs(t); }
 __device__ __forceinline__ int linear_w_of_kind(int kind)
 {
 	return kind == GHOST_KIND_LINEAR_EQ ? 3 : kind == GHOST_KIND_LINEAR_LEQ ? 1 : kind == GHOST_KIND_LINEAR_GEQ ? 2
@@ -376,7 +385,7 @@ template <class WS>
 __device__ inline int constraint_delta(const MV& mv, const WS& s, int c, int va, int ea, int na, int vb, int eb, int nb)
 {
 	int kind = mv.kind(c);
-	if (kind == GHOST_KIND_ALL_DIFFERENT) {
+	if (feat_on<WS>(GB_FEAT_ALLDIFF) && kind == GHOST_KIND_ALL_DIFFERENT) {
 		if (vb >= 0) {
 			// two changes; in the search these are always the swap {va,vb} -> {x[vb],x[va]}: no change
 			int oa = s.x[va], ob = s.x[vb];
@@ -401,23 +410,23 @@ __device__ inline int constraint_delta(const MV& mv, const WS& s, int c, int va,
 	if (kind_is_linear(kind)) {
 		int t = s.T_of(c) + ea * (na - s.x[va]);
 		if (vb >= 0) t += eb * (nb - s.x[vb]);
-		return linear_error_w(linear_w_of_kind(kind), t) - s.err_of(c);
+		return linear_error_f<WS>(linear_w_of_kind(kind), t) - s.err_of(c);
 	}
-	if (kind == GHOST_KIND_FIX_VALUE) {
+	if (feat_on<WS>(GB_FEAT_FIX) && kind == GHOST_KIND_FIX_VALUE) {
 		int k = mv.rhs(c);
 		int d = abs(na - k) - abs(s.x[va] - k);
 		if (vb >= 0) d += abs(nb - k) - abs(s.x[vb] - k);
 		return d;
 	}
-	if (kind == GHOST_KIND_ALL_DIFFERENT_OFFSET) {
+	if (feat_on<WS>(GB_FEAT_OFFSET) && kind == GHOST_KIND_ALL_DIFFERENT_OFFSET) {
 		// ea / eb = the variables' offsets; the count table is indexed by x + offset
 		const int tab = mv.cnt_tab(c), oa = s.x[va];
 		if (vb >= 0) return alldiff_four_key_delta(s, tab + ea + oa, tab + ea + na, tab + eb + s.x[vb], tab + eb + nb);
 		if (na == oa) return 0;
 		return s.cnt(tab + ea + na) - (s.cnt(tab + ea + oa) - 1);
 	}
-	if (kind == GHOST_KIND_ALL_DIFFERENT_ABS_DIFF || kind == GHOST_KIND_ALL_DIFFERENT_LAG_DIFF) return absdiff_delta(mv, s, c, ea, na, vb >= 0 ? eb : -1, nb);
-	if (kind == GHOST_KIND_ALL_EQUAL) {
+	if (feat_on<WS>(GB_FEAT_PAIRDIFF) && (kind == GHOST_KIND_ALL_DIFFERENT_ABS_DIFF || kind == GHOST_KIND_ALL_DIFFERENT_LAG_DIFF)) return absdiff_delta(mv, s, c, ea, na, vb >= 0 ? eb : -1, nb);
+	if (feat_on<WS>(GB_FEAT_ALLEQ) && kind == GHOST_KIND_ALL_EQUAL) {
 		const int tab = mv.cnt_tab(c), oa = s.x[va];
 		if (vb >= 0) {
 			const int ob = s.x[vb];
@@ -853,18 +862,18 @@ __device__ inline int hoist_variable(const DevModel& m, const WS& s, int v, int*
 			if (cls == GB_CLS_LINEAR) {
 				h.y = e.y; h.z = s.T_of(c) - e.y * xv;
 				contrib = -s.err_of(c);
-			} else if (cls == GB_CLS_ALLDIFF || cls == GB_CLS_ALLDIFF_OFF) {
+			} else if ((feat_on<WS>(GB_FEAT_ALLDIFF) && cls == GB_CLS_ALLDIFF) || (feat_on<WS>(GB_FEAT_OFFSET) && cls == GB_CLS_ALLDIFF_OFF)) {
 				const int tab = mv.cnt_tab(c) + e.y;   // e.y: the variable's offset (0 for a stock AllDifferent)
 				const int sub = s.cnt(tab + xv) - 1;
 				h.y = tab; h.z = sub;
 				contrib = -sub;
-			} else if (cls == GB_CLS_FIX) {
+			} else if (feat_on<WS>(GB_FEAT_FIX) && cls == GB_CLS_FIX) {
 				const int kk = mv.rhs(c);
 				h.y = kk;
 				contrib = -abs(xv - kk);
-			} else if (cls == GB_CLS_ABSDIFF) {
+			} else if (feat_on<WS>(GB_FEAT_PAIRDIFF) && cls == GB_CLS_ABSDIFF) {
 				h.y = e.y;
-			} else if (cls == GB_CLS_ALLEQ) {
+			} else if (feat_on<WS>(GB_FEAT_ALLEQ) && cls == GB_CLS_ALLEQ) {
 				const int tab = mv.cnt_tab(c), state = s.T_of(c);
 				h.y = tab; h.z = alleq_base(state, s.cnt(tab + xv));
 				contrib = alleq_max1(state);
@@ -945,11 +954,11 @@ template <class WS>
 __device__ __forceinline__ int hoisted_term(const MV& mv, const WS& s, const int4 h, int d)
 {
 	int type = h.x & 0xF;
-	if (type == GB_CLS_LINEAR) return linear_error_w((h.x >> 4) & 7, h.z + h.y * d);
-	if (type == GB_CLS_ALLDIFF || type == GB_CLS_ALLDIFF_OFF) return s.cnt(h.y + d);
-	if (type == GB_CLS_FIX) return abs(d - h.y);
-	if (type == GB_CLS_ABSDIFF) return absdiff_delta(mv, s, h.x >> 8, h.y, d, -1, 0);
-	if (type == GB_CLS_ALLEQ) return -max(s.cnt(h.y + d) + 1, h.z);
+	if (type == GB_CLS_LINEAR) return linear_error_f<WS>((h.x >> 4) & 7, h.z + h.y * d);
+	if ((feat_on<WS>(GB_FEAT_ALLDIFF) && type == GB_CLS_ALLDIFF) || (feat_on<WS>(GB_FEAT_OFFSET) && type == GB_CLS_ALLDIFF_OFF)) return s.cnt(h.y + d);
+	if (feat_on<WS>(GB_FEAT_FIX) && type == GB_CLS_FIX) return abs(d - h.y);
+	if (feat_on<WS>(GB_FEAT_PAIRDIFF) && type == GB_CLS_ABSDIFF) return absdiff_delta(mv, s, h.x >> 8, h.y, d, -1, 0);
+	if (feat_on<WS>(GB_FEAT_ALLEQ) && type == GB_CLS_ALLEQ) return -max(s.cnt(h.y + d) + 1, h.z);
 	return 0;
 }
 
@@ -981,7 +990,7 @@ __device__ __forceinline__ bool candidate_sum(const DevModel& m, const MV& mv, c
 		const int4 h = s.hoist[k];
 		// a pair-difference constraint over ALL variables holds the partner too: its single-variable term would only be
 		// taken out again by the two-variable one below (two recounts out of three saved on a Costas model)
-		if ((h.x & 0xF) == GB_CLS_ABSDIFF && h.w) continue;
+		if (feat_on<WS>(GB_FEAT_PAIRDIFF) && (h.x & 0xF) == GB_CLS_ABSDIFF && h.w) continue;
 		sum += hoisted_term(mv, s, h, xj);
 	}
 	for (int k = 0; k < m.ell_stride; ++k) {
@@ -992,31 +1001,31 @@ __device__ __forceinline__ bool candidate_sum(const DevModel& m, const MV& mv, c
 		int cls = ell_cls(e.x);
 		if (st.w == 0) {
 			// constraint of the partner only: {j} -> {x_v}  (search_unit.hpp:881-885)
-			if (cls == GB_CLS_LINEAR) sum += linear_error_w(ell_w(e.x), st.x + e.y * dx) - st.z;
-			else if (cls == GB_CLS_ALLDIFF || cls == GB_CLS_ALLDIFF_OFF) {
+			if (cls == GB_CLS_LINEAR) sum += linear_error_f<WS>(ell_w(e.x), st.x + e.y * dx) - st.z;
+			else if ((feat_on<WS>(GB_FEAT_ALLDIFF) && cls == GB_CLS_ALLDIFF) || (feat_on<WS>(GB_FEAT_OFFSET) && cls == GB_CLS_ALLDIFF_OFF)) {
 				int tab = mv.cnt_tab(c) + e.y;
 				sum += s.cnt(tab + xv) - (s.cnt(tab + xj) - 1);
-			} else if (cls == GB_CLS_FIX) {
+			} else if (feat_on<WS>(GB_FEAT_FIX) && cls == GB_CLS_FIX) {
 				int kk = mv.rhs(c);
 				sum += abs(xv - kk) - abs(xj - kk);
-			} else if (cls == GB_CLS_ABSDIFF) sum += absdiff_delta(mv, s, c, e.y, xv, -1, 0);
-			else if (cls == GB_CLS_ALLEQ) sum += alleq_single_delta(s, st.x, mv.cnt_tab(c), xj, xv);
+			} else if (feat_on<WS>(GB_FEAT_PAIRDIFF) && cls == GB_CLS_ABSDIFF) sum += absdiff_delta(mv, s, c, e.y, xv, -1, 0);
+			else if (feat_on<WS>(GB_FEAT_ALLEQ) && cls == GB_CLS_ALLEQ) sum += alleq_single_delta(s, st.x, mv.cnt_tab(c), xj, xv);
 		} else {
 			// both variables in scope: {v,j} -> {x_j,x_v} (search_unit.hpp:872-874); replace the
 			// single-variable delta already added from the hoisted entry
 			const int4 h = s.hoist[st.w - 1];
 			if (cls == GB_CLS_LINEAR) {
 				int w = ell_w(e.x), t1 = h.z + h.y * xj;
-				sum += linear_error_w(w, t1 + e.y * dx) - linear_error_w(w, t1);
-			} else if (cls == GB_CLS_ALLDIFF) sum -= s.cnt(h.y + xj) - h.z;
-			else if (cls == GB_CLS_ALLDIFF_OFF) {
+				sum += linear_error_f<WS>(w, t1 + e.y * dx) - linear_error_f<WS>(w, t1);
+			} else if (feat_on<WS>(GB_FEAT_ALLDIFF) && cls == GB_CLS_ALLDIFF) sum -= s.cnt(h.y + xj) - h.z;
+			else if (feat_on<WS>(GB_FEAT_OFFSET) && cls == GB_CLS_ALLDIFF_OFF) {
 				// the hoisted single-variable delta out, the swap's own delta in (h.y = table + offset of v)
 				const int tabj = mv.cnt_tab(c) + e.y;
 				sum += alldiff_four_key_delta(s, h.y + xv, h.y + xj, tabj + xj, tabj + xv) - (s.cnt(h.y + xj) - h.z);
 			}
-			else if (cls == GB_CLS_FIX) sum += abs(xv - h.y) - abs(xj - h.y);
-			else if (cls == GB_CLS_ABSDIFF) sum += absdiff_delta(mv, s, c, h.y, xj, e.y, xv) - (h.w ? 0 : absdiff_delta(mv, s, c, h.y, xj, -1, 0));
-			else if (cls == GB_CLS_ALLEQ) sum += max(s.cnt(h.y + xj) + 1, h.z) - alleq_max1(st.x); // the swap changes nothing
+			else if (feat_on<WS>(GB_FEAT_FIX) && cls == GB_CLS_FIX) sum += abs(xv - h.y) - abs(xj - h.y);
+			else if (feat_on<WS>(GB_FEAT_PAIRDIFF) && cls == GB_CLS_ABSDIFF) sum += absdiff_delta(mv, s, c, h.y, xj, e.y, xv) - (h.w ? 0 : absdiff_delta(mv, s, c, h.y, xj, -1, 0));
+			else if (feat_on<WS>(GB_FEAT_ALLEQ) && cls == GB_CLS_ALLEQ) sum += max(s.cnt(h.y + xj) + 1, h.z) - alleq_max1(st.x); // the swap changes nothing
 		}
 	}
 	*out = sum;
@@ -1994,9 +2003,9 @@ __device__ inline void apply_move(const DevModel& m, const WS& s, int v, int new
 	auto first_row_cache = [&](int c, int ey, bool both, int eb, bool force) {
 		if (CULPRIT && !force) return;
 		const int kind = mv.kind(c);
-		if (kind == GHOST_KIND_ALL_DIFFERENT || kind == GHOST_KIND_ALL_EQUAL) {
+		if (feat_on<WS>(GB_FEAT_ALLDIFF | GB_FEAT_ALLEQ) && (kind == GHOST_KIND_ALL_DIFFERENT || kind == GHOST_KIND_ALL_EQUAL)) {
 			if (!both && nv_new != xv) { int tab = mv.cnt_tab(c); s.cnt_add(tab + xv, -1); s.cnt_add(tab + nv_new, +1); }
-		} else if (kind == GHOST_KIND_ALL_DIFFERENT_OFFSET) {
+		} else if (feat_on<WS>(GB_FEAT_OFFSET) && kind == GHOST_KIND_ALL_DIFFERENT_OFFSET) {
 			const int tab = mv.cnt_tab(c);
 			if (nv_new != xv) { s.cnt_add(tab + ey + xv, -1); s.cnt_add(tab + ey + nv_new, +1); }
 			if (both && xj != xv) { s.cnt_add(tab + eb + xj, -1); s.cnt_add(tab + eb + xv, +1); } // the partner's shifted value moves too
@@ -2007,9 +2016,9 @@ __device__ inline void apply_move(const DevModel& m, const WS& s, int v, int new
 	auto second_row_cache = [&](int c, int ey, bool force) {
 		if (CULPRIT && !force) return;
 		const int kind = mv.kind(c);
-		if (kind == GHOST_KIND_ALL_DIFFERENT || kind == GHOST_KIND_ALL_EQUAL) {
+		if (feat_on<WS>(GB_FEAT_ALLDIFF | GB_FEAT_ALLEQ) && (kind == GHOST_KIND_ALL_DIFFERENT || kind == GHOST_KIND_ALL_EQUAL)) {
 			if (xv != xj) { int tab = mv.cnt_tab(c); s.cnt_add(tab + xj, -1); s.cnt_add(tab + xv, +1); }
-		} else if (kind == GHOST_KIND_ALL_DIFFERENT_OFFSET) {
+		} else if (feat_on<WS>(GB_FEAT_OFFSET) && kind == GHOST_KIND_ALL_DIFFERENT_OFFSET) {
 			if (xv != xj) { int tab = mv.cnt_tab(c) + ey; s.cnt_add(tab + xj, -1); s.cnt_add(tab + xv, +1); }
 		} else if (kind_is_linear(kind)) s.T_of(c) += ey * (xv - xj);
 	};
@@ -2080,7 +2089,7 @@ __device__ inline void apply_move(const DevModel& m, const WS& s, int v, int new
 		int b = mv.scope_begin(c), e = mv.scope_begin(c + 1);
 		for (int i = b + tid; i < e; i += T) atomicAdd(&s.err_var[mv.scope_pos(i)], delta);
 	}
-	if (m.has_all_equal) {
+	if (feat_on<WS>(GB_FEAT_ALLEQ) && m.has_all_equal) {
 		// the count tables changed: new lead counts of the AllEqual constraints among the affected ones
 		for (int k = 0; k < naff; ++k) {
 			const int c = s.upd[2 * k];
@@ -2092,7 +2101,7 @@ __device__ inline void apply_move(const DevModel& m, const WS& s, int v, int new
 		if (m.permutation) s.x[j] = xv;
 	}
 	G::sync();
-	if (m.has_abs_diff) {
+	if (feat_on<WS>(GB_FEAT_PAIRDIFF) && m.has_abs_diff) {
 		// refresh the |difference| tables of the extension kind from the new assignment
 		for (int k = tid; k < naff; k += T) {
 			int c = s.upd[2 * k];
