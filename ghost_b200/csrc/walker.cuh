@@ -631,7 +631,10 @@ static __device__ GB_OUTLINE int regs_pick_kth_impl(int key, unsigned bits, int 
 	const int src = __ffs(owner) - 1;
 	const int excl = __shfl_sync(0xffffffffu, incl - c, src);
 	const unsigned wb = __shfl_sync(0xffffffffu, b, src);
-	return src * 32 + __fns(wb, 0, k - excl + 1);
+	// the (k - excl)-th set bit of wb, by the lanes (lane l: "bit l is set and as many set bits lie below it"); __fns is a
+	// software loop of several dozen instructions
+	const bool me = ((wb >> lane) & 1u) && __popc(wb & ((1u << lane) - 1u)) == k - excl;
+	return src * 32 + __ffs(__ballot_sync(0xffffffffu, me)) - 1;
 }
 // n = size of the set (known to the caller)
 __device__ __forceinline__ int regs_pick_kth(const ChunkRegs& q, int best, int k, int n) { return regs_pick_kth_impl(q.key, q.bits, best, k, n); }
