@@ -375,6 +375,20 @@ int lower_model(const GhostModelDesc* d, LoweredModel* out, std::string* why)
 		o.c2v_pos = put(packed);
 	}
 	o.has_ctr = put(has_ctr);
+	{
+		while (blob.size() % 4) blob.push_back(0);   // 16-byte alignment of the int4 records
+		std::vector<int32_t> pd(static_cast<size_t>(C) * 4, 0);
+		for (int c = 0; c < C; ++c) {
+			if (!is_pair_diff(kind[c])) continue;
+			const int b = c2v_off[c], n = c2v_off[c + 1] - b;
+			bool identity = true;
+			for (int p2 = 0; p2 < n; ++p2) if (c2v[b + p2] != p2) { identity = false; break; }
+			const bool absolute = kind[c] == GHOST_KIND_ALL_DIFFERENT_ABS_DIFF;
+			pd[4 * c + 0] = b; pd[4 * c + 1] = n; pd[4 * c + 2] = cnt_tab[c];
+			pd[4 * c + 3] = static_cast<int32_t>(static_cast<uint32_t>(absolute ? 1 : rhs[c]) | (absolute ? (1u << 30) : 0u) | (identity ? (1u << 31) : 0u));
+		}
+		o.pd_desc = put(pd);
+	}
 	bool given_sorted = true;
 	{
 		std::vector<int32_t> given(d->dom_values, d->dom_values + d->dom_offset[V]);

@@ -37,6 +37,8 @@ struct BlobOffsets {
 	                           // that carry further constraints}
 	int c2v_pos;               // uint16 per scope entry: scan_pos() of the variable (projection scatter)
 	int has_ctr;               // [ceil(V/32)] bit v%32 set iff variable v appears in some constraint
+	int pd_desc;               // int4 per constraint, pair-difference kinds only: {scope begin, scope length, count-table base,
+	                           // lag | absolute << 30 | identity << 31}; identity: scope entry p is variable p
 	int dom_given;             // the domain values in the order of the descriptor (Culprit projection: Variable::get_partial_domain
 	                           // works on the domain as the user gave it), same offsets as dom_vals
 	int total;

@@ -263,11 +263,16 @@ __device__ __forceinline__ int pair_value(bool absolute, int first, int second) 
 // registers, no scratch arrays.  A pair that does not exist (or is the duplicate that arises when |pa - pb| = lag) is
 // replaced by "remove 0, add 0", which cancels.
 template <class XT>
-__device__ __noinline__ int absdiff_delta(const int32_t* blob, int c2v_off_sec, int c2v_sec, int cnt_tab_sec,
-                                          const XT* x, const unsigned* cnt32, int c, int pa, int na, int pb, int nb, int lag, bool absolute)
+__device__ __noinline__ int absdiff_delta(const int32_t* blob, int pd_desc_sec, int c2v_sec, const XT* x, const unsigned* cnt32,
+                                          int c, int pa, int na, int pb, int nb)
 {
-	const int b = __ldg(blob + c2v_off_sec + c), n = __ldg(blob + c2v_off_sec + c + 1) - b;
-	const unsigned short* cnt = reinterpret_cast<const unsigned short*>(cnt32) + __ldg(blob + cnt_tab_sec + c);
+	// one 128-bit record per constraint (lower.cpp, pd_desc): scope begin, scope length, count-table base, lag + flags
+	const int4 desc = __ldg(reinterpret_cast<const int4*>(blob + pd_desc_sec) + c);
+	const int b = desc.x, n = desc.y;
+	const unsigned short* cnt = reinterpret_cast<const unsigned short*>(cnt32) + desc.z;
+	const int lag = desc.w & 0xFFFF;
+	const bool absolute = (desc.w >> 30) & 1, identity = desc.w < 0;   // identity: scope entry p is variable p (no lookup)
+	const int32_t* scope = blob + c2v_sec + b;
 	int first[4] = { pa - lag, pa, pb - lag, pb };
 	if (pb < 0) { first[2] = -1; first[3] = -1; }
 	else { if (pb - lag == pa) first[2] = -1; if (pa - lag == pb) first[0] = -1; }
@@ -277,7 +282,7 @@ __device__ __noinline__ int absdiff_delta(const int32_t* blob, int c2v_off_sec, 
 		const int p = first[z];
 		ko[z] = 0; kn[z] = 0;
 		if (p >= 0 && p + lag < n) {
-			const int oa = x[__ldg(blob + c2v_sec + b + p)], ob = x[__ldg(blob + c2v_sec + b + p + lag)];
+			const int oa = identity ? x[p] : x[__ldg(scope + p)], ob = identity ? x[p + lag] : x[__ldg(scope + p + lag)];
 			const int va = (p == pa) ? na : (p == pb ? nb : oa);
 			const int vb = (p + lag == pa) ? na : (p + lag == pb ? nb : ob);
 			ko[z] = pair_value(absolute, oa, ob);
@@ -306,8 +311,7 @@ __device__ __noinline__ int absdiff_delta(const int32_t* blob, int c2v_off_sec, 
 template <class WS>
 __device__ __forceinline__ int absdiff_delta(const MV& mv, const WS& s, int c, int pa, int na, int pb, int nb)
 {
-	const bool absolute = mv.kind(c) == GHOST_KIND_ALL_DIFFERENT_ABS_DIFF;
-	return absdiff_delta(mv.m.blob, mv.m.o.c2v_off, mv.m.o.c2v, mv.m.o.cnt_tab, s.x, s.cnt32, c, pa, na, pb, nb, absolute ? 1 : mv.rhs(c), absolute);
+	return absdiff_delta(mv.m.blob, mv.m.o.pd_desc, mv.m.o.c2v, s.x, s.cnt32, c, pa, na, pb, nb);
 }
 
 // AllEqual (src/global_constraints/all_equal.cpp:47-95): error = scope size - largest count; the delta of
