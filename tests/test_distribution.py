@@ -40,8 +40,17 @@ def test_iterations_to_solution_and_reset_rate(name, runs, ref_built):
     # median) is caught at these sample sizes, while a correct restatement fails one run in a thousand
     p = ks_2samp(oi, ri).pvalue
     assert p > 1e-3, (name, "iterations to solution", p, np.median(oi), np.median(ri))
-    rate_o, rate_r = np.sum(orr) / np.sum(oi), np.sum(rr) / np.sum(ri)
-    assert abs(rate_o - rate_r) <= 0.2 * rate_r, (name, "resets per iteration", rate_o, rate_r)
+    # resets per iteration, pooled over the runs: a ratio of two heavy-tailed sums (run lengths span three orders of
+    # magnitude), so its spread is estimated from the samples themselves (jackknife) instead of assumed: measured over
+    # repeated batches of 300 runs both sides scatter by about 10 % around 0.031 on the 4x4 square.  Four standard
+    # errors of the difference: a correct restatement fails six times in 100 000.
+    def ratio_and_se(num, den):
+        num, den = np.asarray(num, dtype=np.float64), np.asarray(den, dtype=np.float64)
+        n = len(num)
+        loo = (num.sum() - num) / (den.sum() - den)
+        return num.sum() / den.sum(), np.sqrt((n - 1) / n * np.sum((loo - loo.mean()) ** 2))
+    (rate_o, se_o), (rate_r, se_r) = ratio_and_se(orr, oi), ratio_and_se(rr, ri)
+    assert abs(rate_o - rate_r) <= 4.0 * np.hypot(se_o, se_r), (name, "resets per iteration", rate_o, se_o, rate_r, se_r)
 
 
 def test_deviation_d1_best_assignment_follows_best_error(oracle_built):
