@@ -135,7 +135,8 @@ class Model:
 
     def variant(self, threads_per_walker: int = 0) -> int:
         """GHOST_B200_VARIANT_* bits of the search kernel this model dispatches to (1 permutation, 2 LinearEq only,
-        4 16-bit assignment, 8 fp32 swap evaluation)."""
+        4 16-bit assignment, 8 fp32 swap evaluation, 16 structured grid, 32 generic kernel compiled for a feature set,
+        named in bits 8..14)."""
         v = C.c_int32()
         _check(lib.ghost_b200_model_variant(self.h, threads_per_walker, C.byref(v)))
         return v.value

@@ -106,6 +106,8 @@ extern "C" int ghost_b200_model_variant(const GhostModel* gm, int32_t threads_pe
 	const int T = gm->low.effective_threads_per_walker(threads_per_walker);
 	int v = (m.permutation ? GHOST_B200_VARIANT_PERMUTATION : 0) | (m.eq_only ? GHOST_B200_VARIANT_LINEAR_EQ_ONLY : 0) | (m.x16 ? GHOST_B200_VARIANT_X16 : 0);
 	if (T == 32 && v == 7 && m.f32_ok) v |= GHOST_B200_VARIANT_F32 | (m.sg_ok ? GHOST_B200_VARIANT_GRID : 0); // the rule of GB_DISPATCH (launch_impl.cuh)
+	// generic one-warp kernels: the feature set the model's kernel is compiled for (launch_impl.cuh; strategy 0)
+	if (T == 32 && !m.eq_only && feature_set_of(m.feat) != 0) v |= GHOST_B200_VARIANT_FEATURE_SET | (feature_set_of(m.feat) << 8);
 	*variant = v;
 	return GHOST_B200_OK;
 }

@@ -21,20 +21,19 @@ static cudaError_t do_search_feat(int grid, int block, size_t smem, cudaStream_t
 	search_kernel<GB_T, PERM, false, XT, false, 0, 0, FEAT><<<grid, block, smem, st>>>(m, L, p);
 	return cudaGetLastError();
 }
-enum : int { GB_FEAT_SET_BASIC = GB_FEAT_ALLDIFF,                // AllDifferent + LinearEquationEq, no objective: n-queens, Costas (stock forms)
-             GB_FEAT_SET_LINEAR_OBJ = GB_FEAT_LINW | GB_FEAT_OBJ, // linear (in)equalities under an objective: the knapsack
-             GB_FEAT_SET_PAIRDIFF = GB_FEAT_ALLDIFF | GB_FEAT_PAIRDIFF,  // all-interval series, Costas as a difference triangle
-             GB_FEAT_SET_OFFSET = GB_FEAT_ALLDIFF | GB_FEAT_OFFSET       // n-queens as three AllDifferent
-};
 template <bool PERM, bool EQ, class XT, bool F32, int FS>
 static cudaError_t do_search_fs(int grid, int block, size_t smem, cudaStream_t st, const DevModel& m, const WalkerLayout& L, const SearchParams& p)
 {
 #ifndef GB_NO_FEAT
 	if (GB_T == 32 && !EQ && !F32 && FS == 0) {
-		if ((m.feat & ~GB_FEAT_SET_BASIC) == 0) return do_search_feat<PERM, XT, (GB_T == 32 && !EQ && !F32) ? GB_FEAT_SET_BASIC : GB_FEAT_ALL>(grid, block, smem, st, m, L, p);
-		if ((m.feat & ~GB_FEAT_SET_LINEAR_OBJ) == 0) return do_search_feat<PERM, XT, (GB_T == 32 && !EQ && !F32) ? GB_FEAT_SET_LINEAR_OBJ : GB_FEAT_ALL>(grid, block, smem, st, m, L, p);
-		if ((m.feat & ~GB_FEAT_SET_PAIRDIFF) == 0) return do_search_feat<PERM, XT, (GB_T == 32 && !EQ && !F32) ? GB_FEAT_SET_PAIRDIFF : GB_FEAT_ALL>(grid, block, smem, st, m, L, p);
-		if ((m.feat & ~GB_FEAT_SET_OFFSET) == 0) return do_search_feat<PERM, XT, (GB_T == 32 && !EQ && !F32) ? GB_FEAT_SET_OFFSET : GB_FEAT_ALL>(grid, block, smem, st, m, L, p);
+		constexpr bool G = GB_T == 32 && !EQ && !F32;   // (the other instantiations of this template never get here: no extra kernels)
+		switch (feature_set_of(m.feat)) {
+		case GB_FEAT_SET_BASIC: return do_search_feat<PERM, XT, G ? GB_FEAT_SET_BASIC : GB_FEAT_ALL>(grid, block, smem, st, m, L, p);
+		case GB_FEAT_SET_LINEAR_OBJ: return do_search_feat<PERM, XT, G ? GB_FEAT_SET_LINEAR_OBJ : GB_FEAT_ALL>(grid, block, smem, st, m, L, p);
+		case GB_FEAT_SET_PAIRDIFF: return do_search_feat<PERM, XT, G ? GB_FEAT_SET_PAIRDIFF : GB_FEAT_ALL>(grid, block, smem, st, m, L, p);
+		case GB_FEAT_SET_OFFSET: return do_search_feat<PERM, XT, G ? GB_FEAT_SET_OFFSET : GB_FEAT_ALL>(grid, block, smem, st, m, L, p);
+		default: break;
+		}
 	}
 #endif
 	cudaError_t e = allow_smem(search_kernel<GB_T, PERM, EQ, XT, F32, FS>, smem);

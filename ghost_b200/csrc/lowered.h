@@ -90,6 +90,20 @@ enum : int { GB_FEAT_LINW = 1,      // linear kinds other than LinearEquationEq
              GB_FEAT_OBJ = 32,      // an objective function
              GB_FEAT_ALLDIFF = 64,
              GB_FEAT_ALL = 127 };
+// the feature sets the generic one-warp kernels are instantiated for (launch_impl.cuh), smallest first
+enum : int { GB_FEAT_SET_BASIC = GB_FEAT_ALLDIFF,                        // AllDifferent + LinearEquationEq, no objective: n-queens, Costas (stock forms)
+             GB_FEAT_SET_LINEAR_OBJ = GB_FEAT_LINW | GB_FEAT_OBJ,        // linear (in)equalities under an objective: the knapsack
+             GB_FEAT_SET_PAIRDIFF = GB_FEAT_ALLDIFF | GB_FEAT_PAIRDIFF,  // all-interval series, Costas as a difference triangle
+             GB_FEAT_SET_OFFSET = GB_FEAT_ALLDIFF | GB_FEAT_OFFSET };    // n-queens as three AllDifferent
+// which of them a model runs (0: the kernel with everything compiled in); one rule for the launcher and the diagnostics
+inline int feature_set_of(int feat)
+{
+	if ((feat & ~GB_FEAT_SET_BASIC) == 0) return GB_FEAT_SET_BASIC;
+	if ((feat & ~GB_FEAT_SET_LINEAR_OBJ) == 0) return GB_FEAT_SET_LINEAR_OBJ;
+	if ((feat & ~GB_FEAT_SET_PAIRDIFF) == 0) return GB_FEAT_SET_PAIRDIFF;
+	if ((feat & ~GB_FEAT_SET_OFFSET) == 0) return GB_FEAT_SET_OFFSET;
+	return 0;
+}
 
 // ELL entry encoding (word 0)
 enum : int { GB_ELL_END = 0xFFFFF, GB_CLS_LINEAR = 0, GB_CLS_ALLDIFF = 1, GB_CLS_FIX = 2, GB_CLS_ABSDIFF = 3, GB_CLS_ZERO = 4, GB_CLS_ALLEQ = 5,

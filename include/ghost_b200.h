@@ -213,6 +213,9 @@ int ghost_b200_model_info(const GhostModel* model, int32_t* max_candidates, int6
 #define GHOST_B200_VARIANT_F32 8           /* swap deltas evaluated in fp32 on the FMA pipe (exact: all magnitudes < 2^22) */
 #define GHOST_B200_VARIANT_GRID 16         /* ... and the variables form a grid of group / position constraints (rows and
                                             * columns of a matrix model): their state stays in registers in the candidate loop */
+#define GHOST_B200_VARIANT_FEATURE_SET 32  /* a generic one-warp kernel compiled for the constraint classes the model uses
+                                            * only; bits 8..14 name the set: 1 linear (in)equalities other than Eq, 2 FixValue,
+                                            * 4 pair differences, 8 AllEqual, 16 offsets, 32 objective, 64 AllDifferent */
 int ghost_b200_model_variant(const GhostModel* model, int32_t threads_per_walker, int32_t* variant);
 
 /* Fill opts with ghost::Options() defaults (src/options.cpp:36-50) and resolve the -1 ones

@@ -185,3 +185,24 @@ def test_model_variant_bits(monkeypatch):
     m = capi.Model(problems.by_name("magic_square:6"))
     assert m.variant(32) == 1 | 2 | 4
     m.close()
+
+
+def test_model_variant_feature_sets():
+    """The generic one-warp kernels are compiled per feature set (lowered.h GB_FEAT_*): lowering records what a model uses and
+    ghost_b200_model_variant names the set its kernel is compiled for (bit 32, the set in bits 8..14); a model outside every
+    set, or one that takes the LinearEq-only kernels, reports none."""
+    from ghost_b200 import capi, problems
+    from tests.helpers import model_by_name
+    ALLDIFF, LINW, OBJ, PAIRDIFF, OFFSET = 64, 1, 32, 4, 16
+    want = {"n_queens:8": ALLDIFF, "costas:6": ALLDIFF, "knapsack:20x3": LINW | OBJ, "all_interval:10": ALLDIFF | PAIRDIFF,
+            "costas_lag:8": ALLDIFF | PAIRDIFF, "n_queens_offset:12": ALLDIFF | OFFSET}
+    for name, fs in want.items():
+        m = capi.Model(problems.by_name(name))
+        v = m.variant(32)
+        assert v & 32 and (v >> 8) == fs, (name, v)
+        assert m.variant(64) & 32 == 0, name          # wider walkers run the kernel with everything compiled in
+        m.close()
+    for name in ("mixed", "mixed_eq", "magic_square:6"):  # several classes at once / AllEqual / LinearEq-only
+        m = capi.Model(model_by_name(name))
+        assert m.variant(32) & 32 == 0, name
+        m.close()
