@@ -282,9 +282,9 @@ extern "C" int ghost_b200_search_begin(GhostModel* gm, const GhostSearchOpts* op
 	ghost_b200_resolve_opts(gm, &s->opts);
 	const DevModel& m = gm->low.dev;
 	if (s->opts.number_variables_to_reset > m.V) s->opts.number_variables_to_reset = m.V;
-	if (s->opts.strategy != GHOST_STRATEGY_ADAPTIVE_SEARCH && s->opts.strategy != GHOST_STRATEGY_ANTIDOTE && s->opts.strategy != GHOST_STRATEGY_CULPRIT) {
+	if (s->opts.strategy < GHOST_STRATEGY_ADAPTIVE_SEARCH || s->opts.strategy > GHOST_STRATEGY_RANDOM_WALK) {
 		delete s;
-		return set_error(GHOST_B200_ERR_INVALID, "strategy must be GHOST_STRATEGY_ADAPTIVE_SEARCH, GHOST_STRATEGY_ANTIDOTE or GHOST_STRATEGY_CULPRIT");
+		return set_error(GHOST_B200_ERR_INVALID, "strategy must be one of GHOST_STRATEGY_* (0..4)");
 	}
 	s->layout = gm->low.layout(s->opts.threads_per_walker, s->opts.number_variables_to_reset, s->opts.strategy);
 	LaunchCfg cfg;
@@ -314,9 +314,9 @@ extern "C" int ghost_b200_search_begin(GhostModel* gm, const GhostSearchOpts* op
 		const double cap = 4294967295.0;
 		if ((double)gm->low.error_bound * std::max(m.V, m.max_candidates) > cap) { delete s; return set_error(GHOST_B200_ERR_UNSUPPORTED, "the Antidote strategy needs (error bound x variables) below 2^32"); }
 	}
-	if (s->opts.strategy == GHOST_STRATEGY_CULPRIT && cfg.T != 32) {
+	if (s->opts.strategy >= GHOST_STRATEGY_CULPRIT && cfg.T != 32) {
 		delete s;
-		return set_error(GHOST_B200_ERR_UNSUPPORTED, "the Culprit strategy runs one warp per walker: at most 1024 variables and 1024 candidates");
+		return set_error(GHOST_B200_ERR_UNSUPPORTED, "the Culprit, hill-climbing and random-walk strategies run one warp per walker: at most 1024 variables and 1024 candidates");
 	}
 	if (s->opts.strategy == GHOST_STRATEGY_CULPRIT && m.static_error > 0) {
 		// the projection simulates single-value changes on every constraint in error; the constant AllDifferent of a

@@ -400,7 +400,8 @@ static __device__ __noinline__ ColdState walker_reinit(const DevModel& m, const 
 }
 
 // F32: the fp32 form of the LinearEq-only swap evaluation (walker.cuh, evaluate_f32); T == 32, PERM, EQ, 16-bit x only
-// STRAT: GhostStrategy (1 = the Antidote heuristic set, 2 = the Culprit error projection, walker.cuh; T == 32 and not F32)
+// STRAT: GhostStrategy (1 = the Antidote heuristic set, 2 = the Culprit error projection, 3 / 4 = hill climbing / random walk,
+// walker.cuh; T == 32 and not F32)
 // FEAT: the constraint classes / options the generic code is compiled for (GB_FEAT_*, lowered.h; walker.cuh WST)
 template <int T, bool PERM, bool EQ, class XT, bool F32 = false, int FS = 0, int STRAT = 0, int FEAT = GB_FEAT_ALL>
 __global__ void __launch_bounds__(T == 32 ? 128 : T, (GB_WARPS_PER_SM * 32) / (T == 32 ? 128 : T))
@@ -440,7 +441,7 @@ search_kernel(const __grid_constant__ DevModel m, const __grid_constant__ Walker
 		for (int i = 0; i < 8; ++i) s.counters[i] = k[i];
 		s.cs[m.C] = make_int2(0, 0); s.cem[m.C] = make_int2(0, 0); // the dummy constraint that pads the ELL rows
 	}
-	if (STRAT == 1) for (int k = m.max_candidates + tid; k < L.nchunks_c * 32; k += T) s.sums[k] = GB_INT_MAX; // slots beyond the last candidate
+	if (STRAT == 1 || STRAT == 4) for (int k = m.max_candidates + tid; k < L.nchunks_c * 32; k += T) s.sums[k] = GB_INT_MAX; // slots beyond the last candidate
 
 	unsigned char* const walker_base = smem_raw + (size_t)local * L.total_bytes;
 	auto reinit = [&](int mode) {
@@ -508,6 +509,11 @@ search_kernel(const __grid_constant__ DevModel m, const __grid_constant__ Walker
 			if (r.must_compute) cq.bits = 0u;
 			rnd_early = rng.block(rng.next_event, 0);
 			v_antidote = antidote_select(m, s, L.nchunks_v, r.local_moves - r.tabu_base, rnd_early.x, cq, &r.n_tabu, &r.ncand);
+		} else if (STRAT == 3 || STRAT == 4) {
+			if (r.must_compute) {
+				r.ncand = scan_candidates_all_free(m, s, L.nchunks_v, r.local_moves - r.tabu_base, &r.n_tabu, cq);
+				r.cand_max = 0;
+			}
 		} else if (STRAT == 2) {
 			if (r.must_compute) {
 				r.ncand = scan_candidates_culprit(m, s, L.nchunks_v, r.local_moves - r.tabu_base, optimization && r.cur_sat == 0, &r.n_tabu, cq);
@@ -563,7 +569,7 @@ search_kernel(const __grid_constant__ DevModel m, const __grid_constant__ Walker
 			else if (T == 32) { if (tid == (v >> 5)) cq.bits &= ~(1u << (v & 31)); }
 			else if (tid == 0) s.cand_bits[v >> 5] &= ~(1u << (v & 31));
 			int gkey, nties;
-			const int mine = evaluate_candidates<T, PERM, EQ, F32, FS>(m, s, v, nh, bias, L.nchunks_c, STRAT == 1 ? s.sums : nullptr, vq);
+			const int mine = evaluate_candidates<T, PERM, EQ, F32, FS>(m, s, v, nh, bias, L.nchunks_c, (STRAT == 1 || STRAT == 4) ? s.sums : nullptr, vq);
 			evals_lane += mine;
 			G::sync();
 			// AdaptiveSearchValueHeuristic::select_value (adaptive_search_value_heuristic.cpp:43-81)
@@ -585,6 +591,13 @@ search_kernel(const __grid_constant__ DevModel m, const __grid_constant__ Walker
 				gmin = slot >= 0 ? chosen : GB_INT_MAX;
 				if (slot >= 0) new_value = PERM ? slot : mv.dom_value(v, slot);
 				G::sync();
+			} else if (STRAT == 4) {
+				// RandomWalkValueHeuristic::select_value: any candidate, uniformly; min_conflict = its cumulated delta
+				int chosen = GB_INT_MAX;
+				const int slot = random_walk_value(s.sums, L.nchunks_c, rnd.y, &chosen);
+				gmin = slot >= 0 ? chosen : GB_INT_MAX;
+				if (slot >= 0) new_value = PERM ? slot : mv.dom_value(v, slot);
+				G::sync();
 			} else if (nties > 0) {
 				int k;
 				if (optimization && !PERM) {
@@ -601,6 +614,13 @@ search_kernel(const __grid_constant__ DevModel m, const __grid_constant__ Walker
 			if (p.trace) trace_ncand = T == 32 ? __reduce_add_sync(0xffffffffu, mine) : G::sum(mine, s.red + 16);
 
 			int plateau = 0, local_min = 0;
+			if (STRAT == 4) { // search_unit.hpp:1007-1036: the move is made whatever its delta
+				if (gmin != GB_INT_MAX) {
+					local_move<T, PERM, EQ, F32, STRAT>(m, s, r, p, best_x, v, new_value, gmin, nh, tmask);
+					if (optimization) r.cur_opt = internal_cost(m, r.obj_sum);
+					trace_branch = 1;
+				} else { r.must_compute = 0; trace_branch = 6; }   // (no candidate at all: undefined behaviour in the reference)
+			} else
 			if (gmin < 0) { // search_unit.hpp:1042-1050
 				local_move<T, PERM, EQ, F32, STRAT>(m, s, r, p, best_x, v, new_value, gmin, nh, tmask);
 				if (optimization) r.cur_opt = internal_cost(m, r.obj_sum);

@@ -50,6 +50,18 @@ static cudaError_t do_search(int grid, int block, size_t smem, cudaStream_t st, 
 		search_kernel<GB_T, PERM, EQ, XT, false, 0, GB_T == 32 ? 1 : 0><<<grid, block, smem, st>>>(m, L, p);
 		return cudaGetLastError();
 	}
+	if (GB_T == 32 && (p.strategy == GHOST_STRATEGY_HILL_CLIMBING || p.strategy == GHOST_STRATEGY_RANDOM_WALK)) {   // generic integer kernels
+		if (p.strategy == GHOST_STRATEGY_HILL_CLIMBING) {
+			cudaError_t e = allow_smem(search_kernel<GB_T, PERM, false, XT, false, 0, GB_T == 32 ? 3 : 0>, smem);
+			if (e != cudaSuccess) return e;
+			search_kernel<GB_T, PERM, false, XT, false, 0, GB_T == 32 ? 3 : 0><<<grid, block, smem, st>>>(m, L, p);
+		} else {
+			cudaError_t e = allow_smem(search_kernel<GB_T, PERM, false, XT, false, 0, GB_T == 32 ? 4 : 0>, smem);
+			if (e != cudaSuccess) return e;
+			search_kernel<GB_T, PERM, false, XT, false, 0, GB_T == 32 ? 4 : 0><<<grid, block, smem, st>>>(m, L, p);
+		}
+		return cudaGetLastError();
+	}
 	if (GB_T == 32 && p.strategy == GHOST_STRATEGY_CULPRIT) {   // the Culprit error projection: generic integer kernels, fp64 projected errors
 		cudaError_t e = allow_smem(search_kernel<GB_T, PERM, false, XT, false, 0, GB_T == 32 ? 2 : 0>, smem);
 		if (e != cudaSuccess) return e;

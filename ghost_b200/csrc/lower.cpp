@@ -559,7 +559,7 @@ WalkerLayout LoweredModel::layout(int /*threads_per_walker*/, int nreset, int st
 	w.upd = take(4 * 2 * 2 * m.max_degree);
 	w.sample = (8 * std::max(1, nreset) <= 4 * m.V) ? w.err_var : take(4 * 2 * std::max(1, nreset));
 	w.red = take(4 * 32);   // [0,8) per-warp partials, [8] stop-flag broadcast, [16,32) 64-bit partials
-	w.sums = strategy == GHOST_STRATEGY_ANTIDOTE ? take(4 * 32 * w.nchunks_c) : w.red;
+	w.sums = (strategy == GHOST_STRATEGY_ANTIDOTE || strategy == GHOST_STRATEGY_RANDOM_WALK) ? take(4 * 32 * w.nchunks_c) : w.red;
 	w.total_bytes = at;
 	return w;
 }

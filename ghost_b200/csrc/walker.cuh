@@ -1478,6 +1478,51 @@ __device__ inline int scan_candidates_culprit(const DevModel& m, const WS& s, in
 }
 
 // ---------------------------------------------------------------------------------------------
+// The reference's landscape-analysis builds as strategies (GHOST_STRATEGY_HILL_CLIMBING / _RANDOM_WALK; include/solver.hpp:
+// 502-515): AllFreeVariableCandidatesHeuristic — every variable that is not tabu is a candidate, constrained or not
+// (all_free_variable_candidates_heuristic.cpp:38-46) — with no error projection; the random walk also draws the value
+// uniformly among the candidates (random_walk_value_heuristic.cpp:47-57) and always moves (search_unit.hpp:1007-1036).
+// The candidate set comes back in the default strategy's form (key 0 for every chunk), so picking / erasing / persisting
+// are the default code with cand_max = 0.
+// ---------------------------------------------------------------------------------------------
+template <class WS>
+__device__ inline int scan_candidates_all_free(const DevModel& m, const WS& s, int nchunks_v, int local_moves, int* ntabu_out, ChunkRegs& q)
+{
+	const int lane = threadIdx.x & 31;
+	unsigned mine = 0u;
+	for (int ch = 0; ch < nchunks_v; ++ch) {
+		const int v = ch * 32 + lane;
+		const unsigned b = __ballot_sync(0xffffffffu, v < m.V && (int)s.tabu[scan_pos(m, v)] <= local_moves);
+		if (lane == ch) mine = b;
+	}
+	q.key = 0; q.bits = mine;
+	const int n = __reduce_add_sync(0xffffffffu, (int)__popc(mine));
+	*ntabu_out = m.V - n;
+	return n;
+}
+// uniform draw among the candidate slots (sums[slot] != INT_MAX), in ascending slot order; -1 if there is none
+__device__ inline int random_walk_value(const int* sums, int nchunks_c, uint32_t word, int* delta_out)
+{
+	const int lane = threadIdx.x & 31;
+	int my_c = 0;
+	for (int ch = 0; ch < nchunks_c; ++ch) {
+		const unsigned b = __ballot_sync(0xffffffffu, sums[ch * 32 + lane] != GB_INT_MAX);
+		if (lane == ch) my_c = __popc(b);
+	}
+	const int total = __reduce_add_sync(0xffffffffu, my_c);
+	if (total == 0) return -1;
+	const int k = (int)below(word, (uint32_t)total);
+	const int incl = (int)warp_inclusive_sum((unsigned)my_c);
+	const int ch = __ffs(__ballot_sync(0xffffffffu, incl > k)) - 1;
+	const int before = __shfl_sync(0xffffffffu, incl - my_c, ch);
+	const unsigned isc = __ballot_sync(0xffffffffu, sums[ch * 32 + lane] != GB_INT_MAX);
+	const bool me = ((isc >> lane) & 1u) && __popc(isc & ((1u << lane) - 1u)) == k - before;
+	const int slot = ch * 32 + __ffs(__ballot_sync(0xffffffffu, me)) - 1;
+	*delta_out = sums[slot];
+	return slot;
+}
+
+// ---------------------------------------------------------------------------------------------
 // fp32 form of the swap evaluation (DevModel::f32_ok: permutation problem, LinearEquationEq only, one
 // common domain, distinct start values, <= 4 live constraints per variable, one warp per walker).
 //

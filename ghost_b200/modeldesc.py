@@ -37,6 +37,8 @@ NOT_A_CANDIDATE = 2**31 - 1
 STRATEGY_ADAPTIVE_SEARCH = 0
 STRATEGY_ANTIDOTE = 1
 STRATEGY_CULPRIT = 2
+STRATEGY_HILL_CLIMBING = 3
+STRATEGY_RANDOM_WALK = 4
 
 
 class GhostModelDescStruct(C.Structure):

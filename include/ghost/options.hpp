@@ -33,7 +33,7 @@ namespace ghost
 		int epoch_iterations = 0;               //!< iterations per kernel launch; 0 = adaptive
 		std::uint64_t seed = 0;                 //!< Philox key; 0 = drawn from std::random_device
 		int number_gpus = 1;                    //!< GPUs of this process to search on; 0 = every visible one
-		int strategy = 0;                       //!< 0 = Adaptive Search heuristics (what the reference's Solver builds), 1 = Antidote
+		int strategy = 0;                       //!< GhostStrategy: 0 = Adaptive Search heuristics (what the reference's Solver builds), 1 = Antidote heuristics, 2 = Culprit error projection, 3 = hill climbing, 4 = random walk (the reference's GHOST_HILL_CLIMBING / GHOST_RANDOM_WALK builds)
 		int elite_restart_percent = 0;          //!< cooperative walkers: chance (%) that a restart begins from the search's best assignment
 	};
 }

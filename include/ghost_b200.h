@@ -156,10 +156,16 @@ typedef struct GhostSearchOpts {
 typedef enum GhostStrategy {
 	GHOST_STRATEGY_ADAPTIVE_SEARCH = 0,
 	GHOST_STRATEGY_ANTIDOTE = 1,
-	GHOST_STRATEGY_CULPRIT = 2       /* the default picks over the Culprit Search error projection
+	GHOST_STRATEGY_CULPRIT = 2,      /* the default picks over the Culprit Search error projection
 	                                    (src/algorithms/culprit_search_error_projection_algorithm.cpp:50-151): a constraint's
 	                                    error is shared out among the variables in proportion to how much moving each
 	                                    to a neighbouring value of its domain would lower it; fp64 */
+	GHOST_STRATEGY_HILL_CLIMBING = 3, /* the reference's GHOST_HILL_CLIMBING build (include/solver.hpp:509-515): every non-tabu
+	                                    variable is a candidate (AllFreeVariableCandidatesHeuristic), no error projection
+	                                    (NullErrorProjection), the default value heuristic */
+	GHOST_STRATEGY_RANDOM_WALK = 4    /* the reference's GHOST_RANDOM_WALK build (include/solver.hpp:502-508,
+	                                    include/search_unit.hpp:1007-1036): as above with a value drawn uniformly among the
+	                                    candidates (RandomWalkValueHeuristic) and the move ALWAYS made */
 } GhostStrategy;
 
 /* Counters: the seven of SearchUnitData (include/search_unit_data.hpp:67-73) plus the

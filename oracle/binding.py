@@ -23,6 +23,7 @@ REF_DIR = os.path.join(HERE, "_ref")
 REF_SO = os.path.join(REF_DIR, "libghost_ref.so")
 REF_BENCH = os.path.join(REF_DIR, "ref_bench")
 REF_TRACE = os.path.join(REF_DIR, "ref_trace")
+REF_TRACE_RW = os.path.join(REF_DIR, "ref_trace_rw")   # the same with the reference's GHOST_RANDOM_WALK loop compiled in
 REFERENCE_TREE = "/root/reference"
 
 

@@ -765,6 +765,12 @@ static void compute_variable_candidates(Walker* w)
 	const OracleModel* m = w->m;
 	double worst = -1;
 	w->ncand = 0;
+	if (w->opt.strategy == GHOST_STRATEGY_HILL_CLIMBING || w->opt.strategy == GHOST_STRATEGY_RANDOM_WALK) {
+		/* AllFreeVariableCandidatesHeuristic::compute_variable_candidates (all_free_variable_candidates_heuristic.cpp:38-46):
+		 * every variable that is not tabu, constrained or not */
+		for (int v = 0; v < m->V; ++v) if (w->tabu[v] <= w->k.local_moves) w->cand[w->ncand++] = v;
+		return;
+	}
 	for (int v = 0; v < m->V; ++v)
 		if (worst <= w->err_var[v] && w->tabu[v] <= w->k.local_moves
 		    && (m->v2c_off[v + 1] > m->v2c_off[v] || (is_optimization(m) && w->cur_sat == 0))) {
@@ -1095,6 +1101,7 @@ static int walker_iteration(Walker* w, const Forced* forced, OracleTraceRow* row
 	if (nties_out) *nties_out = 0;
 
 	const int antidote = w->opt.strategy == GHOST_STRATEGY_ANTIDOTE;
+	const int random_walk = w->opt.strategy == GHOST_STRATEGY_RANDOM_WALK;
 	if (w->must_compute) { if (antidote) antidote_candidates(w); else compute_variable_candidates(w); } /* 749-750 */
 
 	int ntabu = 0; /* 761-763 */
@@ -1143,7 +1150,7 @@ static int walker_iteration(Walker* w, const Forced* forced, OracleTraceRow* row
 
 	double min_conflict;
 	int32_t ncandidates = 0;
-	int nties = evaluate_candidates(w, v, antidote ? w->cand_sum : NULL, ties, &min_conflict, &ncandidates); /* 831-891 */
+	int nties = evaluate_candidates(w, v, (antidote || random_walk) ? w->cand_sum : NULL, ties, &min_conflict, &ncandidates); /* 831-891 */
 	w->k.candidates_evaluated += ncandidates;
 	if (nties_out) *nties_out = nties;
 
@@ -1186,10 +1193,30 @@ static int walker_iteration(Walker* w, const Forced* forced, OracleTraceRow* row
 			min_conflict = w->cand_sum[idx];
 		}
 	}
+	else if (random_walk) {
+		/* RandomWalkValueHeuristic::select_value (random_walk_value_heuristic.cpp:47-57): rng.pick over the map of candidates
+		 * (ascending key), min_conflict = the picked candidate's cumulated delta.  (An empty map is undefined behaviour there;
+		 * here: the variable keeps its value and nothing moves.) */
+		const int slots = num_candidate_slots(m, v);
+		int nc = 0, idx = -1;
+		for (int k = 0; k < slots; ++k) if (!isnan(w->cand_sum[k])) ++nc;
+		new_value = v; min_conflict = DBL_MAX;
+		if (nc > 0) {
+			int want = (int)below(rnd[1], (uint32_t)nc);
+			for (int k = 0, seen = 0; k < slots; ++k) {
+				if (isnan(w->cand_sum[k])) continue;
+				int32_t key; is_candidate(w, v, k, &key);
+				if (forced ? key == forced->value : seen == want) { idx = k; new_value = key; break; }
+				++seen;
+			}
+			if (idx < 0) return -2;
+			min_conflict = w->cand_sum[idx];
+		}
+	}
 	else if (nties == 0) new_value = v; /* adaptive_search_value_heuristic.cpp:68-69 */
 	else if (optimization && !m->permutation) new_value = heuristic_value(w, v, ties, nties, rnd[1]);
 	else new_value = ties[below(rnd[1], (uint32_t)nties)];
-	if (!antidote && forced && nties > 0) {
+	if (!antidote && !random_walk && forced && nties > 0) {
 		int found = 0;
 		for (int i = 0; i < nties; ++i) if (ties[i] == forced->value) found = 1;
 		if (found && optimization && !m->permutation) {
@@ -1209,6 +1236,13 @@ static int walker_iteration(Walker* w, const Forced* forced, OracleTraceRow* row
 	row->num_candidates = ncandidates;
 
 	int plateau = 0;
+	if (random_walk) { /* search_unit.hpp:1007-1036: the move is made whatever its delta, then the best-so-far bookkeeping */
+		if (min_conflict != DBL_MAX) {
+			local_move(w, v, new_value, min_conflict);
+			if (optimization) w->cur_opt = objective_cost(w);
+			row->branch = 1;
+		} else { w->must_compute = 0; row->branch = 6; }
+	} else
 	if (min_conflict < 0.0) { /* 1042-1050 */
 		local_move(w, v, new_value, min_conflict);
 		if (optimization) w->cur_opt = objective_cost(w);

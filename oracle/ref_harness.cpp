@@ -52,6 +52,9 @@
 #include "algorithms/adaptive_search_variable_candidates_heuristic.hpp"
 #include "algorithms/adaptive_search_value_heuristic.hpp"
 #include "algorithms/antidote_search_variable_candidates_heuristic.hpp"
+#include "algorithms/all_free_variable_candidates_heuristic.hpp"
+#include "algorithms/null_error_projection_algorithm.hpp"
+#include "algorithms/random_walk_value_heuristic.hpp"
 #include "algorithms/antidote_search_value_heuristic.hpp"
 
 #include "../include/ghost_b200.h"
@@ -578,7 +581,7 @@ extern "C" int ref_complete_search( const GhostModelDesc* d, int64_t max_solutio
  *         reference itself prints.  usage: ref_bench desc.txt timeout_us parallel threads [custom_start] */
 int main( int argc, char** argv )
 {
-	if( argc < 5 ) { std::fprintf( stderr, "usage: %s desc.txt timeout_us parallel_runs threads [custom_start [strategy: 0 adaptive search, 1 antidote, 2 culprit projection]]\n", argv[0] ); return 2; }
+	if( argc < 5 ) { std::fprintf( stderr, "usage: %s desc.txt timeout_us parallel_runs threads [custom_start [strategy: 0 adaptive search, 1 antidote, 2 culprit projection, 3 hill climbing, 4 random walk]]\n", argv[0] ); return 2; }
 	auto desc = std::make_shared<DescCopy>();
 	if( !desc->load( argv[1] ) ) { std::fprintf( stderr, "cannot read %s\n", argv[1] ); return 2; }
 	DescBuilder builder( desc );
@@ -590,7 +593,7 @@ int main( int argc, char** argv )
 	double cost = 0;
 	std::vector<int> solution;
 	const int strategy = argc > 6 ? std::atoi( argv[6] ) : 0;
-	if( strategy == 1 || strategy == 2 )
+	if( strategy >= 1 && strategy <= 4 )
 	{
 		/* The Antidote heuristic set.  Solver::fast_search never builds it (include/solver.hpp:499-518), so the SearchUnit
 		 * is constructed here the way fast_search does for the default set, with the option defaults resolved as at
@@ -603,7 +606,10 @@ int main( int argc, char** argv )
 		if( options.restart_threshold < 0 ) options.restart_threshold = V;
 		if( options.number_variables_to_reset < 0 ) options.number_variables_to_reset = std::max( 2, static_cast<int>( std::ceil( V * 0.1 ) ) );
 		if( options.number_start_samplings < 0 ) options.number_start_samplings = 10;
-		/* 1: the three Antidote heuristics over the default projection; 2: the default heuristics over the Culprit projection */
+		/* 1: the three Antidote heuristics over the default projection; 2: the default heuristics over the Culprit projection;
+		 * 3 / 4: what Solver::fast_search builds under GHOST_HILL_CLIMBING / GHOST_RANDOM_WALK (include/solver.hpp:502-515) —
+		 * 4 only means a random walk in a binary compiled with -DGHOST_RANDOM_WALK (the loop itself changes under that macro,
+		 * include/search_unit.hpp:1007-1036): oracle/_ref/ref_trace_rw */
 		std::unique_ptr<algorithms::VariableHeuristic> vh;
 		std::unique_ptr<algorithms::VariableCandidatesHeuristic> vch;
 		std::unique_ptr<algorithms::ValueHeuristic> valh;
@@ -615,12 +621,23 @@ int main( int argc, char** argv )
 			valh = std::make_unique<algorithms::AntidoteSearchValueHeuristic>();
 			ep = std::make_unique<algorithms::AdaptiveSearchErrorProjection>();
 		}
-		else
+		else if( strategy == 2 )
 		{
 			vh = std::make_unique<algorithms::UniformVariableHeuristic>();
 			vch = std::make_unique<algorithms::AdaptiveSearchVariableCandidatesHeuristic>();
 			valh = std::make_unique<algorithms::AdaptiveSearchValueHeuristic>();
 			ep = std::make_unique<algorithms::CulpritSearchErrorProjection>();
+		}
+		else
+		{
+#if !defined GHOST_RANDOM_WALK
+			if( strategy == 4 ) { std::fprintf( stderr, "strategy 4 needs the binary compiled with -DGHOST_RANDOM_WALK (ref_trace_rw)\n" ); return 2; }
+#endif
+			vh = std::make_unique<algorithms::UniformVariableHeuristic>();
+			vch = std::make_unique<algorithms::AllFreeVariableCandidatesHeuristic>();
+			if( strategy == 4 ) valh = std::make_unique<algorithms::RandomWalkValueHeuristic>();
+			else valh = std::make_unique<algorithms::AdaptiveSearchValueHeuristic>();
+			ep = std::make_unique<algorithms::NullErrorProjection>();
 		}
 		SearchUnit unit( Access::build( builder ), options, std::move( vh ), std::move( vch ), std::move( valh ), std::move( ep ) );
 		unit.local_search( std::atof( argv[2] ) );

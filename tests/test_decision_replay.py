@@ -71,7 +71,8 @@ def _parse(out, permutation):
 
 
 def _replay(name, ref_built, tmp_path, timeout_us, min_iterations, need=(), strategy=0):
-    if not os.path.exists(ref_built.REF_TRACE):
+    exe = ref_built.REF_TRACE_RW if strategy == 4 else ref_built.REF_TRACE   # the random-walk LOOP is a compile-time variant
+    if not os.path.exists(exe):
         pytest.skip("ref_trace not built")
     desc = model_by_name(name)
     path = desc.dump(str(tmp_path / "m.desc"))
@@ -79,7 +80,7 @@ def _replay(name, ref_built, tmp_path, timeout_us, min_iterations, need=(), stra
     opts = port.resolve_opts(default_opts(seed=1, strategy=strategy))
     seen = {"branches": set(), "resets": 0, "iterations": 0, "ties>1": 0}
     for attempt in range(6):   # the reference's run is random: repeat until the trace shows every behaviour asked for
-        out = subprocess.run([ref_built.REF_TRACE, path, str(timeout_us), "0", "1", "0", str(strategy)], capture_output=True, text=True,
+        out = subprocess.run([exe, path, str(timeout_us), "0", "1", "0", str(strategy)], capture_output=True, text=True,
                              timeout=300).stdout
         its = _parse(out, desc.permutation_problem)
         if not its:
@@ -109,11 +110,14 @@ def _replay(name, ref_built, tmp_path, timeout_us, min_iterations, need=(), stra
             s = st.step(r["var"], value, force)
             assert s["rc"] == 0, (name, r["it"], "choice rejected", s["rc"], r["var"], value)
             assert s["counters"]["search_iterations"] == r["it"], (name, r["it"], "iteration counter (resets included)")
-            if strategy != 1:
+            if strategy not in (1, 4):   # (the random walk prints the candidates at or below the PICKED delta under that heading)
                 assert s["ties"] == r["ties"], (name, r["it"], "ties", s["ties"], r["ties"])
-            if r["ties"] or (strategy == 1 and r["delta"] is not None):
+            if r["ties"] or (strategy in (1, 4) and r["delta"] is not None):
                 assert s["min_conflict"] == r["delta"], (name, r["it"])
-            assert s["branch"] == r["branch"], (name, r["it"], "branch", s["branch"], r["branch"])
+            if strategy == 4:   # no branch message: the move is made whatever its delta (search_unit.hpp:1007-1036)
+                assert r["branch"] is None and s["branch"] == 1, (name, r["it"], "branch", s["branch"], r["branch"])
+            else:
+                assert s["branch"] == r["branch"], (name, r["it"], "branch", s["branch"], r["branch"])
             seen["branches"].add(s["branch"])
             seen["iterations"] += 1
             seen["ties>1"] += len(r["ties"]) > 1
@@ -181,3 +185,22 @@ def test_replay_culprit_projection(name, timeout_us, ref_built, tmp_path):
     #  "x_v is in D(j)")
     seen = _replay(name, ref_built, tmp_path, timeout_us, 40, need=(1,), strategy=2)
     assert seen["iterations"] >= 40
+
+
+@pytest.mark.parametrize("name,timeout_us", [("magic_square:4", 40000), ("n_queens:8", 30000), ("knapsack:12x3", 20000), ("mixed", 30000)])
+def test_replay_hill_climbing(name, timeout_us, ref_built, tmp_path):
+    """GHOST_STRATEGY_HILL_CLIMBING: what Solver::fast_search builds under the reference's GHOST_HILL_CLIMBING macro
+    (include/solver.hpp:509-515) — every non-tabu variable a candidate (AllFreeVariableCandidatesHeuristic, constraint-free
+    variables included), no error projection, the default value heuristic; the loop is the stock one, so the harness builds
+    that SearchUnit in the ordinary trace binary."""
+    seen = _replay(name, ref_built, tmp_path, timeout_us, 60, need=(1,), strategy=3)
+    assert seen["iterations"] >= 60
+
+
+@pytest.mark.parametrize("name,timeout_us", [("magic_square:4", 20000), ("n_queens:8", 20000), ("knapsack:12x3", 20000), ("costas_lag:8", 20000)])
+def test_replay_random_walk(name, timeout_us, ref_built, tmp_path):
+    """GHOST_STRATEGY_RANDOM_WALK against oracle/_ref/ref_trace_rw, the reference compiled with GHOST_RANDOM_WALK: a value
+    drawn uniformly among the candidates and the move made whatever its delta (include/search_unit.hpp:1007-1036).  Replayed:
+    candidate variables, tabu list, counters, the picked candidate's delta, every resulting assignment and error."""
+    seen = _replay(name, ref_built, tmp_path, timeout_us, 100, need=(1,), strategy=4)
+    assert seen["iterations"] >= 100

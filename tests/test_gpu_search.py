@@ -358,3 +358,18 @@ def test_culprit_strategy_unsorted_domains(oracle_built):
     rng = np.random.default_rng(5)
     desc.domains = [list(rng.permutation(np.asarray(d))) for d in desc.domains]
     _check_against_oracle(desc, oracle_built, iterations=400, walkers=6, seed=13, strategy=2)
+
+
+@pytest.mark.parametrize("strategy", [3, 4])
+@pytest.mark.parametrize("name", ["magic_square:5", "n_queens:8", "costas_lag:9", "knapsack:20x3", "mixed", "mixed_perm", "n_queens_offset:12",
+                                  "all_interval:10", "mixed_eq", "weighted_perm"])
+def test_hill_climbing_and_random_walk_trajectories_match_oracle(name, strategy, oracle_built):
+    """GHOST_STRATEGY_HILL_CLIMBING (3) / GHOST_STRATEGY_RANDOM_WALK (4), the reference's two landscape-analysis builds
+    (include/solver.hpp:502-515): every non-tabu variable a candidate, no projection; the random walk draws any candidate
+    value and always moves.  The CUDA walkers against the oracle, whose restatement tests/test_decision_replay.py replays
+    against the reference's own traces (for the random walk: the reference compiled with GHOST_RANDOM_WALK)."""
+    _check_against_oracle(model_by_name(name), oracle_built, iterations=400, walkers=8, seed=99, strategy=strategy)
+
+
+def test_random_walk_survives_epochs(oracle_built):
+    _check_against_oracle(model_by_name("n_queens:8"), oracle_built, iterations=400, walkers=6, seed=14, epochs=10, strategy=4)
