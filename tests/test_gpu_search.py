@@ -373,3 +373,11 @@ def test_hill_climbing_and_random_walk_trajectories_match_oracle(name, strategy,
 
 def test_random_walk_survives_epochs(oracle_built):
     _check_against_oracle(model_by_name("n_queens:8"), oracle_built, iterations=400, walkers=6, seed=14, epochs=10, strategy=4)
+
+
+def test_tabu_list_rebase_after_30000_moves(oracle_built):
+    """The 16-bit tabu entries are relative to a base that moves up every 30 000 moves without a reset (kernels.cuh).  Ordinary
+    searches reset long before; a random walk (always moves, never resets) on an unsatisfiable model crosses the threshold:
+    33 000 iterations with tabu marks alive at the crossing, trajectories equal to the oracle's."""
+    _check_against_oracle(model_by_name("n_queens:3"), oracle_built, iterations=33000, walkers=3, seed=8, strategy=4,
+                          tabu_time_selected=4)
