@@ -1,4 +1,4 @@
-"""Iterations/s and solved fraction of the three strategies (default, Antidote, Culprit) on one model: the CUDA walkers
+"""Iterations/s and solved fraction of the five strategies (default, Antidote, Culprit, hill climbing, random walk) on one model: the CUDA walkers
 (one B200) and, when oracle/_ref is built, the reference's own SearchUnit with the same strategy on one host core
 (oracle/ref_harness.cpp builds it; this script is a measurement aid, nothing of the product imports it).
 usage: strategy_throughput.py MODEL [seconds_per_run] [--out file.json]"""
@@ -15,7 +15,7 @@ seconds = float(sys.argv[2]) if len(sys.argv) > 2 and not sys.argv[2].startswith
 out_path = sys.argv[sys.argv.index("--out") + 1] if "--out" in sys.argv else None
 desc = model_by_name(name)
 rows = []
-for strategy, label in ((0, "adaptive_search"), (1, "antidote"), (2, "culprit")):
+for strategy, label in ((0, "adaptive_search"), (1, "antidote"), (2, "culprit"), (3, "hill_climbing"), (4, "random_walk")):
     row = {"model": name, "strategy": label}
     model = capi.Model(desc)
     try:
@@ -43,6 +43,8 @@ for strategy, label in ((0, "adaptive_search"), (1, "antidote"), (2, "culprit"))
     if os.path.exists(binding.REF_BENCH):
         with tempfile.TemporaryDirectory() as d:
             try:
+                if strategy == 4:
+                    raise RuntimeError("the reference's random walk is a compile-time build (oracle/_ref/ref_trace_rw, traced: not timed)")
                 rep = binding.run_ref_bench(desc, seconds * 1e6, False, 1, d, strategy=strategy)
                 it = rep.get("antidote_iterations", rep.get("iterations"))
                 row.update(ref_cpu_iterations_per_s=it / seconds if it else None,
