@@ -536,7 +536,7 @@ WalkerLayout LoweredModel::layout(int /*threads_per_walker*/, int nreset, int st
 	w.cs = take(8 * (m.C + 1));  // + the all-zero dummy constraint that pads the ELL rows
 	w.cs_em = take(8 * (m.C + 1));
 	// (at least 32 entries each, back to back: a one-warp walker keeps these summaries in registers while a launch runs
-	//  and the fp32 kernels use the 256 bytes as their cache of 16 Philox blocks, kernels.cuh)
+	//  and the one-warp kernels of the default strategy use the 256 bytes as their cache of 16 Philox blocks, kernels.cuh)
 	w.cand_key = take(4 * std::max(w.nchunks_v, 32));
 	w.cand_bits = take(4 * std::max(w.nchunks_v, 32));
 	w.cnt = take(2 * std::max(1, m.cnt_total));
