@@ -25,7 +25,7 @@ def test_host_api_cpu(tmp_path):
 
 
 def test_examples_compile(tmp_path):
-    for name in ("magic_square", "knapsack", "all_magic_squares", "n_queens"):
+    for name in ("magic_square", "knapsack", "all_magic_squares", "n_queens", "costas"):
         _compile(os.path.join(ROOT, "examples", name + ".cpp"), str(tmp_path / name))
 
 
@@ -66,6 +66,10 @@ def test_examples_run_on_gpu(tmp_path):
     exe = _compile(os.path.join(ROOT, "examples", "n_queens.cpp"), str(tmp_path / "queens"))   # AllDifferentOffset, V = 100, C = 3
     r = subprocess.run([exe, "100", "20"], capture_output=True, text=True, timeout=120)
     assert r.returncode == 0 and "Solution found, cost 0, verified" in r.stdout, r.stdout + r.stderr
+    exe = _compile(os.path.join(ROOT, "examples", "costas.cpp"), str(tmp_path / "costas"))   # AllDifferentLagDiff, V = 14, C = 13
+    for strategy in ("0", "1"):                                                               # default and Antidote heuristics
+        r = subprocess.run([exe, "14", "20", strategy], capture_output=True, text=True, timeout=120)
+        assert r.returncode == 0 and "Solution found, cost 0, verified" in r.stdout, (strategy, r.stdout + r.stderr)
     exe = _compile(os.path.join(ROOT, "examples", "knapsack.cpp"), str(tmp_path / "knap"))
     r = subprocess.run([exe, "100", "5", "1"], capture_output=True, text=True, timeout=120)
     assert r.returncode == 0 and "Feasible" in r.stdout, r.stdout + r.stderr
