@@ -171,7 +171,7 @@ def test_replay_antidote_strategy(name, timeout_us, ref_built, tmp_path):
 
 
 @pytest.mark.parametrize("name,timeout_us", [("magic_square:4", 60000), ("n_queens:8", 60000), ("knapsack:12x3", 30000), ("mixed", 40000),
-                                              ("costas_lag:8", 60000)])
+                                              ("costas_lag:8", 60000), ("n_queens_offset:8", 40000), ("mixed_eq", 40000), ("all_interval:8", 40000)])
 def test_replay_culprit_projection(name, timeout_us, ref_built, tmp_path):
     """GHOST_STRATEGY_CULPRIT: the default heuristics over the reference's Culprit Search error projection (the harness builds
     the SearchUnit with CulpritSearchErrorProjection).  The candidate list printed at every iteration is the arg-max set of the
@@ -187,7 +187,8 @@ def test_replay_culprit_projection(name, timeout_us, ref_built, tmp_path):
     assert seen["iterations"] >= 40
 
 
-@pytest.mark.parametrize("name,timeout_us", [("magic_square:4", 40000), ("n_queens:8", 30000), ("knapsack:12x3", 20000), ("mixed", 30000)])
+@pytest.mark.parametrize("name,timeout_us", [("magic_square:4", 40000), ("n_queens:8", 30000), ("knapsack:12x3", 20000), ("mixed", 30000),
+                                              ("costas_lag:8", 30000), ("n_queens_offset:8", 30000), ("mixed_eq", 30000)])
 def test_replay_hill_climbing(name, timeout_us, ref_built, tmp_path):
     """GHOST_STRATEGY_HILL_CLIMBING: what Solver::fast_search builds under the reference's GHOST_HILL_CLIMBING macro
     (include/solver.hpp:509-515) — every non-tabu variable a candidate (AllFreeVariableCandidatesHeuristic, constraint-free
@@ -197,7 +198,8 @@ def test_replay_hill_climbing(name, timeout_us, ref_built, tmp_path):
     assert seen["iterations"] >= 60
 
 
-@pytest.mark.parametrize("name,timeout_us", [("magic_square:4", 20000), ("n_queens:8", 20000), ("knapsack:12x3", 20000), ("costas_lag:8", 20000)])
+@pytest.mark.parametrize("name,timeout_us", [("magic_square:4", 20000), ("n_queens:8", 20000), ("knapsack:12x3", 20000), ("costas_lag:8", 20000),
+                                              ("n_queens_offset:8", 20000), ("mixed", 20000), ("mixed_eq", 20000), ("all_interval:8", 20000)])
 def test_replay_random_walk(name, timeout_us, ref_built, tmp_path):
     """GHOST_STRATEGY_RANDOM_WALK against oracle/_ref/ref_trace_rw, the reference compiled with GHOST_RANDOM_WALK: a value
     drawn uniformly among the candidates and the move made whatever its delta (include/search_unit.hpp:1007-1036).  Replayed:
